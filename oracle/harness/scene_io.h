@@ -1,0 +1,90 @@
+/* TEST INFRASTRUCTURE — reader for the little-endian scene interchange file the Python
+ * scene generators write (mitsuba-renderer_b200/scenefile.py documents the same layout).
+ * Used only by the oracle harness; the CUDA library takes plain arrays through its C ABI. */
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <stdexcept>
+
+namespace sio {
+
+enum MaterialType { MAT_LAMBERTIAN = 0, MAT_MICROFACET = 1, MAT_MIRROR = 2, MAT_ROUGHMETAL = 3, MAT_DIELECTRIC = 4 };
+
+struct Material { uint32_t type; float p[16]; };
+struct Emitter  { float intensity[3]; float samplingWeight; };
+struct Shape {
+	uint32_t nVert, nTri; int32_t matId, emitId; uint32_t hasNormals;
+	std::vector<float> pos, nrm; std::vector<uint32_t> tri;
+};
+
+struct Scene {
+	float cameraToWorld[16];
+	float fov, nearClip, farClip, apertureRadius, focusDepth;
+	uint32_t mapSmallerSide;
+	uint32_t width, height, cropX, cropY, cropW, cropH, filterType;
+	uint32_t spp, mode; int32_t maxDepth, rrDepth; uint32_t strictNormals, nLumSamples, nBsdfSamples;
+	std::vector<Material> materials;
+	std::vector<Emitter> emitters;
+	std::vector<Shape> shapes;
+};
+
+struct Reader {
+	FILE *f;
+	explicit Reader(const std::string &path) : f(fopen(path.c_str(), "rb")) {
+		if (!f) throw std::runtime_error("cannot open " + path);
+	}
+	~Reader() { if (f) fclose(f); }
+	void raw(void *dst, size_t n) { if (n && fread(dst, 1, n, f) != n) throw std::runtime_error("short read"); }
+	template <typename T> T get() { T v; raw(&v, sizeof(T)); return v; }
+};
+
+inline void load(const std::string &path, Scene &s) {
+	Reader r(path);
+	char magic[8]; r.raw(magic, 8);
+	if (memcmp(magic, "MTSB200", 8) != 0) throw std::runtime_error("bad magic in " + path);
+	if (r.get<uint32_t>() != 1) throw std::runtime_error("bad version in " + path);
+	r.raw(s.cameraToWorld, 64);
+	s.fov = r.get<float>(); s.nearClip = r.get<float>(); s.farClip = r.get<float>();
+	s.apertureRadius = r.get<float>(); s.focusDepth = r.get<float>();
+	s.mapSmallerSide = r.get<uint32_t>();
+	s.width = r.get<uint32_t>(); s.height = r.get<uint32_t>();
+	s.cropX = r.get<uint32_t>(); s.cropY = r.get<uint32_t>();
+	s.cropW = r.get<uint32_t>(); s.cropH = r.get<uint32_t>();
+	s.filterType = r.get<uint32_t>();
+	s.spp = r.get<uint32_t>(); s.mode = r.get<uint32_t>();
+	s.maxDepth = r.get<int32_t>(); s.rrDepth = r.get<int32_t>();
+	s.strictNormals = r.get<uint32_t>(); s.nLumSamples = r.get<uint32_t>(); s.nBsdfSamples = r.get<uint32_t>();
+	s.materials.resize(r.get<uint32_t>());
+	for (auto &m : s.materials) { m.type = r.get<uint32_t>(); r.raw(m.p, 64); }
+	s.emitters.resize(r.get<uint32_t>());
+	for (auto &e : s.emitters) { r.raw(e.intensity, 12); e.samplingWeight = r.get<float>(); }
+	s.shapes.resize(r.get<uint32_t>());
+	for (auto &sh : s.shapes) {
+		sh.nVert = r.get<uint32_t>(); sh.nTri = r.get<uint32_t>();
+		sh.matId = r.get<int32_t>(); sh.emitId = r.get<int32_t>();
+		sh.hasNormals = r.get<uint32_t>();
+		sh.pos.resize(3 * (size_t) sh.nVert); r.raw(sh.pos.data(), sh.pos.size() * 4);
+		if (sh.hasNormals) { sh.nrm.resize(3 * (size_t) sh.nVert); r.raw(sh.nrm.data(), sh.nrm.size() * 4); }
+		sh.tri.resize(3 * (size_t) sh.nTri); r.raw(sh.tri.data(), sh.tri.size() * 4);
+	}
+}
+
+inline std::vector<float> loadFloats(const std::string &path) {
+	Reader r(path);
+	fseek(r.f, 0, SEEK_END); long n = ftell(r.f); fseek(r.f, 0, SEEK_SET);
+	std::vector<float> v((size_t) n / 4);
+	r.raw(v.data(), v.size() * 4);
+	return v;
+}
+
+inline void save(const std::string &path, const void *data, size_t bytes) {
+	FILE *f = fopen(path.c_str(), "wb");
+	if (!f) throw std::runtime_error("cannot write " + path);
+	if (bytes && fwrite(data, 1, bytes, f) != bytes) { fclose(f); throw std::runtime_error("short write"); }
+	fclose(f);
+}
+
+} // namespace sio
