@@ -1,0 +1,222 @@
+/*
+ * mtsgpu.h — C ABI of libmtscuda.so, the CUDA (sm_100a) implementation of Mitsuba 0.2.1's
+ * Monte Carlo path-tracing hot path. This is the drop-in boundary: the only things that
+ * cross it are plain pointers, sizes and POD structs. The caller is the `gpupath`
+ * SampleIntegrator plugin (mitsuba-renderer_b200/plugin/gpupath.cpp) or any FFI binding
+ * (ctypes binding: mitsuba-renderer_b200/api.py).
+ *
+ * Citations are file:line under the reference tree (tomka/mitsuba-renderer).
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative mtsgpu_status on failure;
+ *     mtsgpu_last_error(ctx) returns a human-readable message for the last failure
+ *   - the caller owns every host buffer; the library copies during the call
+ *   - pointers named d_* are DEVICE pointers on the context's GPU; all others are host
+ *   - matrices are row-major float[16] acting on column vectors (core/transform.h:133-149)
+ *   - one host thread drives one context; `cancel` is the only cross-thread input
+ *   - there is no CPU fallback: without a usable CUDA device every call fails
+ */
+#ifndef MTSGPU_H
+#define MTSGPU_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MTSGPU_API __attribute__((visibility("default")))
+
+typedef struct mtsgpu_ctx mtsgpu_ctx;
+
+enum mtsgpu_status {
+	MTSGPU_OK = 0,
+	MTSGPU_ERR_CUDA = -1,       /* a CUDA runtime call failed */
+	MTSGPU_ERR_ARG = -2,        /* invalid argument / call order */
+	MTSGPU_ERR_UNSUPPORTED = -3,/* scene feature outside the hot path (non-mesh shape, texture, medium ...) */
+	MTSGPU_ERR_CANCELLED = -4,  /* *cancel became non-zero during mtsgpu_render */
+	MTSGPU_ERR_LIMIT = -5       /* a documented size limit was exceeded */
+};
+
+/* BSDF models (SURVEY.md "things a fresh reader must know" #3 maps them to north_star names) */
+enum mtsgpu_bsdf_type {
+	MTSGPU_BSDF_LAMBERTIAN = 0, /* src/bsdfs/lambertian.cpp:66   p[0..2] reflectance */
+	MTSGPU_BSDF_MICROFACET = 1, /* src/bsdfs/microfacet.cpp:35   p[0..2] diffuseReflectance, p[3..5] specularReflectance,
+	                               p[6] diffuseAmount, p[7] specularAmount, p[8] alphaB, p[9] intIOR, p[10] extIOR */
+	MTSGPU_BSDF_MIRROR = 2,     /* src/bsdfs/mirror.cpp:26       p[0..2] specularReflectance */
+	MTSGPU_BSDF_ROUGHMETAL = 3, /* src/bsdfs/roughmetal.cpp:33   p[0..2] specularReflectance, p[3] alphaB, p[4..6] ior, p[7..9] k */
+	MTSGPU_BSDF_DIELECTRIC = 4  /* src/bsdfs/dielectric.cpp:47   p[0..2] specularReflectance, p[3..5] specularTransmittance,
+	                               p[6] intIOR, p[7] extIOR */
+};
+
+typedef struct mtsgpu_material {
+	uint32_t type;   /* mtsgpu_bsdf_type */
+	float p[16];
+} mtsgpu_material;
+
+/* Area luminaire bound to a mesh (src/luminaires/area.cpp:35-83). Emitters must be listed in the
+ * order Scene::addShape meets their shapes (src/librender/scene.cpp:656-664), which is the order
+ * of Scene::getLuminaires() and therefore of the luminaire CDF (scene.cpp:320-330). */
+typedef struct mtsgpu_emitter {
+	float intensity[3];
+	float samplingWeight; /* Luminaire::getSamplingWeight(), luminaire.h:180; weight in the luminaire CDF */
+} mtsgpu_emitter;
+
+enum mtsgpu_mode { MTSGPU_MODE_PATH = 0, MTSGPU_MODE_DIRECT = 1 };
+
+/* Integrator + sampler properties (src/librender/integrator.cpp:270-295, src/integrators/direct/direct.cpp:34-36,
+ * src/samplers/independent.cpp:34) and the sample range this context renders. */
+typedef struct mtsgpu_render_params {
+	int32_t mode;             /* mtsgpu_mode: MIPathTracer::Li (path.cpp:47-216) or MIDirectIntegrator::Li (direct.cpp:63-203) */
+	int32_t maxDepth;         /* -1 = unbounded */
+	int32_t rrDepth;          /* Russian roulette from this depth (default 10) */
+	int32_t strictNormals;
+	int32_t luminaireSamples; /* direct only */
+	int32_t bsdfSamples;      /* direct only */
+	uint32_t sppTotal;        /* sampler sampleCount for the whole image */
+	uint32_t sppBegin;        /* this call renders samples [sppBegin, sppEnd) of every pixel: */
+	uint32_t sppEnd;          /*   the multi-GPU shard; 0..sppTotal on one GPU */
+	uint32_t seed;            /* counter-based RNG key; streams are keyed by (pixel, global sample index) */
+	uint32_t importanceSampleLuminaires; /* Scene property, scene.cpp:51; default 1 */
+	uint32_t reserved;
+} mtsgpu_render_params;
+
+typedef struct mtsgpu_stats {
+	uint64_t cameraRays;      /* "Camera ray generations" (perspective.cpp:24) */
+	uint64_t normalRays;      /* closest-hit queries, "Normal rays traced" (skdtree.cpp:40) */
+	uint64_t shadowRays;      /* any-hit queries,   "Shadow rays traced" (skdtree.cpp:41) */
+	uint64_t samples;         /* completed pixel samples */
+	uint64_t kernelLaunches;  /* kernels launched by this call */
+	double   traceClosestMs;  /* device time spent in the closest-hit kernel (CUDA events) */
+	double   traceAnyMs;      /* ... in the any-hit kernel */
+	double   shadeMs;         /* ... in ray generation + shading + splatting */
+	double   totalMs;         /* whole call, device time */
+} mtsgpu_stats;
+
+/* Closest-hit record returned by mtsgpu_trace; mirrors the reference's IntersectionCache
+ * (include/mitsuba/render/skdtree.h:232-236) plus t. Miss: t = +inf, shape = prim = 0xFFFFFFFF. */
+typedef struct mtsgpu_hit {
+	float t, u, v;
+	uint32_t shape, prim;
+} mtsgpu_hit;
+
+enum mtsgpu_trace_mode {
+	MTSGPU_TRACE_CLOSEST = 0, /* ShapeKDTree::rayIntersect(const Ray&, Intersection&), skdtree.cpp:108-132 */
+	MTSGPU_TRACE_ANY = 1      /* ShapeKDTree::rayIntersect(const Ray&), skdtree.cpp:180-199 (shadow rays) */
+};
+
+/* ---- life cycle ---------------------------------------------------------------------------- */
+
+/* Create a context on CUDA device `device`. Replaces nothing in the reference (it has no device). */
+MTSGPU_API int mtsgpu_create(int device, mtsgpu_ctx **out);
+MTSGPU_API void mtsgpu_destroy(mtsgpu_ctx *ctx);
+MTSGPU_API const char *mtsgpu_last_error(const mtsgpu_ctx *ctx);
+MTSGPU_API const char *mtsgpu_version(void);
+
+/* ---- scene upload: what the plugin reads through Scene's public getters ------ */
+
+/* BSDF parameter blocks, decoded by the plugin from BSDF::serialize (e.g. roughmetal.cpp:169-176). */
+MTSGPU_API int mtsgpu_upload_materials(mtsgpu_ctx *ctx, const mtsgpu_material *materials, int count);
+
+/* Scene::getLuminaires() (scene.h) restricted to AreaLuminaire. */
+MTSGPU_API int mtsgpu_upload_emitters(mtsgpu_ctx *ctx, const mtsgpu_emitter *emitters, int count);
+
+/* One TriMesh (include/mitsuba/render/trimesh.h:100-133) at kd-tree shape index `shapeIndex`
+ * (ShapeKDTree::addShape order, skdtree.cpp:45-60). Shapes must be uploaded in index order 0,1,2...
+ * positions: 3*nVert floats; normals: 3*nVert floats or NULL (=> shading frame = geometric frame,
+ * skdtree.h:405-408); texcoords are accepted and ignored (constant textures only).
+ * materialId < 0: shape has no BSDF => not an occluder (shape.h:361) and paths end on it (path.cpp:70-77).
+ * emitterId  < 0: not a luminaire. */
+MTSGPU_API int mtsgpu_upload_mesh(mtsgpu_ctx *ctx, int shapeIndex,
+	const float *positions, const float *normals, const float *texcoords, uint32_t nVert,
+	const uint32_t *triangles, uint32_t nTri, int materialId, int emitterId);
+
+/* PerspectiveCameraImpl (src/cameras/perspective.cpp:43-112): m_rasterToCamera, m_cameraToWorld,
+ * clip planes, thin-lens parameters, shutter. */
+MTSGPU_API int mtsgpu_set_camera(mtsgpu_ctx *ctx, const float rasterToCamera[16], const float cameraToWorld[16],
+	float nearClip, float farClip, float apertureRadius, float focusDepth, float shutterOpen, float shutterOpenTime);
+
+/* Film geometry (src/librender/film.cpp:24-51) and the film's TabulatedFilter
+ * (include/mitsuba/render/rfilter.h:65-118): the 16x16 table m_values, and the filter half-size. */
+MTSGPU_API int mtsgpu_set_film(mtsgpu_ctx *ctx, int width, int height, int cropX, int cropY, int cropW, int cropH,
+	const float filterTable[256], float filterSizeX, float filterSizeY);
+
+/* Replaces ShapeKDTree::build (skdtree.cpp:62-106): TriAccel precompute (triaccel.h:63-96) and a
+ * GPU-built wide BVH instead of the SAH kd-tree (gkdtree.h:913-1214). Also builds the luminaire and
+ * per-mesh area CDFs (scene.cpp:320-330, trimesh.cpp:266-283). */
+MTSGPU_API int mtsgpu_build_accel(mtsgpu_ctx *ctx);
+
+/* ---- the hot path ---------------------------------------------------------------------------- */
+
+/* Replaces SampleIntegrator::render -> BlockedRenderProcess -> renderBlock -> Li -> putSample ->
+ * Film::putImageBlock (integrator.cpp:87-268, renderproc.cpp:106-160, imageblock.h:80-138).
+ * outFilm: HOST buffer of cropW*cropH*5 floats, per pixel {sum spec R,G,B, sum alpha, sum weight}
+ * (the un-normalised accumulators of exrfilm.cpp:37-44), overwritten.
+ * cancel may be NULL; polled between wavefront iterations (Integrator::cancel, integrator.cpp:82-85). */
+MTSGPU_API int mtsgpu_render(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, volatile const int *cancel,
+	float *outFilm, mtsgpu_stats *stats);
+
+/* Same, but the film stays on the device: d_outFilm is a DEVICE buffer (cropW*cropH*5 floats) that the
+ * caller then reduces across GPUs (one ncclReduce; replaces the mutex-guarded merge of
+ * BlockedRenderProcess::processResult, renderproc.cpp:123-130). */
+MTSGPU_API int mtsgpu_render_device(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, volatile const int *cancel,
+	float *d_outFilm, mtsgpu_stats *stats);
+
+/* Batch ray queries against the scene; rays are rows of 8 floats {o.xyz, mint, d.xyz, maxt}
+ * (include/mitsuba/core/ray.h:34-40 without dRcp/time). mode CLOSEST writes n mtsgpu_hit records,
+ * mode ANY writes n uint32 (1 = occluded). Host buffers; copies are part of the call. */
+MTSGPU_API int mtsgpu_trace(mtsgpu_ctx *ctx, const float *rays, size_t n, int mode, void *out);
+
+/* Device-resident variant: d_rays / d_out are DEVICE pointers; runs on the context's stream and
+ * returns after the kernel has completed. elapsedMs (may be NULL) receives the kernel's device time. */
+MTSGPU_API int mtsgpu_trace_device(mtsgpu_ctx *ctx, const float *d_rays, size_t n, int mode, void *d_out,
+	float *elapsedMs);
+
+/* ---- per-function test hooks (parity tests call the device functions through these) -------- */
+
+/* BSDF::f / pdf / sample (bsdf.h:246-292; bsdf.cpp:37-48). queries: rows of 9 floats
+ * {materialId, wi.xyz, wo.xyz, sample.x, sample.y}; out: rows of 16 floats
+ * {f.rgb, pdf | sampled wo.xyz, sampled f.rgb, sampled pdf, sampledType | 2-arg sample value rgb, 0}. */
+MTSGPU_API int mtsgpu_bsdf_eval(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out);
+
+/* Scene::sampleLuminaire without the visibility test + Scene::pdfLuminaire (scene.cpp:381-415).
+ * queries: rows {p.xyz, sample.x, sample.y}; out rows of 16 floats
+ * {sRec.p, sRec.n, d, pdf, value.rgb, luminaireIndex (-1 = failed), pdfLuminaire, 0}. */
+MTSGPU_API int mtsgpu_emitter_sample(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out);
+
+/* PerspectiveCameraImpl::generateRay (perspective.cpp:77-112). samples: rows {x, y, lens.x, lens.y};
+ * out rows of 8 floats {o.xyz, mint, d.xyz, maxt}. */
+MTSGPU_API int mtsgpu_camera_rays(mtsgpu_ctx *ctx, const float *samples, size_t n, float *out);
+
+/* ImageBlock::putSample + Film::putImageBlock (imageblock.h:80-138, exrfilm.cpp:130-156).
+ * samples: rows {x, y, r, g, b, alpha}; outFilm as in mtsgpu_render. */
+MTSGPU_API int mtsgpu_film_splat(mtsgpu_ctx *ctx, const float *samples, size_t n, float *outFilm);
+
+/* Closest-hit query that also fills the Intersection record (fillIntersectionRecord<true>,
+ * skdtree.h:352-432): out rows of 12 floats {p, geoFrame.n, shFrame.n, wi}; zeros on a miss. */
+MTSGPU_API int mtsgpu_intersect_full(mtsgpu_ctx *ctx, const float *rays, size_t n, mtsgpu_hit *hits, float *out);
+
+/* The precomputed TriAccel records (48 B each, triaccel.h:34-46) in kd-tree primitive order
+ * (shape-major), preceded by nothing; aabb6 receives the enlarged scene box (gkdtree.h:1172-1176). */
+MTSGPU_API int mtsgpu_get_triaccel(mtsgpu_ctx *ctx, void *outRecords, size_t maxRecords, float aabb6[6]);
+
+/* Acceleration-structure figures for the roofline accounting. */
+typedef struct mtsgpu_accel_info {
+	uint64_t triangles, nodes, nodeBytes, triBytes;
+	double buildMs;
+} mtsgpu_accel_info;
+MTSGPU_API int mtsgpu_accel_info_get(mtsgpu_ctx *ctx, mtsgpu_accel_info *info);
+
+/* Mean per-ray traversal work of the last mtsgpu_trace* call made with counters enabled
+ * (mtsgpu_set_counters(ctx, 1)); counters are off by default and cost nothing when off. */
+typedef struct mtsgpu_trace_counters {
+	uint64_t rays, nodeVisits, triTests;
+} mtsgpu_trace_counters;
+MTSGPU_API int mtsgpu_set_counters(mtsgpu_ctx *ctx, int enabled);
+MTSGPU_API int mtsgpu_get_counters(mtsgpu_ctx *ctx, mtsgpu_trace_counters *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MTSGPU_H */

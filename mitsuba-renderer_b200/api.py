@@ -1,0 +1,309 @@
+"""ctypes binding of the C ABI in include/mtsgpu.h (libmtscuda.so).
+
+This is the Python host side of the drop-in boundary: the same calls, in the same order, that
+the C++ `gpupath` plugin makes from `Integrator::render`. There is no CPU
+fallback: if the shared library is missing or no CUDA device is usable, construction raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+from .scenefile import SceneDesc, raster_to_camera, MODE_PATH, MODE_DIRECT, FILTER_BOX, FILTER_GAUSSIAN
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmtscuda.so")
+
+TRACE_CLOSEST, TRACE_ANY = 0, 1
+
+# every symbol include/mtsgpu.h declares (checked by the CPU test-suite against the header)
+EXPORTED_SYMBOLS = [
+    "mtsgpu_create", "mtsgpu_destroy", "mtsgpu_last_error", "mtsgpu_version", "mtsgpu_upload_materials",
+    "mtsgpu_upload_emitters", "mtsgpu_upload_mesh", "mtsgpu_set_camera", "mtsgpu_set_film", "mtsgpu_build_accel",
+    "mtsgpu_render", "mtsgpu_render_device", "mtsgpu_trace", "mtsgpu_trace_device", "mtsgpu_bsdf_eval",
+    "mtsgpu_emitter_sample", "mtsgpu_camera_rays", "mtsgpu_film_splat", "mtsgpu_intersect_full",
+    "mtsgpu_get_triaccel", "mtsgpu_accel_info_get", "mtsgpu_set_counters", "mtsgpu_get_counters",
+]
+
+
+class MtsGpuError(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__(f"mtsgpu error {code}: {message}")
+        self.code = code
+
+
+class Material(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("p", C.c_float * 16)]
+
+
+class Emitter(C.Structure):
+    _fields_ = [("intensity", C.c_float * 3), ("samplingWeight", C.c_float)]
+
+
+class RenderParams(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("maxDepth", C.c_int32), ("rrDepth", C.c_int32), ("strictNormals", C.c_int32),
+                ("luminaireSamples", C.c_int32), ("bsdfSamples", C.c_int32), ("sppTotal", C.c_uint32),
+                ("sppBegin", C.c_uint32), ("sppEnd", C.c_uint32), ("seed", C.c_uint32),
+                ("importanceSampleLuminaires", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("cameraRays", C.c_uint64), ("normalRays", C.c_uint64), ("shadowRays", C.c_uint64),
+                ("samples", C.c_uint64), ("kernelLaunches", C.c_uint64), ("traceClosestMs", C.c_double),
+                ("traceAnyMs", C.c_double), ("shadeMs", C.c_double), ("totalMs", C.c_double)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class AccelInfo(C.Structure):
+    _fields_ = [("triangles", C.c_uint64), ("nodes", C.c_uint64), ("nodeBytes", C.c_uint64),
+                ("triBytes", C.c_uint64), ("buildMs", C.c_double)]
+
+
+class TraceCounters(C.Structure):
+    _fields_ = [("rays", C.c_uint64), ("nodeVisits", C.c_uint64), ("triTests", C.c_uint64)]
+
+
+HIT_DTYPE = np.dtype([("t", np.float32), ("u", np.float32), ("v", np.float32), ("shape", np.uint32), ("prim", np.uint32)])
+TRIACCEL_DTYPE = np.dtype([("k", np.uint32), ("n_u", np.float32), ("n_v", np.float32), ("n_d", np.float32),
+                           ("a_u", np.float32), ("a_v", np.float32), ("b_nu", np.float32), ("b_nv", np.float32),
+                           ("c_nu", np.float32), ("c_nv", np.float32), ("shapeIndex", np.uint32), ("primIndex", np.uint32)])
+
+_lib = None
+
+
+def load_library(path: Optional[str] = None):
+    """dlopen libmtscuda.so and declare the prototypes. Raises if the library is not built."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise MtsGpuError(-1, f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(there is no CPU fallback)")
+    lib = C.CDLL(path)
+    vp, fp, u32p = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint32)
+    lib.mtsgpu_create.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.mtsgpu_destroy.argtypes = [vp]; lib.mtsgpu_destroy.restype = None
+    lib.mtsgpu_last_error.argtypes = [vp]; lib.mtsgpu_last_error.restype = C.c_char_p
+    lib.mtsgpu_version.restype = C.c_char_p
+    lib.mtsgpu_upload_materials.argtypes = [vp, C.POINTER(Material), C.c_int]
+    lib.mtsgpu_upload_emitters.argtypes = [vp, C.POINTER(Emitter), C.c_int]
+    lib.mtsgpu_upload_mesh.argtypes = [vp, C.c_int, vp, vp, vp, C.c_uint32, vp, C.c_uint32, C.c_int, C.c_int]
+    lib.mtsgpu_set_camera.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float]
+    lib.mtsgpu_set_film.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_float, C.c_float]
+    lib.mtsgpu_build_accel.argtypes = [vp]
+    lib.mtsgpu_render.argtypes = [vp, C.POINTER(RenderParams), vp, vp, C.POINTER(Stats)]
+    lib.mtsgpu_render_device.argtypes = [vp, C.POINTER(RenderParams), vp, vp, C.POINTER(Stats)]
+    lib.mtsgpu_trace.argtypes = [vp, vp, C.c_size_t, C.c_int, vp]
+    lib.mtsgpu_trace_device.argtypes = [vp, vp, C.c_size_t, C.c_int, vp, C.POINTER(C.c_float)]
+    for name in ("mtsgpu_bsdf_eval", "mtsgpu_emitter_sample", "mtsgpu_camera_rays", "mtsgpu_film_splat"):
+        getattr(lib, name).argtypes = [vp, vp, C.c_size_t, vp]
+    lib.mtsgpu_intersect_full.argtypes = [vp, vp, C.c_size_t, vp, vp]
+    lib.mtsgpu_get_triaccel.argtypes = [vp, vp, C.c_size_t, vp]
+    lib.mtsgpu_accel_info_get.argtypes = [vp, C.POINTER(AccelInfo)]
+    lib.mtsgpu_set_counters.argtypes = [vp, C.c_int]
+    lib.mtsgpu_get_counters.argtypes = [vp, C.POINTER(TraceCounters)]
+    for name in EXPORTED_SYMBOLS:
+        fn = getattr(lib, name)
+        if name not in ("mtsgpu_destroy", "mtsgpu_last_error", "mtsgpu_version"):
+            fn.restype = C.c_int
+    if path == LIB_PATH:
+        _lib = lib
+    return lib
+
+
+def gaussian_table():
+    """TabulatedFilter of the gaussian rfilter (src/rfilters/gaussian.cpp:30-43: halfSize 2, sigma 0.5;
+    tabulated by src/librender/rfilter.cpp:40-69), fp32 arithmetic in the reference's order."""
+    f32 = np.float32
+    size = f32(2.0)
+    sigma = f32(0.5)
+    alpha = f32(-1.0) / (f32(2.0) * sigma * sigma)
+    const = f32(np.exp(alpha * size * size, dtype=np.float32))
+
+    def ev(x, y):
+        return max(f32(0), f32(np.exp(alpha * x * x, dtype=np.float32)) - const) * \
+               max(f32(0), f32(np.exp(alpha * y * y, dtype=np.float32)) - const)
+    vals = np.zeros((16, 16), np.float32)
+    total = f32(0)
+    for y in range(16):
+        ypos = (f32(y) + f32(0.5)) / f32(15) * size
+        for x in range(16):
+            if x != 15 and y != 15:
+                vals[y, x] = ev((f32(x) + f32(0.5)) / f32(15) * size, ypos)
+            total = f32(total + vals[y, x])
+    total = f32(total * (f32(4) * size * size / f32(15 * 15)))
+    return (vals / total).astype(np.float32), 2.0
+
+
+def box_table():
+    """TabulatedFilter of the box rfilter (src/rfilters/box.cpp:26-47: size 0.5, value 1)."""
+    vals = np.zeros((16, 16), np.float32)
+    vals[:15, :15] = 1.0
+    total = np.float32(225.0) * np.float32(4 * 0.5 * 0.5 / 225.0)
+    return (vals / total).astype(np.float32), 0.5
+
+
+def filter_table(filter_type):
+    return box_table() if filter_type == FILTER_BOX else gaussian_table()
+
+
+class Context:
+    """One GPU context (`mtsgpu_ctx`). Mirrors the call sequence of the plugin's render()."""
+
+    def __init__(self, device: int = 0, lib_path: Optional[str] = None):
+        self.lib = load_library(lib_path)
+        h = C.c_void_p()
+        rc = self.lib.mtsgpu_create(device, C.byref(h))
+        if rc != 0:
+            raise MtsGpuError(rc, self.lib.mtsgpu_last_error(None).decode())
+        self.h = h
+        self.device = device
+        self.film_shape = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.mtsgpu_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise MtsGpuError(rc, self.lib.mtsgpu_last_error(self.h).decode())
+
+    @staticmethod
+    def _ptr(a):
+        return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+    # ---- scene upload -----------------------------------------------------------------------
+    def upload_scene(self, scene: SceneDesc, build: bool = True):
+        mats = (Material * max(1, len(scene.materials)))()
+        for i, m in enumerate(scene.materials):
+            mats[i].type = m.type
+            mats[i].p[:] = [float(v) for v in m.p]
+        self._check(self.lib.mtsgpu_upload_materials(self.h, mats, len(scene.materials)))
+        ems = (Emitter * max(1, len(scene.emitters)))()
+        for i, e in enumerate(scene.emitters):
+            ems[i].intensity[:] = [float(v) for v in e.intensity]
+            ems[i].samplingWeight = e.sampling_weight
+        self._check(self.lib.mtsgpu_upload_emitters(self.h, ems, len(scene.emitters)))
+        for i, s in enumerate(scene.shapes):
+            pos = np.ascontiguousarray(s.positions, np.float32)
+            nrm = None if s.normals is None else np.ascontiguousarray(s.normals, np.float32)
+            tri = np.ascontiguousarray(s.triangles, np.uint32)
+            self._check(self.lib.mtsgpu_upload_mesh(self.h, i, self._ptr(pos), self._ptr(nrm), None, len(pos),
+                                                    self._ptr(tri), len(tri), s.material, s.emitter))
+        self.set_camera(scene)
+        self.set_film(scene)
+        if build:
+            self.build_accel()
+
+    def set_camera(self, scene: SceneDesc):
+        r2c = np.ascontiguousarray(raster_to_camera(scene), np.float32)
+        c2w = np.ascontiguousarray(scene.camera_to_world, np.float32)
+        self._check(self.lib.mtsgpu_set_camera(self.h, self._ptr(r2c), self._ptr(c2w), scene.near_clip, scene.far_clip,
+                                               scene.aperture_radius, scene.focus_depth, 0.0, 0.0))
+
+    def set_film(self, scene: SceneDesc, table=None, size=None):
+        cx, cy, cw, ch = scene.crop_rect
+        if table is None:
+            table, size = filter_table(scene.filter_type)
+        table = np.ascontiguousarray(table, np.float32)
+        self._check(self.lib.mtsgpu_set_film(self.h, scene.width, scene.height, cx, cy, cw, ch, self._ptr(table), size, size))
+        self.film_shape = (ch, cw, 5)
+
+    def build_accel(self):
+        self._check(self.lib.mtsgpu_build_accel(self.h))
+
+    def accel_info(self):
+        info = AccelInfo()
+        self._check(self.lib.mtsgpu_accel_info_get(self.h, C.byref(info)))
+        return {n: getattr(info, n) for n, _ in info._fields_}
+
+    # ---- hot path ---------------------------------------------------------------------------
+    @staticmethod
+    def params_from_scene(scene: SceneDesc, spp_begin=0, spp_end=None, seed=0) -> RenderParams:
+        p = RenderParams()
+        p.mode = scene.mode; p.maxDepth = scene.max_depth; p.rrDepth = scene.rr_depth
+        p.strictNormals = int(scene.strict_normals)
+        p.luminaireSamples = scene.luminaire_samples; p.bsdfSamples = scene.bsdf_samples
+        p.sppTotal = scene.spp; p.sppBegin = spp_begin; p.sppEnd = scene.spp if spp_end is None else spp_end
+        p.seed = seed; p.importanceSampleLuminaires = 1
+        return p
+
+    def render(self, params: RenderParams):
+        """mtsgpu_render: returns (film[cropH, cropW, 5] host array, stats dict)."""
+        out = np.empty(self.film_shape, np.float32)
+        st = Stats()
+        self._check(self.lib.mtsgpu_render(self.h, C.byref(params), None, self._ptr(out), C.byref(st)))
+        return out, st.as_dict()
+
+    def render_device(self, params: RenderParams, d_film_ptr: int):
+        st = Stats()
+        self._check(self.lib.mtsgpu_render_device(self.h, C.byref(params), None, C.c_void_p(d_film_ptr), C.byref(st)))
+        return st.as_dict()
+
+    def trace(self, rays: np.ndarray, mode: int = TRACE_CLOSEST):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        n = len(rays)
+        out = np.empty(n, HIT_DTYPE if mode == TRACE_CLOSEST else np.uint32)
+        self._check(self.lib.mtsgpu_trace(self.h, self._ptr(rays), n, mode, self._ptr(out)))
+        return out
+
+    def trace_device(self, d_rays_ptr: int, n: int, mode: int, d_out_ptr: int) -> float:
+        ms = C.c_float(0)
+        self._check(self.lib.mtsgpu_trace_device(self.h, C.c_void_p(d_rays_ptr), n, mode, C.c_void_p(d_out_ptr), C.byref(ms)))
+        return ms.value
+
+    def set_counters(self, enabled: bool):
+        self._check(self.lib.mtsgpu_set_counters(self.h, int(enabled)))
+
+    def counters(self):
+        c = TraceCounters()
+        self._check(self.lib.mtsgpu_get_counters(self.h, C.byref(c)))
+        return {n: getattr(c, n) for n, _ in c._fields_}
+
+    # ---- test hooks -------------------------------------------------------------------------
+    def _hook(self, fn, q, cols_in, cols_out):
+        q = np.ascontiguousarray(q, np.float32).reshape(-1, cols_in)
+        out = np.zeros((len(q), cols_out), np.float32)
+        self._check(fn(self.h, self._ptr(q), len(q), self._ptr(out)))
+        return out
+
+    def bsdf_eval(self, queries):
+        return self._hook(self.lib.mtsgpu_bsdf_eval, queries, 9, 16)
+
+    def emitter_sample(self, queries):
+        return self._hook(self.lib.mtsgpu_emitter_sample, queries, 5, 16)
+
+    def camera_rays(self, samples):
+        return self._hook(self.lib.mtsgpu_camera_rays, samples, 4, 8)
+
+    def film_splat(self, samples):
+        q = np.ascontiguousarray(samples, np.float32).reshape(-1, 6)
+        out = np.zeros(self.film_shape, np.float32)
+        self._check(self.lib.mtsgpu_film_splat(self.h, self._ptr(q), len(q), self._ptr(out)))
+        return out
+
+    def intersect_full(self, rays):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        hits = np.empty(len(rays), HIT_DTYPE)
+        out = np.zeros((len(rays), 12), np.float32)
+        self._check(self.lib.mtsgpu_intersect_full(self.h, self._ptr(rays), len(rays), self._ptr(hits), self._ptr(out)))
+        return hits, out
+
+    def triaccel(self, n):
+        rec = np.empty(n, TRIACCEL_DTYPE)
+        box = np.zeros(6, np.float32)
+        self._check(self.lib.mtsgpu_get_triaccel(self.h, self._ptr(rec), n, self._ptr(box)))
+        return rec, box

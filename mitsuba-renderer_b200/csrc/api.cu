@@ -1,0 +1,225 @@
+// C ABI entry points of libmtscuda.so (declared in include/mtsgpu.h).
+#include "context.h"
+#include <cstring>
+#include <cmath>
+
+int setError(mtsgpu_ctx *ctx, int code, const char *fmt, ...) {
+	char buf[1024];
+	va_list ap; va_start(ap, fmt);
+	vsnprintf(buf, sizeof(buf), fmt, ap);
+	va_end(ap);
+	if (ctx) ctx->error = buf;
+	return code;
+}
+
+static thread_local std::string g_createError;
+
+extern "C" {
+
+const char *mtsgpu_version(void) { return "mtsgpu 0.1 (sm_100a)"; }
+
+int mtsgpu_create(int device, mtsgpu_ctx **out) {
+	if (!out) return MTSGPU_ERR_ARG;
+	*out = nullptr;
+	int count = 0;
+	cudaError_t e = cudaGetDeviceCount(&count);
+	if (e != cudaSuccess || count == 0) {
+		g_createError = std::string("no usable CUDA device: ") + cudaGetErrorString(e);
+		return MTSGPU_ERR_CUDA;      // no CPU fallback by design
+	}
+	if (device < 0 || device >= count) { g_createError = "device index out of range"; return MTSGPU_ERR_ARG; }
+	if ((e = cudaSetDevice(device)) != cudaSuccess) { g_createError = cudaGetErrorString(e); return MTSGPU_ERR_CUDA; }
+	mtsgpu_ctx *ctx = new mtsgpu_ctx();
+	ctx->device = device;
+	memset(&ctx->scene, 0, sizeof(ctx->scene));
+	if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+		g_createError = cudaGetErrorString(e); delete ctx; return MTSGPU_ERR_CUDA;
+	}
+	for (int i = 0; i < 8; ++i) cudaEventCreate(&ctx->ev[i]);
+	*out = ctx;
+	return MTSGPU_OK;
+}
+
+void mtsgpu_destroy(mtsgpu_ctx *ctx) {
+	if (!ctx) return;
+	cudaSetDevice(ctx->device);
+	cudaStreamSynchronize(ctx->stream);
+	for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+	cudaStreamDestroy(ctx->stream);
+	delete ctx;
+}
+
+const char *mtsgpu_last_error(const mtsgpu_ctx *ctx) {
+	return ctx ? ctx->error.c_str() : g_createError.c_str();
+}
+
+#define ENTER(ctx) do { if (!(ctx)) return MTSGPU_ERR_ARG; cudaError_t _e = cudaSetDevice((ctx)->device); \
+	if (_e != cudaSuccess) return setError((ctx), MTSGPU_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(_e)); } while (0)
+
+int mtsgpu_upload_materials(mtsgpu_ctx *ctx, const mtsgpu_material *materials, int count) {
+	ENTER(ctx);
+	REQUIRE(ctx, count >= 0 && (count == 0 || materials), MTSGPU_ERR_ARG, "upload_materials: bad arguments");
+	for (int i = 0; i < count; ++i)
+		REQUIRE(ctx, materials[i].type <= MTSGPU_BSDF_DIELECTRIC, MTSGPU_ERR_UNSUPPORTED, "material %d: unsupported BSDF type %u", i, materials[i].type);
+	ctx->materials.assign(materials, materials + count);
+	ctx->built = false;
+	return MTSGPU_OK;
+}
+
+int mtsgpu_upload_emitters(mtsgpu_ctx *ctx, const mtsgpu_emitter *emitters, int count) {
+	ENTER(ctx);
+	REQUIRE(ctx, count >= 0 && (count == 0 || emitters), MTSGPU_ERR_ARG, "upload_emitters: bad arguments");
+	ctx->emitters.assign(emitters, emitters + count);
+	ctx->built = false;
+	return MTSGPU_OK;
+}
+
+int mtsgpu_upload_mesh(mtsgpu_ctx *ctx, int shapeIndex, const float *positions, const float *normals, const float *texcoords,
+		uint32_t nVert, const uint32_t *triangles, uint32_t nTri, int materialId, int emitterId) {
+	ENTER(ctx);
+	(void) texcoords;
+	REQUIRE(ctx, positions && triangles && nVert > 0 && nTri > 0, MTSGPU_ERR_ARG, "upload_mesh: empty mesh (TriMesh::configure rejects these too)");
+	REQUIRE(ctx, shapeIndex >= 0 && (size_t) shapeIndex <= ctx->meshes.size(), MTSGPU_ERR_ARG,
+		"upload_mesh: shapes must be uploaded in kd-tree order (got %d, expected <= %zu)", shapeIndex, ctx->meshes.size());
+	if ((size_t) shapeIndex < ctx->meshes.size()) ctx->meshes.resize(shapeIndex);   // re-upload from this shape on
+	HostMesh m;
+	m.nVert = nVert; m.nTri = nTri; m.materialId = materialId; m.emitterId = emitterId; m.hasNormals = normals != nullptr;
+	m.pos.assign(positions, positions + 3 * (size_t) nVert);
+	if (normals) m.nrm.assign(normals, normals + 3 * (size_t) nVert);
+	m.tri.assign(triangles, triangles + 3 * (size_t) nTri);
+	ctx->meshes.push_back(std::move(m));
+	ctx->built = false;
+	return MTSGPU_OK;
+}
+
+int mtsgpu_set_camera(mtsgpu_ctx *ctx, const float rasterToCamera[16], const float cameraToWorld[16], float nearClip, float farClip,
+		float apertureRadius, float focusDepth, float shutterOpen, float shutterOpenTime) {
+	ENTER(ctx);
+	REQUIRE(ctx, rasterToCamera && cameraToWorld, MTSGPU_ERR_ARG, "set_camera: null matrix");
+	memcpy(ctx->camera.rasterToCamera, rasterToCamera, 64);
+	memcpy(ctx->camera.cameraToWorld, cameraToWorld, 64);
+	ctx->camera.nearClip = nearClip; ctx->camera.farClip = farClip;
+	ctx->camera.apertureRadius = apertureRadius; ctx->camera.focusDepth = focusDepth;
+	ctx->camera.shutterOpen = shutterOpen; ctx->camera.shutterOpenTime = shutterOpenTime;
+	ctx->haveCamera = true;
+	return MTSGPU_OK;
+}
+
+int mtsgpu_set_film(mtsgpu_ctx *ctx, int width, int height, int cropX, int cropY, int cropW, int cropH,
+		const float filterTable[256], float filterSizeX, float filterSizeY) {
+	ENTER(ctx);
+	REQUIRE(ctx, filterTable, MTSGPU_ERR_ARG, "set_film: null filter table");
+	// same validity rule as Film::Film (src/librender/film.cpp:40-45)
+	REQUIRE(ctx, !(cropX < 0 || cropY < 0 || cropW <= 0 || cropH <= 0 || cropX + cropW > width || cropY + cropH > height),
+		MTSGPU_ERR_ARG, "Invalid crop window specification!");
+	REQUIRE(ctx, filterSizeX > 0 && filterSizeY > 0, MTSGPU_ERR_ARG, "set_film: filter size must be positive");
+	FilmDev &f = ctx->film;
+	f.width = width; f.height = height; f.cropX = cropX; f.cropY = cropY; f.cropW = cropW; f.cropH = cropH;
+	f.filterSizeX = filterSizeX; f.filterSizeY = filterSizeY;
+	f.factorX = 15.0f / filterSizeX; f.factorY = 15.0f / filterSizeY;      // FILTER_RESOLUTION / m_size (rfilter.cpp:43-45)
+	f.border = (int) std::ceil(std::max(filterSizeX, filterSizeY) - 0.5f);  // renderproc.cpp:142-144
+	REQUIRE(ctx, f.border <= 8, MTSGPU_ERR_LIMIT, "set_film: filter radius %g exceeds the supported maximum", std::max(filterSizeX, filterSizeY));
+	memcpy(ctx->filterTable, filterTable, sizeof(ctx->filterTable));
+	ctx->haveFilm = true;
+	return MTSGPU_OK;
+}
+
+int mtsgpu_build_accel(mtsgpu_ctx *ctx) {
+	ENTER(ctx);
+	return buildAccel(ctx);
+}
+
+int mtsgpu_accel_info_get(mtsgpu_ctx *ctx, mtsgpu_accel_info *info) {
+	ENTER(ctx);
+	REQUIRE(ctx, ctx->built && info, MTSGPU_ERR_ARG, "accel_info: call mtsgpu_build_accel first");
+	*info = ctx->accel;
+	return MTSGPU_OK;
+}
+
+int mtsgpu_render_device(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, volatile const int *cancel, float *d_outFilm, mtsgpu_stats *stats) {
+	ENTER(ctx);
+	REQUIRE(ctx, params && d_outFilm, MTSGPU_ERR_ARG, "render: null argument");
+	return renderDevice(ctx, params, cancel, d_outFilm, stats);
+}
+
+int mtsgpu_render(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, volatile const int *cancel, float *outFilm, mtsgpu_stats *stats) {
+	ENTER(ctx);
+	REQUIRE(ctx, params && outFilm, MTSGPU_ERR_ARG, "render: null argument");
+	REQUIRE(ctx, ctx->haveFilm, MTSGPU_ERR_ARG, "render: call mtsgpu_set_film first");
+	const size_t bytes = (size_t) ctx->film.cropW * ctx->film.cropH * 5 * sizeof(float);
+	CUDA_TRY(ctx, ctx->dFilm.alloc(bytes));
+	int rc = renderDevice(ctx, params, cancel, ctx->dFilm.as<float>(), stats);
+	if (rc) return rc;
+	CUDA_TRY(ctx, cudaMemcpyAsync(outFilm, ctx->dFilm.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	return MTSGPU_OK;
+}
+
+int mtsgpu_trace_device(mtsgpu_ctx *ctx, const float *d_rays, size_t n, int mode, void *d_out, float *elapsedMs) {
+	ENTER(ctx);
+	REQUIRE(ctx, n == 0 || (d_rays && d_out), MTSGPU_ERR_ARG, "trace: null buffer");
+	uint64_t *cnt = nullptr;
+	if (ctx->countersEnabled) {
+		CUDA_TRY(ctx, ctx->dCounters.alloc(16));
+		CUDA_TRY(ctx, cudaMemsetAsync(ctx->dCounters.p, 0, 16, ctx->stream));
+		cnt = ctx->dCounters.as<uint64_t>();
+	}
+	CUDA_TRY(ctx, cudaEventRecord(ctx->ev[4], ctx->stream));
+	int rc = launchTrace(ctx, reinterpret_cast<const float4 *>(d_rays), n, mode, d_out, cnt);
+	if (rc) return rc;
+	CUDA_TRY(ctx, cudaEventRecord(ctx->ev[5], ctx->stream));
+	CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	CUDA_TRY(ctx, cudaGetLastError());
+	if (elapsedMs) { float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[4], ctx->ev[5]); *elapsedMs = ms; }
+	if (cnt) {
+		uint64_t h[2];
+		CUDA_TRY(ctx, cudaMemcpy(h, cnt, 16, cudaMemcpyDeviceToHost));
+		ctx->lastCounters.rays = n; ctx->lastCounters.nodeVisits = h[0]; ctx->lastCounters.triTests = h[1];
+	}
+	return MTSGPU_OK;
+}
+
+int mtsgpu_trace(mtsgpu_ctx *ctx, const float *rays, size_t n, int mode, void *out) {
+	ENTER(ctx);
+	REQUIRE(ctx, n == 0 || (rays && out), MTSGPU_ERR_ARG, "trace: null buffer");
+	REQUIRE(ctx, mode == MTSGPU_TRACE_CLOSEST || mode == MTSGPU_TRACE_ANY, MTSGPU_ERR_ARG, "trace: unknown mode %d", mode);
+	if (n == 0) return MTSGPU_OK;
+	const size_t outBytes = n * (mode == MTSGPU_TRACE_CLOSEST ? sizeof(mtsgpu_hit) : sizeof(uint32_t));
+	CUDA_TRY(ctx, ctx->dRays.alloc(n * 32));
+	CUDA_TRY(ctx, ctx->dHits.alloc(outBytes));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dRays.p, rays, n * 32, cudaMemcpyHostToDevice, ctx->stream));
+	int rc = mtsgpu_trace_device(ctx, ctx->dRays.as<float>(), n, mode, ctx->dHits.p, nullptr);
+	if (rc) return rc;
+	CUDA_TRY(ctx, cudaMemcpyAsync(out, ctx->dHits.p, outBytes, cudaMemcpyDeviceToHost, ctx->stream));
+	CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	return MTSGPU_OK;
+}
+
+int mtsgpu_bsdf_eval(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out) { ENTER(ctx); return hookBsdfEval(ctx, queries, n, out); }
+int mtsgpu_emitter_sample(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out) { ENTER(ctx); return hookEmitterSample(ctx, queries, n, out); }
+int mtsgpu_camera_rays(mtsgpu_ctx *ctx, const float *samples, size_t n, float *out) { ENTER(ctx); return hookCameraRays(ctx, samples, n, out); }
+int mtsgpu_film_splat(mtsgpu_ctx *ctx, const float *samples, size_t n, float *outFilm) { ENTER(ctx); return hookFilmSplat(ctx, samples, n, outFilm); }
+int mtsgpu_intersect_full(mtsgpu_ctx *ctx, const float *rays, size_t n, mtsgpu_hit *hits, float *out) { ENTER(ctx); return hookIntersectFull(ctx, rays, n, hits, out); }
+
+int mtsgpu_get_triaccel(mtsgpu_ctx *ctx, void *outRecords, size_t maxRecords, float aabb6[6]) {
+	ENTER(ctx);
+	REQUIRE(ctx, ctx->built, MTSGPU_ERR_ARG, "get_triaccel: call mtsgpu_build_accel first");
+	const size_t n = std::min<size_t>(maxRecords, ctx->accel.triangles);
+	if (outRecords && n)
+		CUDA_TRY(ctx, cudaMemcpy(outRecords, ctx->dTriAccelOrig.p, n * sizeof(TriAccelRec), cudaMemcpyDeviceToHost));
+	if (aabb6) {
+		for (int c = 0; c < 3; ++c) { aabb6[c] = ctx->scene.aabbMin[c]; aabb6[3 + c] = ctx->scene.aabbMax[c]; }
+	}
+	return MTSGPU_OK;
+}
+
+int mtsgpu_set_counters(mtsgpu_ctx *ctx, int enabled) { ENTER(ctx); ctx->countersEnabled = enabled != 0; return MTSGPU_OK; }
+
+int mtsgpu_get_counters(mtsgpu_ctx *ctx, mtsgpu_trace_counters *out) {
+	ENTER(ctx);
+	REQUIRE(ctx, out, MTSGPU_ERR_ARG, "get_counters: null argument");
+	*out = ctx->lastCounters;
+	return MTSGPU_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,296 @@
+// BSDF sample / eval / pdf device functions for the five models on the hot path, each restating
+// the reference's arithmetic in its operation order (this TU is compiled with --fmad=false so that
+// intermediate values match the reference's SSE build):
+//   lambertian  src/bsdfs/lambertian.cpp:95-126      mirror      src/bsdfs/mirror.cpp:61-94
+//   microfacet  src/bsdfs/microfacet.cpp:95-269      roughmetal  src/bsdfs/roughmetal.cpp:75-167
+//   dielectric  src/bsdfs/dielectric.cpp:101-290     base 3-arg fallback src/librender/bsdf.cpp:37-48
+// All directions are in the local shading frame (wi.z = cos theta). Queries use the full type
+// mask, component = -1 and quantity = ERadiance, which is what path.cpp / direct.cpp pass.
+#pragma once
+#include "types.cuh"
+
+#define BSDF_DIFFUSE_REFLECTION  0x0001u
+#define BSDF_DELTA_REFLECTION    0x0004u
+#define BSDF_DELTA_TRANSMISSION  0x0008u
+#define BSDF_GLOSSY_REFLECTION   0x0010u
+#define BSDF_DELTA               (BSDF_DELTA_REFLECTION | BSDF_DELTA_TRANSMISSION)
+#define BSDF_TRANSMISSION        (0x0002u | BSDF_DELTA_TRANSMISSION | 0x0020u)
+
+// ---- src/libcore/util.cpp helpers ---------------------------------------------------------------
+__device__ inline V3 sphericalDirection(float theta, float phi) {           // util.cpp:543-550
+	const float sinTheta = sinf(theta);
+	return v3(sinTheta * cosf(phi), sinTheta * sinf(phi), cosf(theta));
+}
+
+__device__ inline V3 squareToHemispherePSA(float sx, float sy) {            // util.cpp:572-588
+	const float r = sqrtf(sx);
+	const float phi = 2.0f * MTS_PI * sy;
+	const float dirX = r * cosf(phi);
+	const float dirY = r * sinf(phi);
+	const float z = sqrtf(1 - fminf(1.0f, dirX * dirX + dirY * dirY));
+	if (z == 0)
+		return normalize(v3(dirX, dirY, MTS_EPSILON));
+	return v3(dirX, dirY, z);
+}
+
+__device__ inline float fresnelDielectric(float cosTheta1, float cosTheta2, float etaI, float etaT) {   // util.cpp:680-689
+	const float Rs = (etaI * cosTheta1 - etaT * cosTheta2) / (etaI * cosTheta1 + etaT * cosTheta2);
+	const float Rp = (etaT * cosTheta1 - etaI * cosTheta2) / (etaT * cosTheta1 + etaI * cosTheta2);
+	return (Rs * Rs + Rp * Rp) / 2.0f;
+}
+
+__device__ inline V3 fresnelConductor(float cosTheta, V3 eta, V3 k) {       // util.cpp:691-704
+	const float c2 = cosTheta * cosTheta;
+	const float two = 2.0f * cosTheta;
+	V3 out;
+	const float e[3] = { eta.x, eta.y, eta.z }, kk[3] = { k.x, k.y, k.z };
+	float res[3];
+	for (int i = 0; i < 3; ++i) {
+		const float tmpF = e[i] * e[i] + kk[i] * kk[i];
+		const float tmp = tmpF * c2;
+		const float rParl2 = (tmp - (e[i] * two) + 1.0f) / (tmp + (e[i] * two) + 1.0f);
+		const float rPerp2 = (tmpF - (e[i] * two) + c2) / (tmpF + (e[i] * two) + c2);
+		res[i] = (rParl2 + rPerp2) / 2.0f;
+	}
+	out = v3(res[0], res[1], res[2]);
+	return out;
+}
+
+__device__ inline float fresnel(float cosThetaI, float etaExt, float etaInt) {   // util.cpp:706-725
+	float etaI = etaExt, etaT = etaInt;
+	if (cosThetaI < 0.0f) { const float t = etaI; etaI = etaT; etaT = t; }
+	const float sinThetaT = etaI / etaT * sqrtf(fmaxf(0.0f, 1.0f - cosThetaI * cosThetaI));
+	if (sinThetaT > 1.0f)
+		return 1.0f;
+	const float cosThetaT = sqrtf(1.0f - sinThetaT * sinThetaT);
+	return fresnelDielectric(fabsf(cosThetaI), cosThetaT, etaI, etaT);
+}
+
+__device__ inline float frameTanTheta(V3 v) {                                // core/frame.h:102-107
+	const float temp = 1 - v.z * v.z;
+	if (temp <= 0.0f) return 0.0f;
+	return sqrtf(temp) / v.z;
+}
+
+// ---- Beckmann microfacet terms shared by microfacet.cpp:95-134 and roughmetal.cpp:75-114 -----------
+__device__ inline float beckmannD(V3 m, float alphaB) {
+	const float ex = frameTanTheta(m) / alphaB;
+	return expf(-(ex * ex)) / (MTS_PI * alphaB * alphaB * powf(m.z, 4.0f));
+}
+
+__device__ inline V3 sampleBeckmannD(float sx, float sy, float alphaB) {
+	const float thetaM = atanf(sqrtf(-alphaB * alphaB * logf(1.0f - sx)));
+	const float phiM = (2.0f * MTS_PI) * sy;
+	return sphericalDirection(thetaM, phiM);
+}
+
+__device__ inline float smithBeckmannG1(V3 v, V3 m, float alphaB) {
+	if (dot(v, m) * v.z <= 0)
+		return 0.0f;
+	const float tanTheta = frameTanTheta(v);
+	if (tanTheta == 0.0f)
+		return 1.0f;
+	const float a = 1.0f / (alphaB * tanTheta);
+	const float aSqr = a * a;
+	if (a >= 1.6f)
+		return 1.0f;
+	return (3.535f * a + 2.181f * aSqr) / (1.0f + 2.276f * a + 2.577f * aSqr);
+}
+
+__device__ inline V3 reflectAbout(V3 wi, V3 n) {                             // n*(2*dot(n,wi)) - wi
+	return n * (2.0f * dot(n, wi)) - wi;
+}
+
+__device__ inline V3 mp3(const MaterialDev &m, int o) { return v3(m.p[o], m.p[o + 1], m.p[o + 2]); }
+
+// ---- f ---------------------------------------------------------------------------------------------
+__device__ inline V3 bsdfF(const MaterialDev &m, V3 wi, V3 wo) {
+	const V3 zero = v3(0, 0, 0);
+	switch (m.type) {
+		case MTSGPU_BSDF_LAMBERTIAN:
+			if (wi.z <= 0 || wo.z <= 0) return zero;
+			return mp3(m, 0) * MTS_INV_PI;
+		case MTSGPU_BSDF_MICROFACET: {
+			if (wi.z <= 0 || wo.z <= 0) return zero;
+			const float kd = m.p[6], ks = m.p[7], alphaB = m.p[8], intIOR = m.p[9], extIOR = m.p[10];
+			const V3 Hr = normalize(wi + wo);
+			const float F = fresnel(dot(wi, Hr), extIOR, intIOR);
+			const float D = beckmannD(Hr, alphaB);
+			const float G = smithBeckmannG1(wi, Hr, alphaB) * smithBeckmannG1(wo, Hr, alphaB);
+			const float specRef = D * G / (4.0f * wi.z * wo.z);
+			V3 result = (mp3(m, 3) * specRef) * (F * ks);
+			result = result + mp3(m, 0) * (MTS_INV_PI * (1 - F) * kd);
+			return result;
+		}
+		case MTSGPU_BSDF_ROUGHMETAL: {
+			if (wi.z <= 0 || wo.z <= 0) return zero;
+			const float alphaB = m.p[3];
+			const V3 Hr = normalize(wi + wo);
+			const V3 F = fresnelConductor(dot(wi, Hr), mp3(m, 4), mp3(m, 7));
+			const float D = beckmannD(Hr, alphaB);
+			const float G = smithBeckmannG1(wi, Hr, alphaB) * smithBeckmannG1(wo, Hr, alphaB);
+			const V3 specRef = F * (D * G / (4.0f * wi.z * wo.z));
+			return mp3(m, 0) * specRef;
+		}
+		default:   // mirror, dielectric: delta lobes only
+			return zero;
+	}
+}
+
+// ---- pdf -------------------------------------------------------------------------------------------
+__device__ inline float pdfSpecBeckmann(V3 wi, V3 wo, float alphaB) {
+	const V3 Hr = normalize(wi + wo);
+	return beckmannD(Hr, alphaB) * Hr.z / (4.0f * fabsf(dot(wo, Hr)));
+}
+
+__device__ inline float bsdfPdf(const MaterialDev &m, V3 wi, V3 wo) {
+	switch (m.type) {
+		case MTSGPU_BSDF_LAMBERTIAN:
+			if (wi.z <= 0 || wo.z <= 0) return 0.0f;
+			return wo.z * MTS_INV_PI;
+		case MTSGPU_BSDF_MICROFACET: {
+			if (wi.z <= 0 || wo.z <= 0) return 0.0f;
+			const float kd = m.p[6], ks = m.p[7], alphaB = m.p[8], intIOR = m.p[9], extIOR = m.p[10];
+			float fr = fresnel(wi.z, extIOR, intIOR);
+			fr = fminf(fmaxf(fr, 0.05f), 0.95f);
+			const float diffuseSamplingWeight = (1 - fr) * kd;
+			const float specularSamplingWeight = fr * ks;
+			const float normalization = 1 / (diffuseSamplingWeight + specularSamplingWeight);
+			return (specularSamplingWeight * pdfSpecBeckmann(wi, wo, alphaB)
+				+ diffuseSamplingWeight * (wo.z * MTS_INV_PI)) * normalization;
+		}
+		case MTSGPU_BSDF_ROUGHMETAL: {
+			if (wi.z <= 0 || wo.z <= 0) return 0.0f;
+			const float alphaB = m.p[3];
+			const V3 Hr = normalize(wi + wo);
+			const float dwhr_dwo = 1.0f / (4.0f * fabsf(dot(wo, Hr)));
+			return beckmannD(Hr, alphaB) * Hr.z * dwhr_dwo;
+		}
+		default:
+			return 0.0f;
+	}
+}
+
+// ---- dielectric core (dielectric.cpp:116-146): Fresnel reflectance + transmitted cosine -------------
+__device__ inline void dielectricSetup(const MaterialDev &m, V3 wi, float &Fr, float &eta, float &cosThetaT) {
+	const float cosThetaI = wi.z;
+	float etaI = m.p[7], etaT = m.p[6];       // extIOR, intIOR
+	const bool entering = cosThetaI > 0.0f;
+	if (!entering) { const float t = etaI; etaI = etaT; etaT = t; }
+	eta = etaI / etaT;
+	const float sinThetaTSqr = eta * eta * (1.0f - wi.z * wi.z);
+	cosThetaT = 0;
+	if (sinThetaTSqr >= 1.0f) {
+		Fr = 1.0f;
+	} else {
+		cosThetaT = sqrtf(1.0f - sinThetaTSqr);
+		Fr = fresnelDielectric(fabsf(cosThetaI), cosThetaT, etaI, etaT);
+		if (entering)
+			cosThetaT = -cosThetaT;
+	}
+}
+
+// ---- 2-argument sample: returns f / pdf (NOT multiplied by the cosine); zero => no sample ----------
+__device__ inline V3 bsdfSample2(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, uint32_t &type) {
+	const V3 zero = v3(0, 0, 0);
+	switch (m.type) {
+		case MTSGPU_BSDF_LAMBERTIAN:
+			if (wi.z <= 0) return zero;
+			wo = squareToHemispherePSA(sx, sy);
+			type = BSDF_DIFFUSE_REFLECTION;
+			return mp3(m, 0) * (1.0f / wo.z);              // Spectrum / Float multiplies by the reciprocal
+		case MTSGPU_BSDF_MIRROR:
+			wo = v3(-wi.x, -wi.y, wi.z);
+			type = BSDF_DELTA_REFLECTION;
+			return mp3(m, 0);                               // Mirror::sample(2-arg) forwards to the 3-arg one
+		case MTSGPU_BSDF_MICROFACET: {
+			if (wi.z <= 0) return zero;
+			const float kd = m.p[6], ks = m.p[7], alphaB = m.p[8], intIOR = m.p[9], extIOR = m.p[10];
+			float fr = fresnel(wi.z, extIOR, intIOR);
+			fr = fminf(fmaxf(fr, 0.05f), 0.95f);
+			float diffuseSamplingWeight = (1 - fr) * kd;
+			float specularSamplingWeight = fr * ks;
+			const float normalization = 1 / (diffuseSamplingWeight + specularSamplingWeight);
+			specularSamplingWeight *= normalization;
+			diffuseSamplingWeight *= normalization;
+			if (sx < specularSamplingWeight) {
+				sx /= specularSamplingWeight;
+				const V3 mm = sampleBeckmannD(sx, sy, alphaB);
+				wo = reflectAbout(wi, mm);
+				type = BSDF_GLOSSY_REFLECTION;
+				if (wo.z <= 0) return zero;
+				const float pdfValue = bsdfPdf(m, wi, wo);
+				if (pdfValue == 0) return zero;
+				return bsdfF(m, wi, wo) * (1.0f / pdfValue);
+			} else {
+				sx = (sx - specularSamplingWeight) / diffuseSamplingWeight;
+				wo = squareToHemispherePSA(sx, sy);
+				type = BSDF_DIFFUSE_REFLECTION;
+				return bsdfF(m, wi, wo) * (1.0f / bsdfPdf(m, wi, wo));
+			}
+		}
+		case MTSGPU_BSDF_ROUGHMETAL: {
+			if (wi.z <= 0) return zero;
+			const V3 mm = sampleBeckmannD(sx, sy, m.p[3]);
+			wo = reflectAbout(wi, mm);
+			type = BSDF_GLOSSY_REFLECTION;
+			if (wo.z <= 0) return zero;
+			return bsdfF(m, wi, wo) * (1.0f / bsdfPdf(m, wi, wo));
+		}
+		case MTSGPU_BSDF_DIELECTRIC: {
+			float Fr, eta, cosThetaT;
+			dielectricSetup(m, wi, Fr, eta, cosThetaT);
+			if (sx <= Fr) {
+				type = BSDF_DELTA_REFLECTION;
+				wo = v3(-wi.x, -wi.y, wi.z);
+				return mp3(m, 0) * (1.0f / fabsf(wo.z));
+			} else {
+				type = BSDF_DELTA_TRANSMISSION;
+				wo = v3(-eta * wi.x, -eta * wi.y, cosThetaT);
+				return (mp3(m, 3) * (eta * eta)) * (1.0f / fabsf(wo.z));
+			}
+		}
+		default:
+			return zero;
+	}
+}
+
+// ---- 3-argument sample: returns f (not divided by pdf) and the pdf; zero => no sample ---------------
+__device__ inline V3 bsdfSample3(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, float &pdf, uint32_t &type) {
+	const V3 zero = v3(0, 0, 0);
+	switch (m.type) {
+		case MTSGPU_BSDF_LAMBERTIAN:
+			if (wi.z <= 0) return zero;
+			wo = squareToHemispherePSA(sx, sy);
+			type = BSDF_DIFFUSE_REFLECTION;
+			pdf = wo.z * MTS_INV_PI;
+			return mp3(m, 0) * MTS_INV_PI;
+		case MTSGPU_BSDF_MIRROR:
+			wo = v3(-wi.x, -wi.y, wi.z);
+			type = BSDF_DELTA_REFLECTION;
+			pdf = fabsf(wo.z);
+			return mp3(m, 0);
+		case MTSGPU_BSDF_DIELECTRIC: {
+			float Fr, eta, cosThetaT;
+			dielectricSetup(m, wi, Fr, eta, cosThetaT);
+			if (sx <= Fr) {
+				type = BSDF_DELTA_REFLECTION;
+				wo = v3(-wi.x, -wi.y, wi.z);
+				pdf = Fr * fabsf(wo.z);
+				return mp3(m, 0) * Fr;
+			} else {
+				type = BSDF_DELTA_TRANSMISSION;
+				wo = v3(-eta * wi.x, -eta * wi.y, cosThetaT);
+				pdf = (1 - Fr) * fabsf(wo.z);
+				return (mp3(m, 3) * (1 - Fr)) * (eta * eta);
+			}
+		}
+		default: {
+			// BSDF::sample(bRec, pdf, sample) fallback (bsdf.cpp:37-48): 2-arg sample, then pdf() and f()
+			const V3 s = bsdfSample2(m, wi, sx, sy, wo, type);
+			if (isZero(s)) { pdf = 0.0f; return zero; }
+			pdf = bsdfPdf(m, wi, wo);
+			return bsdfF(m, wi, wo);
+		}
+	}
+}

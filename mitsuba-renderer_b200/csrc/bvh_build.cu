@@ -1,0 +1,545 @@
+// GPU acceleration-structure build. Replaces ShapeKDTree::build (src/librender/skdtree.cpp:62-106)
+// and GenericKDTree::buildInternal (include/mitsuba/render/gkdtree.h:913-1214):
+//   1. k_prepare_tris   TriAccel::load for every triangle, bit-exact (triaccel.h:63-96), triangle
+//                       boxes and the tight scene box
+//   2. k_morton + radix sort of 63-bit Morton keys (the sort itself is cub::DeviceRadixSort)
+//   3. k_lbvh_hierarchy binary radix tree over the sorted keys (Karras 2012)
+//   4. k_refit          bottom-up boxes with one atomic counter per inner node
+//   5. k_collapse       binary tree -> 4-wide nodes of 128 B, widest-surface-area child opened
+//                       first; subtrees of <= BVH_LEAF_MAX triangles become leaves
+//   6. k_reorder        TriAccel records gathered into leaf order so a leaf is one contiguous run
+// Only hit results must agree with the reference's kd-tree, not the tree.
+#include "context.h"
+#include <cub/device/device_radix_sort.cuh>
+#include <algorithm>
+#include <cfloat>
+
+namespace {
+
+__device__ __forceinline__ int floatToOrdered(float f) {
+	int i = __float_as_int(f);
+	return i >= 0 ? i : i ^ 0x7FFFFFFF;
+}
+inline float orderedToFloat(int i) {
+	int j = i >= 0 ? i : i ^ 0x7FFFFFFF;
+	float f; memcpy(&f, &j, 4); return f;
+}
+
+__device__ __forceinline__ float comp(const float4 &v, int i) { return i == 0 ? v.x : (i == 1 ? v.y : v.z); }
+
+// TriAccel::load (triaccel.h:63-96) with every operation rounded separately, as the
+// reference's SSE build does (no FMA contraction).
+__device__ void triAccelLoad(const float4 &A, const float4 &B, const float4 &C, TriAccelRec &r) {
+	const float bx = __fsub_rn(C.x, A.x), by = __fsub_rn(C.y, A.y), bz = __fsub_rn(C.z, A.z);
+	const float cx = __fsub_rn(B.x, A.x), cy = __fsub_rn(B.y, A.y), cz = __fsub_rn(B.z, A.z);
+	// N = cross(c, b)
+	float N[3] = {
+		__fsub_rn(__fmul_rn(cy, bz), __fmul_rn(cz, by)),
+		__fsub_rn(__fmul_rn(cz, bx), __fmul_rn(cx, bz)),
+		__fsub_rn(__fmul_rn(cx, by), __fmul_rn(cy, bx)) };
+	const float b[3] = { bx, by, bz }, c[3] = { cx, cy, cz };
+	int k = 0;
+	for (int j = 0; j < 3; ++j)
+		if (fabsf(N[j]) > fabsf(N[k])) k = j;
+	const int u = (k + 1) % 3, v = (k + 2) % 3;   // waldModulo
+	const float n_k = N[k];
+	const float denom = __fsub_rn(__fmul_rn(b[u], c[v]), __fmul_rn(b[v], c[u]));
+	if (denom == 0) {
+		r.k = 3; r.n_u = r.n_v = r.n_d = r.a_u = r.a_v = r.b_nu = r.b_nv = r.c_nu = r.c_nv = 0;
+		return;
+	}
+	r.k = (uint32_t) k;
+	r.n_u = __fdiv_rn(N[u], n_k);
+	r.n_v = __fdiv_rn(N[v], n_k);
+	const float dotAN = __fadd_rn(__fadd_rn(__fmul_rn(A.x, N[0]), __fmul_rn(A.y, N[1])), __fmul_rn(A.z, N[2]));
+	r.n_d = __fdiv_rn(dotAN, n_k);
+	r.b_nu = __fdiv_rn(b[u], denom);
+	r.b_nv = __fdiv_rn(-b[v], denom);
+	r.a_u = comp(A, u);
+	r.a_v = comp(A, v);
+	r.c_nu = __fdiv_rn(c[v], denom);
+	r.c_nv = __fdiv_rn(-c[u], denom);
+}
+
+__global__ void k_prepare_tris(const uint4 *triIdx, const float4 *pos, const ShapeInfo *shapes, uint32_t n,
+		TriAccelRec *accelOrig, float4 *triLo, float4 *triHi, int *bounds) {
+	const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+	float lo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, hi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
+	if (g < n) {
+		const uint4 t = triIdx[g];
+		const float4 A = pos[t.x], B = pos[t.y], C = pos[t.z];
+		TriAccelRec r;
+		triAccelLoad(A, B, C, r);
+		const ShapeInfo sh = shapes[t.w];
+		r.shapeIndex = t.w;
+		r.primIndex = g - sh.triOffset;
+		if (sh.materialId < 0) r.k |= TRI_NONOCCLUDER;
+		accelOrig[g] = r;
+		lo[0] = fminf(A.x, fminf(B.x, C.x)); hi[0] = fmaxf(A.x, fmaxf(B.x, C.x));
+		lo[1] = fminf(A.y, fminf(B.y, C.y)); hi[1] = fmaxf(A.y, fmaxf(B.y, C.y));
+		lo[2] = fminf(A.z, fminf(B.z, C.z)); hi[2] = fmaxf(A.z, fmaxf(B.z, C.z));
+		triLo[g] = make_float4(lo[0], lo[1], lo[2], 0);
+		triHi[g] = make_float4(hi[0], hi[1], hi[2], 0);
+	}
+	// warp reduce, then one atomic per warp and component
+	for (int c = 0; c < 3; ++c) {
+		float l = lo[c], h = hi[c];
+		for (int o = 16; o > 0; o >>= 1) {
+			l = fminf(l, __shfl_xor_sync(0xFFFFFFFFu, l, o));
+			h = fmaxf(h, __shfl_xor_sync(0xFFFFFFFFu, h, o));
+		}
+		if ((threadIdx.x & 31) == 0) {
+			atomicMin(&bounds[c], floatToOrdered(l));
+			atomicMax(&bounds[3 + c], floatToOrdered(h));
+		}
+	}
+}
+
+__device__ __forceinline__ uint64_t expandBits21(uint32_t v) {
+	uint64_t x = v & 0x1FFFFFu;
+	x = (x | x << 32) & 0x1F00000000FFFFull;
+	x = (x | x << 16) & 0x1F0000FF0000FFull;
+	x = (x | x << 8) & 0x100F00F00F00F00Full;
+	x = (x | x << 4) & 0x10C30C30C30C30C3ull;
+	x = (x | x << 2) & 0x1249249249249249ull;
+	return x;
+}
+
+__global__ void k_morton(const float4 *triLo, const float4 *triHi, uint32_t n, float3 bmin, float3 invExt,
+		uint64_t *keys, uint32_t *vals) {
+	const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+	if (g >= n) return;
+	const float4 lo = triLo[g], hi = triHi[g];
+	const float cx = ((lo.x + hi.x) * 0.5f - bmin.x) * invExt.x;
+	const float cy = ((lo.y + hi.y) * 0.5f - bmin.y) * invExt.y;
+	const float cz = ((lo.z + hi.z) * 0.5f - bmin.z) * invExt.z;
+	const uint32_t qx = (uint32_t) fminf(fmaxf(cx * 2097152.0f, 0.0f), 2097151.0f);
+	const uint32_t qy = (uint32_t) fminf(fmaxf(cy * 2097152.0f, 0.0f), 2097151.0f);
+	const uint32_t qz = (uint32_t) fminf(fmaxf(cz * 2097152.0f, 0.0f), 2097151.0f);
+	keys[g] = (expandBits21(qx) << 2) | (expandBits21(qy) << 1) | expandBits21(qz);
+	vals[g] = g;
+}
+
+// Binary radix tree: inner nodes 0..n-2 (root 0), leaves n-1..2n-2 (leaf l at n-1+l).
+__device__ __forceinline__ int delta(const uint64_t *keys, int n, int i, int j) {
+	if (j < 0 || j >= n) return -1;
+	const uint64_t a = keys[i], b = keys[j];
+	if (a == b) return 64 + __clz(i ^ j);
+	return __clzll((long long) (a ^ b));
+}
+
+__global__ void k_lbvh_hierarchy(const uint64_t *keys, int n, int2 *children, int2 *range, int *parent) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n - 1) return;
+	const int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+	const int dmin = delta(keys, n, i, i - d);
+	int lmax = 2;
+	while (delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+	int l = 0;
+	for (int t = lmax / 2; t >= 1; t /= 2)
+		if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+	const int j = i + l * d;
+	const int dnode = delta(keys, n, i, j);
+	int s = 0, t = l;
+	do {
+		t = (t + 1) / 2;
+		if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+	} while (t > 1);
+	const int gamma = i + s * d + min(d, 0);
+	const int first = min(i, j), last = max(i, j);
+	const int left = (first == gamma) ? (n - 1 + gamma) : gamma;
+	const int right = (last == gamma + 1) ? (n - 1 + gamma + 1) : gamma + 1;
+	children[i] = make_int2(left, right);
+	range[i] = make_int2(first, last);
+	parent[left] = i;
+	parent[right] = i;
+	if (i == 0) parent[0] = -1;
+}
+
+__global__ void k_refit(const uint32_t *sortedIdx, const float4 *triLo, const float4 *triHi, int n, float pad,
+		const int2 *children, const int *parent, int *flags, float4 *boxLo, float4 *boxHi) {
+	const int l = blockIdx.x * blockDim.x + threadIdx.x;
+	if (l >= n) return;
+	const uint32_t g = sortedIdx[l];
+	float4 lo = triLo[g], hi = triHi[g];
+	// Conservative pad: the TriAccel test works on rounded plane/barycentric values, so an accepted
+	// hit can lie a few ulps of the coordinate magnitude outside the exact triangle box.
+	lo.x -= pad; lo.y -= pad; lo.z -= pad; hi.x += pad; hi.y += pad; hi.z += pad;
+	int node = n - 1 + l;
+	boxLo[node] = lo; boxHi[node] = hi;
+	node = parent[node];
+	while (node >= 0) {
+		__threadfence();
+		if (atomicAdd(&flags[node], 1) == 0) return;   // first arrival leaves; second one has both children
+		const int2 c = children[node];
+		const float4 al = __ldcg(&boxLo[c.x]), ah = __ldcg(&boxHi[c.x]);
+		const float4 bl = __ldcg(&boxLo[c.y]), bh = __ldcg(&boxHi[c.y]);
+		boxLo[node] = make_float4(fminf(al.x, bl.x), fminf(al.y, bl.y), fminf(al.z, bl.z), 0);
+		boxHi[node] = make_float4(fmaxf(ah.x, bh.x), fmaxf(ah.y, bh.y), fmaxf(ah.z, bh.z), 0);
+		node = parent[node];
+	}
+}
+
+__device__ __forceinline__ int subtreeCount(int node, int n, const int2 *range) {
+	if (node >= n - 1) return 1;
+	const int2 r = range[node];
+	return r.y - r.x + 1;
+}
+__device__ __forceinline__ int subtreeFirst(int node, int n, const int2 *range) {
+	return node >= n - 1 ? node - (n - 1) : range[node].x;
+}
+__device__ __forceinline__ float halfArea(const float4 &lo, const float4 &hi) {
+	const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+	return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void k_collapse(const uint2 *qIn, uint32_t nIn, uint2 *qOut, uint32_t *qOutCount, uint32_t *nodeCount,
+		int n, const int2 *children, const int2 *range, const float4 *boxLo, const float4 *boxHi, BVH4Node *nodes) {
+	const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+	if (w >= nIn) return;
+	const uint2 item = qIn[w];
+	int ch[4]; int cnt;
+	{
+		const int2 c = children[item.x];
+		ch[0] = c.x; ch[1] = c.y; cnt = 2;
+	}
+	while (cnt < 4) {
+		int best = -1; float bestArea = -1.0f;
+		for (int i = 0; i < cnt; ++i) {
+			if (subtreeCount(ch[i], n, range) <= BVH_LEAF_MAX) continue;
+			const float a = halfArea(boxLo[ch[i]], boxHi[ch[i]]);
+			if (a > bestArea) { bestArea = a; best = i; }
+		}
+		if (best < 0) break;
+		const int2 c = children[ch[best]];
+		ch[best] = c.x; ch[cnt++] = c.y;
+	}
+	float lo[3][4], hi[3][4]; uint32_t cw[4];
+	for (int i = 0; i < 4; ++i) {
+		if (i >= cnt) {
+			lo[0][i] = lo[1][i] = lo[2][i] = INFINITY; hi[0][i] = hi[1][i] = hi[2][i] = -INFINITY;
+			cw[i] = BVH_EMPTY;
+			continue;
+		}
+		const float4 l = boxLo[ch[i]], h = boxHi[ch[i]];
+		lo[0][i] = l.x; lo[1][i] = l.y; lo[2][i] = l.z; hi[0][i] = h.x; hi[1][i] = h.y; hi[2][i] = h.z;
+		const int c = subtreeCount(ch[i], n, range);
+		if (c <= BVH_LEAF_MAX) {
+			cw[i] = BVH_LEAF | ((uint32_t) (c - 1) << 28) | (uint32_t) subtreeFirst(ch[i], n, range);
+		} else {
+			const uint32_t idx = atomicAdd(nodeCount, 1u);
+			cw[i] = idx;
+			qOut[atomicAdd(qOutCount, 1u)] = make_uint2((uint32_t) ch[i], idx);
+		}
+	}
+	BVH4Node nd;
+	nd.lox = make_float4(lo[0][0], lo[0][1], lo[0][2], lo[0][3]);
+	nd.loy = make_float4(lo[1][0], lo[1][1], lo[1][2], lo[1][3]);
+	nd.loz = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]);
+	nd.hix = make_float4(hi[0][0], hi[0][1], hi[0][2], hi[0][3]);
+	nd.hiy = make_float4(hi[1][0], hi[1][1], hi[1][2], hi[1][3]);
+	nd.hiz = make_float4(hi[2][0], hi[2][1], hi[2][2], hi[2][3]);
+	nd.child = make_uint4(cw[0], cw[1], cw[2], cw[3]);
+	nd.pad = make_uint4(0, 0, 0, 0);
+	nodes[item.y] = nd;
+}
+
+__global__ void k_reorder(const uint32_t *sortedIdx, const TriAccelRec *orig, uint32_t n, TriAccelRec *sorted) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) sorted[i] = orig[sortedIdx[i]];
+}
+
+inline unsigned blocksFor(size_t n, unsigned bs) { return (unsigned) ((n + bs - 1) / bs); }
+
+} // namespace
+
+// Host-side DiscretePDF::build (include/mitsuba/core/pdf.h:82-100), float arithmetic in the same order.
+static float buildCdf(const std::vector<float> &pdf, std::vector<float> &cdf) {
+	cdf.assign(pdf.size() + 1, 0.0f);
+	for (size_t i = 1; i < cdf.size(); ++i) {
+		volatile float s = cdf[i - 1] + pdf[i - 1];
+		cdf[i] = s;
+	}
+	const float sum = cdf.back();
+	for (size_t i = 0; i < pdf.size(); ++i) {
+		volatile float q = cdf[i] / sum;
+		cdf[i] = q;
+	}
+	cdf.back() = 1.0f;
+	return sum;
+}
+
+// Luminaire-selection CDF (Scene::initialize, scene.cpp:320-330): weights are the luminaires'
+// samplingWeight when importanceSampleLuminaires is set (the default), else 1 each.
+int rebuildLuminaireCdf(mtsgpu_ctx *ctx, bool importance) {
+	if (ctx->lumImportance == (int) importance) return MTSGPU_OK;
+	cudaStream_t st = ctx->stream;
+	std::vector<EmitterDev> emitters(ctx->emitters.size());
+	std::vector<float> lumPdf(ctx->emitters.size()), lumCdf;
+	for (size_t e = 0; e < emitters.size(); ++e) {
+		memset(&emitters[e], 0, sizeof(EmitterDev));
+		memcpy(emitters[e].intensity, ctx->emitters[e].intensity, 12);
+		emitters[e].shape = (uint32_t) ctx->emitterShape[e];
+		emitters[e].weight = ctx->emitters[e].samplingWeight;
+		lumPdf[e] = importance ? ctx->emitters[e].samplingWeight : 1.0f;
+	}
+	float lumSum = 0.0f;
+	if (!emitters.empty()) {
+		lumSum = buildCdf(lumPdf, lumCdf);
+		for (size_t e = 0; e < emitters.size(); ++e) {
+			volatile float q = lumPdf[e] / lumSum;
+			emitters[e].pdf = q;
+		}
+	} else {
+		lumCdf.assign(1, 0.0f);
+	}
+	CUDA_TRY(ctx, ctx->dEmitters.alloc(std::max<size_t>(emitters.size(), 1) * sizeof(EmitterDev)));
+	CUDA_TRY(ctx, ctx->dLumCdf.alloc(lumCdf.size() * sizeof(float)));
+	if (!emitters.empty())
+		CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dEmitters.p, emitters.data(), emitters.size() * sizeof(EmitterDev), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dLumCdf.p, lumCdf.data(), lumCdf.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, cudaStreamSynchronize(st));
+	ctx->scene.emitters = ctx->dEmitters.as<EmitterDev>();
+	ctx->scene.lumCdf = ctx->dLumCdf.as<float>();
+	ctx->scene.nEmitters = (uint32_t) emitters.size();
+	ctx->scene.lumOriginalSum = lumSum;
+	ctx->lumImportance = (int) importance;
+	return MTSGPU_OK;
+}
+
+int buildAccel(mtsgpu_ctx *ctx) {
+	REQUIRE(ctx, !ctx->meshes.empty(), MTSGPU_ERR_ARG, "mtsgpu_build_accel: no meshes uploaded");
+	cudaStream_t st = ctx->stream;
+	const size_t nShapes = ctx->meshes.size();
+	size_t nTri = 0, nVert = 0;
+	for (auto &m : ctx->meshes) { nTri += m.nTri; nVert += m.nVert; }
+	REQUIRE(ctx, nTri > 0, MTSGPU_ERR_ARG, "mtsgpu_build_accel: scene has no triangles");
+	REQUIRE(ctx, nTri < (1u << 28), MTSGPU_ERR_LIMIT, "mtsgpu_build_accel: more than 2^28 triangles");
+
+	// ---- flatten meshes (global vertex ids; float4-padded vertices for 128-bit loads) ----
+	std::vector<uint4> triIdx(nTri);
+	std::vector<float4> pos(nVert), nrm(nVert);
+	std::vector<ShapeInfo> shapes(nShapes);
+	std::vector<float> areaCdfAll;
+	std::vector<int> emitterShape(ctx->emitters.size(), -1);
+	size_t tOff = 0, vOff = 0;
+	for (size_t s = 0; s < nShapes; ++s) {
+		const HostMesh &m = ctx->meshes[s];
+		ShapeInfo &si = shapes[s];
+		memset(&si, 0, sizeof(si));
+		si.materialId = m.materialId; si.emitterId = m.emitterId;
+		si.triOffset = (uint32_t) tOff; si.vertOffset = (uint32_t) vOff;
+		si.nTri = m.nTri; si.nVert = m.nVert; si.hasNormals = m.hasNormals ? 1u : 0u;
+		REQUIRE(ctx, m.materialId < (int) ctx->materials.size(), MTSGPU_ERR_ARG, "shape %zu: material id %d out of range", s, m.materialId);
+		REQUIRE(ctx, m.emitterId < (int) ctx->emitters.size(), MTSGPU_ERR_ARG, "shape %zu: emitter id %d out of range", s, m.emitterId);
+		for (uint32_t v = 0; v < m.nVert; ++v) {
+			pos[vOff + v] = make_float4(m.pos[3*v], m.pos[3*v+1], m.pos[3*v+2], 0);
+			nrm[vOff + v] = m.hasNormals ? make_float4(m.nrm[3*v], m.nrm[3*v+1], m.nrm[3*v+2], 0) : make_float4(0, 0, 0, 0);
+		}
+		for (uint32_t t = 0; t < m.nTri; ++t) {
+			for (int c = 0; c < 3; ++c)
+				REQUIRE(ctx, m.tri[3*t+c] < m.nVert, MTSGPU_ERR_ARG, "shape %zu: triangle %u references vertex %u >= %u", s, t, m.tri[3*t+c], m.nVert);
+			triIdx[tOff + t] = make_uint4((uint32_t) vOff + m.tri[3*t], (uint32_t) vOff + m.tri[3*t+1], (uint32_t) vOff + m.tri[3*t+2], (uint32_t) s);
+		}
+		if (m.emitterId >= 0) {
+			REQUIRE(ctx, emitterShape[m.emitterId] < 0, MTSGPU_ERR_ARG, "emitter %d is bound to more than one shape", m.emitterId);
+			emitterShape[m.emitterId] = (int) s;
+			// TriMesh::configure: area PDF over Triangle::surfaceArea (trimesh.cpp:266-283, triangle.cpp:49-55)
+			std::vector<float> areas(m.nTri), cdf;
+			for (uint32_t t = 0; t < m.nTri; ++t) {
+				const float *p0 = &m.pos[3 * m.tri[3*t]], *p1 = &m.pos[3 * m.tri[3*t+1]], *p2 = &m.pos[3 * m.tri[3*t+2]];
+				volatile float ax = p1[0] - p0[0], ay = p1[1] - p0[1], az = p1[2] - p0[2];
+				volatile float bx = p2[0] - p0[0], by = p2[1] - p0[1], bz = p2[2] - p0[2];
+				volatile float m0 = ay * bz, m1 = az * by, m2 = az * bx, m3 = ax * bz, m4 = ax * by, m5 = ay * bx;
+				volatile float cx = m0 - m1, cy = m2 - m3, cz = m4 - m5;
+				volatile float q0 = cx * cx, q1 = cy * cy, q2 = cz * cz;
+				volatile float s01 = q0 + q1; volatile float s012 = s01 + q2;
+				areas[t] = 0.5f * sqrtf(s012);
+			}
+			const float total = buildCdf(areas, cdf);
+			si.cdfOffset = (uint32_t) areaCdfAll.size();
+			si.invSurfaceArea = 1.0f / total;
+			areaCdfAll.insert(areaCdfAll.end(), cdf.begin(), cdf.end());
+		}
+		tOff += m.nTri; vOff += m.nVert;
+	}
+	for (size_t e = 0; e < emitterShape.size(); ++e)
+		REQUIRE(ctx, emitterShape[e] >= 0, MTSGPU_ERR_ARG, "emitter %zu is not bound to any shape", e);
+	// emitters must appear in first-shape order (scene.cpp:656-664)
+	for (size_t e = 1; e < emitterShape.size(); ++e)
+		REQUIRE(ctx, emitterShape[e] > emitterShape[e-1], MTSGPU_ERR_ARG, "emitters must be listed in the order of their shapes");
+
+	ctx->emitterShape = emitterShape;
+
+	std::vector<MaterialDev> mats(std::max<size_t>(ctx->materials.size(), 1));
+	memset(mats.data(), 0, mats.size() * sizeof(MaterialDev));
+	for (size_t i = 0; i < ctx->materials.size(); ++i) {
+		mats[i].type = ctx->materials[i].type;
+		memcpy(mats[i].p, ctx->materials[i].p, 64);
+	}
+
+	// ---- upload ----
+	CUDA_TRY(ctx, ctx->dTriIdx.alloc(nTri * sizeof(uint4)));
+	CUDA_TRY(ctx, ctx->dPositions.alloc(nVert * sizeof(float4)));
+	CUDA_TRY(ctx, ctx->dNormals.alloc(nVert * sizeof(float4)));
+	CUDA_TRY(ctx, ctx->dShapes.alloc(nShapes * sizeof(ShapeInfo)));
+	CUDA_TRY(ctx, ctx->dMaterials.alloc(mats.size() * sizeof(MaterialDev)));
+	CUDA_TRY(ctx, ctx->dAreaCdf.alloc(std::max<size_t>(areaCdfAll.size(), 1) * sizeof(float)));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dTriIdx.p, triIdx.data(), nTri * sizeof(uint4), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dPositions.p, pos.data(), nVert * sizeof(float4), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dNormals.p, nrm.data(), nVert * sizeof(float4), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dShapes.p, shapes.data(), nShapes * sizeof(ShapeInfo), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dMaterials.p, mats.data(), mats.size() * sizeof(MaterialDev), cudaMemcpyHostToDevice, st));
+	if (!areaCdfAll.empty())
+		CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dAreaCdf.p, areaCdfAll.data(), areaCdfAll.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, cudaStreamSynchronize(st));
+
+	cudaEvent_t e0 = ctx->ev[0], e1 = ctx->ev[1];
+	CUDA_TRY(ctx, cudaEventRecord(e0, st));
+
+	const int n = (int) nTri;
+	DevBuf dTriLo, dTriHi, dBounds, dKeys, dKeysAlt, dVals, dValsAlt, dTemp, dChildren, dRange, dParent, dFlags,
+	       dBoxLo, dBoxHi, dQ0, dQ1, dCounts, dNodesTmp;
+	CUDA_TRY(ctx, ctx->dTriAccelOrig.alloc(nTri * sizeof(TriAccelRec)));
+	CUDA_TRY(ctx, ctx->dTriAccel.alloc(nTri * sizeof(TriAccelRec)));
+	CUDA_TRY(ctx, dTriLo.alloc(nTri * sizeof(float4)));
+	CUDA_TRY(ctx, dTriHi.alloc(nTri * sizeof(float4)));
+	CUDA_TRY(ctx, dBounds.alloc(6 * sizeof(int)));
+	{
+		int init[6] = { INT32_MAX, INT32_MAX, INT32_MAX, INT32_MIN, INT32_MIN, INT32_MIN };
+		CUDA_TRY(ctx, cudaMemcpyAsync(dBounds.p, init, sizeof(init), cudaMemcpyHostToDevice, st));
+	}
+	k_prepare_tris<<<blocksFor(nTri, 256), 256, 0, st>>>(ctx->dTriIdx.as<uint4>(), ctx->dPositions.as<float4>(),
+		ctx->dShapes.as<ShapeInfo>(), (uint32_t) nTri, ctx->dTriAccelOrig.as<TriAccelRec>(),
+		dTriLo.as<float4>(), dTriHi.as<float4>(), dBounds.as<int>());
+	CUDA_TRY(ctx, cudaGetLastError());
+	int enc[6];
+	CUDA_TRY(ctx, cudaMemcpyAsync(enc, dBounds.p, sizeof(enc), cudaMemcpyDeviceToHost, st));
+	CUDA_TRY(ctx, cudaStreamSynchronize(st));
+	float tmin[3], tmax[3];
+	for (int c = 0; c < 3; ++c) { tmin[c] = orderedToFloat(enc[c]); tmax[c] = orderedToFloat(enc[3 + c]); }
+
+	// enlarged box, same two statements as gkdtree.h:1172-1176 (note: max uses the already-moved min)
+	DeviceScene &sc = ctx->scene;
+	float maxAbs = 0.0f;
+	for (int c = 0; c < 3; ++c) {
+		volatile float ext = tmax[c] - tmin[c];
+		volatile float grow = ext * MTS_EPSILON;
+		volatile float grow2 = grow + MTS_EPSILON;
+		volatile float nmin = tmin[c] - grow2;
+		volatile float ext2 = tmax[c] - nmin;
+		volatile float g3 = ext2 * MTS_EPSILON;
+		volatile float g4 = g3 + MTS_EPSILON;
+		volatile float nmax = tmax[c] + g4;
+		sc.aabbMin[c] = nmin; sc.aabbMax[c] = nmax;
+		maxAbs = std::max(maxAbs, std::max(std::fabs(tmin[c]), std::fabs(tmax[c])));
+	}
+
+	// ---- Morton keys + sort ----
+	CUDA_TRY(ctx, dKeys.alloc(nTri * 8)); CUDA_TRY(ctx, dKeysAlt.alloc(nTri * 8));
+	CUDA_TRY(ctx, dVals.alloc(nTri * 4)); CUDA_TRY(ctx, dValsAlt.alloc(nTri * 4));
+	float3 bmin = make_float3(tmin[0], tmin[1], tmin[2]);
+	float3 invExt = make_float3(tmax[0] > tmin[0] ? 1.0f / (tmax[0] - tmin[0]) : 0.0f,
+		tmax[1] > tmin[1] ? 1.0f / (tmax[1] - tmin[1]) : 0.0f, tmax[2] > tmin[2] ? 1.0f / (tmax[2] - tmin[2]) : 0.0f);
+	k_morton<<<blocksFor(nTri, 256), 256, 0, st>>>(dTriLo.as<float4>(), dTriHi.as<float4>(), (uint32_t) nTri, bmin, invExt,
+		dKeys.as<uint64_t>(), dVals.as<uint32_t>());
+	CUDA_TRY(ctx, cudaGetLastError());
+	{
+		cub::DoubleBuffer<uint64_t> kb(dKeys.as<uint64_t>(), dKeysAlt.as<uint64_t>());
+		cub::DoubleBuffer<uint32_t> vb(dVals.as<uint32_t>(), dValsAlt.as<uint32_t>());
+		size_t tempBytes = 0;
+		CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tempBytes, kb, vb, n, 0, 63, st));
+		CUDA_TRY(ctx, dTemp.alloc(tempBytes));
+		CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(dTemp.p, tempBytes, kb, vb, n, 0, 63, st));
+		if (kb.Current() != dKeys.as<uint64_t>()) std::swap(dKeys.p, dKeysAlt.p);
+		if (vb.Current() != dVals.as<uint32_t>()) std::swap(dVals.p, dValsAlt.p);
+	}
+	const uint64_t *keys = dKeys.as<uint64_t>();
+	const uint32_t *sortedIdx = dVals.as<uint32_t>();
+
+	// ---- binary radix tree + refit ----
+	const size_t nBin = 2 * nTri - 1;
+	CUDA_TRY(ctx, dChildren.alloc(std::max<size_t>(nTri - 1, 1) * sizeof(int2)));
+	CUDA_TRY(ctx, dRange.alloc(std::max<size_t>(nTri - 1, 1) * sizeof(int2)));
+	CUDA_TRY(ctx, dParent.alloc(nBin * sizeof(int)));
+	CUDA_TRY(ctx, dFlags.alloc(std::max<size_t>(nTri - 1, 1) * sizeof(int)));
+	CUDA_TRY(ctx, dBoxLo.alloc(nBin * sizeof(float4)));
+	CUDA_TRY(ctx, dBoxHi.alloc(nBin * sizeof(float4)));
+	CUDA_TRY(ctx, cudaMemsetAsync(dFlags.p, 0, dFlags.bytes, st));
+	CUDA_TRY(ctx, cudaMemsetAsync(dParent.p, 0xFF, nBin * sizeof(int), st));
+	if (n > 1) {
+		k_lbvh_hierarchy<<<blocksFor(nTri - 1, 256), 256, 0, st>>>(keys, n, dChildren.as<int2>(), dRange.as<int2>(), dParent.as<int>());
+		CUDA_TRY(ctx, cudaGetLastError());
+	}
+	const float pad = 4e-6f * std::max(maxAbs, 1e-3f);
+	k_refit<<<blocksFor(nTri, 256), 256, 0, st>>>(sortedIdx, dTriLo.as<float4>(), dTriHi.as<float4>(), n, pad,
+		dChildren.as<int2>(), dParent.as<int>(), dFlags.as<int>(), dBoxLo.as<float4>(), dBoxHi.as<float4>());
+	CUDA_TRY(ctx, cudaGetLastError());
+
+	// ---- collapse to 4-wide nodes ----
+	const size_t maxNodes = nTri + 1;
+	CUDA_TRY(ctx, dNodesTmp.alloc(maxNodes * sizeof(BVH4Node)));
+	uint32_t nodeCount = 1;
+	if (n == 1) {
+		float4 lo, hi;
+		CUDA_TRY(ctx, cudaMemcpyAsync(&lo, dBoxLo.p, sizeof(float4), cudaMemcpyDeviceToHost, st));
+		CUDA_TRY(ctx, cudaMemcpyAsync(&hi, dBoxHi.p, sizeof(float4), cudaMemcpyDeviceToHost, st));
+		CUDA_TRY(ctx, cudaStreamSynchronize(st));
+		BVH4Node nd;
+		const float inf = INFINITY;
+		nd.lox = make_float4(lo.x, inf, inf, inf); nd.loy = make_float4(lo.y, inf, inf, inf); nd.loz = make_float4(lo.z, inf, inf, inf);
+		nd.hix = make_float4(hi.x, -inf, -inf, -inf); nd.hiy = make_float4(hi.y, -inf, -inf, -inf); nd.hiz = make_float4(hi.z, -inf, -inf, -inf);
+		nd.child = make_uint4(BVH_LEAF | 0u, BVH_EMPTY, BVH_EMPTY, BVH_EMPTY);
+		nd.pad = make_uint4(0, 0, 0, 0);
+		CUDA_TRY(ctx, cudaMemcpyAsync(dNodesTmp.p, &nd, sizeof(nd), cudaMemcpyHostToDevice, st));
+	} else {
+		const size_t qCap = nTri / 4 + 64;
+		CUDA_TRY(ctx, dQ0.alloc(qCap * sizeof(uint2))); CUDA_TRY(ctx, dQ1.alloc(qCap * sizeof(uint2)));
+		CUDA_TRY(ctx, dCounts.alloc(2 * sizeof(uint32_t)));
+		uint2 rootItem = make_uint2(0u, 0u);
+		CUDA_TRY(ctx, cudaMemcpyAsync(dQ0.p, &rootItem, sizeof(rootItem), cudaMemcpyHostToDevice, st));
+		uint32_t counts[2] = { 0u, 1u };   // [queue-out count, node count]
+		uint32_t nIn = 1;
+		uint2 *qIn = dQ0.as<uint2>(), *qOut = dQ1.as<uint2>();
+		while (nIn > 0) {
+			counts[0] = 0;
+			CUDA_TRY(ctx, cudaMemcpyAsync(dCounts.p, counts, sizeof(counts), cudaMemcpyHostToDevice, st));
+			k_collapse<<<blocksFor(nIn, 128), 128, 0, st>>>(qIn, nIn, qOut, dCounts.as<uint32_t>(), dCounts.as<uint32_t>() + 1,
+				n, dChildren.as<int2>(), dRange.as<int2>(), dBoxLo.as<float4>(), dBoxHi.as<float4>(), dNodesTmp.as<BVH4Node>());
+			CUDA_TRY(ctx, cudaGetLastError());
+			CUDA_TRY(ctx, cudaMemcpyAsync(counts, dCounts.p, sizeof(counts), cudaMemcpyDeviceToHost, st));
+			CUDA_TRY(ctx, cudaStreamSynchronize(st));
+			nIn = counts[0];
+			REQUIRE(ctx, nIn <= qCap, MTSGPU_ERR_LIMIT, "BVH collapse queue overflow (%u > %zu)", nIn, qCap);
+			std::swap(qIn, qOut);
+		}
+		nodeCount = counts[1];
+	}
+	CUDA_TRY(ctx, ctx->dNodes.alloc((size_t) nodeCount * sizeof(BVH4Node)));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dNodes.p, dNodesTmp.p, (size_t) nodeCount * sizeof(BVH4Node), cudaMemcpyDeviceToDevice, st));
+	k_reorder<<<blocksFor(nTri, 256), 256, 0, st>>>(sortedIdx, ctx->dTriAccelOrig.as<TriAccelRec>(), (uint32_t) nTri, ctx->dTriAccel.as<TriAccelRec>());
+	CUDA_TRY(ctx, cudaGetLastError());
+	CUDA_TRY(ctx, cudaEventRecord(e1, st));
+	CUDA_TRY(ctx, cudaStreamSynchronize(st));
+	float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+
+	sc.triAccel = ctx->dTriAccel.as<float4>();
+	sc.nodes = ctx->dNodes.as<float4>();
+	sc.triIdx = ctx->dTriIdx.as<uint4>();
+	sc.positions = ctx->dPositions.as<float4>();
+	sc.normals = ctx->dNormals.as<float4>();
+	sc.shapes = ctx->dShapes.as<ShapeInfo>();
+	sc.materials = ctx->dMaterials.as<MaterialDev>();
+	sc.areaCdf = ctx->dAreaCdf.as<float>();
+	sc.nShapes = (uint32_t) nShapes;
+	sc.nTris = (uint32_t) nTri;
+	sc.rootIsLeaf = 0;
+	ctx->accel.triangles = nTri;
+	ctx->accel.nodes = nodeCount;
+	ctx->accel.nodeBytes = (uint64_t) nodeCount * sizeof(BVH4Node);
+	ctx->accel.triBytes = (uint64_t) nTri * sizeof(TriAccelRec);
+	ctx->accel.buildMs = ms;
+	ctx->built = true;
+	ctx->lumImportance = -1;
+	return rebuildLuminaireCdf(ctx, true);
+}

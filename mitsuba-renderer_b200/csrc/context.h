@@ -1,0 +1,85 @@
+// Host-side context of libmtscuda: owns the uploaded scene, the acceleration structure and
+// the wavefront queues of one GPU. Internal; the C ABI in include/mtsgpu.h is the only surface.
+#pragma once
+#include <string>
+#include <vector>
+#include <cstdio>
+#include <cstdarg>
+#include "types.cuh"
+
+struct DevBuf {
+	void *p = nullptr; size_t bytes = 0;
+	DevBuf() {}
+	DevBuf(const DevBuf &) = delete;
+	DevBuf &operator=(const DevBuf &) = delete;
+	~DevBuf() { release(); }
+	void release() { if (p) cudaFree(p); p = nullptr; bytes = 0; }
+	cudaError_t alloc(size_t n) {           // grow-only
+		if (n <= bytes && p) return cudaSuccess;
+		release();
+		cudaError_t e = cudaMalloc(&p, n ? n : 16);
+		if (e == cudaSuccess) bytes = n ? n : 16;
+		return e;
+	}
+	template <typename T> T *as() const { return static_cast<T *>(p); }
+};
+
+struct HostMesh {
+	uint32_t nVert, nTri; int materialId, emitterId; bool hasNormals;
+	std::vector<float> pos, nrm; std::vector<uint32_t> tri;
+};
+
+struct mtsgpu_ctx {
+	int device = 0;
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev[8] = {};
+	std::string error;
+
+	// host-side scene staging
+	std::vector<mtsgpu_material> materials;
+	std::vector<mtsgpu_emitter> emitters;
+	std::vector<HostMesh> meshes;
+	std::vector<int> emitterShape;   // emitter id -> shape index
+	int lumImportance = -1;          // which luminaire CDF is on the device (-1: none)
+	CameraDev camera; bool haveCamera = false;
+	FilmDev film; bool haveFilm = false;
+	float filterTable[256];
+
+	// device scene
+	bool built = false;
+	DeviceScene scene;
+	DevBuf dTriAccel, dTriAccelOrig, dNodes, dTriIdx, dPositions, dNormals, dShapes, dMaterials, dEmitters,
+	       dLumCdf, dAreaCdf;
+	mtsgpu_accel_info accel = {};
+
+	// trace staging + counters
+	DevBuf dRays, dHits, dCounters;
+	bool countersEnabled = false;
+	mtsgpu_trace_counters lastCounters = {};
+
+	// wavefront state (integrate.cu)
+	DevBuf dPathState, dRayA, dRayB, dHit, dShadowRay, dShadowPayload, dQueueA, dQueueB, dQueueCounts,
+	       dResult, dFilm, dStage, dStageOut;
+	uint32_t pathCapacity = 0;
+};
+
+int setError(mtsgpu_ctx *ctx, int code, const char *fmt, ...);
+
+#define CUDA_TRY(ctx, expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) \
+	return setError((ctx), MTSGPU_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); } while (0)
+
+#define REQUIRE(ctx, cond, code, ...) do { if (!(cond)) return setError((ctx), (code), __VA_ARGS__); } while (0)
+
+// bvh_build.cu
+int buildAccel(mtsgpu_ctx *ctx);
+int rebuildLuminaireCdf(mtsgpu_ctx *ctx, bool importance);
+// trace.cu
+int launchTrace(mtsgpu_ctx *ctx, const float4 *dRays, size_t n, int mode, void *dOut, uint64_t *dCounters);
+// integrate.cu
+int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, volatile const int *cancel,
+	float *dOutFilm, mtsgpu_stats *stats);
+int hookBsdfEval(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out);
+int hookEmitterSample(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out);
+int hookCameraRays(mtsgpu_ctx *ctx, const float *samples, size_t n, float *out);
+int hookFilmSplat(mtsgpu_ctx *ctx, const float *samples, size_t n, float *outFilm);
+int hookIntersectFull(mtsgpu_ctx *ctx, const float *rays, size_t n, mtsgpu_hit *hits, float *out);

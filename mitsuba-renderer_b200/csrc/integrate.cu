@@ -1,0 +1,781 @@
+// Wavefront path / direct-lighting integrator. Replaces, for one GPU and one sample range,
+//   SampleIntegrator::render + BlockedRenderProcess + renderBlock   (src/librender/integrator.cpp:87-268,
+//                                                                    src/librender/renderproc.cpp:106-160)
+//   MIPathTracer::Li                                               (src/integrators/path/path.cpp:47-216)
+//   MIDirectIntegrator::Li                                         (src/integrators/direct/direct.cpp:63-203)
+//   ImageBlock::putSample + Film::putImageBlock                    (include/mitsuba/render/imageblock.h:80-138)
+//
+// The recursion of Li() becomes a loop over SoA queues in HBM:
+//   k_generate        one camera ray per (pixel, sample) slot of the batch
+//   k_closest_wf      closest hit for the active ray queue            (trace.cuh)
+//   k_shade<MODE>     finish the previous bounce (MIS-weighted emitter hit, roulette, throughput),
+//                     then at the new hit: emission, next-event estimation -> shadow queue,
+//                     BSDF sampling -> next ray queue (warp-aggregated compaction)
+//   k_shadow_wf       any-hit for the shadow queue; unoccluded contributions are added to the path
+//   k_splat           per 16x16 tile: reconstruction-filter splat into shared memory, then one
+//                     coalesced flush to the film accumulators {sum spec, sum alpha, sum weight}
+// Batches are whole tiles x a chunk of samples, slot = (tile, sample, pixel-in-tile): a warp holds 32
+// neighbouring pixels of one sample index, so primary rays are coherent and a warp's splats never
+// collide on one pixel under the box filter.
+#include "context.h"
+#include "trace.cuh"
+#include "bsdf.cuh"
+#include "sampling.cuh"
+#include <algorithm>
+
+#define TILE 16
+#define TILE_PIX (TILE * TILE)
+#define WF_BLOCK 128
+
+// path-state flag word
+#define PF_DEPTH_MASK   0x0000FFFFu
+#define PF_EMITTED      0x00010000u   // EEmittedRadiance still set (camera hit only, path.cpp:191)
+#define PF_PREV_DELTA   0x00020000u   // previous BSDF sample was a delta lobe
+#define PF_PREV_TRANS   0x00040000u   // previous BSDF sample was transmission
+#define PF_PENDING      0x00080000u   // a BSDF-sampled ray is in flight (steps 7-8 of the loop are outstanding)
+
+struct WfArrays {
+	float4 *thr;        // per slot: throughput.rgb, previous bsdfPdf
+	float4 *li;         // per slot: Li.rgb, alpha
+	float4 *bsdfVal;    // per slot: previous bsdfVal.rgb (f*cos/pdf), flag word
+	float2 *samplePos;  // per slot: film sample position; x = NaN marks a slot outside the crop window
+	uint32_t *slotCur, *slotNext;     // ray queues: slot ids by queue position
+	float4 *rayCur, *rayNext;         // 2 x float4 per queue position
+	uint4 *hit;                       // per queue position {t, u, v, sorted triangle}
+	float4 *shadowRay;                // 2 x float4 per shadow-queue position
+	float4 *shadowPayload;            // contribution.rgb, slot
+	uint32_t *counters;               // [0] next-queue count, [1] shadow-queue count
+	// direct mode keeps the primary hit while secondary rays are traced
+	uint32_t *slotPrim; float4 *rayPrim; uint4 *hitPrim;
+};
+
+struct BatchDesc {
+	uint32_t tileBegin, tileCount;       // tiles of this batch (row-major tile index over the crop window)
+	uint32_t tilesX;
+	uint32_t sampleBegin, sampleCount;   // global sample indices [sampleBegin, sampleBegin + sampleCount)
+	uint32_t slots;                      // tileCount * sampleCount * TILE_PIX
+	uint32_t seed;
+};
+
+struct IntegratorDev {
+	int mode, maxDepth, rrDepth, strictNormals, nLum, nBsdf;
+	int importance;
+};
+
+namespace {
+
+__device__ __forceinline__ uint32_t warpAppend(uint32_t *counter, bool pred) {
+	// warp-aggregated queue append: one atomic per warp, ballot + prefix popcount for the lane offset
+	const uint32_t mask = __ballot_sync(0xFFFFFFFFu, pred);
+	if (mask == 0) return 0;
+	const int lane = threadIdx.x & 31;
+	const int leader = __ffs(mask) - 1;
+	uint32_t base = 0;
+	if (lane == leader) base = atomicAdd(counter, (uint32_t) __popc(mask));
+	base = __shfl_sync(0xFFFFFFFFu, base, leader);
+	return base + __popc(mask & ((1u << lane) - 1u));
+}
+
+__device__ __forceinline__ void slotToPixel(const BatchDesc &b, const FilmDev &film, uint32_t slot,
+		int &px, int &py, uint32_t &sample) {
+	const uint32_t pix = slot % TILE_PIX;
+	const uint32_t rest = slot / TILE_PIX;
+	const uint32_t s = rest % b.sampleCount;
+	const uint32_t tile = b.tileBegin + rest / b.sampleCount;
+	px = (int) ((tile % b.tilesX) * TILE + pix % TILE);
+	py = (int) ((tile / b.tilesX) * TILE + pix / TILE);
+	sample = b.sampleBegin + s;
+}
+
+__global__ void __launch_bounds__(WF_BLOCK)
+k_generate(const CameraDev cam, const FilmDev film, const BatchDesc b, WfArrays wf) {
+	const uint32_t slot = blockIdx.x * WF_BLOCK + threadIdx.x;
+	bool alive = false;
+	float4 r0, r1;
+	if (slot < b.slots) {
+		int px, py; uint32_t sample;
+		slotToPixel(b, film, slot, px, py, sample);
+		if (px < film.cropW && py < film.cropH) {
+			alive = true;
+			const int fx = px + film.cropX, fy = py + film.cropY;     // sensor pixel
+			Sampler smp; smp.init((uint32_t) (fy * film.width + fx), sample, b.seed);
+			float lx = 0, ly = 0, sx, sy;
+			if (cam.apertureRadius > 0.0f) smp.get2D(DIM_LENS, lx, ly);      // renderBlock: lens, time, then pixel sample
+			smp.get2D(DIM_PIXEL, sx, sy);
+			sx += (float) fx; sy += (float) fy;
+			V3 o, d; float mint, maxt;
+			cameraRay(cam, sx, sy, lx, ly, o, d, mint, maxt);
+			r0 = make_float4(o.x, o.y, o.z, mint);
+			r1 = make_float4(d.x, d.y, d.z, maxt);
+			wf.samplePos[slot] = make_float2(sx, sy);
+			wf.thr[slot] = make_float4(1, 1, 1, 0);
+			wf.li[slot] = make_float4(0, 0, 0, 0);
+			wf.bsdfVal[slot] = make_float4(0, 0, 0, __uint_as_float(1u | PF_EMITTED));   // depth = 1 (integrator.h:186-191)
+		} else {
+			wf.samplePos[slot] = make_float2(__int_as_float(0x7FC00000), 0);
+		}
+	}
+	const uint32_t pos = warpAppend(&wf.counters[0], alive);
+	if (alive) {
+		wf.slotNext[pos] = slot;
+		wf.rayNext[2 * (size_t) pos] = r0;
+		wf.rayNext[2 * (size_t) pos + 1] = r1;
+	}
+}
+
+__global__ void __launch_bounds__(TRACE_BLOCK)
+k_closest_wf(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint4 *__restrict__ hits) {
+	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
+	const uint32_t i = blockIdx.x * TRACE_BLOCK + threadIdx.x;
+	if (i >= n) return;
+	const float4 a = __ldg(rays + 2 * (size_t) i), b = __ldg(rays + 2 * (size_t) i + 1);
+	RayIn r = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+	HitOut ho; ho.t = INFINITY; ho.u = ho.v = 0; ho.tri = 0xFFFFFFFFu;
+	float mint, maxt; uint32_t c0 = 0, c1 = 0;
+	if (clipToScene<false>(sc, r, mint, maxt))
+		traverse<false, false>(sc, r, mint, maxt, sstack, ho, c0, c1);
+	hits[i] = make_uint4(__float_as_uint(ho.t), __float_as_uint(ho.u), __float_as_uint(ho.v), ho.tri);
+}
+
+__global__ void __launch_bounds__(TRACE_BLOCK)
+k_shadow_wf(const DeviceScene sc, const float4 *__restrict__ rays, const float4 *__restrict__ payload, uint32_t n, float4 *li) {
+	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
+	const uint32_t i = blockIdx.x * TRACE_BLOCK + threadIdx.x;
+	if (i >= n) return;
+	const float4 a = __ldg(rays + 2 * (size_t) i), b = __ldg(rays + 2 * (size_t) i + 1);
+	RayIn r = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+	float mint, maxt; uint32_t c0 = 0, c1 = 0;
+	bool occluded = false;
+	if (clipToScene<true>(sc, r, mint, maxt)) {
+		HitOut ho;
+		occluded = traverse<true, false>(sc, r, mint, maxt, sstack, ho, c0, c1);
+	}
+	if (!occluded) {
+		const float4 p = __ldg(payload + i);
+		const uint32_t slot = __float_as_uint(p.w);
+		float4 l = li[slot];                 // one shadow ray per slot and pass: plain read-modify-write
+		l.x += p.x; l.y += p.y; l.z += p.z;
+		li[slot] = l;
+	}
+}
+
+__device__ __forceinline__ float miWeight(float pdfA, float pdfB) {     // path.cpp:218-222 (power heuristic)
+	pdfA *= pdfA; pdfB *= pdfB;
+	return pdfA / (pdfA + pdfB);
+}
+
+// Next-event estimation at `its` (path.cpp:97-125 / direct.cpp:128-150). Returns true and fills the
+// shadow ray + contribution when a visibility test is needed.
+__device__ __forceinline__ bool nextEvent(const DeviceScene &sc, const IntegratorDev &ig, const Isect &its,
+		const MaterialDev &mat, V3 rayD, V3 scale, float sx, float sy, float fracLum, float fracBsdf, float weightLum,
+		float4 &s0, float4 &s1, V3 &contrib) {
+	LumSample ls;
+	sampleLuminaire(sc, its.p, sx, sy, ig.importance != 0, ls);
+	if (ls.pdf == 0) return false;
+	const V3 wo = -ls.d;
+	const V3 woLocal = toLocal(its.sh, wo);
+	const V3 f = bsdfF(mat, its.wi, woLocal);
+	const V3 bsdfVal = f * fabsf(woLocal.z);                               // fCos
+	if (isZero(bsdfVal)) return false;
+	if (ig.strictNormals && !(dot(its.geoN, wo) * woLocal.z > 0)) return false;
+	const float bPdf = bsdfPdf(mat, its.wi, woLocal);                      // area luminaires are intersectable
+	const float weight = miWeight(ls.pdf * fracLum, bPdf * fracBsdf) * weightLum;
+	contrib = ((scale * ls.value) * bsdfVal) * weight;
+	// Scene::isOccluded(p1, p2): Ray(p1, p2 - p1, ShadowEpsilon, 1 - ShadowEpsilon) (scene.h:241-246)
+	const V3 dd = ls.p - its.p;
+	s0 = make_float4(its.p.x, its.p.y, its.p.z, MTS_SHADOW_EPSILON);
+	s1 = make_float4(dd.x, dd.y, dd.z, 1.0f - MTS_SHADOW_EPSILON);
+	return true;
+}
+
+// One shading step for the queue entry i. MODE 0 = path, 1 = direct (primary pass), 2 = direct (secondary pass).
+template <int MODE>
+__global__ void __launch_bounds__(WF_BLOCK)
+k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const FilmDev film, WfArrays wf, uint32_t n, uint32_t round) {
+	const uint32_t i = blockIdx.x * WF_BLOCK + threadIdx.x;
+	bool emitRay = false, emitShadow = false;
+	float4 nr0, nr1, sr0, sr1; V3 contrib = v3(0, 0, 0);
+	uint32_t slot = 0;
+
+	if (i < n) {
+		const uint32_t *slots = (MODE == 1) ? wf.slotPrim : wf.slotCur;
+		const float4 *rays = (MODE == 1) ? wf.rayPrim : wf.rayCur;
+		const uint4 *hits = (MODE == 1) ? wf.hitPrim : wf.hit;
+		slot = slots[i];
+		const float4 ra = rays[2 * (size_t) i], rb = rays[2 * (size_t) i + 1];
+		const uint4 h = hits[i];
+		const V3 rayO = v3(ra), rayD = v3(rb);
+		const bool valid = h.w != 0xFFFFFFFFu;
+		float4 thr4 = wf.thr[slot], li4 = wf.li[slot], bv4 = wf.bsdfVal[slot];
+		uint32_t flags = __float_as_uint(bv4.w);
+		uint32_t depth = flags & PF_DEPTH_MASK;
+		V3 thr = v3(thr4), Li = v3(li4);
+		int px, py; uint32_t sample;
+		slotToPixel(b, film, slot, px, py, sample);
+		Sampler smp; smp.init((uint32_t) ((py + film.cropY) * film.width + px + film.cropX), sample, b.seed);
+
+		Isect its;
+		bool alive = valid;
+		if (valid) {
+			const float4 q2 = __ldg(sc.triAccel + (size_t) h.w * 3 + 2);
+			fillIntersection(sc, __float_as_uint(q2.z), __float_as_uint(q2.w), __uint_as_float(h.y), __uint_as_float(h.z), rayD, its);
+		}
+
+		if (MODE == 2) {
+			// direct.cpp:170-199: BSDF-sampled ray hit something — only emitters contribute
+			if (valid && its.emitterId >= 0) {
+				const V3 Le = emitterLe(sc, its.emitterId, its.geoN, -rayD);
+				const float lumPdf = (flags & PF_PREV_DELTA) ? 0.0f : pdfLuminaire(sc, rayO, its.p, its.geoN, its.emitterId, ig.importance != 0);
+				const float total = (float) (ig.nLum + ig.nBsdf);          // direct.cpp:49-54
+				const float fracBsdf = ig.nBsdf / total, fracLum = ig.nLum / total;
+				const float weightBsdf = 1 / (float) ig.nBsdf;
+				const float w = miWeight(thr4.w * fracBsdf, lumPdf * fracLum) * weightBsdf;
+				Li = Li + (Le * v3(bv4)) * w;
+				wf.li[slot] = make_float4(Li.x, Li.y, Li.z, li4.w);
+			}
+			alive = false;
+		} else {
+			if (MODE == 0 && (flags & PF_PENDING)) {
+				// ---- steps after "trace a ray in this direction" of the previous iteration (path.cpp:152-208)
+				const V3 bsdfVal = v3(bv4);
+				if (!valid) {
+					depth++;                                   // path.cpp:166
+					alive = false;
+				} else {
+					if (its.emitterId >= 0) {
+						const V3 Le = emitterLe(sc, its.emitterId, its.geoN, -rayD);
+						const float lumPdf = (flags & PF_PREV_DELTA) ? 0.0f : pdfLuminaire(sc, rayO, its.p, its.geoN, its.emitterId, ig.importance != 0);
+						const float w = miWeight(thr4.w, lumPdf);
+						Li = Li + ((thr * Le) * bsdfVal) * w;
+					}
+					flags &= ~PF_EMITTED;                      // rRec.type = ERadianceNoEmission
+					bool survive = true;
+					if ((int) depth >= ig.rrDepth && !(flags & PF_PREV_TRANS)) {
+						const float approxAlbedo = fminf(0.9f, maxc(bsdfVal));
+						if (smp.get1D(DIM_BOUNCE(depth - 1, 2)) > approxAlbedo) survive = false;
+						else thr = thr * (1.0f / approxAlbedo);
+					}
+					if (survive) { thr = thr * bsdfVal; depth++; }
+					else alive = false;
+				}
+			} else if (MODE == 0 || round == 0) {
+				// camera hit: rRec.alpha (records.inl:93-99)
+				li4.w = valid ? 1.0f : 0.0f;
+			}
+
+			// ---- top of the loop body at the new hit (path.cpp:58-95 / direct.cpp:74-100)
+			if (alive && its.materialId < 0 && its.emitterId >= 0 && (flags & PF_EMITTED) && (MODE == 0 || round == 0)) {
+				// direct.cpp adds emission before the BSDF check; path.cpp checks the BSDF first
+				if (MODE == 1) Li = Li + emitterLe(sc, its.emitterId, its.geoN, -rayD);
+			}
+			if (alive && its.materialId < 0) alive = false;             // no BSDF: give up (path.cpp:70-77)
+			MaterialDev mat;
+			if (alive) {
+				mat = sc.materials[its.materialId];
+				if (its.emitterId >= 0 && (flags & PF_EMITTED) && (MODE == 0 || round == 0))
+					Li = Li + (MODE == 0 ? thr : v3(1, 1, 1)) * emitterLe(sc, its.emitterId, its.geoN, -rayD);
+				if (MODE == 0 && ig.maxDepth > 0 && (int) depth >= ig.maxDepth) alive = false;
+			}
+			if (alive && MODE == 0 && ig.strictNormals) {
+				const float wiDotGeoN = -dot(its.geoN, rayD);
+				if (wiDotGeoN * its.wi.z < 0) alive = false;
+			}
+			if (alive) {
+				float fracLum = 1.0f, fracBsdf = 1.0f, weightLum = 1.0f, weightBsdf = 1.0f;
+				bool doLum = true, doBsdf = true;
+				uint32_t dimL, dimB;
+				if (MODE == 1) {
+					const float total = (float) (ig.nLum + ig.nBsdf);
+					fracLum = ig.nLum / total; fracBsdf = ig.nBsdf / total;
+					weightLum = 1 / (float) ig.nLum; weightBsdf = 1 / (float) ig.nBsdf;
+					doLum = (int) round < ig.nLum; doBsdf = (int) round < ig.nBsdf;
+					dimL = DIM_DIRECT(round, 0); dimB = DIM_DIRECT(round, 1);
+				} else {
+					dimL = DIM_BOUNCE(depth - 1, 0); dimB = DIM_BOUNCE(depth - 1, 1);
+				}
+				(void) weightBsdf;
+				// ---- luminaire sampling
+				if (doLum) {
+					float sx, sy; smp.get2D(dimL, sx, sy);
+					// delta-only BSDFs have f = 0: the reference still traces the shadow ray, the result is unused
+					if (mat.type != MTSGPU_BSDF_MIRROR && mat.type != MTSGPU_BSDF_DIELECTRIC)
+						emitShadow = nextEvent(sc, ig, its, mat, rayD, MODE == 0 ? thr : v3(1, 1, 1), sx, sy,
+							fracLum, fracBsdf, weightLum, sr0, sr1, contrib);
+				}
+				// ---- BSDF sampling
+				bool cont = false;
+				if (doBsdf) {
+					float sx, sy; smp.get2D(dimB, sx, sy);
+					V3 woLocal; float pdf = 0; uint32_t type = 0;
+					V3 val = bsdfSample3(mat, its.wi, sx, sy, woLocal, pdf, type);
+					if (!isZero(val)) {
+						val = val * fabsf(woLocal.z);                         // sampleCos
+						if (!isZero(val)) {
+							val = val * (1.0f / pdf);                         // bsdfVal /= bsdfPdf
+							const V3 wo = toWorld(its.sh, woLocal);
+							bool ok = true;
+							if (MODE == 0 && ig.strictNormals && dot(its.geoN, wo) * woLocal.z <= 0) ok = false;
+							if (ok) {
+								cont = true;
+								nr0 = make_float4(its.p.x, its.p.y, its.p.z, MTS_EPSILON);
+								nr1 = make_float4(wo.x, wo.y, wo.z, INFINITY);
+								flags &= ~(PF_PREV_DELTA | PF_PREV_TRANS);
+								if (type & BSDF_DELTA) flags |= PF_PREV_DELTA;
+								if (type & BSDF_TRANSMISSION) flags |= PF_PREV_TRANS;
+								flags |= PF_PENDING;
+								bv4 = make_float4(val.x, val.y, val.z, 0);
+								thr4.w = pdf;
+							}
+						}
+					}
+				}
+				emitRay = cont;
+				if (MODE == 0 && !cont) alive = false;
+			}
+			flags = (flags & ~PF_DEPTH_MASK) | (depth & PF_DEPTH_MASK);
+			wf.li[slot] = make_float4(Li.x, Li.y, Li.z, li4.w);
+			if (emitRay) {
+				wf.thr[slot] = make_float4(thr.x, thr.y, thr.z, thr4.w);
+				wf.bsdfVal[slot] = make_float4(bv4.x, bv4.y, bv4.z, __uint_as_float(flags));
+			}
+		}
+	}
+
+	const uint32_t rp = warpAppend(&wf.counters[0], emitRay);
+	if (emitRay) {
+		wf.slotNext[rp] = slot;
+		wf.rayNext[2 * (size_t) rp] = nr0;
+		wf.rayNext[2 * (size_t) rp + 1] = nr1;
+	}
+	const uint32_t sp = warpAppend(&wf.counters[1], emitShadow);
+	if (emitShadow) {
+		wf.shadowRay[2 * (size_t) sp] = sr0;
+		wf.shadowRay[2 * (size_t) sp + 1] = sr1;
+		wf.shadowPayload[sp] = make_float4(contrib.x, contrib.y, contrib.z, __uint_as_float(slot));
+	}
+}
+
+// ImageBlock::putSample (imageblock.h:80-138) for all samples of one tile, accumulated in shared
+// memory over the tile plus the filter border, then flushed once.
+__global__ void __launch_bounds__(TILE_PIX)
+k_splat(const FilmDev film, const BatchDesc b, const float4 *__restrict__ li, const float2 *__restrict__ samplePos,
+		const float *__restrict__ filterTable, float *filmAcc) {
+	extern __shared__ float acc[];          // (TILE + 2*border)^2 * 5
+	__shared__ float table[256];
+	const int border = film.border;
+	const int side = TILE + 2 * border;
+	const int nAcc = side * side * 5;
+	for (int k = threadIdx.x; k < nAcc; k += TILE_PIX) acc[k] = 0.0f;
+	table[threadIdx.x] = filterTable[threadIdx.x];
+	__syncthreads();
+
+	const uint32_t tile = b.tileBegin + blockIdx.x;
+	const int tx0 = (int) (tile % b.tilesX) * TILE, ty0 = (int) (tile / b.tilesX) * TILE;   // crop-relative
+	const size_t base = (size_t) blockIdx.x * b.sampleCount * TILE_PIX;
+	const uint32_t nSlots = b.sampleCount * TILE_PIX;
+	const bool box = (border == 0);
+	for (uint32_t k = threadIdx.x; k < nSlots; k += TILE_PIX) {
+		const float2 sp = samplePos[base + k];
+		if (sp.x != sp.x) continue;                              // slot outside the crop window
+		const float4 v = li[base + k];
+		// !spec.isValid(): NaN or negative components drop the sample (imageblock.h:85-88)
+		if (v.x != v.x || v.y != v.y || v.z != v.z || v.x < 0.0f || v.y < 0.0f || v.z < 0.0f) continue;
+		// position relative to this tile's accumulator (block offset = tile origin, same border)
+		const float fx = sp.x - 0.5f - (float) (film.cropX + tx0 - border);
+		const float fy = sp.y - 0.5f - (float) (film.cropY + ty0 - border);
+		int xStart = (int) ceilf(fx - film.filterSizeX), xEnd = (int) floorf(fx + film.filterSizeX);
+		int yStart = (int) ceilf(fy - film.filterSizeY), yEnd = (int) floorf(fy + film.filterSizeY);
+		xStart = max(0, xStart); yStart = max(0, yStart);
+		xEnd = min(xEnd, side - 1); yEnd = min(yEnd, side - 1);
+		for (int y = yStart; y <= yEnd; ++y) {
+			const int iy = min((int) (film.factorY * fabsf((float) y - fy)), 15);
+			for (int x = xStart; x <= xEnd; ++x) {
+				const int ix = min((int) (film.factorX * fabsf((float) x - fx)), 15);
+				const float w = table[iy * 16 + ix];
+				float *a = &acc[(y * side + x) * 5];
+				// shared-memory atomics: other warps splat other sample indices into the same pixels
+				atomicAdd(a + 0, v.x * w); atomicAdd(a + 1, v.y * w); atomicAdd(a + 2, v.z * w);
+				atomicAdd(a + 3, v.w * w); atomicAdd(a + 4, w);
+			}
+		}
+	}
+	__syncthreads();
+	// flush: consecutive threads write consecutive floats of a row (5 floats per pixel)
+	const int rowFloats = side * 5;
+	for (int k = threadIdx.x; k < nAcc; k += TILE_PIX) {
+		const int y = k / rowFloats, xf = k % rowFloats;
+		const int gx = tx0 - border + xf / 5, gy = ty0 - border + y;    // crop-relative pixel
+		if (gx < 0 || gy < 0 || gx >= film.cropW || gy >= film.cropH) continue;
+		const float val = acc[k];
+		float *dst = &filmAcc[((size_t) gy * film.cropW + gx) * 5 + xf % 5];
+		if (box) *dst += val;            // tiles are disjoint under the box filter: plain coalesced RMW
+		else if (val != 0.0f) atomicAdd(dst, val);   // borders overlap neighbouring tiles
+	}
+}
+
+__global__ void k_zero(float *p, size_t n) {
+	const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) p[i] = 0.0f;
+}
+
+inline unsigned blocksFor(size_t n, unsigned bs) { return (unsigned) ((n + bs - 1) / bs); }
+
+} // namespace
+
+static int ensureWavefront(mtsgpu_ctx *ctx, uint32_t capacity) {
+	if (ctx->pathCapacity >= capacity) return MTSGPU_OK;
+	const size_t c = capacity;
+	CUDA_TRY(ctx, ctx->dPathState.alloc(c * (16 * 3 + 8)));
+	CUDA_TRY(ctx, ctx->dRayA.alloc(c * 32)); CUDA_TRY(ctx, ctx->dRayB.alloc(c * 32));
+	CUDA_TRY(ctx, ctx->dHit.alloc(c * 16));
+	CUDA_TRY(ctx, ctx->dShadowRay.alloc(c * 32)); CUDA_TRY(ctx, ctx->dShadowPayload.alloc(c * 16));
+	CUDA_TRY(ctx, ctx->dQueueA.alloc(c * 4)); CUDA_TRY(ctx, ctx->dQueueB.alloc(c * 4));
+	CUDA_TRY(ctx, ctx->dQueueCounts.alloc(64));
+	ctx->pathCapacity = capacity;
+	return MTSGPU_OK;
+}
+
+static int uploadFilter(mtsgpu_ctx *ctx, DevBuf &dTable) {
+	CUDA_TRY(ctx, dTable.alloc(256 * sizeof(float)));
+	CUDA_TRY(ctx, cudaMemcpyAsync(dTable.p, ctx->filterTable, 256 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+	return MTSGPU_OK;
+}
+
+int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const int *cancel, float *dOutFilm, mtsgpu_stats *stats) {
+	REQUIRE(ctx, ctx->built, MTSGPU_ERR_ARG, "render: call mtsgpu_build_accel first");
+	REQUIRE(ctx, ctx->haveCamera && ctx->haveFilm, MTSGPU_ERR_ARG, "render: camera and film must be set");
+	REQUIRE(ctx, P->mode == MTSGPU_MODE_PATH || P->mode == MTSGPU_MODE_DIRECT, MTSGPU_ERR_ARG, "render: unknown mode %d", P->mode);
+	REQUIRE(ctx, P->sppBegin <= P->sppEnd && P->sppEnd <= P->sppTotal, MTSGPU_ERR_ARG, "render: bad sample range [%u, %u) of %u", P->sppBegin, P->sppEnd, P->sppTotal);
+	if (P->mode == MTSGPU_MODE_DIRECT)
+		REQUIRE(ctx, P->luminaireSamples >= 0 && P->bsdfSamples >= 0 && P->luminaireSamples + P->bsdfSamples > 0, MTSGPU_ERR_ARG, "render: luminaireSamples + bsdfSamples must be > 0");
+	cudaStream_t st = ctx->stream;
+	const FilmDev film = ctx->film;
+	const size_t filmFloats = (size_t) film.cropW * film.cropH * 5;
+	{
+		int rc = rebuildLuminaireCdf(ctx, P->importanceSampleLuminaires != 0);
+		if (rc) return rc;
+	}
+	DevBuf dTable;
+	{ int rc = uploadFilter(ctx, dTable); if (rc) return rc; }
+
+	k_zero<<<blocksFor(filmFloats, 256), 256, 0, st>>>(dOutFilm, filmFloats);
+	CUDA_TRY(ctx, cudaGetLastError());
+	mtsgpu_stats S; memset(&S, 0, sizeof(S));
+	S.kernelLaunches = 1;
+
+	const uint32_t tilesX = (film.cropW + TILE - 1) / TILE, tilesY = (film.cropH + TILE - 1) / TILE;
+	const uint32_t nTiles = tilesX * tilesY;
+	const uint32_t spp = P->sppEnd - P->sppBegin;
+	cudaEvent_t evBegin = ctx->ev[0], evEnd = ctx->ev[1], evA = ctx->ev[2], evB = ctx->ev[3];
+	CUDA_TRY(ctx, cudaEventRecord(evBegin, st));
+	if (spp > 0) {
+		const uint32_t maxSlots = 1u << 23;
+		uint32_t sampleChunk = std::min<uint32_t>(spp, maxSlots / TILE_PIX);
+		uint32_t tilesPerBatch = std::max<uint32_t>(1u, std::min<uint32_t>(nTiles, maxSlots / (TILE_PIX * sampleChunk)));
+		const uint32_t capacity = tilesPerBatch * sampleChunk * TILE_PIX;
+		{ int rc = ensureWavefront(ctx, capacity); if (rc) return rc; }
+		DevBuf dPrimSlot, dPrimRay, dPrimHit;
+		if (P->mode == MTSGPU_MODE_DIRECT) {
+			CUDA_TRY(ctx, dPrimSlot.alloc((size_t) capacity * 4));
+			CUDA_TRY(ctx, dPrimRay.alloc((size_t) capacity * 32));
+			CUDA_TRY(ctx, dPrimHit.alloc((size_t) capacity * 16));
+		}
+		WfArrays wf;
+		char *ps = ctx->dPathState.as<char>();
+		wf.thr = (float4 *) ps; wf.li = (float4 *) (ps + (size_t) capacity * 16); wf.bsdfVal = (float4 *) (ps + (size_t) capacity * 32);
+		wf.samplePos = (float2 *) (ps + (size_t) capacity * 48);
+		wf.hit = ctx->dHit.as<uint4>();
+		wf.shadowRay = ctx->dShadowRay.as<float4>(); wf.shadowPayload = ctx->dShadowPayload.as<float4>();
+		wf.counters = ctx->dQueueCounts.as<uint32_t>();
+		wf.slotPrim = dPrimSlot.as<uint32_t>(); wf.rayPrim = dPrimRay.as<float4>(); wf.hitPrim = dPrimHit.as<uint4>();
+		uint32_t *slotBuf[2] = { ctx->dQueueA.as<uint32_t>(), ctx->dQueueB.as<uint32_t>() };
+		float4 *rayBuf[2] = { ctx->dRayA.as<float4>(), ctx->dRayB.as<float4>() };
+
+		IntegratorDev ig;
+		ig.mode = P->mode; ig.maxDepth = P->maxDepth; ig.rrDepth = P->rrDepth; ig.strictNormals = P->strictNormals;
+		ig.nLum = P->luminaireSamples; ig.nBsdf = P->bsdfSamples; ig.importance = (int) P->importanceSampleLuminaires;
+		if (P->mode == MTSGPU_MODE_DIRECT) ig.strictNormals = 0;     // MIDirectIntegrator has no such property
+		const int splatSmem = (TILE + 2 * film.border) * (TILE + 2 * film.border) * 5 * (int) sizeof(float);
+
+		uint32_t *hCounts = nullptr;
+		CUDA_TRY(ctx, cudaMallocHost(&hCounts, 64));
+		int rc = MTSGPU_OK;
+		auto fail = [&](int code) { cudaFreeHost(hCounts); return code; };
+		float msClosest = 0, msShadow = 0;
+
+		for (uint32_t t0 = 0; t0 < nTiles && rc == MTSGPU_OK; t0 += tilesPerBatch) {
+			for (uint32_t s0 = 0; s0 < spp; s0 += sampleChunk) {
+				if (cancel && *cancel) { rc = setError(ctx, MTSGPU_ERR_CANCELLED, "render cancelled"); break; }
+				BatchDesc b;
+				b.tileBegin = t0; b.tileCount = std::min(tilesPerBatch, nTiles - t0); b.tilesX = tilesX;
+				b.sampleBegin = P->sppBegin + s0; b.sampleCount = std::min(sampleChunk, spp - s0);
+				b.slots = b.tileCount * b.sampleCount * TILE_PIX; b.seed = P->seed;
+				int cur = 0;
+				wf.slotNext = slotBuf[cur]; wf.rayNext = rayBuf[cur];
+				CUDA_TRY(ctx, cudaMemsetAsync(wf.counters, 0, 8, st));
+				k_generate<<<blocksFor(b.slots, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->camera, film, b, wf);
+				S.kernelLaunches++;
+				CUDA_TRY(ctx, cudaMemcpyAsync(hCounts, wf.counters, 8, cudaMemcpyDeviceToHost, st));
+				CUDA_TRY(ctx, cudaStreamSynchronize(st));
+				uint32_t nRays = hCounts[0];
+				S.cameraRays += nRays;
+
+				if (P->mode == MTSGPU_MODE_PATH) {
+					while (nRays > 0) {
+						if (cancel && *cancel) { rc = setError(ctx, MTSGPU_ERR_CANCELLED, "render cancelled"); break; }
+						wf.slotCur = slotBuf[cur]; wf.rayCur = rayBuf[cur];
+						wf.slotNext = slotBuf[cur ^ 1]; wf.rayNext = rayBuf[cur ^ 1];
+						cudaEventRecord(evA, st);
+						k_closest_wf<<<blocksFor(nRays, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(ctx->scene, wf.rayCur, nRays, wf.hit);
+						cudaEventRecord(evB, st);
+						S.normalRays += nRays;
+						CUDA_TRY(ctx, cudaMemsetAsync(wf.counters, 0, 8, st));
+						k_shade<0><<<blocksFor(nRays, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nRays, 0);
+						CUDA_TRY(ctx, cudaMemcpyAsync(hCounts, wf.counters, 8, cudaMemcpyDeviceToHost, st));
+						CUDA_TRY(ctx, cudaStreamSynchronize(st));
+						{ float ms = 0; cudaEventElapsedTime(&ms, evA, evB); msClosest += ms; }
+						S.kernelLaunches += 2;
+						const uint32_t nShadow = hCounts[1];
+						if (nShadow > 0) {
+							cudaEventRecord(evA, st);
+							k_shadow_wf<<<blocksFor(nShadow, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(ctx->scene, wf.shadowRay, wf.shadowPayload, nShadow, wf.li);
+							cudaEventRecord(evB, st);
+							CUDA_TRY(ctx, cudaEventSynchronize(evB));
+							{ float ms = 0; cudaEventElapsedTime(&ms, evA, evB); msShadow += ms; }
+							S.shadowRays += nShadow; S.kernelLaunches++;
+						}
+						nRays = hCounts[0];
+						cur ^= 1;
+					}
+				} else {
+					// primary hit once, kept in the *Prim buffers; then `rounds` passes of (NEE, BSDF ray)
+					wf.slotCur = slotBuf[cur]; wf.rayCur = rayBuf[cur];
+					cudaEventRecord(evA, st);
+					k_closest_wf<<<blocksFor(nRays, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(ctx->scene, wf.rayCur, nRays, wf.hitPrim);
+					cudaEventRecord(evB, st);
+					CUDA_TRY(ctx, cudaMemcpyAsync(wf.slotPrim, wf.slotCur, (size_t) nRays * 4, cudaMemcpyDeviceToDevice, st));
+					CUDA_TRY(ctx, cudaMemcpyAsync(wf.rayPrim, wf.rayCur, (size_t) nRays * 32, cudaMemcpyDeviceToDevice, st));
+					CUDA_TRY(ctx, cudaEventSynchronize(evB));
+					{ float ms = 0; cudaEventElapsedTime(&ms, evA, evB); msClosest += ms; }
+					S.normalRays += nRays; S.kernelLaunches++;
+					const uint32_t nPrim = nRays;
+					const int rounds = std::max(P->luminaireSamples, P->bsdfSamples);
+					for (int r = 0; r < rounds; ++r) {
+						wf.slotNext = slotBuf[cur ^ 1]; wf.rayNext = rayBuf[cur ^ 1];
+						CUDA_TRY(ctx, cudaMemsetAsync(wf.counters, 0, 8, st));
+						k_shade<1><<<blocksFor(nPrim, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nPrim, (uint32_t) r);
+						CUDA_TRY(ctx, cudaMemcpyAsync(hCounts, wf.counters, 8, cudaMemcpyDeviceToHost, st));
+						CUDA_TRY(ctx, cudaStreamSynchronize(st));
+						S.kernelLaunches++;
+						const uint32_t nSec = hCounts[0], nShadow = hCounts[1];
+						if (nShadow > 0) {
+							cudaEventRecord(evA, st);
+							k_shadow_wf<<<blocksFor(nShadow, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(ctx->scene, wf.shadowRay, wf.shadowPayload, nShadow, wf.li);
+							cudaEventRecord(evB, st);
+							CUDA_TRY(ctx, cudaEventSynchronize(evB));
+							{ float ms = 0; cudaEventElapsedTime(&ms, evA, evB); msShadow += ms; }
+							S.shadowRays += nShadow; S.kernelLaunches++;
+						}
+						if (nSec > 0) {
+							wf.slotCur = slotBuf[cur ^ 1]; wf.rayCur = rayBuf[cur ^ 1];
+							cudaEventRecord(evA, st);
+							k_closest_wf<<<blocksFor(nSec, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(ctx->scene, wf.rayCur, nSec, wf.hit);
+							cudaEventRecord(evB, st);
+							k_shade<2><<<blocksFor(nSec, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nSec, (uint32_t) r);
+							CUDA_TRY(ctx, cudaStreamSynchronize(st));
+							{ float ms = 0; cudaEventElapsedTime(&ms, evA, evB); msClosest += ms; }
+							S.normalRays += nSec; S.kernelLaunches += 2;
+						}
+					}
+				}
+				if (rc != MTSGPU_OK) break;
+				k_splat<<<b.tileCount, TILE_PIX, splatSmem, st>>>(film, b, wf.li, wf.samplePos, dTable.as<float>(), dOutFilm);
+				S.kernelLaunches++;
+				CUDA_TRY(ctx, cudaGetLastError());
+			}
+		}
+		S.samples = S.cameraRays;
+		S.traceClosestMs = msClosest; S.traceAnyMs = msShadow;
+		if (rc != MTSGPU_OK) return fail(rc);
+		cudaFreeHost(hCounts);
+	}
+	CUDA_TRY(ctx, cudaEventRecord(evEnd, st));
+	CUDA_TRY(ctx, cudaStreamSynchronize(st));
+	CUDA_TRY(ctx, cudaGetLastError());
+	{ float ms = 0; cudaEventElapsedTime(&ms, evBegin, evEnd); S.totalMs = ms; }
+	S.shadeMs = S.totalMs - S.traceClosestMs - S.traceAnyMs;
+	if (stats) *stats = S;
+	return MTSGPU_OK;
+}
+
+// ================================================================================================
+// Per-function test hooks (C ABI: mtsgpu_bsdf_eval, mtsgpu_emitter_sample, mtsgpu_camera_rays,
+// mtsgpu_film_splat, mtsgpu_intersect_full). They run the same device functions as the render loop.
+// ================================================================================================
+namespace {
+
+__global__ void k_hook_bsdf(const DeviceScene sc, const float *q, uint32_t n, uint32_t nMat, float *out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const float *e = q + (size_t) i * 9;
+	float *o = out + (size_t) i * 16;
+	for (int k = 0; k < 16; ++k) o[k] = 0;
+	const uint32_t id = (uint32_t) e[0];
+	if (id >= nMat) return;
+	const MaterialDev m = sc.materials[id];
+	const V3 wi = v3(e[1], e[2], e[3]), wo = v3(e[4], e[5], e[6]);
+	const V3 f = bsdfF(m, wi, wo);
+	o[0] = f.x; o[1] = f.y; o[2] = f.z; o[3] = bsdfPdf(m, wi, wo);
+	V3 swo = v3(0, 0, 0); float pdf = 0; uint32_t type = 0;
+	const V3 s3 = bsdfSample3(m, wi, e[7], e[8], swo, pdf, type);
+	if (!isZero(s3)) {
+		o[4] = swo.x; o[5] = swo.y; o[6] = swo.z; o[7] = s3.x; o[8] = s3.y; o[9] = s3.z; o[10] = pdf; o[11] = (float) type;
+	}
+	const V3 s2 = bsdfSample2(m, wi, e[7], e[8], swo, type);
+	o[12] = s2.x; o[13] = s2.y; o[14] = s2.z;
+}
+
+__global__ void k_hook_emitter(const DeviceScene sc, const float *q, uint32_t n, int importance, float *out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const float *e = q + (size_t) i * 5;
+	float *o = out + (size_t) i * 16;
+	for (int k = 0; k < 16; ++k) o[k] = 0;
+	const V3 p = v3(e[0], e[1], e[2]);
+	LumSample ls;
+	ls.p = ls.n = ls.d = ls.value = v3(0, 0, 0);
+	sampleLuminaire(sc, p, e[3], e[4], importance != 0, ls);
+	o[0] = ls.p.x; o[1] = ls.p.y; o[2] = ls.p.z; o[3] = ls.n.x; o[4] = ls.n.y; o[5] = ls.n.z;
+	if (ls.pdf != 0) {
+		o[6] = ls.d.x; o[7] = ls.d.y; o[8] = ls.d.z; o[9] = ls.pdf;
+		o[10] = ls.value.x; o[11] = ls.value.y; o[12] = ls.value.z; o[13] = (float) ls.emitter;
+		o[14] = pdfLuminaire(sc, p, ls.p, ls.n, ls.emitter, importance != 0);
+	} else {
+		o[13] = -1.0f;
+	}
+}
+
+__global__ void k_hook_camera(const CameraDev cam, const float *q, uint32_t n, float *out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	V3 o, d; float mint, maxt;
+	cameraRay(cam, q[4 * (size_t) i], q[4 * (size_t) i + 1], q[4 * (size_t) i + 2], q[4 * (size_t) i + 3], o, d, mint, maxt);
+	float *r = out + (size_t) i * 8;
+	r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = mint; r[4] = d.x; r[5] = d.y; r[6] = d.z; r[7] = maxt;
+}
+
+__global__ void k_hook_isect(const DeviceScene sc, const float4 *rays, const mtsgpu_hit *hits, uint32_t n, float *out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	float *o = out + (size_t) i * 12;
+	const mtsgpu_hit h = hits[i];
+	if (h.shape == 0xFFFFFFFFu) { for (int k = 0; k < 12; ++k) o[k] = 0; return; }
+	const float4 b = rays[2 * (size_t) i + 1];
+	Isect its;
+	fillIntersection(sc, h.shape, h.prim, h.u, h.v, v3(b), its);
+	o[0] = its.p.x; o[1] = its.p.y; o[2] = its.p.z; o[3] = its.geoN.x; o[4] = its.geoN.y; o[5] = its.geoN.z;
+	o[6] = its.shN.x; o[7] = its.shN.y; o[8] = its.shN.z; o[9] = its.wi.x; o[10] = its.wi.y; o[11] = its.wi.z;
+}
+
+} // namespace
+
+static int upload(mtsgpu_ctx *ctx, DevBuf &buf, const void *src, size_t bytes) {
+	CUDA_TRY(ctx, buf.alloc(bytes));
+	if (bytes) CUDA_TRY(ctx, cudaMemcpyAsync(buf.p, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+	return MTSGPU_OK;
+}
+static int download(mtsgpu_ctx *ctx, void *dst, const DevBuf &buf, size_t bytes) {
+	if (bytes) CUDA_TRY(ctx, cudaMemcpyAsync(dst, buf.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	CUDA_TRY(ctx, cudaGetLastError());
+	return MTSGPU_OK;
+}
+
+int hookBsdfEval(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out) {
+	REQUIRE(ctx, ctx->built, MTSGPU_ERR_ARG, "bsdf_eval: call mtsgpu_build_accel first");
+	if (n == 0) return MTSGPU_OK;
+	int rc;
+	if ((rc = upload(ctx, ctx->dStage, queries, n * 9 * 4))) return rc;
+	CUDA_TRY(ctx, ctx->dStageOut.alloc(n * 16 * 4));
+	k_hook_bsdf<<<blocksFor(n, 128), 128, 0, ctx->stream>>>(ctx->scene, ctx->dStage.as<float>(), (uint32_t) n,
+		(uint32_t) ctx->materials.size(), ctx->dStageOut.as<float>());
+	return download(ctx, out, ctx->dStageOut, n * 16 * 4);
+}
+
+int hookEmitterSample(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out) {
+	REQUIRE(ctx, ctx->built, MTSGPU_ERR_ARG, "emitter_sample: call mtsgpu_build_accel first");
+	if (n == 0) return MTSGPU_OK;
+	int rc;
+	if ((rc = rebuildLuminaireCdf(ctx, true))) return rc;
+	if ((rc = upload(ctx, ctx->dStage, queries, n * 5 * 4))) return rc;
+	CUDA_TRY(ctx, ctx->dStageOut.alloc(n * 16 * 4));
+	k_hook_emitter<<<blocksFor(n, 128), 128, 0, ctx->stream>>>(ctx->scene, ctx->dStage.as<float>(), (uint32_t) n, 1, ctx->dStageOut.as<float>());
+	return download(ctx, out, ctx->dStageOut, n * 16 * 4);
+}
+
+int hookCameraRays(mtsgpu_ctx *ctx, const float *samples, size_t n, float *out) {
+	REQUIRE(ctx, ctx->haveCamera, MTSGPU_ERR_ARG, "camera_rays: call mtsgpu_set_camera first");
+	if (n == 0) return MTSGPU_OK;
+	int rc;
+	if ((rc = upload(ctx, ctx->dStage, samples, n * 4 * 4))) return rc;
+	CUDA_TRY(ctx, ctx->dStageOut.alloc(n * 8 * 4));
+	k_hook_camera<<<blocksFor(n, 128), 128, 0, ctx->stream>>>(ctx->camera, ctx->dStage.as<float>(), (uint32_t) n, ctx->dStageOut.as<float>());
+	return download(ctx, out, ctx->dStageOut, n * 8 * 4);
+}
+
+int hookIntersectFull(mtsgpu_ctx *ctx, const float *rays, size_t n, mtsgpu_hit *hits, float *out) {
+	REQUIRE(ctx, ctx->built, MTSGPU_ERR_ARG, "intersect_full: call mtsgpu_build_accel first");
+	if (n == 0) return MTSGPU_OK;
+	int rc;
+	if ((rc = upload(ctx, ctx->dRays, rays, n * 32))) return rc;
+	CUDA_TRY(ctx, ctx->dHits.alloc(n * sizeof(mtsgpu_hit)));
+	if ((rc = launchTrace(ctx, ctx->dRays.as<float4>(), n, MTSGPU_TRACE_CLOSEST, ctx->dHits.p, nullptr))) return rc;
+	CUDA_TRY(ctx, ctx->dStageOut.alloc(n * 12 * 4));
+	k_hook_isect<<<blocksFor(n, 128), 128, 0, ctx->stream>>>(ctx->scene, ctx->dRays.as<float4>(), ctx->dHits.as<mtsgpu_hit>(), (uint32_t) n, ctx->dStageOut.as<float>());
+	if (hits) CUDA_TRY(ctx, cudaMemcpyAsync(hits, ctx->dHits.p, n * sizeof(mtsgpu_hit), cudaMemcpyDeviceToHost, ctx->stream));
+	return download(ctx, out, ctx->dStageOut, n * 12 * 4);
+}
+
+// Film splat of an arbitrary sample list through the render loop's own k_splat: samples are
+// bucketed by the tile that holds their pixel, padded to whole 256-slot passes.
+int hookFilmSplat(mtsgpu_ctx *ctx, const float *samples, size_t n, float *outFilm) {
+	REQUIRE(ctx, ctx->haveFilm, MTSGPU_ERR_ARG, "film_splat: call mtsgpu_set_film first");
+	const FilmDev film = ctx->film;
+	const uint32_t tilesX = (film.cropW + TILE - 1) / TILE, tilesY = (film.cropH + TILE - 1) / TILE;
+	const uint32_t nTiles = tilesX * tilesY;
+	std::vector<std::vector<uint32_t> > buckets(nTiles);
+	for (size_t i = 0; i < n; ++i) {
+		const float *s = samples + i * 6;
+		const int px = (int) floorf(s[0]) - film.cropX, py = (int) floorf(s[1]) - film.cropY;
+		REQUIRE(ctx, px >= 0 && py >= 0 && px < film.cropW && py < film.cropH, MTSGPU_ERR_ARG,
+			"film_splat: sample %zu at (%g, %g) lies outside the crop window", i, s[0], s[1]);
+		buckets[(py / TILE) * tilesX + px / TILE].push_back((uint32_t) i);
+	}
+	size_t maxCount = 1;
+	for (auto &b : buckets) maxCount = std::max(maxCount, b.size());
+	const uint32_t passes = (uint32_t) ((maxCount + TILE_PIX - 1) / TILE_PIX);
+	const size_t perTile = (size_t) passes * TILE_PIX, total = perTile * nTiles;
+	std::vector<float4> li(total, make_float4(0, 0, 0, 0));
+	std::vector<float2> pos(total);
+	float nanv; { uint32_t b = 0x7FC00000u; memcpy(&nanv, &b, 4); }
+	for (auto &p : pos) p = make_float2(nanv, 0);
+	for (uint32_t t = 0; t < nTiles; ++t)
+		for (size_t k = 0; k < buckets[t].size(); ++k) {
+			const float *s = samples + (size_t) buckets[t][k] * 6;
+			li[t * perTile + k] = make_float4(s[2], s[3], s[4], s[5]);
+			pos[t * perTile + k] = make_float2(s[0], s[1]);
+		}
+	const size_t filmFloats = (size_t) film.cropW * film.cropH * 5;
+	DevBuf dTable;
+	int rc;
+	if ((rc = uploadFilter(ctx, dTable))) return rc;
+	if ((rc = upload(ctx, ctx->dStage, li.data(), total * sizeof(float4)))) return rc;
+	if ((rc = upload(ctx, ctx->dStageOut, pos.data(), total * sizeof(float2)))) return rc;
+	CUDA_TRY(ctx, ctx->dFilm.alloc(filmFloats * 4));
+	k_zero<<<blocksFor(filmFloats, 256), 256, 0, ctx->stream>>>(ctx->dFilm.as<float>(), filmFloats);
+	BatchDesc b; memset(&b, 0, sizeof(b));
+	b.tileBegin = 0; b.tileCount = nTiles; b.tilesX = tilesX; b.sampleCount = passes; b.slots = (uint32_t) total;
+	const int smem = (TILE + 2 * film.border) * (TILE + 2 * film.border) * 5 * (int) sizeof(float);
+	k_splat<<<nTiles, TILE_PIX, smem, ctx->stream>>>(film, b, ctx->dStage.as<float4>(), ctx->dStageOut.as<float2>(), dTable.as<float>(), ctx->dFilm.as<float>());
+	return download(ctx, outFilm, ctx->dFilm, filmFloats * 4);
+}

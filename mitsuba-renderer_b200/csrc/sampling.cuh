@@ -1,0 +1,206 @@
+// Device functions for the non-BSDF stages of the hot path: counter-based sampler, perspective
+// camera, intersection record, area-luminaire sampling. Compiled with --fmad=false (see bsdf.cuh).
+#pragma once
+#include "types.cuh"
+
+// ---- sampler ----------------------------------------------------------------------------------
+// Stands in for IndependentSampler/Random (src/samplers/independent.cpp:72-81,
+// src/libcore/random.cpp:141-228). The reference's MT19937-64 stream depends on which worker
+// thread renders which block, so it is not reproducible even between two CPU runs; what is kept is
+// (a) independent uniform samples, (b) the uint->float mapping of Random::nextFloat
+// (random.cpp:218-227: 23 mantissa bits, [0,1)), (c) the per-sample consumption order.
+// Streams are keyed by (pixel, global sample index, seed) so the image does not depend on how
+// samples are split over batches or GPUs.
+__host__ __device__ inline uint64_t splitmix64(uint64_t z) {
+	z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+	z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+	return z ^ (z >> 31);
+}
+__host__ __device__ inline float uintToUnitFloat(uint32_t u) {
+	union { uint32_t u; float f; } c;
+	c.u = (u >> 9) | 0x3f800000u;
+	return c.f - 1.0f;
+}
+struct Sampler {
+	uint64_t key;
+	__host__ __device__ void init(uint32_t pixel, uint32_t sample, uint32_t seed) {
+		key = splitmix64((((uint64_t) pixel << 32) | sample) + 0x9E3779B97F4A7C15ull * (uint64_t) (seed + 1));
+	}
+	// dimension pair `dim`: independent of call order, so no counter has to live in the path state
+	__host__ __device__ void get2D(uint32_t dim, float &x, float &y) const {
+		const uint64_t z = splitmix64(key + 0x9E3779B97F4A7C15ull * (uint64_t) (dim + 1));
+		x = uintToUnitFloat((uint32_t) z);
+		y = uintToUnitFloat((uint32_t) (z >> 32));
+	}
+	__host__ __device__ float get1D(uint32_t dim) const { float x, y; get2D(dim, x, y); return x; }
+};
+// dimension layout per pixel sample: 0 lens, 1 time, 2 pixel, then per bounce b (depth b+1):
+#define DIM_LENS 0u
+#define DIM_TIME 1u
+#define DIM_PIXEL 2u
+#define DIM_BOUNCE(b, k) (3u + 3u * (b) + (k))   // k: 0 luminaire 2D, 1 BSDF 2D, 2 roulette 1D
+#define DIM_DIRECT(round, k) (3u + 2u * (round) + (k))
+
+// ---- camera: PerspectiveCameraImpl::generateRay (src/cameras/perspective.cpp:77-112) ----------
+__device__ inline void squareToDiskConcentric(float sx, float sy, float &ox, float &oy) {   // util.cpp:626-649
+	const float r1 = 2.0f * sx - 1.0f, r2 = 2.0f * sy - 1.0f;
+	float cx, cy;
+	if (r1 == 0 && r2 == 0) { cx = 0; cy = 0; }
+	else if (r1 > -r2) {
+		if (r1 > r2) { cx = r1; cy = (MTS_PI / 4.0f) * r2 / r1; }
+		else { cx = r2; cy = (MTS_PI / 4.0f) * (2.0f - r1 / r2); }
+	} else {
+		if (r1 < r2) { cx = -r1; cy = (MTS_PI / 4.0f) * (4.0f + r2 / r1); }
+		else { cx = -r2; cy = (MTS_PI / 4.0f) * (6.0f - r1 / r2); }
+	}
+	ox = cx * cosf(cy); oy = cx * sinf(cy);
+}
+
+__device__ inline void cameraRay(const CameraDev &cam, float sx, float sy, float lx, float ly,
+		V3 &o, V3 &d, float &mint, float &maxt) {
+	const float *m = cam.rasterToCamera;
+	// Transform::operator()(Point, Point&) with the projective divide (core/transform.h:133-149)
+	float x = m[0] * sx + m[1] * sy + m[2] * 0.0f + m[3];
+	float y = m[4] * sx + m[5] * sy + m[6] * 0.0f + m[7];
+	float z = m[8] * sx + m[9] * sy + m[10] * 0.0f + m[11];
+	const float w = m[12] * sx + m[13] * sy + m[14] * 0.0f + m[15];
+	if (w != 1.0f) { const float rw = 1.0f / w; x *= rw; y *= rw; z *= rw; }
+	V3 lo = v3(0, 0, 0), ld = v3(x, y, z);
+	if (cam.apertureRadius > 0.0f) {
+		float px, py;
+		squareToDiskConcentric(lx, ly, px, py);
+		px *= cam.apertureRadius; py *= cam.apertureRadius;
+		const float ft = cam.focusDepth / ld.z;
+		const V3 itsFocal = lo + ld * ft;
+		lo.x += px; lo.y += py;
+		ld = itsFocal - lo;
+	}
+	ld = normalize(ld);
+	const float invZ = 1.0f / ld.z;
+	mint = cam.nearClip * invZ;
+	maxt = cam.farClip * invZ;
+	const float *c = cam.cameraToWorld;
+	{
+		float ox = c[0] * lo.x + c[1] * lo.y + c[2] * lo.z + c[3];
+		float oy = c[4] * lo.x + c[5] * lo.y + c[6] * lo.z + c[7];
+		float oz = c[8] * lo.x + c[9] * lo.y + c[10] * lo.z + c[11];
+		const float ow = c[12] * lo.x + c[13] * lo.y + c[14] * lo.z + c[15];
+		if (ow != 1.0f) { const float rw = 1.0f / ow; ox *= rw; oy *= rw; oz *= rw; }
+		o = v3(ox, oy, oz);
+	}
+	d = v3(c[0] * ld.x + c[1] * ld.y + c[2] * ld.z,
+	       c[4] * ld.x + c[5] * ld.y + c[6] * ld.z,
+	       c[8] * ld.x + c[9] * ld.y + c[10] * ld.z);
+}
+
+// ---- intersection record: ShapeKDTree::fillIntersectionRecord<true> (skdtree.h:352-432) -----------
+struct Isect {
+	V3 p, geoN, shN, wi;
+	Frame3 sh;
+	uint32_t shape;
+	int materialId, emitterId;
+};
+
+__device__ inline void fillIntersection(const DeviceScene &sc, uint32_t shape, uint32_t prim, float u, float v,
+		V3 rayD, Isect &its) {
+	const ShapeInfo si = sc.shapes[shape];
+	const uint4 idx = __ldg(sc.triIdx + si.triOffset + prim);
+	const V3 p0 = v3(__ldg(sc.positions + idx.x)), p1 = v3(__ldg(sc.positions + idx.y)), p2 = v3(__ldg(sc.positions + idx.z));
+	const float bx = 1 - u - v, by = u, bz = v;
+	its.p = p0 * bx + p1 * by + p2 * bz;      // barycentric position, NOT o + t*d
+	V3 fn = cross(p1 - p0, p2 - p0);
+	const float len = length(fn);
+	if (!isZero(fn)) fn = fn * (1.0f / len);
+	its.geoN = fn;
+	if (si.hasNormals) {
+		const V3 n0 = v3(__ldg(sc.normals + idx.x)), n1 = v3(__ldg(sc.normals + idx.y)), n2 = v3(__ldg(sc.normals + idx.z));
+		its.shN = normalize(n0 * bx + n1 * by + n2 * bz);
+	} else {
+		its.shN = fn;
+	}
+	its.sh = makeFrame(its.shN);
+	its.wi = toLocal(its.sh, -rayD);
+	its.shape = shape; its.materialId = si.materialId; its.emitterId = si.emitterId;
+}
+
+// ---- DiscretePDF::sampleReuse (include/mitsuba/core/pdf.h:107-148) on a device CDF ----------------
+// std::lower_bound: first entry >= value; index = clamp(pos - 1, 0, n - 1)
+__device__ inline int cdfSampleReuse(const float *cdf, int n, float &value) {
+	int lo = 0, count = n + 1;
+	while (count > 0) {
+		const int step = count / 2, mid = lo + step;
+		if (cdf[mid] < value) { lo = mid + 1; count -= step + 1; } else count = step;
+	}
+	int index = max(0, lo - 1);
+	index = min(index, n - 1);
+	value = (value - cdf[index]) / (cdf[index + 1] - cdf[index]);
+	return index;
+}
+
+// ---- Scene::sampleLuminaire without the visibility test (scene.cpp:396-415) -----------------------
+struct LumSample {
+	V3 p, n, d, value;   // sRec.p, sRec.n, lRec.d (normalised, light -> point), lRec.value (already / pdf)
+	float pdf;           // lRec.pdf after multiplication by the luminaire-selection pdf; 0 => failed
+	int emitter;
+};
+
+__device__ inline void sampleLuminaire(const DeviceScene &sc, V3 p, float sx, float sy, bool importance, LumSample &out) {
+	out.pdf = 0; out.emitter = -1;
+	if (sc.nEmitters == 0) return;
+	const int index = cdfSampleReuse(sc.lumCdf, (int) sc.nEmitters, sx);
+	const EmitterDev em = sc.emitters[index];
+	const float lumPdf = em.pdf;
+	const ShapeInfo si = sc.shapes[em.shape];
+	// TriMesh::sampleArea (trimesh.cpp:297-302) + Triangle::sample (triangle.cpp:23-47)
+	const int tri = cdfSampleReuse(sc.areaCdf + si.cdfOffset, (int) si.nTri, sy);
+	const uint4 idx = __ldg(sc.triIdx + si.triOffset + tri);
+	const V3 p0 = v3(__ldg(sc.positions + idx.x)), p1 = v3(__ldg(sc.positions + idx.y)), p2 = v3(__ldg(sc.positions + idx.z));
+	const float a = sqrtf(1.0f - sx);
+	const float baryX = 1 - a, baryY = a * sy;
+	const V3 sideA = p1 - p0, sideB = p2 - p0;
+	out.p = p0 + (sideA * baryX) + (sideB * baryY);
+	if (si.hasNormals) {
+		const V3 n0 = v3(__ldg(sc.normals + idx.x)), n1 = v3(__ldg(sc.normals + idx.y)), n2 = v3(__ldg(sc.normals + idx.z));
+		out.n = normalize(n0 * (1.0f - baryX - baryY) + n1 * baryX + n2 * baryY);
+	} else {
+		out.n = normalize(cross(sideA, sideB));
+	}
+	// Shape::sampleSolidAngle (shape.cpp:65-75)
+	const V3 lumToPoint = p - out.p;
+	const float distSquared = dot(lumToPoint, lumToPoint), dp = dot(lumToPoint, out.n);
+	float pdf = 0.0f;
+	if (dp > 0)
+		pdf = si.invSurfaceArea * distSquared * sqrtf(distSquared) / dp;
+	// AreaLuminaire::sample (area.cpp:68-79)
+	V3 d = p - out.p;
+	if (pdf > 0 && dot(d, out.n) > 0) {
+		d = normalize(d);
+	} else {
+		pdf = 0;
+	}
+	out.d = d; out.emitter = index;
+	if (pdf != 0) {
+		pdf *= lumPdf;
+		const V3 inten = v3(em.intensity[0], em.intensity[1], em.intensity[2]);
+		out.value = inten * (1.0f / pdf);
+		out.pdf = pdf;
+	}
+}
+
+// Scene::pdfLuminaire (scene.cpp:381-394) with AreaLuminaire::pdf -> Shape::pdfSolidAngle (shape.cpp:77-83)
+__device__ inline float pdfLuminaire(const DeviceScene &sc, V3 from, V3 lumP, V3 lumN, int emitter, bool importance) {
+	const EmitterDev em = sc.emitters[emitter];
+	const float luminance = importance ? em.weight : 1.0f;
+	const float fraction = luminance / sc.lumOriginalSum;
+	const V3 lumToPoint = from - lumP;
+	const float distSquared = dot(lumToPoint, lumToPoint);
+	const float invDP = fmaxf(0.0f, sqrtf(distSquared) / dot(lumToPoint, lumN));
+	return (sc.shapes[em.shape].invSurfaceArea * distSquared * invDP) * fraction;
+}
+
+// AreaLuminaire::Le (area.cpp:62-66)
+__device__ inline V3 emitterLe(const DeviceScene &sc, int emitter, V3 n, V3 d) {
+	if (dot(d, n) <= 0) return v3(0, 0, 0);
+	const EmitterDev em = sc.emitters[emitter];
+	return v3(em.intensity[0], em.intensity[1], em.intensity[2]);
+}

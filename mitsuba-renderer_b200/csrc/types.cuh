@@ -1,0 +1,112 @@
+// Internal device-side data layout of libmtscuda (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+#include "../../include/mtsgpu.h"
+
+#define MTS_EPSILON        1e-4f   // include/mitsuba/core/constants.h:27-35
+#define MTS_SHADOW_EPSILON 1e-3f
+#define MTS_PI             3.14159265358979323846f
+#define MTS_INV_PI         0.31830988618379067154f
+
+// ---- TriAccel record: same 48-byte layout as include/mitsuba/render/triaccel.h:34-46 --------
+// Bit 31 of `k` is ours: set when the owning shape has no BSDF, i.e. is not an occluder for
+// shadow rays (shape.h:361, skdtree.h:324-334). Closest-hit masks it off.
+struct __align__(16) TriAccelRec {
+	uint32_t k; float n_u, n_v, n_d;
+	float a_u, a_v, b_nu, b_nv;
+	float c_nu, c_nv; uint32_t shapeIndex, primIndex;
+};
+#define TRI_K_MASK         3u
+#define TRI_NONOCCLUDER    0x80000000u
+
+// ---- 4-wide BVH node, one 128-byte line: eight 128-bit loads ------------------------------
+// child[i]: 0xFFFFFFFF empty | bit31 leaf: (count-1)<<28 | first sorted triangle | else node index
+struct __align__(128) BVH4Node {
+	float4 lox, loy, loz, hix, hiy, hiz;
+	uint4 child;
+	uint4 pad;
+};
+#define BVH_EMPTY      0xFFFFFFFFu
+#define BVH_LEAF       0x80000000u
+#define BVH_LEAF_MAX   4
+
+struct ShapeInfo {
+	int32_t materialId, emitterId;
+	uint32_t triOffset, vertOffset;
+	uint32_t nTri, nVert;
+	uint32_t hasNormals;
+	uint32_t cdfOffset;       // into DeviceScene::areaCdf (emitter meshes only)
+	float invSurfaceArea;     // TriMesh::m_invSurfaceArea (trimesh.cpp:281)
+	uint32_t pad[3];
+};
+
+struct MaterialDev { uint32_t type; float p[16]; uint32_t pad[3]; };
+struct EmitterDev { float intensity[3]; uint32_t shape; float pdf; float weight; uint32_t pad[2]; };
+
+struct CameraDev {
+	float rasterToCamera[16];
+	float cameraToWorld[16];
+	float nearClip, farClip, apertureRadius, focusDepth;
+	float shutterOpen, shutterOpenTime;
+};
+
+struct FilmDev {
+	int width, height, cropX, cropY, cropW, cropH;
+	float filterSizeX, filterSizeY;   // TabulatedFilter::m_size
+	float factorX, factorY;           // TabulatedFilter::m_factor = 15 / size
+	int border;                       // ceil(max(size) - 0.5), renderproc.cpp:142-144
+};
+
+struct DeviceScene {
+	const float4 *triAccel;     // sorted leaf order, 3 x float4 per triangle
+	const float4 *nodes;        // BVH4Node as 8 x float4
+	const uint4 *triIdx;        // kd primitive order: {v0, v1, v2 (global vertex ids), shape}
+	const float4 *positions;    // global vertex arrays, xyz + pad
+	const float4 *normals;
+	const ShapeInfo *shapes;
+	const MaterialDev *materials;
+	const EmitterDev *emitters;
+	const float *lumCdf;        // nEmitters + 1 (DiscretePDF::m_cdf, pdf.h:82-100)
+	const float *areaCdf;       // per emitter mesh: nTri + 1 entries at ShapeInfo::cdfOffset
+	uint32_t nEmitters, nShapes, nTris, rootIsLeaf;
+	float lumOriginalSum;       // DiscretePDF::getOriginalSum()
+	float aabbMin[3], aabbMax[3]; // enlarged kd-tree box (gkdtree.h:1172-1176)
+};
+
+// ---- small vector helpers (shading math; not bit-exactness critical) ----------------------
+struct V3 { float x, y, z; };
+__host__ __device__ inline V3 v3(float x, float y, float z) { V3 r = { x, y, z }; return r; }
+__host__ __device__ inline V3 v3(float4 a) { V3 r = { a.x, a.y, a.z }; return r; }
+__host__ __device__ inline V3 operator+(V3 a, V3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__host__ __device__ inline V3 operator-(V3 a, V3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__host__ __device__ inline V3 operator*(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
+__host__ __device__ inline V3 operator*(V3 a, V3 b) { return v3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__host__ __device__ inline V3 operator-(V3 a) { return v3(-a.x, -a.y, -a.z); }
+__host__ __device__ inline float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__host__ __device__ inline V3 cross(V3 a, V3 b) {
+	return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+__host__ __device__ inline float length(V3 a) { return sqrtf(dot(a, a)); }
+// TVector3::operator/ multiplies by the reciprocal (core/vector.h:311-318)
+__host__ __device__ inline V3 normalize(V3 a) { float r = 1.0f / length(a); return a * r; }
+__host__ __device__ inline float maxc(V3 a) { return fmaxf(a.x, fmaxf(a.y, a.z)); }
+__host__ __device__ inline bool isZero(V3 a) { return a.x == 0 && a.y == 0 && a.z == 0; }
+
+// Frame(n) built by coordinateSystem (src/libcore/util.cpp:602-611, core/frame.h:35-83)
+struct Frame3 { V3 s, t, n; };
+__host__ __device__ inline Frame3 makeFrame(V3 n) {
+	Frame3 f; f.n = n;
+	if (fabsf(n.x) > fabsf(n.y)) {
+		float invLen = 1.0f / sqrtf(n.x * n.x + n.z * n.z);
+		f.s = v3(-n.z * invLen, 0.0f, n.x * invLen);
+	} else {
+		float invLen = 1.0f / sqrtf(n.y * n.y + n.z * n.z);
+		f.s = v3(0.0f, -n.z * invLen, n.y * invLen);
+	}
+	f.t = cross(n, f.s);
+	return f;
+}
+__host__ __device__ inline V3 toLocal(const Frame3 &f, V3 v) { return v3(dot(v, f.s), dot(v, f.t), dot(v, f.n)); }
+__host__ __device__ inline V3 toWorld(const Frame3 &f, V3 v) { return f.s * v.x + f.t * v.y + f.n * v.z; }

@@ -18,10 +18,13 @@ static int cmdTraceImpl(int argc, char **argv) {
 	if (mode == 1) full.resize(n * 12);
 	TraceCtx ctx = { b.scene.get(), rays.data(), mode, tuv.data(), ids.data(), full.data(), occl.data() };
 	double best = 1e30;
+	std::string all;
 	for (int r = 0; r < repeat; ++r) {
 		double t0 = now();
 		parallelFor(n, threads, traceRange, &ctx);
-		best = std::min(best, now() - t0);
+		const double dt = now() - t0;
+		best = std::min(best, dt);
+		all += (r ? ", " : "") + formatString("%.6f", dt);
 	}
 	FILE *f = fopen(argv[4], "wb");
 	if (!f) { std::cerr << "cannot write output\n"; return 1; }
@@ -37,9 +40,9 @@ static int cmdTraceImpl(int argc, char **argv) {
 	else for (size_t i = 0; i < n; ++i) hits += ids[i*2] != 0xFFFFFFFFu;
 	const AABB &bb = b.scene->getKDTree()->getAABB();
 	printf("{\"cmd\": \"trace\", \"mode\": \"%s\", \"rays\": %zu, \"hits\": %zu, \"threads\": %d, "
-		"\"kd_build_s\": %.6f, \"trace_s\": %.6f, \"mrays_per_s\": %.6f, "
+		"\"kd_build_s\": %.6f, \"trace_s\": %.6f, \"trace_s_all\": [%s], \"mrays_per_s\": %.6f, "
 		"\"aabb\": [%.9g, %.9g, %.9g, %.9g, %.9g, %.9g]}\n",
-		modeStr.c_str(), n, hits, threads, b.buildSeconds, best, n / best * 1e-6,
+		modeStr.c_str(), n, hits, threads, b.buildSeconds, best, all.c_str(), n / best * 1e-6,
 		bb.min.x, bb.min.y, bb.min.z, bb.max.x, bb.max.y, bb.max.z);
 	return 0;
 }

@@ -1,0 +1,124 @@
+"""TEST INFRASTRUCTURE: drives oracle/_ref/<variant>/mts_oracle (the reference's own code, compiled
+by oracle/Makefile) on scenes written by mitsuba_renderer_b200.scenefile. Only tests/, smoke() and
+bench.py's cpu_baseline / --impl reference legs may import this."""
+import json
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HIT_DTYPE = np.dtype([("t", np.float32), ("u", np.float32), ("v", np.float32), ("shape", np.uint32), ("prim", np.uint32)])
+
+
+def binary(variant="parity"):
+    return os.path.join(ROOT, "oracle", "_ref", variant, "mts_oracle")
+
+
+def available(variant="parity"):
+    return os.path.exists(binary(variant))
+
+
+def _run(args, variant="parity", timeout=3600, env=None):
+    e = dict(os.environ)
+    if env:
+        e.update(env)
+    p = subprocess.run([binary(variant)] + [str(a) for a in args], capture_output=True, text=True, timeout=timeout, env=e)
+    if p.returncode != 0:
+        raise RuntimeError(f"mts_oracle {' '.join(map(str, args))} failed ({p.returncode}):\n{p.stdout}\n{p.stderr}")
+    for line in reversed(p.stdout.strip().splitlines()):
+        i = line.find('{"cmd"')
+        if i >= 0:
+            return json.loads(line[i:])
+    raise RuntimeError("mts_oracle printed no result line:\n" + p.stdout + p.stderr)
+
+
+class Session:
+    """A scene written once to a temp dir; each call runs one harness command on it."""
+
+    def __init__(self, scene, variant="parity"):
+        from mitsuba_renderer_b200 import scenefile
+        self.variant = variant
+        self.dir = tempfile.TemporaryDirectory(prefix="mtsoracle_")
+        self.scene_path = os.path.join(self.dir.name, "scene.bin")
+        scenefile.write_scene(self.scene_path, scene)
+        self.scene = scene
+
+    def _io(self, cmd, arr, extra=()):
+        inp = os.path.join(self.dir.name, "in.bin")
+        out = os.path.join(self.dir.name, "out.bin")
+        np.ascontiguousarray(arr, np.float32).tofile(inp)
+        info = _run([cmd, self.scene_path, inp, out] + list(extra), self.variant)
+        return out, info
+
+    def trace(self, rays, mode="closest", threads=1, repeat=1):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        out, info = self._io("trace", rays, [mode, threads, repeat])
+        n = len(rays)
+        raw = np.fromfile(out, np.uint32)
+        if mode == "any":
+            return raw.astype(np.uint32), info
+        hits = np.empty(n, HIT_DTYPE)
+        tuv = raw[:3 * n].view(np.float32).reshape(n, 3)
+        ids = raw[3 * n:5 * n].reshape(n, 2)
+        hits["t"], hits["u"], hits["v"] = tuv[:, 0], tuv[:, 1], tuv[:, 2]
+        hits["shape"], hits["prim"] = ids[:, 0], ids[:, 1]
+        if mode == "closest_full":
+            full = raw[5 * n:].view(np.float32).reshape(n, 12)
+            return hits, full, info
+        return hits, info
+
+    def triaccel(self):
+        out = os.path.join(self.dir.name, "ta.bin")
+        info = _run(["triaccel", self.scene_path, out], self.variant)
+        raw = np.fromfile(out, np.uint8)
+        box = raw[:24].view(np.float32).copy()
+        from mitsuba_renderer_b200.api import TRIACCEL_DTYPE
+        return raw[24:].view(TRIACCEL_DTYPE).copy(), box, info
+
+    def bsdf(self, queries):
+        out, _ = self._io("bsdf", queries)
+        return np.fromfile(out, np.float32).reshape(-1, 16)
+
+    def emitter(self, queries):
+        out, _ = self._io("emitter", queries)
+        return np.fromfile(out, np.float32).reshape(-1, 16)
+
+    def camera(self, samples):
+        out, _ = self._io("camera", samples)
+        return np.fromfile(out, np.float32).reshape(-1, 8)
+
+    def splat(self, samples):
+        table = os.path.join(self.dir.name, "table.bin")
+        out, info = self._io("splat", samples, [table])
+        cx, cy, cw, ch = self.scene.crop_rect
+        return np.fromfile(out, np.float32).reshape(ch, cw, 5), np.fromfile(table, np.float32).reshape(16, 16), info
+
+    def render(self, threads=None, integrator=None, env=None):
+        out = os.path.join(self.dir.name, "film.bin")
+        threads = threads or os.cpu_count() or 1
+        args = ["render", self.scene_path, out, threads] + ([integrator] if integrator else [])
+        e = dict(os.environ)
+        if env:
+            e.update(env)
+        p = subprocess.run([binary(self.variant)] + [str(a) for a in args], capture_output=True, text=True, timeout=7200, env=e)
+        if p.returncode != 0:
+            raise RuntimeError(f"mts_oracle render failed:\n{p.stdout}\n{p.stderr}")
+        info = None
+        for line in p.stdout.splitlines():
+            i = line.find('{"cmd"')
+            if i >= 0:
+                info = json.loads(line[i:])
+        cx, cy, cw, ch = self.scene.crop_rect
+        return np.fromfile(out, np.float32).reshape(ch, cw, 5), info
+
+
+def parse_count(s):
+    """Statistics prints '1.234 M' style numbers."""
+    parts = str(s).split()
+    if not parts:
+        return 0.0
+    v = float(parts[0])
+    mult = {"K": 1e3, "M": 1e6, "G": 1e9, "T": 1e12}
+    return v * mult.get(parts[1], 1.0) if len(parts) > 1 else v
