@@ -18,15 +18,15 @@
 
 // ---- src/libcore/util.cpp helpers ---------------------------------------------------------------
 __device__ inline V3 sphericalDirection(float theta, float phi) {           // util.cpp:543-550
-	const float sinTheta = sinf(theta);
-	return v3(sinTheta * cosf(phi), sinTheta * sinf(phi), cosf(theta));
+	const float sinTheta = mts_sin(theta);
+	return v3(sinTheta * mts_cos(phi), sinTheta * mts_sin(phi), mts_cos(theta));
 }
 
 __device__ inline V3 squareToHemispherePSA(float sx, float sy) {            // util.cpp:572-588
 	const float r = sqrtf(sx);
 	const float phi = 2.0f * MTS_PI * sy;
-	const float dirX = r * cosf(phi);
-	const float dirY = r * sinf(phi);
+	const float dirX = r * mts_cos(phi);
+	const float dirY = r * mts_sin(phi);
 	const float z = sqrtf(1 - fminf(1.0f, dirX * dirX + dirY * dirY));
 	if (z == 0)
 		return normalize(v3(dirX, dirY, MTS_EPSILON));
@@ -75,11 +75,11 @@ __device__ inline float frameTanTheta(V3 v) {                                // 
 // ---- Beckmann microfacet terms shared by microfacet.cpp:95-134 and roughmetal.cpp:75-114 -----------
 __device__ inline float beckmannD(V3 m, float alphaB) {
 	const float ex = frameTanTheta(m) / alphaB;
-	return expf(-(ex * ex)) / (MTS_PI * alphaB * alphaB * powf(m.z, 4.0f));
+	return mts_exp(-(ex * ex)) / (MTS_PI * alphaB * alphaB * mts_pow(m.z, 4.0f));
 }
 
 __device__ inline V3 sampleBeckmannD(float sx, float sy, float alphaB) {
-	const float thetaM = atanf(sqrtf(-alphaB * alphaB * logf(1.0f - sx)));
+	const float thetaM = mts_atan(sqrtf(-alphaB * alphaB * mts_log(1.0f - sx)));
 	const float phiM = (2.0f * MTS_PI) * sy;
 	return sphericalDirection(thetaM, phiM);
 }

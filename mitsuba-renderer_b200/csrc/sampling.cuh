@@ -53,7 +53,7 @@ __device__ inline void squareToDiskConcentric(float sx, float sy, float &ox, flo
 		if (r1 < r2) { cx = -r1; cy = (MTS_PI / 4.0f) * (4.0f + r2 / r1); }
 		else { cx = -r2; cy = (MTS_PI / 4.0f) * (6.0f - r1 / r2); }
 	}
-	ox = cx * cosf(cy); oy = cx * sinf(cy);
+	ox = cx * mts_cos(cy); oy = cx * mts_sin(cy);
 }
 
 __device__ inline void cameraRay(const CameraDev &cam, float sx, float sy, float lx, float ly,

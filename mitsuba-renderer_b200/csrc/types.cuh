@@ -75,6 +75,19 @@ struct DeviceScene {
 	float aabbMin[3], aabbMax[3]; // enlarged kd-tree box (gkdtree.h:1172-1176)
 };
 
+// ---- transcendental functions -------------------------------------------------------------------
+// The reference calls glibc's float routines (sinf, cosf, expf, logf, powf: correctly rounded in nearly
+// all cases since glibc 2.28). CUDA's float versions are 1-2 ulp off, and a one-ulp difference in a
+// sampled direction is amplified ~100x by a sharp Beckmann lobe. Evaluating in fp64 and rounding once
+// reproduces the correctly rounded fp32 result, so sampled directions match the reference bit for bit
+// in almost every case. These run a handful of times per shading event, never in traversal.
+__device__ __forceinline__ float mts_sin(float x) { return (float) sin((double) x); }
+__device__ __forceinline__ float mts_cos(float x) { return (float) cos((double) x); }
+__device__ __forceinline__ float mts_atan(float x) { return (float) atan((double) x); }
+__device__ __forceinline__ float mts_log(float x) { return (float) log((double) x); }
+__device__ __forceinline__ float mts_exp(float x) { return (float) exp((double) x); }
+__device__ __forceinline__ float mts_pow(float x, float y) { return (float) pow((double) x, (double) y); }
+
 // ---- small vector helpers (shading math; not bit-exactness critical) ----------------------
 struct V3 { float x, y, z; };
 __host__ __device__ inline V3 v3(float x, float y, float z) { V3 r = { x, y, z }; return r; }

@@ -173,6 +173,7 @@ static int cmdSplat(int argc, char **argv) {
 	std::vector<float> q = sio::loadFloats(argv[3]);
 	const size_t n = q.size() / 6;
 	Built b = buildScene(sf, "", false);
+	Thread::getThread()->getLogger()->setLogLevel(EError);   /* silence the per-sample 'Invalid sample value' warnings */
 	const TabulatedFilter *filter = b.film->getTabulatedFilter();
 	int border = (int) std::ceil(std::max(filter->getFilterSize().x, filter->getFilterSize().y) - 0.5f);
 	ref<ImageBlock> block = new ImageBlock(b.film->getCropSize(), border, true, true, false, false);
@@ -182,7 +183,7 @@ static int cmdSplat(int argc, char **argv) {
 	for (size_t i = 0; i < n; ++i) {
 		const float *e = &q[i * 6];
 		Spectrum s; s.fromLinearRGB(e[2], e[3], e[4]);
-		block->putSample(Point2(e[0], e[1]), s, e[5], filter, false);
+		block->putSample(Point2(e[0], e[1]), s, e[5], filter);   /* complain=true: invalid spectra are dropped, as in renderBlock */
 	}
 	b.film->clear();
 	b.film->putImageBlock(block);

@@ -31,8 +31,10 @@ def compare(scene, oracle, gpu_ctx_factory, spp, ref_mult=16):
     ctx = gpu_ctx_factory(cpu_scene)
     gpu, stats = ctx.render(Context.params_from_scene(cpu_scene, seed=1))
     gpu_hi, _ = ctx.render(Context.params_from_scene(ref_scene, seed=2))
-    # accumulators: weight = spp per pixel under the box filter, alpha matches the reference
-    assert np.allclose(gpu[..., 4], cpu[..., 4])
+    # accumulators: weight = spp per pixel under the box filter — up to the few samples whose fp32 position
+    # pixel + u rounds up into the next pixel (u within 2^-18 of 1), which happens in the reference too
+    assert np.abs(gpu[..., 4] - spp).max() <= 3 and np.abs(cpu[..., 4] - spp).max() <= 3
+    assert abs(gpu[..., 4].sum() - cpu[..., 4].sum()) <= 1e-4 * cpu[..., 4].sum()
     assert abs(gpu[..., 3].sum() - cpu[..., 3].sum()) <= 0.01 * max(1.0, cpu[..., 3].sum())
     r, c, g, gh = develop(ref), develop(cpu), develop(gpu), develop(gpu_hi)
     e_cpu, e_gpu = rel_mse(c, r), rel_mse(g, r)

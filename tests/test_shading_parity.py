@@ -55,8 +55,21 @@ def test_bsdf_f_pdf_sample(oracle, gpu_ctx_factory):
     # which samples succeeded must agree exactly
     assert np.array_equal(ref[:, 11], gpu[:, 11]), "sampled lobe type differs"
     for c, nm in enumerate(names):
-        ok = close(gpu[:, c], ref[:, c])
-        assert ok.all(), f"{nm}: {np.count_nonzero(~ok)} of {len(q)} outside 1e-5; worst gpu={gpu[~ok][0, c]} ref={ref[~ok][0, c]} q={q[~ok][0]}"
+        rel, abs_ = REL, ABS
+        if nm.startswith("wo"):
+            abs_ = 1e-5       # sampled directions are unit vectors: 1e-5 of the vector length, not of each component
+        if nm.startswith("sf") or nm == "spdf":
+            # f and pdf re-evaluated AT the sampled direction: the direction itself agrees to ~1e-7 (libm vs CUDA
+            # sinf/cosf/atanf/logf differ by an ulp), and a Beckmann lobe amplifies that by
+            # |d ln D / d theta| = 2 tan(theta) / (alpha^2 cos^2(theta)) ~ 1e2 at alphaB = 0.1. The quantity the
+            # integrators consume, f/pdf (columns s2.* and the ratio checked below), is held to 1e-5.
+            rel = 2e-4
+        ok = close(gpu[:, c], ref[:, c], rel, abs_)
+        assert ok.all(), f"{nm}: {np.count_nonzero(~ok)} of {len(q)} outside {rel}; worst gpu={gpu[~ok][0, c]} ref={ref[~ok][0, c]} q={q[~ok][0]}"
+    got = gpu[:, 11] != 0
+    for c in (7, 8, 9):
+        rg = gpu[got, c] / gpu[got, 10]; rr = ref[got, c] / ref[got, 10]
+        assert close(rg, rr, REL, 1e-6).all(), f"sampled f/pdf ratio column {c}: max rel {np.max(np.abs(rg - rr) / np.maximum(np.abs(rr), 1e-6))}"
 
 
 def test_emitter_sampling(oracle, gpu_ctx_factory):
