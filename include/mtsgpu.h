@@ -193,6 +193,23 @@ MTSGPU_API int mtsgpu_camera_rays(mtsgpu_ctx *ctx, const float *samples, size_t 
  * samples: rows {x, y, r, g, b, alpha}; outFilm as in mtsgpu_render. */
 MTSGPU_API int mtsgpu_film_splat(mtsgpu_ctx *ctx, const float *samples, size_t n, float *outFilm);
 
+/* No counterpart in the reference. The same splat as mtsgpu_film_splat (host samples in, host film out,
+ * identical arithmetic) for callers that are not allowed to allocate GPU memory while they run: a progress
+ * or preview refresh on a latency-critical thread while a render already holds most of the device's memory
+ * (cudaMalloc may fail there, and it stalls the device), or a host that fixes the library's memory budget up
+ * front. This call performs no cudaMalloc/cudaFree and uses no allocating library routine: the staged
+ * samples, the filter table and the film accumulators live in one fixed block of device memory that is part
+ * of the library image, MTSGPU_STATIC_SCRATCH_BYTES per GPU, held from library load until process exit.
+ *   - limit: 1024 + 20*cropW*cropH + 24*n bytes (256-byte rounding between the parts) must fit in the block;
+ *     otherwise the call fails with MTSGPU_ERR_LIMIT and a message that names both sizes.
+ *   - the first call on a device also looks up the block's device address (once per device); make that
+ *     first call before starting any stream capture.
+ *   - all calls on a GPU share the block and it keeps the previous call's contents; the call clears the
+ *     accumulators itself, but two calls that overlap on the same GPU (different contexts or threads)
+ *     race on it — serialise them. */
+#define MTSGPU_STATIC_SCRATCH_BYTES (4u << 20)
+MTSGPU_API int mtsgpu_film_splat_static(mtsgpu_ctx *ctx, const float *samples, size_t n, float *outFilm);
+
 /* Closest-hit query that also fills the Intersection record (fillIntersectionRecord<true>,
  * skdtree.h:352-432): out rows of 12 floats {p, geoFrame.n, shFrame.n, wi}; zeros on a miss. */
 MTSGPU_API int mtsgpu_intersect_full(mtsgpu_ctx *ctx, const float *rays, size_t n, mtsgpu_hit *hits, float *out);

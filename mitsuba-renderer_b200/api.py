@@ -26,7 +26,9 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_render", "mtsgpu_render_device", "mtsgpu_trace", "mtsgpu_trace_device", "mtsgpu_bsdf_eval",
     "mtsgpu_emitter_sample", "mtsgpu_camera_rays", "mtsgpu_film_splat", "mtsgpu_intersect_full",
     "mtsgpu_get_triaccel", "mtsgpu_accel_info_get", "mtsgpu_set_counters", "mtsgpu_get_counters",
+    "mtsgpu_film_splat_static",
 ]
+STATIC_SCRATCH_BYTES = 4 << 20
 
 
 class MtsGpuError(RuntimeError):
@@ -101,7 +103,8 @@ def load_library(path: Optional[str] = None):
     lib.mtsgpu_render_device.argtypes = [vp, C.POINTER(RenderParams), vp, vp, C.POINTER(Stats)]
     lib.mtsgpu_trace.argtypes = [vp, vp, C.c_size_t, C.c_int, vp]
     lib.mtsgpu_trace_device.argtypes = [vp, vp, C.c_size_t, C.c_int, vp, C.POINTER(C.c_float)]
-    for name in ("mtsgpu_bsdf_eval", "mtsgpu_emitter_sample", "mtsgpu_camera_rays", "mtsgpu_film_splat"):
+    for name in ("mtsgpu_bsdf_eval", "mtsgpu_emitter_sample", "mtsgpu_camera_rays", "mtsgpu_film_splat",
+                 "mtsgpu_film_splat_static"):
         getattr(lib, name).argtypes = [vp, vp, C.c_size_t, vp]
     lib.mtsgpu_intersect_full.argtypes = [vp, vp, C.c_size_t, vp, vp]
     lib.mtsgpu_get_triaccel.argtypes = [vp, vp, C.c_size_t, vp]
@@ -293,6 +296,14 @@ class Context:
         q = np.ascontiguousarray(samples, np.float32).reshape(-1, 6)
         out = np.zeros(self.film_shape, np.float32)
         self._check(self.lib.mtsgpu_film_splat(self.h, self._ptr(q), len(q), self._ptr(out)))
+        return out
+
+    def film_splat_static(self, samples):
+        """mtsgpu_film_splat_static: the splat for callers that may not allocate GPU memory (fixed built-in
+        scratch block; see include/mtsgpu.h for the size limit)."""
+        q = np.ascontiguousarray(samples, np.float32).reshape(-1, 6)
+        out = np.zeros(self.film_shape, np.float32)
+        self._check(self.lib.mtsgpu_film_splat_static(self.h, self._ptr(q), len(q), self._ptr(out)))
         return out
 
     def intersect_full(self, rays):
