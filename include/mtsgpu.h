@@ -119,7 +119,8 @@ MTSGPU_API const char *mtsgpu_version(void);
 /* BSDF parameter blocks, decoded by the plugin from BSDF::serialize (e.g. roughmetal.cpp:169-176). */
 MTSGPU_API int mtsgpu_upload_materials(mtsgpu_ctx *ctx, const mtsgpu_material *materials, int count);
 
-/* Scene::getLuminaires() (scene.h) restricted to AreaLuminaire. */
+/* Scene::getLuminaires() (include/mitsuba/render/scene.h:517-519) restricted to AreaLuminaire
+ * (src/luminaires/area.cpp:35-83): intensity + Luminaire::getSamplingWeight. */
 MTSGPU_API int mtsgpu_upload_emitters(mtsgpu_ctx *ctx, const mtsgpu_emitter *emitters, int count);
 
 /* One TriMesh (include/mitsuba/render/trimesh.h:100-133) at kd-tree shape index `shapeIndex`
@@ -168,8 +169,8 @@ MTSGPU_API int mtsgpu_render_device(mtsgpu_ctx *ctx, const mtsgpu_render_params 
  * mode ANY writes n uint32 (1 = occluded). Host buffers; copies are part of the call. */
 MTSGPU_API int mtsgpu_trace(mtsgpu_ctx *ctx, const float *rays, size_t n, int mode, void *out);
 
-/* Device-resident variant: d_rays / d_out are DEVICE pointers; runs on the context's stream and
- * returns after the kernel has completed. elapsedMs (may be NULL) receives the kernel's device time. */
+/* Device-resident variant of mtsgpu_trace (same reference entry points, skdtree.cpp:108-132,180-199):
+ * d_rays / d_out are DEVICE pointers; runs on the context's stream and returns after the kernel has completed. elapsedMs (may be NULL) receives the kernel's device time. */
 MTSGPU_API int mtsgpu_trace_device(mtsgpu_ctx *ctx, const float *d_rays, size_t n, int mode, void *d_out,
 	float *elapsedMs);
 
@@ -218,15 +219,18 @@ MTSGPU_API int mtsgpu_intersect_full(mtsgpu_ctx *ctx, const float *rays, size_t 
  * (shape-major), preceded by nothing; aabb6 receives the enlarged scene box (gkdtree.h:1172-1176). */
 MTSGPU_API int mtsgpu_get_triaccel(mtsgpu_ctx *ctx, void *outRecords, size_t maxRecords, float aabb6[6]);
 
-/* Acceleration-structure figures for the roofline accounting. */
+/* Acceleration-structure figures for the roofline accounting; the counterpart of the
+ * "Structural kd-tree statistics" the reference logs after its build (include/mitsuba/render/gkdtree.h:1178-1214). */
 typedef struct mtsgpu_accel_info {
 	uint64_t triangles, nodes, nodeBytes, triBytes;
 	double buildMs;
 } mtsgpu_accel_info;
 MTSGPU_API int mtsgpu_accel_info_get(mtsgpu_ctx *ctx, mtsgpu_accel_info *info);
 
-/* Mean per-ray traversal work of the last mtsgpu_trace* call made with counters enabled
- * (mtsgpu_set_counters(ctx, 1)); counters are off by default and cost nothing when off. */
+/* Per-ray traversal work (node visits, triangle tests) of the last mtsgpu_trace* call made with counters
+ * enabled (mtsgpu_set_counters(ctx, 1)) — what rayIntersectHavranCollectStatistics returns per ray in the
+ * reference (include/mitsuba/render/sahkdtree3.h:310-410). Off by default; a separate kernel instantiation,
+ * so the timed kernels carry no counter code. */
 typedef struct mtsgpu_trace_counters {
 	uint64_t rays, nodeVisits, triTests;
 } mtsgpu_trace_counters;

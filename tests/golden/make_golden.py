@@ -1,0 +1,69 @@
+#!/usr/bin/env python
+"""Regenerates tests/golden/*.npz from the compiled reference (oracle/_ref/parity, built from
+/root/reference by oracle/Makefile). Run in the build container:  python tests/golden/make_golden.py"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from tests import golden_cases as gc, oracle_util  # noqa: E402
+from mitsuba_renderer_b200 import scenes  # noqa: E402
+
+OUT = os.path.dirname(os.path.abspath(__file__))
+
+
+def save(name, **arrays):
+    np.savez_compressed(os.path.join(OUT, name), **arrays)
+    print(name, {k: getattr(v, "shape", v) for k, v in arrays.items()})
+
+
+def main():
+    assert oracle_util.available(), "build oracle/_ref first (make -C oracle VARIANT=parity)"
+    # ---- ray queries -------------------------------------------------------------------------------
+    for name, scene in (("trace_materials", gc.scene_materials()), ("trace_grid", gc.scene_grid())):
+        rays = gc.trace_rays(scene)
+        sess = oracle_util.Session(scene)
+        hits, full, _ = sess.trace(rays, "closest_full")
+        seg = scenes.shadow_segments(rays, scene)
+        save(name, rays_digest=gc.digest(rays), hits=hits.view(np.uint8), full=full,
+             any_segments=sess.trace(seg, "any")[0].astype(np.uint8), any_rays=sess.trace(rays, "any")[0].astype(np.uint8))
+    scene = gc.scene_smoke()
+    rays = scenes.incoherent_rays(scene, 20000, 7)
+    sess = oracle_util.Session(scene)
+    save("smoke_cornell", rays_digest=gc.digest(rays), hits=sess.trace(rays, "closest")[0].view(np.uint8),
+         occluded=sess.trace(scenes.shadow_segments(rays, scene), "any")[0])
+    # ---- TriAccel records + enlarged scene box --------------------------------------------------------
+    rec, box, _ = oracle_util.Session(gc.scene_materials()).triaccel()
+    save("triaccel_materials", records=rec.view(np.uint8), box=box)
+    # ---- BSDF f / pdf / sample -------------------------------------------------------------------------
+    bs = gc.bsdf_scene()
+    q = gc.bsdf_queries(len(bs.materials), 4000, 21)
+    save("bsdf", queries_digest=gc.digest(q), out=oracle_util.Session(bs).bsdf(q))
+    # ---- luminaire sampling ---------------------------------------------------------------------------
+    ms = gc.scene_materials()
+    q = gc.emitter_queries(ms, 4000)
+    save("emitter", queries_digest=gc.digest(q), out=oracle_util.Session(ms).emitter(q))
+    # ---- camera -------------------------------------------------------------------------------------
+    for ap in (0.0, 0.05):
+        cs = gc.camera_scene(ap)
+        q = gc.camera_samples(cs, 4000)
+        save(f"camera_{'pinhole' if ap == 0 else 'thinlens'}", samples_digest=gc.digest(q), rays=oracle_util.Session(cs).camera(q))
+    # ---- film splat + tabulated filters ----------------------------------------------------------------
+    for name, (ft, crop) in gc.SPLAT_CASES.items():
+        ss = gc.splat_scene(ft, crop)
+        q = gc.splat_samples(ss, 8000)
+        film, table, info = oracle_util.Session(ss).splat(q)
+        save(f"splat_{name}", samples_digest=gc.digest(q), film=film, table=table, filter_size=np.float32(info["filter_size"][0]))
+    # ---- image: the reference's own path tracer at high spp ---------------------------------------------
+    rs = gc.render_scene()
+    import copy
+    hi = copy.copy(rs); hi.spp = 4096
+    ref, _ = oracle_util.Session(hi).render()
+    cpu, _ = oracle_util.Session(rs).render()
+    save("render_cornell48", ref_4096=ref, cpu_64=cpu)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,126 @@
+"""Seeded inputs of the golden fixtures under tests/golden/. Shared by the generator
+(tests/golden/make_golden.py, which runs the compiled reference) and by the tests that replay them."""
+import numpy as np
+
+from mitsuba_renderer_b200 import scenes, scenefile
+
+
+def scene_materials():
+    return scenes.material_test_scene(32, 32, 1)
+
+
+def scene_grid():
+    return scenes.microbench_scene(cells=64, pad_cells=9)
+
+
+def scene_smoke():
+    return scenes.cornell_box(64, 64, 16)
+
+
+def trace_rays(scene, n=3000, seed=11):
+    """Six ray families: kdbench incoherent, pinhole coherent, interior origins, axis-parallel, box-missing,
+    finite intervals. Returns one [N,8] array."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    inc = scenes.incoherent_rays(scene, n, seed)
+    coh = scenes.coherent_rays(scene, int(np.sqrt(n)))
+    lo, hi = scenes.scene_bounds(scene)
+    o = lo + (hi - lo) * rng.random((n, 3))
+    d = rng.normal(size=(n, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    inside = np.empty((n, 8), np.float32)
+    inside[:, :3] = o; inside[:, 3] = 1e-4; inside[:, 4:7] = d; inside[:, 7] = np.inf
+    axis = inside[: n // 4].copy()
+    ax = rng.integers(0, 3, len(axis))
+    axis[:, 4:7] = 0
+    axis[np.arange(len(axis)), 4 + ax] = rng.choice([-1.0, 1.0], len(axis))
+    miss = inc[: n // 4].copy(); miss[:, :3] += (hi - lo).max() * 10
+    finite = inc[: n // 4].copy()
+    finite[:, 7] = rng.random(len(finite)).astype(np.float32) * np.float32(np.linalg.norm(hi - lo))
+    finite[:, 3] = 1e-3
+    return np.ascontiguousarray(np.vstack([inc, coh, inside, axis, miss, finite]), np.float32)
+
+
+def bsdf_scene():
+    s = scenes.cornell_box(16, 16, 1)
+    s.materials = [scenefile.lambertian((0.5, 0.3, 0.7)),
+                   scenefile.microfacet((0.5, 0.5, 0.5), (0.5, 0.5, 0.5), 0.5, 0.5, 0.1),      # data/tests/test_bsdf.xml
+                   scenefile.microfacet((0.2, 0.4, 0.1), (1, 0.9, 0.8), 1.0, 1.0, 0.3, 1.33, 1.0),
+                   scenefile.mirror((0.8, 0.7, 0.9)),
+                   scenefile.roughmetal((1, 1, 1), 0.1),                                         # data/tests/test_bsdf.xml
+                   scenefile.roughmetal((0.9, 0.8, 0.7), 0.4, (0.2, 0.92, 1.1), (3.9, 2.45, 2.14)),
+                   scenefile.dielectric(), scenefile.dielectric(1.33, 1.0, (0.9, 1, 1), (1, 0.8, 0.9))]
+    for sh in s.shapes:
+        sh.material = 0
+    return s
+
+
+def bsdf_queries(n_mat, n, seed):
+    rng = np.random.Generator(np.random.PCG64(seed))
+    q = np.zeros((n, 9), np.float32)
+    q[:, 0] = rng.integers(0, n_mat, n)
+
+    def dirs(k):
+        d = rng.normal(size=(k, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+        return d
+    wi, wo = dirs(n), dirs(n)
+    flip = rng.random(n) < 0.7
+    wi[flip, 2] = np.abs(wi[flip, 2]); wo[flip, 2] = np.abs(wo[flip, 2])
+    q[:, 1:4] = wi; q[:, 4:7] = wo
+    q[:, 7:9] = rng.random((n, 2))
+    for c in (slice(1, 4), slice(4, 7)):
+        q[:, c] /= np.linalg.norm(q[:, c].astype(np.float64), axis=1, keepdims=True).astype(np.float32)
+    return q
+
+
+def emitter_queries(scene, n, seed=4):
+    rng = np.random.Generator(np.random.PCG64(seed))
+    lo, hi = scenes.scene_bounds(scene)
+    q = np.empty((n, 5), np.float32)
+    q[:, :3] = lo + (hi - lo) * rng.random((n, 3))
+    q[:, 3:] = rng.random((n, 2))
+    return q
+
+
+def camera_scene(aperture):
+    s = scenes.cornell_box(200, 120, 1)
+    s.aperture_radius = aperture
+    s.focus_depth = 9.0
+    return s
+
+
+def camera_samples(scene, n, seed=8):
+    q = np.random.Generator(np.random.PCG64(seed)).random((n, 4)).astype(np.float32)
+    q[:, 0] *= scene.width; q[:, 1] *= scene.height
+    return q
+
+
+def splat_scene(filter_type, crop):
+    s = scenes.cornell_box(70, 53, 1)
+    s.filter_type = filter_type
+    s.crop = crop
+    return s
+
+
+def splat_samples(scene, n, seed=12):
+    cx, cy, cw, ch = scene.crop_rect
+    rng = np.random.Generator(np.random.PCG64(seed))
+    q = np.empty((n, 6), np.float32)
+    q[:, 0] = np.minimum(cx + rng.random(n) * cw, np.float32(cx + cw) - np.float32(1e-3))
+    q[:, 1] = np.minimum(cy + rng.random(n) * ch, np.float32(cy + ch) - np.float32(1e-3))
+    q[:, 2:5] = rng.random((n, 3)) * 3; q[:, 5] = rng.integers(0, 2, n)
+    q[::97, 2] = np.nan; q[::89, 3] = -1.0
+    q[:50, 0] = np.floor(q[:50, 0]) + 0.5
+    return q
+
+
+SPLAT_CASES = {"box": (scenefile.FILTER_BOX, None), "gaussian": (scenefile.FILTER_GAUSSIAN, None),
+               "gaussian_crop": (scenefile.FILTER_GAUSSIAN, (5, 9, 50, 37))}
+
+
+def render_scene():
+    return scenes.cornell_box(48, 48, 64, max_depth=8)
+
+
+def digest(a):
+    """Cheap content hash to notice when a generator drifts away from the stored fixtures."""
+    import hashlib
+    return hashlib.sha1(np.ascontiguousarray(a).tobytes()).hexdigest()[:16]

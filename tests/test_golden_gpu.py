@@ -1,0 +1,103 @@
+"""GPU parity against the committed golden vectors (tests/golden/*.npz, produced by the compiled reference
+with tests/golden/make_golden.py). These run on any B200 box, also where neither /root/reference nor
+oracle/_ref exist; the live-oracle tests in test_*_parity.py cover larger randomised inputs."""
+import os
+
+import numpy as np
+import pytest
+
+from mitsuba_renderer_b200 import api, scenes
+from mitsuba_renderer_b200.api import TRACE_CLOSEST, TRACE_ANY, Context
+from tests import golden_cases as gc
+from tests.test_trace_parity import check_closest
+from tests.test_shading_parity import close
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def gold(name):
+    return np.load(os.path.join(GOLD, name + ".npz"))
+
+
+@pytest.mark.parametrize("name,make", [("trace_materials", gc.scene_materials), ("trace_grid", gc.scene_grid)])
+def test_ray_queries_match_golden(name, make, gpu_ctx_factory):
+    scene = make()
+    g = gold(name)
+    rays = gc.trace_rays(scene)
+    assert gc.digest(rays) == str(g["rays_digest"])
+    ctx = gpu_ctx_factory(scene)
+    ref = g["hits"].view(api.HIT_DTYPE).reshape(-1)
+    check_closest(ctx.trace(rays, TRACE_CLOSEST), ref, name)
+    assert np.array_equal(ctx.trace(scenes.shadow_segments(rays, scene), TRACE_ANY), g["any_segments"])
+    assert np.array_equal(ctx.trace(rays, TRACE_ANY), g["any_rays"])
+    hits, full = ctx.intersect_full(rays)
+    same = (hits["shape"] == ref["shape"]) & (hits["prim"] == ref["prim"]) & (ref["shape"] != 0xFFFFFFFF)
+    assert close(full[same], g["full"][same], 1e-5, 1e-6).all()
+
+
+def test_triaccel_matches_golden(gpu_ctx_factory):
+    g = gold("triaccel_materials")
+    ref = g["records"].view(api.TRIACCEL_DTYPE)
+    ctx = gpu_ctx_factory(gc.scene_materials())
+    rec, box = ctx.triaccel(len(ref))
+    assert np.array_equal(box.view(np.uint32), g["box"].view(np.uint32))
+    for f in ("n_u", "n_v", "n_d", "a_u", "a_v", "b_nu", "b_nv", "c_nu", "c_nv"):
+        assert np.array_equal(rec[f].view(np.uint32), ref[f].view(np.uint32)), f
+    assert np.array_equal(rec["k"] & 3, ref["k"] & 3)
+
+
+def test_bsdf_matches_golden(gpu_ctx_factory):
+    bs = gc.bsdf_scene()
+    q = gc.bsdf_queries(len(bs.materials), 4000, 21)
+    g = gold("bsdf")
+    assert gc.digest(q) == str(g["queries_digest"])
+    out = gpu_ctx_factory(bs).bsdf_eval(q)
+    ref = g["out"]
+    assert np.array_equal(out[:, 11], ref[:, 11])
+    assert close(out[:, :4], ref[:, :4]).all()                 # f, pdf at given directions: 1e-5
+    assert close(out[:, 4:7], ref[:, 4:7], 1e-5, 1e-5).all()   # sampled direction: 1e-5 of unit length
+    assert close(out[:, 7:11], ref[:, 7:11], 2e-4, 1e-7).all() and close(out[:, 12:15], ref[:, 12:15], 2e-4, 1e-7).all()
+    bit_exact = np.mean(out[:, 4:7].view(np.uint32) == ref[:, 4:7].view(np.uint32))
+    print(f"sampled directions bit-identical: {bit_exact:.4f}")
+    assert bit_exact > 0.95
+
+
+def test_emitter_and_camera_match_golden(gpu_ctx_factory):
+    ms = gc.scene_materials()
+    out = gpu_ctx_factory(ms).emitter_sample(gc.emitter_queries(ms, 4000))
+    ref = gold("emitter")["out"]
+    assert np.array_equal(out[:, 13], ref[:, 13]) and close(out[:, :15], ref[:, :15], 1e-5, 1e-6).all()
+    for ap, name in ((0.0, "camera_pinhole"), (0.05, "camera_thinlens")):
+        cs = gc.camera_scene(ap)
+        rays = gpu_ctx_factory(cs).camera_rays(gc.camera_samples(cs, 4000))
+        assert close(rays, gold(name)["rays"], 1e-5, 1e-6).all()
+
+
+@pytest.mark.parametrize("name", list(gc.SPLAT_CASES))
+def test_film_splat_matches_golden(name, gpu_ctx_factory):
+    ft, crop = gc.SPLAT_CASES[name]
+    ss = gc.splat_scene(ft, crop)
+    g = gold("splat_" + name)
+    q = gc.splat_samples(ss, 8000)
+    assert gc.digest(q) == str(g["samples_digest"])
+    ctx = gpu_ctx_factory()
+    ctx.set_film(ss, g["table"], float(g["filter_size"]))
+    film = ctx.film_splat(q)
+    assert np.abs(film - g["film"]).max() <= 2e-4 * max(1.0, np.abs(g["film"]).max())
+
+
+def test_render_matches_golden_reference_image(gpu_ctx_factory):
+    rs = gc.render_scene()
+    g = gold("render_cornell48")
+    dev = lambda f: f[..., :3] / np.maximum(f[..., 4:5], 1e-20)
+    ref = dev(g["ref_4096"])
+    rel = lambda a: float(np.mean((a - ref) ** 2 / (ref ** 2 + 1e-4)))
+    ctx = gpu_ctx_factory(rs)
+    gpu, _ = ctx.render(Context.params_from_scene(rs, seed=1))
+    assert rel(dev(gpu)) <= 1.25 * rel(dev(g["cpu_64"])) + 1e-4
+    import copy
+    hi = copy.copy(rs); hi.spp = 4096
+    gpu_hi, _ = ctx.render(Context.params_from_scene(hi, seed=2))
+    assert abs(dev(gpu_hi).mean() - ref.mean()) <= 0.01 * ref.mean()
+    assert rel(dev(gpu_hi)) < 0.2 * rel(dev(g["cpu_64"]))
