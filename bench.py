@@ -221,7 +221,8 @@ def run_ours(args, rank, local_rank, world):
         rctx = api.Context(local_rank)
         rctx.upload_scene(rs)
         film = torch.zeros(512 * 512 * 5, dtype=torch.float32, device="cuda")
-        lo, hi = rs.spp * rank // world, rs.spp * (rank + 1) // world     # sample-range shard of this rank
+        from mitsuba_renderer_b200 import multigpu
+        lo, hi = multigpu.sample_range(rs.spp, rank, world)             # sample-range shard of this rank
         params = api.Context.params_from_scene(rs, lo, hi, seed=1)
         rctx.render_device(params, film.data_ptr())
         torch.cuda.synchronize(); barrier()
@@ -229,7 +230,7 @@ def run_ours(args, rank, local_rank, world):
         st = rctx.render_device(params, film.data_ptr())
         torch.cuda.synchronize()
         if world > 1:
-            dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)     # the one collective: film accumulators over NVLink
+            multigpu.reduce_film(film, dst=0)                   # the one collective: film accumulators over NVLink
             torch.cuda.synchronize()
         barrier()
         dt = max_over_ranks(time.perf_counter() - t0)

@@ -1,0 +1,310 @@
+/*
+ * gpupath — Mitsuba 0.2.1 integrator plugin that runs the `path` / `direct` hot path on a B200 through
+ * libmtscuda.so (C ABI: include/mtsgpu.h). Drop-in: same plugin ABI (MTS_EXPORT_PLUGIN,
+ * include/mitsuba/core/cobject.h:79-87), same scene XML, same Film/Sampler/Camera interfaces.
+ *
+ *   <integrator type="gpupath"> <string name="mode" value="path"/> <integer name="maxDepth" value="8"/> ... </integrator>
+ *
+ * It subclasses SampleIntegrator (include/mitsuba/render/integrator.h:281-398) and overrides render(),
+ * bypassing BlockedRenderProcess (src/librender/integrator.cpp:87-121); the precedent for an integrator
+ * that renders on a device and hands the film a finished image is VPLIntegrator::render
+ * (src/integrators/vpl/vpl.cpp:99-198). There is no CPU fallback: Li() raises an error.
+ */
+#include <mitsuba/render/scene.h>
+#include <mitsuba/render/renderjob.h>
+#include <mitsuba/render/renderqueue.h>
+#include <mitsuba/render/trimesh.h>
+#include <mitsuba/render/imageblock.h>
+#include <mitsuba/core/mstream.h>
+#include <mitsuba/core/statistics.h>
+#include <mitsuba/core/timer.h>
+#include <map>
+#include "mtsgpu.h"
+
+MTS_NAMESPACE_BEGIN
+
+static StatsCounter gpuNormalRays("GPU path tracer", "Normal rays traced");
+static StatsCounter gpuShadowRays("GPU path tracer", "Shadow rays traced");
+
+class GPUPathIntegrator : public SampleIntegrator {
+public:
+	GPUPathIntegrator(const Properties &props) : SampleIntegrator(props), m_cancel(0) {
+		std::string mode = props.getString("mode", "path");
+		if (mode == "path") m_mode = MTSGPU_MODE_PATH;
+		else if (mode == "direct") m_mode = MTSGPU_MODE_DIRECT;
+		else Log(EError, "gpupath: unknown mode \"%s\" (must be \"path\" or \"direct\")", mode.c_str());
+		/* same property names and defaults as MonteCarloIntegrator (integrator.cpp:270-295) and
+		   MIDirectIntegrator (direct.cpp:34-36) */
+		m_maxDepth = props.getInteger("maxDepth", -1);
+		m_rrDepth = props.getInteger("rrDepth", 10);
+		m_strictNormals = props.getBoolean("strictNormals", false);
+		m_luminaireSamples = props.getInteger("luminaireSamples", 1);
+		m_bsdfSamples = props.getInteger("bsdfSamples", 1);
+		m_device = props.getInteger("device", 0);
+		m_seed = props.getInteger("seed", 0);
+		AssertEx(m_rrDepth > 0, "rrDepth == 0 breaks the computation of alpha values!");
+		Assert(m_luminaireSamples + m_bsdfSamples > 0);
+	}
+
+	GPUPathIntegrator(Stream *stream, InstanceManager *manager) : SampleIntegrator(stream, manager), m_cancel(0) {
+		m_mode = stream->readInt(); m_maxDepth = stream->readInt(); m_rrDepth = stream->readInt();
+		m_strictNormals = stream->readBool(); m_luminaireSamples = stream->readInt(); m_bsdfSamples = stream->readInt();
+		m_device = stream->readInt(); m_seed = stream->readInt();
+	}
+
+	void serialize(Stream *stream, InstanceManager *manager) const {
+		SampleIntegrator::serialize(stream, manager);
+		stream->writeInt(m_mode); stream->writeInt(m_maxDepth); stream->writeInt(m_rrDepth);
+		stream->writeBool(m_strictNormals); stream->writeInt(m_luminaireSamples); stream->writeInt(m_bsdfSamples);
+		stream->writeInt(m_device); stream->writeInt(m_seed);
+	}
+
+	Spectrum Li(const RayDifferential &, RadianceQueryRecord &) const {
+		Log(EError, "gpupath has no CPU path: Li() must not be called (use the 'path' or 'direct' plugin on the CPU)");
+		return Spectrum(0.0f);
+	}
+
+	void cancel() { m_cancel = 1; }
+
+	bool render(Scene *scene, RenderQueue *queue, const RenderJob *job, int, int, int) {
+		m_cancel = 0;
+		mtsgpu_ctx *ctx = NULL;
+		if (mtsgpu_create(m_device, &ctx) != MTSGPU_OK)
+			Log(EError, "gpupath: %s", mtsgpu_last_error(NULL));
+		bool ok = false;
+		try {
+			ok = renderImpl(ctx, scene, queue, job);
+		} catch (...) {
+			mtsgpu_destroy(ctx);
+			throw;
+		}
+		mtsgpu_destroy(ctx);
+		return ok;
+	}
+
+	MTS_DECLARE_CLASS()
+private:
+	void check(mtsgpu_ctx *ctx, int rc) const {
+		/* Log(EError) throws std::runtime_error (src/libcore/logger.cpp:137); RenderJob::run catches it and
+		   marks the job cancelled (src/librender/renderjob.cpp:126-130) */
+		if (rc != MTSGPU_OK && rc != MTSGPU_ERR_CANCELLED)
+			Log(EError, "gpupath: %s", mtsgpu_last_error(ctx));
+	}
+
+	/* ---- BSDF parameters: no getters exist, so decode the object's own wire format ---------------------- */
+	static Spectrum readConstantTexture(Stream *s) {
+		/* InstanceManager::serialize (serialization.cpp:75-89): id, class name, payload */
+		if (s->readUInt() == 0)
+			SLog(EError, "gpupath: BSDF without a texture");
+		std::string cls = s->readString();
+		if (cls != "ConstantSpectrumTexture")
+			SLog(EError, "gpupath: texture class \"%s\" is outside the supported hot path (constant spectra only)", cls.c_str());
+		if (s->readUInt() != 0)   /* ConfigurableObject::serialize: parent reference */
+			SLog(EError, "gpupath: unexpected texture parent");
+		return Spectrum(s);
+	}
+
+	static void put(float *dst, const Spectrum &v) { Float r, g, b; v.toLinearRGB(r, g, b); dst[0] = r; dst[1] = g; dst[2] = b; }
+
+	static mtsgpu_material decodeBSDF(const BSDF *bsdf) {
+		mtsgpu_material m; memset(&m, 0, sizeof(m));
+		ref<MemoryStream> s = new MemoryStream();
+		ref<InstanceManager> mgr = new InstanceManager();
+		bsdf->serialize(s, mgr);
+		s->setPos(0);
+		if (s->readUInt() != 0)            /* BSDF::setParent is a no-op (bsdf.cpp:55-57) => parent id 0 */
+			SLog(EError, "gpupath: unexpected BSDF parent");
+		s->readString();                   /* BSDF::serialize: m_name (bsdf.cpp:50-53) */
+		const std::string cls = bsdf->getClass()->getName();
+		if (cls == "Lambertian") {                    /* lambertian.cpp:137-141 */
+			m.type = MTSGPU_BSDF_LAMBERTIAN;
+			put(m.p, readConstantTexture(s));
+		} else if (cls == "Microfacet") {             /* microfacet.cpp:283-293 */
+			m.type = MTSGPU_BSDF_MICROFACET;
+			put(m.p, readConstantTexture(s)); put(m.p + 3, readConstantTexture(s));
+			m.p[8] = s->readFloat(); m.p[6] = s->readFloat(); m.p[7] = s->readFloat();   /* alphaB, kd, ks */
+			m.p[9] = s->readFloat(); m.p[10] = s->readFloat();                            /* intIOR, extIOR */
+		} else if (cls == "Mirror") {                 /* mirror.cpp:51-55 */
+			m.type = MTSGPU_BSDF_MIRROR;
+			put(m.p, Spectrum(s));
+		} else if (cls == "RoughMetal") {             /* roughmetal.cpp:169-176 */
+			m.type = MTSGPU_BSDF_ROUGHMETAL;
+			put(m.p, readConstantTexture(s));
+			m.p[3] = s->readFloat();
+			put(m.p + 4, Spectrum(s)); put(m.p + 7, Spectrum(s));
+		} else if (cls == "Dielectric") {             /* dielectric.cpp:88-95 */
+			m.type = MTSGPU_BSDF_DIELECTRIC;
+			m.p[6] = s->readFloat(); m.p[7] = s->readFloat();
+			put(m.p, readConstantTexture(s)); put(m.p + 3, readConstantTexture(s));
+		} else {
+			SLog(EError, "gpupath: BSDF class \"%s\" is outside the supported hot path "
+				"(lambertian, microfacet, mirror, roughmetal, dielectric)", cls.c_str());
+		}
+		return m;
+	}
+
+	bool renderImpl(mtsgpu_ctx *ctx, Scene *scene, RenderQueue *queue, const RenderJob *job) {
+		ref<Timer> timer = new Timer();
+		const Camera *camera = scene->getCamera();
+		Film *film = scene->getFilm();
+		const Sampler *sampler = scene->getSampler();
+
+		/* ---- refuse what the hot path does not cover ---- */
+		if (!camera->getClass()->derivesFrom(MTS_CLASS(PerspectiveCamera)))
+			Log(EError, "gpupath: only the perspective camera is supported");
+		if (scene->hasBackgroundLuminaire())
+			Log(EError, "gpupath: background luminaires are outside the supported hot path");
+		if (!scene->getMedia().empty() || camera->getMedium() != NULL)
+			Log(EError, "gpupath: participating media are outside the supported hot path");
+
+		/* ---- shapes in kd-tree order, materials, emitters ---- */
+		const std::vector<const Shape *> &shapes = scene->getKDTree()->getShapes();
+		const std::vector<Luminaire *> &luminaires = scene->getLuminaires();
+		std::vector<mtsgpu_material> materials;
+		std::map<const BSDF *, int> materialIds;
+		std::vector<mtsgpu_emitter> emitters(luminaires.size());
+		std::map<const Luminaire *, int> emitterIds;
+		for (size_t i = 0; i < luminaires.size(); ++i) {
+			const Luminaire *lum = luminaires[i];
+			if (lum->getClass()->getName() != "AreaLuminaire")
+				Log(EError, "gpupath: luminaire class \"%s\" is outside the supported hot path (area only)",
+					lum->getClass()->getName().c_str());
+			/* AreaLuminaire::Le returns m_intensity for any direction on the normal's side (area.cpp:62-66) */
+			put(emitters[i].intensity, lum->Le(ShapeSamplingRecord(Point(0.0f), Normal(0, 0, 1)), Vector(0, 0, 1)));
+			emitters[i].samplingWeight = lum->getSamplingWeight();
+			emitterIds[lum] = (int) i;
+		}
+		struct MeshRef { const TriMesh *mesh; int mat, emit; };
+		std::vector<MeshRef> meshes;
+		for (size_t i = 0; i < shapes.size(); ++i) {
+			const Shape *shape = shapes[i];
+			if (!shape->getClass()->derivesFrom(MTS_CLASS(TriMesh)))
+				Log(EError, "gpupath: shape %i (%s) is not a triangle mesh", (int) i, shape->getClass()->getName().c_str());
+			if (shape->hasSubsurface() || shape->isMediumTransition())
+				Log(EError, "gpupath: subsurface / medium transitions are outside the supported hot path");
+			MeshRef r; r.mesh = static_cast<const TriMesh *>(shape); r.mat = -1; r.emit = -1;
+			if (shape->hasBSDF()) {
+				const BSDF *bsdf = shape->getBSDF();
+				if (!materialIds.count(bsdf)) {
+					materialIds[bsdf] = (int) materials.size();
+					materials.push_back(decodeBSDF(bsdf));
+				}
+				r.mat = materialIds[bsdf];
+			}
+			if (shape->isLuminaire())
+				r.emit = emitterIds[shape->getLuminaire()];
+			meshes.push_back(r);
+		}
+		check(ctx, mtsgpu_upload_materials(ctx, materials.empty() ? NULL : &materials[0], (int) materials.size()));
+		check(ctx, mtsgpu_upload_emitters(ctx, emitters.empty() ? NULL : &emitters[0], (int) emitters.size()));
+		for (size_t i = 0; i < meshes.size(); ++i) {
+			const TriMesh *m = meshes[i].mesh;
+			/* Point/Normal are 3 packed floats, Triangle is 3 packed uint32 (core/triangle.h) */
+			check(ctx, mtsgpu_upload_mesh(ctx, (int) i,
+				reinterpret_cast<const float *>(m->getVertexPositions()),
+				reinterpret_cast<const float *>(m->getVertexNormals()), NULL, (uint32_t) m->getVertexCount(),
+				reinterpret_cast<const uint32_t *>(m->getTriangles()), (uint32_t) m->getTriangleCount(),
+				meshes[i].mat, meshes[i].emit));
+		}
+
+		/* ---- camera: m_rasterToCamera is private to the plugin class, so rebuild it with the same
+		        Transform operations as PerspectiveCameraImpl::configure (perspective.cpp:43-71) ---- */
+		const PerspectiveCamera *pc = static_cast<const PerspectiveCamera *>(camera);
+		const Vector2i fsize = film->getSize();
+		const Float aspect = (Float) fsize.x / (Float) fsize.y;
+		const bool mapSmallerSide = camera->getProperties().getBoolean("mapSmallerSide", true);
+		Transform screenToRaster;
+		if ((aspect >= 1.0f) ^ !mapSmallerSide) {
+			screenToRaster = Transform::scale(Vector((Float) fsize.x, (Float) fsize.y, 1.0f))
+				* Transform::scale(Vector(1 / (2 * aspect), -0.5f, 1.0f))
+				* Transform::translate(Vector(aspect, -1.0f, 0));
+		} else {
+			screenToRaster = Transform::scale(Vector((Float) fsize.x, (Float) fsize.y, 1.0f))
+				* Transform::scale(Vector(0.5f, -0.5f * aspect, 1.0f))
+				* Transform::translate(Vector(1.0f, -1 / aspect, 0));
+		}
+		const Transform rasterToCamera = pc->getProjectionTransform().inverse() * screenToRaster.inverse();
+		{
+			/* cross-check against the camera's own generateRay at three raster positions */
+			const Point2 probes[3] = { Point2(0.5f, 0.5f), Point2(fsize.x - 0.5f, 0.5f), Point2(fsize.x * 0.5f, fsize.y - 0.5f) };
+			for (int k = 0; k < 3 && pc->getApertureRadius() == 0; ++k) {
+				Ray r; camera->generateRay(probes[k], Point2(0.5f), 0.0f, r);
+				Point ic = rasterToCamera(Point(probes[k].x, probes[k].y, 0));
+				Vector d = camera->getInverseViewTransform()(normalize(Vector(ic)));
+				if ((d - r.d).length() > 1e-4f)
+					Log(EError, "gpupath: could not reproduce the camera's raster-to-camera transform");
+			}
+		}
+		float r2c[16], c2w[16];
+		for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) {
+			r2c[i * 4 + j] = rasterToCamera.getMatrix().m[i][j];
+			c2w[i * 4 + j] = camera->getInverseViewTransform().getMatrix().m[i][j];
+		}
+		check(ctx, mtsgpu_set_camera(ctx, r2c, c2w, pc->getNearClip(), pc->getFarClip(), pc->getApertureRadius(),
+			pc->getFocusDepth(), camera->getShutterOpen(), camera->getShutterOpenTime()));
+
+		/* ---- film + tabulated filter (rfilter.h:65-118) ---- */
+		const TabulatedFilter *filter = film->getTabulatedFilter();
+		float table[256];
+		for (int y = 0; y < 16; ++y) for (int x = 0; x < 16; ++x) table[y * 16 + x] = filter->lookup(x, y);
+		const Vector2i csize = film->getCropSize(); const Point2i coff = film->getCropOffset();
+		check(ctx, mtsgpu_set_film(ctx, fsize.x, fsize.y, coff.x, coff.y, csize.x, csize.y, table,
+			filter->getFilterSize().x, filter->getFilterSize().y));
+
+		check(ctx, mtsgpu_build_accel(ctx));
+		mtsgpu_accel_info info; check(ctx, mtsgpu_accel_info_get(ctx, &info));
+		Log(EInfo, "gpupath: %u triangles, %u BVH nodes, built on the GPU in %.1f ms (upload + build %i ms)",
+			(unsigned) info.triangles, (unsigned) info.nodes, info.buildMs, timer->getMilliseconds());
+
+		/* ---- render ---- */
+		mtsgpu_render_params P; memset(&P, 0, sizeof(P));
+		P.mode = m_mode; P.maxDepth = m_maxDepth; P.rrDepth = m_rrDepth; P.strictNormals = m_strictNormals ? 1 : 0;
+		P.luminaireSamples = m_luminaireSamples; P.bsdfSamples = m_bsdfSamples;
+		P.sppTotal = (uint32_t) sampler->getSampleCount(); P.sppBegin = 0; P.sppEnd = P.sppTotal;
+		P.seed = (uint32_t) m_seed; P.importanceSampleLuminaires = 1;
+		const size_t nPix = (size_t) csize.x * csize.y;
+		std::vector<float> accum(nPix * 5);
+		mtsgpu_stats stats;
+		timer->reset();
+		const int rc = mtsgpu_render(ctx, &P, &m_cancel, &accum[0], &stats);
+		if (rc == MTSGPU_ERR_CANCELLED)
+			return false;
+		check(ctx, rc);
+		gpuNormalRays += (size_t) stats.normalRays; gpuShadowRays += (size_t) stats.shadowRays;
+		Log(EInfo, "gpupath: %.1f M samples in %i ms (%.1f Msamples/s), %.1f M closest-hit + %.1f M shadow rays "
+			"(closest %.1f ms, shadow %.1f ms on the device)", stats.samples * 1e-6, timer->getMilliseconds(),
+			stats.samples * 1e-3 / std::max(stats.totalMs, 1e-3), stats.normalRays * 1e-6, stats.shadowRays * 1e-6,
+			stats.traceClosestMs, stats.traceAnyMs);
+
+		/* ---- hand {sum spec, sum alpha, sum weight} to the film as one full-frame ImageBlock, through the
+		        block's own wire format (ImageBlock::load, imageblock.cpp:89-106): there is no alpha setter ---- */
+		ref<ImageBlock> block = new ImageBlock(csize, 0, true, true, false, false);
+		ref<MemoryStream> ms = new MemoryStream(nPix * 20 + 64);
+		coff.serialize(ms); csize.serialize(ms);
+		std::vector<Float> tmp(nPix * 3);
+		for (size_t i = 0; i < nPix; ++i) {
+			Spectrum s; s.fromLinearRGB(accum[i * 5], accum[i * 5 + 1], accum[i * 5 + 2]);
+			Float r, g, b; s.toLinearRGB(r, g, b);
+			tmp[i * 3] = r; tmp[i * 3 + 1] = g; tmp[i * 3 + 2] = b;
+		}
+		ms->writeFloatArray(&tmp[0], nPix * 3);
+		for (size_t i = 0; i < nPix; ++i) tmp[i] = accum[i * 5 + 3];
+		ms->writeFloatArray(&tmp[0], nPix);
+		for (size_t i = 0; i < nPix; ++i) tmp[i] = accum[i * 5 + 4];
+		ms->writeFloatArray(&tmp[0], nPix);
+		ms->writeInt(0);
+		ms->setPos(0);
+		block->load(ms);
+		film->putImageBlock(block);
+		queue->signalWorkEnd(job, block);
+		return true;
+	}
+
+	int m_mode, m_maxDepth, m_rrDepth, m_luminaireSamples, m_bsdfSamples, m_device, m_seed;
+	bool m_strictNormals;
+	volatile int m_cancel;
+};
+
+MTS_IMPLEMENT_CLASS_S(GPUPathIntegrator, false, SampleIntegrator)
+MTS_EXPORT_PLUGIN(GPUPathIntegrator, "CUDA (sm_100a) wavefront path tracer");
+MTS_NAMESPACE_END

@@ -1,0 +1,56 @@
+"""Drop-in test of plugins/gpupath.so: the REAL Mitsuba PluginManager (compiled reference) dlopens the
+plugin, Scene::render calls GPUPathIntegrator::render, the image comes back through Film::putImageBlock.
+The scene is built by the harness exactly as SceneHandler would from
+<integrator type="gpupath">; nothing else in the scene changes."""
+import os
+
+import numpy as np
+import pytest
+
+from mitsuba_renderer_b200 import scenes, scenefile
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PLUGIN_DIR = os.path.join(ROOT, "mitsuba-renderer_b200")
+PLUGIN = os.path.join(PLUGIN_DIR, "plugins", "gpupath.so")
+
+
+def develop(film):
+    return film[..., :3] / np.maximum(film[..., 4:5], 1e-20)
+
+
+def need_plugin():
+    if not os.path.exists(PLUGIN):
+        pytest.skip("plugins/gpupath.so is not built (needs the reference headers)")
+
+
+def test_plugin_fails_loudly_without_a_gpu(oracle):
+    """No CPU fallback: without a CUDA device the job is cancelled through the reference's own error path
+    (Log(EError) -> exception -> RenderJob marks the job cancelled, renderjob.cpp:126-130)."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    need_plugin()
+    s = scenes.cornell_box(16, 16, 1)
+    film, info = oracle.Session(s).render(1, "gpupath", env={"MTS_PLUGIN_PATH": PLUGIN_DIR})
+    assert info["integrator"] == "gpupath" and not film.any()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", [scenefile.MODE_PATH, scenefile.MODE_DIRECT])
+def test_plugin_renders_through_mitsuba(oracle, mode):
+    need_plugin()
+    s = scenes.material_test_scene(64, 64, 256, mode, max_depth=8)
+    s.filter_type = scenefile.FILTER_GAUSSIAN if mode == scenefile.MODE_DIRECT else scenefile.FILTER_BOX
+    sess = oracle.Session(s)
+    gpu, info = sess.render(2, "gpupath", env={"MTS_PLUGIN_PATH": PLUGIN_DIR})
+    cpu, _ = sess.render()
+    assert gpu[..., 4].sum() > 0, "the plugin produced no image (did the job get cancelled?)"
+    assert np.isclose(gpu[..., 4].sum(), cpu[..., 4].sum(), rtol=1e-3)
+    assert np.isclose(gpu[..., 3].sum(), cpu[..., 3].sum(), rtol=1e-2)
+    g, c = develop(gpu), develop(cpu)
+    assert abs(g.mean() - c.mean()) <= 0.02 * c.mean()
+    for ch in range(3):
+        assert abs(g[..., ch].mean() - c[..., ch].mean()) <= 0.03 * c[..., ch].mean() + 1e-4
+    rel = float(np.mean((g - c) ** 2 / (c ** 2 + 1e-4)))
+    print(f"mode {mode}: relMSE gpu-plugin vs cpu at 256 spp = {rel:.5f}; {info}")
+    assert rel < 0.2
