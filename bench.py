@@ -217,28 +217,47 @@ def run_ours(args, rank, local_rank, world):
     # ---- render leg: config C1 (Cornell box, path maxDepth 8, 64 spp, 512x512, box filter) -----------
     render = None
     if not args.no_render:
-        rs = scenes.cornell_box(512, 512, 64)
+        from mitsuba_renderer_b200 import multigpu
+        if args.render == "c1":
+            rs, rname = scenes.cornell_box(512, 512, 64), "C1: Cornell box 512x512, path maxDepth 8, 64 spp, box filter"
+        elif args.render == "c3":
+            rs, rname = scenes.direct_scene(), "C3: direct 1+1, 1M triangles, 3 BSDFs + mirror, 8 area lights, 1920x1080, 256 spp"
+        elif args.render == "c4":
+            rs, rname = scenes.path_scene(), "C4: path maxDepth 16 + RR, 10M triangles (roughmetal terrain + roughmetal/dielectric spheres), 1920x1080, 1024 spp"
+        else:
+            rs, rname = scenes.path_scene(width=3840, height=2160, spp=4096), "C5: as C4 at 3840x2160, 4096 spp"
+        if args.render_spp:
+            rs.spp = args.render_spp
+            rname += f" [spp overridden to {args.render_spp}]"
         rctx = api.Context(local_rank)
         rctx.upload_scene(rs)
-        film = torch.zeros(512 * 512 * 5, dtype=torch.float32, device="cuda")
-        from mitsuba_renderer_b200 import multigpu
+        raccel = rctx.accel_info()
+        film = torch.zeros(rs.width * rs.height * 5, dtype=torch.float32, device="cuda")
         lo, hi = multigpu.sample_range(rs.spp, rank, world)             # sample-range shard of this rank
         params = api.Context.params_from_scene(rs, lo, hi, seed=1)
-        rctx.render_device(params, film.data_ptr())
+        warm = api.Context.params_from_scene(rs, lo, min(hi, lo + 1), seed=1)
+        rctx.render_device(warm, film.data_ptr())                       # warm-up: 1 spp
         torch.cuda.synchronize(); barrier()
         t0 = time.perf_counter()
         st = rctx.render_device(params, film.data_ptr())
         torch.cuda.synchronize()
+        t_render = time.perf_counter() - t0
         if world > 1:
             multigpu.reduce_film(film, dst=0)                   # the one collective: film accumulators over NVLink
             torch.cuda.synchronize()
+        t_reduce = time.perf_counter() - t0 - t_render
         barrier()
         dt = max_over_ranks(time.perf_counter() - t0)
-        rays_total = st["normalRays"] + st["shadowRays"]
-        render = {"workload": "C1: Cornell box 512x512, path maxDepth 8, 64 spp, box filter", "seconds": dt,
-                  "samples_per_s": 512 * 512 * 64 / dt, "mrays_per_s_rank0": rays_total / dt * 1e-6 * 1.0,
-                  "kernel_launches_rank0": st["kernelLaunches"], "trace_closest_ms": st["traceClosestMs"], "trace_any_ms": st["traceAnyMs"],
-                  "film_reduce": "ncclReduce(sum)" if world > 1 else "none (1 GPU)"}
+        rays = torch.tensor([float(st["normalRays"]), float(st["shadowRays"])], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(rays)
+        render = {"workload": rname, "triangles": rs.triangle_count, "seconds": dt, "scaling": "strong",
+                  "samples_per_s": rs.width * rs.height * rs.spp / dt, "mrays_per_s": float(rays.sum().item()) / dt * 1e-6,
+                  "normal_rays": float(rays[0].item()), "shadow_rays": float(rays[1].item()),
+                  "kernel_launches_rank0": st["kernelLaunches"], "trace_closest_ms_rank0": st["traceClosestMs"],
+                  "trace_any_ms_rank0": st["traceAnyMs"], "other_ms_rank0": st["shadeMs"], "render_s_rank0": t_render,
+                  "film_reduce_s_rank0": t_reduce, "film_reduce": "ncclReduce(sum) of W*H*5 floats" if world > 1 else "none (1 GPU)",
+                  "bvh_build_ms": raccel["buildMs"], "bvh_nodes": raccel["nodes"]}
         rctx.close()
 
     cpu_baseline = None
@@ -277,6 +296,8 @@ def main():
     ap.add_argument("--rays", type=int, default=1 << 24, help="rays per batch (coherent batch is the nearest square)")
     ap.add_argument("--cpu-rays", type=int, default=0, help="rays per batch of the bounded CPU sample (0 = auto)")
     ap.add_argument("--no-render", action="store_true")
+    ap.add_argument("--render", default="c1", choices=["c1", "c3", "c4", "c5"], help="config of the render leg")
+    ap.add_argument("--render-spp", type=int, default=0, help="override the render leg's samples per pixel")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); local_rank = int(os.environ.get("LOCAL_RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
