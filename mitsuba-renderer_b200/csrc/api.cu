@@ -46,6 +46,7 @@ void mtsgpu_destroy(mtsgpu_ctx *ctx) {
 	cudaStreamSynchronize(ctx->stream);
 	for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
 	cudaStreamDestroy(ctx->stream);
+	if (ctx->hCounts) cudaFreeHost(ctx->hCounts);
 	delete ctx;
 }
 

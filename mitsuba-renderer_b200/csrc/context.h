@@ -53,13 +53,17 @@ struct mtsgpu_ctx {
 	mtsgpu_accel_info accel = {};
 
 	// trace staging + counters
-	DevBuf dRays, dHits, dCounters;
+	DevBuf dRays, dHits, dCounters, dRayCounters;
+	uint32_t rayCounterNext = 0;
+	int smCount = 0;
 	bool countersEnabled = false;
 	mtsgpu_trace_counters lastCounters = {};
 
 	// wavefront state (integrate.cu)
 	DevBuf dPathState, dRayA, dRayB, dHit, dShadowRay, dShadowPayload, dQueueA, dQueueB, dQueueCounts,
 	       dResult, dFilm, dStage, dStageOut;
+	DevBuf dPrimSlot, dPrimRay, dPrimHit, dFilterTable;
+	uint32_t *hCounts = nullptr;     // pinned host mirror of the queue counters
 	uint32_t pathCapacity = 0;
 };
 
@@ -74,6 +78,8 @@ int setError(mtsgpu_ctx *ctx, int code, const char *fmt, ...);
 int buildAccel(mtsgpu_ctx *ctx);
 int rebuildLuminaireCdf(mtsgpu_ctx *ctx, bool importance);
 // trace.cu
+unsigned tracePersistentBlocks(mtsgpu_ctx *ctx, size_t n);
+int traceRayCounter(mtsgpu_ctx *ctx, uint32_t **out);
 int launchTrace(mtsgpu_ctx *ctx, const float4 *dRays, size_t n, int mode, void *dOut, uint64_t *dCounters);
 // integrate.cu
 int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, volatile const int *cancel,

@@ -22,6 +22,7 @@
 #include "bsdf.cuh"
 #include "sampling.cuh"
 #include <algorithm>
+#include <cstdlib>
 
 #define TILE 16
 #define TILE_PIX (TILE * TILE)
@@ -123,6 +124,10 @@ k_generate(const CameraDev cam, const FilmDev film, const BatchDesc b, WfArrays 
 	}
 }
 
+// Wavefront traversal kernels: one thread per queue entry. Path-tracing queues are largely coherent
+// (camera rays, glossy bounces off neighbouring pixels, shadow rays towards a handful of emitters), and for
+// those the plain lock-step kernel measured faster than the persistent-warp variant the ray-query API uses
+// (C4, 10M triangles: 101 ms vs 120 ms per 16 spp; see profiles/ and DESIGN.md §5).
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_closest_wf(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint4 *__restrict__ hits) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
@@ -455,7 +460,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 		int rc = rebuildLuminaireCdf(ctx, P->importanceSampleLuminaires != 0);
 		if (rc) return rc;
 	}
-	DevBuf dTable;
+	DevBuf &dTable = ctx->dFilterTable;
 	{ int rc = uploadFilter(ctx, dTable); if (rc) return rc; }
 
 	k_zero<<<blocksFor(filmFloats, 256), 256, 0, st>>>(dOutFilm, filmFloats);
@@ -469,12 +474,12 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 	cudaEvent_t evBegin = ctx->ev[0], evEnd = ctx->ev[1], evA = ctx->ev[2], evB = ctx->ev[3];
 	CUDA_TRY(ctx, cudaEventRecord(evBegin, st));
 	if (spp > 0) {
-		const uint32_t maxSlots = 1u << 23;
+		const uint32_t maxSlots = 1u << 25;     // 192 B of queue + path state per slot => ~6.4 GB at full size
 		uint32_t sampleChunk = std::min<uint32_t>(spp, maxSlots / TILE_PIX);
 		uint32_t tilesPerBatch = std::max<uint32_t>(1u, std::min<uint32_t>(nTiles, maxSlots / (TILE_PIX * sampleChunk)));
 		const uint32_t capacity = tilesPerBatch * sampleChunk * TILE_PIX;
 		{ int rc = ensureWavefront(ctx, capacity); if (rc) return rc; }
-		DevBuf dPrimSlot, dPrimRay, dPrimHit;
+		DevBuf &dPrimSlot = ctx->dPrimSlot, &dPrimRay = ctx->dPrimRay, &dPrimHit = ctx->dPrimHit;
 		if (P->mode == MTSGPU_MODE_DIRECT) {
 			CUDA_TRY(ctx, dPrimSlot.alloc((size_t) capacity * 4));
 			CUDA_TRY(ctx, dPrimRay.alloc((size_t) capacity * 32));
@@ -497,10 +502,10 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 		if (P->mode == MTSGPU_MODE_DIRECT) ig.strictNormals = 0;     // MIDirectIntegrator has no such property
 		const int splatSmem = (TILE + 2 * film.border) * (TILE + 2 * film.border) * 5 * (int) sizeof(float);
 
-		uint32_t *hCounts = nullptr;
-		CUDA_TRY(ctx, cudaMallocHost(&hCounts, 64));
+		if (!ctx->hCounts) CUDA_TRY(ctx, cudaMallocHost(&ctx->hCounts, 64));     // pinned, kept for the context's lifetime
+		uint32_t *hCounts = ctx->hCounts;
 		int rc = MTSGPU_OK;
-		auto fail = [&](int code) { cudaFreeHost(hCounts); return code; };
+		auto fail = [&](int code) { return code; };
 		float msClosest = 0, msShadow = 0;
 
 		for (uint32_t t0 = 0; t0 < nTiles && rc == MTSGPU_OK; t0 += tilesPerBatch) {
@@ -551,7 +556,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 					// primary hit once, kept in the *Prim buffers; then `rounds` passes of (NEE, BSDF ray)
 					wf.slotCur = slotBuf[cur]; wf.rayCur = rayBuf[cur];
 					cudaEventRecord(evA, st);
-					k_closest_wf<<<blocksFor(nRays, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(ctx->scene, wf.rayCur, nRays, wf.hitPrim);
+						k_closest_wf<<<blocksFor(nRays, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(ctx->scene, wf.rayCur, nRays, wf.hitPrim);
 					cudaEventRecord(evB, st);
 					CUDA_TRY(ctx, cudaMemcpyAsync(wf.slotPrim, wf.slotCur, (size_t) nRays * 4, cudaMemcpyDeviceToDevice, st));
 					CUDA_TRY(ctx, cudaMemcpyAsync(wf.rayPrim, wf.rayCur, (size_t) nRays * 32, cudaMemcpyDeviceToDevice, st));
@@ -579,7 +584,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 						if (nSec > 0) {
 							wf.slotCur = slotBuf[cur ^ 1]; wf.rayCur = rayBuf[cur ^ 1];
 							cudaEventRecord(evA, st);
-							k_closest_wf<<<blocksFor(nSec, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(ctx->scene, wf.rayCur, nSec, wf.hit);
+						k_closest_wf<<<blocksFor(nSec, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(ctx->scene, wf.rayCur, nSec, wf.hit);
 							cudaEventRecord(evB, st);
 							k_shade<2><<<blocksFor(nSec, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nSec, (uint32_t) r);
 							CUDA_TRY(ctx, cudaStreamSynchronize(st));
@@ -597,7 +602,6 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 		S.samples = S.cameraRays;
 		S.traceClosestMs = msClosest; S.traceAnyMs = msShadow;
 		if (rc != MTSGPU_OK) return fail(rc);
-		cudaFreeHost(hCounts);
 	}
 	CUDA_TRY(ctx, cudaEventRecord(evEnd, st));
 	CUDA_TRY(ctx, cudaStreamSynchronize(st));

@@ -1,87 +1,104 @@
 // Batch ray-query kernels behind mtsgpu_trace / mtsgpu_trace_device and the wavefront loop.
 #include "context.h"
 #include "trace.cuh"
+#include <algorithm>
+#include <cstdlib>
 
 namespace {
 
-// rays: 2 x float4 per ray {o.xyz, mint}{d.xyz, maxt}. One thread per ray; 128-bit loads.
-template <bool COUNT>
-__global__ void __launch_bounds__(TRACE_BLOCK)
-k_trace_closest(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, mtsgpu_hit *__restrict__ out,
-		unsigned long long *counters) {
-	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
-	const uint32_t i = blockIdx.x * TRACE_BLOCK + threadIdx.x;
-	uint32_t nodeVisits = 0, triTests = 0;
-	if (i < n) {
-		const float4 a = __ldg(rays + 2 * (size_t) i), b = __ldg(rays + 2 * (size_t) i + 1);
-		RayIn r = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+// Output sinks of the persistent traversal (trace.cuh)
+struct HitSink {
+	const DeviceScene &sc; mtsgpu_hit *out;
+	__device__ __forceinline__ void closest(uint32_t ray, bool found, float t, float u, float v, uint32_t tri) {
 		mtsgpu_hit h; h.t = INFINITY; h.u = h.v = 0; h.shape = h.prim = 0xFFFFFFFFu;
-		float mint, maxt;
-		if (clipToScene<false>(sc, r, mint, maxt)) {
-			HitOut ho;
-			if (traverse<false, COUNT>(sc, r, mint, maxt, sstack, ho, nodeVisits, triTests)) {
-				const float4 q2 = __ldg(sc.triAccel + (size_t) ho.tri * 3 + 2);
-				h.t = ho.t; h.u = ho.u; h.v = ho.v;
-				h.shape = __float_as_uint(q2.z); h.prim = __float_as_uint(q2.w);
-			}
+		if (found) {
+			const float4 q2 = __ldg(sc.triAccel + (size_t) tri * 3 + 2);
+			h.t = t; h.u = u; h.v = v; h.shape = __float_as_uint(q2.z); h.prim = __float_as_uint(q2.w);
 		}
-		out[i] = h;
+		out[ray] = h;
 	}
-	if (COUNT) {
-		for (int o = 16; o > 0; o >>= 1) {
-			nodeVisits += __shfl_xor_sync(0xFFFFFFFFu, nodeVisits, o);
-			triTests += __shfl_xor_sync(0xFFFFFFFFu, triTests, o);
-		}
-		if ((threadIdx.x & 31) == 0) {
-			atomicAdd(&counters[0], (unsigned long long) nodeVisits);
-			atomicAdd(&counters[1], (unsigned long long) triTests);
-		}
+	__device__ __forceinline__ void any(uint32_t, bool) { }
+};
+struct OccludedSink {
+	uint32_t *out;
+	__device__ __forceinline__ void closest(uint32_t, bool, float, float, float, uint32_t) { }
+	__device__ __forceinline__ void any(uint32_t ray, bool occluded) { out[ray] = occluded ? 1u : 0u; }
+};
+
+__device__ __forceinline__ void flushCounters(uint32_t nodeVisits, uint32_t triTests, unsigned long long *counters) {
+	for (int o = 16; o > 0; o >>= 1) {
+		nodeVisits += __shfl_xor_sync(0xFFFFFFFFu, nodeVisits, o);
+		triTests += __shfl_xor_sync(0xFFFFFFFFu, triTests, o);
+	}
+	if ((threadIdx.x & 31) == 0) {
+		atomicAdd(&counters[0], (unsigned long long) nodeVisits);
+		atomicAdd(&counters[1], (unsigned long long) triTests);
 	}
 }
 
+// rays: 2 x float4 per ray {o.xyz, mint}{d.xyz, maxt}; 128-bit loads. Persistent warps pull rays from
+// `rayCounter` (zeroed by the host before the launch).
 template <bool COUNT>
-__global__ void __launch_bounds__(TRACE_BLOCK)
-k_trace_any(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint32_t *__restrict__ out,
-		unsigned long long *counters) {
+__global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
+k_trace_closest(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, mtsgpu_hit *__restrict__ out,
+		uint32_t *rayCounter, unsigned long long *counters, int refetchBelow, int speculate) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
-	const uint32_t i = blockIdx.x * TRACE_BLOCK + threadIdx.x;
 	uint32_t nodeVisits = 0, triTests = 0;
-	if (i < n) {
-		const float4 a = __ldg(rays + 2 * (size_t) i), b = __ldg(rays + 2 * (size_t) i + 1);
-		RayIn r = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
-		float mint, maxt; uint32_t occluded = 0;
-		if (clipToScene<true>(sc, r, mint, maxt)) {
-			HitOut ho;
-			occluded = traverse<true, COUNT>(sc, r, mint, maxt, sstack, ho, nodeVisits, triTests) ? 1u : 0u;
-		}
-		out[i] = occluded;
-	}
-	if (COUNT) {
-		for (int o = 16; o > 0; o >>= 1) {
-			nodeVisits += __shfl_xor_sync(0xFFFFFFFFu, nodeVisits, o);
-			triTests += __shfl_xor_sync(0xFFFFFFFFu, triTests, o);
-		}
-		if ((threadIdx.x & 31) == 0) {
-			atomicAdd(&counters[0], (unsigned long long) nodeVisits);
-			atomicAdd(&counters[1], (unsigned long long) triTests);
-		}
-	}
+	HitSink sink = { sc, out };
+	tracePersistent<false, COUNT>(sc, rays, n, rayCounter, sink, sstack, nodeVisits, triTests, refetchBelow, speculate != 0);
+	if (COUNT) flushCounters(nodeVisits, triTests, counters);
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
+k_trace_any(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint32_t *__restrict__ out,
+		uint32_t *rayCounter, unsigned long long *counters, int refetchBelow, int speculate) {
+	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
+	uint32_t nodeVisits = 0, triTests = 0;
+	OccludedSink sink = { out };
+	tracePersistent<true, COUNT>(sc, rays, n, rayCounter, sink, sstack, nodeVisits, triTests, refetchBelow, speculate != 0);
+	if (COUNT) flushCounters(nodeVisits, triTests, counters);
 }
 
 } // namespace
+
+// Grid of the persistent kernels: one wave of resident CTAs (SM count x CTAs per SM), fewer for small batches.
+unsigned tracePersistentBlocks(mtsgpu_ctx *ctx, size_t n) {
+	if (ctx->smCount == 0) {
+		int sms = 0; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+		ctx->smCount = sms > 0 ? sms : 148;
+	}
+	const size_t full = (size_t) ctx->smCount * TRACE_PERSISTENT_BLOCKS_PER_SM;
+	const size_t want = (n + TRACE_BLOCK - 1) / TRACE_BLOCK;
+	return (unsigned) std::max<size_t>(1, std::min(full, want));
+}
+
+// A zeroed ray counter for the next persistent launch: a ring of counters so that consecutive launches on
+// the stream never share one; each is re-zeroed (async memset) right before use.
+int traceRayCounter(mtsgpu_ctx *ctx, uint32_t **out) {
+	CUDA_TRY(ctx, ctx->dRayCounters.alloc(64 * sizeof(uint32_t)));
+	uint32_t *p = ctx->dRayCounters.as<uint32_t>() + (ctx->rayCounterNext++ & 63);
+	CUDA_TRY(ctx, cudaMemsetAsync(p, 0, sizeof(uint32_t), ctx->stream));
+	*out = p;
+	return MTSGPU_OK;
+}
 
 int launchTrace(mtsgpu_ctx *ctx, const float4 *dRays, size_t n, int mode, void *dOut, uint64_t *dCounters) {
 	REQUIRE(ctx, ctx->built, MTSGPU_ERR_ARG, "trace: call mtsgpu_build_accel first");
 	REQUIRE(ctx, n < (1ull << 31), MTSGPU_ERR_LIMIT, "trace: at most 2^31-1 rays per call");
 	if (n == 0) return MTSGPU_OK;
-	const unsigned blocks = (unsigned) ((n + TRACE_BLOCK - 1) / TRACE_BLOCK);
+	const unsigned blocks = tracePersistentBlocks(ctx, n);
 	unsigned long long *cnt = reinterpret_cast<unsigned long long *>(dCounters);
+	uint32_t *rayCounter = nullptr;
+	{ int rc = traceRayCounter(ctx, &rayCounter); if (rc) return rc; }
+	static const int rb = getenv("MTSGPU_REFETCH_BELOW") ? atoi(getenv("MTSGPU_REFETCH_BELOW")) : TRACE_REFETCH_BELOW;
+	static const int spec = getenv("MTSGPU_SPECULATE") ? atoi(getenv("MTSGPU_SPECULATE")) : 1;
 	if (mode == MTSGPU_TRACE_CLOSEST) {
-		if (cnt) k_trace_closest<true><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (mtsgpu_hit *) dOut, cnt);
-		else k_trace_closest<false><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (mtsgpu_hit *) dOut, nullptr);
+		if (cnt) k_trace_closest<true><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (mtsgpu_hit *) dOut, rayCounter, cnt, rb, spec);
+		else k_trace_closest<false><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (mtsgpu_hit *) dOut, rayCounter, nullptr, rb, spec);
 	} else if (mode == MTSGPU_TRACE_ANY) {
-		if (cnt) k_trace_any<true><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (uint32_t *) dOut, cnt);
-		else k_trace_any<false><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (uint32_t *) dOut, nullptr);
+		if (cnt) k_trace_any<true><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (uint32_t *) dOut, rayCounter, cnt, rb, spec);
+		else k_trace_any<false><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (uint32_t *) dOut, rayCounter, nullptr, rb, spec);
 	} else {
 		return setError(ctx, MTSGPU_ERR_ARG, "trace: unknown mode %d", mode);
 	}

@@ -29,7 +29,7 @@ __device__ __forceinline__ bool clipToScene(const DeviceScene &sc, const RayIn &
 		if (d[i] == 0) {
 			if (o[i] < minVal || o[i] > maxVal) return false;
 		} else {
-			const float rcp = __fdiv_rn(1.0f, d[i]);
+			const float rcp = __frcp_rn(d[i]);                 // correctly rounded, bit-identical to 1.0f / d
 			float t1 = __fmul_rn(__fsub_rn(minVal, o[i]), rcp);
 			float t2 = __fmul_rn(__fsub_rn(maxVal, o[i]), rcp);
 			if (t1 > t2) { const float tmp = t1; t1 = t2; t2 = tmp; }
@@ -61,7 +61,7 @@ __device__ __forceinline__ bool triAccelTest(const float4 &q0, const float4 &q1,
 		default: return false;
 	}
 	const float n_u = q0.y, n_v = q0.z, n_d = q0.w;
-	const float recip = __fdiv_rn(1.0f, __fadd_rn(__fadd_rn(__fmul_rn(d_u, n_u), __fmul_rn(d_v, n_v)), d_k));
+	const float recip = __frcp_rn(__fadd_rn(__fadd_rn(__fmul_rn(d_u, n_u), __fmul_rn(d_v, n_v)), d_k));   // == 1.0f / x, correctly rounded
 	t = __fmul_rn(__fsub_rn(__fsub_rn(__fsub_rn(n_d, __fmul_rn(o_u, n_u)), __fmul_rn(o_v, n_v)), o_k), recip);
 	if (t < mint || t > maxt) return false;
 	const float hu = __fsub_rn(__fadd_rn(o_u, __fmul_rn(t, d_u)), q1.x);
@@ -172,4 +172,175 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 			break;
 		}
 	}
+}
+
+// =====================================================================================================
+// Persistent-warp traversal with per-lane ray refetch.
+//
+// ncu on the one-thread-per-ray kernel (profiles/r01_trace_closest_bvh4_details.csv) showed 4.4 of 32
+// lanes active per issued instruction on incoherent rays: lanes whose ray missed the scene box or finished
+// early idle until the slowest ray of the warp is done. Here a fixed grid of warps pulls rays from a global
+// counter (in chunks of TRACE_CHUNK per warp, handed out lane by lane with ballot + popcount); a lane that
+// finishes its ray gets the next one at the top of the loop, so a warp stays full until the queue is empty.
+// Each loop iteration performs one traversal step (one 4-wide node, or one leaf) per active lane.
+// =====================================================================================================
+#define TRACE_CHUNK 128
+#define TRACE_PERSISTENT_BLOCKS_PER_SM 8
+#define TRACE_FETCH_ATTEMPTS 8
+#define TRACE_REFETCH_BELOW 12      // leave the step loop to refetch when fewer lanes than this are active
+
+struct LaneState {
+	RayIn r;
+	float mint, maxt, idx, idy, idz, oix, oiy, oiz;
+	uint32_t cur, leaf, ray, tri;     // cur: next node/leaf to visit (BVH_EMPTY: none); leaf: postponed leaf
+	float t, u, v;
+	int sp;
+	bool active, found;
+};
+
+// Sink concept:  void closest(uint32_t ray, bool found, float t, float u, float v, uint32_t tri);
+//                void any(uint32_t ray, bool occluded);
+//
+// Step structure ("while-while" with one postponed leaf, after Aila & Laine 2009): all lanes walk inner nodes
+// until every lane holds a leaf (lanes that already hold one keep walking speculatively), then all lanes test
+// their leaf's triangles together. The first version tested a leaf as soon as a lane reached it; ncu's source
+// view showed the TriAccel test — 55 % of all issued instructions — running with 2 of 32 lanes active.
+// The visiting order never changes the closest hit (only which of several bit-identical t values is kept).
+template <bool SHADOW, bool COUNT, class Sink>
+__device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const float4 *__restrict__ rays, uint32_t n,
+		uint32_t *counter, Sink &sink, uint2 *sstack, uint32_t &nodeVisits, uint32_t &triTests, int refetchBelow, bool speculate = true) {
+	uint2 lstack[TRACE_LOCAL_STACK];
+	const uint32_t lane = threadIdx.x & 31u;
+	const uint32_t ltMask = (1u << lane) - 1u;
+	uint32_t poolNext = 0, poolEnd = 0;            // warp-uniform
+	bool exhausted = false;                        // this lane drew an index >= n
+	LaneState s;
+	s.active = false; s.sp = 0; s.cur = BVH_EMPTY; s.leaf = BVH_EMPTY; s.found = false;
+
+#define STACK_PUSH(e) do { if (s.sp < TRACE_SMEM_STACK) SSTACK(s.sp) = (e); else lstack[min(s.sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)] = (e); s.sp++; } while (0)
+	// pop the next entry that can still matter; BVH_EMPTY when the stack is empty
+#define STACK_POP(dst) do { (dst) = BVH_EMPTY; while (s.sp > 0) { --s.sp; \
+		const uint2 e_ = (s.sp < TRACE_SMEM_STACK) ? SSTACK(s.sp) : lstack[min(s.sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)]; \
+		if (!SHADOW && __uint_as_float(e_.y) > s.maxt) continue; (dst) = e_.x; break; } } while (0)
+
+	while (true) {
+		// ---- refetch: lanes without a ray draw the next ray index; a ray that misses the scene box is
+		//      answered on the spot, so try a few times before stepping
+#pragma unroll 1
+		for (int attempt = 0; attempt < TRACE_FETCH_ATTEMPTS; ++attempt) {
+			const bool mine = !s.active && !exhausted;
+			const uint32_t need = __ballot_sync(0xFFFFFFFFu, mine);
+			if (need == 0) break;
+			const uint32_t cnt = __popc(need), rank = __popc(need & ltMask);
+			const uint32_t avail = poolEnd - poolNext;
+			uint32_t idx = 0xFFFFFFFFu;
+			if (mine && rank < avail) idx = poolNext + rank;
+			if (cnt > avail) {
+				uint32_t nb = 0;
+				if (lane == 0) nb = atomicAdd(counter, (uint32_t) TRACE_CHUNK);
+				nb = __shfl_sync(0xFFFFFFFFu, nb, 0);
+				if (mine && rank >= avail) idx = nb + (rank - avail);
+				poolNext = nb + (cnt - avail); poolEnd = nb + TRACE_CHUNK;
+			} else {
+				poolNext += cnt;
+			}
+			if (mine) {
+				if (idx >= n) {
+					exhausted = true;
+				} else {
+					const float4 a = __ldg(rays + 2 * (size_t) idx), b = __ldg(rays + 2 * (size_t) idx + 1);
+					s.r.ox = a.x; s.r.oy = a.y; s.r.oz = a.z; s.r.mint = a.w; s.r.dx = b.x; s.r.dy = b.y; s.r.dz = b.z; s.r.maxt = b.w;
+					s.ray = idx;
+					if (clipToScene<SHADOW>(sc, s.r, s.mint, s.maxt)) {
+						s.idx = safeRcp(s.r.dx); s.idy = safeRcp(s.r.dy); s.idz = safeRcp(s.r.dz);
+						s.oix = s.r.ox * s.idx; s.oiy = s.r.oy * s.idy; s.oiz = s.r.oz * s.idz;
+						s.cur = 0; s.leaf = BVH_EMPTY; s.sp = 0; s.found = false; s.active = true;
+						s.t = INFINITY; s.u = s.v = 0; s.tri = 0xFFFFFFFFu;
+					} else {
+						if (SHADOW) sink.any(idx, false); else sink.closest(idx, false, INFINITY, 0.0f, 0.0f, 0xFFFFFFFFu);
+					}
+				}
+			}
+		}
+		if (!__any_sync(0xFFFFFFFFu, s.active)) {
+			if (__all_sync(0xFFFFFFFFu, exhausted)) break;
+			continue;
+		}
+
+		// ---- traversal; stay here while the warp is reasonably full (or no rays are left to fetch)
+		while (true) {
+			// (A) inner nodes, until every lane holds a leaf or has run out of nodes
+			while (true) {
+				const bool inner = s.active && !(s.cur & BVH_LEAF) && (speculate || s.leaf == BVH_EMPTY);      // BVH_EMPTY has the leaf bit set
+				if (inner) {
+					if (COUNT) nodeVisits++;
+					const float4 *np = sc.nodes + (size_t) s.cur * 8;
+					const float4 lox = __ldg(np + 0), loy = __ldg(np + 1), loz = __ldg(np + 2);
+					const float4 hix = __ldg(np + 3), hiy = __ldg(np + 4), hiz = __ldg(np + 5);
+					const uint4 child = __ldg(reinterpret_cast<const uint4 *>(np + 6));
+					float tn[4]; uint32_t cw[4] = { child.x, child.y, child.z, child.w };
+					const float lx[4] = { lox.x, lox.y, lox.z, lox.w }, ly[4] = { loy.x, loy.y, loy.z, loy.w }, lz[4] = { loz.x, loz.y, loz.z, loz.w };
+					const float hx[4] = { hix.x, hix.y, hix.z, hix.w }, hy[4] = { hiy.x, hiy.y, hiy.z, hiy.w }, hz[4] = { hiz.x, hiz.y, hiz.z, hiz.w };
+#pragma unroll
+					for (int i = 0; i < 4; ++i) {
+						const float t0x = fmaf(lx[i], s.idx, -s.oix), t1x = fmaf(hx[i], s.idx, -s.oix);
+						const float t0y = fmaf(ly[i], s.idy, -s.oiy), t1y = fmaf(hy[i], s.idy, -s.oiy);
+						const float t0z = fmaf(lz[i], s.idz, -s.oiz), t1z = fmaf(hz[i], s.idz, -s.oiz);
+						const float tnear = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), s.mint));
+						const float tfar = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), s.maxt));
+						tn[i] = (cw[i] != BVH_EMPTY && tnear <= tfar) ? tnear : INFINITY;
+					}
+					if (!SHADOW) {
+						// ascending by entry distance: 5-comparator network, then push far-to-near
+#define CSWAP(a, b) if (tn[b] < tn[a]) { float tt = tn[a]; tn[a] = tn[b]; tn[b] = tt; uint32_t cc = cw[a]; cw[a] = cw[b]; cw[b] = cc; }
+						CSWAP(0, 1) CSWAP(2, 3) CSWAP(0, 2) CSWAP(1, 3) CSWAP(1, 2)
+#undef CSWAP
+					}
+#pragma unroll
+					for (int i = 3; i >= 1; --i)
+						if (tn[i] != INFINITY) STACK_PUSH(make_uint2(cw[i], __float_as_uint(tn[i])));
+					if (tn[0] != INFINITY) s.cur = cw[0]; else STACK_POP(s.cur);
+					// reached a leaf: park it (one slot) and keep walking
+					if ((s.cur & BVH_LEAF) && s.cur != BVH_EMPTY && s.leaf == BVH_EMPTY) { s.leaf = s.cur; STACK_POP(s.cur); }
+				}
+				const bool canWalk = s.active && !(s.cur & BVH_LEAF);
+				if (!__any_sync(0xFFFFFFFFu, canWalk && s.leaf == BVH_EMPTY)) break;   // nobody without a leaf can go on
+			}
+			// (B) leaves: every lane that holds one tests its triangles; a second leaf waiting in `cur` moves up
+			while (true) {
+				const bool has = s.active && s.leaf != BVH_EMPTY;
+				if (!__any_sync(0xFFFFFFFFu, has)) break;
+				if (has) {
+					const uint32_t first = s.leaf & 0x0FFFFFFFu, count = ((s.leaf >> 28) & 7u) + 1u;
+					s.leaf = BVH_EMPTY;
+					for (uint32_t i = 0; i < count; ++i) {
+						const float4 *tp = sc.triAccel + (size_t) (first + i) * 3;
+						const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+						const uint32_t kraw = __float_as_uint(q0.x);
+						if (SHADOW && (kraw & TRI_NONOCCLUDER)) continue;
+						if (COUNT) triTests++;
+						float u, v, t;
+						if (triAccelTest(q0, q1, q2, kraw & TRI_K_MASK, s.r, s.mint, s.maxt, u, v, t)) {
+							s.found = true;
+							if (SHADOW) break;
+							s.maxt = t;                    // sahkdtree3.h:278-283: a later equal t replaces an earlier one
+							s.t = t; s.u = u; s.v = v; s.tri = first + i;
+						}
+					}
+					if (SHADOW && s.found) { s.sp = 0; s.cur = BVH_EMPTY; }          // any-hit: done
+					else if ((s.cur & BVH_LEAF) && s.cur != BVH_EMPTY) { s.leaf = s.cur; STACK_POP(s.cur); }
+				}
+			}
+			// (C) rays with nothing left to visit are finished
+			if (s.active && s.cur == BVH_EMPTY) {
+				s.active = false;
+				if (SHADOW) sink.any(s.ray, s.found); else sink.closest(s.ray, s.found, s.t, s.u, s.v, s.tri);
+			}
+			const uint32_t act = __ballot_sync(0xFFFFFFFFu, s.active);
+			if (act == 0) break;
+			if (__popc(act) < refetchBelow && !__all_sync(0xFFFFFFFFu, exhausted || s.active)) break;
+		}
+	}
+#undef STACK_PUSH
+#undef STACK_POP
 }
