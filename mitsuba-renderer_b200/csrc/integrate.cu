@@ -124,10 +124,11 @@ k_generate(const CameraDev cam, const FilmDev film, const BatchDesc b, WfArrays 
 	}
 }
 
-// Wavefront traversal kernels: one thread per queue entry. Path-tracing queues are largely coherent
-// (camera rays, glossy bounces off neighbouring pixels, shadow rays towards a handful of emitters), and for
-// those the plain lock-step kernel measured faster than the persistent-warp variant the ray-query API uses
-// (C4, 10M triangles: 101 ms vs 120 ms per 16 spp; see profiles/ and DESIGN.md §5).
+// Wavefront traversal kernels, one thread per queue entry (lock-step). Measured inside renders at 64 spp
+// (B200): closest-hit queues run faster through the persistent-warp variant below (C3 33.2 -> 25.6 ms,
+// C4 177.8 -> 167.1 ms), shadow queues — coherent rays towards a handful of emitters — do not on the
+// 10M-triangle scene (61.0 -> 71.3 ms), so shadow rays keep this kernel. MTSGPU_WF_PERSIST_{CLOSEST,SHADOW}
+// override the choice for experiments.
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_closest_wf(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint4 *__restrict__ hits) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
@@ -162,6 +163,41 @@ k_shadow_wf(const DeviceScene sc, const float4 *__restrict__ rays, const float4 
 		l.x += p.x; l.y += p.y; l.z += p.z;
 		li[slot] = l;
 	}
+}
+
+// Persistent-warp variants (trace.cuh) of the two wavefront traversal kernels.
+struct WfHitSink {
+	uint4 *hits;
+	__device__ __forceinline__ void closest(uint32_t ray, bool found, float t, float u, float v, uint32_t tri) {
+		hits[ray] = make_uint4(__float_as_uint(found ? t : INFINITY), __float_as_uint(u), __float_as_uint(v), found ? tri : 0xFFFFFFFFu);
+	}
+	__device__ __forceinline__ void any(uint32_t, bool) { }
+};
+struct WfShadowSink {
+	const float4 *payload; float4 *li;
+	__device__ __forceinline__ void closest(uint32_t, bool, float, float, float, uint32_t) { }
+	__device__ __forceinline__ void any(uint32_t ray, bool occluded) {
+		if (occluded) return;
+		const float4 p = __ldg(payload + ray);
+		const uint32_t slot = __float_as_uint(p.w);
+		float4 l = li[slot];
+		l.x += p.x; l.y += p.y; l.z += p.z;
+		li[slot] = l;
+	}
+};
+__global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
+k_closest_wfp(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint4 *__restrict__ hits, uint32_t *rayCounter) {
+	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
+	uint32_t c0 = 0, c1 = 0;
+	WfHitSink sink = { hits };
+	tracePersistent<false, false>(sc, rays, n, rayCounter, sink, sstack, c0, c1, TRACE_REFETCH_BELOW);
+}
+__global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
+k_shadow_wfp(const DeviceScene sc, const float4 *__restrict__ rays, const float4 *__restrict__ payload, uint32_t n, float4 *li, uint32_t *rayCounter) {
+	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
+	uint32_t c0 = 0, c1 = 0;
+	WfShadowSink sink = { payload, li };
+	tracePersistent<true, false>(sc, rays, n, rayCounter, sink, sstack, c0, c1, TRACE_REFETCH_BELOW);
 }
 
 __device__ __forceinline__ float miWeight(float pdfA, float pdfB) {     // path.cpp:218-222 (power heuristic)
@@ -427,6 +463,26 @@ inline unsigned blocksFor(size_t n, unsigned bs) { return (unsigned) ((n + bs - 
 
 } // namespace
 
+// Launch helpers: pick the traversal kernel variant per queue.
+static int launchClosestWf(mtsgpu_ctx *ctx, const float4 *rays, uint32_t n, uint4 *hits, bool persistent) {
+	if (persistent) {
+		uint32_t *rc = nullptr; int e = traceRayCounter(ctx, &rc); if (e) return e;
+		k_closest_wfp<<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, rc);
+	} else {
+		k_closest_wf<<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits);
+	}
+	return MTSGPU_OK;
+}
+static int launchShadowWf(mtsgpu_ctx *ctx, const float4 *rays, const float4 *payload, uint32_t n, float4 *li, bool persistent) {
+	if (persistent) {
+		uint32_t *rc = nullptr; int e = traceRayCounter(ctx, &rc); if (e) return e;
+		k_shadow_wfp<<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li, rc);
+	} else {
+		k_shadow_wf<<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li);
+	}
+	return MTSGPU_OK;
+}
+
 static int ensureWavefront(mtsgpu_ctx *ctx, uint32_t capacity) {
 	if (ctx->pathCapacity >= capacity) return MTSGPU_OK;
 	const size_t c = capacity;
@@ -454,6 +510,8 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 	if (P->mode == MTSGPU_MODE_DIRECT)
 		REQUIRE(ctx, P->luminaireSamples >= 0 && P->bsdfSamples >= 0 && P->luminaireSamples + P->bsdfSamples > 0, MTSGPU_ERR_ARG, "render: luminaireSamples + bsdfSamples must be > 0");
 	cudaStream_t st = ctx->stream;
+	static const bool persistClosest = getenv("MTSGPU_WF_PERSIST_CLOSEST") ? atoi(getenv("MTSGPU_WF_PERSIST_CLOSEST")) != 0 : true;
+	static const bool persistShadow = getenv("MTSGPU_WF_PERSIST_SHADOW") ? atoi(getenv("MTSGPU_WF_PERSIST_SHADOW")) != 0 : false;
 	const FilmDev film = ctx->film;
 	const size_t filmFloats = (size_t) film.cropW * film.cropH * 5;
 	{
@@ -478,12 +536,18 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 		uint32_t sampleChunk = std::min<uint32_t>(spp, maxSlots / TILE_PIX);
 		uint32_t tilesPerBatch = std::max<uint32_t>(1u, std::min<uint32_t>(nTiles, maxSlots / (TILE_PIX * sampleChunk)));
 		const uint32_t capacity = tilesPerBatch * sampleChunk * TILE_PIX;
-		{ int rc = ensureWavefront(ctx, capacity); if (rc) return rc; }
+		{
+			// size the queues for the whole job (sppTotal), so that a short warm-up call and the full render
+			// share one allocation
+			const uint64_t wholeJob = (uint64_t) nTiles * TILE_PIX * std::max<uint32_t>(P->sppTotal, spp);
+			const uint32_t allocSlots = (uint32_t) std::min<uint64_t>(maxSlots, std::max<uint64_t>(capacity, wholeJob));
+			int rc = ensureWavefront(ctx, allocSlots); if (rc) return rc;
+		}
 		DevBuf &dPrimSlot = ctx->dPrimSlot, &dPrimRay = ctx->dPrimRay, &dPrimHit = ctx->dPrimHit;
 		if (P->mode == MTSGPU_MODE_DIRECT) {
-			CUDA_TRY(ctx, dPrimSlot.alloc((size_t) capacity * 4));
-			CUDA_TRY(ctx, dPrimRay.alloc((size_t) capacity * 32));
-			CUDA_TRY(ctx, dPrimHit.alloc((size_t) capacity * 16));
+			CUDA_TRY(ctx, dPrimSlot.alloc((size_t) ctx->pathCapacity * 4));
+			CUDA_TRY(ctx, dPrimRay.alloc((size_t) ctx->pathCapacity * 32));
+			CUDA_TRY(ctx, dPrimHit.alloc((size_t) ctx->pathCapacity * 16));
 		}
 		WfArrays wf;
 		char *ps = ctx->dPathState.as<char>();
@@ -531,7 +595,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 						wf.slotCur = slotBuf[cur]; wf.rayCur = rayBuf[cur];
 						wf.slotNext = slotBuf[cur ^ 1]; wf.rayNext = rayBuf[cur ^ 1];
 						cudaEventRecord(evA, st);
-						k_closest_wf<<<blocksFor(nRays, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(ctx->scene, wf.rayCur, nRays, wf.hit);
+						if (launchClosestWf(ctx, wf.rayCur, nRays, wf.hit, persistClosest)) return fail(MTSGPU_ERR_CUDA);
 						cudaEventRecord(evB, st);
 						S.normalRays += nRays;
 						CUDA_TRY(ctx, cudaMemsetAsync(wf.counters, 0, 8, st));
@@ -543,7 +607,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 						const uint32_t nShadow = hCounts[1];
 						if (nShadow > 0) {
 							cudaEventRecord(evA, st);
-							k_shadow_wf<<<blocksFor(nShadow, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(ctx->scene, wf.shadowRay, wf.shadowPayload, nShadow, wf.li);
+							if (launchShadowWf(ctx, wf.shadowRay, wf.shadowPayload, nShadow, wf.li, persistShadow)) return fail(MTSGPU_ERR_CUDA);
 							cudaEventRecord(evB, st);
 							CUDA_TRY(ctx, cudaEventSynchronize(evB));
 							{ float ms = 0; cudaEventElapsedTime(&ms, evA, evB); msShadow += ms; }
@@ -556,7 +620,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 					// primary hit once, kept in the *Prim buffers; then `rounds` passes of (NEE, BSDF ray)
 					wf.slotCur = slotBuf[cur]; wf.rayCur = rayBuf[cur];
 					cudaEventRecord(evA, st);
-						k_closest_wf<<<blocksFor(nRays, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(ctx->scene, wf.rayCur, nRays, wf.hitPrim);
+						if (launchClosestWf(ctx, wf.rayCur, nRays, wf.hitPrim, persistClosest)) return fail(MTSGPU_ERR_CUDA);
 					cudaEventRecord(evB, st);
 					CUDA_TRY(ctx, cudaMemcpyAsync(wf.slotPrim, wf.slotCur, (size_t) nRays * 4, cudaMemcpyDeviceToDevice, st));
 					CUDA_TRY(ctx, cudaMemcpyAsync(wf.rayPrim, wf.rayCur, (size_t) nRays * 32, cudaMemcpyDeviceToDevice, st));
@@ -575,7 +639,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 						const uint32_t nSec = hCounts[0], nShadow = hCounts[1];
 						if (nShadow > 0) {
 							cudaEventRecord(evA, st);
-							k_shadow_wf<<<blocksFor(nShadow, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(ctx->scene, wf.shadowRay, wf.shadowPayload, nShadow, wf.li);
+							if (launchShadowWf(ctx, wf.shadowRay, wf.shadowPayload, nShadow, wf.li, persistShadow)) return fail(MTSGPU_ERR_CUDA);
 							cudaEventRecord(evB, st);
 							CUDA_TRY(ctx, cudaEventSynchronize(evB));
 							{ float ms = 0; cudaEventElapsedTime(&ms, evA, evB); msShadow += ms; }
@@ -584,7 +648,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 						if (nSec > 0) {
 							wf.slotCur = slotBuf[cur ^ 1]; wf.rayCur = rayBuf[cur ^ 1];
 							cudaEventRecord(evA, st);
-						k_closest_wf<<<blocksFor(nSec, TRACE_BLOCK), TRACE_BLOCK, 0, st>>>(ctx->scene, wf.rayCur, nSec, wf.hit);
+						if (launchClosestWf(ctx, wf.rayCur, nSec, wf.hit, persistClosest)) return fail(MTSGPU_ERR_CUDA);
 							cudaEventRecord(evB, st);
 							k_shade<2><<<blocksFor(nSec, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nSec, (uint32_t) r);
 							CUDA_TRY(ctx, cudaStreamSynchronize(st));
