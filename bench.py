@@ -182,8 +182,15 @@ def run_ours(args, rank, local_rank, world):
     bytes_per_ray = queue_bytes + nodes_per_ray * 128 + tris_per_ray * 48
     peak, peak_src = measured_peaks()
     achieved = n * bytes_per_ray / (kernel_ms[dom] * 1e-3) * 1e-9
-    roofline = {"bound": "hbm", "kernel": "k_trace_any" if mode else "k_trace_closest", "batch": label, "achieved": achieved, "peak": peak,
-                "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    traffic, traffic_src = None, None
+    tpath = os.path.join(ROOT, "profiles", "r01_kernel_traffic.json")
+    kname = "k_trace_any" if mode else "k_trace_closest"
+    if os.path.exists(tpath):
+        rec = json.load(open(tpath)).get(kname)
+        if rec and rec.get("batch") == label:       # per launch, scaled to this run's ray count
+            traffic, traffic_src = rec["traffic"] * n / rec["rays"], rec["source"]
+    roofline = {"bound": "hbm", "kernel": kname, "batch": label, "achieved": achieved, "peak": peak,
+                "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                 "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray,
                 "kernel_ms": float(kernel_ms[dom]), "mrays_per_s": n / kernel_ms[dom] * 1e-3,
                 "per_batch_ms": {d[0]: float(ms) for d, ms in zip(dev, kernel_ms)},
