@@ -50,8 +50,14 @@ enum mtsgpu_bsdf_type {
 	                               p[6] intIOR, p[7] extIOR */
 };
 
+/* OR-ed into mtsgpu_material.type: the BRDF is wrapped in the `twosided` adapter (src/bsdfs/twosided.cpp:36-143),
+ * i.e. queries with wi.z < 0 are mirrored to the upper side. Not valid for dielectric (the adapter rejects
+ * BSDFs with transmission, twosided.cpp:72-74). */
+#define MTSGPU_BSDF_TWOSIDED  0x100u
+#define MTSGPU_BSDF_TYPE_MASK 0x0FFu
+
 typedef struct mtsgpu_material {
-	uint32_t type;   /* mtsgpu_bsdf_type */
+	uint32_t type;   /* mtsgpu_bsdf_type, optionally | MTSGPU_BSDF_TWOSIDED */
 	float p[16];
 } mtsgpu_material;
 

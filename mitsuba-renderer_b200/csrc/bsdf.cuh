@@ -104,9 +104,9 @@ __device__ inline V3 reflectAbout(V3 wi, V3 n) {                             // 
 __device__ inline V3 mp3(const MaterialDev &m, int o) { return v3(m.p[o], m.p[o + 1], m.p[o + 2]); }
 
 // ---- f ---------------------------------------------------------------------------------------------
-__device__ inline V3 bsdfF(const MaterialDev &m, V3 wi, V3 wo) {
+__device__ inline V3 bsdfF_base(const MaterialDev &m, V3 wi, V3 wo) {
 	const V3 zero = v3(0, 0, 0);
-	switch (m.type) {
+	switch (m.type & MTSGPU_BSDF_TYPE_MASK) {
 		case MTSGPU_BSDF_LAMBERTIAN:
 			if (wi.z <= 0 || wo.z <= 0) return zero;
 			return mp3(m, 0) * MTS_INV_PI;
@@ -143,8 +143,8 @@ __device__ inline float pdfSpecBeckmann(V3 wi, V3 wo, float alphaB) {
 	return beckmannD(Hr, alphaB) * Hr.z / (4.0f * fabsf(dot(wo, Hr)));
 }
 
-__device__ inline float bsdfPdf(const MaterialDev &m, V3 wi, V3 wo) {
-	switch (m.type) {
+__device__ inline float bsdfPdf_base(const MaterialDev &m, V3 wi, V3 wo) {
+	switch (m.type & MTSGPU_BSDF_TYPE_MASK) {
 		case MTSGPU_BSDF_LAMBERTIAN:
 			if (wi.z <= 0 || wo.z <= 0) return 0.0f;
 			return wo.z * MTS_INV_PI;
@@ -191,9 +191,9 @@ __device__ inline void dielectricSetup(const MaterialDev &m, V3 wi, float &Fr, f
 }
 
 // ---- 2-argument sample: returns f / pdf (NOT multiplied by the cosine); zero => no sample ----------
-__device__ inline V3 bsdfSample2(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, uint32_t &type) {
+__device__ inline V3 bsdfSample2_base(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, uint32_t &type) {
 	const V3 zero = v3(0, 0, 0);
-	switch (m.type) {
+	switch (m.type & MTSGPU_BSDF_TYPE_MASK) {
 		case MTSGPU_BSDF_LAMBERTIAN:
 			if (wi.z <= 0) return zero;
 			wo = squareToHemispherePSA(sx, sy);
@@ -219,14 +219,14 @@ __device__ inline V3 bsdfSample2(const MaterialDev &m, V3 wi, float sx, float sy
 				wo = reflectAbout(wi, mm);
 				type = BSDF_GLOSSY_REFLECTION;
 				if (wo.z <= 0) return zero;
-				const float pdfValue = bsdfPdf(m, wi, wo);
+				const float pdfValue = bsdfPdf_base(m, wi, wo);
 				if (pdfValue == 0) return zero;
-				return bsdfF(m, wi, wo) * (1.0f / pdfValue);
+				return bsdfF_base(m, wi, wo) * (1.0f / pdfValue);
 			} else {
 				sx = (sx - specularSamplingWeight) / diffuseSamplingWeight;
 				wo = squareToHemispherePSA(sx, sy);
 				type = BSDF_DIFFUSE_REFLECTION;
-				return bsdfF(m, wi, wo) * (1.0f / bsdfPdf(m, wi, wo));
+				return bsdfF_base(m, wi, wo) * (1.0f / bsdfPdf_base(m, wi, wo));
 			}
 		}
 		case MTSGPU_BSDF_ROUGHMETAL: {
@@ -235,7 +235,7 @@ __device__ inline V3 bsdfSample2(const MaterialDev &m, V3 wi, float sx, float sy
 			wo = reflectAbout(wi, mm);
 			type = BSDF_GLOSSY_REFLECTION;
 			if (wo.z <= 0) return zero;
-			return bsdfF(m, wi, wo) * (1.0f / bsdfPdf(m, wi, wo));
+			return bsdfF_base(m, wi, wo) * (1.0f / bsdfPdf_base(m, wi, wo));
 		}
 		case MTSGPU_BSDF_DIELECTRIC: {
 			float Fr, eta, cosThetaT;
@@ -256,9 +256,9 @@ __device__ inline V3 bsdfSample2(const MaterialDev &m, V3 wi, float sx, float sy
 }
 
 // ---- 3-argument sample: returns f (not divided by pdf) and the pdf; zero => no sample ---------------
-__device__ inline V3 bsdfSample3(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, float &pdf, uint32_t &type) {
+__device__ inline V3 bsdfSample3_base(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, float &pdf, uint32_t &type) {
 	const V3 zero = v3(0, 0, 0);
-	switch (m.type) {
+	switch (m.type & MTSGPU_BSDF_TYPE_MASK) {
 		case MTSGPU_BSDF_LAMBERTIAN:
 			if (wi.z <= 0) return zero;
 			wo = squareToHemispherePSA(sx, sy);
@@ -287,10 +287,34 @@ __device__ inline V3 bsdfSample3(const MaterialDev &m, V3 wi, float sx, float sy
 		}
 		default: {
 			// BSDF::sample(bRec, pdf, sample) fallback (bsdf.cpp:37-48): 2-arg sample, then pdf() and f()
-			const V3 s = bsdfSample2(m, wi, sx, sy, wo, type);
+			const V3 s = bsdfSample2_base(m, wi, sx, sy, wo, type);
 			if (isZero(s)) { pdf = 0.0f; return zero; }
-			pdf = bsdfPdf(m, wi, wo);
-			return bsdfF(m, wi, wo);
+			pdf = bsdfPdf_base(m, wi, wo);
+			return bsdfF_base(m, wi, wo);
 		}
 	}
+}
+
+// ---- twosided adapter (src/bsdfs/twosided.cpp:81-131): a BRDF seen from below behaves as from above --------
+__device__ inline V3 bsdfF(const MaterialDev &m, V3 wi, V3 wo) {
+	if ((m.type & MTSGPU_BSDF_TWOSIDED) && wi.z < 0) { wi.z *= -1; wo.z *= -1; }
+	return bsdfF_base(m, wi, wo);
+}
+__device__ inline float bsdfPdf(const MaterialDev &m, V3 wi, V3 wo) {
+	if ((m.type & MTSGPU_BSDF_TWOSIDED) && wi.z < 0) { wi.z *= -1; wo.z *= -1; }
+	return bsdfPdf_base(m, wi, wo);
+}
+__device__ inline V3 bsdfSample2(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, uint32_t &type) {
+	const bool flipped = (m.type & MTSGPU_BSDF_TWOSIDED) && wi.z < 0;
+	if (flipped) wi.z *= -1;
+	const V3 result = bsdfSample2_base(m, wi, sx, sy, wo, type);
+	if (flipped && !isZero(result)) wo.z *= -1;
+	return result;
+}
+__device__ inline V3 bsdfSample3(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, float &pdf, uint32_t &type) {
+	const bool flipped = (m.type & MTSGPU_BSDF_TWOSIDED) && wi.z < 0;
+	if (flipped) wi.z *= -1;
+	const V3 result = bsdfSample3_base(m, wi, sx, sy, wo, pdf, type);
+	if (flipped && !isZero(result) && pdf != 0) wo.z *= -1;
+	return result;
 }

@@ -339,7 +339,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 				if (doLum) {
 					float sx, sy; smp.get2D(dimL, sx, sy);
 					// delta-only BSDFs have f = 0: the reference still traces the shadow ray, the result is unused
-					if (mat.type != MTSGPU_BSDF_MIRROR && mat.type != MTSGPU_BSDF_DIELECTRIC)
+					if ((mat.type & MTSGPU_BSDF_TYPE_MASK) != MTSGPU_BSDF_MIRROR && (mat.type & MTSGPU_BSDF_TYPE_MASK) != MTSGPU_BSDF_DIELECTRIC)
 						emitShadow = nextEvent(sc, ig, its, mat, rayD, MODE == 0 ? thr : v3(1, 1, 1), sx, sy,
 							fracLum, fracBsdf, weightLum, sr0, sr1, contrib);
 				}

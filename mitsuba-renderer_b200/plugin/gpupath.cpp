@@ -106,17 +106,21 @@ private:
 
 	static void put(float *dst, const Spectrum &v) { Float r, g, b; v.toLinearRGB(r, g, b); dst[0] = r; dst[1] = g; dst[2] = b; }
 
-	static mtsgpu_material decodeBSDF(const BSDF *bsdf) {
+	/* `s` is positioned at the serialised form of an object of class `cls` */
+	static mtsgpu_material decodePayload(const std::string &cls, Stream *s) {
 		mtsgpu_material m; memset(&m, 0, sizeof(m));
-		ref<MemoryStream> s = new MemoryStream();
-		ref<InstanceManager> mgr = new InstanceManager();
-		bsdf->serialize(s, mgr);
-		s->setPos(0);
 		if (s->readUInt() != 0)            /* BSDF::setParent is a no-op (bsdf.cpp:55-57) => parent id 0 */
 			SLog(EError, "gpupath: unexpected BSDF parent");
 		s->readString();                   /* BSDF::serialize: m_name (bsdf.cpp:50-53) */
-		const std::string cls = bsdf->getClass()->getName();
-		if (cls == "Lambertian") {                    /* lambertian.cpp:137-141 */
+		if (cls == "TwoSidedBRDF") {                  /* twosided.cpp:55-59: the nested BRDF instance */
+			if (s->readUInt() == 0)
+				SLog(EError, "gpupath: TwoSidedBRDF without a nested BRDF");
+			const std::string nested = s->readString();
+			m = decodePayload(nested, s);
+			if ((m.type & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_DIELECTRIC || (m.type & MTSGPU_BSDF_TWOSIDED))
+				SLog(EError, "gpupath: TwoSidedBRDF around \"%s\" is not supported", nested.c_str());
+			m.type |= MTSGPU_BSDF_TWOSIDED;
+		} else if (cls == "Lambertian") {             /* lambertian.cpp:137-141 */
 			m.type = MTSGPU_BSDF_LAMBERTIAN;
 			put(m.p, readConstantTexture(s));
 		} else if (cls == "Microfacet") {             /* microfacet.cpp:283-293 */
@@ -138,9 +142,17 @@ private:
 			put(m.p, readConstantTexture(s)); put(m.p + 3, readConstantTexture(s));
 		} else {
 			SLog(EError, "gpupath: BSDF class \"%s\" is outside the supported hot path "
-				"(lambertian, microfacet, mirror, roughmetal, dielectric)", cls.c_str());
+				"(lambertian, microfacet, mirror, roughmetal, dielectric, twosided)", cls.c_str());
 		}
 		return m;
+	}
+
+	static mtsgpu_material decodeBSDF(const BSDF *bsdf) {
+		ref<MemoryStream> s = new MemoryStream();
+		ref<InstanceManager> mgr = new InstanceManager();
+		bsdf->serialize(s, mgr);
+		s->setPos(0);
+		return decodePayload(bsdf->getClass()->getName(), s);
 	}
 
 	bool renderImpl(mtsgpu_ctx *ctx, Scene *scene, RenderQueue *queue, const RenderJob *job) {

@@ -20,6 +20,7 @@ from typing import List, Optional
 import numpy as np
 
 MAT_LAMBERTIAN, MAT_MICROFACET, MAT_MIRROR, MAT_ROUGHMETAL, MAT_DIELECTRIC = range(5)
+BSDF_TWOSIDED = 0x100     # OR-ed into Material.type: wrapped in the `twosided` adapter (src/bsdfs/twosided.cpp)
 MODE_PATH, MODE_DIRECT = 0, 1
 FILTER_BOX, FILTER_GAUSSIAN = 0, 1
 
@@ -61,6 +62,12 @@ def roughmetal(specular=(1.0, 1.0, 1.0), alphaB=0.1, ior=(0.37, 0.37, 0.37), k=(
 def dielectric(intIOR=1.5046, extIOR=1.0, reflectance=(1.0, 1.0, 1.0), transmittance=(1.0, 1.0, 1.0)):
     """src/bsdfs/dielectric.cpp:49-60"""
     return _mat(MAT_DIELECTRIC, list(reflectance) + list(transmittance) + [intIOR, extIOR])
+
+
+def twosided(material: Material) -> Material:
+    """src/bsdfs/twosided.cpp:36-143 around a BRDF (not valid for dielectric)."""
+    assert (material.type & 0xFF) != MAT_DIELECTRIC
+    return Material(material.type | BSDF_TWOSIDED, material.p.copy())
 
 
 @dataclass

@@ -104,7 +104,18 @@ static ConfigurableObject *create(const Class *cls, const Properties &props) {
 
 static Spectrum rgb(const float *v) { Spectrum s; s.fromLinearRGB(v[0], v[1], v[2]); return s; }
 
-static ref<BSDF> makeBSDF(const sio::Material &m) {
+static ref<BSDF> makeBSDF(const sio::Material &mIn) {
+	if (mIn.type & 0x100u) {
+		/* <bsdf type="twosided"> <bsdf type="..."/> </bsdf>  (twosided.cpp:30-35) */
+		sio::Material inner = mIn; inner.type &= 0xFFu;
+		ref<BSDF> nested = makeBSDF(inner);
+		ref<BSDF> outer = static_cast<BSDF *>(create(MTS_CLASS(BSDF), Properties("twosided")));
+		outer->addChild("", nested);
+		nested->setParent(outer);
+		outer->configure();
+		return outer;
+	}
+	const sio::Material &m = mIn;
 	Properties p;
 	switch (m.type) {
 		case sio::MAT_LAMBERTIAN:

@@ -161,8 +161,12 @@ def _normalize(v):
 
 def bsdf_f_pdf(mtype, p, wi, wo):
     """f(wi,wo) [3] and pdf(wi,wo) of one material (type + 16-float block, include/mtsgpu.h layout)."""
-    wi, wo, p = np.asarray(wi, F), np.asarray(wo, F), np.asarray(p, F)
+    wi, wo, p = np.asarray(wi, F).copy(), np.asarray(wo, F).copy(), np.asarray(p, F)
     zero = np.zeros(3, F)
+    if mtype & 0x100:   # twosided adapter (twosided.cpp:81-100)
+        if wi[2] < 0:
+            wi[2] *= -1; wo[2] *= -1
+        mtype &= 0xFF
     if mtype == 0:      # lambertian.cpp:95-108
         if wi[2] <= 0 or wo[2] <= 0:
             return zero, F(0)

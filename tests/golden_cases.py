@@ -47,7 +47,10 @@ def bsdf_scene():
                    scenefile.mirror((0.8, 0.7, 0.9)),
                    scenefile.roughmetal((1, 1, 1), 0.1),                                         # data/tests/test_bsdf.xml
                    scenefile.roughmetal((0.9, 0.8, 0.7), 0.4, (0.2, 0.92, 1.1), (3.9, 2.45, 2.14)),
-                   scenefile.dielectric(), scenefile.dielectric(1.33, 1.0, (0.9, 1, 1), (1, 0.8, 0.9))]
+                   scenefile.dielectric(), scenefile.dielectric(1.33, 1.0, (0.9, 1, 1), (1, 0.8, 0.9)),
+                   scenefile.twosided(scenefile.lambertian((0.2, 0.6, 0.4))),                     # twosided.cpp adapter
+                   scenefile.twosided(scenefile.roughmetal((1, 1, 1), 0.2)),
+                   scenefile.twosided(scenefile.microfacet((0.3, 0.3, 0.3), (1, 1, 1), 1.0, 1.0, 0.15))]
     for sh in s.shapes:
         sh.material = 0
     return s
