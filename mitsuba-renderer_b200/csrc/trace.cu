@@ -41,22 +41,22 @@ __device__ __forceinline__ void flushCounters(uint32_t nodeVisits, uint32_t triT
 template <bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
 k_trace_closest(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, mtsgpu_hit *__restrict__ out,
-		uint32_t *rayCounter, unsigned long long *counters, int refetchBelow, int speculate) {
+		uint32_t *rayCounter, unsigned long long *counters, int refetchBelow, int speculate, int leafThreshold) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
 	uint32_t nodeVisits = 0, triTests = 0;
 	HitSink sink = { sc, out };
-	tracePersistent<false, COUNT>(sc, rays, n, rayCounter, sink, sstack, nodeVisits, triTests, refetchBelow, speculate != 0);
+	tracePersistent<false, COUNT>(sc, rays, n, rayCounter, sink, sstack, nodeVisits, triTests, refetchBelow, speculate != 0, leafThreshold);
 	if (COUNT) flushCounters(nodeVisits, triTests, counters);
 }
 
 template <bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
 k_trace_any(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint32_t *__restrict__ out,
-		uint32_t *rayCounter, unsigned long long *counters, int refetchBelow, int speculate) {
+		uint32_t *rayCounter, unsigned long long *counters, int refetchBelow, int speculate, int leafThreshold) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
 	uint32_t nodeVisits = 0, triTests = 0;
 	OccludedSink sink = { out };
-	tracePersistent<true, COUNT>(sc, rays, n, rayCounter, sink, sstack, nodeVisits, triTests, refetchBelow, speculate != 0);
+	tracePersistent<true, COUNT>(sc, rays, n, rayCounter, sink, sstack, nodeVisits, triTests, refetchBelow, speculate != 0, leafThreshold);
 	if (COUNT) flushCounters(nodeVisits, triTests, counters);
 }
 
@@ -92,13 +92,14 @@ int launchTrace(mtsgpu_ctx *ctx, const float4 *dRays, size_t n, int mode, void *
 	uint32_t *rayCounter = nullptr;
 	{ int rc = traceRayCounter(ctx, &rayCounter); if (rc) return rc; }
 	static const int rb = getenv("MTSGPU_REFETCH_BELOW") ? atoi(getenv("MTSGPU_REFETCH_BELOW")) : TRACE_REFETCH_BELOW;
+	static const int lt = getenv("MTSGPU_LEAF_THRESHOLD") ? atoi(getenv("MTSGPU_LEAF_THRESHOLD")) : 16;
 	static const int spec = getenv("MTSGPU_SPECULATE") ? atoi(getenv("MTSGPU_SPECULATE")) : 1;
 	if (mode == MTSGPU_TRACE_CLOSEST) {
-		if (cnt) k_trace_closest<true><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (mtsgpu_hit *) dOut, rayCounter, cnt, rb, spec);
-		else k_trace_closest<false><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (mtsgpu_hit *) dOut, rayCounter, nullptr, rb, spec);
+		if (cnt) k_trace_closest<true><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (mtsgpu_hit *) dOut, rayCounter, cnt, rb, spec, lt);
+		else k_trace_closest<false><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (mtsgpu_hit *) dOut, rayCounter, nullptr, rb, spec, lt);
 	} else if (mode == MTSGPU_TRACE_ANY) {
-		if (cnt) k_trace_any<true><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (uint32_t *) dOut, rayCounter, cnt, rb, spec);
-		else k_trace_any<false><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (uint32_t *) dOut, rayCounter, nullptr, rb, spec);
+		if (cnt) k_trace_any<true><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (uint32_t *) dOut, rayCounter, cnt, rb, spec, lt);
+		else k_trace_any<false><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (uint32_t *) dOut, rayCounter, nullptr, rb, spec, lt);
 	} else {
 		return setError(ctx, MTSGPU_ERR_ARG, "trace: unknown mode %d", mode);
 	}

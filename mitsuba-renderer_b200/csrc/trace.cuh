@@ -208,7 +208,7 @@ struct LaneState {
 // The visiting order never changes the closest hit (only which of several bit-identical t values is kept).
 template <bool SHADOW, bool COUNT, class Sink>
 __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const float4 *__restrict__ rays, uint32_t n,
-		uint32_t *counter, Sink &sink, uint2 *sstack, uint32_t &nodeVisits, uint32_t &triTests, int refetchBelow, bool speculate = true) {
+		uint32_t *counter, Sink &sink, uint2 *sstack, uint32_t &nodeVisits, uint32_t &triTests, int refetchBelow, bool speculate = true, int leafThreshold = 16) {
 	uint2 lstack[TRACE_LOCAL_STACK];
 	const uint32_t lane = threadIdx.x & 31u;
 	const uint32_t ltMask = (1u << lane) - 1u;
@@ -293,7 +293,11 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 					if (!SHADOW) {
 						// ascending by entry distance: 5-comparator network, then push far-to-near
 #define CSWAP(a, b) if (tn[b] < tn[a]) { float tt = tn[a]; tn[a] = tn[b]; tn[b] = tt; uint32_t cc = cw[a]; cw[a] = cw[b]; cw[b] = cc; }
+#ifdef TRACE_NEAREST_ONLY
+						CSWAP(0, 1) CSWAP(0, 2) CSWAP(0, 3)
+#else
 						CSWAP(0, 1) CSWAP(2, 3) CSWAP(0, 2) CSWAP(1, 3) CSWAP(1, 2)
+#endif
 #undef CSWAP
 					}
 #pragma unroll
@@ -305,6 +309,7 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 				}
 				const bool canWalk = s.active && !(s.cur & BVH_LEAF);
 				if (!__any_sync(0xFFFFFFFFu, canWalk && s.leaf == BVH_EMPTY)) break;   // nobody without a leaf can go on
+				if (__popc(__ballot_sync(0xFFFFFFFFu, s.active && s.leaf != BVH_EMPTY)) >= leafThreshold) break;   // enough leaves to test together
 			}
 			// (B) leaves: every lane that holds one tests its triangles; a second leaf waiting in `cur` moves up
 			while (true) {
