@@ -170,6 +170,16 @@ MTSGPU_API int mtsgpu_render(mtsgpu_ctx *ctx, const mtsgpu_render_params *params
 MTSGPU_API int mtsgpu_render_device(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, volatile const int *cancel,
 	float *d_outFilm, mtsgpu_stats *stats);
 
+/* Several GPUs, one process (the `mitsuba` CLI case). ctxs[i] are contexts on DIFFERENT devices that hold the
+ * same scene, camera and film. The sample range [sppBegin, sppEnd) of `params` is split evenly over them and
+ * rendered concurrently (one host thread per GPU); the film accumulators are then summed on ctxs[0]'s GPU by a
+ * single kernel that loads the peers' buffers over NVLink peer mappings, and copied to outFilm (host). Replaces the
+ * distribution of work units to local/remote workers and the mutex-guarded merge of their results
+ * (BlockedRenderProcess, src/librender/renderproc.cpp:106-160; RemoteWorker, src/libcore/sched_remote.cpp).
+ * stats: counters summed, times = max over GPUs (+ the reduce). */
+MTSGPU_API int mtsgpu_render_multi(mtsgpu_ctx **ctxs, int nCtx, const mtsgpu_render_params *params,
+	volatile const int *cancel, float *outFilm, mtsgpu_stats *stats);
+
 /* Batch ray queries against the scene; rays are rows of 8 floats {o.xyz, mint, d.xyz, maxt}
  * (include/mitsuba/core/ray.h:34-40 without dRcp/time). mode CLOSEST writes n mtsgpu_hit records,
  * mode ANY writes n uint32 (1 = occluded). Host buffers; copies are part of the call. */

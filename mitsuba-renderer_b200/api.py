@@ -26,7 +26,7 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_render", "mtsgpu_render_device", "mtsgpu_trace", "mtsgpu_trace_device", "mtsgpu_bsdf_eval",
     "mtsgpu_emitter_sample", "mtsgpu_camera_rays", "mtsgpu_film_splat", "mtsgpu_intersect_full",
     "mtsgpu_get_triaccel", "mtsgpu_accel_info_get", "mtsgpu_set_counters", "mtsgpu_get_counters",
-    "mtsgpu_film_splat_static",
+    "mtsgpu_film_splat_static", "mtsgpu_render_multi",
 ]
 STATIC_SCRATCH_BYTES = 4 << 20
 
@@ -101,6 +101,7 @@ def load_library(path: Optional[str] = None):
     lib.mtsgpu_build_accel.argtypes = [vp]
     lib.mtsgpu_render.argtypes = [vp, C.POINTER(RenderParams), vp, vp, C.POINTER(Stats)]
     lib.mtsgpu_render_device.argtypes = [vp, C.POINTER(RenderParams), vp, vp, C.POINTER(Stats)]
+    lib.mtsgpu_render_multi.argtypes = [C.POINTER(vp), C.c_int, C.POINTER(RenderParams), vp, vp, C.POINTER(Stats)]
     lib.mtsgpu_trace.argtypes = [vp, vp, C.c_size_t, C.c_int, vp]
     lib.mtsgpu_trace_device.argtypes = [vp, vp, C.c_size_t, C.c_int, vp, C.POINTER(C.c_float)]
     for name in ("mtsgpu_bsdf_eval", "mtsgpu_emitter_sample", "mtsgpu_camera_rays", "mtsgpu_film_splat",
@@ -154,6 +155,19 @@ def box_table():
 
 def filter_table(filter_type):
     return box_table() if filter_type == FILTER_BOX else gaussian_table()
+
+
+def render_multi(contexts, params: RenderParams):
+    """mtsgpu_render_multi: contexts on different GPUs holding the same scene render disjoint sample ranges;
+    returns (film summed over NVLink peer memory, stats)."""
+    lib = contexts[0].lib
+    arr = (C.c_void_p * len(contexts))(*[c.h for c in contexts])
+    out = np.empty(contexts[0].film_shape, np.float32)
+    st = Stats()
+    rc = lib.mtsgpu_render_multi(arr, len(contexts), C.byref(params), None, out.ctypes.data_as(C.c_void_p), C.byref(st))
+    if rc != 0:
+        raise MtsGpuError(rc, lib.mtsgpu_last_error(contexts[0].h).decode())
+    return out, st.as_dict()
 
 
 class Context:

@@ -19,6 +19,8 @@
 #include <mitsuba/core/statistics.h>
 #include <mitsuba/core/timer.h>
 #include <map>
+#include <vector>
+#include <algorithm>
 #include "mtsgpu.h"
 
 MTS_NAMESPACE_BEGIN
@@ -41,6 +43,8 @@ public:
 		m_luminaireSamples = props.getInteger("luminaireSamples", 1);
 		m_bsdfSamples = props.getInteger("bsdfSamples", 1);
 		m_device = props.getInteger("device", 0);
+		/* number of GPUs to shard the sample range over (devices device .. device+gpus-1) */
+		m_gpus = props.getInteger("gpus", 1);
 		m_seed = props.getInteger("seed", 0);
 		AssertEx(m_rrDepth > 0, "rrDepth == 0 breaks the computation of alpha values!");
 		Assert(m_luminaireSamples + m_bsdfSamples > 0);
@@ -49,14 +53,14 @@ public:
 	GPUPathIntegrator(Stream *stream, InstanceManager *manager) : SampleIntegrator(stream, manager), m_cancel(0) {
 		m_mode = stream->readInt(); m_maxDepth = stream->readInt(); m_rrDepth = stream->readInt();
 		m_strictNormals = stream->readBool(); m_luminaireSamples = stream->readInt(); m_bsdfSamples = stream->readInt();
-		m_device = stream->readInt(); m_seed = stream->readInt();
+		m_device = stream->readInt(); m_seed = stream->readInt(); m_gpus = stream->readInt();
 	}
 
 	void serialize(Stream *stream, InstanceManager *manager) const {
 		SampleIntegrator::serialize(stream, manager);
 		stream->writeInt(m_mode); stream->writeInt(m_maxDepth); stream->writeInt(m_rrDepth);
 		stream->writeBool(m_strictNormals); stream->writeInt(m_luminaireSamples); stream->writeInt(m_bsdfSamples);
-		stream->writeInt(m_device); stream->writeInt(m_seed);
+		stream->writeInt(m_device); stream->writeInt(m_seed); stream->writeInt(m_gpus);
 	}
 
 	Spectrum Li(const RayDifferential &, RadianceQueryRecord &) const {
@@ -68,17 +72,21 @@ public:
 
 	bool render(Scene *scene, RenderQueue *queue, const RenderJob *job, int, int, int) {
 		m_cancel = 0;
-		mtsgpu_ctx *ctx = NULL;
-		if (mtsgpu_create(m_device, &ctx) != MTSGPU_OK)
-			Log(EError, "gpupath: %s", mtsgpu_last_error(NULL));
+		std::vector<mtsgpu_ctx *> ctxs;
 		bool ok = false;
 		try {
-			ok = renderImpl(ctx, scene, queue, job);
+			for (int g = 0; g < std::max(1, m_gpus); ++g) {
+				mtsgpu_ctx *ctx = NULL;
+				if (mtsgpu_create(m_device + g, &ctx) != MTSGPU_OK)
+					Log(EError, "gpupath: GPU %i: %s", m_device + g, mtsgpu_last_error(NULL));
+				ctxs.push_back(ctx);
+			}
+			ok = renderImpl(ctxs, scene, queue, job);
 		} catch (...) {
-			mtsgpu_destroy(ctx);
+			for (size_t i = 0; i < ctxs.size(); ++i) mtsgpu_destroy(ctxs[i]);
 			throw;
 		}
-		mtsgpu_destroy(ctx);
+		for (size_t i = 0; i < ctxs.size(); ++i) mtsgpu_destroy(ctxs[i]);
 		return ok;
 	}
 
@@ -155,7 +163,8 @@ private:
 		return decodePayload(bsdf->getClass()->getName(), s);
 	}
 
-	bool renderImpl(mtsgpu_ctx *ctx, Scene *scene, RenderQueue *queue, const RenderJob *job) {
+	bool renderImpl(std::vector<mtsgpu_ctx *> &ctxs, Scene *scene, RenderQueue *queue, const RenderJob *job) {
+		mtsgpu_ctx *ctx = ctxs[0];
 		ref<Timer> timer = new Timer();
 		const Camera *camera = scene->getCamera();
 		Film *film = scene->getFilm();
@@ -207,16 +216,19 @@ private:
 				r.emit = emitterIds[shape->getLuminaire()];
 			meshes.push_back(r);
 		}
-		check(ctx, mtsgpu_upload_materials(ctx, materials.empty() ? NULL : &materials[0], (int) materials.size()));
-		check(ctx, mtsgpu_upload_emitters(ctx, emitters.empty() ? NULL : &emitters[0], (int) emitters.size()));
-		for (size_t i = 0; i < meshes.size(); ++i) {
-			const TriMesh *m = meshes[i].mesh;
-			/* Point/Normal are 3 packed floats, Triangle is 3 packed uint32 (core/triangle.h) */
-			check(ctx, mtsgpu_upload_mesh(ctx, (int) i,
-				reinterpret_cast<const float *>(m->getVertexPositions()),
-				reinterpret_cast<const float *>(m->getVertexNormals()), NULL, (uint32_t) m->getVertexCount(),
-				reinterpret_cast<const uint32_t *>(m->getTriangles()), (uint32_t) m->getTriangleCount(),
-				meshes[i].mat, meshes[i].emit));
+		for (size_t g = 0; g < ctxs.size(); ++g) {       /* the scene is replicated on every GPU */
+			mtsgpu_ctx *c = ctxs[g];
+			check(c, mtsgpu_upload_materials(c, materials.empty() ? NULL : &materials[0], (int) materials.size()));
+			check(c, mtsgpu_upload_emitters(c, emitters.empty() ? NULL : &emitters[0], (int) emitters.size()));
+			for (size_t i = 0; i < meshes.size(); ++i) {
+				const TriMesh *m = meshes[i].mesh;
+				/* Point/Normal are 3 packed floats, Triangle is 3 packed uint32 (core/triangle.h) */
+				check(c, mtsgpu_upload_mesh(c, (int) i,
+					reinterpret_cast<const float *>(m->getVertexPositions()),
+					reinterpret_cast<const float *>(m->getVertexNormals()), NULL, (uint32_t) m->getVertexCount(),
+					reinterpret_cast<const uint32_t *>(m->getTriangles()), (uint32_t) m->getTriangleCount(),
+					meshes[i].mat, meshes[i].emit));
+			}
 		}
 
 		/* ---- camera: m_rasterToCamera is private to the plugin class, so rebuild it with the same
@@ -252,18 +264,20 @@ private:
 			r2c[i * 4 + j] = rasterToCamera.getMatrix().m[i][j];
 			c2w[i * 4 + j] = camera->getInverseViewTransform().getMatrix().m[i][j];
 		}
-		check(ctx, mtsgpu_set_camera(ctx, r2c, c2w, pc->getNearClip(), pc->getFarClip(), pc->getApertureRadius(),
-			pc->getFocusDepth(), camera->getShutterOpen(), camera->getShutterOpenTime()));
+		for (size_t g = 0; g < ctxs.size(); ++g)
+			check(ctxs[g], mtsgpu_set_camera(ctxs[g], r2c, c2w, pc->getNearClip(), pc->getFarClip(), pc->getApertureRadius(),
+				pc->getFocusDepth(), camera->getShutterOpen(), camera->getShutterOpenTime()));
 
 		/* ---- film + tabulated filter (rfilter.h:65-118) ---- */
 		const TabulatedFilter *filter = film->getTabulatedFilter();
 		float table[256];
 		for (int y = 0; y < 16; ++y) for (int x = 0; x < 16; ++x) table[y * 16 + x] = filter->lookup(x, y);
 		const Vector2i csize = film->getCropSize(); const Point2i coff = film->getCropOffset();
-		check(ctx, mtsgpu_set_film(ctx, fsize.x, fsize.y, coff.x, coff.y, csize.x, csize.y, table,
-			filter->getFilterSize().x, filter->getFilterSize().y));
-
-		check(ctx, mtsgpu_build_accel(ctx));
+		for (size_t g = 0; g < ctxs.size(); ++g) {
+			check(ctxs[g], mtsgpu_set_film(ctxs[g], fsize.x, fsize.y, coff.x, coff.y, csize.x, csize.y, table,
+				filter->getFilterSize().x, filter->getFilterSize().y));
+			check(ctxs[g], mtsgpu_build_accel(ctxs[g]));
+		}
 		mtsgpu_accel_info info; check(ctx, mtsgpu_accel_info_get(ctx, &info));
 		Log(EInfo, "gpupath: %u triangles, %u BVH nodes, built on the GPU in %.1f ms (upload + build %i ms)",
 			(unsigned) info.triangles, (unsigned) info.nodes, info.buildMs, timer->getMilliseconds());
@@ -278,7 +292,8 @@ private:
 		std::vector<float> accum(nPix * 5);
 		mtsgpu_stats stats;
 		timer->reset();
-		const int rc = mtsgpu_render(ctx, &P, &m_cancel, &accum[0], &stats);
+		const int rc = ctxs.size() == 1 ? mtsgpu_render(ctx, &P, &m_cancel, &accum[0], &stats)
+			: mtsgpu_render_multi(&ctxs[0], (int) ctxs.size(), &P, &m_cancel, &accum[0], &stats);   /* sample range split + NVLink peer reduce */
 		if (rc == MTSGPU_ERR_CANCELLED)
 			return false;
 		check(ctx, rc);
@@ -312,7 +327,7 @@ private:
 		return true;
 	}
 
-	int m_mode, m_maxDepth, m_rrDepth, m_luminaireSamples, m_bsdfSamples, m_device, m_seed;
+	int m_mode, m_maxDepth, m_rrDepth, m_luminaireSamples, m_bsdfSamples, m_device, m_seed, m_gpus;
 	bool m_strictNormals;
 	volatile int m_cancel;
 };

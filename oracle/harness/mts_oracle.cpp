@@ -182,6 +182,7 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 			p.setBoolean("strictNormals", s.strictNormals != 0);
 			p.setInteger("luminaireSamples", (int) s.nLumSamples);
 			p.setInteger("bsdfSamples", (int) s.nBsdfSamples);
+			if (getenv("MTS_ORACLE_GPUS")) p.setInteger("gpus", atoi(getenv("MTS_ORACLE_GPUS")));
 		}
 		ref<Integrator> integrator = static_cast<Integrator *>(create(MTS_CLASS(Integrator), p));
 		scene->addChild("", integrator);
