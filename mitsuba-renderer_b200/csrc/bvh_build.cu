@@ -217,7 +217,8 @@ __global__ void k_collapse(const uint2 *qIn, uint32_t nIn, uint2 *qOut, uint32_t
 	float lo[3][4], hi[3][4]; uint32_t cw[4];
 	for (int i = 0; i < 4; ++i) {
 		if (i >= cnt) {
-			lo[0][i] = lo[1][i] = lo[2][i] = INFINITY; hi[0][i] = hi[1][i] = hi[2][i] = -INFINITY;
+			// empty slot: lo = hi = +inf, which no finite ray interval can enter (trace.cuh relies on this)
+			lo[0][i] = lo[1][i] = lo[2][i] = INFINITY; hi[0][i] = hi[1][i] = hi[2][i] = INFINITY;
 			cw[i] = BVH_EMPTY;
 			continue;
 		}
@@ -488,7 +489,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		BVH4Node nd;
 		const float inf = INFINITY;
 		nd.lox = make_float4(lo.x, inf, inf, inf); nd.loy = make_float4(lo.y, inf, inf, inf); nd.loz = make_float4(lo.z, inf, inf, inf);
-		nd.hix = make_float4(hi.x, -inf, -inf, -inf); nd.hiy = make_float4(hi.y, -inf, -inf, -inf); nd.hiz = make_float4(hi.z, -inf, -inf, -inf);
+		nd.hix = make_float4(hi.x, inf, inf, inf); nd.hiy = make_float4(hi.y, inf, inf, inf); nd.hiz = make_float4(hi.z, inf, inf, inf);
 		nd.child = make_uint4(BVH_LEAF | 0u, BVH_EMPTY, BVH_EMPTY, BVH_EMPTY);
 		nd.pad = make_uint4(0, 0, 0, 0);
 		CUDA_TRY(ctx, cudaMemcpyAsync(dNodesTmp.p, &nd, sizeof(nd), cudaMemcpyHostToDevice, st));
