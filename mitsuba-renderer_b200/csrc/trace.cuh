@@ -113,37 +113,30 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 				const float t0z = fmaf(lz[i], idz, -oiz), t1z = fmaf(hz[i], idz, -oiz);
 				const float tnear = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), mint));
 				const float tfar = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), maxt));
-				tn[i] = (cw[i] != BVH_EMPTY && tnear <= tfar) ? tnear : INFINITY;
+				tn[i] = (tnear <= tfar) ? tnear : INFINITY;      // empty slots have lo = hi = +inf: never entered
 			}
-			if (!SHADOW) {
-				// sort the four (tn, cw) pairs ascending: 5-comparator network
+			{
+				// nearest hit first; the others in any order (popped entries are culled by their entry distance)
 #define CSWAP(a, b) if (tn[b] < tn[a]) { float tt = tn[a]; tn[a] = tn[b]; tn[b] = tt; uint32_t cc = cw[a]; cw[a] = cw[b]; cw[b] = cc; }
-				CSWAP(0, 1) CSWAP(2, 3) CSWAP(0, 2) CSWAP(1, 3) CSWAP(1, 2)
+				CSWAP(0, 1) CSWAP(0, 2) CSWAP(0, 3)
 #undef CSWAP
+				const int h1 = tn[1] != INFINITY, h2 = tn[2] != INFINITY, h3 = tn[3] != INFINITY;
+				if (sp + 3 <= TRACE_SMEM_STACK) {       // common case: three predicated stores, no branches
+					if (h1) SSTACK(sp) = make_uint2(cw[1], __float_as_uint(tn[1]));
+					if (h2) SSTACK(sp + h1) = make_uint2(cw[2], __float_as_uint(tn[2]));
+					if (h3) SSTACK(sp + h1 + h2) = make_uint2(cw[3], __float_as_uint(tn[3]));
+					sp += h1 + h2 + h3;
+				} else {
 #pragma unroll
-				for (int i = 3; i >= 1; --i) {
-					if (tn[i] != INFINITY) {
-						const uint2 e = make_uint2(cw[i], __float_as_uint(tn[i]));
-						if (sp < TRACE_SMEM_STACK) SSTACK(sp) = e; else lstack[min(sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)] = e;
-						sp++;
-					}
-				}
-				if (tn[0] != INFINITY) { cur = cw[0]; continue; }
-			} else {
-				// any-hit: order is irrelevant; take the first hit child, push the rest
-				uint32_t next = BVH_EMPTY;
-#pragma unroll
-				for (int i = 0; i < 4; ++i) {
-					if (tn[i] != INFINITY) {
-						if (next == BVH_EMPTY) next = cw[i];
-						else {
-							const uint2 e = make_uint2(cw[i], 0u);
+					for (int i = 1; i <= 3; ++i) {
+						if (tn[i] != INFINITY) {
+							const uint2 e = make_uint2(cw[i], __float_as_uint(tn[i]));
 							if (sp < TRACE_SMEM_STACK) SSTACK(sp) = e; else lstack[min(sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)] = e;
 							sp++;
 						}
 					}
 				}
-				if (next != BVH_EMPTY) { cur = next; continue; }
+				if (tn[0] != INFINITY) { cur = cw[0]; continue; }
 			}
 		} else {
 			// leaf: (count-1)<<28 | first
