@@ -2,6 +2,7 @@
 #include "context.h"
 #include <cstring>
 #include <cmath>
+#include <algorithm>
 
 int setError(mtsgpu_ctx *ctx, int code, const char *fmt, ...) {
 	char buf[1024];
@@ -45,6 +46,10 @@ void mtsgpu_destroy(mtsgpu_ctx *ctx) {
 	cudaSetDevice(ctx->device);
 	cudaStreamSynchronize(ctx->stream);
 	for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+	if (ctx->copyIn) {
+		cudaStreamDestroy(ctx->copyIn); cudaStreamDestroy(ctx->copyOut);
+		for (int i = 0; i < 2 * MTSGPU_PIPE_CHUNKS; ++i) cudaEventDestroy(ctx->pipeEv[i]);
+	}
 	cudaStreamDestroy(ctx->stream);
 	if (ctx->hCounts) cudaFreeHost(ctx->hCounts);
 	delete ctx;
@@ -193,11 +198,41 @@ int mtsgpu_trace(mtsgpu_ctx *ctx, const float *rays, size_t n, int mode, void *o
 	const size_t outBytes = n * (mode == MTSGPU_TRACE_CLOSEST ? sizeof(mtsgpu_hit) : sizeof(uint32_t));
 	CUDA_TRY(ctx, ctx->dRays.alloc(n * 32));
 	CUDA_TRY(ctx, ctx->dHits.alloc(outBytes));
-	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dRays.p, rays, n * 32, cudaMemcpyHostToDevice, ctx->stream));
-	int rc = mtsgpu_trace_device(ctx, ctx->dRays.as<float>(), n, mode, ctx->dHits.p, nullptr);
-	if (rc) return rc;
-	CUDA_TRY(ctx, cudaMemcpyAsync(out, ctx->dHits.p, outBytes, cudaMemcpyDeviceToHost, ctx->stream));
+	const size_t outStride = mode == MTSGPU_TRACE_CLOSEST ? sizeof(mtsgpu_hit) : sizeof(uint32_t);
+	if (n < (1u << 21) || ctx->countersEnabled) {
+		CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dRays.p, rays, n * 32, cudaMemcpyHostToDevice, ctx->stream));
+		int rc = mtsgpu_trace_device(ctx, ctx->dRays.as<float>(), n, mode, ctx->dHits.p, nullptr);
+		if (rc) return rc;
+		CUDA_TRY(ctx, cudaMemcpyAsync(out, ctx->dHits.p, outBytes, cudaMemcpyDeviceToHost, ctx->stream));
+		CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+		return MTSGPU_OK;
+	}
+	// Large batches: three-stage pipeline over chunks — upload of chunk k+1, traversal of chunk k and download of
+	// chunk k-1 run concurrently on three streams (PCIe is full duplex), ordered by events. With pinned host
+	// buffers the copies are truly asynchronous; with pageable ones CUDA stages them and the result is the same.
+	if (!ctx->copyIn) {
+		CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->copyIn, cudaStreamNonBlocking));
+		CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->copyOut, cudaStreamNonBlocking));
+		for (int i = 0; i < 2 * MTSGPU_PIPE_CHUNKS; ++i) CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->pipeEv[i], cudaEventDisableTiming));
+	}
+	const size_t chunk = std::max<size_t>((size_t) 1 << 20, (n + MTSGPU_PIPE_CHUNKS - 1) / MTSGPU_PIPE_CHUNKS);
+	int k = 0;
+	for (size_t off = 0; off < n; off += chunk, ++k) {
+		const size_t m = std::min(chunk, n - off);
+		float *dIn = ctx->dRays.as<float>() + off * 8;
+		char *dOut = ctx->dHits.as<char>() + off * outStride;
+		CUDA_TRY(ctx, cudaMemcpyAsync(dIn, rays + off * 8, m * 32, cudaMemcpyHostToDevice, ctx->copyIn));
+		CUDA_TRY(ctx, cudaEventRecord(ctx->pipeEv[2 * k], ctx->copyIn));
+		CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipeEv[2 * k], 0));
+		int rc = launchTrace(ctx, reinterpret_cast<const float4 *>(dIn), m, mode, dOut, nullptr);
+		if (rc) return rc;
+		CUDA_TRY(ctx, cudaEventRecord(ctx->pipeEv[2 * k + 1], ctx->stream));
+		CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->copyOut, ctx->pipeEv[2 * k + 1], 0));
+		CUDA_TRY(ctx, cudaMemcpyAsync(static_cast<char *>(out) + off * outStride, dOut, m * outStride, cudaMemcpyDeviceToHost, ctx->copyOut));
+	}
+	CUDA_TRY(ctx, cudaStreamSynchronize(ctx->copyOut));
 	CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	CUDA_TRY(ctx, cudaGetLastError());
 	return MTSGPU_OK;
 }
 

@@ -7,6 +7,8 @@
 #include <cstdarg>
 #include "types.cuh"
 
+#define MTSGPU_PIPE_CHUNKS 16
+
 struct DevBuf {
 	void *p = nullptr; size_t bytes = 0;
 	DevBuf() {}
@@ -33,6 +35,9 @@ struct mtsgpu_ctx {
 	int device = 0;
 	cudaStream_t stream = nullptr;
 	cudaEvent_t ev[8] = {};
+	// upload / download streams + ordering events of the pipelined host-buffer ray query (api.cu)
+	cudaStream_t copyIn = nullptr, copyOut = nullptr;
+	cudaEvent_t pipeEv[2 * 16] = {};
 	std::string error;
 
 	// host-side scene staging
