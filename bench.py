@@ -303,7 +303,7 @@ def main():
     ap.add_argument("--rays", type=int, default=1 << 24, help="rays per batch (coherent batch is the nearest square)")
     ap.add_argument("--cpu-rays", type=int, default=0, help="rays per batch of the bounded CPU sample (0 = auto)")
     ap.add_argument("--no-render", action="store_true")
-    ap.add_argument("--render", default="c1", choices=["c1", "c3", "c4", "c5"], help="config of the render leg")
+    ap.add_argument("--render", default="c4", choices=["c1", "c3", "c4", "c5"], help="config of the render leg")
     ap.add_argument("--render-spp", type=int, default=0, help="override the render leg's samples per pixel")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
