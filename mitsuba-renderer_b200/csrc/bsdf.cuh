@@ -171,6 +171,89 @@ __device__ inline float bsdfPdf_base(const MaterialDev &m, V3 wi, V3 wo) {
 	}
 }
 
+// ---- f and pdf together ----------------------------------------------------------------------------
+// The reference evaluates f() and pdf() separately (and again after sampling, bsdf.cpp:37-48); both depend on
+// the same half-vector and Beckmann term. Computing those once gives bit-identical values (same expressions on
+// the same inputs) for a third of the transcendental work.
+__device__ inline void bsdfFPdf_base(const MaterialDev &m, V3 wi, V3 wo, V3 &f, float &pdf) {
+	f = v3(0, 0, 0); pdf = 0.0f;
+	switch (m.type & MTSGPU_BSDF_TYPE_MASK) {
+		case MTSGPU_BSDF_LAMBERTIAN:
+			if (wi.z <= 0 || wo.z <= 0) return;
+			f = mp3(m, 0) * MTS_INV_PI; pdf = wo.z * MTS_INV_PI;
+			return;
+		case MTSGPU_BSDF_MICROFACET: {
+			if (wi.z <= 0 || wo.z <= 0) return;
+			const float kd = m.p[6], ks = m.p[7], alphaB = m.p[8], intIOR = m.p[9], extIOR = m.p[10];
+			const V3 Hr = normalize(wi + wo);
+			const float F = fresnel(dot(wi, Hr), extIOR, intIOR);
+			const float D = beckmannD(Hr, alphaB);
+			const float G = smithBeckmannG1(wi, Hr, alphaB) * smithBeckmannG1(wo, Hr, alphaB);
+			const float specRef = D * G / (4.0f * wi.z * wo.z);
+			f = (mp3(m, 3) * specRef) * (F * ks);
+			f = f + mp3(m, 0) * (MTS_INV_PI * (1 - F) * kd);
+			float fr = fresnel(wi.z, extIOR, intIOR);
+			fr = fminf(fmaxf(fr, 0.05f), 0.95f);
+			const float diffuseSamplingWeight = (1 - fr) * kd;
+			const float specularSamplingWeight = fr * ks;
+			const float normalization = 1 / (diffuseSamplingWeight + specularSamplingWeight);
+			const float pdfSpec = D * Hr.z / (4.0f * fabsf(dot(wo, Hr)));
+			pdf = (specularSamplingWeight * pdfSpec + diffuseSamplingWeight * (wo.z * MTS_INV_PI)) * normalization;
+			return;
+		}
+		case MTSGPU_BSDF_ROUGHMETAL: {
+			if (wi.z <= 0 || wo.z <= 0) return;
+			const float alphaB = m.p[3];
+			const V3 Hr = normalize(wi + wo);
+			const V3 F = fresnelConductor(dot(wi, Hr), mp3(m, 4), mp3(m, 7));
+			const float D = beckmannD(Hr, alphaB);
+			const float G = smithBeckmannG1(wi, Hr, alphaB) * smithBeckmannG1(wo, Hr, alphaB);
+			f = mp3(m, 0) * (F * (D * G / (4.0f * wi.z * wo.z)));
+			const float dwhr_dwo = 1.0f / (4.0f * fabsf(dot(wo, Hr)));
+			pdf = D * Hr.z * dwhr_dwo;
+			return;
+		}
+		default:
+			return;
+	}
+}
+
+// Sampling of the two rough models (microfacet.cpp:201-269, roughmetal.cpp:147-167): direction, then f and pdf at
+// it. Returns false exactly when the reference's 2-argument sample() returns a zero spectrum.
+__device__ inline bool bsdfSampleRough(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, uint32_t &type, V3 &f, float &pdf, V3 &ratio) {
+	if (wi.z <= 0) return false;
+	if ((m.type & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_MICROFACET) {
+		const float kd = m.p[6], ks = m.p[7], alphaB = m.p[8], intIOR = m.p[9], extIOR = m.p[10];
+		float fr = fresnel(wi.z, extIOR, intIOR);
+		fr = fminf(fmaxf(fr, 0.05f), 0.95f);
+		float diffuseSamplingWeight = (1 - fr) * kd;
+		float specularSamplingWeight = fr * ks;
+		const float normalization = 1 / (diffuseSamplingWeight + specularSamplingWeight);
+		specularSamplingWeight *= normalization;
+		diffuseSamplingWeight *= normalization;
+		if (sx < specularSamplingWeight) {
+			sx /= specularSamplingWeight;
+			wo = reflectAbout(wi, sampleBeckmannD(sx, sy, alphaB));
+			type = BSDF_GLOSSY_REFLECTION;
+			if (wo.z <= 0) return false;
+			bsdfFPdf_base(m, wi, wo, f, pdf);
+			if (pdf == 0) return false;
+		} else {
+			sx = (sx - specularSamplingWeight) / diffuseSamplingWeight;
+			wo = squareToHemispherePSA(sx, sy);
+			type = BSDF_DIFFUSE_REFLECTION;
+			bsdfFPdf_base(m, wi, wo, f, pdf);
+		}
+	} else {
+		wo = reflectAbout(wi, sampleBeckmannD(sx, sy, m.p[3]));
+		type = BSDF_GLOSSY_REFLECTION;
+		if (wo.z <= 0) return false;
+		bsdfFPdf_base(m, wi, wo, f, pdf);
+	}
+	ratio = f * (1.0f / pdf);
+	return !isZero(ratio);
+}
+
 // ---- dielectric core (dielectric.cpp:116-146): Fresnel reflectance + transmitted cosine -------------
 __device__ inline void dielectricSetup(const MaterialDev &m, V3 wi, float &Fr, float &eta, float &cosThetaT) {
 	const float cosThetaI = wi.z;
@@ -203,39 +286,10 @@ __device__ inline V3 bsdfSample2_base(const MaterialDev &m, V3 wi, float sx, flo
 			wo = v3(-wi.x, -wi.y, wi.z);
 			type = BSDF_DELTA_REFLECTION;
 			return mp3(m, 0);                               // Mirror::sample(2-arg) forwards to the 3-arg one
-		case MTSGPU_BSDF_MICROFACET: {
-			if (wi.z <= 0) return zero;
-			const float kd = m.p[6], ks = m.p[7], alphaB = m.p[8], intIOR = m.p[9], extIOR = m.p[10];
-			float fr = fresnel(wi.z, extIOR, intIOR);
-			fr = fminf(fmaxf(fr, 0.05f), 0.95f);
-			float diffuseSamplingWeight = (1 - fr) * kd;
-			float specularSamplingWeight = fr * ks;
-			const float normalization = 1 / (diffuseSamplingWeight + specularSamplingWeight);
-			specularSamplingWeight *= normalization;
-			diffuseSamplingWeight *= normalization;
-			if (sx < specularSamplingWeight) {
-				sx /= specularSamplingWeight;
-				const V3 mm = sampleBeckmannD(sx, sy, alphaB);
-				wo = reflectAbout(wi, mm);
-				type = BSDF_GLOSSY_REFLECTION;
-				if (wo.z <= 0) return zero;
-				const float pdfValue = bsdfPdf_base(m, wi, wo);
-				if (pdfValue == 0) return zero;
-				return bsdfF_base(m, wi, wo) * (1.0f / pdfValue);
-			} else {
-				sx = (sx - specularSamplingWeight) / diffuseSamplingWeight;
-				wo = squareToHemispherePSA(sx, sy);
-				type = BSDF_DIFFUSE_REFLECTION;
-				return bsdfF_base(m, wi, wo) * (1.0f / bsdfPdf_base(m, wi, wo));
-			}
-		}
+		case MTSGPU_BSDF_MICROFACET:
 		case MTSGPU_BSDF_ROUGHMETAL: {
-			if (wi.z <= 0) return zero;
-			const V3 mm = sampleBeckmannD(sx, sy, m.p[3]);
-			wo = reflectAbout(wi, mm);
-			type = BSDF_GLOSSY_REFLECTION;
-			if (wo.z <= 0) return zero;
-			return bsdfF_base(m, wi, wo) * (1.0f / bsdfPdf_base(m, wi, wo));
+			V3 f, ratio; float pdf;
+			return bsdfSampleRough(m, wi, sx, sy, wo, type, f, pdf, ratio) ? ratio : zero;
 		}
 		case MTSGPU_BSDF_DIELECTRIC: {
 			float Fr, eta, cosThetaT;
@@ -287,10 +341,9 @@ __device__ inline V3 bsdfSample3_base(const MaterialDev &m, V3 wi, float sx, flo
 		}
 		default: {
 			// BSDF::sample(bRec, pdf, sample) fallback (bsdf.cpp:37-48): 2-arg sample, then pdf() and f()
-			const V3 s = bsdfSample2_base(m, wi, sx, sy, wo, type);
-			if (isZero(s)) { pdf = 0.0f; return zero; }
-			pdf = bsdfPdf_base(m, wi, wo);
-			return bsdfF_base(m, wi, wo);
+			V3 f, ratio;
+			if (!bsdfSampleRough(m, wi, sx, sy, wo, type, f, pdf, ratio)) { pdf = 0.0f; return zero; }
+			return f;          // pdf() and f() re-evaluated by the reference give these same values
 		}
 	}
 }
@@ -299,6 +352,10 @@ __device__ inline V3 bsdfSample3_base(const MaterialDev &m, V3 wi, float sx, flo
 __device__ inline V3 bsdfF(const MaterialDev &m, V3 wi, V3 wo) {
 	if ((m.type & MTSGPU_BSDF_TWOSIDED) && wi.z < 0) { wi.z *= -1; wo.z *= -1; }
 	return bsdfF_base(m, wi, wo);
+}
+__device__ inline void bsdfFPdf(const MaterialDev &m, V3 wi, V3 wo, V3 &f, float &pdf) {
+	if ((m.type & MTSGPU_BSDF_TWOSIDED) && wi.z < 0) { wi.z *= -1; wo.z *= -1; }
+	bsdfFPdf_base(m, wi, wo, f, pdf);
 }
 __device__ inline float bsdfPdf(const MaterialDev &m, V3 wi, V3 wo) {
 	if ((m.type & MTSGPU_BSDF_TWOSIDED) && wi.z < 0) { wi.z *= -1; wo.z *= -1; }

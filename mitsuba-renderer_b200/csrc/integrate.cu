@@ -215,11 +215,11 @@ __device__ __forceinline__ bool nextEvent(const DeviceScene &sc, const Integrato
 	if (ls.pdf == 0) return false;
 	const V3 wo = -ls.d;
 	const V3 woLocal = toLocal(its.sh, wo);
-	const V3 f = bsdfF(mat, its.wi, woLocal);
+	V3 f; float bPdf;                                                      // area luminaires are intersectable: pdf is needed
+	bsdfFPdf(mat, its.wi, woLocal, f, bPdf);
 	const V3 bsdfVal = f * fabsf(woLocal.z);                               // fCos
 	if (isZero(bsdfVal)) return false;
 	if (ig.strictNormals && !(dot(its.geoN, wo) * woLocal.z > 0)) return false;
-	const float bPdf = bsdfPdf(mat, its.wi, woLocal);                      // area luminaires are intersectable
 	const float weight = miWeight(ls.pdf * fracLum, bPdf * fracBsdf) * weightLum;
 	contrib = ((scale * ls.value) * bsdfVal) * weight;
 	// Scene::isOccluded(p1, p2): Ray(p1, p2 - p1, ShadowEpsilon, 1 - ShadowEpsilon) (scene.h:241-246)
