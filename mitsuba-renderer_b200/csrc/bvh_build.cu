@@ -13,6 +13,7 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <algorithm>
 #include <cfloat>
+#include <cstdlib>
 
 namespace {
 
@@ -440,8 +441,15 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	CUDA_TRY(ctx, dKeys.alloc(nTri * 8)); CUDA_TRY(ctx, dKeysAlt.alloc(nTri * 8));
 	CUDA_TRY(ctx, dVals.alloc(nTri * 4)); CUDA_TRY(ctx, dValsAlt.alloc(nTri * 4));
 	float3 bmin = make_float3(tmin[0], tmin[1], tmin[2]);
-	float3 invExt = make_float3(tmax[0] > tmin[0] ? 1.0f / (tmax[0] - tmin[0]) : 0.0f,
-		tmax[1] > tmin[1] ? 1.0f / (tmax[1] - tmin[1]) : 0.0f, tmax[2] > tmin[2] ? 1.0f / (tmax[2] - tmin[2]) : 0.0f);
+	// Isotropic quantisation: one scale (the largest extent) for all three axes, so that Morton cells are
+	// cubes. Per-axis normalisation spends every third key bit on the thin axis of a flat scene (terrain,
+	// rooms) and produces slab-shaped nodes with a large surface area.
+	const float maxExt = std::max(tmax[0] - tmin[0], std::max(tmax[1] - tmin[1], tmax[2] - tmin[2]));
+	const float inv = maxExt > 0.0f ? 1.0f / maxExt : 0.0f;
+	float3 invExt = make_float3(inv, inv, inv);
+	if (getenv("MTSGPU_MORTON_ANISO"))       // experiment switch: the per-axis normalisation
+		invExt = make_float3(tmax[0] > tmin[0] ? 1.0f / (tmax[0] - tmin[0]) : 0.0f,
+			tmax[1] > tmin[1] ? 1.0f / (tmax[1] - tmin[1]) : 0.0f, tmax[2] > tmin[2] ? 1.0f / (tmax[2] - tmin[2]) : 0.0f);
 	k_morton<<<blocksFor(nTri, 256), 256, 0, st>>>(dTriLo.as<float4>(), dTriHi.as<float4>(), (uint32_t) nTri, bmin, invExt,
 		dKeys.as<uint64_t>(), dVals.as<uint32_t>());
 	CUDA_TRY(ctx, cudaGetLastError());
