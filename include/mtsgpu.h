@@ -46,8 +46,12 @@ enum mtsgpu_bsdf_type {
 	                               p[6] diffuseAmount, p[7] specularAmount, p[8] alphaB, p[9] intIOR, p[10] extIOR */
 	MTSGPU_BSDF_MIRROR = 2,     /* src/bsdfs/mirror.cpp:26       p[0..2] specularReflectance */
 	MTSGPU_BSDF_ROUGHMETAL = 3, /* src/bsdfs/roughmetal.cpp:33   p[0..2] specularReflectance, p[3] alphaB, p[4..6] ior, p[7..9] k */
-	MTSGPU_BSDF_DIELECTRIC = 4  /* src/bsdfs/dielectric.cpp:47   p[0..2] specularReflectance, p[3..5] specularTransmittance,
+	MTSGPU_BSDF_DIELECTRIC = 4, /* src/bsdfs/dielectric.cpp:47   p[0..2] specularReflectance, p[3..5] specularTransmittance,
 	                               p[6] intIOR, p[7] extIOR */
+	MTSGPU_BSDF_PHONG = 5       /* src/bsdfs/phong.cpp:30        p[0..2] diffuseReflectance, p[3..5] specularReflectance, then the
+	                               values AFTER Phong::configure (phong.cpp:79-99), as Phong::serialize writes them:
+	                               p[6] diffuseAmount, p[7] specularAmount, p[8] exponent, p[9] specularSamplingWeight,
+	                               p[10] diffuseSamplingWeight */
 };
 
 /* OR-ed into mtsgpu_material.type: the BRDF is wrapped in the `twosided` adapter (src/bsdfs/twosided.cpp:36-143),

@@ -9,6 +9,7 @@
 #pragma once
 #include "types.cuh"
 
+#define MTS_INV_TWOPI 0.15915494309189533577f
 #define BSDF_DIFFUSE_REFLECTION  0x0001u
 #define BSDF_DELTA_REFLECTION    0x0004u
 #define BSDF_DELTA_TRANSMISSION  0x0008u
@@ -132,6 +133,17 @@ __device__ inline V3 bsdfF_base(const MaterialDev &m, V3 wi, V3 wo) {
 			const V3 specRef = F * (D * G / (4.0f * wi.z * wo.z));
 			return mp3(m, 0) * specRef;
 		}
+		case MTSGPU_BSDF_PHONG: {                  // phong.cpp:104-131
+			if (wi.z <= 0 || wo.z <= 0) return zero;
+			const float kd = m.p[6], ks = m.p[7], exponent = m.p[8];
+			const float alpha = dot(v3(-wi.x, -wi.y, wi.z), wo);
+			float specRef;
+			if (alpha <= 0.0f) specRef = 0.0f;
+			else specRef = (exponent + 2) * MTS_INV_TWOPI * mts_pow(alpha, exponent) * ks;
+			V3 result = mp3(m, 3) * specRef;
+			result = result + mp3(m, 0) * (MTS_INV_PI * kd);
+			return result;
+		}
 		default:   // mirror, dielectric: delta lobes only
 			return zero;
 	}
@@ -165,6 +177,14 @@ __device__ inline float bsdfPdf_base(const MaterialDev &m, V3 wi, V3 wo) {
 			const V3 Hr = normalize(wi + wo);
 			const float dwhr_dwo = 1.0f / (4.0f * fabsf(dot(wo, Hr)));
 			return beckmannD(Hr, alphaB) * Hr.z * dwhr_dwo;
+		}
+		case MTSGPU_BSDF_PHONG: {                  // phong.cpp:133-162
+			if (wo.z <= 0 || wi.z <= 0) return 0.0f;
+			const float exponent = m.p[8];
+			const float alpha = dot(v3(-wi.x, -wi.y, wi.z), wo);
+			float specPdf = mts_pow(alpha, exponent) * (exponent + 1.0f) / (2.0f * MTS_PI);
+			if (alpha <= 0) specPdf = 0;
+			return m.p[9] * specPdf + m.p[10] * (wo.z * MTS_INV_PI);
 		}
 		default:
 			return 0.0f;
@@ -213,6 +233,9 @@ __device__ inline void bsdfFPdf_base(const MaterialDev &m, V3 wi, V3 wo, V3 &f, 
 			pdf = D * Hr.z * dwhr_dwo;
 			return;
 		}
+		case MTSGPU_BSDF_PHONG:
+			f = bsdfF_base(m, wi, wo); pdf = bsdfPdf_base(m, wi, wo);
+			return;
 		default:
 			return;
 	}
@@ -240,6 +263,26 @@ __device__ inline bool bsdfSampleRough(const MaterialDev &m, V3 wi, float sx, fl
 			if (pdf == 0) return false;
 		} else {
 			sx = (sx - specularSamplingWeight) / diffuseSamplingWeight;
+			wo = squareToHemispherePSA(sx, sy);
+			type = BSDF_DIFFUSE_REFLECTION;
+			bsdfFPdf_base(m, wi, wo, f, pdf);
+		}
+	} else if ((m.type & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_PHONG) {      // phong.cpp:164-234
+		const float exponent = m.p[8], ssw = m.p[9], dsw = m.p[10];
+		if (sx <= ssw) {
+			sx /= ssw;
+			const V3 R = v3(-wi.x, -wi.y, wi.z);
+			const float sinAlpha = sqrtf(1 - mts_pow(sy, 2 / (exponent + 1)));
+			const float cosAlpha = mts_pow(sy, 1 / (exponent + 1));
+			const float phi = (2.0f * MTS_PI) * sx;
+			const V3 localDir = v3(sinAlpha * mts_cos(phi), sinAlpha * mts_sin(phi), cosAlpha);
+			wo = toWorld(makeFrame(R), localDir);
+			type = BSDF_GLOSSY_REFLECTION;
+			if (wo.z <= 0) return false;
+			bsdfFPdf_base(m, wi, wo, f, pdf);
+			if (pdf == 0) return false;
+		} else {
+			sx = (sx - ssw) / dsw;
 			wo = squareToHemispherePSA(sx, sy);
 			type = BSDF_DIFFUSE_REFLECTION;
 			bsdfFPdf_base(m, wi, wo, f, pdf);
@@ -287,6 +330,7 @@ __device__ inline V3 bsdfSample2_base(const MaterialDev &m, V3 wi, float sx, flo
 			type = BSDF_DELTA_REFLECTION;
 			return mp3(m, 0);                               // Mirror::sample(2-arg) forwards to the 3-arg one
 		case MTSGPU_BSDF_MICROFACET:
+		case MTSGPU_BSDF_PHONG:
 		case MTSGPU_BSDF_ROUGHMETAL: {
 			V3 f, ratio; float pdf;
 			return bsdfSampleRough(m, wi, sx, sy, wo, type, f, pdf, ratio) ? ratio : zero;

@@ -144,13 +144,18 @@ private:
 			put(m.p, readConstantTexture(s));
 			m.p[3] = s->readFloat();
 			put(m.p + 4, Spectrum(s)); put(m.p + 7, Spectrum(s));
+		} else if (cls == "Phong") {                  /* phong.cpp:247-257 */
+			m.type = MTSGPU_BSDF_PHONG;
+			put(m.p, readConstantTexture(s)); put(m.p + 3, readConstantTexture(s));
+			m.p[8] = s->readFloat(); m.p[6] = s->readFloat(); m.p[7] = s->readFloat();   /* exponent, kd, ks */
+			m.p[9] = s->readFloat(); m.p[10] = s->readFloat();                            /* sampling weights */
 		} else if (cls == "Dielectric") {             /* dielectric.cpp:88-95 */
 			m.type = MTSGPU_BSDF_DIELECTRIC;
 			m.p[6] = s->readFloat(); m.p[7] = s->readFloat();
 			put(m.p, readConstantTexture(s)); put(m.p + 3, readConstantTexture(s));
 		} else {
 			SLog(EError, "gpupath: BSDF class \"%s\" is outside the supported hot path "
-				"(lambertian, microfacet, mirror, roughmetal, dielectric, twosided)", cls.c_str());
+				"(lambertian, microfacet, mirror, roughmetal, dielectric, phong, twosided)", cls.c_str());
 		}
 		return m;
 	}

@@ -19,7 +19,7 @@ from typing import List, Optional
 
 import numpy as np
 
-MAT_LAMBERTIAN, MAT_MICROFACET, MAT_MIRROR, MAT_ROUGHMETAL, MAT_DIELECTRIC = range(5)
+MAT_LAMBERTIAN, MAT_MICROFACET, MAT_MIRROR, MAT_ROUGHMETAL, MAT_DIELECTRIC, MAT_PHONG = range(6)
 BSDF_TWOSIDED = 0x100     # OR-ed into Material.type: wrapped in the `twosided` adapter (src/bsdfs/twosided.cpp)
 MODE_PATH, MODE_DIRECT = 0, 1
 FILTER_BOX, FILTER_GAUSSIAN = 0, 1
@@ -62,6 +62,18 @@ def roughmetal(specular=(1.0, 1.0, 1.0), alphaB=0.1, ior=(0.37, 0.37, 0.37), k=(
 def dielectric(intIOR=1.5046, extIOR=1.0, reflectance=(1.0, 1.0, 1.0), transmittance=(1.0, 1.0, 1.0)):
     """src/bsdfs/dielectric.cpp:49-60"""
     return _mat(MAT_DIELECTRIC, list(reflectance) + list(transmittance) + [intIOR, extIOR])
+
+
+def phong(diffuse=(0.5, 0.5, 0.5), specular=(0.2, 0.2, 0.2), kd=1.0, ks=1.0, exponent=10.0, specular_sampling_weight=None):
+    """src/bsdfs/phong.cpp:32-99. Stores the values after Phong::configure: energy conservation is the caller's
+    business (the harness passes verifyEnergyConservation=false) and the sampling weights are explicit."""
+    f32 = np.float32
+    if specular_sampling_weight is None:
+        avg = lambda c: f32(f32(f32(f32(c[0]) + f32(c[1])) + f32(c[2])) * f32(1.0 / 3.0))
+        ad, as_ = f32(avg(diffuse) * f32(kd)), f32(avg(specular) * f32(ks))
+        specular_sampling_weight = float(f32(as_ / f32(ad + as_)))
+    ssw = f32(specular_sampling_weight)
+    return _mat(MAT_PHONG, list(diffuse) + list(specular) + [kd, ks, exponent, float(ssw), float(f32(1.0) - ssw)])
 
 
 def twosided(material: Material) -> Material:

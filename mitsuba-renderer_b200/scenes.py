@@ -8,7 +8,7 @@ from __future__ import annotations
 import numpy as np
 
 from .scenefile import (SceneDesc, Shape, Emitter, lambertian, microfacet, mirror, roughmetal,
-                        dielectric, twosided, look_at, MODE_PATH, MODE_DIRECT, FILTER_BOX)
+                        dielectric, twosided, phong, look_at, MODE_PATH, MODE_DIRECT, FILTER_BOX)
 
 F32 = np.float32
 
@@ -353,7 +353,7 @@ def material_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6
     s.emitters.append(Emitter((4.0, 6.0, 9.0), 2.0))
     s.shapes.append(Shape(q[0], q[1], q[2], material=-1, emitter=1))   # emitter without a BSDF
     # a free-standing two-sided panel (seen from both sides) and a one-sided one next to it
-    s.materials += [twosided(lambertian((0.7, 0.6, 0.2))), lambertian((0.7, 0.6, 0.2))]
+    s.materials += [twosided(lambertian((0.7, 0.6, 0.2))), phong((0.4, 0.3, 0.2), (0.3, 0.3, 0.3), 1.0, 1.0, 25.0)]
     pa = quad((3.6, 0.4, 1.2), (4.6, 0.4, 2.2), (4.6, 2.2, 2.2), (3.6, 2.2, 1.2), toward=(10, 1, 10))
     pb = quad((0.6, 3.2, 3.8), (1.6, 3.2, 3.2), (1.6, 4.6, 3.2), (0.6, 4.6, 3.8), toward=(10, 4, 10))
     s.shapes.append(Shape(pa[0], pa[1], pa[2], material=8))

@@ -150,6 +150,16 @@ static ref<BSDF> makeBSDF(const sio::Material &mIn) {
 			p.setFloat("intIOR", m.p[6]);
 			p.setFloat("extIOR", m.p[7]);
 			break;
+		case 5: /* phong: the file holds post-configure values (phong.cpp:79-99) */
+			p = Properties("phong");
+			p.setSpectrum("diffuseReflectance", rgb(m.p));
+			p.setSpectrum("specularReflectance", rgb(m.p + 3));
+			p.setFloat("diffuseAmount", m.p[6]);
+			p.setFloat("specularAmount", m.p[7]);
+			p.setFloat("exponent", m.p[8]);
+			p.setFloat("specularSamplingWeight", m.p[9]);
+			p.setBoolean("verifyEnergyConservation", false);
+			break;
 		default:
 			SLog(EError, "unknown material type %u", m.type);
 	}

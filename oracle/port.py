@@ -171,6 +171,17 @@ def bsdf_f_pdf(mtype, p, wi, wo):
         if wi[2] <= 0 or wo[2] <= 0:
             return zero, F(0)
         return (p[0:3] * INV_PI).astype(F), F(wo[2] * INV_PI)
+    if mtype == 5:      # phong.cpp:104-162
+        if wi[2] <= 0 or wo[2] <= 0:
+            return zero, F(0)
+        kd, ks, ex, ssw, dsw = p[6], p[7], p[8], p[9], p[10]
+        alpha = _dot(np.array([-wi[0], -wi[1], wi[2]], F), wo)
+        with np.errstate(all="ignore"):
+            pw = F(np.power(alpha, ex, dtype=F))
+        spec = F(0) if alpha <= 0 else F(F(F(F(ex + F(2)) * F(0.15915494309189533577)) * pw) * ks)
+        f = ((p[3:6] * spec).astype(F) + (p[0:3] * F(INV_PI * kd)).astype(F)).astype(F)
+        sp = F(0) if alpha <= 0 else F(F(pw * F(ex + F(1.0))) / F(F(2.0) * PI))
+        return f, F(F(ssw * sp) + F(dsw * F(wo[2] * INV_PI)))
     if mtype in (2, 4):  # mirror / dielectric: delta only
         return zero, F(0)
     if wi[2] <= 0 or wo[2] <= 0:
