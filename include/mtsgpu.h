@@ -48,10 +48,16 @@ enum mtsgpu_bsdf_type {
 	MTSGPU_BSDF_ROUGHMETAL = 3, /* src/bsdfs/roughmetal.cpp:33   p[0..2] specularReflectance, p[3] alphaB, p[4..6] ior, p[7..9] k */
 	MTSGPU_BSDF_DIELECTRIC = 4, /* src/bsdfs/dielectric.cpp:47   p[0..2] specularReflectance, p[3..5] specularTransmittance,
 	                               p[6] intIOR, p[7] extIOR */
-	MTSGPU_BSDF_PHONG = 5       /* src/bsdfs/phong.cpp:30        p[0..2] diffuseReflectance, p[3..5] specularReflectance, then the
+	MTSGPU_BSDF_PHONG = 5,      /* src/bsdfs/phong.cpp:30        p[0..2] diffuseReflectance, p[3..5] specularReflectance, then the
 	                               values AFTER Phong::configure (phong.cpp:79-99), as Phong::serialize writes them:
 	                               p[6] diffuseAmount, p[7] specularAmount, p[8] exponent, p[9] specularSamplingWeight,
 	                               p[10] diffuseSamplingWeight */
+	MTSGPU_BSDF_ROUGHGLASS = 6  /* src/bsdfs/roughglass.cpp:81   p[0..2] specularReflectance, p[3..5] specularTransmittance,
+	                               p[6] value of the constant alpha texture as RoughGlass::serialize writes it (for the
+	                               phong distribution that is the exponent 2/alpha^2 - 2, roughglass.cpp:132-138),
+	                               p[7] intIOR, p[8] extIOR, p[9] distribution: 0 beckmann, 1 phong, 2 ggx
+	                               (roughglass.cpp:84-91); p[10] is ignored by the library (scene files keep the
+	                               user-facing roughness of a phong distribution there for the oracle harness) */
 };
 
 /* OR-ed into mtsgpu_material.type: the BRDF is wrapped in the `twosided` adapter (src/bsdfs/twosided.cpp:36-143),

@@ -4,6 +4,7 @@
 //   lambertian  src/bsdfs/lambertian.cpp:95-126      mirror      src/bsdfs/mirror.cpp:61-94
 //   microfacet  src/bsdfs/microfacet.cpp:95-269      roughmetal  src/bsdfs/roughmetal.cpp:75-167
 //   dielectric  src/bsdfs/dielectric.cpp:101-290     base 3-arg fallback src/librender/bsdf.cpp:37-48
+//   phong       src/bsdfs/phong.cpp:104-234          roughglass  src/bsdfs/roughglass.cpp:209-598
 // All directions are in the local shading frame (wi.z = cos theta). Queries use the full type
 // mask, component = -1 and quantity = ERadiance, which is what path.cpp / direct.cpp pass.
 #pragma once
@@ -14,8 +15,9 @@
 #define BSDF_DELTA_REFLECTION    0x0004u
 #define BSDF_DELTA_TRANSMISSION  0x0008u
 #define BSDF_GLOSSY_REFLECTION   0x0010u
+#define BSDF_GLOSSY_TRANSMISSION 0x0020u
 #define BSDF_DELTA               (BSDF_DELTA_REFLECTION | BSDF_DELTA_TRANSMISSION)
-#define BSDF_TRANSMISSION        (0x0002u | BSDF_DELTA_TRANSMISSION | 0x0020u)
+#define BSDF_TRANSMISSION        (0x0002u | BSDF_DELTA_TRANSMISSION | BSDF_GLOSSY_TRANSMISSION)
 
 // ---- src/libcore/util.cpp helpers ---------------------------------------------------------------
 __device__ inline V3 sphericalDirection(float theta, float phi) {           // util.cpp:543-550
@@ -104,6 +106,154 @@ __device__ inline V3 reflectAbout(V3 wi, V3 n) {                             // 
 
 __device__ inline V3 mp3(const MaterialDev &m, int o) { return v3(m.p[o], m.p[o + 1], m.p[o + 2]); }
 
+
+// ---- roughglass (src/bsdfs/roughglass.cpp): Walter et al. microfacet refraction, three distributions ---------
+// p[0..2] specularReflectance, p[3..5] specularTransmittance, p[6] value of the alpha texture (for the Phong
+// distribution: the exponent the constructor derives, roughglass.cpp:132-138), p[7] intIOR, p[8] extIOR,
+// p[9] distribution (0 beckmann, 1 phong, 2 ggx). bRec.sampler is NULL in path.cpp / direct.cpp
+// (records.inl:24-37), so the branch that recycles the 2D sample is the one that runs.
+__device__ inline float rgSignum(float v) { return (v < 0) ? -1.0f : 1.0f; }                 // roughglass.cpp:198-200
+
+__device__ inline float rgAlpha(const MaterialDev &m) {          // ConstantFloatTexture -> Spectrum::average (spectrum.h:299-304)
+	float result = 0.0f;
+	result += m.p[6]; result += m.p[6]; result += m.p[6];
+	return result * (1.0f / 3);
+}
+
+__device__ inline float rgEvalD(V3 m, float alpha, int distr) {                                // roughglass.cpp:209-252
+	if (m.z <= 0) return 0.0f;
+	float result;
+	if (distr == 0) {
+		const float ex = frameTanTheta(m) / alpha;
+		result = mts_exp(-(ex * ex)) / (MTS_PI * alpha * alpha * mts_pow(m.z, 4.0f));
+	} else if (distr == 1) {
+		result = (alpha + 2) * MTS_INV_TWOPI * mts_pow(m.z, alpha);
+	} else {
+		const float tanTheta = frameTanTheta(m), cosTheta = m.z;
+		const float root = alpha / (cosTheta * cosTheta * (alpha * alpha + tanTheta * tanTheta));
+		result = MTS_INV_PI * (root * root);
+	}
+	if ((double) result < 1e-40) result = 0;
+	return result;
+}
+
+__device__ inline V3 rgSampleD(float sx, float sy, float alpha, int distr) {                    // roughglass.cpp:261-288
+	const float phiM = (2.0f * MTS_PI) * sy;
+	float thetaM;
+	if (distr == 0) thetaM = mts_atan(sqrtf(-alpha * alpha * mts_log(1.0f - sx)));
+	else if (distr == 1) thetaM = mts_acos(mts_pow(sx, (float) 1 / (alpha + 2)));
+	else thetaM = mts_atan(alpha * sqrtf(sx) / sqrtf(1.0f - sx));
+	return sphericalDirection(thetaM, phiM);
+}
+
+__device__ inline float rgSmithG1(V3 v, V3 m, float alpha, int distr) {                         // roughglass.cpp:298-340
+	const float tanTheta = fabsf(frameTanTheta(v));
+	if (tanTheta == 0.0f) return 1.0f;
+	if (dot(v, m) * v.z <= 0) return 0.0f;
+	if (distr == 2) {
+		const float root = alpha * tanTheta;
+		return 2.0f / (1.0f + sqrtf(1.0f + root * root));
+	}
+	if (distr == 1) alpha = sqrtf(0.5f * alpha + 1) / tanTheta;
+	const float a = 1.0f / (alpha * tanTheta);
+	const float aSqr = a * a;
+	if (a >= 1.6f) return 1.0f;
+	return (3.535f * a + 2.181f * aSqr) / (1.0f + 2.276f * a + 2.577f * aSqr);
+}
+
+// half-vector of a reflection / transmission pair (roughglass.cpp:356-376)
+__device__ inline V3 rgHalf(V3 wi, V3 wo, bool reflect, float etaI, float etaT, float extIOR, float intIOR) {
+	if (reflect) return normalize(wo + wi) * rgSignum(wo.z);
+	return normalize(wi * etaI + wo * etaT) * (extIOR > intIOR ? 1.0f : -1.0f);
+}
+
+__device__ inline V3 roughglassF(const MaterialDev &m, V3 wi, V3 wo) {                         // roughglass.cpp:345-412
+	const float intIOR = m.p[7], extIOR = m.p[8]; const int distr = (int) m.p[9];
+	const bool reflect = wi.z * wo.z > 0;
+	float etaI = extIOR, etaT = intIOR;
+	if (wi.z < 0) { const float t = etaI; etaI = etaT; etaT = t; }
+	const V3 H = rgHalf(wi, wo, reflect, etaI, etaT, extIOR, intIOR);
+	const float alpha = rgAlpha(m);
+	const float D = rgEvalD(H, alpha, distr);
+	if (D == 0) return v3(0, 0, 0);
+	const float F = fresnel(dot(wi, H), extIOR, intIOR);
+	const float G = rgSmithG1(wi, H, alpha, distr) * rgSmithG1(wo, H, alpha, distr);
+	if (reflect) {
+		const float value = F * D * G / (4.0f * wi.z * wo.z);
+		return mp3(m, 0) * value;
+	}
+	const float sqrtDenom = etaI * dot(wi, H) + etaT * dot(wo, H);
+	float value = ((1 - F) * D * G * etaT * etaT * dot(wi, H) * dot(wo, H)) / (wi.z * wo.z * sqrtDenom * sqrtDenom);
+	value *= (etaI * etaI) / (etaT * etaT);            // quantity == ERadiance
+	return mp3(m, 3) * fabsf(value);
+}
+
+__device__ inline float rgClampedFresnel(const MaterialDev &m, V3 wi) {
+	return fminf(0.9f, fmaxf(0.1f, fresnel(wi.z, m.p[8], m.p[7])));
+}
+
+__device__ inline float roughglassPdf(const MaterialDev &m, V3 wi, V3 wo) {                    // roughglass.cpp:414-488
+	const float intIOR = m.p[7], extIOR = m.p[8]; const int distr = (int) m.p[9];
+	const bool reflect = wi.z * wo.z > 0;
+	float etaI = extIOR, etaT = intIOR;
+	if (wi.z < 0) { const float t = etaI; etaI = etaT; etaT = t; }
+	const V3 H = rgHalf(wi, wo, reflect, etaI, etaT, extIOR, intIOR);
+	float dwh_dwo;
+	if (reflect) {
+		dwh_dwo = 1.0f / (4.0f * dot(wo, H));
+	} else {
+		const float sqrtDenom = etaI * dot(wi, H) + etaT * dot(wo, H);
+		dwh_dwo = (etaT * etaT * dot(wo, H)) / (sqrtDenom * sqrtDenom);
+	}
+	float alpha = rgAlpha(m);
+	alpha = alpha * (1.2f - 0.2f * sqrtf(fabsf(wi.z)));
+	float prob = rgEvalD(H, alpha, distr);
+	const float F = rgClampedFresnel(m, wi);
+	prob *= reflect ? F : (1 - F);
+	return fabsf(prob * H.z * dwh_dwo);
+}
+
+// 2-argument sample (roughglass.cpp:490-598): returns the sampling weight; zero => no sample
+__device__ inline V3 roughglassSample2(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, uint32_t &type) {
+	const V3 zero = v3(0, 0, 0);
+	const float intIOR = m.p[7], extIOR = m.p[8]; const int distr = (int) m.p[9];
+	bool choseReflection = true;
+	float sampleF = rgClampedFresnel(m, wi);
+	if (sx < sampleF) {
+		sx /= sampleF;
+	} else {
+		sx = (sx - sampleF) / (1 - sampleF);
+		choseReflection = false;
+	}
+	const float alpha = rgAlpha(m);
+	const float sampleAlpha = alpha * (1.2f - 0.2f * sqrtf(fabsf(wi.z)));
+	const V3 mN = rgSampleD(sx, sy, sampleAlpha, distr);
+	V3 result;
+	if (choseReflection) {
+		wo = mN * (2 * dot(wi, mN)) - wi;
+		type = BSDF_GLOSSY_REFLECTION;
+		if (wi.z * wo.z <= 0) return zero;
+		result = mp3(m, 0);
+	} else {
+		float etaI = extIOR, etaT = intIOR;
+		if (wi.z < 0) { const float t = etaI; etaI = etaT; etaT = t; }
+		const float eta = etaI / etaT, c = dot(wi, mN);                     // refract(), roughglass.cpp:181-196
+		const float cosThetaTSqr = 1 + eta * eta * (c * c - 1);
+		if (cosThetaTSqr < 0) return zero;
+		wo = mN * (eta * c - rgSignum(wi.z) * sqrtf(cosThetaTSqr)) - wi * eta;
+		type = BSDF_GLOSSY_TRANSMISSION;
+		if (wi.z * wo.z >= 0) return zero;
+		result = mp3(m, 3) * ((etaI * etaI) / (etaT * etaT));
+	}
+	float numerator = rgEvalD(mN, alpha, distr) * rgSmithG1(wi, mN, alpha, distr) * rgSmithG1(wo, mN, alpha, distr) * dot(wi, mN);
+	float denominator = rgEvalD(mN, sampleAlpha, distr) * mN.z * wi.z * wo.z;
+	float F = fresnel(dot(wi, mN), extIOR, intIOR);
+	if (!choseReflection) { sampleF = 1 - sampleF; F = 1 - F; }
+	numerator *= F;
+	denominator *= sampleF;
+	return result * fabsf(numerator / denominator);
+}
+
 // ---- f ---------------------------------------------------------------------------------------------
 __device__ inline V3 bsdfF_base(const MaterialDev &m, V3 wi, V3 wo) {
 	const V3 zero = v3(0, 0, 0);
@@ -144,6 +294,8 @@ __device__ inline V3 bsdfF_base(const MaterialDev &m, V3 wi, V3 wo) {
 			result = result + mp3(m, 0) * (MTS_INV_PI * kd);
 			return result;
 		}
+		case MTSGPU_BSDF_ROUGHGLASS:
+			return roughglassF(m, wi, wo);
 		default:   // mirror, dielectric: delta lobes only
 			return zero;
 	}
@@ -186,6 +338,8 @@ __device__ inline float bsdfPdf_base(const MaterialDev &m, V3 wi, V3 wo) {
 			if (alpha <= 0) specPdf = 0;
 			return m.p[9] * specPdf + m.p[10] * (wo.z * MTS_INV_PI);
 		}
+		case MTSGPU_BSDF_ROUGHGLASS:
+			return roughglassPdf(m, wi, wo);
 		default:
 			return 0.0f;
 	}
@@ -234,6 +388,7 @@ __device__ inline void bsdfFPdf_base(const MaterialDev &m, V3 wi, V3 wo, V3 &f, 
 			return;
 		}
 		case MTSGPU_BSDF_PHONG:
+		case MTSGPU_BSDF_ROUGHGLASS:
 			f = bsdfF_base(m, wi, wo); pdf = bsdfPdf_base(m, wi, wo);
 			return;
 		default:
@@ -335,6 +490,8 @@ __device__ inline V3 bsdfSample2_base(const MaterialDev &m, V3 wi, float sx, flo
 			V3 f, ratio; float pdf;
 			return bsdfSampleRough(m, wi, sx, sy, wo, type, f, pdf, ratio) ? ratio : zero;
 		}
+		case MTSGPU_BSDF_ROUGHGLASS:
+			return roughglassSample2(m, wi, sx, sy, wo, type);
 		case MTSGPU_BSDF_DIELECTRIC: {
 			float Fr, eta, cosThetaT;
 			dielectricSetup(m, wi, Fr, eta, cosThetaT);
@@ -382,6 +539,13 @@ __device__ inline V3 bsdfSample3_base(const MaterialDev &m, V3 wi, float sx, flo
 				pdf = (1 - Fr) * fabsf(wo.z);
 				return (mp3(m, 3) * (1 - Fr)) * (eta * eta);
 			}
+		}
+		case MTSGPU_BSDF_ROUGHGLASS: {
+			// RoughGlass's 3-argument sample takes the pdf by value (roughglass.cpp:619) and so never overrides
+			// the virtual: the base fallback runs (bsdf.cpp:37-48)
+			if (isZero(roughglassSample2(m, wi, sx, sy, wo, type))) { pdf = 0.0f; return zero; }
+			pdf = roughglassPdf(m, wi, wo);
+			return roughglassF(m, wi, wo);
 		}
 		default: {
 			// BSDF::sample(bRec, pdf, sample) fallback (bsdf.cpp:37-48): 2-arg sample, then pdf() and f()

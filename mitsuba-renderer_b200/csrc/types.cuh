@@ -84,6 +84,7 @@ struct DeviceScene {
 __device__ __forceinline__ float mts_sin(float x) { return (float) sin((double) x); }
 __device__ __forceinline__ float mts_cos(float x) { return (float) cos((double) x); }
 __device__ __forceinline__ float mts_atan(float x) { return (float) atan((double) x); }
+__device__ __forceinline__ float mts_acos(float x) { return (float) acos((double) x); }
 __device__ __forceinline__ float mts_log(float x) { return (float) log((double) x); }
 __device__ __forceinline__ float mts_exp(float x) { return (float) exp((double) x); }
 __device__ __forceinline__ float mts_pow(float x, float y) { return (float) pow((double) x, (double) y); }

@@ -125,7 +125,8 @@ private:
 				SLog(EError, "gpupath: TwoSidedBRDF without a nested BRDF");
 			const std::string nested = s->readString();
 			m = decodePayload(nested, s);
-			if ((m.type & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_DIELECTRIC || (m.type & MTSGPU_BSDF_TWOSIDED))
+			if ((m.type & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_DIELECTRIC || (m.type & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_ROUGHGLASS
+					|| (m.type & MTSGPU_BSDF_TWOSIDED))
 				SLog(EError, "gpupath: TwoSidedBRDF around \"%s\" is not supported", nested.c_str());
 			m.type |= MTSGPU_BSDF_TWOSIDED;
 		} else if (cls == "Lambertian") {             /* lambertian.cpp:137-141 */
@@ -149,13 +150,21 @@ private:
 			put(m.p, readConstantTexture(s)); put(m.p + 3, readConstantTexture(s));
 			m.p[8] = s->readFloat(); m.p[6] = s->readFloat(); m.p[7] = s->readFloat();   /* exponent, kd, ks */
 			m.p[9] = s->readFloat(); m.p[10] = s->readFloat();                            /* sampling weights */
+		} else if (cls == "RoughGlass") {             /* roughglass.cpp:735-744 */
+			m.type = MTSGPU_BSDF_ROUGHGLASS;
+			m.p[9] = (float) s->readInt();
+			if (s->readUInt() == 0 || s->readString() != "ConstantFloatTexture" || s->readUInt() != 0)
+				SLog(EError, "gpupath: RoughGlass: only a constant alpha is inside the supported hot path");
+			m.p[6] = s->readFloat();                   /* ConstantFloatTexture::serialize (texture.cpp:100-103) */
+			put(m.p, readConstantTexture(s)); put(m.p + 3, readConstantTexture(s));
+			m.p[7] = s->readFloat(); m.p[8] = s->readFloat();
 		} else if (cls == "Dielectric") {             /* dielectric.cpp:88-95 */
 			m.type = MTSGPU_BSDF_DIELECTRIC;
 			m.p[6] = s->readFloat(); m.p[7] = s->readFloat();
 			put(m.p, readConstantTexture(s)); put(m.p + 3, readConstantTexture(s));
 		} else {
 			SLog(EError, "gpupath: BSDF class \"%s\" is outside the supported hot path "
-				"(lambertian, microfacet, mirror, roughmetal, dielectric, phong, twosided)", cls.c_str());
+				"(lambertian, microfacet, mirror, roughmetal, dielectric, phong, roughglass, twosided)", cls.c_str());
 		}
 		return m;
 	}

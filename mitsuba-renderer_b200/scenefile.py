@@ -19,7 +19,7 @@ from typing import List, Optional
 
 import numpy as np
 
-MAT_LAMBERTIAN, MAT_MICROFACET, MAT_MIRROR, MAT_ROUGHMETAL, MAT_DIELECTRIC, MAT_PHONG = range(6)
+MAT_LAMBERTIAN, MAT_MICROFACET, MAT_MIRROR, MAT_ROUGHMETAL, MAT_DIELECTRIC, MAT_PHONG, MAT_ROUGHGLASS = range(7)
 BSDF_TWOSIDED = 0x100     # OR-ed into Material.type: wrapped in the `twosided` adapter (src/bsdfs/twosided.cpp)
 MODE_PATH, MODE_DIRECT = 0, 1
 FILTER_BOX, FILTER_GAUSSIAN = 0, 1
@@ -74,6 +74,22 @@ def phong(diffuse=(0.5, 0.5, 0.5), specular=(0.2, 0.2, 0.2), kd=1.0, ks=1.0, exp
         specular_sampling_weight = float(f32(as_ / f32(ad + as_)))
     ssw = f32(specular_sampling_weight)
     return _mat(MAT_PHONG, list(diffuse) + list(specular) + [kd, ks, exponent, float(ssw), float(f32(1.0) - ssw)])
+
+
+ROUGHGLASS_DISTRIBUTIONS = {"beckmann": 0, "phong": 1, "ggx": 2}
+
+
+def roughglass(specular_reflectance=(1, 1, 1), specular_transmittance=(1, 1, 1), alpha=0.1, int_ior=1.5046, ext_ior=1.0,
+               distribution="beckmann"):
+    """src/bsdfs/roughglass.cpp:93-146. p[6] is the value the constructor stores in the alpha texture: the
+    roughness itself, or for the phong distribution the exponent 2/alpha^2 - 2 (p[10] then keeps the roughness)."""
+    f32 = np.float32
+    d = ROUGHGLASS_DISTRIBUTIONS[distribution]
+    stored = f32(alpha)
+    if d == 1:
+        stored = f32(f32(f32(2) / f32(f32(alpha) * f32(alpha))) - f32(2))
+    return _mat(MAT_ROUGHGLASS, list(specular_reflectance) + list(specular_transmittance)
+                + [float(stored), int_ior, ext_ior, float(d), float(f32(alpha))])
 
 
 def twosided(material: Material) -> Material:

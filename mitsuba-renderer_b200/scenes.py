@@ -8,7 +8,7 @@ from __future__ import annotations
 import numpy as np
 
 from .scenefile import (SceneDesc, Shape, Emitter, lambertian, microfacet, mirror, roughmetal,
-                        dielectric, twosided, phong, look_at, MODE_PATH, MODE_DIRECT, FILTER_BOX)
+                        dielectric, twosided, phong, roughglass, look_at, MODE_PATH, MODE_DIRECT, FILTER_BOX)
 
 F32 = np.float32
 
@@ -339,7 +339,7 @@ def path_scene(terrain_cells=2000, n_spheres=6250, width=1920, height=1080, spp=
 # small scenes for tests
 # --------------------------------------------------------------------------------------------
 def material_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6) -> SceneDesc:
-    """Small box scene exercising all five BSDFs, a BSDF-less emitter mesh and two lights."""
+    """Small box scene exercising every supported BSDF, a BSDF-less emitter mesh and two lights."""
     s = cornell_box(width, height, spp, max_depth)
     s.materials += [microfacet((0.5, 0.3, 0.2), (1, 1, 1), 0.5, 0.5, 0.1), mirror((0.8, 0.8, 0.8)),
                     roughmetal((1, 1, 1), 0.15), dielectric()]
@@ -358,5 +358,9 @@ def material_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6
     pb = quad((0.6, 3.2, 3.8), (1.6, 3.2, 3.2), (1.6, 4.6, 3.2), (0.6, 4.6, 3.8), toward=(10, 4, 10))
     s.shapes.append(Shape(pa[0], pa[1], pa[2], material=8))
     s.shapes.append(Shape(pb[0], pb[1], pb[2], material=9))
+    # a rough glass ball (GGX) in front
+    s.materials.append(roughglass((1, 1, 1), (0.9, 1.0, 0.9), 0.2, 1.5046, 1.0, "ggx"))
+    c2 = np.array([4.1, 1.3, 4.3])
+    s.shapes.append(Shape((v * 0.55 + c2).astype(F32), f.astype(np.uint32), v.astype(F32), material=10))
     s.mode = mode
     return s

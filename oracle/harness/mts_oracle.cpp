@@ -160,6 +160,19 @@ static ref<BSDF> makeBSDF(const sio::Material &mIn) {
 			p.setFloat("specularSamplingWeight", m.p[9]);
 			p.setBoolean("verifyEnergyConservation", false);
 			break;
+		case 6: { /* roughglass: p[6] is the stored alpha-texture value; the phong distribution derives it from
+		             the user-facing roughness kept in p[10] (roughglass.cpp:132-138) */
+			static const char *distr[3] = { "beckmann", "phong", "ggx" };
+			const int d = (int) m.p[9];
+			p = Properties("roughglass");
+			p.setSpectrum("specularReflectance", rgb(m.p));
+			p.setSpectrum("specularTransmittance", rgb(m.p + 3));
+			p.setFloat("alpha", d == 1 ? m.p[10] : m.p[6]);
+			p.setFloat("intIOR", m.p[7]);
+			p.setFloat("extIOR", m.p[8]);
+			p.setString("distribution", distr[d < 0 || d > 2 ? 0 : d]);
+			break;
+		}
 		default:
 			SLog(EError, "unknown material type %u", m.type);
 	}

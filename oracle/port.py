@@ -159,6 +159,79 @@ def _normalize(v):
     return (v * r).astype(F)
 
 
+def _rg_eval_d(m, alpha, distr):                      # roughglass.cpp:209-252
+    if m[2] <= 0:
+        return F(0)
+    with np.errstate(all="ignore"):
+        if distr == 0:
+            r = _beckmann_d(m, alpha)
+        elif distr == 1:
+            r = F(F(F(alpha + F(2)) * F(0.15915494309189533577)) * F(np.power(m[2], alpha, dtype=F)))
+        else:
+            tt, ct = _tan_theta(m), m[2]
+            root = F(alpha / F(F(ct * ct) * F(F(alpha * alpha) + F(tt * tt))))
+            r = F(INV_PI * F(root * root))
+    return F(0) if float(r) < 1e-40 else r
+
+
+def _rg_g1(v, m, alpha, distr):                        # roughglass.cpp:298-340
+    tt = abs(_tan_theta(v))
+    if tt == 0:
+        return F(1)
+    if F(_dot(v, m) * v[2]) <= 0:
+        return F(0)
+    if distr == 2:
+        root = F(alpha * tt)
+        return F(F(2.0) / F(F(1.0) + np.sqrt(F(F(1.0) + F(root * root))).astype(F)))
+    if distr == 1:
+        alpha = F(np.sqrt(F(F(F(0.5) * alpha) + F(1))).astype(F) / tt)
+    a = F(F(1.0) / F(alpha * tt))
+    if a >= 1.6:
+        return F(1)
+    a2 = F(a * a)
+    return F(F(F(F(3.535) * a) + F(F(2.181) * a2)) / F(F(F(1.0) + F(F(2.276) * a)) + F(F(2.577) * a2)))
+
+
+def _roughglass_f_pdf(p, wi, wo):
+    intI, extI, distr = p[7], p[8], int(p[9])
+    alpha = F(F(F(F(F(0) + p[6]) + p[6]) + p[6]) * F(F(1.0) / F(3)))
+    reflect = F(wi[2] * wo[2]) > 0
+    etaI, etaT = (extI, intI) if wi[2] >= 0 else (intI, extI)
+    if reflect:
+        H = (_normalize((wo + wi).astype(F)) * (F(-1) if wo[2] < 0 else F(1))).astype(F)
+    else:
+        H = (_normalize(((wi * etaI).astype(F) + (wo * etaT).astype(F)).astype(F)) * (F(1) if extI > intI else F(-1))).astype(F)
+    wiH, woH = _dot(wi, H), _dot(wo, H)
+    sqrt_denom = F(F(etaI * wiH) + F(etaT * woH))
+    with np.errstate(all="ignore"):
+        # ---- f
+        D = _rg_eval_d(H, alpha, distr)
+        if D == 0:
+            f = np.zeros(3, F)
+        else:
+            Fr = _fresnel(wiH, extI, intI)
+            G = F(_rg_g1(wi, H, alpha, distr) * _rg_g1(wo, H, alpha, distr))
+            if reflect:
+                value = F(F(F(Fr * D) * G) / F(F(F(4.0) * wi[2]) * wo[2]))
+                f = (p[0:3] * value).astype(F)
+            else:
+                num = F(F(F(F(F(F(F(1) - Fr) * D) * G) * etaT) * etaT) * wiH) * woH
+                value = F(F(num) / F(F(F(wi[2] * wo[2]) * sqrt_denom) * sqrt_denom))
+                value = F(value * F(F(etaI * etaI) / F(etaT * etaT)))
+                f = (p[3:6] * abs(value)).astype(F)
+        # ---- pdf
+        if reflect:
+            dwh = F(F(1.0) / F(F(4.0) * woH))
+        else:
+            dwh = F(F(F(etaT * etaT) * woH) / F(sqrt_denom * sqrt_denom))
+        sa = F(alpha * F(F(1.2) - F(F(0.2) * np.sqrt(abs(wi[2])).astype(F))))
+        prob = _rg_eval_d(H, sa, distr)
+        Fc = min(F(0.9), max(F(0.1), _fresnel(wi[2], extI, intI)))
+        prob = F(prob * (Fc if reflect else F(F(1) - Fc)))
+        pdf = abs(F(F(prob * H[2]) * dwh))
+    return f, F(pdf)
+
+
 def bsdf_f_pdf(mtype, p, wi, wo):
     """f(wi,wo) [3] and pdf(wi,wo) of one material (type + 16-float block, include/mtsgpu.h layout)."""
     wi, wo, p = np.asarray(wi, F).copy(), np.asarray(wo, F).copy(), np.asarray(p, F)
@@ -182,6 +255,8 @@ def bsdf_f_pdf(mtype, p, wi, wo):
         f = ((p[3:6] * spec).astype(F) + (p[0:3] * F(INV_PI * kd)).astype(F)).astype(F)
         sp = F(0) if alpha <= 0 else F(F(pw * F(ex + F(1.0))) / F(F(2.0) * PI))
         return f, F(F(ssw * sp) + F(dsw * F(wo[2] * INV_PI)))
+    if mtype == 6:      # roughglass.cpp:345-488
+        return _roughglass_f_pdf(p, wi, wo)
     if mtype in (2, 4):  # mirror / dielectric: delta only
         return zero, F(0)
     if wi[2] <= 0 or wo[2] <= 0:

@@ -52,7 +52,10 @@ def bsdf_scene():
                    scenefile.twosided(scenefile.roughmetal((1, 1, 1), 0.2)),
                    scenefile.twosided(scenefile.microfacet((0.3, 0.3, 0.3), (1, 1, 1), 1.0, 1.0, 0.15)),
                    scenefile.phong((0.5, 0.4, 0.3), (0.2, 0.3, 0.4), 1.0, 1.0, 10.0),                # phong.cpp defaults
-                   scenefile.twosided(scenefile.phong((0.3, 0.3, 0.3), (0.6, 0.6, 0.6), 0.9, 0.8, 60.0, 0.7))]
+                   scenefile.twosided(scenefile.phong((0.3, 0.3, 0.3), (0.6, 0.6, 0.6), 0.9, 0.8, 60.0, 0.7)),
+                   scenefile.roughglass((0.9, 1.0, 0.8), (0.8, 0.9, 1.0), 0.1, 1.5046, 1.0, "beckmann"),  # roughglass.cpp defaults
+                   scenefile.roughglass((1, 1, 1), (1, 1, 1), 0.3, 1.33, 1.0, "ggx"),
+                   scenefile.roughglass((1, 1, 1), (0.9, 0.9, 0.9), 0.25, 1.0, 1.5, "phong")]
     for sh in s.shapes:
         sh.material = 0
     return s
