@@ -237,6 +237,40 @@ MTSGPU_API int mtsgpu_film_splat(mtsgpu_ctx *ctx, const float *samples, size_t n
 #define MTSGPU_STATIC_SCRATCH_BYTES (4u << 20)
 MTSGPU_API int mtsgpu_film_splat_static(mtsgpu_ctx *ctx, const float *samples, size_t n, float *outFilm);
 
+/* ---- `.serialized` triangle-mesh files (host side; the data format in front of the path) ------
+ * A mesh as the reference's `serialized` shape would hand it to the kd-tree: file read
+ * (TriMesh::TriMesh(Stream *, int), src/librender/trimesh.cpp:156-237), object-to-world transform and winding
+ * (SerializedMesh::SerializedMesh, src/shapes/serialized.cpp:30-91), vertex normals (TriMesh::computeNormals,
+ * src/librender/trimesh.cpp:472-540). Arrays are malloc'ed by the library and released by
+ * mtsgpu_serialized_free. These three calls need no GPU and no context; errors are reported through
+ * mtsgpu_last_error(NULL). */
+typedef struct mtsgpu_mesh_data {
+	uint32_t nVert, nTri;
+	uint32_t flags;        /* the file's flag word (trimesh.cpp:72-80): 1 normals, 2 texcoords, 8 colors, 0x10 face normals,
+	                          0x1000 / 0x2000 single / double precision */
+	float *positions;      /* 3 per vertex */
+	float *normals;        /* 3 per vertex, NULL when the mesh is shaded with face normals */
+	float *texcoords;      /* 2 per vertex or NULL */
+	float *colors;         /* 3 per vertex or NULL */
+	uint32_t *triangles;   /* 3 per triangle */
+} mtsgpu_mesh_data;
+/* Number of meshes in the file: the trailing table written by the converter (src/converter/converter.cpp:293-296). */
+MTSGPU_API int mtsgpu_serialized_count(const char *path, int *count);
+/* toWorld / toWorldInv: row-major 4x4 or NULL (identity; a missing inverse is computed); faceNormals and
+ * flipNormals are the shape properties of the same names (src/librender/trimesh.cpp:62-63). */
+MTSGPU_API int mtsgpu_serialized_load(const char *path, int shapeIndex, const float *toWorld, const float *toWorldInv,
+                                      int faceNormals, int flipNormals, mtsgpu_mesh_data *out);
+/* Releases the arrays of a loaded mesh (what TriMesh::~TriMesh does, src/librender/trimesh.cpp:239-252). */
+MTSGPU_API void mtsgpu_serialized_free(mtsgpu_mesh_data *mesh);
+/* Writer: TriMesh::serialize(Stream *) per mesh (src/librender/trimesh.cpp:748-790, single precision, zlib) followed
+ * by the offset table; the reference's loader reads the result. */
+MTSGPU_API int mtsgpu_serialized_save(const char *path, const mtsgpu_mesh_data *meshes, int count);
+/* mtsgpu_serialized_load + mtsgpu_upload_mesh: file to GPU scene without a detour through the caller
+ * (the `serialized` shape inside a scene, src/shapes/serialized.cpp:30-91). */
+MTSGPU_API int mtsgpu_upload_serialized(mtsgpu_ctx *ctx, int shapeIndex, const char *path, int fileShapeIndex,
+                                        const float *toWorld, const float *toWorldInv, int faceNormals, int flipNormals,
+                                        int materialId, int emitterId);
+
 /* Closest-hit query that also fills the Intersection record (fillIntersectionRecord<true>,
  * skdtree.h:352-432): out rows of 12 floats {p, geoFrame.n, shFrame.n, wi}; zeros on a miss. */
 MTSGPU_API int mtsgpu_intersect_full(mtsgpu_ctx *ctx, const float *rays, size_t n, mtsgpu_hit *hits, float *out);

@@ -26,7 +26,8 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_render", "mtsgpu_render_device", "mtsgpu_trace", "mtsgpu_trace_device", "mtsgpu_bsdf_eval",
     "mtsgpu_emitter_sample", "mtsgpu_camera_rays", "mtsgpu_film_splat", "mtsgpu_intersect_full",
     "mtsgpu_get_triaccel", "mtsgpu_accel_info_get", "mtsgpu_set_counters", "mtsgpu_get_counters",
-    "mtsgpu_film_splat_static", "mtsgpu_render_multi",
+    "mtsgpu_film_splat_static", "mtsgpu_render_multi", "mtsgpu_serialized_count", "mtsgpu_serialized_load",
+    "mtsgpu_serialized_free", "mtsgpu_serialized_save", "mtsgpu_upload_serialized",
 ]
 STATIC_SCRATCH_BYTES = 4 << 20
 
@@ -114,7 +115,7 @@ def load_library(path: Optional[str] = None):
     lib.mtsgpu_get_counters.argtypes = [vp, C.POINTER(TraceCounters)]
     for name in EXPORTED_SYMBOLS:
         fn = getattr(lib, name)
-        if name not in ("mtsgpu_destroy", "mtsgpu_last_error", "mtsgpu_version"):
+        if name not in ("mtsgpu_destroy", "mtsgpu_last_error", "mtsgpu_version", "mtsgpu_serialized_free"):
             fn.restype = C.c_int
     if path == LIB_PATH:
         _lib = lib

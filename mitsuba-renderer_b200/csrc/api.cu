@@ -15,6 +15,14 @@ int setError(mtsgpu_ctx *ctx, int code, const char *fmt, ...) {
 
 static thread_local std::string g_createError;
 
+void setGlobalError(const char *fmt, ...) {      // context-free calls (mtsgpu_create, mtsgpu_serialized_*)
+	char buf[1024];
+	va_list ap; va_start(ap, fmt);
+	vsnprintf(buf, sizeof(buf), fmt, ap);
+	va_end(ap);
+	g_createError = buf;
+}
+
 extern "C" {
 
 const char *mtsgpu_version(void) { return "mtsgpu 0.1 (sm_100a)"; }

@@ -229,8 +229,58 @@ static int cmdRender(int argc, char **argv) {
 	return 0;
 }
 
+/* Load one mesh of a `.serialized` file through the reference's `serialized` shape plugin
+ * (src/shapes/serialized.cpp) and dump what it hands to the kd-tree after TriMesh::configure. */
+static int cmdMesh(int argc, char **argv) {
+	if (argc < 5) { std::cerr << "mesh FILE SHAPEINDEX OUT [faceNormals flipNormals [16 x toWorld]]\n"; return 1; }
+	Properties p("serialized");
+	p.setString("filename", argv[2]);
+	p.setInteger("shapeIndex", atoi(argv[3]));
+	if (argc > 6) { p.setBoolean("faceNormals", atoi(argv[5]) != 0); p.setBoolean("flipNormals", atoi(argv[6]) != 0); }
+	if (argc >= 23) {
+		Matrix4x4 m;
+		for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) m.m[i][j] = (Float) atof(argv[7 + 4 * i + j]);
+		p.setTransform("toWorld", Transform(m));
+	}
+	ref<TriMesh> mesh = static_cast<TriMesh *>(PluginManager::getInstance()->createObject(MTS_CLASS(Shape), p));
+	mesh->configure();
+	FILE *f = fopen(argv[4], "wb");
+	if (!f) { std::cerr << "cannot write output\n"; return 1; }
+	const uint32_t hdr[4] = { (uint32_t) mesh->getVertexCount(), (uint32_t) mesh->getTriangleCount(),
+		mesh->hasVertexNormals() ? 1u : 0u, mesh->hasVertexTexcoords() ? 1u : 0u };
+	fwrite(hdr, 4, 4, f);
+	fwrite(mesh->getVertexPositions(), sizeof(Point), hdr[0], f);
+	if (hdr[2]) fwrite(mesh->getVertexNormals(), sizeof(Normal), hdr[0], f);
+	if (hdr[3]) fwrite(mesh->getVertexTexcoords(), sizeof(Point2), hdr[0], f);
+	fwrite(mesh->getTriangles(), sizeof(Triangle), hdr[1], f);
+	fclose(f);
+	printf("{\"cmd\": \"mesh\", \"vertices\": %u, \"triangles\": %u, \"normals\": %u, \"texcoords\": %u}\n", hdr[0], hdr[1], hdr[2], hdr[3]);
+	return 0;
+}
+
+/* Write every mesh of a scene file with the reference's own writer: TriMesh::serialize(Stream *)
+ * (trimesh.cpp:748-790) per mesh, then the offset table as the converter does (converter.cpp:293-296). */
+static int cmdMeshSave(int argc, char **argv) {
+	if (argc < 4) { std::cerr << "meshsave SCENE OUTFILE\n"; return 1; }
+	sio::Scene sf; sio::load(argv[2], sf);
+	Built b = buildScene(sf, "");
+	ref<FileStream> out = new FileStream(argv[3], FileStream::ETruncReadWrite);
+	out->setByteOrder(Stream::ELittleEndian);
+	std::vector<uint32_t> dict;
+	const std::vector<Shape *> &shapes = b.scene->getShapes();
+	for (size_t i = 0; i < shapes.size(); ++i) {
+		dict.push_back((uint32_t) out->getPos());
+		static_cast<TriMesh *>(shapes[i])->serialize(out);
+	}
+	for (size_t i = 0; i < dict.size(); ++i) out->writeUInt(dict[i]);
+	out->writeUInt((uint32_t) dict.size());
+	out->close();
+	printf("{\"cmd\": \"meshsave\", \"meshes\": %zu}\n", dict.size());
+	return 0;
+}
+
 static int dispatch(int argc, char **argv) {
-	if (argc < 2) { std::cerr << "usage: mts_oracle trace|triaccel|bsdf|emitter|camera|splat|render ...\n"; return 1; }
+	if (argc < 2) { std::cerr << "usage: mts_oracle trace|triaccel|bsdf|emitter|camera|splat|render|mesh|meshsave ...\n"; return 1; }
 	std::string cmd = argv[1];
 	if (cmd == "trace") return cmdTraceImpl(argc, argv);
 	if (cmd == "triaccel") return cmdTriAccel(argc, argv);
@@ -239,6 +289,8 @@ static int dispatch(int argc, char **argv) {
 	if (cmd == "camera") return cmdCamera(argc, argv);
 	if (cmd == "splat") return cmdSplat(argc, argv);
 	if (cmd == "render") return cmdRender(argc, argv);
+	if (cmd == "mesh") return cmdMesh(argc, argv);
+	if (cmd == "meshsave") return cmdMeshSave(argc, argv);
 	std::cerr << "unknown command " << cmd << "\n";
 	return 1;
 }

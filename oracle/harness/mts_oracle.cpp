@@ -28,6 +28,7 @@
 #include <mitsuba/core/sched.h>
 #include <mitsuba/core/appender.h>
 #include <mitsuba/core/bitmap.h>
+#include <mitsuba/core/fstream.h>
 #include <chrono>
 #include <cstdlib>
 #include <iostream>

@@ -34,6 +34,25 @@ def main():
     sess = oracle_util.Session(scene)
     save("smoke_cornell", rays_digest=gc.digest(rays), hits=sess.trace(rays, "closest")[0].view(np.uint8),
          occluded=sess.trace(scenes.shadow_segments(rays, scene), "any")[0])
+    # ---- `.serialized` meshes: the reference's loader on its own fixture and on files written by our writer ----
+    import tempfile
+    from mitsuba_renderer_b200 import serialized
+    fx = {}
+    for i in range(3):
+        m = oracle_util.load_serialized(gc.SERIALIZED_FIXTURE, i)
+        fx[f"fixture{i}"] = np.frombuffer(gc.mesh_digest(m).encode(), np.uint8)
+        fx[f"fixture{i}_counts"] = np.array([len(m["positions"]), len(m["triangles"])])
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, "two.serialized")
+        serialized.save(path, gc.serialized_meshes())
+        for idx in (0, 1):
+            for fn, fl in ((0, 0), (0, 1), (1, 0), (1, 1)):
+                m = oracle_util.load_serialized(path, idx, fn, fl)
+                fx[f"mesh{idx}_{fn}{fl}_normals"] = np.zeros((0, 3), np.float32) if m["normals"] is None else m["normals"]
+                fx[f"mesh{idx}_{fn}{fl}_triangles"] = m["triangles"]
+        m = oracle_util.load_serialized(path, 1, to_world=gc.SERIALIZED_TO_WORLD)
+        fx["mesh1_xf_positions"], fx["mesh1_xf_normals"], fx["mesh1_xf_triangles"] = m["positions"], m["normals"], m["triangles"]
+    save("serialized", **fx)
     # ---- TriAccel records + enlarged scene box --------------------------------------------------------
     rec, box, _ = oracle_util.Session(gc.scene_materials()).triaccel()
     save("triaccel_materials", records=rec.view(np.uint8), box=box)

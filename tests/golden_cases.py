@@ -128,7 +128,34 @@ def render_scene():
     return scenes.cornell_box(48, 48, 64, max_depth=8)
 
 
-def digest(a):
+def digest(*arrays):
     """Cheap content hash to notice when a generator drifts away from the stored fixtures."""
     import hashlib
-    return hashlib.sha1(np.ascontiguousarray(a).tobytes()).hexdigest()[:16]
+    h = hashlib.sha1()
+    for a in arrays:
+        h.update(np.ascontiguousarray(a).tobytes())
+    return h.hexdigest()[:16]
+
+
+# ---- `.serialized` meshes -----------------------------------------------------------------------------------
+SERIALIZED_FIXTURE = "/root/reference/data/blender/mitsuba/matpreview/matpreview.serialized"   # the reference's own file
+SERIALIZED_TO_WORLD = np.array([[0, -2, 0, 1], [1.5, 0, 0, 2], [0, 0, -1, 3], [0, 0, 0, 1]], np.float32)   # det < 0: winding swaps
+
+
+def serialized_meshes():
+    """Two small meshes for the writer / reader / computeNormals cases: an icosphere without normals (so the
+    loader has to compute them) and the Cornell short block with normals and texture coordinates."""
+    v, f = scenes.icosphere(2)
+    ico = {"positions": (v * 0.7 + np.array([1.9, 3.2, 1.6])).astype(np.float32), "triangles": f.astype(np.uint32)}
+    sh = scenes.cornell_box(16, 16, 1).shapes[3]
+    uv = (sh.positions[:, :2] * np.float32(0.25)).astype(np.float32)
+    block = {"positions": sh.positions, "triangles": sh.triangles, "normals": sh.normals, "texcoords": uv}
+    return [ico, block]
+
+
+def mesh_digest(m):
+    parts = [np.ascontiguousarray(m["positions"], np.float32), np.ascontiguousarray(m["triangles"], np.uint32)]
+    for k in ("normals", "texcoords"):
+        if m.get(k) is not None:
+            parts.append(np.ascontiguousarray(m[k], np.float32))
+    return digest(*parts)

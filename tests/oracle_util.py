@@ -34,6 +34,37 @@ def _run(args, variant="parity", timeout=3600, env=None):
     raise RuntimeError("mts_oracle printed no result line:\n" + p.stdout + p.stderr)
 
 
+def load_serialized(path, shape_index=0, face_normals=False, flip_normals=False, to_world=None, variant="parity"):
+    """One mesh of a `.serialized` file as the reference's `serialized` shape plugin produces it."""
+    with tempfile.TemporaryDirectory(prefix="mtsoracle_") as d:
+        out = os.path.join(d, "mesh.bin")
+        args = ["mesh", path, shape_index, out, int(face_normals), int(flip_normals)]
+        if to_world is not None:
+            args += [repr(float(v)) for v in np.asarray(to_world, np.float32).reshape(16)]
+        _run(args, variant)
+        raw = np.fromfile(out, np.uint8)
+    nv, nt, hn, ht = raw[:16].view(np.uint32)
+    o = 16
+    def take(count, dt):
+        nonlocal o
+        a = raw[o:o + 4 * count].view(dt).copy(); o += 4 * count
+        return a
+    pos = take(3 * nv, np.float32).reshape(nv, 3)
+    nrm = take(3 * nv, np.float32).reshape(nv, 3) if hn else None
+    uv = take(2 * nv, np.float32).reshape(nv, 2) if ht else None
+    tri = take(3 * nt, np.uint32).reshape(nt, 3)
+    return {"positions": pos, "normals": nrm, "texcoords": uv, "triangles": tri}
+
+
+def save_serialized(scene, path, variant="parity"):
+    """Every mesh of `scene` written by the reference's TriMesh::serialize + offset table."""
+    from mitsuba_renderer_b200 import scenefile
+    with tempfile.TemporaryDirectory(prefix="mtsoracle_") as d:
+        sp = os.path.join(d, "scene.bin")
+        scenefile.write_scene(sp, scene)
+        return _run(["meshsave", sp, path], variant)
+
+
 class Session:
     """A scene written once to a temp dir; each call runs one harness command on it."""
 
