@@ -71,12 +71,30 @@ typedef struct mtsgpu_material {
 	float p[16];
 } mtsgpu_material;
 
-/* Area luminaire bound to a mesh (src/luminaires/area.cpp:35-83). Emitters must be listed in the
- * order Scene::addShape meets their shapes (src/librender/scene.cpp:656-664), which is the order
- * of Scene::getLuminaires() and therefore of the luminaire CDF (scene.cpp:320-330). */
+/* Luminaires. List them in the order of Scene::getLuminaires(), which is the order of the luminaire CDF
+ * (src/librender/scene.cpp:320-330): luminaires that are scene children come first, in the order they were added
+ * (scene.cpp:604-612); area luminaires follow, in the order Scene::initialize meets their shapes
+ * (scene.cpp:296-299, 656-664). Area luminaires must therefore appear in the order of their shapes.
+ *   AREA         src/luminaires/area.cpp:35-83         bound to the mesh whose emitterId names it; p unused
+ *   POINT        src/luminaires/point.cpp:27-66        p[0..2] position
+ *   SPOT         src/luminaires/spot.cpp:32-127        p[0..2] position, p[3..5] third row of the 3x3 part of
+ *                                                      worldToLuminaire (cosTheta = p[3..5] . d), p[6] beamWidth and
+ *                                                      p[7] cutoffAngle in radians (as SpotLuminaire::serialize writes
+ *                                                      them); constant projection texture only
+ *   DIRECTIONAL  src/luminaires/directional.cpp:29-90  p[0..2] direction (normalised), p[3] diskRadius; 0 = derive it
+ *                                                      from the scene's bounding sphere as preprocess() does
+ *   CONSTANT     src/luminaires/constant.cpp:27-86     background; p[0..2] centre and p[3] radius of its bounding
+ *                                                      sphere; radius 0 = derive it as preprocess() does (scene
+ *                                                      sphere x 1.01, grown to hold the camera). At most one. */
+enum mtsgpu_emitter_type {
+	MTSGPU_EMITTER_AREA = 0, MTSGPU_EMITTER_POINT = 1, MTSGPU_EMITTER_SPOT = 2, MTSGPU_EMITTER_DIRECTIONAL = 3,
+	MTSGPU_EMITTER_CONSTANT = 4
+};
 typedef struct mtsgpu_emitter {
 	float intensity[3];
 	float samplingWeight; /* Luminaire::getSamplingWeight(), luminaire.h:180; weight in the luminaire CDF */
+	uint32_t type;        /* mtsgpu_emitter_type */
+	float p[11];
 } mtsgpu_emitter;
 
 enum mtsgpu_mode { MTSGPU_MODE_PATH = 0, MTSGPU_MODE_DIRECT = 1 };

@@ -43,7 +43,7 @@ class Material(C.Structure):
 
 
 class Emitter(C.Structure):
-    _fields_ = [("intensity", C.c_float * 3), ("samplingWeight", C.c_float)]
+    _fields_ = [("intensity", C.c_float * 3), ("samplingWeight", C.c_float), ("type", C.c_uint32), ("p", C.c_float * 11)]
 
 
 class RenderParams(C.Structure):
@@ -214,6 +214,8 @@ class Context:
         for i, e in enumerate(scene.emitters):
             ems[i].intensity[:] = [float(v) for v in e.intensity]
             ems[i].samplingWeight = e.sampling_weight
+            ems[i].type = e.type
+            ems[i].p[:] = [float(v) for v in e.abi_params()]
         self._check(self.lib.mtsgpu_upload_emitters(self.h, ems, len(scene.emitters)))
         for i, s in enumerate(scene.shapes):
             pos = np.ascontiguousarray(s.positions, np.float32)

@@ -89,6 +89,14 @@ int mtsgpu_upload_materials(mtsgpu_ctx *ctx, const mtsgpu_material *materials, i
 int mtsgpu_upload_emitters(mtsgpu_ctx *ctx, const mtsgpu_emitter *emitters, int count) {
 	ENTER(ctx);
 	REQUIRE(ctx, count >= 0 && (count == 0 || emitters), MTSGPU_ERR_ARG, "upload_emitters: bad arguments");
+	int backgrounds = 0;
+	for (int i = 0; i < count; ++i) {
+		REQUIRE(ctx, emitters[i].type <= MTSGPU_EMITTER_CONSTANT, MTSGPU_ERR_UNSUPPORTED, "emitter %d: unsupported luminaire type %u", i, emitters[i].type);
+		if (emitters[i].type == MTSGPU_EMITTER_SPOT)      // Assert(m_cutoffAngle >= m_beamWidth), spot.cpp:42
+			REQUIRE(ctx, emitters[i].p[7] >= emitters[i].p[6], MTSGPU_ERR_ARG, "emitter %d: cutoffAngle must be >= beamWidth", i);
+		backgrounds += emitters[i].type == MTSGPU_EMITTER_CONSTANT;
+	}
+	REQUIRE(ctx, backgrounds <= 1, MTSGPU_ERR_UNSUPPORTED, "upload_emitters: at most one background luminaire");
 	ctx->emitters.assign(emitters, emitters + count);
 	ctx->built = false;
 	return MTSGPU_OK;
@@ -122,6 +130,7 @@ int mtsgpu_set_camera(mtsgpu_ctx *ctx, const float rasterToCamera[16], const flo
 	ctx->camera.apertureRadius = apertureRadius; ctx->camera.focusDepth = focusDepth;
 	ctx->camera.shutterOpen = shutterOpen; ctx->camera.shutterOpenTime = shutterOpenTime;
 	ctx->haveCamera = true;
+	ctx->lumImportance = -1;          // the background luminaire's sphere depends on the camera position
 	return MTSGPU_OK;
 }
 

@@ -278,12 +278,64 @@ int rebuildLuminaireCdf(mtsgpu_ctx *ctx, bool importance) {
 	cudaStream_t st = ctx->stream;
 	std::vector<EmitterDev> emitters(ctx->emitters.size());
 	std::vector<float> lumPdf(ctx->emitters.size()), lumCdf;
+	ctx->scene.background = -1;
 	for (size_t e = 0; e < emitters.size(); ++e) {
 		memset(&emitters[e], 0, sizeof(EmitterDev));
-		memcpy(emitters[e].intensity, ctx->emitters[e].intensity, 12);
-		emitters[e].shape = (uint32_t) ctx->emitterShape[e];
-		emitters[e].weight = ctx->emitters[e].samplingWeight;
-		lumPdf[e] = importance ? ctx->emitters[e].samplingWeight : 1.0f;
+		const mtsgpu_emitter &src = ctx->emitters[e];
+		EmitterDev &em = emitters[e];
+		memcpy(em.intensity, src.intensity, 12);
+		em.shape = (uint32_t) std::max(ctx->emitterShape[e], 0);
+		em.weight = src.samplingWeight;
+		em.type = src.type;
+		lumPdf[e] = importance ? src.samplingWeight : 1.0f;
+		// Scene::getBSphere(): ShapeKDTree::build takes it from the enlarged kd-tree box (skdtree.cpp:68, aabb.cpp:44-47)
+		float center[3], radius = 0.0f;
+		{
+			float d2 = 0.0f;
+			for (int c = 0; c < 3; ++c) {
+				center[c] = (ctx->scene.aabbMax[c] + ctx->scene.aabbMin[c]) * 0.5f;
+				const float d = center[c] - ctx->scene.aabbMax[c];
+				d2 = c == 0 ? d * d : d2 + d * d;
+			}
+			radius = std::sqrt(d2);
+		}
+		switch (src.type) {
+			case MTSGPU_EMITTER_POINT:
+				memcpy(em.p, src.p, 12);
+				break;
+			case MTSGPU_EMITTER_SPOT: {            // SpotLuminaire::configure (spot.cpp:55-61)
+				memcpy(em.p, src.p, 24);
+				const float beamWidth = src.p[6], cutoffAngle = src.p[7];
+				em.p[6] = cutoffAngle;
+				em.p[7] = 1.0f / (cutoffAngle - beamWidth);
+				em.p[8] = std::cos(beamWidth);
+				em.p[9] = std::cos(cutoffAngle);
+				break;
+			}
+			case MTSGPU_EMITTER_DIRECTIONAL:       // DirectionalLuminaire::preprocess (directional.cpp:64-71)
+				memcpy(em.p, src.p, 16);
+				if (src.p[3] == 0.0f) em.p[3] = radius;
+				break;
+			case MTSGPU_EMITTER_CONSTANT:          // ConstantLuminaire::preprocess (constant.cpp:48-62)
+				memcpy(em.p, src.p, 16);
+				if (!(src.p[3] > 0.0f)) {
+					memcpy(em.p, center, 12);
+					float r = radius * 1.01f;
+					if (ctx->haveCamera) {
+						const float *M = ctx->camera.cameraToWorld;      // Camera::m_position = cameraToWorld(Point(0,0,0))
+						float w = M[15], pos[3] = { M[3], M[7], M[11] };
+						if (w != 1.0f) { const float rw = 1.0f / w; for (int c = 0; c < 3; ++c) pos[c] *= rw; }
+						const float dx = pos[0] - center[0], dy = pos[1] - center[1], dz = pos[2] - center[2];
+						const float dist = std::sqrt(dx * dx + dy * dy + dz * dz);
+						if (dist > r) r = dist * 1.01f;              // BSphere::expandBy, then the second enlargement
+					}
+					em.p[3] = r;
+				}
+				ctx->scene.background = (int32_t) e;
+				break;
+			default:
+				break;
+		}
 	}
 	float lumSum = 0.0f;
 	if (!emitters.empty()) {
@@ -365,11 +417,17 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		}
 		tOff += m.nTri; vOff += m.nVert;
 	}
-	for (size_t e = 0; e < emitterShape.size(); ++e)
+	// area emitters must be bound to exactly one shape and appear in first-shape order (scene.cpp:656-664)
+	int lastShape = -1;
+	for (size_t e = 0; e < emitterShape.size(); ++e) {
+		if (ctx->emitters[e].type != MTSGPU_EMITTER_AREA) {
+			REQUIRE(ctx, emitterShape[e] < 0, MTSGPU_ERR_ARG, "emitter %zu is not an area luminaire but shape %d names it", e, emitterShape[e]);
+			continue;
+		}
 		REQUIRE(ctx, emitterShape[e] >= 0, MTSGPU_ERR_ARG, "emitter %zu is not bound to any shape", e);
-	// emitters must appear in first-shape order (scene.cpp:656-664)
-	for (size_t e = 1; e < emitterShape.size(); ++e)
-		REQUIRE(ctx, emitterShape[e] > emitterShape[e-1], MTSGPU_ERR_ARG, "emitters must be listed in the order of their shapes");
+		REQUIRE(ctx, emitterShape[e] > lastShape, MTSGPU_ERR_ARG, "emitters must be listed in the order of their shapes");
+		lastShape = emitterShape[e];
+	}
 
 	ctx->emitterShape = emitterShape;
 

@@ -215,10 +215,12 @@ __device__ __forceinline__ bool nextEvent(const DeviceScene &sc, const Integrato
 	if (ls.pdf == 0) return false;
 	const V3 wo = -ls.d;
 	const V3 woLocal = toLocal(its.sh, wo);
-	V3 f; float bPdf;                                                      // area luminaires are intersectable: pdf is needed
+	V3 f; float bPdf;
 	bsdfFPdf(mat, its.wi, woLocal, f, bPdf);
 	const V3 bsdfVal = f * fabsf(woLocal.z);                               // fCos
 	if (isZero(bsdfVal)) return false;
+	if (!ls.mis) bPdf = 0.0f;                                              // delta luminaires: BSDF sampling cannot find them
+	if (isZero(ls.value)) return false;                                    // outside a spot's cone: nothing to add, no shadow ray needed
 	if (ig.strictNormals && !(dot(its.geoN, wo) * woLocal.z > 0)) return false;
 	const float weight = miWeight(ls.pdf * fracLum, bPdf * fracBsdf) * weightLum;
 	contrib = ((scale * ls.value) * bsdfVal) * weight;
@@ -263,10 +265,11 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		}
 
 		if (MODE == 2) {
-			// direct.cpp:170-199: BSDF-sampled ray hit something — only emitters contribute
-			if (valid && its.emitterId >= 0) {
-				const V3 Le = emitterLe(sc, its.emitterId, its.geoN, -rayD);
-				const float lumPdf = (flags & PF_PREV_DELTA) ? 0.0f : pdfLuminaire(sc, rayO, its.p, its.geoN, its.emitterId, ig.importance != 0);
+			// direct.cpp:170-199: BSDF-sampled ray — only emitters (or the background on a miss) contribute
+			if ((valid && its.emitterId >= 0) || (!valid && sc.background >= 0)) {
+				const V3 Le = valid ? emitterLe(sc, its.emitterId, its.geoN, -rayD) : backgroundLe(sc);
+				const float lumPdf = (flags & PF_PREV_DELTA) ? 0.0f :
+					(valid ? pdfLuminaire(sc, rayO, its.p, its.geoN, its.emitterId, ig.importance != 0) : pdfBackground(sc, ig.importance != 0));
 				const float total = (float) (ig.nLum + ig.nBsdf);          // direct.cpp:49-54
 				const float fracBsdf = ig.nBsdf / total, fracLum = ig.nLum / total;
 				const float weightBsdf = 1 / (float) ig.nBsdf;
@@ -280,7 +283,13 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 				// ---- steps after "trace a ray in this direction" of the previous iteration (path.cpp:152-208)
 				const V3 bsdfVal = v3(bv4);
 				if (!valid) {
-					depth++;                                   // path.cpp:166
+					if (sc.background >= 0) {                  // path.cpp:158-163, 172-179, then 187-188
+						const float lumPdf = (flags & PF_PREV_DELTA) ? 0.0f : pdfBackground(sc, ig.importance != 0);
+						const float w = miWeight(thr4.w, lumPdf);
+						Li = Li + ((thr * backgroundLe(sc)) * bsdfVal) * w;
+					} else {
+						depth++;                               // path.cpp:166
+					}
 					alive = false;
 				} else {
 					if (its.emitterId >= 0) {
@@ -302,6 +311,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 			} else if (MODE == 0 || round == 0) {
 				// camera hit: rRec.alpha (records.inl:93-99)
 				li4.w = valid ? 1.0f : 0.0f;
+				if (!valid && (flags & PF_EMITTED)) Li = Li + backgroundLe(sc);      // path.cpp:62-68 / direct.cpp:74-81
 			}
 
 			// ---- top of the loop body at the new hit (path.cpp:58-95 / direct.cpp:74-100)
@@ -717,7 +727,10 @@ __global__ void k_hook_emitter(const DeviceScene sc, const float *q, uint32_t n,
 	if (ls.pdf != 0) {
 		o[6] = ls.d.x; o[7] = ls.d.y; o[8] = ls.d.z; o[9] = ls.pdf;
 		o[10] = ls.value.x; o[11] = ls.value.y; o[12] = ls.value.z; o[13] = (float) ls.emitter;
-		o[14] = pdfLuminaire(sc, p, ls.p, ls.n, ls.emitter, importance != 0);
+		// Scene::pdfLuminaire (scene.cpp:381-394): zero for the delta luminaires
+		const uint32_t type = sc.emitters[ls.emitter].type;
+		o[14] = type == MTSGPU_EMITTER_AREA ? pdfLuminaire(sc, p, ls.p, ls.n, ls.emitter, importance != 0)
+			: (type == MTSGPU_EMITTER_CONSTANT ? pdfBackground(sc, importance != 0) : 0.0f);
 	} else {
 		o[13] = -1.0f;
 	}

@@ -142,47 +142,110 @@ struct LumSample {
 	V3 p, n, d, value;   // sRec.p, sRec.n, lRec.d (normalised, light -> point), lRec.value (already / pdf)
 	float pdf;           // lRec.pdf after multiplication by the luminaire-selection pdf; 0 => failed
 	int emitter;
+	bool mis;            // luminaire->isIntersectable() || isBackgroundLuminaire(): BSDF sampling can find it too
 };
 
+__device__ inline V3 squareToSphere(float sx, float sy) {                   // util.cpp:552-558
+	const float z = 1.0f - 2.0f * sy;
+	float r = 1.0f - z * z;
+	r = sqrtf(fmaxf(0.0f, r));
+	const float phi = 2.0f * MTS_PI * sx;
+	return v3(r * mts_cos(phi), r * mts_sin(phi), z);
+}
+
+// BSphere::rayIntersect (core/bsphere.h:85-118) for a ray with mint = 0
+__device__ inline bool bsphereRayIntersect(V3 center, float radius, V3 o, V3 d, float &nearHit, float &farHit) {
+	const V3 originToCenter = center - o;
+	const float distToRayClosest = dot(originToCenter, d);
+	const float tmp1 = dot(originToCenter, originToCenter) - radius * radius;
+	if (tmp1 <= 0.0f) {
+		nearHit = farHit = sqrtf(distToRayClosest * distToRayClosest - tmp1) + distToRayClosest;
+		return true;
+	}
+	if (distToRayClosest < 0.0f) return false;
+	const float sqrHalfChordDist = radius * radius - dot(originToCenter, originToCenter) + distToRayClosest * distToRayClosest;
+	if (sqrHalfChordDist < 0) return false;
+	const float hitDistance = sqrtf(sqrHalfChordDist);
+	nearHit = distToRayClosest - hitDistance; farHit = distToRayClosest + hitDistance;
+	if (nearHit == 0) nearHit = farHit;
+	return true;
+}
+
 __device__ inline void sampleLuminaire(const DeviceScene &sc, V3 p, float sx, float sy, bool importance, LumSample &out) {
-	out.pdf = 0; out.emitter = -1;
+	out.pdf = 0; out.emitter = -1; out.mis = true;
 	if (sc.nEmitters == 0) return;
 	const int index = cdfSampleReuse(sc.lumCdf, (int) sc.nEmitters, sx);
 	const EmitterDev em = sc.emitters[index];
 	const float lumPdf = em.pdf;
-	const ShapeInfo si = sc.shapes[em.shape];
-	// TriMesh::sampleArea (trimesh.cpp:297-302) + Triangle::sample (triangle.cpp:23-47)
-	const int tri = cdfSampleReuse(sc.areaCdf + si.cdfOffset, (int) si.nTri, sy);
-	const uint4 idx = __ldg(sc.triIdx + si.triOffset + tri);
-	const V3 p0 = v3(__ldg(sc.positions + idx.x)), p1 = v3(__ldg(sc.positions + idx.y)), p2 = v3(__ldg(sc.positions + idx.z));
-	const float a = sqrtf(1.0f - sx);
-	const float baryX = 1 - a, baryY = a * sy;
-	const V3 sideA = p1 - p0, sideB = p2 - p0;
-	out.p = p0 + (sideA * baryX) + (sideB * baryY);
-	if (si.hasNormals) {
-		const V3 n0 = v3(__ldg(sc.normals + idx.x)), n1 = v3(__ldg(sc.normals + idx.y)), n2 = v3(__ldg(sc.normals + idx.z));
-		out.n = normalize(n0 * (1.0f - baryX - baryY) + n1 * baryX + n2 * baryY);
-	} else {
-		out.n = normalize(cross(sideA, sideB));
-	}
-	// Shape::sampleSolidAngle (shape.cpp:65-75)
-	const V3 lumToPoint = p - out.p;
-	const float distSquared = dot(lumToPoint, lumToPoint), dp = dot(lumToPoint, out.n);
+	const V3 inten = v3(em.intensity[0], em.intensity[1], em.intensity[2]);
+	out.emitter = index;
 	float pdf = 0.0f;
-	if (dp > 0)
-		pdf = si.invSurfaceArea * distSquared * sqrtf(distSquared) / dp;
-	// AreaLuminaire::sample (area.cpp:68-79)
-	V3 d = p - out.p;
-	if (pdf > 0 && dot(d, out.n) > 0) {
-		d = normalize(d);
+	V3 value = inten;
+	if (em.type == MTSGPU_EMITTER_AREA) {
+		const ShapeInfo si = sc.shapes[em.shape];
+		// TriMesh::sampleArea (trimesh.cpp:297-302) + Triangle::sample (triangle.cpp:23-47)
+		const int tri = cdfSampleReuse(sc.areaCdf + si.cdfOffset, (int) si.nTri, sy);
+		const uint4 idx = __ldg(sc.triIdx + si.triOffset + tri);
+		const V3 p0 = v3(__ldg(sc.positions + idx.x)), p1 = v3(__ldg(sc.positions + idx.y)), p2 = v3(__ldg(sc.positions + idx.z));
+		const float a = sqrtf(1.0f - sx);
+		const float baryX = 1 - a, baryY = a * sy;
+		const V3 sideA = p1 - p0, sideB = p2 - p0;
+		out.p = p0 + (sideA * baryX) + (sideB * baryY);
+		if (si.hasNormals) {
+			const V3 n0 = v3(__ldg(sc.normals + idx.x)), n1 = v3(__ldg(sc.normals + idx.y)), n2 = v3(__ldg(sc.normals + idx.z));
+			out.n = normalize(n0 * (1.0f - baryX - baryY) + n1 * baryX + n2 * baryY);
+		} else {
+			out.n = normalize(cross(sideA, sideB));
+		}
+		// Shape::sampleSolidAngle (shape.cpp:65-75)
+		const V3 lumToPoint = p - out.p;
+		const float distSquared = dot(lumToPoint, lumToPoint), dp = dot(lumToPoint, out.n);
+		if (dp > 0)
+			pdf = si.invSurfaceArea * distSquared * sqrtf(distSquared) / dp;
+		// AreaLuminaire::sample (area.cpp:68-79)
+		V3 d = p - out.p;
+		if (pdf > 0 && dot(d, out.n) > 0) {
+			d = normalize(d);
+		} else {
+			pdf = 0;
+		}
+		out.d = d;
+	} else if (em.type == MTSGPU_EMITTER_POINT || em.type == MTSGPU_EMITTER_SPOT) {
+		// PointLuminaire::sample (point.cpp:58-66) / SpotLuminaire::sample (spot.cpp:117-125)
+		const V3 pos = v3(em.p[0], em.p[1], em.p[2]);
+		const V3 lumToP = p - pos;
+		const float invDist = 1.0f / length(lumToP);
+		out.p = pos; out.n = v3(0, 0, 0);
+		out.d = lumToP * invDist;
+		pdf = 1.0f; out.mis = false;
+		if (em.type == MTSGPU_EMITTER_SPOT) {
+			// falloffCurve (spot.cpp:85-109), constant texture
+			const float cosTheta = em.p[3] * out.d.x + em.p[4] * out.d.y + em.p[5] * out.d.z;
+			if (cosTheta <= em.p[9]) value = v3(0, 0, 0);
+			else if (!(cosTheta >= em.p[8])) value = value * ((em.p[6] - mts_acos(cosTheta)) * em.p[7]);
+		}
+		value = value * (invDist * invDist);
+	} else if (em.type == MTSGPU_EMITTER_DIRECTIONAL) {
+		// DirectionalLuminaire::sample (directional.cpp:83-90)
+		const V3 dir = v3(em.p[0], em.p[1], em.p[2]);
+		out.p = p - dir * (2 * em.p[3]); out.n = v3(0, 0, 0);
+		out.d = dir;
+		pdf = 1.0f; out.mis = false;
 	} else {
-		pdf = 0;
+		// ConstantLuminaire::sample (constant.cpp:72-86)
+		const V3 d = squareToSphere(sx, sy);
+		const V3 center = v3(em.p[0], em.p[1], em.p[2]);
+		float nearHit, farHit;
+		if (length(p - center) <= em.p[3] && bsphereRayIntersect(center, em.p[3], p, d, nearHit, farHit)) {
+			out.p = p + d * nearHit;
+			pdf = 1.0f / (4 * MTS_PI);
+			out.n = normalize(center - out.p);
+			out.d = -d;
+		}
 	}
-	out.d = d; out.emitter = index;
 	if (pdf != 0) {
 		pdf *= lumPdf;
-		const V3 inten = v3(em.intensity[0], em.intensity[1], em.intensity[2]);
-		out.value = inten * (1.0f / pdf);
+		out.value = value * (1.0f / pdf);
 		out.pdf = pdf;
 	}
 }
@@ -196,6 +259,21 @@ __device__ inline float pdfLuminaire(const DeviceScene &sc, V3 from, V3 lumP, V3
 	const float distSquared = dot(lumToPoint, lumToPoint);
 	const float invDP = fmaxf(0.0f, sqrtf(distSquared) / dot(lumToPoint, lumN));
 	return (sc.shapes[em.shape].invSurfaceArea * distSquared * invDP) * fraction;
+}
+
+// Scene::pdfLuminaire for the background luminaire: ConstantLuminaire::pdf (constant.cpp:88-90)
+__device__ inline float pdfBackground(const DeviceScene &sc, bool importance) {
+	const EmitterDev em = sc.emitters[sc.background];
+	const float luminance = importance ? em.weight : 1.0f;
+	const float fraction = luminance / sc.lumOriginalSum;
+	return (1.0f / (4 * MTS_PI)) * fraction;
+}
+
+// Scene::LeBackground (scene.h:403-405) -> ConstantLuminaire::Le (constant.cpp:68-70)
+__device__ inline V3 backgroundLe(const DeviceScene &sc) {
+	if (sc.background < 0) return v3(0, 0, 0);
+	const EmitterDev em = sc.emitters[sc.background];
+	return v3(em.intensity[0], em.intensity[1], em.intensity[2]);
 }
 
 // AreaLuminaire::Le (area.cpp:62-66)

@@ -43,7 +43,9 @@ struct ShapeInfo {
 };
 
 struct MaterialDev { uint32_t type; float p[16]; uint32_t pad[3]; };
-struct EmitterDev { float intensity[3]; uint32_t shape; float pdf; float weight; uint32_t pad[2]; };
+// p[]: POINT pos | SPOT pos, axis row, cutoffAngle, invTransitionWidth, cosBeamWidth, cosCutoffAngle |
+//      DIRECTIONAL dir, diskRadius | CONSTANT sphere centre, radius   (derived values filled by rebuildLuminaireCdf)
+struct EmitterDev { float intensity[3]; uint32_t shape; float pdf; float weight; uint32_t type; float p[13]; };
 
 struct CameraDev {
 	float rasterToCamera[16];
@@ -71,6 +73,7 @@ struct DeviceScene {
 	const float *lumCdf;        // nEmitters + 1 (DiscretePDF::m_cdf, pdf.h:82-100)
 	const float *areaCdf;       // per emitter mesh: nTri + 1 entries at ShapeInfo::cdfOffset
 	uint32_t nEmitters, nShapes, nTris, rootIsLeaf;
+	int32_t background;         // index of the background luminaire (Scene::getBackgroundLuminaire), -1: none
 	float lumOriginalSum;       // DiscretePDF::getOriginalSum()
 	float aabbMin[3], aabbMax[3]; // enlarged kd-tree box (gkdtree.h:1172-1176)
 };

@@ -169,6 +169,62 @@ private:
 		return m;
 	}
 
+	/* Scene-level luminaires (point, spot, directional, constant): no getters either, so decode
+	 * Luminaire::serialize (luminaire.cpp:66-74) + the subclass's fields. ConfigurableObject::serialize writes the
+	 * parent object first (properties.cpp:358-363) — the whole scene here — so the parent link is cleared for the
+	 * duration of the call; render() runs before any worker touches the scene. */
+	static void decodeLuminaire(const Luminaire *lumConst, mtsgpu_emitter &e) {
+		Luminaire *lum = const_cast<Luminaire *>(lumConst);
+		const std::string cls = lum->getClass()->getName();
+		ConfigurableObject *parent = lum->getParent();
+		ref<MemoryStream> s = new MemoryStream();
+		ref<InstanceManager> mgr = new InstanceManager();
+		lum->setParent(NULL);
+		lum->serialize(s, mgr);
+		lum->setParent(parent);
+		s->setPos(0);
+		if (s->readUInt() != 0) SLog(EError, "gpupath: unexpected luminaire parent");
+		if (s->readUInt() != 0) SLog(EError, "gpupath: luminaires inside participating media are outside the supported hot path");
+		s->readFloat(); s->readInt(); s->readBool();           /* samplingWeight, type, intersectable */
+		Transform worldToLuminaire(s);
+		s->readString();
+		const Matrix4x4 &w2l = worldToLuminaire.getMatrix(), &l2w = worldToLuminaire.getInverseMatrix();
+		if (cls == "PointLuminaire") {                          /* point.cpp:41-45 */
+			e.type = MTSGPU_EMITTER_POINT;
+			put(e.intensity, Spectrum(s));
+			const Point pos = worldToLuminaire.inverse()(Point(0, 0, 0));
+			e.p[0] = pos.x; e.p[1] = pos.y; e.p[2] = pos.z;
+		} else if (cls == "SpotLuminaire") {                    /* spot.cpp:63-70 */
+			e.type = MTSGPU_EMITTER_SPOT;
+			if (s->readUInt() == 0 || s->readString() != "ConstantSpectrumTexture" || s->readUInt() != 0)
+				SLog(EError, "gpupath: SpotLuminaire: only a constant projection texture is inside the supported hot path");
+			Spectrum tex(s), intensity(s);
+			Float r, g, b; tex.toLinearRGB(r, g, b);
+			if (r != 1 || g != 1 || b != 1)
+				SLog(EError, "gpupath: SpotLuminaire: projection textures are outside the supported hot path");
+			put(e.intensity, intensity);
+			const Point pos = worldToLuminaire.inverse()(Point(0, 0, 0));
+			e.p[0] = pos.x; e.p[1] = pos.y; e.p[2] = pos.z;
+			e.p[3] = w2l.m[2][0]; e.p[4] = w2l.m[2][1]; e.p[5] = w2l.m[2][2];
+			e.p[6] = s->readFloat(); e.p[7] = s->readFloat();  /* beamWidth, cutoffAngle (radians) */
+		} else if (cls == "DirectionalLuminaire") {             /* directional.cpp:56-62 */
+			e.type = MTSGPU_EMITTER_DIRECTIONAL;
+			Vector d(s);
+			put(e.intensity, Spectrum(s));
+			Point diskOrigin(s);
+			e.p[0] = d.x; e.p[1] = d.y; e.p[2] = d.z; e.p[3] = s->readFloat();
+		} else if (cls == "ConstantLuminaire") {                /* constant.cpp:41-46, after preprocess() */
+			e.type = MTSGPU_EMITTER_CONSTANT;
+			put(e.intensity, Spectrum(s));
+			BSphere bs(s);
+			e.p[0] = bs.center.x; e.p[1] = bs.center.y; e.p[2] = bs.center.z; e.p[3] = bs.radius;
+		} else {
+			SLog(EError, "gpupath: luminaire class \"%s\" is outside the supported hot path "
+				"(area, point, spot, directional, constant)", cls.c_str());
+		}
+		(void) l2w;
+	}
+
 	static mtsgpu_material decodeBSDF(const BSDF *bsdf) {
 		ref<MemoryStream> s = new MemoryStream();
 		ref<InstanceManager> mgr = new InstanceManager();
@@ -187,8 +243,6 @@ private:
 		/* ---- refuse what the hot path does not cover ---- */
 		if (!camera->getClass()->derivesFrom(MTS_CLASS(PerspectiveCamera)))
 			Log(EError, "gpupath: only the perspective camera is supported");
-		if (scene->hasBackgroundLuminaire())
-			Log(EError, "gpupath: background luminaires are outside the supported hot path");
 		if (!scene->getMedia().empty() || camera->getMedium() != NULL)
 			Log(EError, "gpupath: participating media are outside the supported hot path");
 
@@ -201,13 +255,16 @@ private:
 		std::map<const Luminaire *, int> emitterIds;
 		for (size_t i = 0; i < luminaires.size(); ++i) {
 			const Luminaire *lum = luminaires[i];
-			if (lum->getClass()->getName() != "AreaLuminaire")
-				Log(EError, "gpupath: luminaire class \"%s\" is outside the supported hot path (area only)",
-					lum->getClass()->getName().c_str());
-			/* AreaLuminaire::Le returns m_intensity for any direction on the normal's side (area.cpp:62-66) */
-			put(emitters[i].intensity, lum->Le(ShapeSamplingRecord(Point(0.0f), Normal(0, 0, 1)), Vector(0, 0, 1)));
+			memset(&emitters[i], 0, sizeof(mtsgpu_emitter));
 			emitters[i].samplingWeight = lum->getSamplingWeight();
 			emitterIds[lum] = (int) i;
+			if (lum->getClass()->getName() == "AreaLuminaire") {
+				/* AreaLuminaire::Le returns m_intensity for any direction on the normal's side (area.cpp:62-66) */
+				emitters[i].type = MTSGPU_EMITTER_AREA;
+				put(emitters[i].intensity, lum->Le(ShapeSamplingRecord(Point(0.0f), Normal(0, 0, 1)), Vector(0, 0, 1)));
+			} else {
+				decodeLuminaire(lum, emitters[i]);
+			}
 		}
 		struct MeshRef { const TriMesh *mesh; int mat, emit; };
 		std::vector<MeshRef> meshes;

@@ -98,11 +98,109 @@ def twosided(material: Material) -> Material:
     return Material(material.type | BSDF_TWOSIDED, material.p.copy())
 
 
+EMITTER_AREA, EMITTER_POINT, EMITTER_SPOT, EMITTER_DIRECTIONAL, EMITTER_CONSTANT = range(5)
+
+
 @dataclass
 class Emitter:
-    """Area luminaire (src/luminaires/area.cpp:37-43); bound to the shape that names it."""
+    """A luminaire. The default is an area luminaire (src/luminaires/area.cpp:37-43), bound to the shape that
+    names it; the other types are made by point_light / spot_light / directional_light / constant_light.
+    `p` holds the C-ABI parameters (include/mtsgpu.h), `aux` what only the oracle harness needs to build the
+    same luminaire from its properties (toWorld matrix, angles in degrees, the direction before normalisation)."""
     intensity: tuple = (1.0, 1.0, 1.0)
     sampling_weight: float = 1.0
+    type: int = EMITTER_AREA
+    p: tuple = ()
+    aux: tuple = ()
+
+    def abi_params(self):
+        v = np.zeros(11, np.float32); v[:len(self.p)] = self.p
+        return v
+
+    def aux_params(self):
+        v = np.zeros(16, np.float32); v[:len(self.aux)] = self.aux
+        return v
+
+
+def invert4_f32(m):
+    """Inverse of a 4x4 matrix the way the reference gets a Transform's inverse: Gauss-Jordan elimination with
+    full pivoting, every operation in fp32 (Matrix::invert, include/mitsuba/core/matrix.inl:140-195). Restated so
+    that values derived from an inverse (a spot light's axis, transformed normals) match the reference's bits."""
+    f32 = np.float32
+    a = np.array(m, f32).reshape(4, 4).copy()
+    pivoted = [0] * 4
+    rows, cols = [], []
+    for _ in range(4):
+        big, r, c = f32(0), -1, -1
+        for j in range(4):
+            if pivoted[j] == 1:
+                continue
+            for k in range(4):
+                if pivoted[k] == 0 and abs(a[j, k]) >= big:
+                    big, r, c = abs(a[j, k]), j, k
+        pivoted[c] += 1
+        if r != c:
+            a[[r, c]] = a[[c, r]]
+        rows.append(r); cols.append(c)
+        if a[c, c] == 0:
+            raise ValueError("singular matrix")
+        pivinv = f32(f32(1.0) / a[c, c])
+        a[c, c] = f32(1.0)
+        a[c] = (a[c] * pivinv).astype(f32)
+        for j in range(4):
+            if j != c:
+                save = a[j, c]
+                a[j, c] = f32(0)
+                a[j] = (a[j] - (a[c] * save).astype(f32)).astype(f32)
+    for j in range(3, -1, -1):
+        if rows[j] != cols[j]:
+            a[:, [rows[j], cols[j]]] = a[:, [cols[j], rows[j]]]
+    return a
+
+
+def point_light(position, intensity=(1.0, 1.0, 1.0), sampling_weight=1.0):
+    """src/luminaires/point.cpp:29-33 with toWorld = translate(position)"""
+    m = np.eye(4, dtype=np.float32); m[:3, 3] = position
+    return Emitter(tuple(intensity), sampling_weight, EMITTER_POINT, tuple(np.float32(position)), tuple(m.reshape(16)))
+
+
+def spot_light(origin, target, up=(0, 1, 0), intensity=(1.0, 1.0, 1.0), cutoff_angle=20.0, beam_width=None, sampling_weight=1.0):
+    """src/luminaires/spot.cpp:34-61 with toWorld = lookAt(origin, target, up); angles in degrees."""
+    f32 = np.float32
+    cutoff = f32(cutoff_angle)
+    beam = f32(f32(cutoff * f32(3.0)) / f32(4.0)) if beam_width is None else f32(beam_width)
+    rad = f32(np.pi) / f32(180.0)                                  # degToRad (core/util.h:302)
+    m = look_at(origin, target, up)
+    axis = invert4_f32(m)[2, :3]                                   # third row of worldToLuminaire
+    p = list(m[:3, 3]) + list(axis) + [f32(beam * rad), f32(cutoff * rad), beam, cutoff]
+    return Emitter(tuple(intensity), sampling_weight, EMITTER_SPOT, tuple(p), tuple(m.reshape(16)))
+
+
+def directional_light(direction, intensity=(1.0, 1.0, 1.0), sampling_weight=1.0):
+    """src/luminaires/directional.cpp:31-41 with the `direction` property (normalised there as here)."""
+    f32 = np.float32
+    d = np.asarray(direction, f32)
+    n = d * (f32(1.0) / f32(np.sqrt(f32(f32(f32(d[0] * d[0]) + f32(d[1] * d[1])) + f32(d[2] * d[2])))))
+    return Emitter(tuple(intensity), sampling_weight, EMITTER_DIRECTIONAL, tuple(n.astype(f32)) + (0.0,), tuple(d))
+
+
+def constant_light(intensity=(1.0, 1.0, 1.0), sampling_weight=1.0):
+    """src/luminaires/constant.cpp:29-32: constant background; its bounding sphere is derived from the scene."""
+    return Emitter(tuple(intensity), sampling_weight, EMITTER_CONSTANT)
+
+
+def add_light(scene: "SceneDesc", emitter: Emitter) -> int:
+    """Insert a non-area luminaire where Scene::getLuminaires() has it: after the other scene-level luminaires
+    and before every area luminaire (those are appended by Scene::initialize, scene.cpp:296-299)."""
+    assert emitter.type != EMITTER_AREA
+    at = 0
+    while at < len(scene.emitters) and scene.emitters[at].type != EMITTER_AREA:
+        at += 1
+    scene.emitters.insert(at, emitter)
+    for s in scene.shapes:
+        if s.emitter >= at:
+            s.emitter += 1
+    return at
 
 
 @dataclass
@@ -193,7 +291,7 @@ def write_scene(path: str, scene: SceneDesc) -> None:
     cx, cy, cw, ch = scene.crop_rect
     with open(path, "wb") as f:
         f.write(b"MTSB200\0")
-        f.write(struct.pack("<I", 1))
+        f.write(struct.pack("<I", 2))
         f.write(np.ascontiguousarray(scene.camera_to_world, np.float32).tobytes())
         f.write(struct.pack("<5fI", scene.fov, scene.near_clip, scene.far_clip, scene.aperture_radius,
                             scene.focus_depth, int(scene.map_smaller_side)))
@@ -206,7 +304,8 @@ def write_scene(path: str, scene: SceneDesc) -> None:
             f.write(np.ascontiguousarray(m.p, np.float32).tobytes())
         f.write(struct.pack("<I", len(scene.emitters)))
         for e in scene.emitters:
-            f.write(struct.pack("<4f", *e.intensity, e.sampling_weight))
+            f.write(struct.pack("<4fI", *e.intensity, e.sampling_weight, e.type))
+            f.write(e.abi_params().tobytes()); f.write(e.aux_params().tobytes())
         f.write(struct.pack("<I", len(scene.shapes)))
         for s in scene.shapes:
             f.write(struct.pack("<2I2iI", len(s.positions), len(s.triangles), s.material, s.emitter,

@@ -8,7 +8,8 @@ from __future__ import annotations
 import numpy as np
 
 from .scenefile import (SceneDesc, Shape, Emitter, lambertian, microfacet, mirror, roughmetal,
-                        dielectric, twosided, phong, roughglass, look_at, MODE_PATH, MODE_DIRECT, FILTER_BOX)
+                        dielectric, twosided, phong, roughglass, look_at, point_light, spot_light, directional_light,
+                        constant_light, add_light, MODE_PATH, MODE_DIRECT, FILTER_BOX)
 
 F32 = np.float32
 
@@ -124,6 +125,24 @@ def icosphere(subdiv=2):
             nf += [[a, ab, ca], [b, bc, ab], [c, ca, bc], [ab, bc, ca]]
         v = np.array(verts, np.float64); f = np.array(nf, np.int64)
     return v, f
+
+
+def lights_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6, background=True) -> SceneDesc:
+    """The all-BSDF scene opened up (no ceiling, no side walls: a floor and a back wall remain) and lit by every
+    supported luminaire type: the two area lights, a point light, a spot light, a directional light and — with
+    `background` — a constant environment that camera rays and escaping bounce rays see."""
+    s = material_test_scene(width, height, spp, mode, max_depth)
+    floor = quad((8.0, 0, -2.0), (-2.5, 0, -2.0), (-2.5, 0, 5.592), (8.0, 0, 5.592), toward=(2.78, 2.73, 2.8))
+    back = quad((8.0, 0, 5.592), (-2.5, 0, 5.592), (-2.5, 5.488, 5.592), (8.0, 5.488, 5.592), toward=(2.78, 2.73, 2.8))
+    p, t, n = merge([floor, back])
+    s.shapes[0] = Shape(p, t, n, material=s.shapes[0].material)
+    del s.shapes[1:3]                                   # side walls; no shape below index 3 carried an emitter
+    add_light(s, point_light((0.8, 4.2, 1.0), (9.0, 7.0, 5.0)))
+    add_light(s, spot_light((5.2, 4.8, -0.5), (3.6, 1.2, 3.4), (0, 1, 0), (60.0, 70.0, 90.0), 25.0, 12.0, sampling_weight=1.5))
+    add_light(s, directional_light((-0.35, -1.0, 0.45), (0.9, 0.8, 0.7)))
+    if background:
+        add_light(s, constant_light((0.25, 0.3, 0.4), sampling_weight=0.75))
+    return s
 
 
 # --------------------------------------------------------------------------------------------

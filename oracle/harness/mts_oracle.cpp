@@ -252,6 +252,25 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 	for (size_t i = 0; i < s.materials.size(); ++i)
 		out.bsdfs.push_back(makeBSDF(s.materials[i]));
 
+	/* luminaires that are scene children (point.cpp, spot.cpp, directional.cpp, constant.cpp) */
+	for (size_t i = 0; i < s.emitters.size(); ++i) {
+		const sio::Emitter &e = s.emitters[i];
+		if (e.type == 0) continue;
+		static const char *names[5] = { "area", "point", "spot", "directional", "constant" };
+		if (e.type > 4) SLog(EError, "unknown emitter type %u", e.type);
+		Properties lp(names[e.type]);
+		lp.setSpectrum("intensity", rgb(e.intensity));
+		lp.setFloat("samplingWeight", e.samplingWeight);
+		if (e.type == 1 || e.type == 2)
+			lp.setTransform("toWorld", Transform(Matrix4x4(const_cast<float *>(e.aux))));
+		if (e.type == 2) { lp.setFloat("beamWidth", e.p[8]); lp.setFloat("cutoffAngle", e.p[9]); }
+		if (e.type == 3) lp.setPoint("direction", Point(e.aux[0], e.aux[1], e.aux[2]));   /* getVector reads the point-typed entry */
+		ref<Luminaire> lum = static_cast<Luminaire *>(create(MTS_CLASS(Luminaire), lp));
+		lum->configure();
+		scene->addChild("", lum);
+		lum->setParent(scene);
+	}
+
 	if (withGeometry) {
 		for (size_t i = 0; i < s.shapes.size(); ++i) {
 			const sio::Shape &sh = s.shapes[i];

@@ -14,7 +14,7 @@ namespace sio {
 enum MaterialType { MAT_LAMBERTIAN = 0, MAT_MICROFACET = 1, MAT_MIRROR = 2, MAT_ROUGHMETAL = 3, MAT_DIELECTRIC = 4 };
 
 struct Material { uint32_t type; float p[16]; };
-struct Emitter  { float intensity[3]; float samplingWeight; };
+struct Emitter  { float intensity[3]; float samplingWeight; uint32_t type; float p[11]; float aux[16]; };
 struct Shape {
 	uint32_t nVert, nTri; int32_t matId, emitId; uint32_t hasNormals;
 	std::vector<float> pos, nrm; std::vector<uint32_t> tri;
@@ -45,7 +45,7 @@ inline void load(const std::string &path, Scene &s) {
 	Reader r(path);
 	char magic[8]; r.raw(magic, 8);
 	if (memcmp(magic, "MTSB200", 8) != 0) throw std::runtime_error("bad magic in " + path);
-	if (r.get<uint32_t>() != 1) throw std::runtime_error("bad version in " + path);
+	if (r.get<uint32_t>() != 2) throw std::runtime_error("bad version in " + path);
 	r.raw(s.cameraToWorld, 64);
 	s.fov = r.get<float>(); s.nearClip = r.get<float>(); s.farClip = r.get<float>();
 	s.apertureRadius = r.get<float>(); s.focusDepth = r.get<float>();
@@ -60,7 +60,7 @@ inline void load(const std::string &path, Scene &s) {
 	s.materials.resize(r.get<uint32_t>());
 	for (auto &m : s.materials) { m.type = r.get<uint32_t>(); r.raw(m.p, 64); }
 	s.emitters.resize(r.get<uint32_t>());
-	for (auto &e : s.emitters) { r.raw(e.intensity, 12); e.samplingWeight = r.get<float>(); }
+	for (auto &e : s.emitters) { r.raw(e.intensity, 12); e.samplingWeight = r.get<float>(); e.type = r.get<uint32_t>(); r.raw(e.p, 44); r.raw(e.aux, 64); }
 	s.shapes.resize(r.get<uint32_t>());
 	for (auto &sh : s.shapes) {
 		sh.nVert = r.get<uint32_t>(); sh.nTri = r.get<uint32_t>();

@@ -64,6 +64,9 @@ def main():
     ms = gc.scene_materials()
     q = gc.emitter_queries(ms, 4000)
     save("emitter", queries_digest=gc.digest(q), out=oracle_util.Session(ms).emitter(q))
+    ls = gc.scene_lights()                             # point, spot, directional, constant + the two area lights
+    q = gc.emitter_queries(ls, 6000)
+    save("emitter_lights", queries_digest=gc.digest(q), out=oracle_util.Session(ls).emitter(q))
     # ---- camera -------------------------------------------------------------------------------------
     for ap in (0.0, 0.05):
         cs = gc.camera_scene(ap)

@@ -9,6 +9,10 @@ def scene_materials():
     return scenes.material_test_scene(32, 32, 1)
 
 
+def scene_lights():
+    return scenes.lights_test_scene(32, 32, 1)
+
+
 def scene_grid():
     return scenes.microbench_scene(cells=64, pad_cells=9)
 

@@ -68,6 +68,18 @@ def test_emitter_and_camera_match_golden(gpu_ctx_factory):
     out = gpu_ctx_factory(ms).emitter_sample(gc.emitter_queries(ms, 4000))
     ref = gold("emitter")["out"]
     assert np.array_equal(out[:, 13], ref[:, 13]) and close(out[:, :15], ref[:, :15], 1e-5, 1e-6).all()
+    # point / spot / directional / constant luminaires next to the area lights; the reference leaves sRec.n of the
+    # delta luminaires unset, so those three columns are compared for the others only
+    ls = gc.scene_lights()
+    q = gc.emitter_queries(ls, 6000)
+    ref = gold("emitter_lights")
+    assert gc.digest(q) == str(ref["queries_digest"])
+    out, ref = gpu_ctx_factory(ls).emitter_sample(q), ref["out"]
+    assert np.array_equal(out[:, 13], ref[:, 13]) and set(np.unique(ref[:, 13])) >= {0.0, 1.0, 2.0, 3.0, 4.0, 5.0}
+    cols = [c for c in range(15) if c not in (3, 4, 5)]
+    assert close(out[:, cols], ref[:, cols], 2e-5, 1e-6).all()
+    has_n = ref[:, 13] >= 3
+    assert close(out[has_n, 3:6], ref[has_n, 3:6], 1e-5, 1e-6).all()
     for ap, name in ((0.0, "camera_pinhole"), (0.05, "camera_thinlens")):
         cs = gc.camera_scene(ap)
         rays = gpu_ctx_factory(cs).camera_rays(gc.camera_samples(cs, 4000))

@@ -36,10 +36,11 @@ def test_plugin_fails_loudly_without_a_gpu(oracle):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode", [scenefile.MODE_PATH, scenefile.MODE_DIRECT])
-def test_plugin_renders_through_mitsuba(oracle, mode):
+@pytest.mark.parametrize("mode,lights", [(scenefile.MODE_PATH, False), (scenefile.MODE_DIRECT, False), (scenefile.MODE_PATH, True)])
+def test_plugin_renders_through_mitsuba(oracle, mode, lights):
     need_plugin()
-    s = scenes.material_test_scene(64, 64, 256, mode, max_depth=8)
+    # `lights`: point / spot / directional / constant luminaires, decoded by the plugin from Luminaire::serialize
+    s = (scenes.lights_test_scene if lights else scenes.material_test_scene)(64, 64, 256, mode, max_depth=8)
     s.filter_type = scenefile.FILTER_GAUSSIAN if mode == scenefile.MODE_DIRECT else scenefile.FILTER_BOX
     sess = oracle.Session(s)
     gpu, info = sess.render(2, "gpupath", env={"MTS_PLUGIN_PATH": PLUGIN_DIR})

@@ -66,6 +66,23 @@ def test_all_bsdfs_direct(oracle, gpu_ctx_factory):
     compare(s, oracle, gpu_ctx_factory, 64)
 
 
+def test_all_luminaire_types_path(oracle, gpu_ctx_factory):
+    """Area + point + spot + directional lights and a constant background seen by camera and bounce rays."""
+    s = scenes.lights_test_scene(64, 64, 64, scenefile.MODE_PATH, max_depth=8)
+    compare(s, oracle, gpu_ctx_factory, 64)
+
+
+def test_all_luminaire_types_direct(oracle, gpu_ctx_factory):
+    s = scenes.lights_test_scene(64, 64, 64, scenefile.MODE_DIRECT)
+    s.luminaire_samples, s.bsdf_samples = 2, 2
+    compare(s, oracle, gpu_ctx_factory, 64)
+
+
+def test_delta_lights_without_background_path(oracle, gpu_ctx_factory):
+    s = scenes.lights_test_scene(48, 48, 64, scenefile.MODE_PATH, max_depth=5, background=False)
+    compare(s, oracle, gpu_ctx_factory, 64)
+
+
 def test_direct_multi_sample_and_gaussian_filter(oracle, gpu_ctx_factory):
     s = scenes.material_test_scene(48, 48, 32, scenefile.MODE_DIRECT)
     s.luminaire_samples, s.bsdf_samples = 3, 2

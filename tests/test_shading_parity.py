@@ -89,6 +89,30 @@ def test_emitter_sampling(oracle, gpu_ctx_factory):
         assert ok.all(), f"column {c}: {np.count_nonzero(~ok)} mismatches, e.g. gpu={gpu[~ok][0, c]} ref={ref[~ok][0, c]}"
 
 
+def test_emitter_sampling_all_luminaire_types(oracle, gpu_ctx_factory):
+    """point.cpp:58-66, spot.cpp:85-125, directional.cpp:83-90, constant.cpp:72-90 through Scene::sampleLuminaire /
+    Scene::pdfLuminaire, next to the two area lights."""
+    scene = scenes.lights_test_scene(16, 16, 1)
+    ctx = gpu_ctx_factory(scene)
+    rng = np.random.Generator(np.random.PCG64(5))
+    lo, hi = scenes.scene_bounds(scene)
+    q = np.empty((30000, 5), np.float32)
+    q[:, :3] = lo + (hi - lo) * rng.random((len(q), 3))
+    q[:, 3:] = rng.random((len(q), 2))
+    ref = oracle.Session(scene).emitter(q)
+    gpu = ctx.emitter_sample(q)
+    assert np.array_equal(ref[:, 13], gpu[:, 13]), "selected luminaire / success flag differs"
+    assert set(np.unique(ref[:, 13])) >= {0.0, 1.0, 2.0, 3.0, 4.0, 5.0}
+    has_n = ref[:, 13] >= 3                      # the delta luminaires leave sRec.n unset in the reference
+    for c in range(15):
+        rows = has_n if c in (3, 4, 5) else np.ones(len(q), bool)
+        ok = close(gpu[rows, c], ref[rows, c], 2e-5, 1e-6)
+        assert ok.all(), f"column {c}: {np.count_nonzero(~ok)} mismatches, e.g. gpu={gpu[rows][~ok][0, c]} ref={ref[rows][~ok][0, c]}"
+    spot = ref[:, 13] == 1
+    inside = spot & (ref[:, 10] > 0)
+    assert inside.any() and (spot & (ref[:, 10] == 0)).any()          # both sides of the cone were exercised
+
+
 @pytest.mark.parametrize("aperture", [0.0, 0.05])
 def test_camera_rays(oracle, gpu_ctx_factory, aperture):
     scene = scenes.cornell_box(200, 120, 1)
