@@ -289,6 +289,26 @@ MTSGPU_API int mtsgpu_upload_serialized(mtsgpu_ctx *ctx, int shapeIndex, const c
                                         const float *toWorld, const float *toWorldInv, int faceNormals, int flipNormals,
                                         int materialId, int emitterId);
 
+/* ---- film development and image files (what follows the path) --------------------------------
+ * Film accumulators are cropH x cropW x {sum spec.rgb, sum alpha, sum weight} as mtsgpu_render returns them. */
+enum mtsgpu_film_format {
+	MTSGPU_FILM_EXR = 0,  /* EXRFilm::develop (src/films/exrfilm.cpp:156-210) + Bitmap::saveEXR (src/libcore/bitmap.cpp:599-628):
+	                         half RGBA scanline OpenEXR file, ZIP blocks; option = the film's `alpha` property; no banner */
+	MTSGPU_FILM_M = 1     /* MFilm::develop (src/films/mfilm.cpp:174-224): MATLAB matrix text; option = `spectra` property */
+};
+/* EXRFilm::develop's per-pixel normalisation on the GPU (exrfilm.cpp:163-176): rgba = cropH x cropW x 4 floats. */
+MTSGPU_API int mtsgpu_film_develop(mtsgpu_ctx *ctx, const float *film, int hasAlpha, float *rgba);
+/* The same with device pointers (exrfilm.cpp:163-176), for a film that mtsgpu_render_device left on the GPU. */
+MTSGPU_API int mtsgpu_film_develop_device(mtsgpu_ctx *ctx, const float *d_film, int hasAlpha, float *d_rgba);
+/* Film::develop(destFile) for the two film types above (exrfilm.cpp:156-210, mfilm.cpp:174-224): develops on the
+ * GPU (film may be a host or a device pointer) and writes the file. */
+MTSGPU_API int mtsgpu_film_save(mtsgpu_ctx *ctx, const float *film, int filmOnDevice, int format, int option, const char *path);
+/* File writers alone (host code, no GPU, no context; errors through mtsgpu_last_error(NULL)):
+ * Bitmap::saveEXR (src/libcore/bitmap.cpp:599-628) for width x height x 4 floats -> half A,B,G,R channels, and the text
+ * layout of MFilm::develop (src/films/mfilm.cpp:183-221) for width x height x channels (1 or 3) values. */
+MTSGPU_API int mtsgpu_write_exr(const char *path, const float *rgba, int width, int height);
+MTSGPU_API int mtsgpu_write_mfilm(const char *path, const float *values, int width, int height, int channels);
+
 /* Closest-hit query that also fills the Intersection record (fillIntersectionRecord<true>,
  * skdtree.h:352-432): out rows of 12 floats {p, geoFrame.n, shFrame.n, wi}; zeros on a miss. */
 MTSGPU_API int mtsgpu_intersect_full(mtsgpu_ctx *ctx, const float *rays, size_t n, mtsgpu_hit *hits, float *out);

@@ -27,8 +27,10 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_emitter_sample", "mtsgpu_camera_rays", "mtsgpu_film_splat", "mtsgpu_intersect_full",
     "mtsgpu_get_triaccel", "mtsgpu_accel_info_get", "mtsgpu_set_counters", "mtsgpu_get_counters",
     "mtsgpu_film_splat_static", "mtsgpu_render_multi", "mtsgpu_serialized_count", "mtsgpu_serialized_load",
-    "mtsgpu_serialized_free", "mtsgpu_serialized_save", "mtsgpu_upload_serialized",
+    "mtsgpu_serialized_free", "mtsgpu_serialized_save", "mtsgpu_upload_serialized", "mtsgpu_film_develop",
+    "mtsgpu_film_develop_device", "mtsgpu_film_save", "mtsgpu_write_exr", "mtsgpu_write_mfilm",
 ]
+FILM_EXR, FILM_M = 0, 1
 STATIC_SCRATCH_BYTES = 4 << 20
 
 
@@ -113,6 +115,11 @@ def load_library(path: Optional[str] = None):
     lib.mtsgpu_accel_info_get.argtypes = [vp, C.POINTER(AccelInfo)]
     lib.mtsgpu_set_counters.argtypes = [vp, C.c_int]
     lib.mtsgpu_get_counters.argtypes = [vp, C.POINTER(TraceCounters)]
+    lib.mtsgpu_film_develop.argtypes = [vp, vp, C.c_int, vp]
+    lib.mtsgpu_film_develop_device.argtypes = [vp, vp, C.c_int, vp]
+    lib.mtsgpu_film_save.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_char_p]
+    lib.mtsgpu_write_exr.argtypes = [C.c_char_p, vp, C.c_int, C.c_int]
+    lib.mtsgpu_write_mfilm.argtypes = [C.c_char_p, vp, C.c_int, C.c_int, C.c_int]
     for name in EXPORTED_SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("mtsgpu_destroy", "mtsgpu_last_error", "mtsgpu_version", "mtsgpu_serialized_free"):
@@ -330,8 +337,91 @@ class Context:
         self._check(self.lib.mtsgpu_intersect_full(self.h, self._ptr(rays), len(rays), self._ptr(hits), self._ptr(out)))
         return hits, out
 
+    def film_develop(self, film, has_alpha=True):
+        """EXRFilm::develop's normalisation on the GPU: accumulators [H,W,5] -> RGBA [H,W,4]."""
+        film = np.ascontiguousarray(film, np.float32)
+        out = np.empty(film.shape[:2] + (4,), np.float32)
+        self._check(self.lib.mtsgpu_film_develop(self.h, self._ptr(film), int(has_alpha), self._ptr(out)))
+        return out
+
+    def film_save(self, film, path, fmt=FILM_EXR, option=1, device_ptr=None):
+        """Film::develop(destFile): `film` is a host array, or pass `device_ptr` for a film left on the GPU."""
+        if device_ptr is not None:
+            self._check(self.lib.mtsgpu_film_save(self.h, C.c_void_p(device_ptr), 1, fmt, int(option), path.encode()))
+        else:
+            film = np.ascontiguousarray(film, np.float32)
+            self._check(self.lib.mtsgpu_film_save(self.h, self._ptr(film), 0, fmt, int(option), path.encode()))
+
     def triaccel(self, n):
         rec = np.empty(n, TRIACCEL_DTYPE)
         box = np.zeros(6, np.float32)
         self._check(self.lib.mtsgpu_get_triaccel(self.h, self._ptr(rec), n, self._ptr(box)))
         return rec, box
+
+
+def write_exr(path, rgba):
+    """Bitmap::saveEXR layout (half A,B,G,R, ZIP) for an [H,W,4] float array; host only."""
+    lib = load_library()
+    a = np.ascontiguousarray(rgba, np.float32)
+    rc = lib.mtsgpu_write_exr(path.encode(), a.ctypes.data_as(C.c_void_p), a.shape[1], a.shape[0])
+    if rc != 0:
+        raise MtsGpuError(rc, lib.mtsgpu_last_error(None).decode())
+
+
+def write_mfilm(path, values):
+    """MFilm::develop text layout for [H,W] (luminance) or [H,W,3] (spectra) values; host only."""
+    lib = load_library()
+    a = np.ascontiguousarray(values, np.float32)
+    ch = 1 if a.ndim == 2 else a.shape[2]
+    rc = lib.mtsgpu_write_mfilm(path.encode(), a.ctypes.data_as(C.c_void_p), a.shape[1], a.shape[0], ch)
+    if rc != 0:
+        raise MtsGpuError(rc, lib.mtsgpu_last_error(None).decode())
+
+
+def read_exr(path):
+    """Minimal reader for the files write_exr produces (scanline, HALF channels, ZIP / ZIPS / uncompressed): returns
+    {channel name: [H,W] float16}. Used by the tests to check the writer; not a general OpenEXR reader."""
+    import struct
+    import zlib
+    d = open(path, "rb").read()
+    magic, version = struct.unpack_from("<ii", d, 0)
+    if magic != 20000630 or (version & 0xFF) != 2 or (version & ~0xFF):
+        raise ValueError("not a plain scanline OpenEXR file")
+    pos, attrs = 8, {}
+    while d[pos] != 0:
+        e = d.index(b"\0", pos); name = d[pos:e].decode(); pos = e + 1
+        e = d.index(b"\0", pos); typ = d[pos:e].decode(); pos = e + 1
+        size, = struct.unpack_from("<i", d, pos); pos += 4
+        attrs[name] = (typ, d[pos:pos + size]); pos += size
+    pos += 1
+    chans, c = [], attrs["channels"][1]
+    p = 0
+    while c[p] != 0:
+        e = c.index(b"\0", p); nm = c[p:e].decode(); p = e + 1
+        ptype, _, xs, ys = struct.unpack_from("<i4sii", c, p); p += 16
+        if ptype != 1 or xs != 1 or ys != 1:
+            raise ValueError("only HALF channels without subsampling")
+        chans.append(nm)
+    comp = attrs["compression"][1][0]
+    x0, y0, x1, y1 = struct.unpack("<4i", attrs["dataWindow"][1])
+    w, h = x1 - x0 + 1, y1 - y0 + 1
+    lines = {0: 1, 2: 1, 3: 16}[comp]
+    nblk = (h + lines - 1) // lines
+    offs = struct.unpack_from(f"<{nblk}Q", d, pos)
+    out = {nm: np.zeros((h, w), np.float16) for nm in chans}
+    for off in offs:
+        y, size = struct.unpack_from("<ii", d, off)
+        blob = d[off + 8:off + 8 + size]
+        rows = min(lines, y1 + 1 - y)
+        raw_size = rows * len(chans) * w * 2
+        if comp != 0 and size < raw_size:
+            t = np.frombuffer(zlib.decompress(blob), np.uint8).astype(np.int64)
+            t = np.cumsum(np.concatenate([t[:1], t[1:] - 128])) & 0xFF          # undo the delta predictor
+            half = (raw_size + 1) // 2
+            raw = np.empty(raw_size, np.uint8); raw[0::2] = t[:half]; raw[1::2] = t[half:]
+        else:
+            raw = np.frombuffer(blob, np.uint8)
+        v = raw.view(np.float16).reshape(rows, len(chans), w)
+        for k, nm in enumerate(chans):
+            out[nm][y - y0:y - y0 + rows] = v[:, k]
+    return out

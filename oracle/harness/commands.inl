@@ -279,8 +279,36 @@ static int cmdMeshSave(int argc, char **argv) {
 	return 0;
 }
 
+/* Run the reference's MFilm (src/films/mfilm.cpp) on given accumulators {r, g, b, alpha, weight} per pixel:
+ * putImageBlock, then develop() writes OUT.m exactly as a render would. */
+static int cmdDevelop(int argc, char **argv) {
+	if (argc < 7) { std::cerr << "develop ACCUM WIDTH HEIGHT OUT spectra(0|1)\n"; return 1; }
+	std::vector<float> acc = sio::loadFloats(argv[2]);
+	const int w = atoi(argv[3]), h = atoi(argv[4]);
+	if (acc.size() != (size_t) w * h * 5) { std::cerr << "accumulator size mismatch\n"; return 1; }
+	Properties fp("mfilm");
+	fp.setInteger("width", w); fp.setInteger("height", h);
+	fp.setBoolean("spectra", atoi(argv[6]) != 0);
+	ref<Film> film = static_cast<Film *>(PluginManager::getInstance()->createObject(MTS_CLASS(Film), fp));
+	film->configure();
+	ref<ImageBlock> block = new ImageBlock(Vector2i(w, h), 0, true, true, false, false);
+	block->setOffset(Point2i(0, 0));
+	block->setSize(Vector2i(w, h));
+	block->clear();
+	for (size_t i = 0; i < (size_t) w * h; ++i) {
+		Spectrum s; s.fromLinearRGB(acc[i * 5], acc[i * 5 + 1], acc[i * 5 + 2]);
+		block->setPixel(i, s);
+		block->setWeight(i, acc[i * 5 + 4]);
+	}
+	film->clear();
+	film->putImageBlock(block);
+	film->develop(argv[5]);
+	printf("{\"cmd\": \"develop\", \"pixels\": %d}\n", w * h);
+	return 0;
+}
+
 static int dispatch(int argc, char **argv) {
-	if (argc < 2) { std::cerr << "usage: mts_oracle trace|triaccel|bsdf|emitter|camera|splat|render|mesh|meshsave ...\n"; return 1; }
+	if (argc < 2) { std::cerr << "usage: mts_oracle trace|triaccel|bsdf|emitter|camera|splat|render|mesh|meshsave|develop ...\n"; return 1; }
 	std::string cmd = argv[1];
 	if (cmd == "trace") return cmdTraceImpl(argc, argv);
 	if (cmd == "triaccel") return cmdTriAccel(argc, argv);
@@ -291,6 +319,7 @@ static int dispatch(int argc, char **argv) {
 	if (cmd == "render") return cmdRender(argc, argv);
 	if (cmd == "mesh") return cmdMesh(argc, argv);
 	if (cmd == "meshsave") return cmdMeshSave(argc, argv);
+	if (cmd == "develop") return cmdDevelop(argc, argv);
 	std::cerr << "unknown command " << cmd << "\n";
 	return 1;
 }

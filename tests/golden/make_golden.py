@@ -53,6 +53,10 @@ def main():
         m = oracle_util.load_serialized(path, 1, to_world=gc.SERIALIZED_TO_WORLD)
         fx["mesh1_xf_positions"], fx["mesh1_xf_normals"], fx["mesh1_xf_triangles"] = m["positions"], m["normals"], m["triangles"]
     save("serialized", **fx)
+    # ---- MFilm::develop text for fixed accumulators ------------------------------------------------------------------
+    acc = gc.film_accumulators()
+    save("mfilm", acc_digest=gc.digest(acc), luminance=np.frombuffer(oracle_util.develop_mfilm(acc, False), np.uint8),
+         spectra=np.frombuffer(oracle_util.develop_mfilm(acc, True), np.uint8))
     # ---- TriAccel records + enlarged scene box --------------------------------------------------------
     rec, box, _ = oracle_util.Session(gc.scene_materials()).triaccel()
     save("triaccel_materials", records=rec.view(np.uint8), box=box)

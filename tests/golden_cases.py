@@ -163,3 +163,21 @@ def mesh_digest(m):
         if m.get(k) is not None:
             parts.append(np.ascontiguousarray(m[k], np.float32))
     return digest(*parts)
+
+
+# ---- film development ------------------------------------------------------------------------------------------
+def film_accumulators(h=9, w=13, seed=31):
+    """Accumulators {sum rgb, sum alpha, sum weight} with the awkward cases: zero weight, tiny and huge values,
+    a negative lobe (gaussian filters never produce one, tabulated ones with negative lobes would)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    a = np.empty((h, w, 5), np.float32)
+    wt = rng.integers(1, 64, (h, w)).astype(np.float32) * np.float32(0.37)
+    a[..., :3] = rng.random((h, w, 3)).astype(np.float32) * wt[..., None] * np.float32(2.5)
+    a[..., 3] = rng.random((h, w)).astype(np.float32) * wt
+    a[..., 4] = wt
+    a[0, 0] = 0                                   # untouched pixel: weight 0
+    a[1, 2, :3] = (1e-7, 3e-6, 2e-8)
+    a[2, 3, :3] = (7e4, 1.2e5, 3e3); a[2, 3, 4] = 1.0      # beyond the half range
+    a[3, 1, :3] = (-0.5, 0.25, -1e-3)
+    a[4, 4, 4] = 0.0                              # colour without weight
+    return a

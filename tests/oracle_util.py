@@ -56,6 +56,16 @@ def load_serialized(path, shape_index=0, face_normals=False, flip_normals=False,
     return {"positions": pos, "normals": nrm, "texcoords": uv, "triangles": tri}
 
 
+def develop_mfilm(accum, spectra=False, variant="parity"):
+    """The text file the reference's MFilm::develop writes for the accumulators [H,W,5]."""
+    a = np.ascontiguousarray(accum, np.float32)
+    with tempfile.TemporaryDirectory(prefix="mtsoracle_") as d:
+        inp, out = os.path.join(d, "acc.bin"), os.path.join(d, "film.m")
+        a.tofile(inp)
+        _run(["develop", inp, a.shape[1], a.shape[0], out, int(spectra)], variant)
+        return open(out, "rb").read()
+
+
 def save_serialized(scene, path, variant="parity"):
     """Every mesh of `scene` written by the reference's TriMesh::serialize + offset table."""
     from mitsuba_renderer_b200 import scenefile
