@@ -11,9 +11,11 @@
 // Only hit results must agree with the reference's kd-tree, not the tree.
 #include "context.h"
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #include <algorithm>
 #include <cfloat>
 #include <cstdlib>
+#include <cstring>
 
 namespace {
 
@@ -181,39 +183,42 @@ __global__ void k_refit(const uint32_t *sortedIdx, const float4 *triLo, const fl
 	}
 }
 
-__device__ __forceinline__ int subtreeCount(int node, int n, const int2 *range) {
-	if (node >= n - 1) return 1;
-	const int2 r = range[node];
-	return r.y - r.x + 1;
-}
-__device__ __forceinline__ int subtreeFirst(int node, int n, const int2 *range) {
-	return node >= n - 1 ? node - (n - 1) : range[node].x;
+// Subtree sizes of the radix tree (leaves 1, inner nodes from their key range)
+__global__ void k_counts_from_range(const int2 *range, int n, int *count) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= 2 * n - 1) return;
+	count[i] = i >= n - 1 ? 1 : range[i].y - range[i].x + 1;
 }
 __device__ __forceinline__ float halfArea(const float4 &lo, const float4 &hi) {
 	const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
 	return dx * dy + dy * dz + dz * dx;
 }
 
-__global__ void k_collapse(const uint2 *qIn, uint32_t nIn, uint2 *qOut, uint32_t *qOutCount, uint32_t *nodeCount,
-		int n, const int2 *children, const int2 *range, const float4 *boxLo, const float4 *boxHi, BVH4Node *nodes) {
+// Queue item: {binary node, index of the 4-wide node to fill, position of the subtree's first triangle in the
+// final (depth-first) triangle order}. The order is written here, leaf by leaf: `order[pos]` = original triangle.
+__global__ void k_collapse(const uint4 *qIn, uint32_t nIn, uint4 *qOut, uint32_t *qOutCount, uint32_t *nodeCount,
+		int n, const int2 *children, const int *count, const uint32_t *sortedIdx, const float4 *boxLo, const float4 *boxHi,
+		BVH4Node *nodes, uint32_t *order) {
 	const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
 	if (w >= nIn) return;
-	const uint2 item = qIn[w];
-	int ch[4]; int cnt;
+	const uint4 item = qIn[w];
+	int ch[4]; uint32_t first[4]; int cnt;
 	{
 		const int2 c = children[item.x];
 		ch[0] = c.x; ch[1] = c.y; cnt = 2;
+		first[0] = item.z; first[1] = item.z + (uint32_t) count[c.x];
 	}
 	while (cnt < 4) {
 		int best = -1; float bestArea = -1.0f;
 		for (int i = 0; i < cnt; ++i) {
-			if (subtreeCount(ch[i], n, range) <= BVH_LEAF_MAX) continue;
+			if (count[ch[i]] <= BVH_LEAF_MAX) continue;
 			const float a = halfArea(boxLo[ch[i]], boxHi[ch[i]]);
 			if (a > bestArea) { bestArea = a; best = i; }
 		}
 		if (best < 0) break;
 		const int2 c = children[ch[best]];
-		ch[best] = c.x; ch[cnt++] = c.y;
+		ch[best] = c.x; ch[cnt] = c.y;
+		first[cnt++] = first[best] + (uint32_t) count[c.x];
 	}
 	float lo[3][4], hi[3][4]; uint32_t cw[4];
 	for (int i = 0; i < 4; ++i) {
@@ -225,13 +230,20 @@ __global__ void k_collapse(const uint2 *qIn, uint32_t nIn, uint2 *qOut, uint32_t
 		}
 		const float4 l = boxLo[ch[i]], h = boxHi[ch[i]];
 		lo[0][i] = l.x; lo[1][i] = l.y; lo[2][i] = l.z; hi[0][i] = h.x; hi[1][i] = h.y; hi[2][i] = h.z;
-		const int c = subtreeCount(ch[i], n, range);
+		const int c = count[ch[i]];
 		if (c <= BVH_LEAF_MAX) {
-			cw[i] = BVH_LEAF | ((uint32_t) (c - 1) << 28) | (uint32_t) subtreeFirst(ch[i], n, range);
+			cw[i] = BVH_LEAF | ((uint32_t) (c - 1) << 28) | first[i];
+			int stack[8]; int sp = 0; uint32_t k = first[i];          // the subtree's triangles, left to right
+			stack[sp++] = ch[i];
+			while (sp > 0) {
+				const int x = stack[--sp];
+				if (x >= n - 1) order[k++] = sortedIdx[x - (n - 1)];
+				else { const int2 cc = children[x]; stack[sp++] = cc.y; stack[sp++] = cc.x; }
+			}
 		} else {
 			const uint32_t idx = atomicAdd(nodeCount, 1u);
 			cw[i] = idx;
-			qOut[atomicAdd(qOutCount, 1u)] = make_uint2((uint32_t) ch[i], idx);
+			qOut[atomicAdd(qOutCount, 1u)] = make_uint4((uint32_t) ch[i], idx, first[i], 0u);
 		}
 	}
 	BVH4Node nd;
@@ -244,6 +256,88 @@ __global__ void k_collapse(const uint2 *qIn, uint32_t nIn, uint2 *qOut, uint32_t
 	nd.child = make_uint4(cw[0], cw[1], cw[2], cw[3]);
 	nd.pad = make_uint4(0, 0, 0, 0);
 	nodes[item.y] = nd;
+}
+
+// ---- PLOC: parallel locally-ordered clustering (Meister & Bittner 2018) -------------------------------------------
+// Bottom-up agglomeration along the Morton order: every cluster looks `r` neighbours to each side for the partner
+// that gives the smallest merged box, mutual choices merge, the survivors are compacted, repeat. Better trees than
+// the radix tree (merges follow surface area, not key bits) for a few more milliseconds of build.
+// Node numbering: leaves n-1+l as in the radix tree; inner nodes are created upwards from 0, so the root is n-2.
+#define PLOC_BLOCK 256
+#define PLOC_MAX_RADIUS 32
+
+__global__ void k_ploc_init(const uint32_t *sortedIdx, const float4 *triLo, const float4 *triHi, int n, float pad,
+		float4 *boxLo, float4 *boxHi, int *count, int *cluster) {
+	const int l = blockIdx.x * blockDim.x + threadIdx.x;
+	if (l >= n) return;
+	const uint32_t g = sortedIdx[l];
+	float4 lo = triLo[g], hi = triHi[g];
+	lo.x -= pad; lo.y -= pad; lo.z -= pad; hi.x += pad; hi.y += pad; hi.z += pad;      // same conservative pad as k_refit
+	boxLo[n - 1 + l] = lo; boxHi[n - 1 + l] = hi;
+	count[n - 1 + l] = 1;
+	cluster[l] = n - 1 + l;
+}
+
+__global__ void __launch_bounds__(PLOC_BLOCK)
+k_ploc_nn(const int *cluster, int m, const float4 *boxLo, const float4 *boxHi, int r, int *nn) {
+	__shared__ float slo[3][PLOC_BLOCK + 2 * PLOC_MAX_RADIUS], shi[3][PLOC_BLOCK + 2 * PLOC_MAX_RADIUS];
+	const int base = blockIdx.x * PLOC_BLOCK - r;
+	for (int t = threadIdx.x; t < PLOC_BLOCK + 2 * r; t += PLOC_BLOCK) {
+		const int j = base + t;
+		if (j >= 0 && j < m) {
+			const int c = cluster[j];
+			const float4 lo = boxLo[c], hi = boxHi[c];
+			slo[0][t] = lo.x; slo[1][t] = lo.y; slo[2][t] = lo.z; shi[0][t] = hi.x; shi[1][t] = hi.y; shi[2][t] = hi.z;
+		}
+	}
+	__syncthreads();
+	const int i = blockIdx.x * PLOC_BLOCK + threadIdx.x;
+	if (i >= m) return;
+	const int ti = threadIdx.x + r;
+	const float lx = slo[0][ti], ly = slo[1][ti], lz = slo[2][ti], hx = shi[0][ti], hy = shi[1][ti], hz = shi[2][ti];
+	float bestArea = INFINITY; int best = -1;
+	for (int o = -r; o <= r; ++o) {
+		const int j = i + o;
+		if (o == 0 || j < 0 || j >= m) continue;
+		const int tj = ti + o;
+		const float dx = fmaxf(hx, shi[0][tj]) - fminf(lx, slo[0][tj]);
+		const float dy = fmaxf(hy, shi[1][tj]) - fminf(ly, slo[1][tj]);
+		const float dz = fmaxf(hz, shi[2][tj]) - fminf(lz, slo[2][tj]);
+		const float a = dx * dy + dy * dz + dz * dx;
+		if (a < bestArea) { bestArea = a; best = j; }          // ascending j: ties keep the smaller index
+	}
+	nn[i] = best;
+}
+
+// flags: low word 1 if the cluster survives this round (not the higher-indexed half of a merging pair), high word
+// 1 if it is the lower-indexed half of a merging pair (a new node is created in its place)
+__global__ void k_ploc_flags(const int *nn, int m, unsigned long long *flags) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= m) return;
+	const int j = nn[i];
+	const bool mutual = j >= 0 && nn[j] == i;
+	const unsigned long long valid = (mutual && i > j) ? 0ull : 1ull, merge = (mutual && i < j) ? 1ull : 0ull;
+	flags[i] = valid | (merge << 32);
+}
+
+__global__ void k_ploc_apply(const int *cluster, int m, const int *nn, const unsigned long long *flags, const unsigned long long *pos,
+		int nextId, int2 *children, float4 *boxLo, float4 *boxHi, int *count, int *clusterOut) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= m) return;
+	const unsigned long long f = flags[i];
+	if (!(f & 1ull)) return;
+	int id = cluster[i];
+	if (f >> 32) {
+		const int other = cluster[nn[i]];
+		const int nid = nextId + (int) (pos[i] >> 32);
+		children[nid] = make_int2(id, other);
+		const float4 al = boxLo[id], ah = boxHi[id], bl = boxLo[other], bh = boxHi[other];
+		boxLo[nid] = make_float4(fminf(al.x, bl.x), fminf(al.y, bl.y), fminf(al.z, bl.z), 0);
+		boxHi[nid] = make_float4(fmaxf(ah.x, bh.x), fmaxf(ah.y, bh.y), fmaxf(ah.z, bh.z), 0);
+		count[nid] = count[id] + count[other];
+		id = nid;
+	}
+	clusterOut[(uint32_t) (pos[i] & 0xFFFFFFFFull)] = id;
 }
 
 __global__ void k_reorder(const uint32_t *sortedIdx, const TriAccelRec *orig, uint32_t n, TriAccelRec *sorted) {
@@ -524,24 +618,72 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	const uint64_t *keys = dKeys.as<uint64_t>();
 	const uint32_t *sortedIdx = dVals.as<uint32_t>();
 
-	// ---- binary radix tree + refit ----
+	// ---- binary tree: the radix tree + refit (default), or PLOC (MTSGPU_BUILDER=ploc). Measured on B200: PLOC with
+	//      r = 16 buys 2-4 % of traversal time on the 10M-triangle scene and nothing on the 1M-triangle grid (both are
+	//      regular meshes, which Morton order already clusters well) for 10x the build time, so it stays an option.
+	const char *builderEnv = getenv("MTSGPU_BUILDER");
+	const bool usePloc = builderEnv && strcmp(builderEnv, "ploc") == 0 && n > 1;
+	int plocRadius = getenv("MTSGPU_PLOC_RADIUS") ? atoi(getenv("MTSGPU_PLOC_RADIUS")) : 16;
+	plocRadius = std::max(1, std::min(plocRadius, PLOC_MAX_RADIUS));
+	int rootNode = 0;
 	const size_t nBin = 2 * nTri - 1;
+	DevBuf dCount, dOrder;
+	CUDA_TRY(ctx, dCount.alloc(nBin * sizeof(int)));
+	CUDA_TRY(ctx, dOrder.alloc(nTri * sizeof(uint32_t)));
 	CUDA_TRY(ctx, dChildren.alloc(std::max<size_t>(nTri - 1, 1) * sizeof(int2)));
 	CUDA_TRY(ctx, dRange.alloc(std::max<size_t>(nTri - 1, 1) * sizeof(int2)));
 	CUDA_TRY(ctx, dParent.alloc(nBin * sizeof(int)));
 	CUDA_TRY(ctx, dFlags.alloc(std::max<size_t>(nTri - 1, 1) * sizeof(int)));
 	CUDA_TRY(ctx, dBoxLo.alloc(nBin * sizeof(float4)));
 	CUDA_TRY(ctx, dBoxHi.alloc(nBin * sizeof(float4)));
-	CUDA_TRY(ctx, cudaMemsetAsync(dFlags.p, 0, dFlags.bytes, st));
-	CUDA_TRY(ctx, cudaMemsetAsync(dParent.p, 0xFF, nBin * sizeof(int), st));
-	if (n > 1) {
-		k_lbvh_hierarchy<<<blocksFor(nTri - 1, 256), 256, 0, st>>>(keys, n, dChildren.as<int2>(), dRange.as<int2>(), dParent.as<int>());
+	const float pad = 4e-6f * std::max(maxAbs, 1e-3f);
+	int plocRounds = 0;
+	if (usePloc) {
+		DevBuf dClusterA, dClusterB, dNN, dPFlags, dPPos, dScanTemp;
+		CUDA_TRY(ctx, dClusterA.alloc(nTri * sizeof(int))); CUDA_TRY(ctx, dClusterB.alloc(nTri * sizeof(int)));
+		CUDA_TRY(ctx, dNN.alloc(nTri * sizeof(int)));
+		CUDA_TRY(ctx, dPFlags.alloc((nTri + 1) * sizeof(unsigned long long))); CUDA_TRY(ctx, dPPos.alloc((nTri + 1) * sizeof(unsigned long long)));
+		size_t scanBytes = 0;
+		CUDA_TRY(ctx, cub::DeviceScan::ExclusiveSum(nullptr, scanBytes, dPFlags.as<unsigned long long>(), dPPos.as<unsigned long long>(), n + 1, st));
+		CUDA_TRY(ctx, dScanTemp.alloc(scanBytes));
+		k_ploc_init<<<blocksFor(nTri, 256), 256, 0, st>>>(sortedIdx, dTriLo.as<float4>(), dTriHi.as<float4>(), n, pad,
+			dBoxLo.as<float4>(), dBoxHi.as<float4>(), dCount.as<int>(), dClusterA.as<int>());
+		CUDA_TRY(ctx, cudaGetLastError());
+		int *cur = dClusterA.as<int>(), *nxt = dClusterB.as<int>();
+		int m = n, nextId = 0;
+		while (m > 1) {
+			k_ploc_nn<<<blocksFor(m, PLOC_BLOCK), PLOC_BLOCK, 0, st>>>(cur, m, dBoxLo.as<float4>(), dBoxHi.as<float4>(), plocRadius, dNN.as<int>());
+			k_ploc_flags<<<blocksFor(m, 256), 256, 0, st>>>(dNN.as<int>(), m, dPFlags.as<unsigned long long>());
+			CUDA_TRY(ctx, cudaMemsetAsync(dPFlags.as<unsigned long long>() + m, 0, sizeof(unsigned long long), st));   // pos[m] = totals
+			size_t tb = dScanTemp.bytes;
+			CUDA_TRY(ctx, cub::DeviceScan::ExclusiveSum(dScanTemp.p, tb, dPFlags.as<unsigned long long>(), dPPos.as<unsigned long long>(), m + 1, st));
+			k_ploc_apply<<<blocksFor(m, 256), 256, 0, st>>>(cur, m, dNN.as<int>(), dPFlags.as<unsigned long long>(), dPPos.as<unsigned long long>(),
+				nextId, dChildren.as<int2>(), dBoxLo.as<float4>(), dBoxHi.as<float4>(), dCount.as<int>(), nxt);
+			CUDA_TRY(ctx, cudaGetLastError());
+			unsigned long long totals = 0;
+			CUDA_TRY(ctx, cudaMemcpyAsync(&totals, dPPos.as<unsigned long long>() + m, sizeof(totals), cudaMemcpyDeviceToHost, st));
+			CUDA_TRY(ctx, cudaStreamSynchronize(st));
+			const int survivors = (int) (totals & 0xFFFFFFFFull), merges = (int) (totals >> 32);
+			REQUIRE(ctx, merges > 0 && survivors == m - merges, MTSGPU_ERR_CUDA, "PLOC made no progress (m=%d, merges=%d)", m, merges);
+			nextId += merges; m = survivors;
+			std::swap(cur, nxt);
+			plocRounds++;
+		}
+		REQUIRE(ctx, nextId == n - 1, MTSGPU_ERR_CUDA, "PLOC built %d inner nodes for %d triangles", nextId, n);
+		rootNode = n - 2;
+	} else {
+		CUDA_TRY(ctx, cudaMemsetAsync(dFlags.p, 0, dFlags.bytes, st));
+		CUDA_TRY(ctx, cudaMemsetAsync(dParent.p, 0xFF, nBin * sizeof(int), st));
+		if (n > 1) {
+			k_lbvh_hierarchy<<<blocksFor(nTri - 1, 256), 256, 0, st>>>(keys, n, dChildren.as<int2>(), dRange.as<int2>(), dParent.as<int>());
+			CUDA_TRY(ctx, cudaGetLastError());
+		}
+		k_refit<<<blocksFor(nTri, 256), 256, 0, st>>>(sortedIdx, dTriLo.as<float4>(), dTriHi.as<float4>(), n, pad,
+			dChildren.as<int2>(), dParent.as<int>(), dFlags.as<int>(), dBoxLo.as<float4>(), dBoxHi.as<float4>());
+		k_counts_from_range<<<blocksFor(nBin, 256), 256, 0, st>>>(dRange.as<int2>(), n, dCount.as<int>());
 		CUDA_TRY(ctx, cudaGetLastError());
 	}
-	const float pad = 4e-6f * std::max(maxAbs, 1e-3f);
-	k_refit<<<blocksFor(nTri, 256), 256, 0, st>>>(sortedIdx, dTriLo.as<float4>(), dTriHi.as<float4>(), n, pad,
-		dChildren.as<int2>(), dParent.as<int>(), dFlags.as<int>(), dBoxLo.as<float4>(), dBoxHi.as<float4>());
-	CUDA_TRY(ctx, cudaGetLastError());
+	(void) plocRounds;
 
 	// ---- collapse to 4-wide nodes ----
 	const size_t maxNodes = nTri + 1;
@@ -559,20 +701,22 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		nd.child = make_uint4(BVH_LEAF | 0u, BVH_EMPTY, BVH_EMPTY, BVH_EMPTY);
 		nd.pad = make_uint4(0, 0, 0, 0);
 		CUDA_TRY(ctx, cudaMemcpyAsync(dNodesTmp.p, &nd, sizeof(nd), cudaMemcpyHostToDevice, st));
+		CUDA_TRY(ctx, cudaMemcpyAsync(dOrder.p, sortedIdx, sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
 	} else {
 		const size_t qCap = nTri / 4 + 64;
-		CUDA_TRY(ctx, dQ0.alloc(qCap * sizeof(uint2))); CUDA_TRY(ctx, dQ1.alloc(qCap * sizeof(uint2)));
+		CUDA_TRY(ctx, dQ0.alloc(qCap * sizeof(uint4))); CUDA_TRY(ctx, dQ1.alloc(qCap * sizeof(uint4)));
 		CUDA_TRY(ctx, dCounts.alloc(2 * sizeof(uint32_t)));
-		uint2 rootItem = make_uint2(0u, 0u);
+		uint4 rootItem = make_uint4((uint32_t) rootNode, 0u, 0u, 0u);
 		CUDA_TRY(ctx, cudaMemcpyAsync(dQ0.p, &rootItem, sizeof(rootItem), cudaMemcpyHostToDevice, st));
 		uint32_t counts[2] = { 0u, 1u };   // [queue-out count, node count]
 		uint32_t nIn = 1;
-		uint2 *qIn = dQ0.as<uint2>(), *qOut = dQ1.as<uint2>();
+		uint4 *qIn = dQ0.as<uint4>(), *qOut = dQ1.as<uint4>();
 		while (nIn > 0) {
 			counts[0] = 0;
 			CUDA_TRY(ctx, cudaMemcpyAsync(dCounts.p, counts, sizeof(counts), cudaMemcpyHostToDevice, st));
 			k_collapse<<<blocksFor(nIn, 128), 128, 0, st>>>(qIn, nIn, qOut, dCounts.as<uint32_t>(), dCounts.as<uint32_t>() + 1,
-				n, dChildren.as<int2>(), dRange.as<int2>(), dBoxLo.as<float4>(), dBoxHi.as<float4>(), dNodesTmp.as<BVH4Node>());
+				n, dChildren.as<int2>(), dCount.as<int>(), sortedIdx, dBoxLo.as<float4>(), dBoxHi.as<float4>(), dNodesTmp.as<BVH4Node>(),
+				dOrder.as<uint32_t>());
 			CUDA_TRY(ctx, cudaGetLastError());
 			CUDA_TRY(ctx, cudaMemcpyAsync(counts, dCounts.p, sizeof(counts), cudaMemcpyDeviceToHost, st));
 			CUDA_TRY(ctx, cudaStreamSynchronize(st));
@@ -584,7 +728,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	}
 	CUDA_TRY(ctx, ctx->dNodes.alloc((size_t) nodeCount * sizeof(BVH4Node)));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dNodes.p, dNodesTmp.p, (size_t) nodeCount * sizeof(BVH4Node), cudaMemcpyDeviceToDevice, st));
-	k_reorder<<<blocksFor(nTri, 256), 256, 0, st>>>(sortedIdx, ctx->dTriAccelOrig.as<TriAccelRec>(), (uint32_t) nTri, ctx->dTriAccel.as<TriAccelRec>());
+	k_reorder<<<blocksFor(nTri, 256), 256, 0, st>>>(dOrder.as<uint32_t>(), ctx->dTriAccelOrig.as<TriAccelRec>(), (uint32_t) nTri, ctx->dTriAccel.as<TriAccelRec>());
 	CUDA_TRY(ctx, cudaGetLastError());
 	CUDA_TRY(ctx, cudaEventRecord(e1, st));
 	CUDA_TRY(ctx, cudaStreamSynchronize(st));

@@ -156,3 +156,21 @@ def test_full_size_matches_reference(oracle, gpu_ctx_factory):
         seg = scenes.shadow_segments(rays, scene)
         assert np.array_equal(sess.trace(seg, "any", threads)[0], ctx.trace(seg, TRACE_ANY))
         print(label, "ties", ties, info)
+
+
+@pytest.mark.gpu
+def test_ploc_builder_gives_the_same_hits(monkeypatch):
+    """MTSGPU_BUILDER=ploc (agglomerative build, csrc/bvh_build.cu) must not change any answer: same golden vectors."""
+    import os
+    from mitsuba_renderer_b200 import api
+    from tests import golden_cases as gc
+    monkeypatch.setenv("MTSGPU_BUILDER", "ploc")
+    for name, make in (("trace_materials", gc.scene_materials), ("trace_grid", gc.scene_grid)):
+        scene = make()
+        g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name + ".npz"))
+        rays = gc.trace_rays(scene)
+        ctx = api.Context(0)
+        ctx.upload_scene(scene)
+        check_closest(ctx.trace(rays, TRACE_CLOSEST), g["hits"].view(api.HIT_DTYPE).reshape(-1), name + " (ploc)")
+        assert np.array_equal(ctx.trace(scenes.shadow_segments(rays, scene), TRACE_ANY), g["any_segments"])
+        ctx.close()
