@@ -113,8 +113,18 @@ typedef struct mtsgpu_render_params {
 	uint32_t sppEnd;          /*   the multi-GPU shard; 0..sppTotal on one GPU */
 	uint32_t seed;            /* counter-based RNG key; streams are keyed by (pixel, global sample index) */
 	uint32_t importanceSampleLuminaires; /* Scene property, scene.cpp:51; default 1 */
+	uint32_t samplerType;     /* mtsgpu_sampler_type */
+	uint32_t samplerDepth;    /* ldsampler `depth` property (ldsampler.cpp:59): the first samplerDepth 1D and 2D draws of
+	                             every pixel sample come from the low-discrepancy sets, later ones are independent */
 	uint32_t reserved;
 } mtsgpu_render_params;
+
+/* MTSGPU_SAMPLER_INDEPENDENT: src/samplers/independent.cpp:72-81.
+ * MTSGPU_SAMPLER_LD: src/samplers/ldsampler.cpp:104-196 — per pixel and dimension a (0,2)-sequence (van der Corput /
+ * Sobol' radical inverses, XOR-scrambled) visited in a random order; sppTotal must be a power of two (the reference
+ * rounds the sample count up, ldsampler.cpp:61-65). Scrambles and orders are counter-based here too (keyed by pixel,
+ * dimension, seed), so the image does not depend on batching or on the GPU count. */
+enum mtsgpu_sampler_type { MTSGPU_SAMPLER_INDEPENDENT = 0, MTSGPU_SAMPLER_LD = 1 };
 
 typedef struct mtsgpu_stats {
 	uint64_t cameraRays;      /* "Camera ray generations" (perspective.cpp:24) */
@@ -308,6 +318,11 @@ MTSGPU_API int mtsgpu_film_save(mtsgpu_ctx *ctx, const float *film, int filmOnDe
  * layout of MFilm::develop (src/films/mfilm.cpp:183-221) for width x height x channels (1 or 3) values. */
 MTSGPU_API int mtsgpu_write_exr(const char *path, const float *rgba, int width, int height);
 MTSGPU_API int mtsgpu_write_mfilm(const char *path, const float *values, int width, int height, int channels);
+
+/* Test hook for the samplers (src/samplers/independent.cpp:72-81, ldsampler.cpp:104-196): the value pair that 2D draw
+ * number `draw` (0 = first next2D() of a pixel sample) returns for every sample 0..sppTotal-1 of pixel `pixel`
+ * (= y * width + x); out holds sppTotal x 2 floats. */
+MTSGPU_API int mtsgpu_sampler_values(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, uint32_t pixel, uint32_t draw, float *out);
 
 /* Closest-hit query that also fills the Intersection record (fillIntersectionRecord<true>,
  * skdtree.h:352-432): out rows of 12 floats {p, geoFrame.n, shFrame.n, wi}; zeros on a miss. */

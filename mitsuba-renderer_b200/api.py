@@ -28,8 +28,9 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_get_triaccel", "mtsgpu_accel_info_get", "mtsgpu_set_counters", "mtsgpu_get_counters",
     "mtsgpu_film_splat_static", "mtsgpu_render_multi", "mtsgpu_serialized_count", "mtsgpu_serialized_load",
     "mtsgpu_serialized_free", "mtsgpu_serialized_save", "mtsgpu_upload_serialized", "mtsgpu_film_develop",
-    "mtsgpu_film_develop_device", "mtsgpu_film_save", "mtsgpu_write_exr", "mtsgpu_write_mfilm",
+    "mtsgpu_film_develop_device", "mtsgpu_film_save", "mtsgpu_write_exr", "mtsgpu_write_mfilm", "mtsgpu_sampler_values",
 ]
+SAMPLER_INDEPENDENT, SAMPLER_LD = 0, 1
 FILM_EXR, FILM_M = 0, 1
 STATIC_SCRATCH_BYTES = 4 << 20
 
@@ -52,7 +53,8 @@ class RenderParams(C.Structure):
     _fields_ = [("mode", C.c_int32), ("maxDepth", C.c_int32), ("rrDepth", C.c_int32), ("strictNormals", C.c_int32),
                 ("luminaireSamples", C.c_int32), ("bsdfSamples", C.c_int32), ("sppTotal", C.c_uint32),
                 ("sppBegin", C.c_uint32), ("sppEnd", C.c_uint32), ("seed", C.c_uint32),
-                ("importanceSampleLuminaires", C.c_uint32), ("reserved", C.c_uint32)]
+                ("importanceSampleLuminaires", C.c_uint32), ("samplerType", C.c_uint32), ("samplerDepth", C.c_uint32),
+                ("reserved", C.c_uint32)]
 
 
 class Stats(C.Structure):
@@ -115,6 +117,7 @@ def load_library(path: Optional[str] = None):
     lib.mtsgpu_accel_info_get.argtypes = [vp, C.POINTER(AccelInfo)]
     lib.mtsgpu_set_counters.argtypes = [vp, C.c_int]
     lib.mtsgpu_get_counters.argtypes = [vp, C.POINTER(TraceCounters)]
+    lib.mtsgpu_sampler_values.argtypes = [vp, C.POINTER(RenderParams), C.c_uint32, C.c_uint32, vp]
     lib.mtsgpu_film_develop.argtypes = [vp, vp, C.c_int, vp]
     lib.mtsgpu_film_develop_device.argtypes = [vp, vp, C.c_int, vp]
     lib.mtsgpu_film_save.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_char_p]
@@ -266,6 +269,7 @@ class Context:
         p.luminaireSamples = scene.luminaire_samples; p.bsdfSamples = scene.bsdf_samples
         p.sppTotal = scene.spp; p.sppBegin = spp_begin; p.sppEnd = scene.spp if spp_end is None else spp_end
         p.seed = seed; p.importanceSampleLuminaires = 1
+        p.samplerType = getattr(scene, "sampler_type", 0); p.samplerDepth = getattr(scene, "sampler_depth", 3)
         return p
 
     def render(self, params: RenderParams):
@@ -336,6 +340,12 @@ class Context:
         out = np.zeros((len(rays), 12), np.float32)
         self._check(self.lib.mtsgpu_intersect_full(self.h, self._ptr(rays), len(rays), self._ptr(hits), self._ptr(out)))
         return hits, out
+
+    def sampler_values(self, params: RenderParams, pixel: int, draw: int):
+        """2D draw number `draw` of every sample of one pixel: [sppTotal, 2]."""
+        out = np.empty((params.sppTotal, 2), np.float32)
+        self._check(self.lib.mtsgpu_sampler_values(self.h, C.byref(params), pixel, draw, self._ptr(out)))
+        return out
 
     def film_develop(self, film, has_alpha=True):
         """EXRFilm::develop's normalisation on the GPU: accumulators [H,W,5] -> RGBA [H,W,4]."""

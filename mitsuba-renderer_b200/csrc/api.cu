@@ -255,6 +255,11 @@ int mtsgpu_trace(mtsgpu_ctx *ctx, const float *rays, size_t n, int mode, void *o
 }
 
 int mtsgpu_bsdf_eval(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out) { ENTER(ctx); return hookBsdfEval(ctx, queries, n, out); }
+int mtsgpu_sampler_values(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, uint32_t pixel, uint32_t draw, float *out) {
+	ENTER(ctx);
+	REQUIRE(ctx, params && out, MTSGPU_ERR_ARG, "sampler_values: null argument");
+	return hookSamplerValues(ctx, params, pixel, draw, out);
+}
 int mtsgpu_emitter_sample(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out) { ENTER(ctx); return hookEmitterSample(ctx, queries, n, out); }
 int mtsgpu_camera_rays(mtsgpu_ctx *ctx, const float *samples, size_t n, float *out) { ENTER(ctx); return hookCameraRays(ctx, samples, n, out); }
 int mtsgpu_film_splat(mtsgpu_ctx *ctx, const float *samples, size_t n, float *outFilm) { ENTER(ctx); return hookFilmSplat(ctx, samples, n, outFilm); }

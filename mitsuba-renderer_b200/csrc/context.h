@@ -89,6 +89,7 @@ int launchTrace(mtsgpu_ctx *ctx, const float4 *dRays, size_t n, int mode, void *
 // integrate.cu
 int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, volatile const int *cancel,
 	float *dOutFilm, mtsgpu_stats *stats);
+int hookSamplerValues(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, uint32_t pixel, uint32_t draw, float *out);
 int hookBsdfEval(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out);
 int hookEmitterSample(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out);
 int hookCameraRays(mtsgpu_ctx *ctx, const float *samples, size_t n, float *out);

@@ -56,6 +56,7 @@ struct BatchDesc {
 	uint32_t sampleBegin, sampleCount;   // global sample indices [sampleBegin, sampleBegin + sampleCount)
 	uint32_t slots;                      // tileCount * sampleCount * TILE_PIX
 	uint32_t seed;
+	SamplerConfig sampler;
 };
 
 struct IntegratorDev {
@@ -99,7 +100,7 @@ k_generate(const CameraDev cam, const FilmDev film, const BatchDesc b, WfArrays 
 		if (px < film.cropW && py < film.cropH) {
 			alive = true;
 			const int fx = px + film.cropX, fy = py + film.cropY;     // sensor pixel
-			Sampler smp; smp.init((uint32_t) (fy * film.width + fx), sample, b.seed);
+			Sampler smp; smp.init((uint32_t) (fy * film.width + fx), sample, b.seed, b.sampler);
 			float lx = 0, ly = 0, sx, sy;
 			if (cam.apertureRadius > 0.0f) smp.get2D(DIM_LENS, lx, ly);      // renderBlock: lens, time, then pixel sample
 			smp.get2D(DIM_PIXEL, sx, sy);
@@ -255,7 +256,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		V3 thr = v3(thr4), Li = v3(li4);
 		int px, py; uint32_t sample;
 		slotToPixel(b, film, slot, px, py, sample);
-		Sampler smp; smp.init((uint32_t) ((py + film.cropY) * film.width + px + film.cropX), sample, b.seed);
+		Sampler smp; smp.init((uint32_t) ((py + film.cropY) * film.width + px + film.cropX), sample, b.seed, b.sampler);
 
 		Isect its;
 		bool alive = valid;
@@ -302,7 +303,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 					bool survive = true;
 					if ((int) depth >= ig.rrDepth && !(flags & PF_PREV_TRANS)) {
 						const float approxAlbedo = fminf(0.9f, maxc(bsdfVal));
-						if (smp.get1D(DIM_BOUNCE(depth - 1, 2)) > approxAlbedo) survive = false;
+						if (smp.get1D(DIM_BOUNCE(depth - 1, 2), depth - (uint32_t) ig.rrDepth) > approxAlbedo) survive = false;
 						else thr = thr * (1.0f / approxAlbedo);
 					}
 					if (survive) { thr = thr * bsdfVal; depth++; }
@@ -512,6 +513,19 @@ static int uploadFilter(mtsgpu_ctx *ctx, DevBuf &dTable) {
 	return MTSGPU_OK;
 }
 
+static int makeSamplerConfig(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, SamplerConfig &cfg) {
+	REQUIRE(ctx, P->samplerType <= MTSGPU_SAMPLER_LD, MTSGPU_ERR_UNSUPPORTED, "render: unknown sampler type %u", P->samplerType);
+	cfg.type = P->samplerType; cfg.depth = P->samplerDepth; cfg.log2Count = 0;
+	cfg.lensDraw = (ctx->haveCamera && ctx->camera.apertureRadius > 0.0f) ? 1u : 0u;
+	if (cfg.type == MTSGPU_SAMPLER_LD) {
+		// the reference rounds the count up to a power of two and renders that many samples (ldsampler.cpp:61-65)
+		REQUIRE(ctx, P->sppTotal > 0 && (P->sppTotal & (P->sppTotal - 1)) == 0, MTSGPU_ERR_ARG,
+			"render: Sample count should be a power of two (got %u)", P->sppTotal);
+		while ((1u << cfg.log2Count) < P->sppTotal) cfg.log2Count++;
+	}
+	return MTSGPU_OK;
+}
+
 int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const int *cancel, float *dOutFilm, mtsgpu_stats *stats) {
 	REQUIRE(ctx, ctx->built, MTSGPU_ERR_ARG, "render: call mtsgpu_build_accel first");
 	REQUIRE(ctx, ctx->haveCamera && ctx->haveFilm, MTSGPU_ERR_ARG, "render: camera and film must be set");
@@ -519,6 +533,8 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 	REQUIRE(ctx, P->sppBegin <= P->sppEnd && P->sppEnd <= P->sppTotal, MTSGPU_ERR_ARG, "render: bad sample range [%u, %u) of %u", P->sppBegin, P->sppEnd, P->sppTotal);
 	if (P->mode == MTSGPU_MODE_DIRECT)
 		REQUIRE(ctx, P->luminaireSamples >= 0 && P->bsdfSamples >= 0 && P->luminaireSamples + P->bsdfSamples > 0, MTSGPU_ERR_ARG, "render: luminaireSamples + bsdfSamples must be > 0");
+	SamplerConfig samplerConfig;
+	{ int rc = makeSamplerConfig(ctx, P, samplerConfig); if (rc) return rc; }
 	cudaStream_t st = ctx->stream;
 	static const bool persistClosest = getenv("MTSGPU_WF_PERSIST_CLOSEST") ? atoi(getenv("MTSGPU_WF_PERSIST_CLOSEST")) != 0 : true;
 	static const bool persistShadow = getenv("MTSGPU_WF_PERSIST_SHADOW") ? atoi(getenv("MTSGPU_WF_PERSIST_SHADOW")) != 0 : false;
@@ -589,6 +605,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 				b.tileBegin = t0; b.tileCount = std::min(tilesPerBatch, nTiles - t0); b.tilesX = tilesX;
 				b.sampleBegin = P->sppBegin + s0; b.sampleCount = std::min(sampleChunk, spp - s0);
 				b.slots = b.tileCount * b.sampleCount * TILE_PIX; b.seed = P->seed;
+				b.sampler = samplerConfig;
 				int cur = 0;
 				wf.slotNext = slotBuf[cur]; wf.rayNext = rayBuf[cur];
 				CUDA_TRY(ctx, cudaMemsetAsync(wf.counters, 0, 8, st));
@@ -770,6 +787,31 @@ static int download(mtsgpu_ctx *ctx, void *dst, const DevBuf &buf, size_t bytes)
 	CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
 	CUDA_TRY(ctx, cudaGetLastError());
 	return MTSGPU_OK;
+}
+
+namespace {
+__global__ void k_hook_sampler(SamplerConfig cfg, uint32_t pixel, uint32_t draw, uint32_t seed, uint32_t n, float2 *out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	Sampler smp; smp.init(pixel, i, seed, cfg);
+	// dimension whose draw number is `draw`: lens, pixel, then the per-bounce luminaire / BSDF pairs
+	uint32_t dim;
+	if (cfg.lensDraw && draw == 0) dim = DIM_LENS;
+	else if (draw == cfg.lensDraw) dim = DIM_PIXEL;
+	else { const uint32_t k = draw - cfg.lensDraw - 1; dim = DIM_BOUNCE(k / 2, k % 2); }
+	float x, y; smp.get2D(dim, x, y);
+	out[i] = make_float2(x, y);
+}
+}
+
+int hookSamplerValues(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, uint32_t pixel, uint32_t draw, float *out) {
+	SamplerConfig cfg;
+	{ int rc = makeSamplerConfig(ctx, P, cfg); if (rc) return rc; }
+	const uint32_t n = P->sppTotal;
+	if (n == 0) return MTSGPU_OK;
+	CUDA_TRY(ctx, ctx->dStageOut.alloc((size_t) n * 8));
+	k_hook_sampler<<<blocksFor(n, 128), 128, 0, ctx->stream>>>(cfg, pixel, draw, P->seed, n, ctx->dStageOut.as<float2>());
+	return download(ctx, out, ctx->dStageOut, (size_t) n * 8);
 }
 
 int hookBsdfEval(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out) {

@@ -21,25 +21,98 @@ __host__ __device__ inline float uintToUnitFloat(uint32_t u) {
 	c.u = (u >> 9) | 0x3f800000u;
 	return c.f - 1.0f;
 }
+// Low-discrepancy mode (src/samplers/ldsampler.cpp:104-143): per pixel and draw number a scrambled (0,2)-sequence of
+// sppTotal points (van der Corput in x, Sobol' dimension 2 in y), visited in a per-pixel random order. The reference
+// draws the scrambles and the shuffle from its MT19937 stream; here both are functions of (pixel, draw, seed): the
+// scramble words by hashing, the order by a keyed bijection of the sample index (invertible steps on log2(N) bits).
+struct SamplerConfig {
+	uint32_t type;        // mtsgpu_sampler_type
+	uint32_t depth;       // ldsampler depth
+	uint32_t log2Count;   // log2(sppTotal) in LD mode
+	uint32_t lensDraw;    // 1 when the camera takes a lens sample first (renderBlock, integrator.cpp:216-224)
+};
+__host__ __device__ inline float ldVanDerCorput(uint32_t n, uint32_t scramble) {       // ldsampler.cpp:104-112
+	n = (n << 16) | (n >> 16);
+	n = ((n & 0x00ff00ffu) << 8) | ((n & 0xff00ff00u) >> 8);
+	n = ((n & 0x0f0f0f0fu) << 4) | ((n & 0xf0f0f0f0u) >> 4);
+	n = ((n & 0x33333333u) << 2) | ((n & 0xccccccccu) >> 2);
+	n = ((n & 0x55555555u) << 1) | ((n & 0xaaaaaaaau) >> 1);
+	n ^= scramble;
+	return (float) n / 4294967296.0f;
+}
+__host__ __device__ inline float ldSobol2(uint32_t n, uint32_t scramble) {              // ldsampler.cpp:114-118
+	for (uint32_t v = 1u << 31; n != 0; n >>= 1, v ^= v >> 1)
+		if (n & 1u) scramble ^= v;
+	return (float) scramble / 4294967296.0f;
+}
+__host__ __device__ inline uint32_t ldPermute(uint32_t i, uint32_t bits, uint32_t key) {
+	if (bits == 0) return 0;
+	const uint32_t mask = bits >= 32 ? 0xFFFFFFFFu : ((1u << bits) - 1u);
+	const uint32_t half = (bits + 1) / 2;
+	for (int round = 0; round < 4; ++round) {
+		i = (i + (key >> (round * 7))) & mask;          // each line is a bijection on `bits` bits
+		i = (i * (0x9E3779B1u | 1u)) & mask;
+		i ^= i >> half;
+		i = (i * ((key << 1) | 1u)) & mask;
+		i ^= i >> half;
+		key = key * 0x85EBCA6Bu + 0xC2B2AE35u;
+	}
+	return i;
+}
+
+#define DIM_LENS_ 0u
+#define DIM_PIXEL_ 2u
 struct Sampler {
-	uint64_t key;
-	__host__ __device__ void init(uint32_t pixel, uint32_t sample, uint32_t seed) {
-		key = splitmix64((((uint64_t) pixel << 32) | sample) + 0x9E3779B97F4A7C15ull * (uint64_t) (seed + 1));
+	uint64_t key, pixelKey;
+	uint32_t sample;
+	SamplerConfig cfg;
+	__host__ __device__ void init(uint32_t pixel, uint32_t sampleIndex, uint32_t seed, SamplerConfig config) {
+		key = splitmix64((((uint64_t) pixel << 32) | sampleIndex) + 0x9E3779B97F4A7C15ull * (uint64_t) (seed + 1));
+		pixelKey = splitmix64((((uint64_t) pixel << 32) | 0xFFFFFFFFu) + 0xD1B54A32D192ED03ull * (uint64_t) (seed + 1));
+		sample = sampleIndex; cfg = config;
+	}
+	// which next2D() / next1D() call of the pixel sample a dimension is (renderBlock, then Li)
+	__host__ __device__ uint32_t draw2D(uint32_t dim) const {
+		if (dim == DIM_LENS_) return 0;
+		if (dim == DIM_PIXEL_) return cfg.lensDraw;
+		return cfg.lensDraw + 1 + ((dim - 3u) / 3u) * 2u + ((dim - 3u) % 3u);        // bounce b: luminaire, then BSDF
 	}
 	// dimension pair `dim`: independent of call order, so no counter has to live in the path state
 	__host__ __device__ void get2D(uint32_t dim, float &x, float &y) const {
+		if (cfg.type == MTSGPU_SAMPLER_LD) {
+			const uint32_t draw = draw2D(dim);
+			if (draw < cfg.depth) { ld2D(draw, sample, x, y); return; }
+		}
 		const uint64_t z = splitmix64(key + 0x9E3779B97F4A7C15ull * (uint64_t) (dim + 1));
 		x = uintToUnitFloat((uint32_t) z);
 		y = uintToUnitFloat((uint32_t) (z >> 32));
 	}
-	__host__ __device__ float get1D(uint32_t dim) const { float x, y; get2D(dim, x, y); return x; }
+	__host__ __device__ void ld2D(uint32_t draw, uint32_t sampleIndex, float &x, float &y) const {
+		const uint64_t h = splitmix64(pixelKey + 0x9E3779B97F4A7C15ull * (uint64_t) (2 * draw + 1));
+		const uint64_t order = splitmix64(pixelKey + 0x9E3779B97F4A7C15ull * (uint64_t) (2 * draw + 2));
+		const uint32_t n = ldPermute(sampleIndex, cfg.log2Count, (uint32_t) order);
+		x = ldVanDerCorput(n, (uint32_t) h);
+		y = ldSobol2(n, (uint32_t) (h >> 32));
+	}
+	// 1D draws: only the roulette decision uses them; draw number = how far past rrDepth the path is
+	__host__ __device__ float get1D(uint32_t dim, uint32_t draw1D = 0xFFFFFFFFu) const {
+		if (cfg.type == MTSGPU_SAMPLER_LD && draw1D < cfg.depth) {
+			const uint64_t h = splitmix64(pixelKey + 0xA0761D6478BD642Full * (uint64_t) (2 * draw1D + 1));
+			const uint64_t order = splitmix64(pixelKey + 0xA0761D6478BD642Full * (uint64_t) (2 * draw1D + 2));
+			return ldVanDerCorput(ldPermute(sample, cfg.log2Count, (uint32_t) order), (uint32_t) h);
+		}
+		float x, y;
+		const uint64_t z = splitmix64(key + 0x9E3779B97F4A7C15ull * (uint64_t) (dim + 1));
+		x = uintToUnitFloat((uint32_t) z); y = 0; (void) y;
+		return x;
+	}
 };
 // dimension layout per pixel sample: 0 lens, 1 time, 2 pixel, then per bounce b (depth b+1):
 #define DIM_LENS 0u
 #define DIM_TIME 1u
 #define DIM_PIXEL 2u
 #define DIM_BOUNCE(b, k) (3u + 3u * (b) + (k))   // k: 0 luminaire 2D, 1 BSDF 2D, 2 roulette 1D
-#define DIM_DIRECT(round, k) (3u + 2u * (round) + (k))
+#define DIM_DIRECT(round, k) (3u + 3u * (round) + (k))
 
 // ---- camera: PerspectiveCameraImpl::generateRay (src/cameras/perspective.cpp:77-112) ----------
 __device__ inline void squareToDiskConcentric(float sx, float sy, float &ox, float &oy) {   // util.cpp:626-649

@@ -359,6 +359,29 @@ private:
 		P.luminaireSamples = m_luminaireSamples; P.bsdfSamples = m_bsdfSamples;
 		P.sppTotal = (uint32_t) sampler->getSampleCount(); P.sppBegin = 0; P.sppEnd = P.sppTotal;
 		P.seed = (uint32_t) m_seed; P.importanceSampleLuminaires = 1;
+		P.samplerType = MTSGPU_SAMPLER_INDEPENDENT; P.samplerDepth = 0;
+		{
+			const std::string samplerClass = sampler->getClass()->getName();
+			if (samplerClass == "LowDiscrepancySampler") {
+				/* m_depth has no getter: read it from LowDiscrepancySampler::serialize (ldsampler.cpp:76-80), which writes
+				   Sampler::serialize (sampler.cpp:39-49) first; the parent link (the camera) is cleared for the call */
+				Sampler *smp = const_cast<Sampler *>(sampler);
+				ConfigurableObject *parent = smp->getParent();
+				ref<MemoryStream> ms = new MemoryStream();
+				ref<InstanceManager> mgr = new InstanceManager();
+				smp->setParent(NULL);
+				smp->serialize(ms, mgr);
+				smp->setParent(parent);
+				ms->setPos(0);
+				if (ms->readUInt() != 0) Log(EError, "gpupath: unexpected sampler parent");
+				ms->readSize();
+				for (size_t k = ms->readSize(); k > 0; --k) ms->readUInt();
+				for (size_t k = ms->readSize(); k > 0; --k) ms->readUInt();
+				P.samplerType = MTSGPU_SAMPLER_LD; P.samplerDepth = (uint32_t) ms->readInt();
+			} else if (samplerClass != "IndependentSampler") {
+				Log(EError, "gpupath: sampler class \"%s\" is outside the supported hot path (independent, ldsampler)", samplerClass.c_str());
+			}
+		}
 		const size_t nPix = (size_t) csize.x * csize.y;
 		std::vector<float> accum(nPix * 5);
 		mtsgpu_stats stats;

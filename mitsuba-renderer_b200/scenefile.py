@@ -233,6 +233,8 @@ class SceneDesc:
     strict_normals: bool = False
     luminaire_samples: int = 1
     bsdf_samples: int = 1
+    sampler_type: int = 0            # 0 independent (src/samplers/independent.cpp), 1 ldsampler (src/samplers/ldsampler.cpp)
+    sampler_depth: int = 3           # ldsampler `depth`
     materials: List[Material] = field(default_factory=list)
     emitters: List[Emitter] = field(default_factory=list)
     shapes: List[Shape] = field(default_factory=list)
@@ -291,13 +293,14 @@ def write_scene(path: str, scene: SceneDesc) -> None:
     cx, cy, cw, ch = scene.crop_rect
     with open(path, "wb") as f:
         f.write(b"MTSB200\0")
-        f.write(struct.pack("<I", 2))
+        f.write(struct.pack("<I", 3))
         f.write(np.ascontiguousarray(scene.camera_to_world, np.float32).tobytes())
         f.write(struct.pack("<5fI", scene.fov, scene.near_clip, scene.far_clip, scene.aperture_radius,
                             scene.focus_depth, int(scene.map_smaller_side)))
         f.write(struct.pack("<7I", scene.width, scene.height, cx, cy, cw, ch, scene.filter_type))
         f.write(struct.pack("<2I2i3I", scene.spp, scene.mode, scene.max_depth, scene.rr_depth,
                             int(scene.strict_normals), scene.luminaire_samples, scene.bsdf_samples))
+        f.write(struct.pack("<2I", scene.sampler_type, scene.sampler_depth))
         f.write(struct.pack("<I", len(scene.materials)))
         for m in scene.materials:
             f.write(struct.pack("<I", m.type))

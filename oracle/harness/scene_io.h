@@ -26,6 +26,7 @@ struct Scene {
 	uint32_t mapSmallerSide;
 	uint32_t width, height, cropX, cropY, cropW, cropH, filterType;
 	uint32_t spp, mode; int32_t maxDepth, rrDepth; uint32_t strictNormals, nLumSamples, nBsdfSamples;
+	uint32_t samplerType, samplerDepth;
 	std::vector<Material> materials;
 	std::vector<Emitter> emitters;
 	std::vector<Shape> shapes;
@@ -45,7 +46,7 @@ inline void load(const std::string &path, Scene &s) {
 	Reader r(path);
 	char magic[8]; r.raw(magic, 8);
 	if (memcmp(magic, "MTSB200", 8) != 0) throw std::runtime_error("bad magic in " + path);
-	if (r.get<uint32_t>() != 2) throw std::runtime_error("bad version in " + path);
+	if (r.get<uint32_t>() != 3) throw std::runtime_error("bad version in " + path);
 	r.raw(s.cameraToWorld, 64);
 	s.fov = r.get<float>(); s.nearClip = r.get<float>(); s.farClip = r.get<float>();
 	s.apertureRadius = r.get<float>(); s.focusDepth = r.get<float>();
@@ -57,6 +58,7 @@ inline void load(const std::string &path, Scene &s) {
 	s.spp = r.get<uint32_t>(); s.mode = r.get<uint32_t>();
 	s.maxDepth = r.get<int32_t>(); s.rrDepth = r.get<int32_t>();
 	s.strictNormals = r.get<uint32_t>(); s.nLumSamples = r.get<uint32_t>(); s.nBsdfSamples = r.get<uint32_t>();
+	s.samplerType = r.get<uint32_t>(); s.samplerDepth = r.get<uint32_t>();
 	s.materials.resize(r.get<uint32_t>());
 	for (auto &m : s.materials) { m.type = r.get<uint32_t>(); r.raw(m.p, 64); }
 	s.emitters.resize(r.get<uint32_t>());

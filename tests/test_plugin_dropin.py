@@ -41,6 +41,8 @@ def test_plugin_renders_through_mitsuba(oracle, mode, lights):
     need_plugin()
     # `lights`: point / spot / directional / constant luminaires, decoded by the plugin from Luminaire::serialize
     s = (scenes.lights_test_scene if lights else scenes.material_test_scene)(64, 64, 256, mode, max_depth=8)
+    if lights:
+        s.sampler_type, s.sampler_depth = 1, 4          # ldsampler: the plugin reads `depth` from LowDiscrepancySampler::serialize
     s.filter_type = scenefile.FILTER_GAUSSIAN if mode == scenefile.MODE_DIRECT else scenefile.FILTER_BOX
     sess = oracle.Session(s)
     gpu, info = sess.render(2, "gpupath", env={"MTS_PLUGIN_PATH": PLUGIN_DIR})

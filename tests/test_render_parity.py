@@ -37,7 +37,11 @@ def compare(scene, oracle, gpu_ctx_factory, spp, ref_mult=16):
     assert abs(gpu[..., 4].sum() - cpu[..., 4].sum()) <= 1e-4 * cpu[..., 4].sum()
     assert abs(gpu[..., 3].sum() - cpu[..., 3].sum()) <= 0.01 * max(1.0, cpu[..., 3].sum())
     r, c, g, gh = develop(ref), develop(cpu), develop(gpu), develop(gpu_hi)
-    e_cpu, e_gpu = rel_mse(c, r), rel_mse(g, r)
+    # relMSE is heavy-tailed (one firefly next to a point light moves it by 40 %; measured spread over seeds
+    # 0.011-0.017 on the all-luminaires scene, on both sides): compare medians over several runs
+    e_gpu_all = [rel_mse(g, r)] + [rel_mse(develop(ctx.render(Context.params_from_scene(cpu_scene, seed=k))[0]), r) for k in (3, 5, 7, 9)]
+    e_cpu_all = [rel_mse(c, r)] + [rel_mse(develop(oracle.Session(cpu_scene).render()[0]), r) for _ in range(2)]
+    e_cpu, e_gpu = float(np.median(e_cpu_all)), float(np.median(e_gpu_all))
     lum = lambda im: float(im.mean())
     print(f"relMSE cpu@{spp}={e_cpu:.5f} gpu@{spp}={e_gpu:.5f} gpu@{spp*ref_mult} vs ref={rel_mse(gh, r):.5f} "
           f"mean ref={lum(r):.5f} gpu={lum(gh):.5f} stats={stats}")
