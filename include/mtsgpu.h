@@ -69,7 +69,20 @@ enum mtsgpu_bsdf_type {
 typedef struct mtsgpu_material {
 	uint32_t type;   /* mtsgpu_bsdf_type, optionally | MTSGPU_BSDF_TWOSIDED */
 	float p[16];
+	uint32_t texture[2]; /* 0: the spectrum in p[0..2] (slot 0) / p[3..5] (slot 1) is constant; k > 0: it is read from
+	                        texture k-1 of mtsgpu_upload_textures at the hit's uv (Texture::getValue(its), e.g.
+	                        lambertian.cpp:96-102). Slots that the reference keeps as plain spectra (mirror, dielectric,
+	                        roughmetal eta/k) cannot be textured. */
 } mtsgpu_material;
+
+/* 2D textures (src/librender/texture.cpp:43-82: uv' = uv * uvScale + uvOffset, then the texture's own lookup).
+ *   CHECKERBOARD  src/textures/checkerboard.cpp:28-55   p[0..2] brightColor, p[3..5] darkColor, p[6..7] uvOffset,
+ *                                                       p[8..9] uvScale */
+enum mtsgpu_texture_type { MTSGPU_TEXTURE_CHECKERBOARD = 0 };
+typedef struct mtsgpu_texture {
+	uint32_t type;   /* mtsgpu_texture_type */
+	float p[12];
+} mtsgpu_texture;
 
 /* Luminaires. List them in the order of Scene::getLuminaires(), which is the order of the luminaire CDF
  * (src/librender/scene.cpp:320-330): luminaires that are scene children come first, in the order they were added
@@ -165,6 +178,8 @@ MTSGPU_API int mtsgpu_upload_materials(mtsgpu_ctx *ctx, const mtsgpu_material *m
 
 /* Scene::getLuminaires() (include/mitsuba/render/scene.h:517-519) restricted to AreaLuminaire
  * (src/luminaires/area.cpp:35-83): intensity + Luminaire::getSamplingWeight. */
+/* Textures referenced by mtsgpu_material.texture (Texture2D::getValue, src/librender/texture.cpp:73-82). */
+MTSGPU_API int mtsgpu_upload_textures(mtsgpu_ctx *ctx, const mtsgpu_texture *textures, int count);
 MTSGPU_API int mtsgpu_upload_emitters(mtsgpu_ctx *ctx, const mtsgpu_emitter *emitters, int count);
 
 /* One TriMesh (include/mitsuba/render/trimesh.h:100-133) at kd-tree shape index `shapeIndex`
@@ -323,6 +338,11 @@ MTSGPU_API int mtsgpu_write_mfilm(const char *path, const float *values, int wid
  * number `draw` (0 = first next2D() of a pixel sample) returns for every sample 0..sppTotal-1 of pixel `pixel`
  * (= y * width + x); out holds sppTotal x 2 floats. */
 MTSGPU_API int mtsgpu_sampler_values(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, uint32_t pixel, uint32_t draw, float *out);
+
+/* Closest-hit query reporting the interpolated texture coordinates (fillIntersectionRecord, skdtree.h:408-415) and the
+ * two texture slots of the hit's material evaluated there: out rows of 8 floats {uv, slot 0 rgb, slot 1 rgb}; zeros
+ * on a miss or on a shape without a BSDF. */
+MTSGPU_API int mtsgpu_intersect_uv(mtsgpu_ctx *ctx, const float *rays, size_t n, float *out);
 
 /* Closest-hit query that also fills the Intersection record (fillIntersectionRecord<true>,
  * skdtree.h:352-432): out rows of 12 floats {p, geoFrame.n, shFrame.n, wi}; zeros on a miss. */

@@ -29,6 +29,7 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_film_splat_static", "mtsgpu_render_multi", "mtsgpu_serialized_count", "mtsgpu_serialized_load",
     "mtsgpu_serialized_free", "mtsgpu_serialized_save", "mtsgpu_upload_serialized", "mtsgpu_film_develop",
     "mtsgpu_film_develop_device", "mtsgpu_film_save", "mtsgpu_write_exr", "mtsgpu_write_mfilm", "mtsgpu_sampler_values",
+    "mtsgpu_upload_textures", "mtsgpu_intersect_uv",
 ]
 SAMPLER_INDEPENDENT, SAMPLER_LD = 0, 1
 FILM_EXR, FILM_M = 0, 1
@@ -42,7 +43,11 @@ class MtsGpuError(RuntimeError):
 
 
 class Material(C.Structure):
-    _fields_ = [("type", C.c_uint32), ("p", C.c_float * 16)]
+    _fields_ = [("type", C.c_uint32), ("p", C.c_float * 16), ("texture", C.c_uint32 * 2)]
+
+
+class Texture(C.Structure):
+    _fields_ = [("type", C.c_uint32), ("p", C.c_float * 12)]
 
 
 class Emitter(C.Structure):
@@ -100,6 +105,8 @@ def load_library(path: Optional[str] = None):
     lib.mtsgpu_version.restype = C.c_char_p
     lib.mtsgpu_upload_materials.argtypes = [vp, C.POINTER(Material), C.c_int]
     lib.mtsgpu_upload_emitters.argtypes = [vp, C.POINTER(Emitter), C.c_int]
+    lib.mtsgpu_upload_textures.argtypes = [vp, C.POINTER(Texture), C.c_int]
+    lib.mtsgpu_intersect_uv.argtypes = [vp, vp, C.c_size_t, vp]
     lib.mtsgpu_upload_mesh.argtypes = [vp, C.c_int, vp, vp, vp, C.c_uint32, vp, C.c_uint32, C.c_int, C.c_int]
     lib.mtsgpu_set_camera.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float]
     lib.mtsgpu_set_film.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_float, C.c_float]
@@ -215,10 +222,16 @@ class Context:
 
     # ---- scene upload -----------------------------------------------------------------------
     def upload_scene(self, scene: SceneDesc, build: bool = True):
+        texs = (Texture * max(1, len(scene.textures)))()
+        for i, t in enumerate(scene.textures):
+            texs[i].type = t.type
+            texs[i].p[:] = [float(v) for v in t.p]
+        self._check(self.lib.mtsgpu_upload_textures(self.h, texs, len(scene.textures)))
         mats = (Material * max(1, len(scene.materials)))()
         for i, m in enumerate(scene.materials):
             mats[i].type = m.type
             mats[i].p[:] = [float(v) for v in m.p]
+            mats[i].texture[:] = [int(v) for v in m.tex]
         self._check(self.lib.mtsgpu_upload_materials(self.h, mats, len(scene.materials)))
         ems = (Emitter * max(1, len(scene.emitters)))()
         for i, e in enumerate(scene.emitters):
@@ -231,7 +244,8 @@ class Context:
             pos = np.ascontiguousarray(s.positions, np.float32)
             nrm = None if s.normals is None else np.ascontiguousarray(s.normals, np.float32)
             tri = np.ascontiguousarray(s.triangles, np.uint32)
-            self._check(self.lib.mtsgpu_upload_mesh(self.h, i, self._ptr(pos), self._ptr(nrm), None, len(pos),
+            uv = None if s.texcoords is None else np.ascontiguousarray(s.texcoords, np.float32)
+            self._check(self.lib.mtsgpu_upload_mesh(self.h, i, self._ptr(pos), self._ptr(nrm), self._ptr(uv), len(pos),
                                                     self._ptr(tri), len(tri), s.material, s.emitter))
         self.set_camera(scene)
         self.set_film(scene)
@@ -361,6 +375,13 @@ class Context:
         else:
             film = np.ascontiguousarray(film, np.float32)
             self._check(self.lib.mtsgpu_film_save(self.h, self._ptr(film), 0, fmt, int(option), path.encode()))
+
+    def intersect_uv(self, rays):
+        """Closest hit -> rows {uv, texture slot 0 rgb, slot 1 rgb} of the hit's material at that uv."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        out = np.zeros((len(rays), 8), np.float32)
+        self._check(self.lib.mtsgpu_intersect_uv(self.h, self._ptr(rays), len(rays), self._ptr(out)))
+        return out
 
     def triaccel(self, n):
         rec = np.empty(n, TRIACCEL_DTYPE)

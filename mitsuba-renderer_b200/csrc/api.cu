@@ -86,6 +86,16 @@ int mtsgpu_upload_materials(mtsgpu_ctx *ctx, const mtsgpu_material *materials, i
 	return MTSGPU_OK;
 }
 
+int mtsgpu_upload_textures(mtsgpu_ctx *ctx, const mtsgpu_texture *textures, int count) {
+	ENTER(ctx);
+	REQUIRE(ctx, count >= 0 && (count == 0 || textures), MTSGPU_ERR_ARG, "upload_textures: bad arguments");
+	for (int i = 0; i < count; ++i)
+		REQUIRE(ctx, textures[i].type == MTSGPU_TEXTURE_CHECKERBOARD, MTSGPU_ERR_UNSUPPORTED, "texture %d: unsupported texture type %u", i, textures[i].type);
+	ctx->textures.assign(textures, textures + count);
+	ctx->built = false;
+	return MTSGPU_OK;
+}
+
 int mtsgpu_upload_emitters(mtsgpu_ctx *ctx, const mtsgpu_emitter *emitters, int count) {
 	ENTER(ctx);
 	REQUIRE(ctx, count >= 0 && (count == 0 || emitters), MTSGPU_ERR_ARG, "upload_emitters: bad arguments");
@@ -105,7 +115,6 @@ int mtsgpu_upload_emitters(mtsgpu_ctx *ctx, const mtsgpu_emitter *emitters, int 
 int mtsgpu_upload_mesh(mtsgpu_ctx *ctx, int shapeIndex, const float *positions, const float *normals, const float *texcoords,
 		uint32_t nVert, const uint32_t *triangles, uint32_t nTri, int materialId, int emitterId) {
 	ENTER(ctx);
-	(void) texcoords;
 	REQUIRE(ctx, positions && triangles && nVert > 0 && nTri > 0, MTSGPU_ERR_ARG, "upload_mesh: empty mesh (TriMesh::configure rejects these too)");
 	REQUIRE(ctx, shapeIndex >= 0 && (size_t) shapeIndex <= ctx->meshes.size(), MTSGPU_ERR_ARG,
 		"upload_mesh: shapes must be uploaded in kd-tree order (got %d, expected <= %zu)", shapeIndex, ctx->meshes.size());
@@ -114,6 +123,7 @@ int mtsgpu_upload_mesh(mtsgpu_ctx *ctx, int shapeIndex, const float *positions, 
 	m.nVert = nVert; m.nTri = nTri; m.materialId = materialId; m.emitterId = emitterId; m.hasNormals = normals != nullptr;
 	m.pos.assign(positions, positions + 3 * (size_t) nVert);
 	if (normals) m.nrm.assign(normals, normals + 3 * (size_t) nVert);
+	if (texcoords) m.uv.assign(texcoords, texcoords + 2 * (size_t) nVert);
 	m.tri.assign(triangles, triangles + 3 * (size_t) nTri);
 	ctx->meshes.push_back(std::move(m));
 	ctx->built = false;
@@ -260,6 +270,7 @@ int mtsgpu_sampler_values(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, u
 	REQUIRE(ctx, params && out, MTSGPU_ERR_ARG, "sampler_values: null argument");
 	return hookSamplerValues(ctx, params, pixel, draw, out);
 }
+int mtsgpu_intersect_uv(mtsgpu_ctx *ctx, const float *rays, size_t n, float *out) { ENTER(ctx); return hookIntersectUv(ctx, rays, n, out); }
 int mtsgpu_emitter_sample(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out) { ENTER(ctx); return hookEmitterSample(ctx, queries, n, out); }
 int mtsgpu_camera_rays(mtsgpu_ctx *ctx, const float *samples, size_t n, float *out) { ENTER(ctx); return hookCameraRays(ctx, samples, n, out); }
 int mtsgpu_film_splat(mtsgpu_ctx *ctx, const float *samples, size_t n, float *outFilm) { ENTER(ctx); return hookFilmSplat(ctx, samples, n, outFilm); }

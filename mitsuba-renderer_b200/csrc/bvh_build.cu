@@ -467,6 +467,9 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	// ---- flatten meshes (global vertex ids; float4-padded vertices for 128-bit loads) ----
 	std::vector<uint4> triIdx(nTri);
 	std::vector<float4> pos(nVert), nrm(nVert);
+	bool anyTexcoords = false;
+	for (auto &m : ctx->meshes) anyTexcoords |= !m.uv.empty();
+	std::vector<float2> uvs(anyTexcoords ? nVert : 1, make_float2(0, 0));
 	std::vector<ShapeInfo> shapes(nShapes);
 	std::vector<float> areaCdfAll;
 	std::vector<int> emitterShape(ctx->emitters.size(), -1);
@@ -478,6 +481,8 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		si.materialId = m.materialId; si.emitterId = m.emitterId;
 		si.triOffset = (uint32_t) tOff; si.vertOffset = (uint32_t) vOff;
 		si.nTri = m.nTri; si.nVert = m.nVert; si.hasNormals = m.hasNormals ? 1u : 0u;
+		si.hasTexcoords = m.uv.empty() ? 0u : 1u;
+		for (uint32_t v = 0; v < (m.uv.empty() ? 0u : m.nVert); ++v) uvs[vOff + v] = make_float2(m.uv[2*v], m.uv[2*v+1]);
 		REQUIRE(ctx, m.materialId < (int) ctx->materials.size(), MTSGPU_ERR_ARG, "shape %zu: material id %d out of range", s, m.materialId);
 		REQUIRE(ctx, m.emitterId < (int) ctx->emitters.size(), MTSGPU_ERR_ARG, "shape %zu: emitter id %d out of range", s, m.emitterId);
 		for (uint32_t v = 0; v < m.nVert; ++v) {
@@ -530,7 +535,19 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	for (size_t i = 0; i < ctx->materials.size(); ++i) {
 		mats[i].type = ctx->materials[i].type;
 		memcpy(mats[i].p, ctx->materials[i].p, 64);
+		for (int k = 0; k < 2; ++k) {
+			const uint32_t t = ctx->materials[i].texture[k];
+			REQUIRE(ctx, t <= ctx->textures.size(), MTSGPU_ERR_ARG, "material %zu: texture %u of slot %d was not uploaded", i, t, k);
+			const uint32_t bt = mats[i].type & MTSGPU_BSDF_TYPE_MASK;
+			const bool slotOk = k == 0 ? (bt != MTSGPU_BSDF_MIRROR && bt != MTSGPU_BSDF_DIELECTRIC)
+				: (bt == MTSGPU_BSDF_MICROFACET || bt == MTSGPU_BSDF_PHONG || bt == MTSGPU_BSDF_ROUGHGLASS);
+			REQUIRE(ctx, t == 0 || slotOk, MTSGPU_ERR_UNSUPPORTED, "material %zu: slot %d of this BSDF is a plain spectrum in the reference and cannot be textured", i, k);
+			mats[i].tex[k] = t;
+		}
 	}
+	std::vector<TextureDev> texs(std::max<size_t>(ctx->textures.size(), 1));
+	memset(texs.data(), 0, texs.size() * sizeof(TextureDev));
+	for (size_t i = 0; i < ctx->textures.size(); ++i) { texs[i].type = ctx->textures[i].type; memcpy(texs[i].p, ctx->textures[i].p, 48); }
 
 	// ---- upload ----
 	CUDA_TRY(ctx, ctx->dTriIdx.alloc(nTri * sizeof(uint4)));
@@ -542,6 +559,10 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dTriIdx.p, triIdx.data(), nTri * sizeof(uint4), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dPositions.p, pos.data(), nVert * sizeof(float4), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dNormals.p, nrm.data(), nVert * sizeof(float4), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, ctx->dTexcoords.alloc(uvs.size() * sizeof(float2)));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dTexcoords.p, uvs.data(), uvs.size() * sizeof(float2), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, ctx->dTextures.alloc(texs.size() * sizeof(TextureDev)));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dTextures.p, texs.data(), texs.size() * sizeof(TextureDev), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dShapes.p, shapes.data(), nShapes * sizeof(ShapeInfo), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dMaterials.p, mats.data(), mats.size() * sizeof(MaterialDev), cudaMemcpyHostToDevice, st));
 	if (!areaCdfAll.empty())
@@ -739,6 +760,8 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	sc.triIdx = ctx->dTriIdx.as<uint4>();
 	sc.positions = ctx->dPositions.as<float4>();
 	sc.normals = ctx->dNormals.as<float4>();
+	sc.texcoords = ctx->dTexcoords.as<float2>();
+	sc.textures = ctx->dTextures.as<TextureDev>();
 	sc.shapes = ctx->dShapes.as<ShapeInfo>();
 	sc.materials = ctx->dMaterials.as<MaterialDev>();
 	sc.areaCdf = ctx->dAreaCdf.as<float>();

@@ -28,7 +28,7 @@ struct DevBuf {
 
 struct HostMesh {
 	uint32_t nVert, nTri; int materialId, emitterId; bool hasNormals;
-	std::vector<float> pos, nrm; std::vector<uint32_t> tri;
+	std::vector<float> pos, nrm, uv; std::vector<uint32_t> tri;   // uv empty: no texture coordinates
 };
 
 struct mtsgpu_ctx {
@@ -43,6 +43,7 @@ struct mtsgpu_ctx {
 	// host-side scene staging
 	std::vector<mtsgpu_material> materials;
 	std::vector<mtsgpu_emitter> emitters;
+	std::vector<mtsgpu_texture> textures;
 	std::vector<HostMesh> meshes;
 	std::vector<int> emitterShape;   // emitter id -> shape index
 	int lumImportance = -1;          // which luminaire CDF is on the device (-1: none)
@@ -54,7 +55,7 @@ struct mtsgpu_ctx {
 	bool built = false;
 	DeviceScene scene;
 	DevBuf dTriAccel, dTriAccelOrig, dNodes, dTriIdx, dPositions, dNormals, dShapes, dMaterials, dEmitters,
-	       dLumCdf, dAreaCdf;
+	       dLumCdf, dAreaCdf, dTexcoords, dTextures;
 	mtsgpu_accel_info accel = {};
 
 	// trace staging + counters
@@ -94,4 +95,5 @@ int hookBsdfEval(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out);
 int hookEmitterSample(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out);
 int hookCameraRays(mtsgpu_ctx *ctx, const float *samples, size_t n, float *out);
 int hookFilmSplat(mtsgpu_ctx *ctx, const float *samples, size_t n, float *outFilm);
+int hookIntersectUv(mtsgpu_ctx *ctx, const float *rays, size_t n, float *out);
 int hookIntersectFull(mtsgpu_ctx *ctx, const float *rays, size_t n, mtsgpu_hit *hits, float *out);

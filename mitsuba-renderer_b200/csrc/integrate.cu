@@ -324,6 +324,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 			MaterialDev mat;
 			if (alive) {
 				mat = sc.materials[its.materialId];
+				resolveTextures(sc, mat, its.uvx, its.uvy);
 				if (its.emitterId >= 0 && (flags & PF_EMITTED) && (MODE == 0 || round == 0))
 					Li = Li + (MODE == 0 ? thr : v3(1, 1, 1)) * emitterLe(sc, its.emitterId, its.geoN, -rayD);
 				if (MODE == 0 && ig.maxDepth > 0 && (int) depth >= ig.maxDepth) alive = false;
@@ -762,6 +763,22 @@ __global__ void k_hook_camera(const CameraDev cam, const float *q, uint32_t n, f
 	r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = mint; r[4] = d.x; r[5] = d.y; r[6] = d.z; r[7] = maxt;
 }
 
+__global__ void k_hook_uv(const DeviceScene sc, const float4 *rays, const mtsgpu_hit *hits, uint32_t n, float *out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	float *o = out + (size_t) i * 8;
+	for (int k = 0; k < 8; ++k) o[k] = 0;
+	const mtsgpu_hit h = hits[i];
+	if (h.shape == 0xFFFFFFFFu) return;
+	Isect its;
+	fillIntersection(sc, h.shape, h.prim, h.u, h.v, v3(rays[2 * (size_t) i + 1]), its);
+	o[0] = its.uvx; o[1] = its.uvy;
+	if (its.materialId < 0) return;
+	MaterialDev m = sc.materials[its.materialId];
+	resolveTextures(sc, m, its.uvx, its.uvy);
+	for (int k = 0; k < 6; ++k) o[2 + k] = m.p[k];
+}
+
 __global__ void k_hook_isect(const DeviceScene sc, const float4 *rays, const mtsgpu_hit *hits, uint32_t n, float *out) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n) return;
@@ -857,6 +874,18 @@ int hookIntersectFull(mtsgpu_ctx *ctx, const float *rays, size_t n, mtsgpu_hit *
 	k_hook_isect<<<blocksFor(n, 128), 128, 0, ctx->stream>>>(ctx->scene, ctx->dRays.as<float4>(), ctx->dHits.as<mtsgpu_hit>(), (uint32_t) n, ctx->dStageOut.as<float>());
 	if (hits) CUDA_TRY(ctx, cudaMemcpyAsync(hits, ctx->dHits.p, n * sizeof(mtsgpu_hit), cudaMemcpyDeviceToHost, ctx->stream));
 	return download(ctx, out, ctx->dStageOut, n * 12 * 4);
+}
+
+int hookIntersectUv(mtsgpu_ctx *ctx, const float *rays, size_t n, float *out) {
+	REQUIRE(ctx, ctx->built, MTSGPU_ERR_ARG, "intersect_uv: call mtsgpu_build_accel first");
+	if (n == 0) return MTSGPU_OK;
+	int rc;
+	if ((rc = upload(ctx, ctx->dRays, rays, n * 32))) return rc;
+	CUDA_TRY(ctx, ctx->dHits.alloc(n * sizeof(mtsgpu_hit)));
+	if ((rc = launchTrace(ctx, ctx->dRays.as<float4>(), n, MTSGPU_TRACE_CLOSEST, ctx->dHits.p, nullptr))) return rc;
+	CUDA_TRY(ctx, ctx->dStageOut.alloc(n * 8 * 4));
+	k_hook_uv<<<blocksFor(n, 128), 128, 0, ctx->stream>>>(ctx->scene, ctx->dRays.as<float4>(), ctx->dHits.as<mtsgpu_hit>(), (uint32_t) n, ctx->dStageOut.as<float>());
+	return download(ctx, out, ctx->dStageOut, n * 8 * 4);
 }
 
 // Film splat of an arbitrary sample list through the render loop's own k_splat: samples are

@@ -169,6 +169,7 @@ __device__ inline void cameraRay(const CameraDev &cam, float sx, float sy, float
 // ---- intersection record: ShapeKDTree::fillIntersectionRecord<true> (skdtree.h:352-432) -----------
 struct Isect {
 	V3 p, geoN, shN, wi;
+	float uvx, uvy;
 	Frame3 sh;
 	uint32_t shape;
 	int materialId, emitterId;
@@ -191,9 +192,33 @@ __device__ inline void fillIntersection(const DeviceScene &sc, uint32_t shape, u
 	} else {
 		its.shN = fn;
 	}
+	if (si.hasTexcoords) {                     // its.uv = t0 * b.x + t1 * b.y + t2 * b.z (skdtree.h:408-413)
+		const float2 t0 = __ldg(sc.texcoords + idx.x), t1 = __ldg(sc.texcoords + idx.y), t2 = __ldg(sc.texcoords + idx.z);
+		its.uvx = t0.x * bx + t1.x * by + t2.x * bz;
+		its.uvy = t0.y * bx + t1.y * by + t2.y * bz;
+	} else {
+		its.uvx = its.uvy = 0.0f;
+	}
 	its.sh = makeFrame(its.shN);
 	its.wi = toLocal(its.sh, -rayD);
 	its.shape = shape; its.materialId = si.materialId; its.emitterId = si.emitterId;
+}
+
+// ---- textures: Texture2D::getValue (texture.cpp:73-82) + Checkerboard::getValue (checkerboard.cpp:47-55) ----------
+__device__ inline int mtsModulo(int a, int b) { const int r = a % b; return (r < 0) ? r + b : r; }   // util.h modulo()
+__device__ inline V3 textureValue(const TextureDev &t, float u, float v) {
+	const float tu = u * t.p[8] + t.p[6], tv = v * t.p[9] + t.p[7];
+	const int x = 2 * mtsModulo((int) (tu * 2), 2) - 1, y = 2 * mtsModulo((int) (tv * 2), 2) - 1;
+	return (x * y == 1) ? v3(t.p[0], t.p[1], t.p[2]) : v3(t.p[3], t.p[4], t.p[5]);
+}
+// material with its textured slots replaced by their values at (u, v)
+__device__ inline void resolveTextures(const DeviceScene &sc, MaterialDev &m, float u, float v) {
+#pragma unroll
+	for (int k = 0; k < 2; ++k)
+		if (m.tex[k]) {
+			const V3 c = textureValue(sc.textures[m.tex[k] - 1], u, v);
+			m.p[3 * k] = c.x; m.p[3 * k + 1] = c.y; m.p[3 * k + 2] = c.z;
+		}
 }
 
 // ---- DiscretePDF::sampleReuse (include/mitsuba/core/pdf.h:107-148) on a device CDF ----------------

@@ -39,10 +39,12 @@ struct ShapeInfo {
 	uint32_t hasNormals;
 	uint32_t cdfOffset;       // into DeviceScene::areaCdf (emitter meshes only)
 	float invSurfaceArea;     // TriMesh::m_invSurfaceArea (trimesh.cpp:281)
-	uint32_t pad[3];
+	uint32_t hasTexcoords;
+	uint32_t pad[2];
 };
 
-struct MaterialDev { uint32_t type; float p[16]; uint32_t pad[3]; };
+struct MaterialDev { uint32_t type; float p[16]; uint32_t tex[2]; uint32_t pad; };   // tex: 0 constant, k: textures[k-1]
+struct TextureDev { uint32_t type; float p[12]; uint32_t pad[3]; };
 // p[]: POINT pos | SPOT pos, axis row, cutoffAngle, invTransitionWidth, cosBeamWidth, cosCutoffAngle |
 //      DIRECTIONAL dir, diskRadius | CONSTANT sphere centre, radius   (derived values filled by rebuildLuminaireCdf)
 struct EmitterDev { float intensity[3]; uint32_t shape; float pdf; float weight; uint32_t type; float p[13]; };
@@ -67,6 +69,8 @@ struct DeviceScene {
 	const uint4 *triIdx;        // kd primitive order: {v0, v1, v2 (global vertex ids), shape}
 	const float4 *positions;    // global vertex arrays, xyz + pad
 	const float4 *normals;
+	const float2 *texcoords;    // global vertex array; only read for shapes with hasTexcoords
+	const TextureDev *textures;
 	const ShapeInfo *shapes;
 	const MaterialDev *materials;
 	const EmitterDev *emitters;

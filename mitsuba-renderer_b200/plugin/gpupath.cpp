@@ -100,41 +100,84 @@ private:
 	}
 
 	/* ---- BSDF parameters: no getters exist, so decode the object's own wire format ---------------------- */
-	static Spectrum readConstantTexture(Stream *s) {
-		/* InstanceManager::serialize (serialization.cpp:75-89): id, class name, payload */
-		if (s->readUInt() == 0)
-			SLog(EError, "gpupath: BSDF without a texture");
-		std::string cls = s->readString();
-		if (cls != "ConstantSpectrumTexture")
-			SLog(EError, "gpupath: texture class \"%s\" is outside the supported hot path (constant spectra only)", cls.c_str());
-		if (s->readUInt() != 0)   /* ConfigurableObject::serialize: parent reference */
-			SLog(EError, "gpupath: unexpected texture parent");
-		return Spectrum(s);
-	}
-
 	static void put(float *dst, const Spectrum &v) { Float r, g, b; v.toLinearRGB(r, g, b); dst[0] = r; dst[1] = g; dst[2] = b; }
 
+	/* Reading state for one serialised BSDF: the stream, the highest instance id met so far (InstanceManager::serialize
+	 * writes id + class + payload the first time it meets an object and only the id afterwards,
+	 * serialization.cpp:73-87), the textures collected for the C ABI, and which id became which slot value. */
+	struct TexValue { float rgb[3]; uint32_t texture; };
+	struct Decoder {
+		Stream *s; unsigned int maxId;
+		std::vector<mtsgpu_texture> *textures;
+		std::map<unsigned int, TexValue> seen;
+	};
+
+	/* ConfigurableObject::serialize writes the parent (properties.cpp:358-363): nothing, a back-reference, or — for a
+	 * texture shared with a BSDF that is not part of this stream — that BSDF inline, which is read and dropped. */
+	static void readParent(Decoder &d) {
+		const unsigned int id = d.s->readUInt();
+		if (id == 0 || id <= d.maxId) return;
+		d.maxId = id;
+		const std::string cls = d.s->readString();
+		decodePayload(cls, d);
+	}
+
+	/* One spectrum slot: a ConstantSpectrumTexture (texture.cpp:84-93) or a Checkerboard (checkerboard.cpp:35-45) */
+	static void readTextureSlot(Decoder &d, float *rgb, uint32_t &texture) {
+		Stream *s = d.s;
+		const unsigned int id = s->readUInt();
+		if (id == 0)
+			SLog(EError, "gpupath: BSDF without a texture");
+		TexValue v; memset(&v, 0, sizeof(v));
+		if (id <= d.maxId) {
+			if (!d.seen.count(id)) SLog(EError, "gpupath: unexpected instance reference in a BSDF");
+			v = d.seen[id];
+		} else {
+			d.maxId = id;
+			const std::string cls = s->readString();
+			readParent(d);
+			if (cls == "ConstantSpectrumTexture") {
+				put(v.rgb, Spectrum(s));
+			} else if (cls == "Checkerboard") {
+				mtsgpu_texture t; memset(&t, 0, sizeof(t));
+				t.type = MTSGPU_TEXTURE_CHECKERBOARD;
+				Point2 uvOffset(s); Vector2 uvScale(s);              /* Texture2D::serialize (texture.cpp:67-71) */
+				put(t.p, Spectrum(s)); put(t.p + 3, Spectrum(s));    /* bright, dark */
+				t.p[6] = uvOffset.x; t.p[7] = uvOffset.y; t.p[8] = uvScale.x; t.p[9] = uvScale.y;
+				d.textures->push_back(t);
+				v.texture = (uint32_t) d.textures->size();
+			} else {
+				SLog(EError, "gpupath: texture class \"%s\" is outside the supported hot path (constant spectra, checkerboard)", cls.c_str());
+			}
+			d.seen[id] = v;
+		}
+		memcpy(rgb, v.rgb, sizeof(v.rgb));
+		texture = v.texture;
+	}
+
 	/* `s` is positioned at the serialised form of an object of class `cls` */
-	static mtsgpu_material decodePayload(const std::string &cls, Stream *s) {
+	static mtsgpu_material decodePayload(const std::string &cls, Decoder &d) {
+		Stream *s = d.s;
 		mtsgpu_material m; memset(&m, 0, sizeof(m));
-		if (s->readUInt() != 0)            /* BSDF::setParent is a no-op (bsdf.cpp:55-57) => parent id 0 */
-			SLog(EError, "gpupath: unexpected BSDF parent");
+		readParent(d);                     /* BSDF::setParent is a no-op (bsdf.cpp:55-57) => normally 0 */
 		s->readString();                   /* BSDF::serialize: m_name (bsdf.cpp:50-53) */
 		if (cls == "TwoSidedBRDF") {                  /* twosided.cpp:55-59: the nested BRDF instance */
-			if (s->readUInt() == 0)
-				SLog(EError, "gpupath: TwoSidedBRDF without a nested BRDF");
+			const unsigned int id = s->readUInt();
+			if (id == 0 || id <= d.maxId)
+				SLog(EError, "gpupath: TwoSidedBRDF without a nested BRDF of its own");
+			d.maxId = id;
 			const std::string nested = s->readString();
-			m = decodePayload(nested, s);
+			m = decodePayload(nested, d);
 			if ((m.type & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_DIELECTRIC || (m.type & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_ROUGHGLASS
 					|| (m.type & MTSGPU_BSDF_TWOSIDED))
 				SLog(EError, "gpupath: TwoSidedBRDF around \"%s\" is not supported", nested.c_str());
 			m.type |= MTSGPU_BSDF_TWOSIDED;
 		} else if (cls == "Lambertian") {             /* lambertian.cpp:137-141 */
 			m.type = MTSGPU_BSDF_LAMBERTIAN;
-			put(m.p, readConstantTexture(s));
+			readTextureSlot(d, m.p, m.texture[0]);
 		} else if (cls == "Microfacet") {             /* microfacet.cpp:283-293 */
 			m.type = MTSGPU_BSDF_MICROFACET;
-			put(m.p, readConstantTexture(s)); put(m.p + 3, readConstantTexture(s));
+			readTextureSlot(d, m.p, m.texture[0]); readTextureSlot(d, m.p + 3, m.texture[1]);
 			m.p[8] = s->readFloat(); m.p[6] = s->readFloat(); m.p[7] = s->readFloat();   /* alphaB, kd, ks */
 			m.p[9] = s->readFloat(); m.p[10] = s->readFloat();                            /* intIOR, extIOR */
 		} else if (cls == "Mirror") {                 /* mirror.cpp:51-55 */
@@ -142,26 +185,33 @@ private:
 			put(m.p, Spectrum(s));
 		} else if (cls == "RoughMetal") {             /* roughmetal.cpp:169-176 */
 			m.type = MTSGPU_BSDF_ROUGHMETAL;
-			put(m.p, readConstantTexture(s));
+			readTextureSlot(d, m.p, m.texture[0]);
 			m.p[3] = s->readFloat();
 			put(m.p + 4, Spectrum(s)); put(m.p + 7, Spectrum(s));
 		} else if (cls == "Phong") {                  /* phong.cpp:247-257 */
 			m.type = MTSGPU_BSDF_PHONG;
-			put(m.p, readConstantTexture(s)); put(m.p + 3, readConstantTexture(s));
+			readTextureSlot(d, m.p, m.texture[0]); readTextureSlot(d, m.p + 3, m.texture[1]);
 			m.p[8] = s->readFloat(); m.p[6] = s->readFloat(); m.p[7] = s->readFloat();   /* exponent, kd, ks */
 			m.p[9] = s->readFloat(); m.p[10] = s->readFloat();                            /* sampling weights */
 		} else if (cls == "RoughGlass") {             /* roughglass.cpp:735-744 */
 			m.type = MTSGPU_BSDF_ROUGHGLASS;
 			m.p[9] = (float) s->readInt();
-			if (s->readUInt() == 0 || s->readString() != "ConstantFloatTexture" || s->readUInt() != 0)
-				SLog(EError, "gpupath: RoughGlass: only a constant alpha is inside the supported hot path");
-			m.p[6] = s->readFloat();                   /* ConstantFloatTexture::serialize (texture.cpp:100-103) */
-			put(m.p, readConstantTexture(s)); put(m.p + 3, readConstantTexture(s));
+			{
+				const unsigned int id = s->readUInt();
+				if (id == 0 || id <= d.maxId || s->readString() != "ConstantFloatTexture")
+					SLog(EError, "gpupath: RoughGlass: only a constant alpha is inside the supported hot path");
+				d.maxId = id;
+				readParent(d);
+				m.p[6] = s->readFloat();               /* ConstantFloatTexture::serialize (texture.cpp:100-103) */
+			}
+			readTextureSlot(d, m.p, m.texture[0]); readTextureSlot(d, m.p + 3, m.texture[1]);
 			m.p[7] = s->readFloat(); m.p[8] = s->readFloat();
 		} else if (cls == "Dielectric") {             /* dielectric.cpp:88-95 */
 			m.type = MTSGPU_BSDF_DIELECTRIC;
 			m.p[6] = s->readFloat(); m.p[7] = s->readFloat();
-			put(m.p, readConstantTexture(s)); put(m.p + 3, readConstantTexture(s));
+			uint32_t t0 = 0, t1 = 0;
+			readTextureSlot(d, m.p, t0); readTextureSlot(d, m.p + 3, t1);
+			if (t0 || t1) SLog(EError, "gpupath: textured dielectric is outside the supported hot path");
 		} else {
 			SLog(EError, "gpupath: BSDF class \"%s\" is outside the supported hot path "
 				"(lambertian, microfacet, mirror, roughmetal, dielectric, phong, roughglass, twosided)", cls.c_str());
@@ -225,12 +275,17 @@ private:
 		(void) l2w;
 	}
 
-	static mtsgpu_material decodeBSDF(const BSDF *bsdf) {
+	/* Serialised through the manager, so that the BSDF itself has an id (1): textures that are XML children of the
+	 * BSDF carry it as their parent and then write just that id instead of the whole BSDF again. */
+	static mtsgpu_material decodeBSDF(const BSDF *bsdf, std::vector<mtsgpu_texture> &textures) {
 		ref<MemoryStream> s = new MemoryStream();
 		ref<InstanceManager> mgr = new InstanceManager();
-		bsdf->serialize(s, mgr);
+		mgr->serialize(s, bsdf);
 		s->setPos(0);
-		return decodePayload(bsdf->getClass()->getName(), s);
+		Decoder d; d.s = s; d.maxId = 0; d.textures = &textures;
+		d.maxId = s->readUInt();
+		const std::string cls = s->readString();
+		return decodePayload(cls, d);
 	}
 
 	bool renderImpl(std::vector<mtsgpu_ctx *> &ctxs, Scene *scene, RenderQueue *queue, const RenderJob *job) {
@@ -250,6 +305,7 @@ private:
 		const std::vector<const Shape *> &shapes = scene->getKDTree()->getShapes();
 		const std::vector<Luminaire *> &luminaires = scene->getLuminaires();
 		std::vector<mtsgpu_material> materials;
+		std::vector<mtsgpu_texture> textures;
 		std::map<const BSDF *, int> materialIds;
 		std::vector<mtsgpu_emitter> emitters(luminaires.size());
 		std::map<const Luminaire *, int> emitterIds;
@@ -279,7 +335,7 @@ private:
 				const BSDF *bsdf = shape->getBSDF();
 				if (!materialIds.count(bsdf)) {
 					materialIds[bsdf] = (int) materials.size();
-					materials.push_back(decodeBSDF(bsdf));
+					materials.push_back(decodeBSDF(bsdf, textures));
 				}
 				r.mat = materialIds[bsdf];
 			}
@@ -289,6 +345,7 @@ private:
 		}
 		for (size_t g = 0; g < ctxs.size(); ++g) {       /* the scene is replicated on every GPU */
 			mtsgpu_ctx *c = ctxs[g];
+			check(c, mtsgpu_upload_textures(c, textures.empty() ? NULL : &textures[0], (int) textures.size()));
 			check(c, mtsgpu_upload_materials(c, materials.empty() ? NULL : &materials[0], (int) materials.size()));
 			check(c, mtsgpu_upload_emitters(c, emitters.empty() ? NULL : &emitters[0], (int) emitters.size()));
 			for (size_t i = 0; i < meshes.size(); ++i) {
@@ -296,7 +353,8 @@ private:
 				/* Point/Normal are 3 packed floats, Triangle is 3 packed uint32 (core/triangle.h) */
 				check(c, mtsgpu_upload_mesh(c, (int) i,
 					reinterpret_cast<const float *>(m->getVertexPositions()),
-					reinterpret_cast<const float *>(m->getVertexNormals()), NULL, (uint32_t) m->getVertexCount(),
+					reinterpret_cast<const float *>(m->getVertexNormals()),
+					reinterpret_cast<const float *>(m->getVertexTexcoords()), (uint32_t) m->getVertexCount(),
 					reinterpret_cast<const uint32_t *>(m->getTriangles()), (uint32_t) m->getTriangleCount(),
 					meshes[i].mat, meshes[i].emit));
 			}

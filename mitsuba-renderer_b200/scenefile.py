@@ -30,6 +30,30 @@ class Material:
     """BSDF parameter block; `p` uses the slot layout of `mtsgpu_material` (include/mtsgpu.h)."""
     type: int
     p: np.ndarray  # float32[16]
+    tex: tuple = (0, 0)   # per spectrum slot (p[0..2], p[3..5]): 0 constant, k > 0: SceneDesc.textures[k-1]
+
+
+@dataclass
+class Texture:
+    """2D texture; `p` uses the layout of `mtsgpu_texture` (include/mtsgpu.h)."""
+    type: int
+    p: np.ndarray  # float32[12]
+
+
+TEX_CHECKERBOARD = 0
+
+
+def checkerboard(bright=(0.4, 0.4, 0.4), dark=(0.2, 0.2, 0.2), uscale=1.0, vscale=1.0, uoffset=0.0, voffset=0.0):
+    """src/textures/checkerboard.cpp:30-33 + the uv transform of Texture2D (src/librender/texture.cpp:43-56)"""
+    p = np.zeros(12, np.float32)
+    p[:10] = list(bright) + list(dark) + [uoffset, voffset, uscale, vscale]
+    return Texture(TEX_CHECKERBOARD, p)
+
+
+def textured(material: "Material", slot: int, texture_index: int) -> "Material":
+    """`material` with spectrum slot 0 (p[0..2]) or 1 (p[3..5]) read from SceneDesc.textures[texture_index]."""
+    tex = list(material.tex); tex[slot] = texture_index + 1
+    return Material(material.type, material.p.copy(), tuple(tex))
 
 
 def _mat(type_, values):
@@ -95,7 +119,7 @@ def roughglass(specular_reflectance=(1, 1, 1), specular_transmittance=(1, 1, 1),
 def twosided(material: Material) -> Material:
     """src/bsdfs/twosided.cpp:36-143 around a BRDF (not valid for dielectric)."""
     assert (material.type & 0xFF) != MAT_DIELECTRIC
-    return Material(material.type | BSDF_TWOSIDED, material.p.copy())
+    return Material(material.type | BSDF_TWOSIDED, material.p.copy(), material.tex)
 
 
 EMITTER_AREA, EMITTER_POINT, EMITTER_SPOT, EMITTER_DIRECTIONAL, EMITTER_CONSTANT = range(5)
@@ -211,6 +235,7 @@ class Shape:
     normals: Optional[np.ndarray]    # float32 [nVert, 3] or None
     material: int = -1               # index into SceneDesc.materials, -1: no BSDF (not an occluder)
     emitter: int = -1                # index into SceneDesc.emitters, -1: none
+    texcoords: Optional[np.ndarray] = None   # float32 [nVert, 2] or None (uv = 0 everywhere, skdtree.h:414)
 
 
 @dataclass
@@ -237,6 +262,7 @@ class SceneDesc:
     sampler_depth: int = 3           # ldsampler `depth`
     materials: List[Material] = field(default_factory=list)
     emitters: List[Emitter] = field(default_factory=list)
+    textures: List[Texture] = field(default_factory=list)
     shapes: List[Shape] = field(default_factory=list)
 
     @property
@@ -293,7 +319,7 @@ def write_scene(path: str, scene: SceneDesc) -> None:
     cx, cy, cw, ch = scene.crop_rect
     with open(path, "wb") as f:
         f.write(b"MTSB200\0")
-        f.write(struct.pack("<I", 3))
+        f.write(struct.pack("<I", 4))
         f.write(np.ascontiguousarray(scene.camera_to_world, np.float32).tobytes())
         f.write(struct.pack("<5fI", scene.fov, scene.near_clip, scene.far_clip, scene.aperture_radius,
                             scene.focus_depth, int(scene.map_smaller_side)))
@@ -301,19 +327,26 @@ def write_scene(path: str, scene: SceneDesc) -> None:
         f.write(struct.pack("<2I2i3I", scene.spp, scene.mode, scene.max_depth, scene.rr_depth,
                             int(scene.strict_normals), scene.luminaire_samples, scene.bsdf_samples))
         f.write(struct.pack("<2I", scene.sampler_type, scene.sampler_depth))
+        f.write(struct.pack("<I", len(scene.textures)))
+        for t in scene.textures:
+            f.write(struct.pack("<I", t.type))
+            f.write(np.ascontiguousarray(t.p, np.float32).tobytes())
         f.write(struct.pack("<I", len(scene.materials)))
         for m in scene.materials:
             f.write(struct.pack("<I", m.type))
             f.write(np.ascontiguousarray(m.p, np.float32).tobytes())
+            f.write(struct.pack("<2I", *m.tex))
         f.write(struct.pack("<I", len(scene.emitters)))
         for e in scene.emitters:
             f.write(struct.pack("<4fI", *e.intensity, e.sampling_weight, e.type))
             f.write(e.abi_params().tobytes()); f.write(e.aux_params().tobytes())
         f.write(struct.pack("<I", len(scene.shapes)))
         for s in scene.shapes:
-            f.write(struct.pack("<2I2iI", len(s.positions), len(s.triangles), s.material, s.emitter,
-                                0 if s.normals is None else 1))
+            f.write(struct.pack("<2I2i2I", len(s.positions), len(s.triangles), s.material, s.emitter,
+                                0 if s.normals is None else 1, 0 if s.texcoords is None else 1))
             f.write(np.ascontiguousarray(s.positions, np.float32).tobytes())
             if s.normals is not None:
                 f.write(np.ascontiguousarray(s.normals, np.float32).tobytes())
+            if s.texcoords is not None:
+                f.write(np.ascontiguousarray(s.texcoords, np.float32).tobytes())
             f.write(np.ascontiguousarray(s.triangles, np.uint32).tobytes())

@@ -9,7 +9,7 @@ import numpy as np
 
 from .scenefile import (SceneDesc, Shape, Emitter, lambertian, microfacet, mirror, roughmetal,
                         dielectric, twosided, phong, roughglass, look_at, point_light, spot_light, directional_light,
-                        constant_light, add_light, MODE_PATH, MODE_DIRECT, FILTER_BOX)
+                        constant_light, add_light, checkerboard, textured, MODE_PATH, MODE_DIRECT, FILTER_BOX)
 
 F32 = np.float32
 
@@ -125,6 +125,26 @@ def icosphere(subdiv=2):
             nf += [[a, ab, ca], [b, bc, ab], [c, ca, bc], [ab, bc, ca]]
         v = np.array(verts, np.float64); f = np.array(nf, np.int64)
     return v, f
+
+
+def textured_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6) -> SceneDesc:
+    """The all-BSDF scene with texture coordinates on every mesh and checkerboard textures in the reflectance slots of
+    the lambertian, microfacet, roughmetal, phong and roughglass materials (different scales and offsets)."""
+    s = material_test_scene(width, height, spp, mode, max_depth)
+    for sh in s.shapes:
+        P = sh.positions.astype(F32)
+        sh.texcoords = np.stack([P[:, 0] * F32(0.7) + P[:, 1] * F32(0.3), P[:, 2] * F32(0.6) - P[:, 1] * F32(0.2)], 1).astype(F32)
+    s.textures = [checkerboard((0.75, 0.7, 0.6), (0.15, 0.2, 0.3), 2.0, 2.0),
+                  checkerboard((0.9, 0.3, 0.2), (0.2, 0.8, 0.3), 3.0, 1.5, 0.25, -0.4),
+                  checkerboard((1.0, 1.0, 1.0), (0.5, 0.6, 0.9), 6.0, 6.0, 0.1, 0.1)]
+    m = s.materials
+    m[1] = textured(m[1], 0, 1)        # red wall: lambertian
+    m[2] = textured(m[2], 0, 0)        # green wall: lambertian
+    m[4] = textured(m[4], 0, 0)        # walls: microfacet, diffuse slot
+    m[6] = textured(m[6], 0, 2)        # short block: roughmetal specularReflectance
+    m[9] = textured(textured(m[9], 0, 1), 1, 2)    # panel: phong, both slots
+    m[10] = textured(m[10], 1, 2)      # ball: roughglass specularTransmittance
+    return s
 
 
 def lights_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6, background=True) -> SceneDesc:

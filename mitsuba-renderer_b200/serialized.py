@@ -69,7 +69,7 @@ def load(path: str, shape_index: int = 0, to_world=None, to_world_inv=None, face
 
 def load_shape(path: str, shape_index: int = 0, material: int = 0, emitter: int = -1, **kw) -> Shape:
     d = load(path, shape_index, **kw)
-    return Shape(d["positions"], d["triangles"], d["normals"], material=material, emitter=emitter)
+    return Shape(d["positions"], d["triangles"], d["normals"], material=material, emitter=emitter, texcoords=d["texcoords"])
 
 
 def save(path: str, meshes: Sequence, face_normals: Optional[Sequence[bool]] = None):

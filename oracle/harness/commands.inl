@@ -307,8 +307,31 @@ static int cmdDevelop(int argc, char **argv) {
 	return 0;
 }
 
+/* Closest hit -> interpolated texture coordinates (skdtree.h:408-415) and BSDF::getDiffuseReflectance(its), which for
+ * lambertian / microfacet / phong is the (possibly textured) reflectance at the hit (times the diffuse amount). */
+static int cmdUv(int argc, char **argv) {
+	if (argc < 5) { std::cerr << "uv SCENE RAYS OUT\n"; return 1; }
+	sio::Scene sf; sio::load(argv[2], sf);
+	std::vector<float> rays = sio::loadFloats(argv[3]);
+	const size_t n = rays.size() / 8;
+	Built b = buildScene(sf, "");
+	std::vector<float> out(n * 5, 0.0f);
+	for (size_t i = 0; i < n; ++i) {
+		const float *e = &rays[i * 8];
+		Ray ray(Point(e[0], e[1], e[2]), Vector(e[4], e[5], e[6]), e[3], e[7], 0.0f);
+		Intersection its;
+		if (!b.scene->rayIntersect(ray, its)) continue;
+		out[i * 5] = its.uv.x; out[i * 5 + 1] = its.uv.y;
+		if (its.shape->hasBSDF())
+			its.shape->getBSDF()->getDiffuseReflectance(its).toLinearRGB(out[i * 5 + 2], out[i * 5 + 3], out[i * 5 + 4]);
+	}
+	sio::save(argv[4], out.data(), out.size() * 4);
+	printf("{\"cmd\": \"uv\", \"rays\": %zu}\n", n);
+	return 0;
+}
+
 static int dispatch(int argc, char **argv) {
-	if (argc < 2) { std::cerr << "usage: mts_oracle trace|triaccel|bsdf|emitter|camera|splat|render|mesh|meshsave|develop ...\n"; return 1; }
+	if (argc < 2) { std::cerr << "usage: mts_oracle trace|triaccel|bsdf|emitter|camera|splat|render|mesh|meshsave|develop|uv ...\n"; return 1; }
 	std::string cmd = argv[1];
 	if (cmd == "trace") return cmdTraceImpl(argc, argv);
 	if (cmd == "triaccel") return cmdTriAccel(argc, argv);
@@ -320,6 +343,7 @@ static int dispatch(int argc, char **argv) {
 	if (cmd == "mesh") return cmdMesh(argc, argv);
 	if (cmd == "meshsave") return cmdMeshSave(argc, argv);
 	if (cmd == "develop") return cmdDevelop(argc, argv);
+	if (cmd == "uv") return cmdUv(argc, argv);
 	std::cerr << "unknown command " << cmd << "\n";
 	return 1;
 }

@@ -105,6 +105,21 @@ static ConfigurableObject *create(const Class *cls, const Properties &props) {
 
 static Spectrum rgb(const float *v) { Spectrum s; s.fromLinearRGB(v[0], v[1], v[2]); return s; }
 
+static const std::vector<sio::Texture> *g_textures = NULL;   /* texture table of the scene being built */
+
+/* <texture type="checkerboard"> (src/textures/checkerboard.cpp:30-33, src/librender/texture.cpp:43-56) */
+static ref<Texture> makeTexture(const sio::Texture &t) {
+	if (t.type != 0) SLog(EError, "unknown texture type %u", t.type);
+	Properties p("checkerboard");
+	p.setSpectrum("brightColor", rgb(t.p));
+	p.setSpectrum("darkColor", rgb(t.p + 3));
+	p.setFloat("uoffset", t.p[6]); p.setFloat("voffset", t.p[7]);
+	p.setFloat("uscale", t.p[8]); p.setFloat("vscale", t.p[9]);
+	ref<Texture> tex = static_cast<Texture *>(create(MTS_CLASS(Texture), p));
+	tex->configure();
+	return tex;
+}
+
 static ref<BSDF> makeBSDF(const sio::Material &mIn) {
 	if (mIn.type & 0x100u) {
 		/* <bsdf type="twosided"> <bsdf type="..."/> </bsdf>  (twosided.cpp:30-35) */
@@ -178,12 +193,24 @@ static ref<BSDF> makeBSDF(const sio::Material &mIn) {
 			SLog(EError, "unknown material type %u", m.type);
 	}
 	ref<BSDF> bsdf = static_cast<BSDF *>(create(MTS_CLASS(BSDF), p));
+	/* textured slots: <ref name="reflectance" id="..."/> inside the <bsdf> element */
+	static const char *slotNames[7][2] = { { "reflectance", NULL }, { "diffuseReflectance", "specularReflectance" }, { NULL, NULL },
+		{ "specularReflectance", NULL }, { NULL, NULL }, { "diffuseReflectance", "specularReflectance" },
+		{ "specularReflectance", "specularTransmittance" } };
+	for (int k = 0; k < 2; ++k) {
+		if (!m.tex[k]) continue;
+		if (!g_textures || m.tex[k] > g_textures->size() || !slotNames[m.type][k]) SLog(EError, "bad texture reference");
+		ref<Texture> tex = makeTexture((*g_textures)[m.tex[k] - 1]);
+		bsdf->addChild(slotNames[m.type][k], tex);
+		tex->setParent(bsdf);
+	}
 	bsdf->configure();
 	return bsdf;
 }
 
 static Built buildScene(const sio::Scene &s, const std::string &integratorOverride, bool withGeometry = true) {
 	Built out;
+	g_textures = &s.textures;
 	ref<Scene> scene = new Scene(Properties("scene"));
 
 	/* integrator */
@@ -276,7 +303,9 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 		for (size_t i = 0; i < s.shapes.size(); ++i) {
 			const sio::Shape &sh = s.shapes[i];
 			ref<TriMesh> mesh = new TriMesh(formatString("shape%i", (int) i), sh.nTri, sh.nVert,
-				sh.hasNormals != 0, false, false, false, sh.hasNormals == 0 /* faceNormals */);
+				sh.hasNormals != 0, sh.hasUv != 0, false, false, sh.hasNormals == 0 /* faceNormals */);
+			if (sh.hasUv)
+				memcpy(mesh->getVertexTexcoords(), sh.uv.data(), sh.uv.size() * 4);
 			memcpy(mesh->getVertexPositions(), sh.pos.data(), sh.pos.size() * 4);
 			if (sh.hasNormals)
 				memcpy(mesh->getVertexNormals(), sh.nrm.data(), sh.nrm.size() * 4);

@@ -13,11 +13,12 @@ namespace sio {
 
 enum MaterialType { MAT_LAMBERTIAN = 0, MAT_MICROFACET = 1, MAT_MIRROR = 2, MAT_ROUGHMETAL = 3, MAT_DIELECTRIC = 4 };
 
-struct Material { uint32_t type; float p[16]; };
+struct Material { uint32_t type; float p[16]; uint32_t tex[2]; };
+struct Texture  { uint32_t type; float p[12]; };
 struct Emitter  { float intensity[3]; float samplingWeight; uint32_t type; float p[11]; float aux[16]; };
 struct Shape {
-	uint32_t nVert, nTri; int32_t matId, emitId; uint32_t hasNormals;
-	std::vector<float> pos, nrm; std::vector<uint32_t> tri;
+	uint32_t nVert, nTri; int32_t matId, emitId; uint32_t hasNormals, hasUv;
+	std::vector<float> pos, nrm, uv; std::vector<uint32_t> tri;
 };
 
 struct Scene {
@@ -27,6 +28,7 @@ struct Scene {
 	uint32_t width, height, cropX, cropY, cropW, cropH, filterType;
 	uint32_t spp, mode; int32_t maxDepth, rrDepth; uint32_t strictNormals, nLumSamples, nBsdfSamples;
 	uint32_t samplerType, samplerDepth;
+	std::vector<Texture> textures;
 	std::vector<Material> materials;
 	std::vector<Emitter> emitters;
 	std::vector<Shape> shapes;
@@ -46,7 +48,7 @@ inline void load(const std::string &path, Scene &s) {
 	Reader r(path);
 	char magic[8]; r.raw(magic, 8);
 	if (memcmp(magic, "MTSB200", 8) != 0) throw std::runtime_error("bad magic in " + path);
-	if (r.get<uint32_t>() != 3) throw std::runtime_error("bad version in " + path);
+	if (r.get<uint32_t>() != 4) throw std::runtime_error("bad version in " + path);
 	r.raw(s.cameraToWorld, 64);
 	s.fov = r.get<float>(); s.nearClip = r.get<float>(); s.farClip = r.get<float>();
 	s.apertureRadius = r.get<float>(); s.focusDepth = r.get<float>();
@@ -59,17 +61,20 @@ inline void load(const std::string &path, Scene &s) {
 	s.maxDepth = r.get<int32_t>(); s.rrDepth = r.get<int32_t>();
 	s.strictNormals = r.get<uint32_t>(); s.nLumSamples = r.get<uint32_t>(); s.nBsdfSamples = r.get<uint32_t>();
 	s.samplerType = r.get<uint32_t>(); s.samplerDepth = r.get<uint32_t>();
+	s.textures.resize(r.get<uint32_t>());
+	for (auto &t : s.textures) { t.type = r.get<uint32_t>(); r.raw(t.p, 48); }
 	s.materials.resize(r.get<uint32_t>());
-	for (auto &m : s.materials) { m.type = r.get<uint32_t>(); r.raw(m.p, 64); }
+	for (auto &m : s.materials) { m.type = r.get<uint32_t>(); r.raw(m.p, 64); r.raw(m.tex, 8); }
 	s.emitters.resize(r.get<uint32_t>());
 	for (auto &e : s.emitters) { r.raw(e.intensity, 12); e.samplingWeight = r.get<float>(); e.type = r.get<uint32_t>(); r.raw(e.p, 44); r.raw(e.aux, 64); }
 	s.shapes.resize(r.get<uint32_t>());
 	for (auto &sh : s.shapes) {
 		sh.nVert = r.get<uint32_t>(); sh.nTri = r.get<uint32_t>();
 		sh.matId = r.get<int32_t>(); sh.emitId = r.get<int32_t>();
-		sh.hasNormals = r.get<uint32_t>();
+		sh.hasNormals = r.get<uint32_t>(); sh.hasUv = r.get<uint32_t>();
 		sh.pos.resize(3 * (size_t) sh.nVert); r.raw(sh.pos.data(), sh.pos.size() * 4);
 		if (sh.hasNormals) { sh.nrm.resize(3 * (size_t) sh.nVert); r.raw(sh.nrm.data(), sh.nrm.size() * 4); }
+		if (sh.hasUv) { sh.uv.resize(2 * (size_t) sh.nVert); r.raw(sh.uv.data(), sh.uv.size() * 4); }
 		sh.tri.resize(3 * (size_t) sh.nTri); r.raw(sh.tri.data(), sh.tri.size() * 4);
 	}
 }

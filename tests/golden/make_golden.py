@@ -57,6 +57,10 @@ def main():
     acc = gc.film_accumulators()
     save("mfilm", acc_digest=gc.digest(acc), luminance=np.frombuffer(oracle_util.develop_mfilm(acc, False), np.uint8),
          spectra=np.frombuffer(oracle_util.develop_mfilm(acc, True), np.uint8))
+    # ---- texture coordinates + textured reflectances at the hit ---------------------------------------------------------
+    ts = gc.scene_textured()
+    rays = gc.trace_rays(ts)
+    save("uv_textured", rays_digest=gc.digest(rays), out=oracle_util.Session(ts).uv(rays))
     # ---- TriAccel records + enlarged scene box --------------------------------------------------------
     rec, box, _ = oracle_util.Session(gc.scene_materials()).triaccel()
     save("triaccel_materials", records=rec.view(np.uint8), box=box)

@@ -13,6 +13,10 @@ def scene_lights():
     return scenes.lights_test_scene(32, 32, 1)
 
 
+def scene_textured():
+    return scenes.textured_test_scene(32, 32, 1)
+
+
 def scene_grid():
     return scenes.microbench_scene(cells=64, pad_cells=9)
 
@@ -181,3 +185,24 @@ def film_accumulators(h=9, w=13, seed=31):
     a[3, 1, :3] = (-0.5, 0.25, -1e-3)
     a[4, 4, 4] = 0.0                              # colour without weight
     return a
+
+
+def diffuse_reflectance_from_slots(scene, hits, slots):
+    """What BSDF::getDiffuseReflectance(its) returns, from the hit's material and its (texture-resolved) slot 0:
+    lambertian: reflectance (lambertian.cpp:91-93); microfacet / phong: diffuseReflectance * kd; zero for the rest."""
+    out = np.zeros((len(hits), 3), np.float32)
+    for i, h in enumerate(hits):
+        if h["shape"] == 0xFFFFFFFF:
+            continue
+        mid = scene.shapes[int(h["shape"])].material
+        if mid < 0:
+            continue
+        m = scene.materials[mid]
+        t = m.type & 0xFF
+        if m.type & 0x100:          # twosided forwards to the nested BSDF
+            pass
+        if t == 0:
+            out[i] = slots[i]
+        elif t in (1, 5):
+            out[i] = (slots[i] * np.float32(m.p[6])).astype(np.float32)
+    return out

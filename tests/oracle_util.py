@@ -122,6 +122,11 @@ class Session:
         out, _ = self._io("bsdf", queries)
         return np.fromfile(out, np.float32).reshape(-1, 16)
 
+    def uv(self, rays):
+        """rows {its.uv, BSDF::getDiffuseReflectance(its)} of the closest hit; zeros on a miss."""
+        out, _ = self._io("uv", np.ascontiguousarray(rays, np.float32).reshape(-1, 8))
+        return np.fromfile(out, np.float32).reshape(-1, 5)
+
     def emitter(self, queries):
         out, _ = self._io("emitter", queries)
         return np.fromfile(out, np.float32).reshape(-1, 16)

@@ -86,15 +86,16 @@ def test_full_size_scene_shapes():
 
 
 def test_scene_file_round_trip(tmp_path):
-    s = scenes.material_test_scene(20, 10, 3, scenefile.MODE_DIRECT)
+    s = scenes.textured_test_scene(20, 10, 3, scenefile.MODE_DIRECT)
     s.crop = (2, 1, 10, 5)
     path = str(tmp_path / "s.bin")
     scenefile.write_scene(path, s)
     raw = open(path, "rb").read()
     assert raw[:8] == b"MTSB200\0"
-    expect = 8 + 4 + 64 + 24 + 28 + 28 + 8 + 4 + len(s.materials) * 68 + 4 + len(s.emitters) * 128 + 4
+    expect = 8 + 4 + 64 + 24 + 28 + 28 + 8 + 4 + len(s.textures) * 52 + 4 + len(s.materials) * 76 + 4 + len(s.emitters) * 128 + 4
     for sh in s.shapes:
-        expect += 20 + sh.positions.nbytes + (0 if sh.normals is None else sh.normals.nbytes) + sh.triangles.nbytes
+        expect += 24 + sh.positions.nbytes + (0 if sh.normals is None else sh.normals.nbytes) + sh.triangles.nbytes
+        expect += 0 if sh.texcoords is None else sh.texcoords.nbytes
     assert len(raw) == expect
 
 

@@ -36,6 +36,27 @@ def test_ray_queries_match_golden(name, make, gpu_ctx_factory):
     assert close(full[same], g["full"][same], 1e-5, 1e-6).all()
 
 
+def test_texture_coordinates_and_textured_reflectance_match_golden(gpu_ctx_factory):
+    """its.uv (skdtree.h:408-415) and Texture2D / Checkerboard::getValue at it, seen through
+    BSDF::getDiffuseReflectance(its) of the lambertian, microfacet and phong materials."""
+    scene = gc.scene_textured()
+    g = gold("uv_textured")
+    rays = gc.trace_rays(scene)
+    assert gc.digest(rays) == str(g["rays_digest"])
+    ctx = gpu_ctx_factory(scene)
+    hits = ctx.trace(rays, TRACE_CLOSEST)
+    out, ref = ctx.intersect_uv(rays), g["out"]
+    hit = hits["shape"] != 0xFFFFFFFF
+    assert hit.sum() > 5000 and close(out[hit, :2], ref[hit, :2], 1e-5, 1e-6).all()
+    assert np.array_equal(out[~hit], np.zeros_like(out[~hit]))
+    want = gc.diffuse_reflectance_from_slots(scene, hits, out[:, 2:5])
+    # a uv within rounding of a checker edge may land on the other colour: allow a handful
+    bad = ~close(want, ref[:, 2:5], 1e-6, 1e-7).all(axis=1)
+    assert bad.sum() <= 3, bad.sum()
+    textured = np.array([h["shape"] != 0xFFFFFFFF and scene.shapes[int(h["shape"])].material in (1, 2, 4, 9) for h in hits])
+    assert len(np.unique(ref[textured, 2:5].round(4), axis=0)) >= 4        # both colours of several textures were hit
+
+
 def test_triaccel_matches_golden(gpu_ctx_factory):
     g = gold("triaccel_materials")
     ref = g["records"].view(api.TRIACCEL_DTYPE)

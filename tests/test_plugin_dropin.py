@@ -36,12 +36,14 @@ def test_plugin_fails_loudly_without_a_gpu(oracle):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode,lights", [(scenefile.MODE_PATH, False), (scenefile.MODE_DIRECT, False), (scenefile.MODE_PATH, True)])
+@pytest.mark.parametrize("mode,lights", [(scenefile.MODE_PATH, False), (scenefile.MODE_DIRECT, False), (scenefile.MODE_PATH, True),
+                                         (scenefile.MODE_PATH, "textures")])
 def test_plugin_renders_through_mitsuba(oracle, mode, lights):
     need_plugin()
     # `lights`: point / spot / directional / constant luminaires, decoded by the plugin from Luminaire::serialize
-    s = (scenes.lights_test_scene if lights else scenes.material_test_scene)(64, 64, 256, mode, max_depth=8)
-    if lights:
+    make = scenes.textured_test_scene if lights == "textures" else scenes.lights_test_scene if lights else scenes.material_test_scene
+    s = make(64, 64, 256, mode, max_depth=8)       # "textures": checkerboards decoded from the BSDFs' serialised children
+    if lights is True:
         s.sampler_type, s.sampler_depth = 1, 4          # ldsampler: the plugin reads `depth` from LowDiscrepancySampler::serialize
     s.filter_type = scenefile.FILTER_GAUSSIAN if mode == scenefile.MODE_DIRECT else scenefile.FILTER_BOX
     sess = oracle.Session(s)

@@ -87,6 +87,17 @@ def test_delta_lights_without_background_path(oracle, gpu_ctx_factory):
     compare(s, oracle, gpu_ctx_factory, 64)
 
 
+def test_checkerboard_textures_path(oracle, gpu_ctx_factory):
+    """Texture coordinates on every mesh, checkerboards in the reflectance slots of five BSDF types."""
+    s = scenes.textured_test_scene(64, 64, 64, scenefile.MODE_PATH, max_depth=8)
+    compare(s, oracle, gpu_ctx_factory, 64)
+
+
+def test_checkerboard_textures_direct(oracle, gpu_ctx_factory):
+    s = scenes.textured_test_scene(64, 64, 64, scenefile.MODE_DIRECT)
+    compare(s, oracle, gpu_ctx_factory, 64)
+
+
 def test_direct_multi_sample_and_gaussian_filter(oracle, gpu_ctx_factory):
     s = scenes.material_test_scene(48, 48, 32, scenefile.MODE_DIRECT)
     s.luminaire_samples, s.bsdf_samples = 3, 2
