@@ -234,7 +234,10 @@ __device__ __forceinline__ bool nextEvent(const DeviceScene &sc, const Integrato
 
 // One shading step for the queue entry i. MODE 0 = path, 1 = direct (primary pass), 2 = direct (secondary pass).
 template <int MODE>
-__global__ void __launch_bounds__(WF_BLOCK, 6)      // <= 80 registers: measured 9 % faster than the uncapped 122
+#ifndef SHADE_MIN_BLOCKS
+#define SHADE_MIN_BLOCKS 6
+#endif
+__global__ void __launch_bounds__(WF_BLOCK, SHADE_MIN_BLOCKS)      // 6: <= 80 registers, measured 9 % faster than the uncapped 122
 k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const FilmDev film, WfArrays wf, uint32_t n, uint32_t round) {
 	const uint32_t i = blockIdx.x * WF_BLOCK + threadIdx.x;
 	bool emitRay = false, emitShadow = false;

@@ -24,6 +24,7 @@ def main():
     ap.add_argument("--spp", type=int, default=64)
     ap.add_argument("--set", action="append", default=[])
     ap.add_argument("--repeat", type=int, default=2)
+    ap.add_argument("--lib", default=None, help="alternative libmtscuda build to load")
     args = ap.parse_args()
     if args.render == "c1":
         rs = scenes.cornell_box(512, 512, 64)
@@ -34,7 +35,7 @@ def main():
     else:
         rs = scenes.path_scene()
     rs.spp = args.spp
-    ctx = api.Context(0)
+    ctx = api.Context(0, args.lib)
     ctx.upload_scene(rs)
     film = torch.zeros(rs.width * rs.height * 5, dtype=torch.float32, device="cuda")
     params = api.Context.params_from_scene(rs, 0, rs.spp, seed=1)
