@@ -5,6 +5,7 @@
 //   microfacet  src/bsdfs/microfacet.cpp:95-269      roughmetal  src/bsdfs/roughmetal.cpp:75-167
 //   dielectric  src/bsdfs/dielectric.cpp:101-290     base 3-arg fallback src/librender/bsdf.cpp:37-48
 //   phong       src/bsdfs/phong.cpp:104-234          roughglass  src/bsdfs/roughglass.cpp:209-598
+//   ward        src/bsdfs/ward.cpp:145-285
 // All directions are in the local shading frame (wi.z = cos theta). Queries use the full type
 // mask, component = -1 and quantity = ERadiance, which is what path.cpp / direct.cpp pass.
 #pragma once
@@ -254,6 +255,52 @@ __device__ inline V3 roughglassSample2(const MaterialDev &m, V3 wi, float sx, fl
 	return result * fabsf(numerator / denominator);
 }
 
+// ---- ward (src/bsdfs/ward.cpp): p[6] kd, p[7] ks, p[8] alphaX, p[9] alphaY, p[10] / p[11] sampling weights, p[12] model ----
+// std::pow(Float, int) promotes to double (C++11), and the reference keeps that double through the rest of the
+// expression before rounding to Float; the two factors below do the same.
+__device__ inline float wardSpecRef(const MaterialDev &m, V3 wi, V3 wo) {                    // ward.cpp:157-186
+	const float ax = m.p[8], ay = m.p[9];
+	const V3 H = wi + wo;
+	float factor1 = 0.0f;
+	const int model = (int) m.p[12];
+	if (model == 0) factor1 = 1.0f / (4.0f * MTS_PI * ax * ay * sqrtf(wi.z * wo.z));
+	else if (model == 1) factor1 = 1.0f / (4.0f * MTS_PI * ax * ay * wi.z * wo.z);
+	else factor1 = (float) ((double) dot(H, H) / ((double) (MTS_PI * ax * ay) * pow((double) H.z, 4.0)));
+	const float factor2 = H.x / ax, factor3 = H.y / ay;
+	const float exponent = -(factor2 * factor2 + factor3 * factor3) / (H.z * H.z);
+	return factor1 * mts_exp(exponent) * m.p[7];
+}
+__device__ inline float wardPdfSpec(const MaterialDev &m, V3 wi, V3 wo) {                    // ward.cpp:196-205
+	const float ax = m.p[8], ay = m.p[9];
+	const V3 H = normalize(wi + wo);
+	const float factor1 = (float) (1.0 / ((double) (4.0f * MTS_PI * ax * ay * dot(H, wi)) * pow((double) H.z, 3.0)));
+	const float factor2 = H.x / ax, factor3 = H.y / ay;
+	const float exponent = -(factor2 * factor2 + factor3 * factor3) / (H.z * H.z);
+	return factor1 * mts_exp(exponent);
+}
+__device__ inline V3 wardF(const MaterialDev &m, V3 wi, V3 wo) {                             // ward.cpp:145-194
+	V3 result = v3(0, 0, 0);
+	if (wi.z <= 0 || wo.z <= 0) return result;
+	const float specRef = wardSpecRef(m, wi, wo);
+	if (specRef > 1e-10f) result = result + mp3(m, 3) * specRef;
+	result = result + mp3(m, 0) * (MTS_INV_PI * m.p[6]);
+	return result;
+}
+__device__ inline float wardPdf(const MaterialDev &m, V3 wi, V3 wo) {                        // ward.cpp:207-227
+	if (wi.z <= 0 || wo.z <= 0) return 0.0f;
+	return m.p[10] * wardPdfSpec(m, wi, wo) + m.p[11] * (wo.z * MTS_INV_PI);
+}
+// half vector of the specular lobe (ward.cpp:229-243)
+__device__ inline V3 wardSampleH(const MaterialDev &m, float sx, float sy) {
+	const float ax = m.p[8], ay = m.p[9];
+	float phiH = mts_atan(ay / ax * mts_tan(2.0f * MTS_PI * sy));
+	if (sy > 0.5f) phiH += MTS_PI;
+	const float cosPhiH = mts_cos(phiH);
+	const float sinPhiH = sqrtf(fmaxf(0.0f, 1.0f - cosPhiH * cosPhiH));
+	const float thetaH = mts_atan(sqrtf(fmaxf(0.0f, -mts_log(sx) / ((cosPhiH * cosPhiH) / (ax * ax) + (sinPhiH * sinPhiH) / (ay * ay)))));
+	return sphericalDirection(thetaH, phiH);
+}
+
 // ---- f ---------------------------------------------------------------------------------------------
 __device__ inline V3 bsdfF_base(const MaterialDev &m, V3 wi, V3 wo) {
 	const V3 zero = v3(0, 0, 0);
@@ -296,6 +343,8 @@ __device__ inline V3 bsdfF_base(const MaterialDev &m, V3 wi, V3 wo) {
 		}
 		case MTSGPU_BSDF_ROUGHGLASS:
 			return roughglassF(m, wi, wo);
+		case MTSGPU_BSDF_WARD:
+			return wardF(m, wi, wo);
 		default:   // mirror, dielectric: delta lobes only
 			return zero;
 	}
@@ -340,6 +389,8 @@ __device__ inline float bsdfPdf_base(const MaterialDev &m, V3 wi, V3 wo) {
 		}
 		case MTSGPU_BSDF_ROUGHGLASS:
 			return roughglassPdf(m, wi, wo);
+		case MTSGPU_BSDF_WARD:
+			return wardPdf(m, wi, wo);
 		default:
 			return 0.0f;
 	}
@@ -389,6 +440,7 @@ __device__ inline void bsdfFPdf_base(const MaterialDev &m, V3 wi, V3 wo, V3 &f, 
 		}
 		case MTSGPU_BSDF_PHONG:
 		case MTSGPU_BSDF_ROUGHGLASS:
+		case MTSGPU_BSDF_WARD:
 			f = bsdfF_base(m, wi, wo); pdf = bsdfPdf_base(m, wi, wo);
 			return;
 		default:
@@ -442,6 +494,20 @@ __device__ inline bool bsdfSampleRough(const MaterialDev &m, V3 wi, float sx, fl
 			type = BSDF_DIFFUSE_REFLECTION;
 			bsdfFPdf_base(m, wi, wo, f, pdf);
 		}
+	} else if ((m.type & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_WARD) {       // ward.cpp:229-285
+		const float ssw = m.p[10], dsw = m.p[11];
+		if (sx <= ssw) {
+			sx = sx / ssw;
+			const V3 H = wardSampleH(m, sx, sy);
+			wo = H * (2.0f * dot(wi, H)) - wi;
+			type = BSDF_GLOSSY_REFLECTION;
+			if (wo.z <= 0.0f) return false;
+		} else {
+			sx = (sx - ssw) / dsw;
+			wo = squareToHemispherePSA(sx, sy);
+			type = BSDF_DIFFUSE_REFLECTION;
+		}
+		bsdfFPdf_base(m, wi, wo, f, pdf);
 	} else {
 		wo = reflectAbout(wi, sampleBeckmannD(sx, sy, m.p[3]));
 		type = BSDF_GLOSSY_REFLECTION;
@@ -486,6 +552,7 @@ __device__ inline V3 bsdfSample2_base(const MaterialDev &m, V3 wi, float sx, flo
 			return mp3(m, 0);                               // Mirror::sample(2-arg) forwards to the 3-arg one
 		case MTSGPU_BSDF_MICROFACET:
 		case MTSGPU_BSDF_PHONG:
+		case MTSGPU_BSDF_WARD:
 		case MTSGPU_BSDF_ROUGHMETAL: {
 			V3 f, ratio; float pdf;
 			return bsdfSampleRough(m, wi, sx, sy, wo, type, f, pdf, ratio) ? ratio : zero;

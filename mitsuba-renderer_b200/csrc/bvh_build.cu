@@ -349,6 +349,81 @@ inline unsigned blocksFor(size_t n, unsigned bs) { return (unsigned) ((n + bs - 
 
 } // namespace
 
+// Host-side TriMesh::computeTangentSpaceBasis (src/librender/trimesh.cpp:547-662): per-vertex dpdu / dpdv from the
+// texture coordinates, accumulated over the triangles in order and averaged; same float operations in the same order.
+// `nrm` is updated too: zero normals become (1, 0, 0) there. Only dpdu is kept (the shading frame uses nothing else).
+namespace {
+struct HV { float x, y, z; };
+inline HV hsub(HV a, HV b) { return { a.x - b.x, a.y - b.y, a.z - b.z }; }
+inline HV hadd(HV a, HV b) { return { a.x + b.x, a.y + b.y, a.z + b.z }; }
+inline HV hmul(HV a, float f) { return { a.x * f, a.y * f, a.z * f }; }
+inline HV hcross(HV a, HV b) { return { a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x }; }
+inline float hlen2(HV a) { return a.x * a.x + a.y * a.y + a.z * a.z; }
+inline float hlen(HV a) { return std::sqrt(hlen2(a)); }
+inline HV hdiv(HV a, float f) { const float r = 1.0f / f; return hmul(a, r); }
+inline void hcoordinateSystem(HV a, HV &b, HV &c) {                 // src/libcore/util.cpp:602-611
+	if (std::fabs(a.x) > std::fabs(a.y)) {
+		const float invLen = 1.0f / std::sqrt(a.x * a.x + a.z * a.z);
+		b = { -a.z * invLen, 0.0f, a.x * invLen };
+	} else {
+		const float invLen = 1.0f / std::sqrt(a.y * a.y + a.z * a.z);
+		b = { 0.0f, -a.z * invLen, a.y * invLen };
+	}
+	c = hcross(a, b);
+}
+}
+
+static void computeTangents(HostMesh &m, std::vector<float> &dpduOut) {
+	const size_t nv = m.nVert;
+	std::vector<HV> dpdu(nv, HV{ 0, 0, 0 }), dpdv(nv, HV{ 0, 0, 0 });
+	std::vector<uint32_t> sharers(nv, 0u);
+	HV *N = reinterpret_cast<HV *>(m.nrm.data());
+	const HV *P = reinterpret_cast<const HV *>(m.pos.data());
+	for (size_t i = 0; i < nv; ++i)
+		if (N[i].x == 0 && N[i].y == 0 && N[i].z == 0) N[i] = { 1.0f, 0.0f, 0.0f };
+	for (uint32_t t = 0; t < m.nTri; ++t) {
+		const uint32_t i0 = m.tri[3 * t], i1 = m.tri[3 * t + 1], i2 = m.tri[3 * t + 2];
+		const HV v0 = P[i0], v1 = P[i1], v2 = P[i2];
+		const float u0x = m.uv[2 * i0], u0y = m.uv[2 * i0 + 1];
+		const HV dP1 = hsub(v1, v0), dP2 = hsub(v2, v0);
+		const float d1x = m.uv[2 * i1] - u0x, d1y = m.uv[2 * i1 + 1] - u0y, d2x = m.uv[2 * i2] - u0x, d2y = m.uv[2 * i2 + 1] - u0y;
+		float invDet = 1.0f; const float determinant = d1x * d2y - d1y * d2x;
+		if (determinant != 0) invDet = 1.0f / determinant;
+		HV du = hmul(hsub(hmul(dP1, d2y), hmul(dP2, d1y)), invDet);
+		HV dv = hmul(hadd(hmul(dP1, -d2x), hmul(dP2, d1x)), invDet);
+		if (hlen(du) == 0.0f) {
+			HV n = hcross(hsub(v1, v0), hsub(v2, v0));
+			const float length = hlen(n);
+			if (length != 0) {
+				n = hdiv(n, length);
+				du = hcross(n, dv);
+				if (hlen(du) == 0.0f) hcoordinateSystem(n, du, dv);
+			}
+		}
+		if (hlen(dv) == 0.0f) {
+			HV n = hcross(hsub(v1, v0), hsub(v2, v0));
+			const float length = hlen(n);
+			if (length != 0) {
+				n = hdiv(n, length);
+				dv = hcross(du, n);
+				if (hlen(dv) == 0.0f) hcoordinateSystem(n, du, dv);
+			}
+		}
+		dpdu[i0] = hadd(dpdu[i0], du); dpdu[i1] = hadd(dpdu[i1], du); dpdu[i2] = hadd(dpdu[i2], du);
+		dpdv[i0] = hadd(dpdv[i0], dv); dpdv[i1] = hadd(dpdv[i1], dv); dpdv[i2] = hadd(dpdv[i2], dv);
+		sharers[i0]++; sharers[i1]++; sharers[i2]++;
+	}
+	dpduOut.resize(3 * nv);
+	for (size_t i = 0; i < nv; ++i) {
+		if (hlen2(dpdu[i]) == 0.0f || hlen2(dpdv[i]) == 0.0f) {
+			hcoordinateSystem(N[i], dpdu[i], dpdv[i]);
+		} else if (sharers[i] > 0) {
+			dpdu[i] = hdiv(dpdu[i], (float) sharers[i]);
+		}
+		dpduOut[3 * i] = dpdu[i].x; dpduOut[3 * i + 1] = dpdu[i].y; dpduOut[3 * i + 2] = dpdu[i].z;
+	}
+}
+
 // Host-side DiscretePDF::build (include/mitsuba/core/pdf.h:82-100), float arithmetic in the same order.
 static float buildCdf(const std::vector<float> &pdf, std::vector<float> &cdf) {
 	cdf.assign(pdf.size() + 1, 0.0f);
@@ -470,6 +545,23 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	bool anyTexcoords = false;
 	for (auto &m : ctx->meshes) anyTexcoords |= !m.uv.empty();
 	std::vector<float2> uvs(anyTexcoords ? nVert : 1, make_float2(0, 0));
+	// TriMesh::configure (trimesh.cpp:288-290): meshes with an anisotropic BSDF get a tangent space
+	std::vector<std::vector<float> > meshTangents(nShapes);
+	bool anyTangents = false;
+	for (size_t s = 0; s < nShapes; ++s) {
+		HostMesh &m = ctx->meshes[s];
+		if (m.materialId < 0 || m.materialId >= (int) ctx->materials.size()) continue;
+		const mtsgpu_material &mat = ctx->materials[m.materialId];
+		const bool anisotropic = (mat.type & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_WARD && mat.p[8] != mat.p[9];
+		if (!anisotropic) continue;
+		REQUIRE(ctx, !m.uv.empty(), MTSGPU_ERR_ARG, "shape %zu: computeTangentSpace(): texture coordinates are required to generate "
+			"tangent vectors. If you want to render with an anisotropic material, please make sure that all associated shapes have "
+			"valid texture coordinates.", s);
+		if (!m.hasNormals) continue;                  // "Vertex normals are required to compute a tangent space basis!" (warning only)
+		computeTangents(m, meshTangents[s]);
+		anyTangents = true;
+	}
+	std::vector<float4> tangents(anyTangents ? nVert : 1, make_float4(0, 0, 0, 0));
 	std::vector<ShapeInfo> shapes(nShapes);
 	std::vector<float> areaCdfAll;
 	std::vector<int> emitterShape(ctx->emitters.size(), -1);
@@ -482,6 +574,9 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		si.triOffset = (uint32_t) tOff; si.vertOffset = (uint32_t) vOff;
 		si.nTri = m.nTri; si.nVert = m.nVert; si.hasNormals = m.hasNormals ? 1u : 0u;
 		si.hasTexcoords = m.uv.empty() ? 0u : 1u;
+		si.hasTangents = meshTangents[s].empty() ? 0u : 1u;
+		for (uint32_t v = 0; v < (meshTangents[s].empty() ? 0u : m.nVert); ++v)
+			tangents[vOff + v] = make_float4(meshTangents[s][3*v], meshTangents[s][3*v+1], meshTangents[s][3*v+2], 0);
 		for (uint32_t v = 0; v < (m.uv.empty() ? 0u : m.nVert); ++v) uvs[vOff + v] = make_float2(m.uv[2*v], m.uv[2*v+1]);
 		REQUIRE(ctx, m.materialId < (int) ctx->materials.size(), MTSGPU_ERR_ARG, "shape %zu: material id %d out of range", s, m.materialId);
 		REQUIRE(ctx, m.emitterId < (int) ctx->emitters.size(), MTSGPU_ERR_ARG, "shape %zu: emitter id %d out of range", s, m.emitterId);
@@ -540,7 +635,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 			REQUIRE(ctx, t <= ctx->textures.size(), MTSGPU_ERR_ARG, "material %zu: texture %u of slot %d was not uploaded", i, t, k);
 			const uint32_t bt = mats[i].type & MTSGPU_BSDF_TYPE_MASK;
 			const bool slotOk = k == 0 ? (bt != MTSGPU_BSDF_MIRROR && bt != MTSGPU_BSDF_DIELECTRIC)
-				: (bt == MTSGPU_BSDF_MICROFACET || bt == MTSGPU_BSDF_PHONG || bt == MTSGPU_BSDF_ROUGHGLASS);
+				: (bt == MTSGPU_BSDF_MICROFACET || bt == MTSGPU_BSDF_PHONG || bt == MTSGPU_BSDF_ROUGHGLASS || bt == MTSGPU_BSDF_WARD);
 			REQUIRE(ctx, t == 0 || slotOk, MTSGPU_ERR_UNSUPPORTED, "material %zu: slot %d of this BSDF is a plain spectrum in the reference and cannot be textured", i, k);
 			mats[i].tex[k] = t;
 		}
@@ -559,6 +654,8 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dTriIdx.p, triIdx.data(), nTri * sizeof(uint4), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dPositions.p, pos.data(), nVert * sizeof(float4), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dNormals.p, nrm.data(), nVert * sizeof(float4), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, ctx->dTangents.alloc(tangents.size() * sizeof(float4)));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dTangents.p, tangents.data(), tangents.size() * sizeof(float4), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, ctx->dTexcoords.alloc(uvs.size() * sizeof(float2)));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dTexcoords.p, uvs.data(), uvs.size() * sizeof(float2), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, ctx->dTextures.alloc(texs.size() * sizeof(TextureDev)));
@@ -761,6 +858,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	sc.positions = ctx->dPositions.as<float4>();
 	sc.normals = ctx->dNormals.as<float4>();
 	sc.texcoords = ctx->dTexcoords.as<float2>();
+	sc.tangents = ctx->dTangents.as<float4>();
 	sc.textures = ctx->dTextures.as<TextureDev>();
 	sc.shapes = ctx->dShapes.as<ShapeInfo>();
 	sc.materials = ctx->dMaterials.as<MaterialDev>();

@@ -192,6 +192,15 @@ __device__ inline void fillIntersection(const DeviceScene &sc, uint32_t shape, u
 	} else {
 		its.shN = fn;
 	}
+	bool tangentFrame = false;
+	if (si.hasNormals && si.hasTangents) {     // skdtree.h:385-398: the shading frame follows the interpolated dpdu
+		const V3 d0 = v3(__ldg(sc.tangents + idx.x)), d1 = v3(__ldg(sc.tangents + idx.y)), d2 = v3(__ldg(sc.tangents + idx.z));
+		const V3 dpdu = d0 * bx + d1 * by + d2 * bz;
+		its.sh.n = its.shN;
+		its.sh.s = normalize(dpdu - its.shN * dot(its.shN, dpdu));
+		its.sh.t = cross(its.shN, its.sh.s);
+		tangentFrame = true;
+	}
 	if (si.hasTexcoords) {                     // its.uv = t0 * b.x + t1 * b.y + t2 * b.z (skdtree.h:408-413)
 		const float2 t0 = __ldg(sc.texcoords + idx.x), t1 = __ldg(sc.texcoords + idx.y), t2 = __ldg(sc.texcoords + idx.z);
 		its.uvx = t0.x * bx + t1.x * by + t2.x * bz;
@@ -199,7 +208,7 @@ __device__ inline void fillIntersection(const DeviceScene &sc, uint32_t shape, u
 	} else {
 		its.uvx = its.uvy = 0.0f;
 	}
-	its.sh = makeFrame(its.shN);
+	if (!tangentFrame) its.sh = makeFrame(its.shN);
 	its.wi = toLocal(its.sh, -rayD);
 	its.shape = shape; its.materialId = si.materialId; its.emitterId = si.emitterId;
 }

@@ -40,7 +40,8 @@ struct ShapeInfo {
 	uint32_t cdfOffset;       // into DeviceScene::areaCdf (emitter meshes only)
 	float invSurfaceArea;     // TriMesh::m_invSurfaceArea (trimesh.cpp:281)
 	uint32_t hasTexcoords;
-	uint32_t pad[2];
+	uint32_t hasTangents;     // per-vertex dpdu present (TriMesh::computeTangentSpaceBasis ran for this mesh)
+	uint32_t pad;
 };
 
 struct MaterialDev { uint32_t type; float p[16]; uint32_t tex[2]; uint32_t pad; };   // tex: 0 constant, k: textures[k-1]
@@ -69,6 +70,7 @@ struct DeviceScene {
 	const uint4 *triIdx;        // kd primitive order: {v0, v1, v2 (global vertex ids), shape}
 	const float4 *positions;    // global vertex arrays, xyz + pad
 	const float4 *normals;
+	const float4 *tangents;     // global vertex array of dpdu; only read for shapes with hasTangents
 	const float2 *texcoords;    // global vertex array; only read for shapes with hasTexcoords
 	const TextureDev *textures;
 	const ShapeInfo *shapes;
@@ -90,6 +92,7 @@ struct DeviceScene {
 // in almost every case. These run a handful of times per shading event, never in traversal.
 __device__ __forceinline__ float mts_sin(float x) { return (float) sin((double) x); }
 __device__ __forceinline__ float mts_cos(float x) { return (float) cos((double) x); }
+__device__ __forceinline__ float mts_tan(float x) { return (float) tan((double) x); }
 __device__ __forceinline__ float mts_atan(float x) { return (float) atan((double) x); }
 __device__ __forceinline__ float mts_acos(float x) { return (float) acos((double) x); }
 __device__ __forceinline__ float mts_log(float x) { return (float) log((double) x); }

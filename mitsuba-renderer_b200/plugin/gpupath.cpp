@@ -193,6 +193,12 @@ private:
 			readTextureSlot(d, m.p, m.texture[0]); readTextureSlot(d, m.p + 3, m.texture[1]);
 			m.p[8] = s->readFloat(); m.p[6] = s->readFloat(); m.p[7] = s->readFloat();   /* exponent, kd, ks */
 			m.p[9] = s->readFloat(); m.p[10] = s->readFloat();                            /* sampling weights */
+		} else if (cls == "Ward") {                   /* ward.cpp:299-311 */
+			m.type = MTSGPU_BSDF_WARD;
+			m.p[12] = (float) s->readUInt();
+			readTextureSlot(d, m.p, m.texture[0]); readTextureSlot(d, m.p + 3, m.texture[1]);
+			m.p[8] = s->readFloat(); m.p[9] = s->readFloat(); m.p[6] = s->readFloat(); m.p[7] = s->readFloat();   /* alphaX, alphaY, kd, ks */
+			m.p[10] = s->readFloat(); m.p[11] = s->readFloat();                                                    /* sampling weights */
 		} else if (cls == "RoughGlass") {             /* roughglass.cpp:735-744 */
 			m.type = MTSGPU_BSDF_ROUGHGLASS;
 			m.p[9] = (float) s->readInt();
@@ -214,7 +220,7 @@ private:
 			if (t0 || t1) SLog(EError, "gpupath: textured dielectric is outside the supported hot path");
 		} else {
 			SLog(EError, "gpupath: BSDF class \"%s\" is outside the supported hot path "
-				"(lambertian, microfacet, mirror, roughmetal, dielectric, phong, roughglass, twosided)", cls.c_str());
+				"(lambertian, microfacet, mirror, roughmetal, dielectric, phong, roughglass, ward, twosided)", cls.c_str());
 		}
 		return m;
 	}

@@ -19,7 +19,7 @@ from typing import List, Optional
 
 import numpy as np
 
-MAT_LAMBERTIAN, MAT_MICROFACET, MAT_MIRROR, MAT_ROUGHMETAL, MAT_DIELECTRIC, MAT_PHONG, MAT_ROUGHGLASS = range(7)
+MAT_LAMBERTIAN, MAT_MICROFACET, MAT_MIRROR, MAT_ROUGHMETAL, MAT_DIELECTRIC, MAT_PHONG, MAT_ROUGHGLASS, MAT_WARD = range(8)
 BSDF_TWOSIDED = 0x100     # OR-ed into Material.type: wrapped in the `twosided` adapter (src/bsdfs/twosided.cpp)
 MODE_PATH, MODE_DIRECT = 0, 1
 FILTER_BOX, FILTER_GAUSSIAN = 0, 1
@@ -98,6 +98,23 @@ def phong(diffuse=(0.5, 0.5, 0.5), specular=(0.2, 0.2, 0.2), kd=1.0, ks=1.0, exp
         specular_sampling_weight = float(f32(as_ / f32(ad + as_)))
     ssw = f32(specular_sampling_weight)
     return _mat(MAT_PHONG, list(diffuse) + list(specular) + [kd, ks, exponent, float(ssw), float(f32(1.0) - ssw)])
+
+
+WARD_MODELS = {"ward": 0, "ward-duer": 1, "balanced": 2}
+
+
+def ward(diffuse=(0.5, 0.5, 0.5), specular=(0.2, 0.2, 0.2), kd=1.0, ks=1.0, alpha_x=0.1, alpha_y=0.1, model="balanced",
+         specular_sampling_weight=None):
+    """src/bsdfs/ward.cpp:54-139, values after Ward::configure (energy conservation is the caller's business).
+    alpha_x != alpha_y makes it anisotropic: its meshes then need texture coordinates and vertex normals."""
+    f32 = np.float32
+    if specular_sampling_weight is None:
+        avg = lambda c: f32(f32(f32(f32(c[0]) + f32(c[1])) + f32(c[2])) * f32(1.0 / 3.0))
+        ad, as_ = f32(avg(diffuse) * f32(kd)), f32(avg(specular) * f32(ks))
+        specular_sampling_weight = float(f32(as_ / f32(ad + as_)))
+    ssw = f32(specular_sampling_weight)
+    return _mat(MAT_WARD, list(diffuse) + list(specular) + [kd, ks, alpha_x, alpha_y, float(ssw), float(f32(1.0) - ssw),
+                                                             float(WARD_MODELS[model])])
 
 
 ROUGHGLASS_DISTRIBUTIONS = {"beckmann": 0, "phong": 1, "ggx": 2}

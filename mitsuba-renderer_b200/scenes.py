@@ -9,7 +9,7 @@ import numpy as np
 
 from .scenefile import (SceneDesc, Shape, Emitter, lambertian, microfacet, mirror, roughmetal,
                         dielectric, twosided, phong, roughglass, look_at, point_light, spot_light, directional_light,
-                        constant_light, add_light, checkerboard, textured, MODE_PATH, MODE_DIRECT, FILTER_BOX)
+                        constant_light, add_light, checkerboard, textured, ward, MODE_PATH, MODE_DIRECT, FILTER_BOX)
 
 F32 = np.float32
 
@@ -144,6 +144,11 @@ def textured_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6
     m[6] = textured(m[6], 0, 2)        # short block: roughmetal specularReflectance
     m[9] = textured(textured(m[9], 0, 1), 1, 2)    # panel: phong, both slots
     m[10] = textured(m[10], 1, 2)      # ball: roughglass specularTransmittance
+    # anisotropic Ward on the smooth sphere (tangent frames from the texture coordinates) and on the tall block
+    m.append(textured(ward((0.25, 0.2, 0.15), (0.6, 0.6, 0.6), 1.0, 1.0, 0.05, 0.25, "balanced"), 0, 1))
+    m.append(ward((0.2, 0.3, 0.4), (0.5, 0.5, 0.5), 1.0, 1.0, 0.3, 0.06, "ward"))
+    s.shapes[6].material = len(m) - 2
+    s.shapes[4].material = len(m) - 1
     return s
 
 

@@ -189,14 +189,29 @@ static ref<BSDF> makeBSDF(const sio::Material &mIn) {
 			p.setString("distribution", distr[d < 0 || d > 2 ? 0 : d]);
 			break;
 		}
+		case 7: { /* ward: the file holds post-configure values (ward.cpp:120-139) */
+			static const char *models[3] = { "ward", "ward-duer", "balanced" };
+			const int mt = (int) m.p[12];
+			p = Properties("ward");
+			p.setSpectrum("diffuseReflectance", rgb(m.p));
+			p.setSpectrum("specularReflectance", rgb(m.p + 3));
+			p.setFloat("diffuseAmount", m.p[6]);
+			p.setFloat("specularAmount", m.p[7]);
+			p.setFloat("alphaX", m.p[8]);
+			p.setFloat("alphaY", m.p[9]);
+			p.setFloat("specularSamplingWeight", m.p[10]);
+			p.setString("type", models[mt < 0 || mt > 2 ? 2 : mt]);
+			p.setBoolean("verifyEnergyConservation", false);
+			break;
+		}
 		default:
 			SLog(EError, "unknown material type %u", m.type);
 	}
 	ref<BSDF> bsdf = static_cast<BSDF *>(create(MTS_CLASS(BSDF), p));
 	/* textured slots: <ref name="reflectance" id="..."/> inside the <bsdf> element */
-	static const char *slotNames[7][2] = { { "reflectance", NULL }, { "diffuseReflectance", "specularReflectance" }, { NULL, NULL },
+	static const char *slotNames[8][2] = { { "reflectance", NULL }, { "diffuseReflectance", "specularReflectance" }, { NULL, NULL },
 		{ "specularReflectance", NULL }, { NULL, NULL }, { "diffuseReflectance", "specularReflectance" },
-		{ "specularReflectance", "specularTransmittance" } };
+		{ "specularReflectance", "specularTransmittance" }, { "diffuseReflectance", "specularReflectance" } };
 	for (int k = 0; k < 2; ++k) {
 		if (!m.tex[k]) continue;
 		if (!g_textures || m.tex[k] > g_textures->size() || !slotNames[m.type][k]) SLog(EError, "bad texture reference");

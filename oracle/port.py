@@ -255,6 +255,31 @@ def bsdf_f_pdf(mtype, p, wi, wo):
         f = ((p[3:6] * spec).astype(F) + (p[0:3] * F(INV_PI * kd)).astype(F)).astype(F)
         sp = F(0) if alpha <= 0 else F(F(pw * F(ex + F(1.0))) / F(F(2.0) * PI))
         return f, F(F(ssw * sp) + F(dsw * F(wo[2] * INV_PI)))
+    if mtype == 7:      # ward.cpp:145-227
+        if wi[2] <= 0 or wo[2] <= 0:
+            return zero, F(0)
+        kd, ks, ax, ay, ssw, dsw, model = p[6], p[7], p[8], p[9], p[10], p[11], int(p[12])
+        H = (wi + wo).astype(F)
+        with np.errstate(all="ignore"):
+            if model == 0:
+                f1 = F(F(1.0) / F(F(F(F(F(4.0) * PI) * ax) * ay) * np.sqrt(F(wi[2] * wo[2])).astype(F)))
+            elif model == 1:
+                f1 = F(F(1.0) / F(F(F(F(F(F(4.0) * PI) * ax) * ay) * wi[2]) * wo[2]))
+            else:       # std::pow(Float, int) is a double; the expression stays double until the assignment
+                f1 = F(float(_dot(H, H)) / (float(F(F(PI * ax) * ay)) * float(H[2]) ** 4))
+            f2, f3 = F(H[0] / ax), F(H[1] / ay)
+            ex = F(-F(F(f2 * f2) + F(f3 * f3)) / F(H[2] * H[2]))
+            spec = F(F(f1 * F(np.exp(ex, dtype=F))) * ks)
+            f = np.zeros(3, F)
+            if spec > F(1e-10):
+                f = (f + (p[3:6] * spec).astype(F)).astype(F)
+            f = (f + (p[0:3] * F(INV_PI * kd)).astype(F)).astype(F)
+            Hn = _normalize(H)
+            g1 = F(1.0 / (float(F(F(F(F(F(4.0) * PI) * ax) * ay) * _dot(Hn, wi))) * float(Hn[2]) ** 3))
+            g2, g3 = F(Hn[0] / ax), F(Hn[1] / ay)
+            gex = F(-F(F(g2 * g2) + F(g3 * g3)) / F(Hn[2] * Hn[2]))
+            pspec = F(g1 * F(np.exp(gex, dtype=F)))
+        return f, F(F(ssw * pspec) + F(dsw * F(wo[2] * INV_PI)))
     if mtype == 6:      # roughglass.cpp:345-488
         return _roughglass_f_pdf(p, wi, wo)
     if mtype in (2, 4):  # mirror / dielectric: delta only

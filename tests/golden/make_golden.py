@@ -60,7 +60,9 @@ def main():
     # ---- texture coordinates + textured reflectances at the hit ---------------------------------------------------------
     ts = gc.scene_textured()
     rays = gc.trace_rays(ts)
-    save("uv_textured", rays_digest=gc.digest(rays), out=oracle_util.Session(ts).uv(rays))
+    tsess = oracle_util.Session(ts)
+    thits, tfull, _ = tsess.trace(rays, "closest_full")       # `wi` in the tangent frames of the anisotropic Ward meshes
+    save("uv_textured", rays_digest=gc.digest(rays), out=tsess.uv(rays), hits=thits.view(np.uint8), full=tfull)
     # ---- TriAccel records + enlarged scene box --------------------------------------------------------
     rec, box, _ = oracle_util.Session(gc.scene_materials()).triaccel()
     save("triaccel_materials", records=rec.view(np.uint8), box=box)

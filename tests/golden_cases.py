@@ -63,7 +63,10 @@ def bsdf_scene():
                    scenefile.twosided(scenefile.phong((0.3, 0.3, 0.3), (0.6, 0.6, 0.6), 0.9, 0.8, 60.0, 0.7)),
                    scenefile.roughglass((0.9, 1.0, 0.8), (0.8, 0.9, 1.0), 0.1, 1.5046, 1.0, "beckmann"),  # roughglass.cpp defaults
                    scenefile.roughglass((1, 1, 1), (1, 1, 1), 0.3, 1.33, 1.0, "ggx"),
-                   scenefile.roughglass((1, 1, 1), (0.9, 0.9, 0.9), 0.25, 1.0, 1.5, "phong")]
+                   scenefile.roughglass((1, 1, 1), (0.9, 0.9, 0.9), 0.25, 1.0, 1.5, "phong"),
+                   scenefile.ward((0.5, 0.5, 0.5), (0.2, 0.2, 0.2), 1.0, 1.0, 0.1, 0.1, "balanced"),     # ward.cpp defaults
+                   scenefile.ward((0.3, 0.2, 0.1), (0.5, 0.6, 0.7), 0.8, 0.9, 0.05, 0.3, "ward"),
+                   scenefile.twosided(scenefile.ward((0.1, 0.2, 0.3), (0.7, 0.6, 0.5), 1.0, 1.0, 0.25, 0.08, "ward-duer", 0.6))]
     for sh in s.shapes:
         sh.material = 0
     return s
@@ -189,7 +192,7 @@ def film_accumulators(h=9, w=13, seed=31):
 
 def diffuse_reflectance_from_slots(scene, hits, slots):
     """What BSDF::getDiffuseReflectance(its) returns, from the hit's material and its (texture-resolved) slot 0:
-    lambertian: reflectance (lambertian.cpp:91-93); microfacet / phong: diffuseReflectance * kd; zero for the rest."""
+    lambertian: reflectance (lambertian.cpp:91-93); microfacet / phong / ward: diffuseReflectance * kd; zero for the rest."""
     out = np.zeros((len(hits), 3), np.float32)
     for i, h in enumerate(hits):
         if h["shape"] == 0xFFFFFFFF:
@@ -203,6 +206,6 @@ def diffuse_reflectance_from_slots(scene, hits, slots):
             pass
         if t == 0:
             out[i] = slots[i]
-        elif t in (1, 5):
+        elif t in (1, 5, 7):
             out[i] = (slots[i] * np.float32(m.p[6])).astype(np.float32)
     return out

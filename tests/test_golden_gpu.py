@@ -53,6 +53,15 @@ def test_texture_coordinates_and_textured_reflectance_match_golden(gpu_ctx_facto
     # a uv within rounding of a checker edge may land on the other colour: allow a handful
     bad = ~close(want, ref[:, 2:5], 1e-6, 1e-7).all(axis=1)
     assert bad.sum() <= 3, bad.sum()
+    # shading frames: the meshes under the anisotropic Ward materials use tangents computed from the texture
+    # coordinates (trimesh.cpp:547-662, skdtree.h:385-398); `wi` is expressed in that frame
+    ref_hits = g["hits"].view(api.HIT_DTYPE).reshape(-1)
+    check_closest(hits, ref_hits, "textured")
+    full = ctx.intersect_full(rays)[1]
+    same = (hits["shape"] == ref_hits["shape"]) & (hits["prim"] == ref_hits["prim"]) & hit
+    assert close(full[same], g["full"][same], 1e-5, 2e-6).all()
+    on_ward = same & np.isin(hits["shape"], [4, 6])
+    assert on_ward.sum() > 300
     textured = np.array([h["shape"] != 0xFFFFFFFF and scene.shapes[int(h["shape"])].material in (1, 2, 4, 9) for h in hits])
     assert len(np.unique(ref[textured, 2:5].round(4), axis=0)) >= 4        # both colours of several textures were hit
 
