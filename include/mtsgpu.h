@@ -144,7 +144,10 @@ typedef struct mtsgpu_render_params {
  * Sobol' radical inverses, XOR-scrambled) visited in a random order; sppTotal must be a power of two (the reference
  * rounds the sample count up, ldsampler.cpp:61-65). Scrambles and orders are counter-based here too (keyed by pixel,
  * dimension, seed), so the image does not depend on batching or on the GPU count. */
-enum mtsgpu_sampler_type { MTSGPU_SAMPLER_INDEPENDENT = 0, MTSGPU_SAMPLER_LD = 1 };
+/* MTSGPU_SAMPLER_STRATIFIED: src/samplers/stratified.cpp:123-182 — per pixel and draw the R x R strata of the unit square
+ * (R*R = sppTotal, which must be a perfect square; the reference rounds up, stratified.cpp:37-47) are visited in a
+ * random order with a jittered point in each; 1D draws use R*R strata of the unit interval. */
+enum mtsgpu_sampler_type { MTSGPU_SAMPLER_INDEPENDENT = 0, MTSGPU_SAMPLER_LD = 1, MTSGPU_SAMPLER_STRATIFIED = 2 };
 
 typedef struct mtsgpu_stats {
 	uint64_t cameraRays;      /* "Camera ray generations" (perspective.cpp:24) */

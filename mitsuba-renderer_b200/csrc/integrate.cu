@@ -518,13 +518,21 @@ static int uploadFilter(mtsgpu_ctx *ctx, DevBuf &dTable) {
 }
 
 static int makeSamplerConfig(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, SamplerConfig &cfg) {
-	REQUIRE(ctx, P->samplerType <= MTSGPU_SAMPLER_LD, MTSGPU_ERR_UNSUPPORTED, "render: unknown sampler type %u", P->samplerType);
-	cfg.type = P->samplerType; cfg.depth = P->samplerDepth; cfg.log2Count = 0;
+	REQUIRE(ctx, P->samplerType <= MTSGPU_SAMPLER_STRATIFIED, MTSGPU_ERR_UNSUPPORTED, "render: unknown sampler type %u", P->samplerType);
+	cfg.type = P->samplerType; cfg.depth = P->samplerDepth; cfg.log2Count = 0; cfg.resolution = 1;
 	cfg.lensDraw = (ctx->haveCamera && ctx->camera.apertureRadius > 0.0f) ? 1u : 0u;
 	if (cfg.type == MTSGPU_SAMPLER_LD) {
 		// the reference rounds the count up to a power of two and renders that many samples (ldsampler.cpp:61-65)
 		REQUIRE(ctx, P->sppTotal > 0 && (P->sppTotal & (P->sppTotal - 1)) == 0, MTSGPU_ERR_ARG,
 			"render: Sample count should be a power of two (got %u)", P->sppTotal);
+		while ((1u << cfg.log2Count) < P->sppTotal) cfg.log2Count++;
+	}
+	if (cfg.type == MTSGPU_SAMPLER_STRATIFIED) {
+		// the reference rounds the count up to a perfect square and renders that many samples (stratified.cpp:37-47)
+		uint32_t r = 1;
+		while ((uint64_t) r * r < P->sppTotal) ++r;
+		REQUIRE(ctx, P->sppTotal > 0 && r * r == P->sppTotal, MTSGPU_ERR_ARG, "render: Sample count should be a perfect square (got %u)", P->sppTotal);
+		cfg.resolution = r;
 		while ((1u << cfg.log2Count) < P->sppTotal) cfg.log2Count++;
 	}
 	return MTSGPU_OK;

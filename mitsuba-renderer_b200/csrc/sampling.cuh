@@ -30,6 +30,7 @@ struct SamplerConfig {
 	uint32_t depth;       // ldsampler depth
 	uint32_t log2Count;   // log2(sppTotal) in LD mode
 	uint32_t lensDraw;    // 1 when the camera takes a lens sample first (renderBlock, integrator.cpp:216-224)
+	uint32_t resolution;  // stratified: strata per axis (resolution^2 = sppTotal); log2Count = bits that hold sppTotal-1
 };
 __host__ __device__ inline float ldVanDerCorput(uint32_t n, uint32_t scramble) {       // ldsampler.cpp:104-112
 	n = (n << 16) | (n >> 16);
@@ -79,13 +80,25 @@ struct Sampler {
 	}
 	// dimension pair `dim`: independent of call order, so no counter has to live in the path state
 	__host__ __device__ void get2D(uint32_t dim, float &x, float &y) const {
-		if (cfg.type == MTSGPU_SAMPLER_LD) {
-			const uint32_t draw = draw2D(dim);
-			if (draw < cfg.depth) { ld2D(draw, sample, x, y); return; }
-		}
 		const uint64_t z = splitmix64(key + 0x9E3779B97F4A7C15ull * (uint64_t) (dim + 1));
 		x = uintToUnitFloat((uint32_t) z);
 		y = uintToUnitFloat((uint32_t) (z >> 32));
+		if (cfg.type == MTSGPU_SAMPLER_INDEPENDENT) return;
+		const uint32_t draw = draw2D(dim);
+		if (draw >= cfg.depth) return;
+		if (cfg.type == MTSGPU_SAMPLER_LD) { ld2D(draw, sample, x, y); return; }
+		// stratified.cpp:166-176: stratum k of a per-pixel random order, jittered
+		const uint32_t k = stratum(pixelKey + 0x9E3779B97F4A7C15ull * (uint64_t) (2 * draw + 2));
+		const float invRes = 1.0f / (float) cfg.resolution;
+		x = ((float) (k % cfg.resolution) + x) * invRes;
+		y = ((float) (k / cfg.resolution) + y) * invRes;
+	}
+	// this sample's entry in a keyed permutation of 0 .. resolution^2-1 (cycle-walking over the next power of two)
+	__host__ __device__ uint32_t stratum(uint64_t seedKey) const {
+		const uint32_t order = (uint32_t) splitmix64(seedKey), count = cfg.resolution * cfg.resolution;
+		uint32_t k = sample;
+		do { k = ldPermute(k, cfg.log2Count, order); } while (k >= count);
+		return k;
 	}
 	__host__ __device__ void ld2D(uint32_t draw, uint32_t sampleIndex, float &x, float &y) const {
 		const uint64_t h = splitmix64(pixelKey + 0x9E3779B97F4A7C15ull * (uint64_t) (2 * draw + 1));
@@ -96,6 +109,11 @@ struct Sampler {
 	}
 	// 1D draws: only the roulette decision uses them; draw number = how far past rrDepth the path is
 	__host__ __device__ float get1D(uint32_t dim, uint32_t draw1D = 0xFFFFFFFFu) const {
+		if (cfg.type == MTSGPU_SAMPLER_STRATIFIED && draw1D < cfg.depth) {         // stratified.cpp:157-161
+			const uint64_t z = splitmix64(key + 0x9E3779B97F4A7C15ull * (uint64_t) (dim + 1));
+			const uint32_t k = stratum(pixelKey + 0xA0761D6478BD642Full * (uint64_t) (2 * draw1D + 2));
+			return ((float) k + uintToUnitFloat((uint32_t) z)) * (1.0f / (float) (cfg.resolution * cfg.resolution));
+		}
 		if (cfg.type == MTSGPU_SAMPLER_LD && draw1D < cfg.depth) {
 			const uint64_t h = splitmix64(pixelKey + 0xA0761D6478BD642Full * (uint64_t) (2 * draw1D + 1));
 			const uint64_t order = splitmix64(pixelKey + 0xA0761D6478BD642Full * (uint64_t) (2 * draw1D + 2));

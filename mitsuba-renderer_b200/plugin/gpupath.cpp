@@ -426,7 +426,7 @@ private:
 		P.samplerType = MTSGPU_SAMPLER_INDEPENDENT; P.samplerDepth = 0;
 		{
 			const std::string samplerClass = sampler->getClass()->getName();
-			if (samplerClass == "LowDiscrepancySampler") {
+			if (samplerClass == "LowDiscrepancySampler" || samplerClass == "StratifiedSampler") {
 				/* m_depth has no getter: read it from LowDiscrepancySampler::serialize (ldsampler.cpp:76-80), which writes
 				   Sampler::serialize (sampler.cpp:39-49) first; the parent link (the camera) is cleared for the call */
 				Sampler *smp = const_cast<Sampler *>(sampler);
@@ -441,9 +441,11 @@ private:
 				ms->readSize();
 				for (size_t k = ms->readSize(); k > 0; --k) ms->readUInt();
 				for (size_t k = ms->readSize(); k > 0; --k) ms->readUInt();
-				P.samplerType = MTSGPU_SAMPLER_LD; P.samplerDepth = (uint32_t) ms->readInt();
+				/* both classes write Sampler::serialize, then m_depth (ldsampler.cpp:76-80, stratified.cpp:84-90) */
+				P.samplerType = samplerClass == "StratifiedSampler" ? MTSGPU_SAMPLER_STRATIFIED : MTSGPU_SAMPLER_LD;
+				P.samplerDepth = (uint32_t) ms->readInt();
 			} else if (samplerClass != "IndependentSampler") {
-				Log(EError, "gpupath: sampler class \"%s\" is outside the supported hot path (independent, ldsampler)", samplerClass.c_str());
+				Log(EError, "gpupath: sampler class \"%s\" is outside the supported hot path (independent, ldsampler, stratified)", samplerClass.c_str());
 			}
 		}
 		const size_t nPix = (size_t) csize.x * csize.y;

@@ -270,9 +270,9 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 		filter->setParent(out.film);
 		out.film->configure();
 
-		Properties sp(s.samplerType == 1 ? "ldsampler" : "independent");
+		Properties sp(s.samplerType == 1 ? "ldsampler" : s.samplerType == 2 ? "stratified" : "independent");
 		sp.setInteger("sampleCount", (int) s.spp);
-		if (s.samplerType == 1) sp.setInteger("depth", (int) s.samplerDepth);
+		if (s.samplerType != 0) sp.setInteger("depth", (int) s.samplerDepth);
 		ref<Sampler> sampler = static_cast<Sampler *>(create(MTS_CLASS(Sampler), sp));
 		sampler->configure();
 

@@ -65,6 +65,31 @@ def test_low_discrepancy_draws_are_scrambled_02_nets(gpu_ctx_factory):
         ctx.render(bad)
 
 
+def test_stratified_draws_cover_every_stratum_once(gpu_ctx_factory):
+    """stratified.cpp:166-176: the R x R cells of the unit square, one jittered sample in each, in a shuffled order."""
+    scene = scenes.cornell_box(32, 32, 36)
+    ctx = gpu_ctx_factory(scene)
+    s = copy.copy(scene); s.spp = 36; s.sampler_type = api.SAMPLER_STRATIFIED; s.sampler_depth = 2
+    p = Context.params_from_scene(s, seed=4)
+    orders = []
+    for pixel in (0, 7, 300):
+        for draw in range(2):
+            v = ctx.sampler_values(p, pixel, draw)
+            cells = (np.floor(v[:, 0] * 6).astype(int) % 6) + 6 * np.floor(v[:, 1] * 6).astype(int)
+            assert sorted(cells) == list(range(36)), (pixel, draw)
+            frac = v * 6 - np.floor(v * 6)
+            assert frac.std() > 0.2                              # jittered, not cell centres
+            orders.append(tuple(cells))
+        v = ctx.sampler_values(p, pixel, 2)                      # past the depth: independent
+        cells = np.floor(v[:, 0] * 6).astype(int) + 6 * np.floor(v[:, 1] * 6).astype(int)
+        assert len(set(cells)) < 36
+    assert len(set(orders)) == len(orders)                       # every pixel / draw has its own visiting order
+    assert all(o != tuple(range(36)) for o in orders)
+    bad = Context.params_from_scene(s, seed=4); bad.sppTotal = bad.sppEnd = 40
+    with pytest.raises(api.MtsGpuError, match="perfect square"):
+        ctx.render(bad)
+
+
 def develop(film):
     w = film[..., 4:5]
     return np.where(w > 0, film[..., :3] / np.maximum(w, 1e-20), 0.0)
@@ -74,13 +99,14 @@ def rel_mse(a, b, eps=1e-4):
     return float(np.mean((a - b) ** 2 / (b ** 2 + eps)))
 
 
-@pytest.mark.parametrize("mode", [scenefile.MODE_DIRECT, scenefile.MODE_PATH])
-def test_ldsampler_render_matches_reference_statistics(oracle, gpu_ctx_factory, mode):
+@pytest.mark.parametrize("mode,sampler", [(scenefile.MODE_DIRECT, api.SAMPLER_LD), (scenefile.MODE_PATH, api.SAMPLER_LD),
+                                          (scenefile.MODE_DIRECT, api.SAMPLER_STRATIFIED)])
+def test_ldsampler_render_matches_reference_statistics(oracle, gpu_ctx_factory, mode, sampler):
     """Same scene, sampler = ldsampler on both sides. The error against a converged image must match the CPU's at
     equal spp, and both must beat the independent sampler on direct lighting (that is the point of the sampler)."""
     spp = 16
     scene = scenes.material_test_scene(64, 64, spp, mode, max_depth=5)
-    scene.sampler_type, scene.sampler_depth = api.SAMPLER_LD, 3
+    scene.sampler_type, scene.sampler_depth = sampler, 3
     ref_scene = copy.copy(scene); ref_scene.spp = 1024
     ref = develop(oracle.Session(ref_scene).render()[0])
     cpu = develop(oracle.Session(scene).render()[0])
