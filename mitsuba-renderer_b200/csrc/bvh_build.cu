@@ -340,6 +340,26 @@ __global__ void k_ploc_apply(const int *cluster, int m, const int *nn, const uns
 	clusterOut[(uint32_t) (pos[i] & 0xFFFFFFFFull)] = id;
 }
 
+// Shading records (types.cuh: DeviceScene::shadeTris) in sorted triangle order + the inverse permutation
+__global__ void k_shade_tris(const uint32_t *order, const uint4 *triIdx, const float4 *positions, const float4 *normals,
+		const ShapeInfo *shapes, uint32_t n, float4 *out, uint32_t *sortedOf) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const uint32_t g = order[i];                       // kd primitive order (global triangle index)
+	sortedOf[g] = i;
+	const uint4 idx = triIdx[g];
+	const uint32_t prim = g - shapes[idx.w].triOffset;
+	const float4 p0 = positions[idx.x], p1 = positions[idx.y], p2 = positions[idx.z];
+	const float4 n0 = normals[idx.x], n1 = normals[idx.y], n2 = normals[idx.z];
+	float4 *o = out + (size_t) i * 6;
+	o[0] = make_float4(p0.x, p0.y, p0.z, __uint_as_float(idx.w));
+	o[1] = make_float4(p1.x, p1.y, p1.z, __uint_as_float(prim));
+	o[2] = make_float4(p2.x, p2.y, p2.z, __uint_as_float(idx.x));
+	o[3] = make_float4(n0.x, n0.y, n0.z, __uint_as_float(idx.y));
+	o[4] = make_float4(n1.x, n1.y, n1.z, __uint_as_float(idx.z));
+	o[5] = make_float4(n2.x, n2.y, n2.z, 0.0f);
+}
+
 __global__ void k_reorder(const uint32_t *sortedIdx, const TriAccelRec *orig, uint32_t n, TriAccelRec *sorted) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i < n) sorted[i] = orig[sortedIdx[i]];
@@ -846,6 +866,10 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	}
 	CUDA_TRY(ctx, ctx->dNodes.alloc((size_t) nodeCount * sizeof(BVH4Node)));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dNodes.p, dNodesTmp.p, (size_t) nodeCount * sizeof(BVH4Node), cudaMemcpyDeviceToDevice, st));
+	CUDA_TRY(ctx, ctx->dShadeTris.alloc(nTri * 6 * sizeof(float4)));
+	CUDA_TRY(ctx, ctx->dSortedOf.alloc(nTri * sizeof(uint32_t)));
+	k_shade_tris<<<blocksFor(nTri, 256), 256, 0, st>>>(dOrder.as<uint32_t>(), ctx->dTriIdx.as<uint4>(), ctx->dPositions.as<float4>(),
+		ctx->dNormals.as<float4>(), ctx->dShapes.as<ShapeInfo>(), (uint32_t) nTri, ctx->dShadeTris.as<float4>(), ctx->dSortedOf.as<uint32_t>());
 	k_reorder<<<blocksFor(nTri, 256), 256, 0, st>>>(dOrder.as<uint32_t>(), ctx->dTriAccelOrig.as<TriAccelRec>(), (uint32_t) nTri, ctx->dTriAccel.as<TriAccelRec>());
 	CUDA_TRY(ctx, cudaGetLastError());
 	CUDA_TRY(ctx, cudaEventRecord(e1, st));
@@ -859,6 +883,8 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	sc.normals = ctx->dNormals.as<float4>();
 	sc.texcoords = ctx->dTexcoords.as<float2>();
 	sc.tangents = ctx->dTangents.as<float4>();
+	sc.shadeTris = ctx->dShadeTris.as<float4>();
+	sc.sortedOf = ctx->dSortedOf.as<uint32_t>();
 	sc.textures = ctx->dTextures.as<TextureDev>();
 	sc.shapes = ctx->dShapes.as<ShapeInfo>();
 	sc.materials = ctx->dMaterials.as<MaterialDev>();

@@ -55,7 +55,7 @@ struct mtsgpu_ctx {
 	bool built = false;
 	DeviceScene scene;
 	DevBuf dTriAccel, dTriAccelOrig, dNodes, dTriIdx, dPositions, dNormals, dShapes, dMaterials, dEmitters,
-	       dLumCdf, dAreaCdf, dTexcoords, dTextures, dTangents;
+	       dLumCdf, dAreaCdf, dTexcoords, dTextures, dTangents, dShadeTris, dSortedOf;
 	mtsgpu_accel_info accel = {};
 
 	// trace staging + counters

@@ -264,8 +264,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		Isect its;
 		bool alive = valid;
 		if (valid) {
-			const float4 q2 = __ldg(sc.triAccel + (size_t) h.w * 3 + 2);
-			fillIntersection(sc, __float_as_uint(q2.z), __float_as_uint(q2.w), __uint_as_float(h.y), __uint_as_float(h.z), rayD, its);
+			fillIntersectionSorted(sc, h.w, __uint_as_float(h.y), __uint_as_float(h.z), rayD, its);
 		}
 
 		if (MODE == 2) {

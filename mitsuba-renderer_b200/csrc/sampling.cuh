@@ -193,11 +193,17 @@ struct Isect {
 	int materialId, emitterId;
 };
 
-__device__ inline void fillIntersection(const DeviceScene &sc, uint32_t shape, uint32_t prim, float u, float v,
-		V3 rayD, Isect &its) {
+// `tri` is the sorted triangle index the traversal reports. The hit's vertices and normals sit in one 96-byte record
+// (three full sectors, one dependent load after the hit) instead of behind the chain TriAccel -> ShapeInfo -> index
+// triple -> six half-used vertex sectors; ncu on C4 had k_shade waiting on exactly that chain (long-scoreboard
+// stalls 6.9 per issue, 742 B of DRAM traffic per hit).
+__device__ inline void fillIntersectionSorted(const DeviceScene &sc, uint32_t tri, float u, float v, V3 rayD, Isect &its) {
+	const float4 *rec = sc.shadeTris + (size_t) tri * 6;
+	const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2), r3 = __ldg(rec + 3), r4 = __ldg(rec + 4), r5 = __ldg(rec + 5);
+	const uint32_t shape = __float_as_uint(r0.w);
 	const ShapeInfo si = sc.shapes[shape];
-	const uint4 idx = __ldg(sc.triIdx + si.triOffset + prim);
-	const V3 p0 = v3(__ldg(sc.positions + idx.x)), p1 = v3(__ldg(sc.positions + idx.y)), p2 = v3(__ldg(sc.positions + idx.z));
+	const uint4 idx = make_uint4(__float_as_uint(r2.w), __float_as_uint(r3.w), __float_as_uint(r4.w), shape);
+	const V3 p0 = v3(r0), p1 = v3(r1), p2 = v3(r2);
 	const float bx = 1 - u - v, by = u, bz = v;
 	its.p = p0 * bx + p1 * by + p2 * bz;      // barycentric position, NOT o + t*d
 	V3 fn = cross(p1 - p0, p2 - p0);
@@ -205,7 +211,7 @@ __device__ inline void fillIntersection(const DeviceScene &sc, uint32_t shape, u
 	if (!isZero(fn)) fn = fn * (1.0f / len);
 	its.geoN = fn;
 	if (si.hasNormals) {
-		const V3 n0 = v3(__ldg(sc.normals + idx.x)), n1 = v3(__ldg(sc.normals + idx.y)), n2 = v3(__ldg(sc.normals + idx.z));
+		const V3 n0 = v3(r3), n1 = v3(r4), n2 = v3(r5);
 		its.shN = normalize(n0 * bx + n1 * by + n2 * bz);
 	} else {
 		its.shN = fn;
@@ -229,6 +235,12 @@ __device__ inline void fillIntersection(const DeviceScene &sc, uint32_t shape, u
 	if (!tangentFrame) its.sh = makeFrame(its.shN);
 	its.wi = toLocal(its.sh, -rayD);
 	its.shape = shape; its.materialId = si.materialId; its.emitterId = si.emitterId;
+}
+
+// Same, addressed as the C ABI reports hits: (shape, primitive index within the shape)
+__device__ inline void fillIntersection(const DeviceScene &sc, uint32_t shape, uint32_t prim, float u, float v,
+		V3 rayD, Isect &its) {
+	fillIntersectionSorted(sc, __ldg(sc.sortedOf + sc.shapes[shape].triOffset + prim), u, v, rayD, its);
 }
 
 // ---- textures: Texture2D::getValue (texture.cpp:73-82) + Checkerboard::getValue (checkerboard.cpp:47-55) ----------

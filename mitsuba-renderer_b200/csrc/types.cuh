@@ -70,6 +70,9 @@ struct DeviceScene {
 	const uint4 *triIdx;        // kd primitive order: {v0, v1, v2 (global vertex ids), shape}
 	const float4 *positions;    // global vertex arrays, xyz + pad
 	const float4 *normals;
+	const float4 *shadeTris;    // per sorted triangle, 6 x float4 (96 B = three 32-byte sectors): {p0, shape} {p1, prim}
+	                            // {p2, v0} {n0, v1} {n1, v2} {n2, -}: everything fillIntersection needs behind ONE index
+	const uint32_t *sortedOf;   // kd primitive order (ShapeInfo::triOffset + prim) -> sorted triangle index
 	const float4 *tangents;     // global vertex array of dpdu; only read for shapes with hasTangents
 	const float2 *texcoords;    // global vertex array; only read for shapes with hasTexcoords
 	const TextureDev *textures;
