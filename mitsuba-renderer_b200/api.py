@@ -31,7 +31,7 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_film_develop_device", "mtsgpu_film_save", "mtsgpu_write_exr", "mtsgpu_write_mfilm", "mtsgpu_sampler_values",
     "mtsgpu_upload_textures", "mtsgpu_intersect_uv",
 ]
-SAMPLER_INDEPENDENT, SAMPLER_LD, SAMPLER_STRATIFIED = 0, 1, 2
+SAMPLER_INDEPENDENT, SAMPLER_LD, SAMPLER_STRATIFIED, SAMPLER_HALTON = 0, 1, 2, 3
 FILM_EXR, FILM_M = 0, 1
 STATIC_SCRATCH_BYTES = 4 << 20
 

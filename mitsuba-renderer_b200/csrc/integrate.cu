@@ -34,6 +34,8 @@
 #define PF_PREV_DELTA   0x00020000u   // previous BSDF sample was a delta lobe
 #define PF_PREV_TRANS   0x00040000u   // previous BSDF sample was transmission
 #define PF_PENDING      0x00080000u   // a BSDF-sampled ray is in flight (steps 7-8 of the loop are outstanding)
+#define PF_RR_SHIFT     20            // bits 20-27: roulette values drawn so far (the halton sampler's value counter needs it)
+#define PF_RR_MASK      0x0FF00000u
 
 struct WfArrays {
 	float4 *thr;        // per slot: throughput.rgb, previous bsdfPdf
@@ -260,6 +262,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		int px, py; uint32_t sample;
 		slotToPixel(b, film, slot, px, py, sample);
 		Sampler smp; smp.init((uint32_t) ((py + film.cropY) * film.width + px + film.cropX), sample, b.seed, b.sampler);
+		smp.rouletteDraws = (flags & PF_RR_MASK) >> PF_RR_SHIFT;
 
 		Isect its;
 		bool alive = valid;
@@ -305,7 +308,10 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 					bool survive = true;
 					if ((int) depth >= ig.rrDepth && !(flags & PF_PREV_TRANS)) {
 						const float approxAlbedo = fminf(0.9f, maxc(bsdfVal));
-						if (smp.get1D(DIM_BOUNCE(depth - 1, 2), depth - (uint32_t) ig.rrDepth) > approxAlbedo) survive = false;
+						const float rr = smp.get1D(DIM_BOUNCE(depth - 1, 2), depth - (uint32_t) ig.rrDepth);
+						smp.rouletteDraws = min(smp.rouletteDraws + 1u, 255u);
+						flags = (flags & ~PF_RR_MASK) | (smp.rouletteDraws << PF_RR_SHIFT);
+						if (rr > approxAlbedo) survive = false;
 						else thr = thr * (1.0f / approxAlbedo);
 					}
 					if (survive) { thr = thr * bsdfVal; depth++; }
@@ -517,7 +523,9 @@ static int uploadFilter(mtsgpu_ctx *ctx, DevBuf &dTable) {
 }
 
 static int makeSamplerConfig(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, SamplerConfig &cfg) {
-	REQUIRE(ctx, P->samplerType <= MTSGPU_SAMPLER_STRATIFIED, MTSGPU_ERR_UNSUPPORTED, "render: unknown sampler type %u", P->samplerType);
+	REQUIRE(ctx, P->samplerType <= MTSGPU_SAMPLER_HALTON, MTSGPU_ERR_UNSUPPORTED, "render: unknown sampler type %u", P->samplerType);
+	if (P->samplerType == MTSGPU_SAMPLER_HALTON && P->mode == MTSGPU_MODE_DIRECT)      // halton.cpp:99-105
+		REQUIRE(ctx, P->luminaireSamples == 1 && P->bsdfSamples == 1, MTSGPU_ERR_UNSUPPORTED, "request2DArray() is not supported by QMC samplers!");
 	cfg.type = P->samplerType; cfg.depth = P->samplerDepth; cfg.log2Count = 0; cfg.resolution = 1;
 	cfg.lensDraw = (ctx->haveCamera && ctx->camera.apertureRadius > 0.0f) ? 1u : 0u;
 	if (cfg.type == MTSGPU_SAMPLER_LD) {

@@ -63,14 +63,41 @@ __host__ __device__ inline uint32_t ldPermute(uint32_t i, uint32_t bits, uint32_
 
 #define DIM_LENS_ 0u
 #define DIM_PIXEL_ 2u
+// Halton (src/samplers/halton.cpp:68-84): the d-th value drawn for pixel sample i is radicalInverse(d-th prime, i)
+__device__ __constant__ int c_primes[128] = {
+	2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31, 37, 41, 43, 47, 53, 59, 61, 67, 71, 73, 79, 83, 89, 97, 101, 103, 107, 109, 113, 127, 131,
+	137, 139, 149, 151, 157, 163, 167, 173, 179, 181, 191, 193, 197, 199, 211, 223, 227, 229, 233, 239, 241, 251, 257, 263, 269, 271,
+	277, 281, 283, 293, 307, 311, 313, 317, 331, 337, 347, 349, 353, 359, 367, 373, 379, 383, 389, 397, 401, 409, 419, 421, 431, 433,
+	439, 443, 449, 457, 461, 463, 467, 479, 487, 491, 499, 503, 509, 521, 523, 541, 547, 557, 563, 569, 571, 577, 587, 593, 599, 601,
+	607, 613, 617, 619, 631, 641, 643, 647, 653, 659, 661, 673, 677, 683, 691, 701, 709, 719 };
+__device__ inline float radicalInverse(int b, uint32_t i) {                 // src/libcore/util.cpp:740-750
+	const float invB = (float) 1 / (float) b;
+	float x = 0.0f, f = invB;
+	while (i) {
+		x = __fadd_rn(x, __fmul_rn(f, (float) (i % b)));
+		i /= b;
+		f = __fmul_rn(f, invB);
+	}
+	return x;
+}
+
 struct Sampler {
 	uint64_t key, pixelKey;
 	uint32_t sample;
+	uint32_t rouletteDraws;   // halton: 1D values this path has consumed so far (they shift every later value's prime)
 	SamplerConfig cfg;
 	__host__ __device__ void init(uint32_t pixel, uint32_t sampleIndex, uint32_t seed, SamplerConfig config) {
 		key = splitmix64((((uint64_t) pixel << 32) | sampleIndex) + 0x9E3779B97F4A7C15ull * (uint64_t) (seed + 1));
 		pixelKey = splitmix64((((uint64_t) pixel << 32) | 0xFFFFFFFFu) + 0xD1B54A32D192ED03ull * (uint64_t) (seed + 1));
-		sample = sampleIndex; cfg = config;
+		sample = sampleIndex; cfg = config; rouletteDraws = 0;
+	}
+	// halton: index of the first of the values a dimension consumes (renderBlock draws lens and pixel, then every
+	// bounce draws luminaire 2D, BSDF 2D and — from rrDepth on, unless the bounce was a transmission — roulette 1D)
+	__device__ uint32_t haltonValue(uint32_t dim) const {
+		if (dim == DIM_LENS_) return 0;
+		if (dim == DIM_PIXEL_) return 2 * cfg.lensDraw;
+		const uint32_t b = (dim - 3u) / 3u, k = (dim - 3u) % 3u;
+		return 2 * cfg.lensDraw + 2 + 4 * b + rouletteDraws + 2 * k;
 	}
 	// which next2D() / next1D() call of the pixel sample a dimension is (renderBlock, then Li)
 	__host__ __device__ uint32_t draw2D(uint32_t dim) const {
@@ -84,6 +111,16 @@ struct Sampler {
 		x = uintToUnitFloat((uint32_t) z);
 		y = uintToUnitFloat((uint32_t) (z >> 32));
 		if (cfg.type == MTSGPU_SAMPLER_INDEPENDENT) return;
+#ifdef __CUDA_ARCH__
+		if (cfg.type == MTSGPU_SAMPLER_HALTON) {
+			// next2D() is `Point2(nextValue(), nextValue())` (halton.cpp:80-84): the order of the two calls is the
+			// compiler's choice, and GCC (the reference's Linux build, and the oracle's) evaluates arguments right
+			// to left — y takes the first value, x the second
+			const uint32_t v = min(haltonValue(dim), 126u);
+			y = radicalInverse(c_primes[v], sample); x = radicalInverse(c_primes[v + 1], sample);
+			return;
+		}
+#endif
 		const uint32_t draw = draw2D(dim);
 		if (draw >= cfg.depth) return;
 		if (cfg.type == MTSGPU_SAMPLER_LD) { ld2D(draw, sample, x, y); return; }
@@ -109,6 +146,10 @@ struct Sampler {
 	}
 	// 1D draws: only the roulette decision uses them; draw number = how far past rrDepth the path is
 	__host__ __device__ float get1D(uint32_t dim, uint32_t draw1D = 0xFFFFFFFFu) const {
+#ifdef __CUDA_ARCH__
+		if (cfg.type == MTSGPU_SAMPLER_HALTON)
+			return radicalInverse(c_primes[min(haltonValue(dim), 127u)], sample);
+#endif
 		if (cfg.type == MTSGPU_SAMPLER_STRATIFIED && draw1D < cfg.depth) {         // stratified.cpp:157-161
 			const uint64_t z = splitmix64(key + 0x9E3779B97F4A7C15ull * (uint64_t) (dim + 1));
 			const uint32_t k = stratum(pixelKey + 0xA0761D6478BD642Full * (uint64_t) (2 * draw1D + 2));

@@ -444,8 +444,10 @@ private:
 				/* both classes write Sampler::serialize, then m_depth (ldsampler.cpp:76-80, stratified.cpp:84-90) */
 				P.samplerType = samplerClass == "StratifiedSampler" ? MTSGPU_SAMPLER_STRATIFIED : MTSGPU_SAMPLER_LD;
 				P.samplerDepth = (uint32_t) ms->readInt();
+			} else if (samplerClass == "HaltonSequence") {
+				P.samplerType = MTSGPU_SAMPLER_HALTON;
 			} else if (samplerClass != "IndependentSampler") {
-				Log(EError, "gpupath: sampler class \"%s\" is outside the supported hot path (independent, ldsampler, stratified)", samplerClass.c_str());
+				Log(EError, "gpupath: sampler class \"%s\" is outside the supported hot path (independent, ldsampler, stratified, halton)", samplerClass.c_str());
 			}
 		}
 		const size_t nPix = (size_t) csize.x * csize.y;

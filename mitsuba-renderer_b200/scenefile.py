@@ -275,7 +275,7 @@ class SceneDesc:
     strict_normals: bool = False
     luminaire_samples: int = 1
     bsdf_samples: int = 1
-    sampler_type: int = 0            # 0 independent, 1 ldsampler, 2 stratified (src/samplers/*.cpp)
+    sampler_type: int = 0            # 0 independent, 1 ldsampler, 2 stratified, 3 halton (src/samplers/*.cpp)
     sampler_depth: int = 3           # ldsampler `depth`
     materials: List[Material] = field(default_factory=list)
     emitters: List[Emitter] = field(default_factory=list)

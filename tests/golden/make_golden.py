@@ -63,6 +63,9 @@ def main():
     tsess = oracle_util.Session(ts)
     thits, tfull, _ = tsess.trace(rays, "closest_full")       # `wi` in the tangent frames of the anisotropic Ward meshes
     save("uv_textured", rays_digest=gc.digest(rays), out=tsess.uv(rays), hits=thits.view(np.uint8), full=tfull)
+    # ---- deterministic render: halton sampler (the same sample values on every pixel, no random state) ----------------------
+    hs = gc.scene_halton()
+    save("render_halton", film=oracle_util.Session(hs).render()[0])
     # ---- TriAccel records + enlarged scene box --------------------------------------------------------
     rec, box, _ = oracle_util.Session(gc.scene_materials()).triaccel()
     save("triaccel_materials", records=rec.view(np.uint8), box=box)

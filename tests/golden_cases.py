@@ -17,6 +17,13 @@ def scene_textured():
     return scenes.textured_test_scene(32, 32, 1)
 
 
+def scene_halton():
+    s = scenes.textured_test_scene(48, 48, 16, scenefile.MODE_PATH, max_depth=7)
+    s.rr_depth = 3
+    s.sampler_type = 3          # halton
+    return s
+
+
 def scene_grid():
     return scenes.microbench_scene(cells=64, pad_cells=9)
 

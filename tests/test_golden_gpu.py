@@ -66,6 +66,20 @@ def test_texture_coordinates_and_textured_reflectance_match_golden(gpu_ctx_facto
     assert len(np.unique(ref[textured, 2:5].round(4), axis=0)) >= 4        # both colours of several textures were hit
 
 
+def test_deterministic_halton_render_matches_golden_film(gpu_ctx_factory):
+    """Whole-integrator parity without statistics: with the halton sampler (halton.cpp:68-84) both sides trace the same
+    paths in every pixel; the golden film is the reference's `path` integrator on the textured all-BSDF scene."""
+    scene = gc.scene_halton()
+    ref = gold("render_halton")["film"]
+    gpu, _ = gpu_ctx_factory(scene).render(Context.params_from_scene(scene, seed=0))
+    assert np.array_equal(gpu[..., 3:], ref[..., 3:])                  # alpha and weight accumulators: identical
+    w = np.maximum(ref[..., 4:5], 1e-20)
+    c, g = ref[..., :3] / w, gpu[..., :3] / w
+    err = np.abs(g - c).max(axis=-1) / (np.abs(c).max(axis=-1) + 1e-3)
+    assert (err < 2e-3).mean() > 0.995 and np.median(err) < 2e-6, ((err < 2e-3).mean(), np.median(err))
+    assert abs(g.mean() - c.mean()) < 5e-4 * c.mean()
+
+
 def test_triaccel_matches_golden(gpu_ctx_factory):
     g = gold("triaccel_materials")
     ref = g["records"].view(api.TRIACCEL_DTYPE)

