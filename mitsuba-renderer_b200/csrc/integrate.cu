@@ -336,6 +336,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 				if (its.emitterId >= 0 && (flags & PF_EMITTED) && (MODE == 0 || round == 0))
 					Li = Li + (MODE == 0 ? thr : v3(1, 1, 1)) * emitterLe(sc, its.emitterId, its.geoN, -rayD);
 				if (MODE == 0 && ig.maxDepth > 0 && (int) depth >= ig.maxDepth) alive = false;
+				if (MODE == 0 && depth >= PF_DEPTH_MASK - 1u) alive = false;      // safety net: the depth field is 16 bits wide
 			}
 			if (alive && MODE == 0 && ig.strictNormals) {
 				const float wiDotGeoN = -dot(its.geoN, rayD);

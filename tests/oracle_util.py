@@ -20,7 +20,7 @@ def available(variant="parity"):
     return os.path.exists(binary(variant))
 
 
-def _run(args, variant="parity", timeout=3600, env=None):
+def _run(args, variant="parity", timeout=900, env=None):
     e = dict(os.environ)
     if env:
         e.update(env)
