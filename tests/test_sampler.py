@@ -170,7 +170,11 @@ def _halton_variants():
         s.mode, s.max_depth, s.rr_depth, s.strict_normals = scenefile.MODE_PATH, 5, 2, True
         return s
 
-    return [("thin lens + gaussian + crop", thin_lens), ("strict normals on smooth terrain", strict_grid)]
+    def c3_geometry():
+        s = scenes.direct_scene(width=96, height=54, spp=16)   # BASELINE config C3's 1M-triangle scene and integrator, small film
+        return s
+    return [("thin lens + gaussian + crop", thin_lens), ("strict normals on smooth terrain", strict_grid),
+            ("C3 scene (1M triangles), direct", c3_geometry)]
 
 
 @pytest.mark.parametrize("name,make", _halton_variants())
