@@ -13,6 +13,7 @@ oracle/harness/scene_io.h, so that the compiled reference renders exactly the sa
 """
 from __future__ import annotations
 
+import math
 import struct
 from dataclasses import dataclass, field
 from typing import List, Optional
@@ -305,30 +306,44 @@ def look_at(origin, target, up):
     return m
 
 
+def matmul4_f32(a, b):
+    """4x4 product as Matrix::operator* computes it (core/matrix.h:665-679): fp32, `sum = 0; sum += a[i][k] * b[k][j]`
+    for k = 0..3, one rounding per operation."""
+    f32 = np.float32
+    a, b = np.asarray(a, f32), np.asarray(b, f32)
+    out = np.zeros((4, 4), f32)
+    for k in range(4):
+        out = (out + (a[:, k:k + 1] * b[k:k + 1, :]).astype(f32)).astype(f32)
+    return out
+
+
 def raster_to_camera(scene: SceneDesc) -> np.ndarray:
-    """m_rasterToCamera of PerspectiveCameraImpl::configure (src/cameras/perspective.cpp:43-71):
-    inverse(perspective(fov, near, far)) * inverse(screenToRaster), computed in float64 and
-    rounded to fp32 (the reference inverts in fp32; agreement is ~1 ulp, tested at 1e-5)."""
-    w, h = float(scene.width), float(scene.height)
-    aspect = np.float32(w) / np.float32(h)
-    aspect = float(aspect)
+    """m_rasterToCamera of PerspectiveCameraImpl::configure (src/cameras/perspective.cpp:43-71) restated in fp32:
+    cameraToScreen.inverse() * screenToRaster.inverse(), where a Transform product keeps the product of the inverses
+    in the opposite order (transform.cpp:28-31), scale / translate carry analytic inverses (transform.cpp:33-63) and
+    perspective()'s matrix is inverted numerically by Transform(Matrix4x4) (transform.h:45-49, matrix.inl:140-195)."""
+    f32 = np.float32
+    w, h = f32(scene.width), f32(scene.height)
+    aspect = f32(w / h)                                   # ProjectiveCamera::configure, camera.cpp:142
 
-    def scale(x, y, z):
-        return np.diag([x, y, z, 1.0])
+    def scale_inv(x, y, z):
+        return np.diag([f32(f32(1.0) / f32(x)), f32(f32(1.0) / f32(y)), f32(f32(1.0) / f32(z)), f32(1)]).astype(f32)
 
-    def translate(x, y, z):
-        m = np.eye(4); m[:3, 3] = [x, y, z]; return m
+    def translate_inv(x, y, z):
+        m = np.eye(4, dtype=f32); m[:3, 3] = [-f32(x), -f32(y), -f32(z)]; return m
 
     if (aspect >= 1.0) ^ (not scene.map_smaller_side):
-        s2r = scale(w, h, 1.0) @ scale(1.0 / (2.0 * aspect), -0.5, 1.0) @ translate(aspect, -1.0, 0.0)
+        s1, s2, t = (w, h, f32(1)), (f32(f32(1) / f32(f32(2) * aspect)), f32(-0.5), f32(1)), (aspect, f32(-1), f32(0))
     else:
-        s2r = scale(w, h, 1.0) @ scale(0.5, -0.5 * aspect, 1.0) @ translate(1.0, -1.0 / aspect, 0.0)
-    near, far = float(np.float32(scene.near_clip)), float(np.float32(scene.far_clip))
-    recip = 1.0 / (far - near)
-    persp = np.array([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, far * recip, -near * far * recip], [0, 0, 1, 0]], np.float64)
-    cot = 1.0 / np.tan(np.deg2rad(float(np.float32(scene.fov)) / 2.0))
-    c2s = scale(cot, cot, 1.0) @ persp
-    return (np.linalg.inv(c2s) @ np.linalg.inv(s2r)).astype(np.float32)
+        s1, s2, t = (w, h, f32(1)), (f32(0.5), f32(f32(-0.5) * aspect), f32(1)), (f32(1), f32(-f32(f32(1) / aspect)), f32(0))
+    s2r_inv = matmul4_f32(translate_inv(*t), matmul4_f32(scale_inv(*s2), scale_inv(*s1)))
+    near, far = f32(scene.near_clip), f32(scene.far_clip)
+    recip = f32(f32(1.0) / f32(far - near))               # Transform::perspective, transform.cpp:100-124
+    trafo = np.array([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, f32(far * recip), f32(f32(f32(-near) * far) * recip)], [0, 0, 1, 0]], f32)
+    half = f32(f32(f32(scene.fov) / f32(2.0)) * f32(f32(np.pi) / f32(180.0)))     # degToRad (core/util.h:302)
+    cot = f32(f32(1.0) / f32(math.tan(float(half))))     # tanf: correctly rounded in glibc, as is double tan rounded once
+    c2s_inv = matmul4_f32(invert4_f32(trafo), scale_inv(cot, cot, f32(1)))
+    return matmul4_f32(c2s_inv, s2r_inv)
 
 
 def write_scene(path: str, scene: SceneDesc) -> None:

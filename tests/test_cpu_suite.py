@@ -109,7 +109,7 @@ def test_filter_tables_match_reference_tabulation():
 
 
 def test_raster_to_camera_reproduces_reference_rays():
-    """raster_to_camera (Python, float64 -> fp32) + look_at against PerspectiveCameraImpl::generateRay output."""
+    """raster_to_camera (the reference's fp32 transform chain restated) + look_at against PerspectiveCameraImpl::generateRay output."""
     s = gc.camera_scene(0.0)
     q = gc.camera_samples(s, 4000)
     g = gold("camera_pinhole")

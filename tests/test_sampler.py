@@ -136,7 +136,8 @@ def test_halton_render_matches_reference_pixel_by_pixel(oracle, gpu_ctx_factory,
     """The halton sampler is deterministic (halton.cpp:68-84: value d of sample i is radicalInverse(prime d, i), the
     same for every pixel), so here the whole integrator can be compared with the reference without statistics: every
     pixel traces the same paths on both sides. A path whose direction differs in the last bit can still land on the
-    other side of an edge, so a small share of pixels may differ; the rest must agree to fp32 accuracy."""
+    other side of an edge, so a small share of pixels may differ; the rest must agree to fp32 accuracy. (With the camera
+    transform restated in fp32 the camera rays are bit-identical, and so, it turns out, is nearly everything after.)"""
     scene = make(64, 64, 16, mode, max_depth=7)         # all BSDFs + textures + anisotropy, or all luminaire types + background
     scene.rr_depth = 3                                  # roulette values shift the primes of everything after them
     scene.sampler_type = api.SAMPLER_HALTON
@@ -149,9 +150,9 @@ def test_halton_render_matches_reference_pixel_by_pixel(oracle, gpu_ctx_factory,
     close_px = err < 2e-3
     print(f"mode {mode}: pixels within 2e-3: {close_px.mean():.4f}, median rel err {np.median(err):.2e}, "
           f"mean image {c.mean():.6f} vs {g.mean():.6f}; {stats}")
-    assert close_px.mean() > 0.995                      # measured: 0.9998
-    assert np.median(err) < 2e-6                        # measured: 1.3e-7 (summation order inside a pixel)
-    assert abs(g.mean() - c.mean()) < 5e-4 * c.mean()
+    assert close_px.mean() > 0.999                      # measured: 1.0000
+    assert np.median(err) < 1e-6                        # measured: 0 (more than half of the pixels are bit-identical)
+    assert abs(g.mean() - c.mean()) < 1e-4 * c.mean()
     # another seed changes nothing: the sampler has no random state
     gpu2, _ = ctx.render(Context.params_from_scene(scene, seed=99))
     assert np.array_equal(gpu2, gpu)
@@ -202,10 +203,10 @@ def test_halton_render_on_the_c4_scene(oracle, gpu_ctx_factory):
     base = scenes.path_scene(width=96, height=54, spp=16)
     base.sampler_type = api.SAMPLER_HALTON
     ctx = gpu_ctx_factory(base)
-    # measured: maxDepth 2 -> 99.96 % of the pixels within 2e-3, 3 -> 97.4 %, 4 -> 93.7 %, 6 -> 85.9 %, 16 -> 82.2 %; the
-    # median difference stays below 3e-6 and the image means within 7e-4: every bounce off a sharp rough-metal lobe or
-    # through a 320-triangle glass ball amplifies a last-bit difference until the path lands on another triangle
-    for max_depth, share in ((2, 0.995), (16, 0.75)):
+    # measured: maxDepth 2 -> 100 % of the pixels within 2e-3, maxDepth 16 -> 99.98 %, median difference 0 in both.
+    # (Before rasterToCamera was restated in fp32 the camera rays differed in the last bit and only 82 % of the pixels
+    # survived 16 bounces off sharp rough-metal lobes and through 320-triangle glass balls.)
+    for max_depth, share in ((2, 0.999), (16, 0.995)):
         scene = _copy.copy(base); scene.max_depth = max_depth
         cpu = oracle.Session(scene).render()[0]
         gpu, stats = ctx.render(Context.params_from_scene(scene, seed=1))
@@ -213,4 +214,4 @@ def test_halton_render_on_the_c4_scene(oracle, gpu_ctx_factory):
         c, g = develop(cpu), develop(gpu)
         err = np.abs(g - c).max(axis=-1) / (np.abs(c).max(axis=-1) + 1e-3)
         print(f"C4 scene, maxDepth {max_depth}: within 2e-3: {(err < 2e-3).mean():.4f}, median {np.median(err):.2e}, means {c.mean():.6f} {g.mean():.6f}")
-        assert (err < 2e-3).mean() > share and np.median(err) < 1e-5 and abs(g.mean() - c.mean()) < 2e-3 * c.mean()
+        assert (err < 2e-3).mean() > share and np.median(err) < 1e-6 and abs(g.mean() - c.mean()) < 1e-4 * c.mean()
