@@ -59,3 +59,25 @@ def test_plugin_renders_through_mitsuba(oracle, mode, lights):
     rel = float(np.mean((g - c) ** 2 / (c ** 2 + 1e-4)))
     print(f"mode {mode}: relMSE gpu-plugin vs cpu at 256 spp = {rel:.5f}; {info}")
     assert rel < 0.2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("make", [scenes.textured_test_scene, scenes.lights_test_scene])
+def test_plugin_with_the_halton_sampler_reproduces_the_cpu_image(oracle, make):
+    """The deterministic case through the whole drop-in path: Mitsuba parses nothing differently, the plugin decodes
+    BSDFs, textures, luminaires, sampler and camera from the live objects (rasterToCamera rebuilt with the reference's
+    own Transform operations), renders on the GPU and hands the film back through ImageBlock / Film::putImageBlock —
+    and the result has to be the CPU `path` integrator's image, pixel by pixel."""
+    need_plugin()
+    s = make(64, 64, 16, scenefile.MODE_PATH, max_depth=7)
+    s.rr_depth = 3
+    s.sampler_type = 3          # halton
+    sess = oracle.Session(s)
+    gpu, info = sess.render(2, "gpupath", env={"MTS_PLUGIN_PATH": PLUGIN_DIR})
+    cpu, _ = sess.render()
+    assert info["integrator"] == "gpupath" and gpu[..., 4].sum() > 0
+    assert np.array_equal(gpu[..., 3:], cpu[..., 3:])
+    g, c = develop(gpu), develop(cpu)
+    err = np.abs(g - c).max(axis=-1) / (np.abs(c).max(axis=-1) + 1e-3)
+    print(f"plugin vs cpu: within 2e-3: {(err < 2e-3).mean():.4f}, median {np.median(err):.2e}, means {c.mean():.6f} {g.mean():.6f}")
+    assert (err < 2e-3).mean() > 0.999 and np.median(err) < 1e-6
