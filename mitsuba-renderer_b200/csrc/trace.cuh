@@ -75,6 +75,17 @@ struct HitOut { float t, u, v; uint32_t tri; };   // tri = index into the sorted
 
 #define SSTACK(i) sstack[(i) * TRACE_BLOCK + threadIdx.x]
 
+// The same slots through a 32-bit shared-window address computed once per thread: the generic-pointer form above makes
+// the compiler rebuild the window base (S2R SR_CgaCtaId + LEA) next to every predicated store of the push sequence.
+__device__ __forceinline__ void stackStore(uint32_t base, int i, uint2 e) {
+	asm volatile("st.shared.v2.u32 [%0], {%1, %2};" :: "r"(base + (uint32_t) i * (TRACE_BLOCK * 8u)), "r"(e.x), "r"(e.y));
+}
+__device__ __forceinline__ uint2 stackLoad(uint32_t base, int i) {
+	uint2 e;
+	asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(e.x), "=r"(e.y) : "r"(base + (uint32_t) i * (TRACE_BLOCK * 8u)));
+	return e;
+}
+
 __device__ __forceinline__ float safeRcp(float d) {
 	// finite stand-in for 1/0 so that the slab test never produces NaN; the boxes are padded,
 	// which makes the result conservative for axis-parallel rays
@@ -89,6 +100,7 @@ template <bool SHADOW, bool COUNT>
 __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, float mint, float maxt,
 		uint2 *sstack, HitOut &hit, uint32_t &nodeVisits, uint32_t &triTests) {
 	uint2 lstack[TRACE_LOCAL_STACK];
+	const uint32_t sbase = (uint32_t) __cvta_generic_to_shared(sstack) + threadIdx.x * 8u;
 	int sp = 0;
 	const float idx = safeRcp(r.dx), idy = safeRcp(r.dy), idz = safeRcp(r.dz);
 	const float oix = r.ox * idx, oiy = r.oy * idy, oiz = r.oz * idz;
@@ -122,16 +134,16 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 #undef CSWAP
 				const int h1 = tn[1] != INFINITY, h2 = tn[2] != INFINITY, h3 = tn[3] != INFINITY;
 				if (sp + 3 <= TRACE_SMEM_STACK) {       // common case: three predicated stores, no branches
-					if (h1) SSTACK(sp) = make_uint2(cw[1], __float_as_uint(tn[1]));
-					if (h2) SSTACK(sp + h1) = make_uint2(cw[2], __float_as_uint(tn[2]));
-					if (h3) SSTACK(sp + h1 + h2) = make_uint2(cw[3], __float_as_uint(tn[3]));
+					if (h1) stackStore(sbase, sp, make_uint2(cw[1], __float_as_uint(tn[1])));
+					if (h2) stackStore(sbase, sp + h1, make_uint2(cw[2], __float_as_uint(tn[2])));
+					if (h3) stackStore(sbase, sp + h1 + h2, make_uint2(cw[3], __float_as_uint(tn[3])));
 					sp += h1 + h2 + h3;
 				} else {
 #pragma unroll
 					for (int i = 1; i <= 3; ++i) {
 						if (tn[i] != INFINITY) {
 							const uint2 e = make_uint2(cw[i], __float_as_uint(tn[i]));
-							if (sp < TRACE_SMEM_STACK) SSTACK(sp) = e; else lstack[min(sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)] = e;
+							if (sp < TRACE_SMEM_STACK) stackStore(sbase, sp, e); else lstack[min(sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)] = e;
 							sp++;
 						}
 					}
@@ -159,7 +171,7 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 		while (true) {
 			if (sp == 0) return found;
 			--sp;
-			const uint2 e = (sp < TRACE_SMEM_STACK) ? SSTACK(sp) : lstack[min(sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)];
+			const uint2 e = (sp < TRACE_SMEM_STACK) ? stackLoad(sbase, sp) : lstack[min(sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)];
 			if (!SHADOW && __uint_as_float(e.y) > maxt) continue;
 			cur = e.x;
 			break;
@@ -207,13 +219,14 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 	const uint32_t ltMask = (1u << lane) - 1u;
 	uint32_t poolNext = 0, poolEnd = 0;            // warp-uniform
 	bool exhausted = false;                        // this lane drew an index >= n
+	const uint32_t sbase = (uint32_t) __cvta_generic_to_shared(sstack) + threadIdx.x * 8u;
 	LaneState s;
 	s.active = false; s.sp = 0; s.cur = BVH_EMPTY; s.leaf = BVH_EMPTY; s.found = false;
 
-#define STACK_PUSH(e) do { if (s.sp < TRACE_SMEM_STACK) SSTACK(s.sp) = (e); else lstack[min(s.sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)] = (e); s.sp++; } while (0)
+#define STACK_PUSH(e) do { if (s.sp < TRACE_SMEM_STACK) stackStore(sbase, s.sp, (e)); else lstack[min(s.sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)] = (e); s.sp++; } while (0)
 	// pop the next entry that can still matter; BVH_EMPTY when the stack is empty
 #define STACK_POP(dst) do { (dst) = BVH_EMPTY; while (s.sp > 0) { --s.sp; \
-		const uint2 e_ = (s.sp < TRACE_SMEM_STACK) ? SSTACK(s.sp) : lstack[min(s.sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)]; \
+		const uint2 e_ = (s.sp < TRACE_SMEM_STACK) ? stackLoad(sbase, s.sp) : lstack[min(s.sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)]; \
 		if (!SHADOW && __uint_as_float(e_.y) > s.maxt) continue; (dst) = e_.x; break; } } while (0)
 
 	while (true) {
@@ -295,9 +308,9 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 						// stores at computed slots, no branches
 						const int h1 = tn[1] != INFINITY, h2 = tn[2] != INFINITY, h3 = tn[3] != INFINITY;
 						if (s.sp + 3 <= TRACE_SMEM_STACK) {
-							if (h1) SSTACK(s.sp) = make_uint2(cw[1], __float_as_uint(tn[1]));
-							if (h2) SSTACK(s.sp + h1) = make_uint2(cw[2], __float_as_uint(tn[2]));
-							if (h3) SSTACK(s.sp + h1 + h2) = make_uint2(cw[3], __float_as_uint(tn[3]));
+							if (h1) stackStore(sbase, s.sp, make_uint2(cw[1], __float_as_uint(tn[1])));
+							if (h2) stackStore(sbase, s.sp + h1, make_uint2(cw[2], __float_as_uint(tn[2])));
+							if (h3) stackStore(sbase, s.sp + h1 + h2, make_uint2(cw[3], __float_as_uint(tn[3])));
 							s.sp += h1 + h2 + h3;
 						} else {
 #pragma unroll
