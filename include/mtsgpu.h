@@ -208,6 +208,13 @@ MTSGPU_API int mtsgpu_upload_mesh(mtsgpu_ctx *ctx, int shapeIndex,
 
 /* PerspectiveCameraImpl (src/cameras/perspective.cpp:43-112): m_rasterToCamera, m_cameraToWorld,
  * clip planes, thin-lens parameters, shutter. */
+/* Analytic sphere as shape `shapeIndex` (src/shapes/sphere.cpp:31-173): the fields Sphere::serialize writes
+ * (sphere.cpp:71-77) — objectToWorld with the scale removed and its inverse (row-major 4x4), radius, centre,
+ * `inverted`. It is one primitive of the acceleration structure; hits report prim = 0xFFFFFFFF (KNoTriangleFlag,
+ * include/mitsuba/render/triaccel.h:27) and u = v = 0. A sphere cannot carry an area luminaire yet (refused). */
+MTSGPU_API int mtsgpu_upload_sphere(mtsgpu_ctx *ctx, int shapeIndex, const float objectToWorld[16], const float worldToObject[16],
+                                    float radius, const float center[3], int inverted, int materialId, int emitterId);
+
 MTSGPU_API int mtsgpu_set_camera(mtsgpu_ctx *ctx, const float rasterToCamera[16], const float cameraToWorld[16],
 	float nearClip, float farClip, float apertureRadius, float focusDepth, float shutterOpen, float shutterOpenTime);
 

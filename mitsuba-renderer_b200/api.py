@@ -29,7 +29,7 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_film_splat_static", "mtsgpu_render_multi", "mtsgpu_serialized_count", "mtsgpu_serialized_load",
     "mtsgpu_serialized_free", "mtsgpu_serialized_save", "mtsgpu_upload_serialized", "mtsgpu_film_develop",
     "mtsgpu_film_develop_device", "mtsgpu_film_save", "mtsgpu_write_exr", "mtsgpu_write_mfilm", "mtsgpu_sampler_values",
-    "mtsgpu_upload_textures", "mtsgpu_intersect_uv",
+    "mtsgpu_upload_textures", "mtsgpu_intersect_uv", "mtsgpu_upload_sphere",
 ]
 SAMPLER_INDEPENDENT, SAMPLER_LD, SAMPLER_STRATIFIED, SAMPLER_HALTON = 0, 1, 2, 3
 FILM_EXR, FILM_M = 0, 1
@@ -107,6 +107,7 @@ def load_library(path: Optional[str] = None):
     lib.mtsgpu_upload_emitters.argtypes = [vp, C.POINTER(Emitter), C.c_int]
     lib.mtsgpu_upload_textures.argtypes = [vp, C.POINTER(Texture), C.c_int]
     lib.mtsgpu_intersect_uv.argtypes = [vp, vp, C.c_size_t, vp]
+    lib.mtsgpu_upload_sphere.argtypes = [vp, C.c_int, vp, vp, C.c_float, vp, C.c_int, C.c_int, C.c_int]
     lib.mtsgpu_upload_mesh.argtypes = [vp, C.c_int, vp, vp, vp, C.c_uint32, vp, C.c_uint32, C.c_int, C.c_int]
     lib.mtsgpu_set_camera.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float]
     lib.mtsgpu_set_film.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_float, C.c_float]
@@ -241,6 +242,14 @@ class Context:
             ems[i].p[:] = [float(v) for v in e.abi_params()]
         self._check(self.lib.mtsgpu_upload_emitters(self.h, ems, len(scene.emitters)))
         for i, s in enumerate(scene.shapes):
+            if s.sphere is not None:                # center + radius: objectToWorld = translate(center) (sphere.cpp:44-47)
+                center, radius, inverted = s.sphere
+                o2w = np.eye(4, dtype=np.float32); o2w[:3, 3] = center
+                w2o = np.eye(4, dtype=np.float32); w2o[:3, 3] = -np.asarray(center, np.float32)
+                c = np.asarray(center, np.float32)
+                self._check(self.lib.mtsgpu_upload_sphere(self.h, i, self._ptr(o2w), self._ptr(w2o), radius, self._ptr(c),
+                                                          int(inverted), s.material, s.emitter))
+                continue
             pos = np.ascontiguousarray(s.positions, np.float32)
             nrm = None if s.normals is None else np.ascontiguousarray(s.normals, np.float32)
             tri = np.ascontiguousarray(s.triangles, np.uint32)

@@ -130,6 +130,25 @@ int mtsgpu_upload_mesh(mtsgpu_ctx *ctx, int shapeIndex, const float *positions, 
 	return MTSGPU_OK;
 }
 
+int mtsgpu_upload_sphere(mtsgpu_ctx *ctx, int shapeIndex, const float objectToWorld[16], const float worldToObject[16],
+		float radius, const float center[3], int inverted, int materialId, int emitterId) {
+	ENTER(ctx);
+	REQUIRE(ctx, objectToWorld && worldToObject && center, MTSGPU_ERR_ARG, "upload_sphere: null argument");
+	REQUIRE(ctx, shapeIndex >= 0 && (size_t) shapeIndex <= ctx->meshes.size(), MTSGPU_ERR_ARG,
+		"upload_sphere: shapes must be uploaded in kd-tree order (got %d, expected <= %zu)", shapeIndex, ctx->meshes.size());
+	REQUIRE(ctx, emitterId < 0, MTSGPU_ERR_UNSUPPORTED, "upload_sphere: area luminaires on spheres are outside the supported hot path");
+	if ((size_t) shapeIndex < ctx->meshes.size()) ctx->meshes.resize(shapeIndex);
+	HostMesh m;
+	m.nVert = 1; m.nTri = 1; m.materialId = materialId; m.emitterId = -1; m.hasNormals = false;
+	m.pos.assign(center, center + 3);
+	m.tri = { 0u, SPHERE_MARK, SPHERE_MARK };
+	m.sphere = true; m.inverted = inverted != 0; m.radius = radius;
+	memcpy(m.o2w, objectToWorld, 64); memcpy(m.w2o, worldToObject, 64);
+	ctx->meshes.push_back(std::move(m));
+	ctx->built = false;
+	return MTSGPU_OK;
+}
+
 int mtsgpu_set_camera(mtsgpu_ctx *ctx, const float rasterToCamera[16], const float cameraToWorld[16], float nearClip, float farClip,
 		float apertureRadius, float focusDepth, float shutterOpen, float shutterOpenTime) {
 	ENTER(ctx);

@@ -70,17 +70,28 @@ __global__ void k_prepare_tris(const uint4 *triIdx, const float4 *pos, const Sha
 	float lo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, hi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
 	if (g < n) {
 		const uint4 t = triIdx[g];
-		const float4 A = pos[t.x], B = pos[t.y], C = pos[t.z];
-		TriAccelRec r;
-		triAccelLoad(A, B, C, r);
 		const ShapeInfo sh = shapes[t.w];
-		r.shapeIndex = t.w;
-		r.primIndex = g - sh.triOffset;
+		TriAccelRec r;
+		if (t.y == 0xFFFFFFFFu) {
+			// analytic sphere: centre in the vertex, radius in its w; box = centre -+ |radius| (Sphere::getAABB, sphere.cpp:80-86)
+			const float4 c = pos[t.x];
+			memset(&r, 0, sizeof(r));
+			r.k = 3u; r.n_u = c.x; r.n_v = c.y; r.n_d = c.z; r.a_u = c.w;
+			r.shapeIndex = t.w; r.primIndex = 0xFFFFFFFFu;           // KNoTriangleFlag (triaccel.h:27, skdtree.cpp:98)
+			const float ar = fabsf(c.w);
+			lo[0] = __fsub_rn(c.x, ar); lo[1] = __fsub_rn(c.y, ar); lo[2] = __fsub_rn(c.z, ar);
+			hi[0] = __fadd_rn(c.x, ar); hi[1] = __fadd_rn(c.y, ar); hi[2] = __fadd_rn(c.z, ar);
+		} else {
+			const float4 A = pos[t.x], B = pos[t.y], C = pos[t.z];
+			triAccelLoad(A, B, C, r);
+			r.shapeIndex = t.w;
+			r.primIndex = g - sh.triOffset;
+			lo[0] = fminf(A.x, fminf(B.x, C.x)); hi[0] = fmaxf(A.x, fmaxf(B.x, C.x));
+			lo[1] = fminf(A.y, fminf(B.y, C.y)); hi[1] = fmaxf(A.y, fmaxf(B.y, C.y));
+			lo[2] = fminf(A.z, fminf(B.z, C.z)); hi[2] = fmaxf(A.z, fmaxf(B.z, C.z));
+		}
 		if (sh.materialId < 0) r.k |= TRI_NONOCCLUDER;
 		accelOrig[g] = r;
-		lo[0] = fminf(A.x, fminf(B.x, C.x)); hi[0] = fmaxf(A.x, fmaxf(B.x, C.x));
-		lo[1] = fminf(A.y, fminf(B.y, C.y)); hi[1] = fmaxf(A.y, fmaxf(B.y, C.y));
-		lo[2] = fminf(A.z, fminf(B.z, C.z)); hi[2] = fmaxf(A.z, fmaxf(B.z, C.z));
 		triLo[g] = make_float4(lo[0], lo[1], lo[2], 0);
 		triHi[g] = make_float4(hi[0], hi[1], hi[2], 0);
 	}
@@ -342,16 +353,29 @@ __global__ void k_ploc_apply(const int *cluster, int m, const int *nn, const uns
 
 // Shading records (types.cuh: DeviceScene::shadeTris) in sorted triangle order + the inverse permutation
 __global__ void k_shade_tris(const uint32_t *order, const uint4 *triIdx, const float4 *positions, const float4 *normals,
-		const ShapeInfo *shapes, uint32_t n, float4 *out, uint32_t *sortedOf) {
+		const ShapeInfo *shapes, const float *sphereXf, uint32_t n, float4 *out, uint32_t *sortedOf) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n) return;
 	const uint32_t g = order[i];                       // kd primitive order (global triangle index)
 	sortedOf[g] = i;
 	const uint4 idx = triIdx[g];
+	float4 *o = out + (size_t) i * 6;
+	if (idx.y == 0xFFFFFFFFu) {
+		// sphere: {centre, shape} {radius, inverted, -, -} {worldToObject 3x3 rows | objectToWorld 3x3 rows in the .w and the
+		// last record}: filled from the side table below
+		const float4 c = positions[idx.x];
+		const float *xf = sphereXf + (size_t) shapes[idx.w].cdfOffset * 20;       // cdfOffset doubles as the sphere-table index
+		o[0] = make_float4(c.x, c.y, c.z, __uint_as_float(idx.w));
+		o[1] = make_float4(c.w, xf[18], xf[0], xf[1]);                            // radius, inverted, w2o[0][0..1]
+		o[2] = make_float4(xf[2], xf[3], xf[4], xf[5]);                           // w2o[0][2], w2o[1][0..2]
+		o[3] = make_float4(xf[6], xf[7], xf[8], xf[9]);                           // w2o[2][0..2], o2w[0][0]
+		o[4] = make_float4(xf[10], xf[11], xf[12], xf[13]);                       // o2w[0][1..2], o2w[1][0..1]
+		o[5] = make_float4(xf[14], xf[15], xf[16], xf[17]);                       // o2w[1][2], o2w[2][0..2]
+		return;
+	}
 	const uint32_t prim = g - shapes[idx.w].triOffset;
 	const float4 p0 = positions[idx.x], p1 = positions[idx.y], p2 = positions[idx.z];
 	const float4 n0 = normals[idx.x], n1 = normals[idx.y], n2 = normals[idx.z];
-	float4 *o = out + (size_t) i * 6;
 	o[0] = make_float4(p0.x, p0.y, p0.z, __uint_as_float(idx.w));
 	o[1] = make_float4(p1.x, p1.y, p1.z, __uint_as_float(prim));
 	o[2] = make_float4(p2.x, p2.y, p2.z, __uint_as_float(idx.x));
@@ -573,7 +597,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		if (m.materialId < 0 || m.materialId >= (int) ctx->materials.size()) continue;
 		const mtsgpu_material &mat = ctx->materials[m.materialId];
 		const bool anisotropic = (mat.type & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_WARD && mat.p[8] != mat.p[9];
-		if (!anisotropic) continue;
+		if (!anisotropic || m.sphere) continue;       // a sphere brings its own dpdu / dpdv (sphere.cpp:146-161)
 		REQUIRE(ctx, !m.uv.empty(), MTSGPU_ERR_ARG, "shape %zu: computeTangentSpace(): texture coordinates are required to generate "
 			"tangent vectors. If you want to render with an anisotropic material, please make sure that all associated shapes have "
 			"valid texture coordinates.", s);
@@ -586,6 +610,8 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	std::vector<float> areaCdfAll;
 	std::vector<int> emitterShape(ctx->emitters.size(), -1);
 	size_t tOff = 0, vOff = 0;
+	bool anySphere = false;
+	std::vector<float> sphereXf;      // per sphere: worldToObject 3x3, objectToWorld 3x3, inverted, pad
 	for (size_t s = 0; s < nShapes; ++s) {
 		const HostMesh &m = ctx->meshes[s];
 		ShapeInfo &si = shapes[s];
@@ -595,16 +621,24 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		si.nTri = m.nTri; si.nVert = m.nVert; si.hasNormals = m.hasNormals ? 1u : 0u;
 		si.hasTexcoords = m.uv.empty() ? 0u : 1u;
 		si.hasTangents = meshTangents[s].empty() ? 0u : 1u;
+		if (m.sphere) {
+			si.isSphere = 1u; anySphere = true;
+			si.cdfOffset = (uint32_t) (sphereXf.size() / 20);       // index into the sphere transform table
+			for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) sphereXf.push_back(m.w2o[4 * r + c]);
+			for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) sphereXf.push_back(m.o2w[4 * r + c]);
+			sphereXf.push_back(m.inverted ? 1.0f : 0.0f); sphereXf.push_back(0.0f);
+		}
 		for (uint32_t v = 0; v < (meshTangents[s].empty() ? 0u : m.nVert); ++v)
 			tangents[vOff + v] = make_float4(meshTangents[s][3*v], meshTangents[s][3*v+1], meshTangents[s][3*v+2], 0);
 		for (uint32_t v = 0; v < (m.uv.empty() ? 0u : m.nVert); ++v) uvs[vOff + v] = make_float2(m.uv[2*v], m.uv[2*v+1]);
 		REQUIRE(ctx, m.materialId < (int) ctx->materials.size(), MTSGPU_ERR_ARG, "shape %zu: material id %d out of range", s, m.materialId);
 		REQUIRE(ctx, m.emitterId < (int) ctx->emitters.size(), MTSGPU_ERR_ARG, "shape %zu: emitter id %d out of range", s, m.emitterId);
 		for (uint32_t v = 0; v < m.nVert; ++v) {
-			pos[vOff + v] = make_float4(m.pos[3*v], m.pos[3*v+1], m.pos[3*v+2], 0);
+			pos[vOff + v] = make_float4(m.pos[3*v], m.pos[3*v+1], m.pos[3*v+2], m.sphere ? m.radius : 0.0f);
 			nrm[vOff + v] = m.hasNormals ? make_float4(m.nrm[3*v], m.nrm[3*v+1], m.nrm[3*v+2], 0) : make_float4(0, 0, 0, 0);
 		}
 		for (uint32_t t = 0; t < m.nTri; ++t) {
+			if (m.sphere) { triIdx[tOff + t] = make_uint4((uint32_t) vOff, SPHERE_MARK, SPHERE_MARK, (uint32_t) s); continue; }
 			for (int c = 0; c < 3; ++c)
 				REQUIRE(ctx, m.tri[3*t+c] < m.nVert, MTSGPU_ERR_ARG, "shape %zu: triangle %u references vertex %u >= %u", s, t, m.tri[3*t+c], m.nVert);
 			triIdx[tOff + t] = make_uint4((uint32_t) vOff + m.tri[3*t], (uint32_t) vOff + m.tri[3*t+1], (uint32_t) vOff + m.tri[3*t+2], (uint32_t) s);
@@ -868,8 +902,13 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dNodes.p, dNodesTmp.p, (size_t) nodeCount * sizeof(BVH4Node), cudaMemcpyDeviceToDevice, st));
 	CUDA_TRY(ctx, ctx->dShadeTris.alloc(nTri * 6 * sizeof(float4)));
 	CUDA_TRY(ctx, ctx->dSortedOf.alloc(nTri * sizeof(uint32_t)));
+	DevBuf dSphereXf;
+	CUDA_TRY(ctx, dSphereXf.alloc(std::max<size_t>(sphereXf.size(), 1) * sizeof(float)));
+	if (!sphereXf.empty())
+		CUDA_TRY(ctx, cudaMemcpyAsync(dSphereXf.p, sphereXf.data(), sphereXf.size() * sizeof(float), cudaMemcpyHostToDevice, st));
 	k_shade_tris<<<blocksFor(nTri, 256), 256, 0, st>>>(dOrder.as<uint32_t>(), ctx->dTriIdx.as<uint4>(), ctx->dPositions.as<float4>(),
-		ctx->dNormals.as<float4>(), ctx->dShapes.as<ShapeInfo>(), (uint32_t) nTri, ctx->dShadeTris.as<float4>(), ctx->dSortedOf.as<uint32_t>());
+		ctx->dNormals.as<float4>(), ctx->dShapes.as<ShapeInfo>(), dSphereXf.as<float>(), (uint32_t) nTri, ctx->dShadeTris.as<float4>(),
+		ctx->dSortedOf.as<uint32_t>());
 	k_reorder<<<blocksFor(nTri, 256), 256, 0, st>>>(dOrder.as<uint32_t>(), ctx->dTriAccelOrig.as<TriAccelRec>(), (uint32_t) nTri, ctx->dTriAccel.as<TriAccelRec>());
 	CUDA_TRY(ctx, cudaGetLastError());
 	CUDA_TRY(ctx, cudaEventRecord(e1, st));
@@ -885,6 +924,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	sc.tangents = ctx->dTangents.as<float4>();
 	sc.shadeTris = ctx->dShadeTris.as<float4>();
 	sc.sortedOf = ctx->dSortedOf.as<uint32_t>();
+	sc.hasSpheres = anySphere ? 1u : 0u;
 	sc.textures = ctx->dTextures.as<TextureDev>();
 	sc.shapes = ctx->dShapes.as<ShapeInfo>();
 	sc.materials = ctx->dMaterials.as<MaterialDev>();

@@ -29,7 +29,10 @@ struct DevBuf {
 struct HostMesh {
 	uint32_t nVert, nTri; int materialId, emitterId; bool hasNormals;
 	std::vector<float> pos, nrm, uv; std::vector<uint32_t> tri;   // uv empty: no texture coordinates
+	// analytic sphere (mtsgpu_upload_sphere): one vertex (the centre) and one primitive {0, SPHERE_MARK, SPHERE_MARK}
+	bool sphere = false, inverted = false; float radius = 0, o2w[16] = {}, w2o[16] = {};
 };
+#define SPHERE_MARK 0xFFFFFFFFu
 
 struct mtsgpu_ctx {
 	int device = 0;

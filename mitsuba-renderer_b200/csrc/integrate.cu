@@ -132,6 +132,7 @@ k_generate(const CameraDev cam, const FilmDev film, const BatchDesc b, WfArrays 
 // C4 177.8 -> 167.1 ms), shadow queues — coherent rays towards a handful of emitters — do not on the
 // 10M-triangle scene (61.0 -> 71.3 ms), so shadow rays keep this kernel. MTSGPU_WF_PERSIST_{CLOSEST,SHADOW}
 // override the choice for experiments.
+template <bool SPH>
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_closest_wf(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint4 *__restrict__ hits) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
@@ -142,10 +143,11 @@ k_closest_wf(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, 
 	HitOut ho; ho.t = INFINITY; ho.u = ho.v = 0; ho.tri = 0xFFFFFFFFu;
 	float mint, maxt; uint32_t c0 = 0, c1 = 0;
 	if (clipToScene<false>(sc, r, mint, maxt))
-		traverse<false, false>(sc, r, mint, maxt, sstack, ho, c0, c1);
+		traverse<false, false, SPH>(sc, r, mint, maxt, sstack, ho, c0, c1);
 	hits[i] = make_uint4(__float_as_uint(ho.t), __float_as_uint(ho.u), __float_as_uint(ho.v), ho.tri);
 }
 
+template <bool SPH>
 __global__ void __launch_bounds__(TRACE_BLOCK)
 k_shadow_wf(const DeviceScene sc, const float4 *__restrict__ rays, const float4 *__restrict__ payload, uint32_t n, float4 *li) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
@@ -157,7 +159,7 @@ k_shadow_wf(const DeviceScene sc, const float4 *__restrict__ rays, const float4 
 	bool occluded = false;
 	if (clipToScene<true>(sc, r, mint, maxt)) {
 		HitOut ho;
-		occluded = traverse<true, false>(sc, r, mint, maxt, sstack, ho, c0, c1);
+		occluded = traverse<true, false, SPH>(sc, r, mint, maxt, sstack, ho, c0, c1);
 	}
 	if (!occluded) {
 		const float4 p = __ldg(payload + i);
@@ -188,19 +190,21 @@ struct WfShadowSink {
 		li[slot] = l;
 	}
 };
+template <bool SPH>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
 k_closest_wfp(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint4 *__restrict__ hits, uint32_t *rayCounter) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
 	uint32_t c0 = 0, c1 = 0;
 	WfHitSink sink = { hits };
-	tracePersistent<false, false>(sc, rays, n, rayCounter, sink, sstack, c0, c1, TRACE_REFETCH_BELOW);
+	tracePersistent<false, false, WfHitSink, SPH>(sc, rays, n, rayCounter, sink, sstack, c0, c1, TRACE_REFETCH_BELOW);
 }
+template <bool SPH>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
 k_shadow_wfp(const DeviceScene sc, const float4 *__restrict__ rays, const float4 *__restrict__ payload, uint32_t n, float4 *li, uint32_t *rayCounter) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
 	uint32_t c0 = 0, c1 = 0;
 	WfShadowSink sink = { payload, li };
-	tracePersistent<true, false>(sc, rays, n, rayCounter, sink, sstack, c0, c1, TRACE_REFETCH_BELOW);
+	tracePersistent<true, false, WfShadowSink, SPH>(sc, rays, n, rayCounter, sink, sstack, c0, c1, TRACE_REFETCH_BELOW);
 }
 
 __device__ __forceinline__ float miWeight(float pdfA, float pdfB) {     // path.cpp:218-222 (power heuristic)
@@ -267,7 +271,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		Isect its;
 		bool alive = valid;
 		if (valid) {
-			fillIntersectionSorted(sc, h.w, __uint_as_float(h.y), __uint_as_float(h.z), rayD, its);
+			fillIntersectionSorted(sc, h.w, __uint_as_float(h.y), __uint_as_float(h.z), rayO, rayD, __uint_as_float(h.x), its);
 		}
 
 		if (MODE == 2) {
@@ -488,18 +492,22 @@ inline unsigned blocksFor(size_t n, unsigned bs) { return (unsigned) ((n + bs - 
 static int launchClosestWf(mtsgpu_ctx *ctx, const float4 *rays, uint32_t n, uint4 *hits, bool persistent) {
 	if (persistent) {
 		uint32_t *rc = nullptr; int e = traceRayCounter(ctx, &rc); if (e) return e;
-		k_closest_wfp<<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, rc);
+		if (ctx->scene.hasSpheres) k_closest_wfp<true><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, rc);
+		else k_closest_wfp<false><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, rc);
 	} else {
-		k_closest_wf<<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits);
+		if (ctx->scene.hasSpheres) k_closest_wf<true><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits);
+		else k_closest_wf<false><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits);
 	}
 	return MTSGPU_OK;
 }
 static int launchShadowWf(mtsgpu_ctx *ctx, const float4 *rays, const float4 *payload, uint32_t n, float4 *li, bool persistent) {
 	if (persistent) {
 		uint32_t *rc = nullptr; int e = traceRayCounter(ctx, &rc); if (e) return e;
-		k_shadow_wfp<<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li, rc);
+		if (ctx->scene.hasSpheres) k_shadow_wfp<true><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li, rc);
+		else k_shadow_wfp<false><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li, rc);
 	} else {
-		k_shadow_wf<<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li);
+		if (ctx->scene.hasSpheres) k_shadow_wf<true><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li);
+		else k_shadow_wf<false><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li);
 	}
 	return MTSGPU_OK;
 }
@@ -790,7 +798,7 @@ __global__ void k_hook_uv(const DeviceScene sc, const float4 *rays, const mtsgpu
 	const mtsgpu_hit h = hits[i];
 	if (h.shape == 0xFFFFFFFFu) return;
 	Isect its;
-	fillIntersection(sc, h.shape, h.prim, h.u, h.v, v3(rays[2 * (size_t) i + 1]), its);
+	fillIntersection(sc, h.shape, h.prim, h.u, h.v, v3(rays[2 * (size_t) i]), v3(rays[2 * (size_t) i + 1]), h.t, its);
 	o[0] = its.uvx; o[1] = its.uvy;
 	if (its.materialId < 0) return;
 	MaterialDev m = sc.materials[its.materialId];
@@ -804,9 +812,9 @@ __global__ void k_hook_isect(const DeviceScene sc, const float4 *rays, const mts
 	float *o = out + (size_t) i * 12;
 	const mtsgpu_hit h = hits[i];
 	if (h.shape == 0xFFFFFFFFu) { for (int k = 0; k < 12; ++k) o[k] = 0; return; }
-	const float4 b = rays[2 * (size_t) i + 1];
+	const float4 a = rays[2 * (size_t) i], b = rays[2 * (size_t) i + 1];
 	Isect its;
-	fillIntersection(sc, h.shape, h.prim, h.u, h.v, v3(b), its);
+	fillIntersection(sc, h.shape, h.prim, h.u, h.v, v3(a), v3(b), h.t, its);
 	o[0] = its.p.x; o[1] = its.p.y; o[2] = its.p.z; o[3] = its.geoN.x; o[4] = its.geoN.y; o[5] = its.geoN.z;
 	o[6] = its.shN.x; o[7] = its.shN.y; o[8] = its.shN.z; o[9] = its.wi.x; o[10] = its.wi.y; o[11] = its.wi.z;
 }

@@ -238,11 +238,46 @@ struct Isect {
 // (three full sectors, one dependent load after the hit) instead of behind the chain TriAccel -> ShapeInfo -> index
 // triple -> six half-used vertex sectors; ncu on C4 had k_shade waiting on exactly that chain (long-scoreboard
 // stalls 6.9 per issue, 742 B of DRAM traffic per hit).
-__device__ inline void fillIntersectionSorted(const DeviceScene &sc, uint32_t tri, float u, float v, V3 rayD, Isect &its) {
+// Sphere::fillIntersectionRecord (src/shapes/sphere.cpp:133-173) from the sphere's shading record
+__device__ inline void fillSphereIntersection(const DeviceScene &sc, const float4 &r0, const float4 &r1, const float4 &r2,
+		const float4 &r3, const float4 &r4, const float4 &r5, V3 rayO, V3 rayD, float t, Isect &its) {
+	const uint32_t shape = __float_as_uint(r0.w);
+	const ShapeInfo si = sc.shapes[shape];
+	const V3 center = v3(r0);
+	const float radius = r1.x;
+	its.p = rayO + rayD * t;                                                   // ray(its.t)
+	const V3 rel = its.p - center;
+	const V3 local = v3(r1.z * rel.x + r1.w * rel.y + r2.x * rel.z, r2.y * rel.x + r2.z * rel.y + r2.w * rel.z,
+		r3.x * rel.x + r3.y * rel.y + r3.z * rel.z);                           // m_worldToObject(Vector)
+	const float theta = mts_acos(fminf(fmaxf(local.z / radius, -1.0f), 1.0f));
+	float phi = mts_atan2(local.y, local.x);
+	if (phi < 0) phi += 2 * MTS_PI;
+	its.uvx = phi * (0.5f * MTS_INV_PI); its.uvy = theta * MTS_INV_PI;
+	const V3 du = v3(-local.y, local.x, 0.0f) * (2 * MTS_PI);
+	const V3 dpdu = v3(r3.w * du.x + r4.x * du.y + r4.y * du.z, r4.z * du.x + r4.w * du.y + r5.x * du.z, r5.y * du.x + r5.z * du.y + r5.w * du.z);
+	V3 n = normalize(its.p - center);
+	const float zrad = sqrtf(local.x * local.x + local.y * local.y);
+	if (zrad > 0) {
+		const float invZRad = 1.0f / zrad, cosPhi = local.x * invZRad, sinPhi = local.y * invZRad;
+		const V3 dv = v3(local.z * cosPhi, local.z * sinPhi, -mts_sin(theta) * radius) * MTS_PI;
+		const V3 dpdv = v3(r3.w * dv.x + r4.x * dv.y + r4.y * dv.z, r4.z * dv.x + r4.w * dv.y + r5.x * dv.z, r5.y * dv.x + r5.z * dv.y + r5.w * dv.z);
+		its.sh.s = normalize(dpdu); its.sh.t = normalize(dpdv);
+	} else {
+		const Frame3 f = makeFrame(n);
+		its.sh.s = f.s; its.sh.t = f.t;
+	}
+	if (r1.y != 0.0f) n = n * -1.0f;                                           // m_inverted
+	its.sh.n = n; its.geoN = n; its.shN = n;
+	its.wi = toLocal(its.sh, -rayD);
+	its.shape = shape; its.materialId = si.materialId; its.emitterId = si.emitterId;
+}
+
+__device__ inline void fillIntersectionSorted(const DeviceScene &sc, uint32_t tri, float u, float v, V3 rayO, V3 rayD, float t, Isect &its) {
 	const float4 *rec = sc.shadeTris + (size_t) tri * 6;
 	const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2), r3 = __ldg(rec + 3), r4 = __ldg(rec + 4), r5 = __ldg(rec + 5);
 	const uint32_t shape = __float_as_uint(r0.w);
 	const ShapeInfo si = sc.shapes[shape];
+	if (si.isSphere) { fillSphereIntersection(sc, r0, r1, r2, r3, r4, r5, rayO, rayD, t, its); return; }
 	const uint4 idx = make_uint4(__float_as_uint(r2.w), __float_as_uint(r3.w), __float_as_uint(r4.w), shape);
 	const V3 p0 = v3(r0), p1 = v3(r1), p2 = v3(r2);
 	const float bx = 1 - u - v, by = u, bz = v;
@@ -280,8 +315,9 @@ __device__ inline void fillIntersectionSorted(const DeviceScene &sc, uint32_t tr
 
 // Same, addressed as the C ABI reports hits: (shape, primitive index within the shape)
 __device__ inline void fillIntersection(const DeviceScene &sc, uint32_t shape, uint32_t prim, float u, float v,
-		V3 rayD, Isect &its) {
-	fillIntersectionSorted(sc, __ldg(sc.sortedOf + sc.shapes[shape].triOffset + prim), u, v, rayD, its);
+		V3 rayO, V3 rayD, float t, Isect &its) {
+	const ShapeInfo si = sc.shapes[shape];
+	fillIntersectionSorted(sc, __ldg(sc.sortedOf + si.triOffset + (si.isSphere ? 0u : prim)), u, v, rayO, rayD, t, its);
 }
 
 // ---- textures: Texture2D::getValue (texture.cpp:73-82) + Checkerboard::getValue (checkerboard.cpp:47-55) ----------

@@ -38,25 +38,25 @@ __device__ __forceinline__ void flushCounters(uint32_t nodeVisits, uint32_t triT
 
 // rays: 2 x float4 per ray {o.xyz, mint}{d.xyz, maxt}; 128-bit loads. Persistent warps pull rays from
 // `rayCounter` (zeroed by the host before the launch).
-template <bool COUNT>
+template <bool COUNT, bool SPH>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
 k_trace_closest(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, mtsgpu_hit *__restrict__ out,
 		uint32_t *rayCounter, unsigned long long *counters, int refetchBelow, int speculate, int leafThreshold) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
 	uint32_t nodeVisits = 0, triTests = 0;
 	HitSink sink = { sc, out };
-	tracePersistent<false, COUNT>(sc, rays, n, rayCounter, sink, sstack, nodeVisits, triTests, refetchBelow, speculate != 0, leafThreshold);
+	tracePersistent<false, COUNT, HitSink, SPH>(sc, rays, n, rayCounter, sink, sstack, nodeVisits, triTests, refetchBelow, speculate != 0, leafThreshold);
 	if (COUNT) flushCounters(nodeVisits, triTests, counters);
 }
 
-template <bool COUNT>
+template <bool COUNT, bool SPH>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
 k_trace_any(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint32_t *__restrict__ out,
 		uint32_t *rayCounter, unsigned long long *counters, int refetchBelow, int speculate, int leafThreshold) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
 	uint32_t nodeVisits = 0, triTests = 0;
 	OccludedSink sink = { out };
-	tracePersistent<true, COUNT>(sc, rays, n, rayCounter, sink, sstack, nodeVisits, triTests, refetchBelow, speculate != 0, leafThreshold);
+	tracePersistent<true, COUNT, OccludedSink, SPH>(sc, rays, n, rayCounter, sink, sstack, nodeVisits, triTests, refetchBelow, speculate != 0, leafThreshold);
 	if (COUNT) flushCounters(nodeVisits, triTests, counters);
 }
 
@@ -94,15 +94,18 @@ int launchTrace(mtsgpu_ctx *ctx, const float4 *dRays, size_t n, int mode, void *
 	static const int rb = getenv("MTSGPU_REFETCH_BELOW") ? atoi(getenv("MTSGPU_REFETCH_BELOW")) : TRACE_REFETCH_BELOW;
 	static const int lt = getenv("MTSGPU_LEAF_THRESHOLD") ? atoi(getenv("MTSGPU_LEAF_THRESHOLD")) : 16;
 	static const int spec = getenv("MTSGPU_SPECULATE") ? atoi(getenv("MTSGPU_SPECULATE")) : 1;
+	const bool sph = ctx->scene.hasSpheres != 0;
+#define LAUNCH(K, C, S, OUT_T) K<C, S><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (OUT_T *) dOut, rayCounter, (C) ? cnt : nullptr, rb, spec, lt)
 	if (mode == MTSGPU_TRACE_CLOSEST) {
-		if (cnt) k_trace_closest<true><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (mtsgpu_hit *) dOut, rayCounter, cnt, rb, spec, lt);
-		else k_trace_closest<false><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (mtsgpu_hit *) dOut, rayCounter, nullptr, rb, spec, lt);
+		if (cnt) { if (sph) LAUNCH(k_trace_closest, true, true, mtsgpu_hit); else LAUNCH(k_trace_closest, true, false, mtsgpu_hit); }
+		else { if (sph) LAUNCH(k_trace_closest, false, true, mtsgpu_hit); else LAUNCH(k_trace_closest, false, false, mtsgpu_hit); }
 	} else if (mode == MTSGPU_TRACE_ANY) {
-		if (cnt) k_trace_any<true><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (uint32_t *) dOut, rayCounter, cnt, rb, spec, lt);
-		else k_trace_any<false><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (uint32_t *) dOut, rayCounter, nullptr, rb, spec, lt);
+		if (cnt) { if (sph) LAUNCH(k_trace_any, true, true, uint32_t); else LAUNCH(k_trace_any, true, false, uint32_t); }
+		else { if (sph) LAUNCH(k_trace_any, false, true, uint32_t); else LAUNCH(k_trace_any, false, false, uint32_t); }
 	} else {
 		return setError(ctx, MTSGPU_ERR_ARG, "trace: unknown mode %d", mode);
 	}
+#undef LAUNCH
 	CUDA_TRY(ctx, cudaGetLastError());
 	return MTSGPU_OK;
 }

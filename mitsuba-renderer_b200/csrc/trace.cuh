@@ -71,6 +71,49 @@ __device__ __forceinline__ bool triAccelTest(const float4 &q0, const float4 &q1,
 	return u >= 0 && v >= 0 && __fadd_rn(u, v) <= 1.0f;
 }
 
+// Analytic sphere stored in a TriAccel slot (k = 3, the low bits of the reference's KNoTriangleFlag, triaccel.h:27):
+// {k, centre.xyz} {radius, ...}. Sphere::rayIntersect (src/shapes/sphere.cpp:92-131) with solveQuadratic
+// (src/libcore/util.cpp:450-488), fp32 operation by operation; the closest-hit and the shadow version differ in
+// how they treat a ray interval that starts inside the sphere.
+#define TRI_K_SPHERE 3u
+template <bool SHADOW>
+__device__ __forceinline__ bool sphereTest(const float4 &q0, const float4 &q1, const RayIn &r, float mint, float maxt, float &t) {
+	const float ox = __fsub_rn(r.ox, q0.y), oy = __fsub_rn(r.oy, q0.z), oz = __fsub_rn(r.oz, q0.w);
+	const float radius = q1.x;
+	const float A = __fadd_rn(__fadd_rn(__fmul_rn(r.dx, r.dx), __fmul_rn(r.dy, r.dy)), __fmul_rn(r.dz, r.dz));
+	const float B = __fmul_rn(2.0f, __fadd_rn(__fadd_rn(__fmul_rn(r.dx, ox), __fmul_rn(r.dy, oy)), __fmul_rn(r.dz, oz)));
+	const float C = __fsub_rn(__fadd_rn(__fadd_rn(__fmul_rn(ox, ox), __fmul_rn(oy, oy)), __fmul_rn(oz, oz)), __fmul_rn(radius, radius));
+	float nearT, farT;
+	if (A == 0) {
+		if (B == 0) return false;
+		nearT = farT = __fdiv_rn(-C, B);
+	} else {
+		const float discrim = __fsub_rn(__fmul_rn(B, B), __fmul_rn(__fmul_rn(4.0f, A), C));
+		if (discrim < 0) return false;
+		const float sqrtDiscrim = __fsqrt_rn(discrim);
+		const float temp = (B < 0) ? __fmul_rn(-0.5f, __fsub_rn(B, sqrtDiscrim)) : __fmul_rn(-0.5f, __fadd_rn(B, sqrtDiscrim));
+		nearT = __fdiv_rn(temp, A);
+		farT = __fdiv_rn(C, temp);
+		if (nearT > farT) { const float x = nearT; nearT = farT; farT = x; }
+	}
+	if (nearT > maxt || farT < mint) return false;
+	if (SHADOW) return !(nearT < mint && farT > maxt);
+	if (nearT < mint) {
+		if (farT > maxt) return false;
+		t = farT;
+	} else {
+		t = nearT;
+	}
+	return true;
+}
+
+template <bool SHADOW, bool SPH>
+__device__ __forceinline__ bool primTest(const float4 &q0, const float4 &q1, const float4 &q2, uint32_t kraw, const RayIn &r,
+		float mint, float maxt, float &u, float &v, float &t) {
+	if (SPH && (kraw & TRI_K_MASK) == TRI_K_SPHERE) { u = v = 0.0f; return sphereTest<SHADOW>(q0, q1, r, mint, maxt, t); }
+	return triAccelTest(q0, q1, q2, kraw & TRI_K_MASK, r, mint, maxt, u, v, t);
+}
+
 struct HitOut { float t, u, v; uint32_t tri; };   // tri = index into the sorted TriAccel array
 
 #define SSTACK(i) sstack[(i) * TRACE_BLOCK + threadIdx.x]
@@ -96,7 +139,7 @@ __device__ __forceinline__ float safeRcp(float d) {
 // TRACE_BLOCK uint2, interleaved by thread so a warp's accesses are conflict-free); entries
 // beyond it spill to local memory. Stack entries carry the child's entry distance so that
 // nodes lying beyond the current closest hit are dropped when popped.
-template <bool SHADOW, bool COUNT>
+template <bool SHADOW, bool COUNT, bool SPH = false>
 __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, float mint, float maxt,
 		uint2 *sstack, HitOut &hit, uint32_t &nodeVisits, uint32_t &triTests) {
 	uint2 lstack[TRACE_LOCAL_STACK];
@@ -160,7 +203,7 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 				if (SHADOW && (kraw & TRI_NONOCCLUDER)) continue;
 				if (COUNT) triTests++;
 				float u, v, t;
-				if (triAccelTest(q0, q1, q2, kraw & TRI_K_MASK, r, mint, maxt, u, v, t)) {
+				if (primTest<SHADOW, SPH>(q0, q1, q2, kraw, r, mint, maxt, u, v, t)) {
 					if (SHADOW) return true;
 					maxt = t; found = true;            // sahkdtree3.h:278-283: later equal t replaces earlier
 					hit.t = t; hit.u = u; hit.v = v; hit.tri = first + i;
@@ -211,7 +254,7 @@ struct LaneState {
 // their leaf's triangles together. The first version tested a leaf as soon as a lane reached it; ncu's source
 // view showed the TriAccel test — 55 % of all issued instructions — running with 2 of 32 lanes active.
 // The visiting order never changes the closest hit (only which of several bit-identical t values is kept).
-template <bool SHADOW, bool COUNT, class Sink>
+template <bool SHADOW, bool COUNT, class Sink, bool SPH = false>
 __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const float4 *__restrict__ rays, uint32_t n,
 		uint32_t *counter, Sink &sink, uint2 *sstack, uint32_t &nodeVisits, uint32_t &triTests, int refetchBelow, bool speculate = true, int leafThreshold = 16) {
 	uint2 lstack[TRACE_LOCAL_STACK];
@@ -340,7 +383,7 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 						if (SHADOW && (kraw & TRI_NONOCCLUDER)) continue;
 						if (COUNT) triTests++;
 						float u, v, t;
-						if (triAccelTest(q0, q1, q2, kraw & TRI_K_MASK, s.r, s.mint, s.maxt, u, v, t)) {
+						if (primTest<SHADOW, SPH>(q0, q1, q2, kraw, s.r, s.mint, s.maxt, u, v, t)) {
 							s.found = true;
 							if (SHADOW) break;
 							s.maxt = t;                    // sahkdtree3.h:278-283: a later equal t replaces an earlier one

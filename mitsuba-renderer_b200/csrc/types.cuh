@@ -41,7 +41,7 @@ struct ShapeInfo {
 	float invSurfaceArea;     // TriMesh::m_invSurfaceArea (trimesh.cpp:281)
 	uint32_t hasTexcoords;
 	uint32_t hasTangents;     // per-vertex dpdu present (TriMesh::computeTangentSpaceBasis ran for this mesh)
-	uint32_t pad;
+	uint32_t isSphere;        // analytic sphere (src/shapes/sphere.cpp): one primitive, no mesh arrays
 };
 
 struct MaterialDev { uint32_t type; float p[16]; uint32_t tex[2]; uint32_t pad; };   // tex: 0 constant, k: textures[k-1]
@@ -82,6 +82,7 @@ struct DeviceScene {
 	const float *lumCdf;        // nEmitters + 1 (DiscretePDF::m_cdf, pdf.h:82-100)
 	const float *areaCdf;       // per emitter mesh: nTri + 1 entries at ShapeInfo::cdfOffset
 	uint32_t nEmitters, nShapes, nTris, rootIsLeaf;
+	uint32_t hasSpheres;        // some primitives are analytic spheres: traversal kernels take the variant that tests them
 	int32_t background;         // index of the background luminaire (Scene::getBackgroundLuminaire), -1: none
 	float lumOriginalSum;       // DiscretePDF::getOriginalSum()
 	float aabbMin[3], aabbMax[3]; // enlarged kd-tree box (gkdtree.h:1172-1176)
@@ -97,6 +98,7 @@ __device__ __forceinline__ float mts_sin(float x) { return (float) sin((double) 
 __device__ __forceinline__ float mts_cos(float x) { return (float) cos((double) x); }
 __device__ __forceinline__ float mts_tan(float x) { return (float) tan((double) x); }
 __device__ __forceinline__ float mts_atan(float x) { return (float) atan((double) x); }
+__device__ __forceinline__ float mts_atan2(float y, float x) { return (float) atan2((double) y, (double) x); }
 __device__ __forceinline__ float mts_acos(float x) { return (float) acos((double) x); }
 __device__ __forceinline__ float mts_log(float x) { return (float) log((double) x); }
 __device__ __forceinline__ float mts_exp(float x) { return (float) exp((double) x); }

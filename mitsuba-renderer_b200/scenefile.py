@@ -254,6 +254,15 @@ class Shape:
     material: int = -1               # index into SceneDesc.materials, -1: no BSDF (not an occluder)
     emitter: int = -1                # index into SceneDesc.emitters, -1: none
     texcoords: Optional[np.ndarray] = None   # float32 [nVert, 2] or None (uv = 0 everywhere, skdtree.h:414)
+    sphere: Optional[tuple] = None           # (center xyz, radius, inverted): analytic sphere (src/shapes/sphere.cpp); no arrays
+
+
+def sphere_shape(center, radius, material=-1, inverted=False) -> "Shape":
+    """<shape type="sphere"> with `center` and `radius` (sphere.cpp:44-47): one analytic primitive. `positions` holds the
+    two corners of its box so that scene-bound helpers keep working."""
+    c = np.asarray(center, np.float32)
+    box = np.stack([c - np.float32(abs(radius)), c + np.float32(abs(radius))]).astype(np.float32)
+    return Shape(box, np.zeros((0, 3), np.uint32), None, material=material, sphere=(tuple(float(v) for v in c), float(radius), bool(inverted)))
 
 
 @dataclass
@@ -351,7 +360,7 @@ def write_scene(path: str, scene: SceneDesc) -> None:
     cx, cy, cw, ch = scene.crop_rect
     with open(path, "wb") as f:
         f.write(b"MTSB200\0")
-        f.write(struct.pack("<I", 4))
+        f.write(struct.pack("<I", 5))
         f.write(np.ascontiguousarray(scene.camera_to_world, np.float32).tobytes())
         f.write(struct.pack("<5fI", scene.fov, scene.near_clip, scene.far_clip, scene.aperture_radius,
                             scene.focus_depth, int(scene.map_smaller_side)))
@@ -374,6 +383,11 @@ def write_scene(path: str, scene: SceneDesc) -> None:
             f.write(e.abi_params().tobytes()); f.write(e.aux_params().tobytes())
         f.write(struct.pack("<I", len(scene.shapes)))
         for s in scene.shapes:
+            f.write(struct.pack("<I", 0 if s.sphere is None else 1))
+            if s.sphere is not None:
+                (cx, cy, cz), radius, inverted = s.sphere
+                f.write(struct.pack("<2i4fI", s.material, s.emitter, cx, cy, cz, radius, int(inverted)))
+                continue
             f.write(struct.pack("<2I2i2I", len(s.positions), len(s.triangles), s.material, s.emitter,
                                 0 if s.normals is None else 1, 0 if s.texcoords is None else 1))
             f.write(np.ascontiguousarray(s.positions, np.float32).tobytes())

@@ -9,7 +9,7 @@ import numpy as np
 
 from .scenefile import (SceneDesc, Shape, Emitter, lambertian, microfacet, mirror, roughmetal,
                         dielectric, twosided, phong, roughglass, look_at, point_light, spot_light, directional_light,
-                        constant_light, add_light, checkerboard, textured, ward, MODE_PATH, MODE_DIRECT, FILTER_BOX)
+                        constant_light, add_light, checkerboard, textured, ward, sphere_shape, MODE_PATH, MODE_DIRECT, FILTER_BOX)
 
 F32 = np.float32
 
@@ -149,6 +149,22 @@ def textured_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6
     m.append(ward((0.2, 0.3, 0.4), (0.5, 0.5, 0.5), 1.0, 1.0, 0.3, 0.06, "ward"))
     s.shapes[6].material = len(m) - 2
     s.shapes[4].material = len(m) - 1
+    return s
+
+
+def spheres_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6) -> SceneDesc:
+    """The textured all-BSDF scene plus analytic spheres (src/shapes/sphere.cpp): a glass ball, a mirror ball, a
+    checkerboard-textured lambertian ball (uv from the sphere's own parametrisation), an anisotropic Ward ball (its
+    dpdu frame) and an inverted sphere the camera looks into."""
+    s = textured_test_scene(width, height, spp, mode, max_depth)
+    m = s.materials
+    m.append(textured(lambertian((0.5, 0.5, 0.5)), 0, 2))
+    tex_ball = len(m) - 1
+    s.shapes.append(sphere_shape((4.4, 0.6, 1.0), 0.6, material=7))              # dielectric
+    s.shapes.append(sphere_shape((0.9, 0.45, 0.6), 0.45, material=5))             # mirror
+    s.shapes.append(sphere_shape((2.9, 0.5, 0.4), 0.5, material=tex_ball))
+    s.shapes.append(sphere_shape((1.6, 4.6, 4.4), 0.7, material=len(m) - 3))      # anisotropic ward (index 11)
+    s.shapes.append(sphere_shape((4.6, 4.4, 4.6), 0.8, material=0, inverted=True))
     return s
 
 

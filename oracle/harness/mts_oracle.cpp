@@ -317,6 +317,22 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 	if (withGeometry) {
 		for (size_t i = 0; i < s.shapes.size(); ++i) {
 			const sio::Shape &sh = s.shapes[i];
+			if (sh.kind == 1) {      /* <shape type="sphere"> with center + radius (sphere.cpp:44-47) */
+				Properties sp("sphere");
+				sp.setPoint("center", Point(sh.center[0], sh.center[1], sh.center[2]));
+				sp.setFloat("radius", sh.radius);
+				sp.setBoolean("inverted", sh.inverted != 0);
+				ref<Shape> sphere = static_cast<Shape *>(create(MTS_CLASS(Shape), sp));
+				if (sh.matId >= 0) {
+					ref<BSDF> bsdf = makeBSDF(s.materials[sh.matId]);
+					sphere->addChild("", bsdf);
+					bsdf->setParent(sphere);
+				}
+				sphere->configure();
+				scene->addChild("", sphere);
+				sphere->setParent(scene);
+				continue;
+			}
 			ref<TriMesh> mesh = new TriMesh(formatString("shape%i", (int) i), sh.nTri, sh.nVert,
 				sh.hasNormals != 0, sh.hasUv != 0, false, false, sh.hasNormals == 0 /* faceNormals */);
 			if (sh.hasUv)

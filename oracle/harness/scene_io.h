@@ -17,6 +17,8 @@ struct Material { uint32_t type; float p[16]; uint32_t tex[2]; };
 struct Texture  { uint32_t type; float p[12]; };
 struct Emitter  { float intensity[3]; float samplingWeight; uint32_t type; float p[11]; float aux[16]; };
 struct Shape {
+	uint32_t kind;   /* 0 triangle mesh, 1 analytic sphere */
+	float center[3], radius; uint32_t inverted;
 	uint32_t nVert, nTri; int32_t matId, emitId; uint32_t hasNormals, hasUv;
 	std::vector<float> pos, nrm, uv; std::vector<uint32_t> tri;
 };
@@ -48,7 +50,7 @@ inline void load(const std::string &path, Scene &s) {
 	Reader r(path);
 	char magic[8]; r.raw(magic, 8);
 	if (memcmp(magic, "MTSB200", 8) != 0) throw std::runtime_error("bad magic in " + path);
-	if (r.get<uint32_t>() != 4) throw std::runtime_error("bad version in " + path);
+	if (r.get<uint32_t>() != 5) throw std::runtime_error("bad version in " + path);
 	r.raw(s.cameraToWorld, 64);
 	s.fov = r.get<float>(); s.nearClip = r.get<float>(); s.farClip = r.get<float>();
 	s.apertureRadius = r.get<float>(); s.focusDepth = r.get<float>();
@@ -69,6 +71,13 @@ inline void load(const std::string &path, Scene &s) {
 	for (auto &e : s.emitters) { r.raw(e.intensity, 12); e.samplingWeight = r.get<float>(); e.type = r.get<uint32_t>(); r.raw(e.p, 44); r.raw(e.aux, 64); }
 	s.shapes.resize(r.get<uint32_t>());
 	for (auto &sh : s.shapes) {
+		sh.kind = r.get<uint32_t>();
+		if (sh.kind == 1) {
+			sh.nVert = sh.nTri = sh.hasNormals = sh.hasUv = 0;
+			sh.matId = r.get<int32_t>(); sh.emitId = r.get<int32_t>();
+			r.raw(sh.center, 12); sh.radius = r.get<float>(); sh.inverted = r.get<uint32_t>();
+			continue;
+		}
 		sh.nVert = r.get<uint32_t>(); sh.nTri = r.get<uint32_t>();
 		sh.matId = r.get<int32_t>(); sh.emitId = r.get<int32_t>();
 		sh.hasNormals = r.get<uint32_t>(); sh.hasUv = r.get<uint32_t>();
