@@ -283,6 +283,42 @@ private:
 
 	/* Serialised through the manager, so that the BSDF itself has an id (1): textures that are XML children of the
 	 * BSDF carry it as their parent and then write just that id instead of the whole BSDF again. */
+	/* Analytic sphere: Shape::serialize (shape.cpp:130-138) + Sphere::serialize (sphere.cpp:71-77). The parent link (the
+	 * scene) is cleared for the call as for the luminaires; the BSDF that follows inline is read and dropped (the
+	 * material comes from decodeBSDF). */
+	struct SphereData { float o2w[16], w2o[16], radius, center[3]; int inverted; };
+	static SphereData decodeSphere(const Shape *shapeConst) {
+		Shape *shape = const_cast<Shape *>(shapeConst);
+		ConfigurableObject *parent = shape->getParent();
+		ref<MemoryStream> s = new MemoryStream();
+		ref<InstanceManager> mgr = new InstanceManager();
+		shape->setParent(NULL);
+		mgr->serialize(s, shape);
+		shape->setParent(parent);
+		s->setPos(0);
+		std::vector<mtsgpu_texture> scratch;
+		Decoder d; d.s = s; d.textures = &scratch;
+		d.maxId = s->readUInt();
+		s->readString();
+		readParent(d);
+		{   /* m_bsdf */
+			const unsigned int id = s->readUInt();
+			if (id > d.maxId) { d.maxId = id; const std::string cls = s->readString(); decodePayload(cls, d); }
+		}
+		if (s->readUInt() != 0) SLog(EError, "gpupath: subsurface scattering is outside the supported hot path");
+		if (s->readUInt() != 0) SLog(EError, "gpupath: area luminaires on spheres are outside the supported hot path");
+		if (s->readUInt() != 0 || s->readUInt() != 0) SLog(EError, "gpupath: participating media are outside the supported hot path");
+		s->readBool();                                   /* m_occluder */
+		SphereData out;
+		Transform objectToWorld(s);
+		const Matrix4x4 &m = objectToWorld.getMatrix(), &mi = objectToWorld.getInverseMatrix();
+		for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) { out.o2w[4 * i + j] = m.m[i][j]; out.w2o[4 * i + j] = mi.m[i][j]; }
+		out.radius = s->readFloat();
+		Point c(s); out.center[0] = c.x; out.center[1] = c.y; out.center[2] = c.z;
+		out.inverted = s->readBool() ? 1 : 0;
+		return out;
+	}
+
 	static mtsgpu_material decodeBSDF(const BSDF *bsdf, std::vector<mtsgpu_texture> &textures) {
 		ref<MemoryStream> s = new MemoryStream();
 		ref<InstanceManager> mgr = new InstanceManager();
@@ -328,15 +364,17 @@ private:
 				decodeLuminaire(lum, emitters[i]);
 			}
 		}
-		struct MeshRef { const TriMesh *mesh; int mat, emit; };
+		struct MeshRef { const TriMesh *mesh; int mat, emit; bool sphere; SphereData sph; };
 		std::vector<MeshRef> meshes;
 		for (size_t i = 0; i < shapes.size(); ++i) {
 			const Shape *shape = shapes[i];
-			if (!shape->getClass()->derivesFrom(MTS_CLASS(TriMesh)))
-				Log(EError, "gpupath: shape %i (%s) is not a triangle mesh", (int) i, shape->getClass()->getName().c_str());
+			const bool isSphere = shape->getClass()->getName() == "Sphere";
+			if (!isSphere && !shape->getClass()->derivesFrom(MTS_CLASS(TriMesh)))
+				Log(EError, "gpupath: shape %i (%s) is neither a triangle mesh nor a sphere", (int) i, shape->getClass()->getName().c_str());
 			if (shape->hasSubsurface() || shape->isMediumTransition())
 				Log(EError, "gpupath: subsurface / medium transitions are outside the supported hot path");
-			MeshRef r; r.mesh = static_cast<const TriMesh *>(shape); r.mat = -1; r.emit = -1;
+			MeshRef r; r.mesh = isSphere ? NULL : static_cast<const TriMesh *>(shape); r.mat = -1; r.emit = -1; r.sphere = isSphere;
+			if (isSphere) r.sph = decodeSphere(shape);
 			if (shape->hasBSDF()) {
 				const BSDF *bsdf = shape->getBSDF();
 				if (!materialIds.count(bsdf)) {
@@ -355,6 +393,11 @@ private:
 			check(c, mtsgpu_upload_materials(c, materials.empty() ? NULL : &materials[0], (int) materials.size()));
 			check(c, mtsgpu_upload_emitters(c, emitters.empty() ? NULL : &emitters[0], (int) emitters.size()));
 			for (size_t i = 0; i < meshes.size(); ++i) {
+				if (meshes[i].sphere) {
+					const SphereData &sp = meshes[i].sph;
+					check(c, mtsgpu_upload_sphere(c, (int) i, sp.o2w, sp.w2o, sp.radius, sp.center, sp.inverted, meshes[i].mat, meshes[i].emit));
+					continue;
+				}
 				const TriMesh *m = meshes[i].mesh;
 				/* Point/Normal are 3 packed floats, Triangle is 3 packed uint32 (core/triangle.h) */
 				check(c, mtsgpu_upload_mesh(c, (int) i,
