@@ -211,7 +211,10 @@ MTSGPU_API int mtsgpu_upload_mesh(mtsgpu_ctx *ctx, int shapeIndex,
 /* Analytic sphere as shape `shapeIndex` (src/shapes/sphere.cpp:31-173): the fields Sphere::serialize writes
  * (sphere.cpp:71-77) — objectToWorld with the scale removed and its inverse (row-major 4x4), radius, centre,
  * `inverted`. It is one primitive of the acceleration structure; hits report prim = 0xFFFFFFFF (KNoTriangleFlag,
- * include/mitsuba/render/triaccel.h:27) and u = v = 0. A sphere cannot carry an area luminaire yet (refused). */
+ * include/mitsuba/render/triaccel.h:27) and u = v = 0. With emitterId >= 0 the sphere carries that area
+ * luminaire: it is then sampled by solid angle — the cone it subtends from outside, uniformly by area from inside
+ * (Sphere::sampleSolidAngle / pdfSolidAngle, src/shapes/sphere.cpp:191-247, through AreaLuminaire::sample,
+ * src/luminaires/area.cpp:71-86). */
 MTSGPU_API int mtsgpu_upload_sphere(mtsgpu_ctx *ctx, int shapeIndex, const float objectToWorld[16], const float worldToObject[16],
                                     float radius, const float center[3], int inverted, int materialId, int emitterId);
 

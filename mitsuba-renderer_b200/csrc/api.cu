@@ -136,10 +136,9 @@ int mtsgpu_upload_sphere(mtsgpu_ctx *ctx, int shapeIndex, const float objectToWo
 	REQUIRE(ctx, objectToWorld && worldToObject && center, MTSGPU_ERR_ARG, "upload_sphere: null argument");
 	REQUIRE(ctx, shapeIndex >= 0 && (size_t) shapeIndex <= ctx->meshes.size(), MTSGPU_ERR_ARG,
 		"upload_sphere: shapes must be uploaded in kd-tree order (got %d, expected <= %zu)", shapeIndex, ctx->meshes.size());
-	REQUIRE(ctx, emitterId < 0, MTSGPU_ERR_UNSUPPORTED, "upload_sphere: area luminaires on spheres are outside the supported hot path");
 	if ((size_t) shapeIndex < ctx->meshes.size()) ctx->meshes.resize(shapeIndex);
 	HostMesh m;
-	m.nVert = 1; m.nTri = 1; m.materialId = materialId; m.emitterId = -1; m.hasNormals = false;
+	m.nVert = 1; m.nTri = 1; m.materialId = materialId; m.emitterId = emitterId < 0 ? -1 : emitterId; m.hasNormals = false;
 	m.pos.assign(center, center + 3);
 	m.tri = { 0u, SPHERE_MARK, SPHERE_MARK };
 	m.sphere = true; m.inverted = inverted != 0; m.radius = radius;

@@ -646,6 +646,12 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		if (m.emitterId >= 0) {
 			REQUIRE(ctx, emitterShape[m.emitterId] < 0, MTSGPU_ERR_ARG, "emitter %d is bound to more than one shape", m.emitterId);
 			emitterShape[m.emitterId] = (int) s;
+		}
+		if (m.emitterId >= 0 && m.sphere) {
+			// Sphere::m_invSurfaceArea (sphere.cpp:59); points are drawn by Sphere::sampleSolidAngle, no area CDF
+			volatile float a = 4 * 3.14159265358979323846f; a = a * m.radius; a = a * m.radius;
+			si.invSurfaceArea = 1 / a;
+		} else if (m.emitterId >= 0) {
 			// TriMesh::configure: area PDF over Triangle::surfaceArea (trimesh.cpp:266-283, triangle.cpp:49-55)
 			std::vector<float> areas(m.nTri), cdf;
 			for (uint32_t t = 0; t < m.nTri; ++t) {

@@ -385,6 +385,71 @@ __device__ inline bool bsphereRayIntersect(V3 center, float radius, V3 o, V3 d, 
 	return true;
 }
 
+// squareToCone / squareToConePdf (util.cpp:652-662)
+__device__ inline V3 squareToCone(float cosCutoff, float sx, float sy) {
+	const float cosTheta = (1 - sx) + sx * cosCutoff;
+	const float sinTheta = sqrtf(1 - cosTheta * cosTheta);
+	const float phi = sy * (2 * MTS_PI);
+	return v3(mts_cos(phi) * sinTheta, mts_sin(phi) * sinTheta, cosTheta);
+}
+
+// Sphere::rayIntersect(ray, 0, inf, t) (sphere.cpp:92-112) with solveQuadratic (util.cpp:450-488)
+__device__ inline bool sphereRayIntersect(V3 center, float radius, V3 ro, V3 rd, float &t) {
+	const V3 o = ro - center;
+	const float A = rd.x * rd.x + rd.y * rd.y + rd.z * rd.z;
+	const float B = 2 * (rd.x * o.x + rd.y * o.y + rd.z * o.z);
+	const float C = o.x * o.x + o.y * o.y + o.z * o.z - radius * radius;
+	float nearT, farT;
+	if (A == 0) {
+		if (B == 0) return false;
+		nearT = farT = -C / B;
+	} else {
+		const float discrim = B * B - 4.0f * A * C;
+		if (discrim < 0) return false;
+		const float sqrtDiscrim = sqrtf(discrim);
+		const float temp = (B < 0) ? -0.5f * (B - sqrtDiscrim) : -0.5f * (B + sqrtDiscrim);
+		nearT = temp / A; farT = C / temp;
+		if (nearT > farT) { const float x = nearT; nearT = farT; farT = x; }
+	}
+	if (farT < 0.0f) return false;              // nearT > inf cannot happen
+	t = (nearT < 0.0f) ? farT : nearT;           // farT > inf cannot happen
+	return true;
+}
+
+// Sphere::sampleSolidAngle (sphere.cpp:191-229): cone sampling from outside (Shirley, Wang & Zimmerman 1996),
+// uniform area sampling from inside. Returns the pdf wrt. solid angle, 0 on failure.
+__device__ inline float sphereSampleSolidAngle(V3 center, float radius, float invSurfaceArea, V3 p, float sx, float sy, V3 &sp, V3 &sn) {
+	const V3 w = center - p; const float invDistW = 1 / length(w);
+	const float squareTerm = fabsf(radius * invDistW);
+	if (squareTerm >= 1 - MTS_EPSILON) {
+		const V3 d = squareToSphere(sx, sy);
+		sp = center + d * radius; sn = d;
+		const V3 lumToPoint = p - sp;
+		const float distSquared = dot(lumToPoint, lumToPoint), dp = dot(lumToPoint, sn);
+		return dp > 0 ? invSurfaceArea * distSquared * sqrtf(distSquared) / dp : 0.0f;
+	}
+	const float cosThetaMax = sqrtf(fmaxf(0.0f, 1 - squareTerm * squareTerm));
+	const V3 d = toWorld(makeFrame(w * invDistW), squareToCone(cosThetaMax, sx, sy));
+	float t;
+	if (!sphereRayIntersect(center, radius, p, d, t)) return 0.0f;
+	sp = p + d * t;
+	sn = normalize(sp - center);
+	return 1 / ((2 * MTS_PI) * (1 - cosThetaMax));
+}
+
+// Sphere::pdfSolidAngle (sphere.cpp:231-247)
+__device__ inline float spherePdfSolidAngle(V3 center, float radius, float invSurfaceArea, V3 p, V3 sp, V3 sn) {
+	const V3 w = p - center; const float invDistW = 1 / length(w);
+	const float squareTerm = fabsf(radius * invDistW);
+	if (squareTerm >= 1 - MTS_EPSILON) {
+		const V3 lumToPoint = p - sp;
+		const float distSquared = dot(lumToPoint, lumToPoint), dp = dot(lumToPoint, sn);
+		return dp > 0 ? invSurfaceArea * distSquared * sqrtf(distSquared) / dp : 0.0f;
+	}
+	const float cosThetaMax = sqrtf(fmaxf(0.0f, 1 - squareTerm * squareTerm));
+	return 1 / (2 * MTS_PI * (1 - cosThetaMax));
+}
+
 __device__ inline void sampleLuminaire(const DeviceScene &sc, V3 p, float sx, float sy, bool importance, LumSample &out) {
 	out.pdf = 0; out.emitter = -1; out.mis = true;
 	if (sc.nEmitters == 0) return;
@@ -397,6 +462,10 @@ __device__ inline void sampleLuminaire(const DeviceScene &sc, V3 p, float sx, fl
 	V3 value = inten;
 	if (em.type == MTSGPU_EMITTER_AREA) {
 		const ShapeInfo si = sc.shapes[em.shape];
+		if (si.isSphere) {
+			const float4 cr = __ldg(sc.positions + si.vertOffset);            // centre, radius
+			pdf = sphereSampleSolidAngle(v3(cr), cr.w, si.invSurfaceArea, p, sx, sy, out.p, out.n);
+		} else {
 		// TriMesh::sampleArea (trimesh.cpp:297-302) + Triangle::sample (triangle.cpp:23-47)
 		const int tri = cdfSampleReuse(sc.areaCdf + si.cdfOffset, (int) si.nTri, sy);
 		const uint4 idx = __ldg(sc.triIdx + si.triOffset + tri);
@@ -416,6 +485,7 @@ __device__ inline void sampleLuminaire(const DeviceScene &sc, V3 p, float sx, fl
 		const float distSquared = dot(lumToPoint, lumToPoint), dp = dot(lumToPoint, out.n);
 		if (dp > 0)
 			pdf = si.invSurfaceArea * distSquared * sqrtf(distSquared) / dp;
+		}
 		// AreaLuminaire::sample (area.cpp:68-79)
 		V3 d = p - out.p;
 		if (pdf > 0 && dot(d, out.n) > 0) {
@@ -469,10 +539,15 @@ __device__ inline float pdfLuminaire(const DeviceScene &sc, V3 from, V3 lumP, V3
 	const EmitterDev em = sc.emitters[emitter];
 	const float luminance = importance ? em.weight : 1.0f;
 	const float fraction = luminance / sc.lumOriginalSum;
+	const ShapeInfo si = sc.shapes[em.shape];
+	if (si.isSphere) {
+		const float4 cr = __ldg(sc.positions + si.vertOffset);
+		return spherePdfSolidAngle(v3(cr), cr.w, si.invSurfaceArea, from, lumP, lumN) * fraction;
+	}
 	const V3 lumToPoint = from - lumP;
 	const float distSquared = dot(lumToPoint, lumToPoint);
 	const float invDP = fmaxf(0.0f, sqrtf(distSquared) / dot(lumToPoint, lumN));
-	return (sc.shapes[em.shape].invSurfaceArea * distSquared * invDP) * fraction;
+	return (si.invSurfaceArea * distSquared * invDP) * fraction;
 }
 
 // Scene::pdfLuminaire for the background luminaire: ConstantLuminaire::pdf (constant.cpp:88-90)

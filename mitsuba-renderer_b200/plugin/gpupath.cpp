@@ -284,8 +284,8 @@ private:
 	/* Serialised through the manager, so that the BSDF itself has an id (1): textures that are XML children of the
 	 * BSDF carry it as their parent and then write just that id instead of the whole BSDF again. */
 	/* Analytic sphere: Shape::serialize (shape.cpp:130-138) + Sphere::serialize (sphere.cpp:71-77). The parent link (the
-	 * scene) is cleared for the call as for the luminaires; the BSDF that follows inline is read and dropped (the
-	 * material comes from decodeBSDF). */
+	 * scene) is cleared for the call as for the luminaires; the BSDF and the area luminaire that follow inline are read
+	 * and dropped (the material comes from decodeBSDF, the luminaire from Scene::getLuminaires()). */
 	struct SphereData { float o2w[16], w2o[16], radius, center[3]; int inverted; };
 	static SphereData decodeSphere(const Shape *shapeConst) {
 		Shape *shape = const_cast<Shape *>(shapeConst);
@@ -306,7 +306,21 @@ private:
 			if (id > d.maxId) { d.maxId = id; const std::string cls = s->readString(); decodePayload(cls, d); }
 		}
 		if (s->readUInt() != 0) SLog(EError, "gpupath: subsurface scattering is outside the supported hot path");
-		if (s->readUInt() != 0) SLog(EError, "gpupath: area luminaires on spheres are outside the supported hot path");
+		{   /* m_luminaire: an AreaLuminaire written inline (luminaire.cpp:66-74, area.cpp:52-57); its values come through
+		     * getLuminaires(), so it is only skipped here. Its parent and shape references are this sphere's id. */
+			const unsigned int id = s->readUInt();
+			if (id > d.maxId) {
+				d.maxId = id;
+				if (s->readString() != "AreaLuminaire") SLog(EError, "gpupath: unexpected luminaire class on a sphere");
+				s->readUInt();                               /* parent: the sphere, already written */
+				if (s->readUInt() != 0) SLog(EError, "gpupath: luminaires inside participating media are outside the supported hot path");
+				s->readFloat(); s->readInt(); s->readBool();
+				Transform worldToLuminaire(s);
+				s->readString();
+				Spectrum intensity(s);
+				s->readUInt();                               /* m_shape: the sphere again */
+			}
+		}
 		if (s->readUInt() != 0 || s->readUInt() != 0) SLog(EError, "gpupath: participating media are outside the supported hot path");
 		s->readBool();                                   /* m_occluder */
 		SphereData out;

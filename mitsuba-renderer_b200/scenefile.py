@@ -257,12 +257,12 @@ class Shape:
     sphere: Optional[tuple] = None           # (center xyz, radius, inverted): analytic sphere (src/shapes/sphere.cpp); no arrays
 
 
-def sphere_shape(center, radius, material=-1, inverted=False) -> "Shape":
+def sphere_shape(center, radius, material=-1, inverted=False, emitter=-1) -> "Shape":
     """<shape type="sphere"> with `center` and `radius` (sphere.cpp:44-47): one analytic primitive. `positions` holds the
     two corners of its box so that scene-bound helpers keep working."""
     c = np.asarray(center, np.float32)
     box = np.stack([c - np.float32(abs(radius)), c + np.float32(abs(radius))]).astype(np.float32)
-    return Shape(box, np.zeros((0, 3), np.uint32), None, material=material, sphere=(tuple(float(v) for v in c), float(radius), bool(inverted)))
+    return Shape(box, np.zeros((0, 3), np.uint32), None, material=material, emitter=emitter, sphere=(tuple(float(v) for v in c), float(radius), bool(inverted)))
 
 
 @dataclass

@@ -168,6 +168,18 @@ def spheres_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6)
     return s
 
 
+def sphere_lights_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6) -> SceneDesc:
+    """The sphere scene plus two spheres that carry area luminaires (area.cpp:71-82 -> Sphere::sampleSolidAngle,
+    sphere.cpp:191-229): a small ball with a lambertian BSDF — shading points on its own surface take the
+    "inside the sphere" branch — and a bare emitting ball without a BSDF (not an occluder)."""
+    s = spheres_test_scene(width, height, spp, mode, max_depth)
+    s.emitters.append(Emitter((9.0, 7.5, 6.0), 1.0))
+    s.shapes.append(sphere_shape((2.2, 1.9, 1.6), 0.3, material=0, emitter=len(s.emitters) - 1))
+    s.emitters.append(Emitter((3.0, 5.0, 8.0), 2.5))
+    s.shapes.append(sphere_shape((4.0, 3.8, 3.0), 0.45, material=-1, emitter=len(s.emitters) - 1))
+    return s
+
+
 def lights_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6, background=True) -> SceneDesc:
     """The all-BSDF scene opened up (no ceiling, no side walls: a floor and a back wall remain) and lit by every
     supported luminaire type: the two area lights, a point light, a spot light, a directional light and — with

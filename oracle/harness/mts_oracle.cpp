@@ -328,6 +328,16 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 					sphere->addChild("", bsdf);
 					bsdf->setParent(sphere);
 				}
+				if (sh.emitId >= 0) {    /* an <luminaire type="area"> nested in the sphere */
+					const sio::Emitter &e = s.emitters[sh.emitId];
+					Properties lp("area");
+					lp.setSpectrum("intensity", rgb(e.intensity));
+					lp.setFloat("samplingWeight", e.samplingWeight);
+					ref<Luminaire> lum = static_cast<Luminaire *>(create(MTS_CLASS(Luminaire), lp));
+					sphere->addChild("", lum);
+					lum->setParent(sphere);
+					lum->configure();
+				}
 				sphere->configure();
 				scene->addChild("", sphere);
 				sphere->setParent(scene);
