@@ -84,8 +84,16 @@ typedef struct mtsgpu_material {
 
 /* 2D textures (src/librender/texture.cpp:43-82: uv' = uv * uvScale + uvOffset, then the texture's own lookup).
  *   CHECKERBOARD  src/textures/checkerboard.cpp:28-55   p[0..2] brightColor, p[3..5] darkColor, p[6..7] uvOffset,
- *                                                       p[8..9] uvScale */
-enum mtsgpu_texture_type { MTSGPU_TEXTURE_CHECKERBOARD = 0 };
+ *                                                       p[8..9] uvScale
+ *   BITMAP        src/textures/ldrtexture.cpp:35-253 (and exrtexture.cpp) over MIPMap, src/librender/mipmap.cpp:
+ *                 p[0] filterType (0 ewa, 1 trilinear, 2 none: MIPMap::EFilterType, mipmap.h:39-46), p[1] wrapMode
+ *                 (0 repeat, 1 black, 2 white, 3 clamp: mipmap.h:32-37), p[2] maxAnisotropy, p[6..7] uvOffset,
+ *                 p[8..9] uvScale. The pixels follow through mtsgpu_upload_bitmap. At the hit of a camera ray the
+ *                 lookup is filtered with the uv partials of the ray differentials (Intersection::computePartials,
+ *                 src/librender/intersection.cpp:5-75); every later hit takes the bilinear level-0 lookup, which is
+ *                 what the reference's filters reduce to for a ray without differentials. */
+enum mtsgpu_texture_type { MTSGPU_TEXTURE_CHECKERBOARD = 0, MTSGPU_TEXTURE_BITMAP = 1 };
+enum mtsgpu_bitmap_format { MTSGPU_BITMAP_U8 = 0, MTSGPU_BITMAP_F32 = 1 };
 typedef struct mtsgpu_texture {
 	uint32_t type;   /* mtsgpu_texture_type */
 	float p[12];
@@ -194,12 +202,20 @@ MTSGPU_API int mtsgpu_upload_materials(mtsgpu_ctx *ctx, const mtsgpu_material *m
  * (src/luminaires/area.cpp:35-83): intensity + Luminaire::getSamplingWeight. */
 /* Textures referenced by mtsgpu_material.texture (Texture2D::getValue, src/librender/texture.cpp:73-82). */
 MTSGPU_API int mtsgpu_upload_textures(mtsgpu_ctx *ctx, const mtsgpu_texture *textures, int count);
+/* Pixels of BITMAP texture `textureIndex` (after mtsgpu_upload_textures, before mtsgpu_build_accel), top row first.
+ * MTSGPU_BITMAP_U8: `channels` (1, 3 or 4) bytes per pixel as Bitmap::getData() holds them; they are linearised with
+ * the table of LDRTexture::initializeFrom (src/textures/ldrtexture.cpp:124-207): gamma == -1 selects the sRGB curve,
+ * any other value is the exponent. MTSGPU_BITMAP_F32: `channels` (3 or 4) linear floats per pixel, as EXRTexture hands
+ * them to MIPMap::fromBitmap (src/textures/exrtexture.cpp:52-60); gamma is ignored. The library builds the pyramid of
+ * MIPMap::MIPMap (src/librender/mipmap.cpp:31-137: Lanczos up-sampling to powers of two, box-filtered levels). */
+MTSGPU_API int mtsgpu_upload_bitmap(mtsgpu_ctx *ctx, int textureIndex, int width, int height, int channels,
+	const void *pixels, int format, float gamma);
 MTSGPU_API int mtsgpu_upload_emitters(mtsgpu_ctx *ctx, const mtsgpu_emitter *emitters, int count);
 
 /* One TriMesh (include/mitsuba/render/trimesh.h:100-133) at kd-tree shape index `shapeIndex`
  * (ShapeKDTree::addShape order, skdtree.cpp:45-60). Shapes must be uploaded in index order 0,1,2...
  * positions: 3*nVert floats; normals: 3*nVert floats or NULL (=> shading frame = geometric frame,
- * skdtree.h:405-408); texcoords are accepted and ignored (constant textures only).
+ * skdtree.h:405-408); texcoords: 2*nVert floats or NULL (its.uv = 0, skdtree.h:414).
  * materialId < 0: shape has no BSDF => not an occluder (shape.h:361) and paths end on it (path.cpp:70-77).
  * emitterId  < 0: not a luminaire. */
 MTSGPU_API int mtsgpu_upload_mesh(mtsgpu_ctx *ctx, int shapeIndex,
@@ -367,6 +383,16 @@ MTSGPU_API int mtsgpu_sampler_values(mtsgpu_ctx *ctx, const mtsgpu_render_params
  * two texture slots of the hit's material evaluated there: out rows of 8 floats {uv, slot 0 rgb, slot 1 rgb}; zeros
  * on a miss or on a shape without a BSDF. */
 MTSGPU_API int mtsgpu_intersect_uv(mtsgpu_ctx *ctx, const float *rays, size_t n, float *out);
+
+/* Texture filtering at camera-ray hits: `samples` rows are {raster x, raster y, lens x, lens y}. For each one the ray
+ * differential of Camera::generateRayDifferential (src/librender/camera.cpp:79-90), narrowed by 1 / sqrt(sampleCount) as
+ * SampleIntegrator::renderBlock does (src/librender/integrator.cpp:145,165), is intersected, the hit's BSDF is
+ * fetched as Intersection::getBSDF(ray) does (include/mitsuba/render/records.inl:55-61, which runs
+ * Intersection::computePartials, src/librender/intersection.cpp:5-75, when a texture filters), and `out` receives rows
+ * of 12 floats: its.uv, dudx, dudy, dvdx, dvdy, then the BSDF's two spectrum slots as the textures return them
+ * (Texture2D::getValue(its), src/librender/texture.cpp:73-82 -> MIPMap::getValue, src/librender/mipmap.cpp:264-316).
+ * Zeros on a miss. */
+MTSGPU_API int mtsgpu_texture_lookup(mtsgpu_ctx *ctx, const float *samples, size_t n, int sampleCount, float *out);
 
 /* Closest-hit query that also fills the Intersection record (fillIntersectionRecord<true>,
  * skdtree.h:352-432): out rows of 12 floats {p, geoFrame.n, shFrame.n, wi}; zeros on a miss. */

@@ -29,10 +29,11 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_film_splat_static", "mtsgpu_render_multi", "mtsgpu_serialized_count", "mtsgpu_serialized_load",
     "mtsgpu_serialized_free", "mtsgpu_serialized_save", "mtsgpu_upload_serialized", "mtsgpu_film_develop",
     "mtsgpu_film_develop_device", "mtsgpu_film_save", "mtsgpu_write_exr", "mtsgpu_write_mfilm", "mtsgpu_sampler_values",
-    "mtsgpu_upload_textures", "mtsgpu_intersect_uv", "mtsgpu_upload_sphere",
+    "mtsgpu_upload_textures", "mtsgpu_intersect_uv", "mtsgpu_upload_sphere", "mtsgpu_upload_bitmap", "mtsgpu_texture_lookup",
 ]
 SAMPLER_INDEPENDENT, SAMPLER_LD, SAMPLER_STRATIFIED, SAMPLER_HALTON = 0, 1, 2, 3
 FILM_EXR, FILM_M = 0, 1
+BITMAP_U8, BITMAP_F32 = 0, 1
 STATIC_SCRATCH_BYTES = 4 << 20
 
 
@@ -107,6 +108,7 @@ def load_library(path: Optional[str] = None):
     lib.mtsgpu_upload_emitters.argtypes = [vp, C.POINTER(Emitter), C.c_int]
     lib.mtsgpu_upload_textures.argtypes = [vp, C.POINTER(Texture), C.c_int]
     lib.mtsgpu_intersect_uv.argtypes = [vp, vp, C.c_size_t, vp]
+    lib.mtsgpu_upload_bitmap.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_float]
     lib.mtsgpu_upload_sphere.argtypes = [vp, C.c_int, vp, vp, C.c_float, vp, C.c_int, C.c_int, C.c_int]
     lib.mtsgpu_upload_mesh.argtypes = [vp, C.c_int, vp, vp, vp, C.c_uint32, vp, C.c_uint32, C.c_int, C.c_int]
     lib.mtsgpu_set_camera.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float]
@@ -120,6 +122,7 @@ def load_library(path: Optional[str] = None):
     for name in ("mtsgpu_bsdf_eval", "mtsgpu_emitter_sample", "mtsgpu_camera_rays", "mtsgpu_film_splat",
                  "mtsgpu_film_splat_static"):
         getattr(lib, name).argtypes = [vp, vp, C.c_size_t, vp]
+    lib.mtsgpu_texture_lookup.argtypes = [vp, vp, C.c_size_t, C.c_int, vp]
     lib.mtsgpu_intersect_full.argtypes = [vp, vp, C.c_size_t, vp, vp]
     lib.mtsgpu_get_triaccel.argtypes = [vp, vp, C.c_size_t, vp]
     lib.mtsgpu_accel_info_get.argtypes = [vp, C.POINTER(AccelInfo)]
@@ -228,6 +231,11 @@ class Context:
             texs[i].type = t.type
             texs[i].p[:] = [float(v) for v in t.p]
         self._check(self.lib.mtsgpu_upload_textures(self.h, texs, len(scene.textures)))
+        for i, t in enumerate(scene.textures):
+            if t.pixels is not None:
+                px = np.ascontiguousarray(t.pixels, np.uint8)
+                self._check(self.lib.mtsgpu_upload_bitmap(self.h, i, px.shape[1], px.shape[0], px.shape[2], self._ptr(px),
+                                                          BITMAP_U8, t.gamma))
         mats = (Material * max(1, len(scene.materials)))()
         for i, m in enumerate(scene.materials):
             mats[i].type = m.type
@@ -384,6 +392,14 @@ class Context:
         else:
             film = np.ascontiguousarray(film, np.float32)
             self._check(self.lib.mtsgpu_film_save(self.h, self._ptr(film), 0, fmt, int(option), path.encode()))
+
+    def texture_lookup(self, samples, sample_count=1):
+        """Camera samples {x, y, lens x, lens y} -> rows {uv, dudx, dudy, dvdx, dvdy, slot 0 rgb, slot 1 rgb} at the hit
+        of the camera's ray differential (mtsgpu_texture_lookup)."""
+        samples = np.ascontiguousarray(samples, np.float32).reshape(-1, 4)
+        out = np.zeros((len(samples), 12), np.float32)
+        self._check(self.lib.mtsgpu_texture_lookup(self.h, self._ptr(samples), len(samples), sample_count, self._ptr(out)))
+        return out
 
     def intersect_uv(self, rays):
         """Closest hit -> rows {uv, texture slot 0 rgb, slot 1 rgb} of the hit's material at that uv."""

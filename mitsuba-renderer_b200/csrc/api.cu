@@ -90,8 +90,47 @@ int mtsgpu_upload_textures(mtsgpu_ctx *ctx, const mtsgpu_texture *textures, int 
 	ENTER(ctx);
 	REQUIRE(ctx, count >= 0 && (count == 0 || textures), MTSGPU_ERR_ARG, "upload_textures: bad arguments");
 	for (int i = 0; i < count; ++i)
-		REQUIRE(ctx, textures[i].type == MTSGPU_TEXTURE_CHECKERBOARD, MTSGPU_ERR_UNSUPPORTED, "texture %d: unsupported texture type %u", i, textures[i].type);
+		REQUIRE(ctx, textures[i].type == MTSGPU_TEXTURE_CHECKERBOARD || textures[i].type == MTSGPU_TEXTURE_BITMAP, MTSGPU_ERR_UNSUPPORTED,
+			"texture %d: unsupported texture type %u", i, textures[i].type);
+	for (int i = 0; i < count; ++i) {
+		if (textures[i].type != MTSGPU_TEXTURE_BITMAP) continue;
+		const float f = textures[i].p[0], w = textures[i].p[1];
+		REQUIRE(ctx, (f == 0 || f == 1 || f == 2) && (w == 0 || w == 1 || w == 2 || w == 3), MTSGPU_ERR_ARG,
+			"texture %d: unknown filter type / wrap mode (%g, %g)", i, f, w);
+	}
 	ctx->textures.assign(textures, textures + count);
+	ctx->bitmaps.assign(count, HostBitmap());
+	ctx->built = false;
+	return MTSGPU_OK;
+}
+
+int mtsgpu_upload_bitmap(mtsgpu_ctx *ctx, int textureIndex, int width, int height, int channels, const void *pixels, int format, float gamma) {
+	ENTER(ctx);
+	REQUIRE(ctx, textureIndex >= 0 && (size_t) textureIndex < ctx->textures.size() && ctx->textures[textureIndex].type == MTSGPU_TEXTURE_BITMAP,
+		MTSGPU_ERR_ARG, "upload_bitmap: texture %d is not a bitmap texture of the uploaded table", textureIndex);
+	REQUIRE(ctx, pixels && width > 0 && height > 0 && width <= 16384 && height <= 16384, MTSGPU_ERR_ARG, "upload_bitmap: bad size %d x %d", width, height);
+	HostBitmap &b = ctx->bitmaps[textureIndex];
+	const size_t n = (size_t) width * height;
+	if (format == MTSGPU_BITMAP_U8) {
+		// "%i bpp images are currently not supported!" (ldrtexture.cpp:201)
+		REQUIRE(ctx, channels == 1 || channels == 2 || channels == 3 || channels == 4, MTSGPU_ERR_ARG, "upload_bitmap: %d bpp images are currently not supported!", 8 * channels);
+		float tbl[256];                                 // LDRTexture::initializeFrom (ldrtexture.cpp:117-133)
+		for (int i = 0; i < 256; ++i) {
+			const float value = (float) i / (float) 255;
+			if (gamma == -1) tbl[i] = value <= 0.04045f ? value / 12.92f : std::pow((value + 0.055f) / (float) (1.0 + 0.055), 2.4f);
+			else tbl[i] = std::pow(value, gamma);
+		}
+		const uint8_t *d = static_cast<const uint8_t *>(pixels);
+		b.rgb.resize(3 * n);
+		for (size_t i = 0; i < n; ++i)
+			for (int c = 0; c < 3; ++c) b.rgb[3 * i + c] = tbl[d[i * channels + (channels >= 3 ? c : 0)]];
+	} else {
+		REQUIRE(ctx, format == MTSGPU_BITMAP_F32 && (channels == 3 || channels == 4), MTSGPU_ERR_ARG, "upload_bitmap: bad format / channel count");
+		const float *d = static_cast<const float *>(pixels);
+		b.rgb.resize(3 * n);
+		for (size_t i = 0; i < n; ++i) for (int c = 0; c < 3; ++c) b.rgb[3 * i + c] = d[i * channels + c];
+	}
+	b.width = width; b.height = height;
 	ctx->built = false;
 	return MTSGPU_OK;
 }
@@ -289,6 +328,7 @@ int mtsgpu_sampler_values(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, u
 	return hookSamplerValues(ctx, params, pixel, draw, out);
 }
 int mtsgpu_intersect_uv(mtsgpu_ctx *ctx, const float *rays, size_t n, float *out) { ENTER(ctx); return hookIntersectUv(ctx, rays, n, out); }
+int mtsgpu_texture_lookup(mtsgpu_ctx *ctx, const float *samples, size_t n, int sampleCount, float *out) { ENTER(ctx); return hookTextureLookup(ctx, samples, n, sampleCount, out); }
 int mtsgpu_emitter_sample(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out) { ENTER(ctx); return hookEmitterSample(ctx, queries, n, out); }
 int mtsgpu_camera_rays(mtsgpu_ctx *ctx, const float *samples, size_t n, float *out) { ENTER(ctx); return hookCameraRays(ctx, samples, n, out); }
 int mtsgpu_film_splat(mtsgpu_ctx *ctx, const float *samples, size_t n, float *outFilm) { ENTER(ctx); return hookFilmSplat(ctx, samples, n, outFilm); }

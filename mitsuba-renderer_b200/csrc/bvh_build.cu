@@ -417,7 +417,7 @@ inline void hcoordinateSystem(HV a, HV &b, HV &c) {                 // src/libco
 }
 }
 
-static void computeTangents(HostMesh &m, std::vector<float> &dpduOut) {
+static void computeTangents(HostMesh &m, std::vector<float> &dpduOut, std::vector<float> &dpdvOut) {
 	const size_t nv = m.nVert;
 	std::vector<HV> dpdu(nv, HV{ 0, 0, 0 }), dpdv(nv, HV{ 0, 0, 0 });
 	std::vector<uint32_t> sharers(nv, 0u);
@@ -457,14 +457,16 @@ static void computeTangents(HostMesh &m, std::vector<float> &dpduOut) {
 		dpdv[i0] = hadd(dpdv[i0], dv); dpdv[i1] = hadd(dpdv[i1], dv); dpdv[i2] = hadd(dpdv[i2], dv);
 		sharers[i0]++; sharers[i1]++; sharers[i2]++;
 	}
-	dpduOut.resize(3 * nv);
+	dpduOut.resize(3 * nv); dpdvOut.resize(3 * nv);
 	for (size_t i = 0; i < nv; ++i) {
 		if (hlen2(dpdu[i]) == 0.0f || hlen2(dpdv[i]) == 0.0f) {
 			hcoordinateSystem(N[i], dpdu[i], dpdv[i]);
 		} else if (sharers[i] > 0) {
 			dpdu[i] = hdiv(dpdu[i], (float) sharers[i]);
+			dpdv[i] = hdiv(dpdv[i], (float) sharers[i]);
 		}
 		dpduOut[3 * i] = dpdu[i].x; dpduOut[3 * i + 1] = dpdu[i].y; dpduOut[3 * i + 2] = dpdu[i].z;
+		dpdvOut[3 * i] = dpdv[i].x; dpdvOut[3 * i + 1] = dpdv[i].y; dpdvOut[3 * i + 2] = dpdv[i].z;
 	}
 }
 
@@ -590,22 +592,27 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	for (auto &m : ctx->meshes) anyTexcoords |= !m.uv.empty();
 	std::vector<float2> uvs(anyTexcoords ? nVert : 1, make_float2(0, 0));
 	// TriMesh::configure (trimesh.cpp:288-290): meshes with an anisotropic BSDF get a tangent space
-	std::vector<std::vector<float> > meshTangents(nShapes);
+	std::vector<std::vector<float> > meshTangents(nShapes), meshTangentsV(nShapes);
 	bool anyTangents = false;
 	for (size_t s = 0; s < nShapes; ++s) {
 		HostMesh &m = ctx->meshes[s];
 		if (m.materialId < 0 || m.materialId >= (int) ctx->materials.size()) continue;
 		const mtsgpu_material &mat = ctx->materials[m.materialId];
 		const bool anisotropic = (mat.type & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_WARD && mat.p[8] != mat.p[9];
-		if (!anisotropic || m.sphere) continue;       // a sphere brings its own dpdu / dpdv (sphere.cpp:146-161)
+		bool usesRayDifferentials = false;            // a bitmap texture in one of the BSDF's slots (ldrtexture.cpp:243-245)
+		for (int k = 0; k < 2; ++k)
+			if (mat.texture[k] > 0 && mat.texture[k] <= ctx->textures.size())
+				usesRayDifferentials |= ctx->textures[mat.texture[k] - 1].type == MTSGPU_TEXTURE_BITMAP;
+		if (!(anisotropic || usesRayDifferentials) || m.sphere) continue;       // a sphere brings its own dpdu / dpdv (sphere.cpp:146-161)
+		if (!anisotropic && m.uv.empty()) continue;   // computeTangentSpaceBasis returns false without texture coordinates
 		REQUIRE(ctx, !m.uv.empty(), MTSGPU_ERR_ARG, "shape %zu: computeTangentSpace(): texture coordinates are required to generate "
 			"tangent vectors. If you want to render with an anisotropic material, please make sure that all associated shapes have "
 			"valid texture coordinates.", s);
 		if (!m.hasNormals) continue;                  // "Vertex normals are required to compute a tangent space basis!" (warning only)
-		computeTangents(m, meshTangents[s]);
+		computeTangents(m, meshTangents[s], meshTangentsV[s]);
 		anyTangents = true;
 	}
-	std::vector<float4> tangents(anyTangents ? nVert : 1, make_float4(0, 0, 0, 0));
+	std::vector<float4> tangents(anyTangents ? 2 * nVert : 2, make_float4(0, 0, 0, 0));     // {dpdu, dpdv} per vertex
 	std::vector<ShapeInfo> shapes(nShapes);
 	std::vector<float> areaCdfAll;
 	std::vector<int> emitterShape(ctx->emitters.size(), -1);
@@ -629,7 +636,10 @@ int buildAccel(mtsgpu_ctx *ctx) {
 			sphereXf.push_back(m.inverted ? 1.0f : 0.0f); sphereXf.push_back(0.0f);
 		}
 		for (uint32_t v = 0; v < (meshTangents[s].empty() ? 0u : m.nVert); ++v)
-			tangents[vOff + v] = make_float4(meshTangents[s][3*v], meshTangents[s][3*v+1], meshTangents[s][3*v+2], 0);
+		{
+			tangents[2 * (vOff + v)] = make_float4(meshTangents[s][3*v], meshTangents[s][3*v+1], meshTangents[s][3*v+2], 0);
+			tangents[2 * (vOff + v) + 1] = make_float4(meshTangentsV[s][3*v], meshTangentsV[s][3*v+1], meshTangentsV[s][3*v+2], 0);
+		}
 		for (uint32_t v = 0; v < (m.uv.empty() ? 0u : m.nVert); ++v) uvs[vOff + v] = make_float2(m.uv[2*v], m.uv[2*v+1]);
 		REQUIRE(ctx, m.materialId < (int) ctx->materials.size(), MTSGPU_ERR_ARG, "shape %zu: material id %d out of range", s, m.materialId);
 		REQUIRE(ctx, m.emitterId < (int) ctx->emitters.size(), MTSGPU_ERR_ARG, "shape %zu: emitter id %d out of range", s, m.emitterId);
@@ -702,7 +712,18 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	}
 	std::vector<TextureDev> texs(std::max<size_t>(ctx->textures.size(), 1));
 	memset(texs.data(), 0, texs.size() * sizeof(TextureDev));
-	for (size_t i = 0; i < ctx->textures.size(); ++i) { texs[i].type = ctx->textures[i].type; memcpy(texs[i].p, ctx->textures[i].p, 48); }
+	std::vector<float> texels; std::vector<uint32_t> mipLevels;
+	for (size_t i = 0; i < ctx->textures.size(); ++i) {
+		texs[i].type = ctx->textures[i].type; memcpy(texs[i].p, ctx->textures[i].p, 48);
+		if (texs[i].type != MTSGPU_TEXTURE_BITMAP) continue;
+		REQUIRE(ctx, i < ctx->bitmaps.size() && ctx->bitmaps[i].width > 0, MTSGPU_ERR_ARG, "texture %zu: the bitmap's pixels were not uploaded (mtsgpu_upload_bitmap)", i);
+		texs[i].pad[0] = (uint32_t) (mipLevels.size() / 4);
+		buildMipPyramid(ctx->bitmaps[i], (int) texs[i].p[0], (int) texs[i].p[1], texels, mipLevels);
+		texs[i].pad[1] = (uint32_t) (mipLevels.size() / 4) - texs[i].pad[0];
+	}
+	if (texels.empty()) texels.assign(4, 0.0f);
+	if (mipLevels.empty()) mipLevels.assign(4, 0u);
+	float mipLut[128]; mipWeightLut(mipLut);
 
 	// ---- upload ----
 	CUDA_TRY(ctx, ctx->dTriIdx.alloc(nTri * sizeof(uint4)));
@@ -720,6 +741,13 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dTexcoords.p, uvs.data(), uvs.size() * sizeof(float2), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, ctx->dTextures.alloc(texs.size() * sizeof(TextureDev)));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dTextures.p, texs.data(), texs.size() * sizeof(TextureDev), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, ctx->dTexels.alloc(texels.size() * sizeof(float)));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dTexels.p, texels.data(), texels.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, ctx->dMipLevels.alloc(mipLevels.size() * sizeof(uint32_t)));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dMipLevels.p, mipLevels.data(), mipLevels.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, ctx->dMipLut.alloc(sizeof(mipLut)));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dMipLut.p, mipLut, sizeof(mipLut), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, ctx->dCamera.alloc(sizeof(CameraDev)));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dShapes.p, shapes.data(), nShapes * sizeof(ShapeInfo), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dMaterials.p, mats.data(), mats.size() * sizeof(MaterialDev), cudaMemcpyHostToDevice, st));
 	if (!areaCdfAll.empty())
@@ -932,6 +960,8 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	sc.sortedOf = ctx->dSortedOf.as<uint32_t>();
 	sc.hasSpheres = anySphere ? 1u : 0u;
 	sc.textures = ctx->dTextures.as<TextureDev>();
+	sc.texels = ctx->dTexels.as<float4>(); sc.mipLevels = ctx->dMipLevels.as<uint4>(); sc.mipLut = ctx->dMipLut.as<float>();
+	sc.camera = ctx->dCamera.as<CameraDev>();
 	sc.shapes = ctx->dShapes.as<ShapeInfo>();
 	sc.materials = ctx->dMaterials.as<MaterialDev>();
 	sc.areaCdf = ctx->dAreaCdf.as<float>();

@@ -34,6 +34,13 @@ struct HostMesh {
 };
 #define SPHERE_MARK 0xFFFFFFFFu
 
+// Linear RGB pixels of one BITMAP texture (what MIPMap::fromBitmap receives), top row first
+struct HostBitmap { int width = 0, height = 0; std::vector<float> rgb; };
+// mipmap.cpp: the pyramid of MIPMap::MIPMap (src/librender/mipmap.cpp:31-137) appended to `texels` (rgb + pad per
+// texel); `levels` receives {offset into texels, width, height, 0} per level
+void buildMipPyramid(const HostBitmap &bmp, int filterType, int wrapMode, std::vector<float> &texels, std::vector<uint32_t> &levels);
+void mipWeightLut(float *lut128);            // MIPMap's EWA weight table (mipmap.cpp:128-134)
+
 struct mtsgpu_ctx {
 	int device = 0;
 	cudaStream_t stream = nullptr;
@@ -47,6 +54,7 @@ struct mtsgpu_ctx {
 	std::vector<mtsgpu_material> materials;
 	std::vector<mtsgpu_emitter> emitters;
 	std::vector<mtsgpu_texture> textures;
+	std::vector<HostBitmap> bitmaps;          // parallel to textures; filled by mtsgpu_upload_bitmap
 	std::vector<HostMesh> meshes;
 	std::vector<int> emitterShape;   // emitter id -> shape index
 	int lumImportance = -1;          // which luminaire CDF is on the device (-1: none)
@@ -58,7 +66,7 @@ struct mtsgpu_ctx {
 	bool built = false;
 	DeviceScene scene;
 	DevBuf dTriAccel, dTriAccelOrig, dNodes, dTriIdx, dPositions, dNormals, dShapes, dMaterials, dEmitters,
-	       dLumCdf, dAreaCdf, dTexcoords, dTextures, dTangents, dShadeTris, dSortedOf;
+	       dLumCdf, dAreaCdf, dTexcoords, dTextures, dTangents, dShadeTris, dSortedOf, dTexels, dMipLevels, dMipLut, dCamera;
 	mtsgpu_accel_info accel = {};
 
 	// trace staging + counters
@@ -99,4 +107,5 @@ int hookEmitterSample(mtsgpu_ctx *ctx, const float *queries, size_t n, float *ou
 int hookCameraRays(mtsgpu_ctx *ctx, const float *samples, size_t n, float *out);
 int hookFilmSplat(mtsgpu_ctx *ctx, const float *samples, size_t n, float *outFilm);
 int hookIntersectUv(mtsgpu_ctx *ctx, const float *rays, size_t n, float *out);
+int hookTextureLookup(mtsgpu_ctx *ctx, const float *samples, size_t n, int sampleCount, float *out);
 int hookIntersectFull(mtsgpu_ctx *ctx, const float *rays, size_t n, mtsgpu_hit *hits, float *out);

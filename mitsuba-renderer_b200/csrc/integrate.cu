@@ -58,6 +58,7 @@ struct BatchDesc {
 	uint32_t sampleBegin, sampleCount;   // global sample indices [sampleBegin, sampleBegin + sampleCount)
 	uint32_t slots;                      // tileCount * sampleCount * TILE_PIX
 	uint32_t seed;
+	float diffScale;                     // 1 / sqrt(sample count): SampleIntegrator::renderBlock narrows the ray differentials by it
 	SamplerConfig sampler;
 };
 
@@ -239,7 +240,8 @@ __device__ __forceinline__ bool nextEvent(const DeviceScene &sc, const Integrato
 }
 
 // One shading step for the queue entry i. MODE 0 = path, 1 = direct (primary pass), 2 = direct (secondary pass).
-template <int MODE>
+// BMP: the scene has bitmap textures (the variant without them carries none of the filtering code).
+template <int MODE, bool BMP>
 #ifndef SHADE_MIN_BLOCKS
 #define SHADE_MIN_BLOCKS 6
 #endif
@@ -336,7 +338,15 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 			MaterialDev mat;
 			if (alive) {
 				mat = sc.materials[its.materialId];
-				resolveTextures(sc, mat, its.uvx, its.uvy);
+				float4 duv = make_float4(0, 0, 0, 0);
+				if (BMP && MODE != 2 && depth == 1 && (mat.tex[0] | mat.tex[1]) && usesRayDifferentials(sc, mat)) {
+					// Intersection::getBSDF(ray) (records.inl:55-61): the camera ray is the only one with differentials
+					float lx = 0, ly = 0;
+					if (b.sampler.lensDraw) smp.get2D(DIM_LENS, lx, ly);
+					const float2 sp = wf.samplePos[slot];
+					duv = cameraHitPartials(sc, sp.x, sp.y, lx, ly, rayO, rayD, b.diffScale, h.w, __uint_as_float(h.y), __uint_as_float(h.z), its.p, its.geoN);
+				}
+				resolveTextures<BMP>(sc, mat, its.uvx, its.uvy, duv);
 				if (its.emitterId >= 0 && (flags & PF_EMITTED) && (MODE == 0 || round == 0))
 					Li = Li + (MODE == 0 ? thr : v3(1, 1, 1)) * emitterLe(sc, its.emitterId, its.geoN, -rayD);
 				if (MODE == 0 && ig.maxDepth > 0 && (int) depth >= ig.maxDepth) alive = false;
@@ -603,6 +613,8 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 			CUDA_TRY(ctx, dPrimRay.alloc((size_t) ctx->pathCapacity * 32));
 			CUDA_TRY(ctx, dPrimHit.alloc((size_t) ctx->pathCapacity * 16));
 		}
+		// the camera behind DeviceScene::camera (ray differentials for bitmap textures)
+		CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dCamera.p, &ctx->camera, sizeof(CameraDev), cudaMemcpyHostToDevice, st));
 		WfArrays wf;
 		char *ps = ctx->dPathState.as<char>();
 		wf.thr = (float4 *) ps; wf.li = (float4 *) (ps + (size_t) capacity * 16); wf.bsdfVal = (float4 *) (ps + (size_t) capacity * 32);
@@ -614,6 +626,8 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 		uint32_t *slotBuf[2] = { ctx->dQueueA.as<uint32_t>(), ctx->dQueueB.as<uint32_t>() };
 		float4 *rayBuf[2] = { ctx->dRayA.as<float4>(), ctx->dRayB.as<float4>() };
 
+		bool bmp = false;
+		for (const mtsgpu_texture &t : ctx->textures) bmp |= t.type == MTSGPU_TEXTURE_BITMAP;
 		IntegratorDev ig;
 		ig.mode = P->mode; ig.maxDepth = P->maxDepth; ig.rrDepth = P->rrDepth; ig.strictNormals = P->strictNormals;
 		ig.nLum = P->luminaireSamples; ig.nBsdf = P->bsdfSamples; ig.importance = (int) P->importanceSampleLuminaires;
@@ -634,6 +648,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 				b.sampleBegin = P->sppBegin + s0; b.sampleCount = std::min(sampleChunk, spp - s0);
 				b.slots = b.tileCount * b.sampleCount * TILE_PIX; b.seed = P->seed;
 				b.sampler = samplerConfig;
+				b.diffScale = 1.0f / std::sqrt((float) P->sppTotal);          // integrator.cpp:145
 				int cur = 0;
 				wf.slotNext = slotBuf[cur]; wf.rayNext = rayBuf[cur];
 				CUDA_TRY(ctx, cudaMemsetAsync(wf.counters, 0, 8, st));
@@ -654,7 +669,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 						cudaEventRecord(evB, st);
 						S.normalRays += nRays;
 						CUDA_TRY(ctx, cudaMemsetAsync(wf.counters, 0, 8, st));
-						k_shade<0><<<blocksFor(nRays, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nRays, 0);
+						if (bmp) k_shade<0, true><<<blocksFor(nRays, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nRays, 0); else k_shade<0, false><<<blocksFor(nRays, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nRays, 0);
 						CUDA_TRY(ctx, cudaMemcpyAsync(hCounts, wf.counters, 8, cudaMemcpyDeviceToHost, st));
 						CUDA_TRY(ctx, cudaStreamSynchronize(st));
 						{ float ms = 0; cudaEventElapsedTime(&ms, evA, evB); msClosest += ms; }
@@ -687,7 +702,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 					for (int r = 0; r < rounds; ++r) {
 						wf.slotNext = slotBuf[cur ^ 1]; wf.rayNext = rayBuf[cur ^ 1];
 						CUDA_TRY(ctx, cudaMemsetAsync(wf.counters, 0, 8, st));
-						k_shade<1><<<blocksFor(nPrim, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nPrim, (uint32_t) r);
+						if (bmp) k_shade<1, true><<<blocksFor(nPrim, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nPrim, (uint32_t) r); else k_shade<1, false><<<blocksFor(nPrim, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nPrim, (uint32_t) r);
 						CUDA_TRY(ctx, cudaMemcpyAsync(hCounts, wf.counters, 8, cudaMemcpyDeviceToHost, st));
 						CUDA_TRY(ctx, cudaStreamSynchronize(st));
 						S.kernelLaunches++;
@@ -705,7 +720,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 							cudaEventRecord(evA, st);
 						if (launchClosestWf(ctx, wf.rayCur, nSec, wf.hit, persistClosest)) return fail(MTSGPU_ERR_CUDA);
 							cudaEventRecord(evB, st);
-							k_shade<2><<<blocksFor(nSec, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nSec, (uint32_t) r);
+							if (bmp) k_shade<2, true><<<blocksFor(nSec, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nSec, (uint32_t) r); else k_shade<2, false><<<blocksFor(nSec, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nSec, (uint32_t) r);
 							CUDA_TRY(ctx, cudaStreamSynchronize(st));
 							{ float ms = 0; cudaEventElapsedTime(&ms, evA, evB); msClosest += ms; }
 							S.normalRays += nSec; S.kernelLaunches += 2;
@@ -804,6 +819,40 @@ __global__ void k_hook_uv(const DeviceScene sc, const float4 *rays, const mtsgpu
 	MaterialDev m = sc.materials[its.materialId];
 	resolveTextures(sc, m, its.uvx, its.uvy);
 	for (int k = 0; k < 6; ++k) o[2 + k] = m.p[k];
+}
+
+// camera samples [x, y, lens.x, lens.y] -> rays
+__global__ void k_hook_camera_rays(const CameraDev cam, const float *q, uint32_t n, float4 *rays) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	V3 o, d; float mint, maxt;
+	cameraRay(cam, q[4 * (size_t) i], q[4 * (size_t) i + 1], q[4 * (size_t) i + 2], q[4 * (size_t) i + 3], o, d, mint, maxt);
+	rays[2 * (size_t) i] = make_float4(o.x, o.y, o.z, mint); rays[2 * (size_t) i + 1] = make_float4(d.x, d.y, d.z, maxt);
+}
+
+// rows of 12: its.uv, dudx, dudy, dvdx, dvdy, the two spectrum slots of the hit's BSDF with their textures looked up
+__global__ void k_hook_texture(const DeviceScene sc, const float *q, const float4 *rays, const mtsgpu_hit *hits, uint32_t n, float diffScale, float *out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	float *o = out + (size_t) i * 12;
+	for (int k = 0; k < 12; ++k) o[k] = 0;
+	const mtsgpu_hit h = hits[i];
+	if (h.shape == 0xFFFFFFFFu) return;
+	Isect its;
+	fillIntersection(sc, h.shape, h.prim, h.u, h.v, v3(rays[2 * (size_t) i]), v3(rays[2 * (size_t) i + 1]), h.t, its);
+	o[0] = its.uvx; o[1] = its.uvy;
+	if (its.materialId < 0) return;
+	MaterialDev m = sc.materials[its.materialId];
+	float4 duv = make_float4(0, 0, 0, 0);
+	if (usesRayDifferentials(sc, m)) {
+		const ShapeInfo si = sc.shapes[h.shape];
+		const uint32_t tri = __ldg(sc.sortedOf + si.triOffset + (si.isSphere ? 0u : h.prim));
+		duv = cameraHitPartials(sc, q[4 * (size_t) i], q[4 * (size_t) i + 1], q[4 * (size_t) i + 2], q[4 * (size_t) i + 3],
+			v3(rays[2 * (size_t) i]), v3(rays[2 * (size_t) i + 1]), diffScale, tri, h.u, h.v, its.p, its.geoN);
+	}
+	o[2] = duv.x; o[3] = duv.y; o[4] = duv.z; o[5] = duv.w;
+	resolveTextures(sc, m, its.uvx, its.uvy, duv);
+	for (int k = 0; k < 6; ++k) o[6 + k] = m.p[k];
 }
 
 __global__ void k_hook_isect(const DeviceScene sc, const float4 *rays, const mtsgpu_hit *hits, uint32_t n, float *out) {
@@ -913,6 +962,22 @@ int hookIntersectUv(mtsgpu_ctx *ctx, const float *rays, size_t n, float *out) {
 	CUDA_TRY(ctx, ctx->dStageOut.alloc(n * 8 * 4));
 	k_hook_uv<<<blocksFor(n, 128), 128, 0, ctx->stream>>>(ctx->scene, ctx->dRays.as<float4>(), ctx->dHits.as<mtsgpu_hit>(), (uint32_t) n, ctx->dStageOut.as<float>());
 	return download(ctx, out, ctx->dStageOut, n * 8 * 4);
+}
+
+int hookTextureLookup(mtsgpu_ctx *ctx, const float *samples, size_t n, int sampleCount, float *out) {
+	REQUIRE(ctx, ctx->built && ctx->haveCamera, MTSGPU_ERR_ARG, "texture_lookup: call mtsgpu_set_camera and mtsgpu_build_accel first");
+	if (n == 0) return MTSGPU_OK;
+	int rc;
+	if ((rc = upload(ctx, ctx->dStage, samples, n * 16))) return rc;
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dCamera.p, &ctx->camera, sizeof(CameraDev), cudaMemcpyHostToDevice, ctx->stream));
+	CUDA_TRY(ctx, ctx->dRays.alloc(n * 32));
+	CUDA_TRY(ctx, ctx->dHits.alloc(n * sizeof(mtsgpu_hit)));
+	k_hook_camera_rays<<<blocksFor(n, 128), 128, 0, ctx->stream>>>(ctx->camera, ctx->dStage.as<float>(), (uint32_t) n, ctx->dRays.as<float4>());
+	if ((rc = launchTrace(ctx, ctx->dRays.as<float4>(), n, MTSGPU_TRACE_CLOSEST, ctx->dHits.p, nullptr))) return rc;
+	CUDA_TRY(ctx, ctx->dStageOut.alloc(n * 12 * 4));
+	k_hook_texture<<<blocksFor(n, 128), 128, 0, ctx->stream>>>(ctx->scene, ctx->dStage.as<float>(), ctx->dRays.as<float4>(), ctx->dHits.as<mtsgpu_hit>(), (uint32_t) n,
+		1.0f / std::sqrt((float) std::max(sampleCount, 1)), ctx->dStageOut.as<float>());
+	return download(ctx, out, ctx->dStageOut, n * 12 * 4);
 }
 
 // Film splat of an arbitrary sample list through the render loop's own k_splat: samples are

@@ -294,7 +294,7 @@ __device__ inline void fillIntersectionSorted(const DeviceScene &sc, uint32_t tr
 	}
 	bool tangentFrame = false;
 	if (si.hasNormals && si.hasTangents) {     // skdtree.h:385-398: the shading frame follows the interpolated dpdu
-		const V3 d0 = v3(__ldg(sc.tangents + idx.x)), d1 = v3(__ldg(sc.tangents + idx.y)), d2 = v3(__ldg(sc.tangents + idx.z));
+		const V3 d0 = v3(__ldg(sc.tangents + 2 * idx.x)), d1 = v3(__ldg(sc.tangents + 2 * idx.y)), d2 = v3(__ldg(sc.tangents + 2 * idx.z));
 		const V3 dpdu = d0 * bx + d1 * by + d2 * bz;
 		its.sh.n = its.shN;
 		its.sh.s = normalize(dpdu - its.shN * dot(its.shN, dpdu));
@@ -327,12 +327,200 @@ __device__ inline V3 textureValue(const TextureDev &t, float u, float v) {
 	const int x = 2 * mtsModulo((int) (tu * 2), 2) - 1, y = 2 * mtsModulo((int) (tv * 2), 2) - 1;
 	return (x * y == 1) ? v3(t.p[0], t.p[1], t.p[2]) : v3(t.p[3], t.p[4], t.p[5]);
 }
+
+// ---- bitmap textures: MIPMap (src/librender/mipmap.cpp) over the pyramid built by mipmap.cpp ---------------------
+// MIPMap::getTexel (mipmap.cpp:220-243), including its `x <= 0` bounds test
+__device__ inline V3 mipTexel(const DeviceScene &sc, const TextureDev &t, int level, int x, int y) {
+	const uint4 L = __ldg(sc.mipLevels + t.pad[0] + level);
+	const int w = (int) L.y, h = (int) L.z, wrap = (int) t.p[1];
+	if (x <= 0 || y < 0 || x >= w || y >= h) {
+		if (wrap == 0) { x = mtsModulo(x, w); y = mtsModulo(y, h); }
+		else if (wrap == 3) { x = min(max(x, 0), w - 1); y = min(max(y, 0), h - 1); }
+		else return wrap == 1 ? v3(0, 0, 0) : v3(1, 1, 1);
+	}
+	return v3(__ldg(sc.texels + L.x + (uint32_t) (x + w * y)));
+}
+
+// MIPMap::triangle (mipmap.cpp:245-262)
+__device__ inline V3 mipTriangle(const DeviceScene &sc, const TextureDev &t, int level, float x, float y) {
+	if (t.p[0] == 2.0f) {
+		const uint4 L = __ldg(sc.mipLevels + t.pad[0]);
+		return mipTexel(sc, t, 0, (int) floorf(x * (float) (int) L.y), (int) floorf(y * (float) (int) L.z));
+	}
+	level = min(max(level, 0), (int) t.pad[1] - 1);
+	const uint4 L = __ldg(sc.mipLevels + t.pad[0] + level);
+	x = x * (float) (int) L.y - 0.5f;
+	y = y * (float) (int) L.z - 0.5f;
+	const int xPos = (int) floorf(x), yPos = (int) floorf(y);
+	const float dx = x - xPos, dy = y - yPos;
+	return mipTexel(sc, t, level, xPos, yPos) * (1.0f - dx) * (1.0f - dy)
+		+ mipTexel(sc, t, level, xPos, yPos + 1) * (1.0f - dx) * dy
+		+ mipTexel(sc, t, level, xPos + 1, yPos) * dx * (1.0f - dy)
+		+ mipTexel(sc, t, level, xPos + 1, yPos + 1) * dx * dy;
+}
+
+// MIPMap::EWA (mipmap.cpp:318-357)
+__device__ inline V3 mipEWA(const DeviceScene &sc, const TextureDev &t, float u, float v, float dudx, float dudy, float dvdx, float dvdy, int level) {
+	const int levels = (int) t.pad[1];
+	if (level >= levels) return mipTexel(sc, t, levels - 1, 0, 0);
+	const uint4 L = __ldg(sc.mipLevels + t.pad[0] + level);
+	const float lw = (float) (int) L.y, lh = (float) (int) L.z;
+	V3 result = v3(0, 0, 0);
+	float denominator = 0.0f;
+	u = u * lw; v = v * lh;
+	dudx = dudx * lw; dudy = dudy * lh;
+	dvdx = dvdx * lw; dvdy = dvdy * lh;
+	float A = dudy * dudy + dvdy * dvdy + 1.0f;
+	float B = -2.0f * (dudx * dudy + dvdx * dvdy);
+	float C = dudx * dudx + dvdx * dvdx + 1.0f;
+	const float F = A * C - B * B * 0.25f;
+	const float du = sqrtf(C), dv = sqrtf(A);
+	const int u0 = (int) ceilf(u - du), u1 = (int) floorf(u + du);
+	const int v0 = (int) ceilf(v - dv), v1 = (int) floorf(v + dv);
+	const float invF = 1.0f / F;
+	A *= invF; B *= invF; C *= invF;
+	for (int ut = u0; ut <= u1; ++ut) {
+		const float uu = ut - u;
+		for (int vt = v0; vt <= v1; ++vt) {
+			const float vv = vt - v;
+			const float r2 = A * uu * uu + B * uu * vv + C * vv * vv;
+			if (r2 < 1) {
+				const float weight = __ldg(sc.mipLut + max(0, min((int) (r2 * 128), 128 - 1)));
+				result = result + mipTexel(sc, t, level, ut, vt) * weight;
+				denominator += weight;
+			}
+		}
+	}
+	return result * (1.0f / denominator);
+}
+
+__device__ inline float mtsLog2(float x) { return mts_log(x) * (1.0f / 0.693147182464599609375f); }   // util.cpp:365-368, logf(2.0f)
+
+// MIPMap::getValue (mipmap.cpp:264-316) at the uv of Texture2D::getValue (texture.cpp:73-82). duv = {dudx, dudy, dvdx, dvdy}
+// of the hit; all zero for a ray without differentials, which every filter answers with the bilinear level-0 lookup.
+__device__ __noinline__ V3 bitmapValue(const DeviceScene &sc, const TextureDev &t, float u, float v, float4 duv) {
+	const float tu = u * t.p[8] + t.p[6], tv = v * t.p[9] + t.p[7];
+	float dudx = duv.x * t.p[8], dudy = duv.y * t.p[8], dvdx = duv.z * t.p[9], dvdy = duv.w * t.p[9];
+	const int levels = (int) t.pad[1];
+	if (t.p[0] == 1.0f) {                                  // trilinear
+		const float width = 2.0f * fmaxf(fmaxf(fabsf(dudx), fabsf(dudy)), fmaxf(fabsf(dvdx), fabsf(dvdy)));
+		const float mipmapLevel = levels - 1 + mtsLog2(fmaxf(width, 1e-8f));
+		if (mipmapLevel < 0) return mipTriangle(sc, t, 0, tu, tv);
+		else if (mipmapLevel >= levels - 1) return mipTexel(sc, t, levels - 1, 0, 0);
+		const int level = (int) mipmapLevel;
+		const float delta = mipmapLevel - level;
+		const V3 a = mipTriangle(sc, t, level, tu, tv);    // sic: both terms of the blend read the same level
+		return a * (1.0f - delta) + a * delta;
+	} else if (t.p[0] == 0.0f) {                           // EWA
+		if (dudx * dudx + dudy * dudy < dvdx * dvdx + dvdy * dvdy) {
+			float x = dudx; dudx = dvdx; dvdx = x;
+			x = dudy; dudy = dvdy; dvdy = x;
+		}
+		const float majorLength = sqrtf(dudx * dudx + dudy * dudy);
+		float minorLength = sqrtf(dvdx * dvdx + dvdy * dvdy);
+		const float maxAnisotropy = t.p[2];
+		if (minorLength * maxAnisotropy < majorLength && minorLength > 0.0f) {
+			const float scale = majorLength / (minorLength * maxAnisotropy);
+			dvdx *= scale; dvdy *= scale;
+			minorLength *= scale;
+		}
+		if (minorLength == 0) return mipTriangle(sc, t, 0, tu, tv);
+		const float lod = fminf(fmaxf(0.0f, levels - 1 + mtsLog2(minorLength)), (float) (levels - 1));
+		const int ilod = (int) floorf(lod);
+		const float d = lod - ilod;
+		return mipEWA(sc, t, tu, tv, dudx, dudy, dvdx, dvdy, ilod) * (1 - d) + mipEWA(sc, t, tu, tv, dudx, dudy, dvdx, dvdy, ilod + 1) * d;
+	}
+	const uint4 L = __ldg(sc.mipLevels + t.pad[0]);
+	return mipTexel(sc, t, 0, (int) floorf(tu * (float) (int) L.y), (int) floorf(tv * (float) (int) L.z));
+}
+
+// uv partials of a camera-ray hit. The reference carries the two offset rays of Camera::generateRayDifferential
+// (src/librender/camera.cpp:79-90: the same lens sample, the raster position moved by one pixel in x / in y) along with
+// the camera ray (narrowed by 1 / sqrt(spp)) and, when the hit's BSDF reads a texture that filters, solves for du/dx .. dv/dy in
+// Intersection::computePartials (src/librender/intersection.cpp:5-75). Here the offset rays are rebuilt from the
+// sample's raster position and lens sample, and dpdu / dpdv from the hit's shading record: this runs once per path,
+// at the first hit, and only on surfaces with a bitmap texture. `tri` is the sorted triangle index of the hit.
+__device__ __noinline__ float4 cameraHitPartials(const DeviceScene &sc, float sx, float sy, float lx, float ly,
+		V3 rayO, V3 rayD, float diffScale, uint32_t tri, float bu, float bv, V3 p, V3 geoN) {
+	const float4 zero = make_float4(0, 0, 0, 0);
+	// ---- its.dpdu, its.dpdv (skdtree.h:385-406 for meshes, sphere.cpp:146-165 for spheres)
+	const float4 *rec = sc.shadeTris + (size_t) tri * 6;
+	const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2), r3 = __ldg(rec + 3), r4 = __ldg(rec + 4), r5 = __ldg(rec + 5);
+	const ShapeInfo si = sc.shapes[__float_as_uint(r0.w)];
+	V3 dpdu = v3(0, 0, 0), dpdv = v3(0, 0, 0);
+	if (si.isSphere) {
+		const V3 rel = p - v3(r0);
+		const float radius = r1.x;
+		const V3 local = v3(r1.z * rel.x + r1.w * rel.y + r2.x * rel.z, r2.y * rel.x + r2.z * rel.y + r2.w * rel.z,
+			r3.x * rel.x + r3.y * rel.y + r3.z * rel.z);
+		const float theta = mts_acos(fminf(fmaxf(local.z / radius, -1.0f), 1.0f));
+		const V3 du = v3(-local.y, local.x, 0.0f) * (2 * MTS_PI);
+		dpdu = v3(r3.w * du.x + r4.x * du.y + r4.y * du.z, r4.z * du.x + r4.w * du.y + r5.x * du.z, r5.y * du.x + r5.z * du.y + r5.w * du.z);
+		const float zrad = sqrtf(local.x * local.x + local.y * local.y);
+		float cosPhi = 0, sinPhi = 1;
+		if (zrad > 0) { const float invZRad = 1.0f / zrad; cosPhi = local.x * invZRad; sinPhi = local.y * invZRad; }
+		const V3 dv = v3(local.z * cosPhi, local.z * sinPhi, -mts_sin(theta) * radius) * MTS_PI;
+		dpdv = v3(r3.w * dv.x + r4.x * dv.y + r4.y * dv.z, r4.z * dv.x + r4.w * dv.y + r5.x * dv.z, r5.y * dv.x + r5.z * dv.y + r5.w * dv.z);
+	} else if (si.hasNormals && si.hasTangents) {
+		const uint32_t i0 = __float_as_uint(r2.w), i1 = __float_as_uint(r3.w), i2 = __float_as_uint(r4.w);
+		const float bx = 1 - bu - bv, by = bu, bz = bv;
+		dpdu = v3(__ldg(sc.tangents + 2 * i0)) * bx + v3(__ldg(sc.tangents + 2 * i1)) * by + v3(__ldg(sc.tangents + 2 * i2)) * bz;
+		dpdv = v3(__ldg(sc.tangents + 2 * i0 + 1)) * bx + v3(__ldg(sc.tangents + 2 * i1 + 1)) * by + v3(__ldg(sc.tangents + 2 * i2 + 1)) * bz;
+	}
+	if (isZero(dpdu) && isZero(dpdv)) return zero;
+	// ---- the offset rays
+	const CameraDev cam = *sc.camera;
+	V3 rxO, rxD, ryO, ryD; float mint, maxt;
+	cameraRay(cam, sx + 1, sy, lx, ly, rxO, rxD, mint, maxt);
+	cameraRay(cam, sx, sy + 1, lx, ly, ryO, ryD, mint, maxt);
+	// RayDifferential::scaleDifferential (core/ray.h:150-155) by 1 / sqrt(samples per pixel) (integrator.cpp:145,165)
+	rxO = rayO + (rxO - rayO) * diffScale; ryO = rayO + (ryO - rayO) * diffScale;
+	rxD = rayD + (rxD - rayD) * diffScale; ryD = rayD + (ryD - rayD) * diffScale;
+	// ---- Intersection::computePartials
+	const float d = -dot(geoN, p);
+	const float txRecip = dot(geoN, rxD), tyRecip = dot(geoN, ryD);
+	if (txRecip == 0 || tyRecip == 0) return zero;
+	const float tx = -(dot(geoN, rxO) + d) / txRecip;
+	const float ty = -(dot(geoN, ryO) + d) / tyRecip;
+	const float absX = fabsf(geoN.x), absY = fabsf(geoN.y), absZ = fabsf(geoN.z);
+	int a0, a1;
+	if (absX > absY && absX > absZ) { a0 = 1; a1 = 2; }
+	else if (absY > absZ) { a0 = 0; a1 = 2; }
+	else { a0 = 0; a1 = 1; }
+	auto comp = [](V3 v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); };
+	const float A00 = comp(dpdu, a0), A01 = comp(dpdv, a0), A10 = comp(dpdu, a1), A11 = comp(dpdv, a1);
+	const V3 px = rxO + rxD * tx, py = ryO + ryD * ty;
+	const float Bx0 = comp(px, a0) - comp(p, a0), Bx1 = comp(px, a1) - comp(p, a1);
+	const float By0 = comp(py, a0) - comp(p, a0), By1 = comp(py, a1) - comp(p, a1);
+	// solveLinearSystem2x2 (util.cpp:490-502)
+	const float det = A00 * A11 - A01 * A10;
+	float4 out;
+	if (fabsf(det) < MTS_EPSILON) {
+		// the fall-backs of intersection.cpp:64-74; its second one assigns dudy twice and leaves dvdy unset
+		// (left at 0 here)
+		out = make_float4(1, 1, 0, 0);
+	} else {
+		const float inverse = 1.0f / det;
+		out.x = (A11 * Bx0 - A01 * Bx1) * inverse;       // dudx
+		out.z = (A00 * Bx1 - A10 * Bx0) * inverse;       // dvdx
+		out.y = (A11 * By0 - A01 * By1) * inverse;       // dudy
+		out.w = (A00 * By1 - A10 * By0) * inverse;       // dvdy
+	}
+	return out;
+}
+
+__device__ inline bool usesRayDifferentials(const DeviceScene &sc, const MaterialDev &m) {
+	return (m.tex[0] && sc.textures[m.tex[0] - 1].type == MTSGPU_TEXTURE_BITMAP) || (m.tex[1] && sc.textures[m.tex[1] - 1].type == MTSGPU_TEXTURE_BITMAP);
+}
+
 // material with its textured slots replaced by their values at (u, v)
-__device__ inline void resolveTextures(const DeviceScene &sc, MaterialDev &m, float u, float v) {
+template <bool BMP = true>
+__device__ inline void resolveTextures(const DeviceScene &sc, MaterialDev &m, float u, float v, float4 duv = make_float4(0, 0, 0, 0)) {
 #pragma unroll
 	for (int k = 0; k < 2; ++k)
 		if (m.tex[k]) {
-			const V3 c = textureValue(sc.textures[m.tex[k] - 1], u, v);
+			const TextureDev &t = sc.textures[m.tex[k] - 1];
+			const V3 c = (BMP && t.type == MTSGPU_TEXTURE_BITMAP) ? bitmapValue(sc, t, u, v, duv) : textureValue(t, u, v);
 			m.p[3 * k] = c.x; m.p[3 * k + 1] = c.y; m.p[3 * k + 2] = c.z;
 		}
 }

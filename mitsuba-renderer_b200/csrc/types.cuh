@@ -73,9 +73,13 @@ struct DeviceScene {
 	const float4 *shadeTris;    // per sorted triangle, 6 x float4 (96 B = three 32-byte sectors): {p0, shape} {p1, prim}
 	                            // {p2, v0} {n0, v1} {n1, v2} {n2, -}: everything fillIntersection needs behind ONE index
 	const uint32_t *sortedOf;   // kd primitive order (ShapeInfo::triOffset + prim) -> sorted triangle index
-	const float4 *tangents;     // global vertex array of dpdu; only read for shapes with hasTangents
+	const float4 *tangents;     // global vertex array of {dpdu, dpdv} pairs; only read for shapes with hasTangents
 	const float2 *texcoords;    // global vertex array; only read for shapes with hasTexcoords
 	const TextureDev *textures;
+	const float4 *texels;       // mip pyramids of the bitmap textures (rgb + pad per texel)
+	const uint4 *mipLevels;     // {offset into texels, width, height, -} per level; TextureDev::pad = {first level, count}
+	const float *mipLut;        // MIPMap's EWA weight table, 128 entries
+	const struct CameraDev *camera;   // the render's camera: ray differentials of a camera-ray hit are rebuilt from it
 	const ShapeInfo *shapes;
 	const MaterialDev *materials;
 	const EmitterDev *emitters;

@@ -16,6 +16,7 @@
 #include <mitsuba/render/trimesh.h>
 #include <mitsuba/render/imageblock.h>
 #include <mitsuba/core/mstream.h>
+#include <mitsuba/core/bitmap.h>
 #include <mitsuba/core/statistics.h>
 #include <mitsuba/core/timer.h>
 #include <map>
@@ -106,9 +107,12 @@ private:
 	 * writes id + class + payload the first time it meets an object and only the id afterwards,
 	 * serialization.cpp:73-87), the textures collected for the C ABI, and which id became which slot value. */
 	struct TexValue { float rgb[3]; uint32_t texture; };
+	/* pixels of a bitmap texture, decoded by the host's own Bitmap codecs, waiting for mtsgpu_upload_bitmap */
+	struct BitmapUpload { int texture; ref<Bitmap> bitmap; float gamma; };
 	struct Decoder {
 		Stream *s; unsigned int maxId;
 		std::vector<mtsgpu_texture> *textures;
+		std::vector<BitmapUpload> *bitmaps;
 		std::map<unsigned int, TexValue> seen;
 	};
 
@@ -122,7 +126,8 @@ private:
 		decodePayload(cls, d);
 	}
 
-	/* One spectrum slot: a ConstantSpectrumTexture (texture.cpp:84-93) or a Checkerboard (checkerboard.cpp:35-45) */
+	/* One spectrum slot: a ConstantSpectrumTexture (texture.cpp:84-93), a Checkerboard (checkerboard.cpp:35-45) or an
+	 * LDRTexture (ldrtexture.cpp:209-228) */
 	static void readTextureSlot(Decoder &d, float *rgb, uint32_t &texture) {
 		Stream *s = d.s;
 		const unsigned int id = s->readUInt();
@@ -146,8 +151,30 @@ private:
 				t.p[6] = uvOffset.x; t.p[7] = uvOffset.y; t.p[8] = uvScale.x; t.p[9] = uvScale.y;
 				d.textures->push_back(t);
 				v.texture = (uint32_t) d.textures->size();
+			} else if (cls == "LDRTexture") {
+				/* ldrtexture.cpp:209-228: Texture2D, file name, gamma, codec, filter, wrap mode, max. anisotropy, then the
+				 * image file itself — decoded here by the host's Bitmap class, exactly as LDRTexture's own
+				 * unserialising constructor does (ldrtexture.cpp:86-100) */
+				mtsgpu_texture t; memset(&t, 0, sizeof(t));
+				t.type = MTSGPU_TEXTURE_BITMAP;
+				Point2 uvOffset(s); Vector2 uvScale(s);
+				s->readString();
+				BitmapUpload up;
+				up.gamma = s->readFloat();
+				const Bitmap::EFileFormat format = static_cast<Bitmap::EFileFormat>(s->readInt());
+				t.p[0] = (float) s->readInt(); t.p[1] = (float) s->readUInt(); t.p[2] = s->readFloat();
+				t.p[6] = uvOffset.x; t.p[7] = uvOffset.y; t.p[8] = uvScale.x; t.p[9] = uvScale.y;
+				const uint32_t size = s->readUInt();
+				ref<MemoryStream> file = new MemoryStream(size);
+				s->copyTo(file, size);
+				file->setPos(0);
+				up.bitmap = new Bitmap(format, file);
+				d.textures->push_back(t);
+				v.texture = (uint32_t) d.textures->size();
+				up.texture = (int) d.textures->size() - 1;
+				d.bitmaps->push_back(up);
 			} else {
-				SLog(EError, "gpupath: texture class \"%s\" is outside the supported hot path (constant spectra, checkerboard)", cls.c_str());
+				SLog(EError, "gpupath: texture class \"%s\" is outside the supported hot path (constant spectra, checkerboard, ldrtexture)", cls.c_str());
 			}
 			d.seen[id] = v;
 		}
@@ -297,7 +324,8 @@ private:
 		shape->setParent(parent);
 		s->setPos(0);
 		std::vector<mtsgpu_texture> scratch;
-		Decoder d; d.s = s; d.textures = &scratch;
+		std::vector<BitmapUpload> scratchBitmaps;
+		Decoder d; d.s = s; d.textures = &scratch; d.bitmaps = &scratchBitmaps;
 		d.maxId = s->readUInt();
 		s->readString();
 		readParent(d);
@@ -333,12 +361,12 @@ private:
 		return out;
 	}
 
-	static mtsgpu_material decodeBSDF(const BSDF *bsdf, std::vector<mtsgpu_texture> &textures) {
+	static mtsgpu_material decodeBSDF(const BSDF *bsdf, std::vector<mtsgpu_texture> &textures, std::vector<BitmapUpload> &bitmaps) {
 		ref<MemoryStream> s = new MemoryStream();
 		ref<InstanceManager> mgr = new InstanceManager();
 		mgr->serialize(s, bsdf);
 		s->setPos(0);
-		Decoder d; d.s = s; d.maxId = 0; d.textures = &textures;
+		Decoder d; d.s = s; d.maxId = 0; d.textures = &textures; d.bitmaps = &bitmaps;
 		d.maxId = s->readUInt();
 		const std::string cls = s->readString();
 		return decodePayload(cls, d);
@@ -362,6 +390,7 @@ private:
 		const std::vector<Luminaire *> &luminaires = scene->getLuminaires();
 		std::vector<mtsgpu_material> materials;
 		std::vector<mtsgpu_texture> textures;
+		std::vector<BitmapUpload> bitmaps;
 		std::map<const BSDF *, int> materialIds;
 		std::vector<mtsgpu_emitter> emitters(luminaires.size());
 		std::map<const Luminaire *, int> emitterIds;
@@ -393,7 +422,7 @@ private:
 				const BSDF *bsdf = shape->getBSDF();
 				if (!materialIds.count(bsdf)) {
 					materialIds[bsdf] = (int) materials.size();
-					materials.push_back(decodeBSDF(bsdf, textures));
+					materials.push_back(decodeBSDF(bsdf, textures, bitmaps));
 				}
 				r.mat = materialIds[bsdf];
 			}
@@ -404,6 +433,17 @@ private:
 		for (size_t g = 0; g < ctxs.size(); ++g) {       /* the scene is replicated on every GPU */
 			mtsgpu_ctx *c = ctxs[g];
 			check(c, mtsgpu_upload_textures(c, textures.empty() ? NULL : &textures[0], (int) textures.size()));
+			for (size_t i = 0; i < bitmaps.size(); ++i) {
+				const Bitmap *bmp = bitmaps[i].bitmap;
+				const int bpp = bmp->getBitsPerPixel(), w = bmp->getWidth(), h = bmp->getHeight();
+				if (bpp == 1) {                     /* ldrtexture.cpp:185-199: bit k of byte k / 8, set -> 255 */
+					std::vector<uint8_t> bytes((size_t) w * h);
+					for (size_t k = 0; k < bytes.size(); ++k) bytes[k] = (bmp->getData()[k / 8] & (1 << (k % 8))) ? 255 : 0;
+					check(c, mtsgpu_upload_bitmap(c, bitmaps[i].texture, w, h, 1, &bytes[0], MTSGPU_BITMAP_U8, bitmaps[i].gamma));
+				} else {
+					check(c, mtsgpu_upload_bitmap(c, bitmaps[i].texture, w, h, bpp / 8, bmp->getData(), MTSGPU_BITMAP_U8, bitmaps[i].gamma));
+				}
+			}
 			check(c, mtsgpu_upload_materials(c, materials.empty() ? NULL : &materials[0], (int) materials.size()));
 			check(c, mtsgpu_upload_emitters(c, emitters.empty() ? NULL : &emitters[0], (int) emitters.size()));
 			for (size_t i = 0; i < meshes.size(); ++i) {

@@ -36,12 +36,29 @@ class Material:
 
 @dataclass
 class Texture:
-    """2D texture; `p` uses the layout of `mtsgpu_texture` (include/mtsgpu.h)."""
+    """2D texture; `p` uses the layout of `mtsgpu_texture` (include/mtsgpu.h). A bitmap texture also carries its
+    pixels (uint8 [height, width, 3], top row first) and the gamma of LDRTexture (-1: sRGB)."""
     type: int
     p: np.ndarray  # float32[12]
+    pixels: Optional[np.ndarray] = None
+    gamma: float = -1.0
 
 
 TEX_CHECKERBOARD = 0
+TEX_BITMAP = 1
+MIP_EWA, MIP_TRILINEAR, MIP_NONE = 0, 1, 2                 # MIPMap::EFilterType (mipmap.h:39-46)
+WRAP_REPEAT, WRAP_BLACK, WRAP_WHITE, WRAP_CLAMP = 0, 1, 2, 3   # MIPMap::EWrapMode (mipmap.h:32-37)
+
+
+def bitmap_texture(pixels, gamma=-1.0, filter_type=MIP_EWA, wrap_mode=WRAP_REPEAT, max_anisotropy=8.0,
+                   uscale=1.0, vscale=1.0, uoffset=0.0, voffset=0.0):
+    """<texture type="ldrtexture"> (src/textures/ldrtexture.cpp:37-84): gamma-corrected 8-bit RGB bitmap behind a MIPMap."""
+    pixels = np.ascontiguousarray(pixels, np.uint8)
+    assert pixels.ndim == 3 and pixels.shape[2] == 3
+    p = np.zeros(12, np.float32)
+    p[:3] = [filter_type, wrap_mode, max_anisotropy]
+    p[6:10] = [uoffset, voffset, uscale, vscale]
+    return Texture(TEX_BITMAP, p, pixels, float(gamma))
 
 
 def checkerboard(bright=(0.4, 0.4, 0.4), dark=(0.2, 0.2, 0.2), uscale=1.0, vscale=1.0, uoffset=0.0, voffset=0.0):
@@ -360,7 +377,7 @@ def write_scene(path: str, scene: SceneDesc) -> None:
     cx, cy, cw, ch = scene.crop_rect
     with open(path, "wb") as f:
         f.write(b"MTSB200\0")
-        f.write(struct.pack("<I", 5))
+        f.write(struct.pack("<I", 6))
         f.write(np.ascontiguousarray(scene.camera_to_world, np.float32).tobytes())
         f.write(struct.pack("<5fI", scene.fov, scene.near_clip, scene.far_clip, scene.aperture_radius,
                             scene.focus_depth, int(scene.map_smaller_side)))
@@ -372,6 +389,9 @@ def write_scene(path: str, scene: SceneDesc) -> None:
         for t in scene.textures:
             f.write(struct.pack("<I", t.type))
             f.write(np.ascontiguousarray(t.p, np.float32).tobytes())
+            if t.type == TEX_BITMAP:
+                f.write(struct.pack("<f2I", t.gamma, t.pixels.shape[1], t.pixels.shape[0]))
+                f.write(t.pixels.tobytes())
         f.write(struct.pack("<I", len(scene.materials)))
         for m in scene.materials:
             f.write(struct.pack("<I", m.type))

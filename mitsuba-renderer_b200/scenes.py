@@ -9,7 +9,8 @@ import numpy as np
 
 from .scenefile import (SceneDesc, Shape, Emitter, lambertian, microfacet, mirror, roughmetal,
                         dielectric, twosided, phong, roughglass, look_at, point_light, spot_light, directional_light,
-                        constant_light, add_light, checkerboard, textured, ward, sphere_shape, MODE_PATH, MODE_DIRECT, FILTER_BOX)
+                        constant_light, add_light, checkerboard, textured, ward, sphere_shape, bitmap_texture, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
+                        WRAP_REPEAT, WRAP_BLACK, WRAP_WHITE, WRAP_CLAMP, MODE_PATH, MODE_DIRECT, FILTER_BOX)
 
 F32 = np.float32
 
@@ -165,6 +166,37 @@ def spheres_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6)
     s.shapes.append(sphere_shape((2.9, 0.5, 0.4), 0.5, material=tex_ball))
     s.shapes.append(sphere_shape((1.6, 4.6, 4.4), 0.7, material=len(m) - 3))      # anisotropic ward (index 11)
     s.shapes.append(sphere_shape((4.6, 4.4, 4.6), 0.8, material=0, inverted=True))
+    return s
+
+
+def _test_image(width, height, seed):
+    """A deterministic 8-bit RGB image with structure at every scale: stripes, a gradient and per-texel noise."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    y, x = np.mgrid[0:height, 0:width]
+    img = np.empty((height, width, 3), np.float64)
+    img[..., 0] = 0.5 + 0.5 * np.sin(x * 2 * np.pi * 3 / width + seed)
+    img[..., 1] = (x + y) / float(width + height)
+    img[..., 2] = ((x // 2 + y // 2) % 2) * 0.8 + 0.1
+    img = 0.75 * img + 0.25 * rng.random((height, width, 3))
+    return np.clip(img * 255.0, 0, 255).astype(np.uint8)
+
+
+def bitmap_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6) -> SceneDesc:
+    """The sphere scene with bitmap textures (src/textures/ldrtexture.cpp over src/librender/mipmap.cpp) in place of the
+    checkerboards: an EWA-filtered 64 x 32 image on the walls (seen at grazing angles), a trilinear 20 x 24 image (not a
+    power of two: Lanczos up-sampling) with `clamp` wrapping and gamma 2.2, an unfiltered 16 x 8 image, an EWA image
+    with `black` wrapping inside the inverted sphere, and one remaining checkerboard."""
+    s = spheres_test_scene(width, height, spp, mode, max_depth)
+    t = s.textures
+    green_wall = t[0]
+    t[0] = bitmap_texture(_test_image(64, 32, 1), uscale=2.0, vscale=2.0)
+    t[1] = bitmap_texture(_test_image(20, 24, 2), gamma=2.2, filter_type=MIP_TRILINEAR, wrap_mode=WRAP_CLAMP,
+                          uscale=0.3, vscale=0.25, uoffset=0.05, voffset=-0.1)
+    t[2] = bitmap_texture(_test_image(16, 8, 3), filter_type=MIP_NONE, uscale=6.0, vscale=6.0, uoffset=0.1, voffset=0.1)
+    t.append(bitmap_texture(_test_image(32, 32, 4), wrap_mode=WRAP_BLACK, max_anisotropy=4.0, uscale=1.5, vscale=1.2))
+    t.append(green_wall)
+    s.materials[0] = textured(s.materials[0], 0, 3)
+    s.materials[2] = textured(s.materials[2], 0, 4)
     return s
 
 

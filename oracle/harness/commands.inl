@@ -330,8 +330,38 @@ static int cmdUv(int argc, char **argv) {
 	return 0;
 }
 
+/* samples: [x, y, lens.x, lens.y] -> 12 floats: its.uv, dudx, dudy, dvdx, dvdy, diffuse and specular reflectance at
+ * the hit of the camera's ray differential (integrator.cpp:163 -> path.cpp:70: its.getBSDF(ray) runs
+ * Intersection::computePartials when a texture of the BSDF filters) */
+static int cmdTexLookup(int argc, char **argv) {
+	if (argc < 5) { std::cerr << "texlookup SCENE SAMPLES OUT\n"; return 1; }
+	sio::Scene sf; sio::load(argv[2], sf);
+	std::vector<float> q = sio::loadFloats(argv[3]);
+	const size_t n = q.size() / 4;
+	Built b = buildScene(sf, "");
+	const Camera *camera = b.scene->getCamera();
+	std::vector<float> out(n * 12, 0.0f);
+	for (size_t i = 0; i < n; ++i) {
+		const float *e = &q[i * 4];
+		RayDifferential ray;
+		camera->generateRayDifferential(Point2(e[0], e[1]), Point2(e[2], e[3]), 0.0f, ray);
+		ray.scaleDifferential(1.0f / std::sqrt((Float) sf.spp));        /* SampleIntegrator::renderBlock, integrator.cpp:145,165 */
+		Intersection its;
+		if (!b.scene->rayIntersect(ray, its)) continue;
+		float *o = &out[i * 12];
+		o[0] = its.uv.x; o[1] = its.uv.y;
+		const BSDF *bsdf = its.getBSDF(ray);
+		if (!bsdf) continue;
+		if (its.hasUVPartials) { o[2] = its.dudx; o[3] = its.dudy; o[4] = its.dvdx; o[5] = its.dvdy; }
+		bsdf->getDiffuseReflectance(its).toLinearRGB(o[6], o[7], o[8]);
+	}
+	sio::save(argv[4], out.data(), out.size() * 4);
+	printf("{\"cmd\": \"texlookup\", \"samples\": %zu}\n", n);
+	return 0;
+}
+
 static int dispatch(int argc, char **argv) {
-	if (argc < 2) { std::cerr << "usage: mts_oracle trace|triaccel|bsdf|emitter|camera|splat|render|mesh|meshsave|develop|uv ...\n"; return 1; }
+	if (argc < 2) { std::cerr << "usage: mts_oracle trace|triaccel|bsdf|emitter|camera|splat|render|mesh|meshsave|develop|uv|texlookup ...\n"; return 1; }
 	std::string cmd = argv[1];
 	if (cmd == "trace") return cmdTraceImpl(argc, argv);
 	if (cmd == "triaccel") return cmdTriAccel(argc, argv);
@@ -344,6 +374,7 @@ static int dispatch(int argc, char **argv) {
 	if (cmd == "meshsave") return cmdMeshSave(argc, argv);
 	if (cmd == "develop") return cmdDevelop(argc, argv);
 	if (cmd == "uv") return cmdUv(argc, argv);
+	if (cmd == "texlookup") return cmdTexLookup(argc, argv);
 	std::cerr << "unknown command " << cmd << "\n";
 	return 1;
 }

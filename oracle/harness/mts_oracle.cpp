@@ -109,6 +109,43 @@ static const std::vector<sio::Texture> *g_textures = NULL;   /* texture table of
 
 /* <texture type="checkerboard"> (src/textures/checkerboard.cpp:30-33, src/librender/texture.cpp:43-56) */
 static ref<Texture> makeTexture(const sio::Texture &t) {
+	if (t.type == 1) {
+		/* <texture type="ldrtexture"> reading a 24-bit BMP file written here from the scene file's pixels
+		 * (src/textures/ldrtexture.cpp:37-84) */
+		static int serial = 0;
+		char path[256];
+		snprintf(path, sizeof(path), "/tmp/mts_oracle_tex_%d_%d.bmp", (int) getpid(), serial++);
+		const uint32_t line = t.width * 3, padded = (line + 3) & ~3u, dataSize = padded * t.height;
+		std::vector<uint8_t> file(54 + dataSize, 0);
+		auto put32 = [&](size_t at, uint32_t v) { for (int k = 0; k < 4; ++k) file[at + k] = (uint8_t) (v >> (8 * k)); };
+		file[0] = 'B'; file[1] = 'M'; put32(2, (uint32_t) file.size()); put32(10, 54);
+		put32(14, 40); put32(18, t.width); put32(22, t.height); file[26] = 1; file[28] = 24; put32(34, dataSize);
+		for (uint32_t y = 0; y < t.height; ++y)               /* bottom-up rows, BGR */
+			for (uint32_t x = 0; x < t.width; ++x)
+				for (int c = 0; c < 3; ++c)
+					file[54 + (size_t) (t.height - 1 - y) * padded + 3 * x + c] = t.pixels[((size_t) y * t.width + x) * 3 + (2 - c)];
+		FILE *f = fopen(path, "wb");
+		if (!f || fwrite(file.data(), 1, file.size(), f) != file.size()) SLog(EError, "cannot write %s", path);
+		fclose(f);
+		static const char *filters[3] = { "ewa", "trilinear", "none" };
+		static const char *wraps[4] = { "repeat", "black", "white", "clamp" };
+		Properties p("ldrtexture");
+		p.setString("filename", path);
+		p.setFloat("gamma", t.gamma);
+		p.setString("filterType", filters[(int) t.p[0]]);
+		p.setString("wrapMode", wraps[(int) t.p[1]]);
+		p.setFloat("maxAnisotropy", t.p[2]);
+		p.setFloat("uoffset", t.p[6]); p.setFloat("voffset", t.p[7]);
+		p.setFloat("uscale", t.p[8]); p.setFloat("vscale", t.p[9]);
+		ref<Texture> tex = static_cast<Texture *>(create(MTS_CLASS(Texture), p));
+		tex->configure();
+		/* LDRTexture::serialize re-reads the file (ldrtexture.cpp:218-227; the gpupath plugin goes through it), so the
+		 * file stays until the process ends */
+		static std::vector<std::string> files;
+		if (files.empty()) atexit([]() { for (size_t k = 0; k < files.size(); ++k) remove(files[k].c_str()); });
+		files.push_back(path);
+		return tex;
+	}
 	if (t.type != 0) SLog(EError, "unknown texture type %u", t.type);
 	Properties p("checkerboard");
 	p.setSpectrum("brightColor", rgb(t.p));

@@ -14,7 +14,7 @@ namespace sio {
 enum MaterialType { MAT_LAMBERTIAN = 0, MAT_MICROFACET = 1, MAT_MIRROR = 2, MAT_ROUGHMETAL = 3, MAT_DIELECTRIC = 4 };
 
 struct Material { uint32_t type; float p[16]; uint32_t tex[2]; };
-struct Texture  { uint32_t type; float p[12]; };
+struct Texture  { uint32_t type; float p[12]; float gamma; uint32_t width, height; std::vector<uint8_t> pixels; /* bitmap: RGB, top row first */ };
 struct Emitter  { float intensity[3]; float samplingWeight; uint32_t type; float p[11]; float aux[16]; };
 struct Shape {
 	uint32_t kind;   /* 0 triangle mesh, 1 analytic sphere */
@@ -50,7 +50,7 @@ inline void load(const std::string &path, Scene &s) {
 	Reader r(path);
 	char magic[8]; r.raw(magic, 8);
 	if (memcmp(magic, "MTSB200", 8) != 0) throw std::runtime_error("bad magic in " + path);
-	if (r.get<uint32_t>() != 5) throw std::runtime_error("bad version in " + path);
+	if (r.get<uint32_t>() != 6) throw std::runtime_error("bad version in " + path);
 	r.raw(s.cameraToWorld, 64);
 	s.fov = r.get<float>(); s.nearClip = r.get<float>(); s.farClip = r.get<float>();
 	s.apertureRadius = r.get<float>(); s.focusDepth = r.get<float>();
@@ -64,7 +64,14 @@ inline void load(const std::string &path, Scene &s) {
 	s.strictNormals = r.get<uint32_t>(); s.nLumSamples = r.get<uint32_t>(); s.nBsdfSamples = r.get<uint32_t>();
 	s.samplerType = r.get<uint32_t>(); s.samplerDepth = r.get<uint32_t>();
 	s.textures.resize(r.get<uint32_t>());
-	for (auto &t : s.textures) { t.type = r.get<uint32_t>(); r.raw(t.p, 48); }
+	for (auto &t : s.textures) {
+		t.type = r.get<uint32_t>(); r.raw(t.p, 48);
+		t.gamma = -1.0f; t.width = t.height = 0;
+		if (t.type == 1) {
+			t.gamma = r.get<float>(); t.width = r.get<uint32_t>(); t.height = r.get<uint32_t>();
+			t.pixels.resize((size_t) t.width * t.height * 3); r.raw(t.pixels.data(), t.pixels.size());
+		}
+	}
 	s.materials.resize(r.get<uint32_t>());
 	for (auto &m : s.materials) { m.type = r.get<uint32_t>(); r.raw(m.p, 64); r.raw(m.tex, 8); }
 	s.emitters.resize(r.get<uint32_t>());

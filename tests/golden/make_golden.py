@@ -63,6 +63,10 @@ def main():
     tsess = oracle_util.Session(ts)
     thits, tfull, _ = tsess.trace(rays, "closest_full")       # `wi` in the tangent frames of the anisotropic Ward meshes
     save("uv_textured", rays_digest=gc.digest(rays), out=tsess.uv(rays), hits=thits.view(np.uint8), full=tfull)
+    # ---- bitmap textures filtered with the uv partials of the camera's ray differentials -------------------------------------
+    bs_ = gc.scene_bitmaps()
+    q = gc.lens_camera_samples(bs_, 6000, 31)
+    save("texlookup_bitmaps", samples_digest=gc.digest(q), out=oracle_util.Session(bs_).texlookup(q))
     # ---- deterministic render: halton sampler (the same sample values on every pixel, no random state) ----------------------
     hs = gc.scene_halton()
     save("render_halton", film=oracle_util.Session(hs).render()[0])

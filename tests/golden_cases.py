@@ -216,3 +216,18 @@ def diffuse_reflectance_from_slots(scene, hits, slots):
         elif t in (1, 5, 7):
             out[i] = (slots[i] * np.float32(m.p[6])).astype(np.float32)
     return out
+
+
+def scene_bitmaps():
+    s = scenes.bitmap_test_scene(64, 64, 4)
+    s.aperture_radius = 0.05; s.focus_depth = 6.0
+    return s
+
+
+def lens_camera_samples(scene, n, seed):
+    """rows {raster x, raster y, lens x, lens y}"""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    q = np.empty((n, 4), np.float32)
+    q[:, 0] = rng.random(n) * scene.width; q[:, 1] = rng.random(n) * scene.height
+    q[:, 2:] = rng.random((n, 2))
+    return q

@@ -127,6 +127,12 @@ class Session:
         out, _ = self._io("uv", np.ascontiguousarray(rays, np.float32).reshape(-1, 8))
         return np.fromfile(out, np.float32).reshape(-1, 5)
 
+    def texlookup(self, samples):
+        """rows {its.uv, dudx, dudy, dvdx, dvdy, BSDF::getDiffuseReflectance(its), 0 0 0} at the hit of the camera's
+        ray differential through raster position / lens sample {x, y, lx, ly}; zeros on a miss."""
+        out, _ = self._io("texlookup", np.ascontiguousarray(samples, np.float32).reshape(-1, 4))
+        return np.fromfile(out, np.float32).reshape(-1, 12)
+
     def emitter(self, queries):
         out, _ = self._io("emitter", queries)
         return np.fromfile(out, np.float32).reshape(-1, 16)

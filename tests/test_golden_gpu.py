@@ -160,3 +160,23 @@ def test_render_matches_golden_reference_image(gpu_ctx_factory):
     gpu_hi, _ = ctx.render(Context.params_from_scene(hi, seed=2))
     assert abs(dev(gpu_hi).mean() - ref.mean()) <= 0.01 * ref.mean()
     assert rel(dev(gpu_hi)) < 0.2 * rel(dev(g["cpu_64"]))
+
+
+def test_filtered_bitmap_lookups_match_golden(gpu_ctx_factory):
+    """ldrtexture.cpp / mipmap.cpp lookups (EWA, trilinear, unfiltered; repeat, clamp, black) with the uv partials of
+    intersection.cpp:5-75 at camera-ray hits, thin lens on, differentials narrowed for 4 samples per pixel."""
+    scene = gc.scene_bitmaps()
+    g = gold("texlookup_bitmaps")
+    q = gc.lens_camera_samples(scene, 6000, 31)
+    assert gc.digest(q) == str(g["samples_digest"])
+    ctx = gpu_ctx_factory(scene)
+    got, ref = ctx.texture_lookup(q, scene.spp), g["out"]
+    hits = ctx.trace(ctx.camera_rays(q), TRACE_CLOSEST)
+    hit = hits["shape"] != 0xFFFFFFFF
+    assert hit.sum() > 5000 and close(got[hit, :2], ref[hit, :2], 2e-5, 2e-6).all()
+    scale = np.abs(ref[:, 2:6]).max(axis=1, keepdims=True)
+    assert (scale > 0).mean() > 0.5
+    assert (np.abs(got[:, 2:6] - ref[:, 2:6]) <= 1e-4 * (scale + 1e-3)).all()
+    want = gc.diffuse_reflectance_from_slots(scene, hits, got[:, 6:9])
+    err = np.abs(want - ref[:, 6:9]).max(axis=1)
+    assert (err > 1e-5).sum() <= 6 and np.median(err) < 1e-7, ((err > 1e-5).sum(), err.max())
