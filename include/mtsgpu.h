@@ -113,10 +113,15 @@ typedef struct mtsgpu_texture {
  *                                                      from the scene's bounding sphere as preprocess() does
  *   CONSTANT     src/luminaires/constant.cpp:27-86     background; p[0..2] centre and p[3] radius of its bounding
  *                                                      sphere; radius 0 = derive it as preprocess() does (scene
- *                                                      sphere x 1.01, grown to hold the camera). At most one. */
+ *                                                      sphere x 1.01, grown to hold the camera). At most one.
+ *   ENVMAP       src/luminaires/envmap.cpp:38-199      background from a latitude-longitude map, importance-sampled
+ *                                                      through a coarse MIP level; p[0..3] bounding sphere as for
+ *                                                      CONSTANT, p[4] intensityScale; intensity unused. The map and
+ *                                                      its transform follow through mtsgpu_upload_envmap. CONSTANT and
+ *                                                      ENVMAP exclude each other (one background luminaire). */
 enum mtsgpu_emitter_type {
 	MTSGPU_EMITTER_AREA = 0, MTSGPU_EMITTER_POINT = 1, MTSGPU_EMITTER_SPOT = 2, MTSGPU_EMITTER_DIRECTIONAL = 3,
-	MTSGPU_EMITTER_CONSTANT = 4
+	MTSGPU_EMITTER_CONSTANT = 4, MTSGPU_EMITTER_ENVMAP = 5
 };
 typedef struct mtsgpu_emitter {
 	float intensity[3];
@@ -210,6 +215,12 @@ MTSGPU_API int mtsgpu_upload_textures(mtsgpu_ctx *ctx, const mtsgpu_texture *tex
  * MIPMap::MIPMap (src/librender/mipmap.cpp:31-137: Lanczos up-sampling to powers of two, box-filtered levels). */
 MTSGPU_API int mtsgpu_upload_bitmap(mtsgpu_ctx *ctx, int textureIndex, int width, int height, int channels,
 	const void *pixels, int format, float gamma);
+/* The map of ENVMAP luminaire `emitterIndex` (after mtsgpu_upload_emitters, before mtsgpu_build_accel): `channels` (3 or
+ * 4) linear floats per pixel, top row first, as Bitmap::loadEXR hands them to MIPMap::fromBitmap
+ * (src/luminaires/envmap.cpp:44-47; EWA pyramid, `repeat` wrapping), and the luminaire's toWorld transform with its
+ * inverse (Luminaire::m_luminaireToWorld / m_worldToLuminaire; only the 3x3 parts are used, on directions). */
+MTSGPU_API int mtsgpu_upload_envmap(mtsgpu_ctx *ctx, int emitterIndex, int width, int height, int channels,
+	const float *pixels, const float luminaireToWorld[16], const float worldToLuminaire[16]);
 MTSGPU_API int mtsgpu_upload_emitters(mtsgpu_ctx *ctx, const mtsgpu_emitter *emitters, int count);
 
 /* One TriMesh (include/mitsuba/render/trimesh.h:100-133) at kd-tree shape index `shapeIndex`

@@ -29,7 +29,7 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_film_splat_static", "mtsgpu_render_multi", "mtsgpu_serialized_count", "mtsgpu_serialized_load",
     "mtsgpu_serialized_free", "mtsgpu_serialized_save", "mtsgpu_upload_serialized", "mtsgpu_film_develop",
     "mtsgpu_film_develop_device", "mtsgpu_film_save", "mtsgpu_write_exr", "mtsgpu_write_mfilm", "mtsgpu_sampler_values",
-    "mtsgpu_upload_textures", "mtsgpu_intersect_uv", "mtsgpu_upload_sphere", "mtsgpu_upload_bitmap", "mtsgpu_texture_lookup",
+    "mtsgpu_upload_textures", "mtsgpu_intersect_uv", "mtsgpu_upload_sphere", "mtsgpu_upload_bitmap", "mtsgpu_texture_lookup", "mtsgpu_upload_envmap",
 ]
 SAMPLER_INDEPENDENT, SAMPLER_LD, SAMPLER_STRATIFIED, SAMPLER_HALTON = 0, 1, 2, 3
 FILM_EXR, FILM_M = 0, 1
@@ -108,6 +108,7 @@ def load_library(path: Optional[str] = None):
     lib.mtsgpu_upload_emitters.argtypes = [vp, C.POINTER(Emitter), C.c_int]
     lib.mtsgpu_upload_textures.argtypes = [vp, C.POINTER(Texture), C.c_int]
     lib.mtsgpu_intersect_uv.argtypes = [vp, vp, C.c_size_t, vp]
+    lib.mtsgpu_upload_envmap.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp]
     lib.mtsgpu_upload_bitmap.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_float]
     lib.mtsgpu_upload_sphere.argtypes = [vp, C.c_int, vp, vp, C.c_float, vp, C.c_int, C.c_int, C.c_int]
     lib.mtsgpu_upload_mesh.argtypes = [vp, C.c_int, vp, vp, vp, C.c_uint32, vp, C.c_uint32, C.c_int, C.c_int]
@@ -249,6 +250,14 @@ class Context:
             ems[i].type = e.type
             ems[i].p[:] = [float(v) for v in e.abi_params()]
         self._check(self.lib.mtsgpu_upload_emitters(self.h, ems, len(scene.emitters)))
+        for i, e in enumerate(scene.emitters):
+            if e.pixels is not None:               # environment map: toWorld and its fp32 Gauss-Jordan inverse (Transform(Matrix4x4))
+                from .scenefile import invert4_f32
+                l2w = np.ascontiguousarray(np.asarray(e.aux, np.float32).reshape(4, 4))
+                w2l = np.ascontiguousarray(invert4_f32(l2w))
+                px = np.ascontiguousarray(e.pixels, np.float32)
+                self._check(self.lib.mtsgpu_upload_envmap(self.h, i, px.shape[1], px.shape[0], px.shape[2], self._ptr(px),
+                                                          self._ptr(l2w), self._ptr(w2l)))
         for i, s in enumerate(scene.shapes):
             if s.sphere is not None:                # center + radius: objectToWorld = translate(center) (sphere.cpp:44-47)
                 center, radius, inverted = s.sphere

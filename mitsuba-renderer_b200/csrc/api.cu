@@ -140,13 +140,32 @@ int mtsgpu_upload_emitters(mtsgpu_ctx *ctx, const mtsgpu_emitter *emitters, int 
 	REQUIRE(ctx, count >= 0 && (count == 0 || emitters), MTSGPU_ERR_ARG, "upload_emitters: bad arguments");
 	int backgrounds = 0;
 	for (int i = 0; i < count; ++i) {
-		REQUIRE(ctx, emitters[i].type <= MTSGPU_EMITTER_CONSTANT, MTSGPU_ERR_UNSUPPORTED, "emitter %d: unsupported luminaire type %u", i, emitters[i].type);
+		REQUIRE(ctx, emitters[i].type <= MTSGPU_EMITTER_ENVMAP, MTSGPU_ERR_UNSUPPORTED, "emitter %d: unsupported luminaire type %u", i, emitters[i].type);
 		if (emitters[i].type == MTSGPU_EMITTER_SPOT)      // Assert(m_cutoffAngle >= m_beamWidth), spot.cpp:42
 			REQUIRE(ctx, emitters[i].p[7] >= emitters[i].p[6], MTSGPU_ERR_ARG, "emitter %d: cutoffAngle must be >= beamWidth", i);
-		backgrounds += emitters[i].type == MTSGPU_EMITTER_CONSTANT;
+		backgrounds += emitters[i].type == MTSGPU_EMITTER_CONSTANT || emitters[i].type == MTSGPU_EMITTER_ENVMAP;
 	}
 	REQUIRE(ctx, backgrounds <= 1, MTSGPU_ERR_UNSUPPORTED, "upload_emitters: at most one background luminaire");
 	ctx->emitters.assign(emitters, emitters + count);
+	ctx->envEmitter = -1; ctx->envBitmap = HostBitmap();
+	ctx->built = false;
+	return MTSGPU_OK;
+}
+
+int mtsgpu_upload_envmap(mtsgpu_ctx *ctx, int emitterIndex, int width, int height, int channels, const float *pixels,
+		const float luminaireToWorld[16], const float worldToLuminaire[16]) {
+	ENTER(ctx);
+	REQUIRE(ctx, emitterIndex >= 0 && (size_t) emitterIndex < ctx->emitters.size() && ctx->emitters[emitterIndex].type == MTSGPU_EMITTER_ENVMAP,
+		MTSGPU_ERR_ARG, "upload_envmap: emitter %d is not an environment map of the uploaded table", emitterIndex);
+	REQUIRE(ctx, pixels && luminaireToWorld && worldToLuminaire && width > 0 && height > 0 && width <= 16384 && height <= 16384 && (channels == 3 || channels == 4),
+		MTSGPU_ERR_ARG, "upload_envmap: bad arguments");
+	HostBitmap &b = ctx->envBitmap;
+	const size_t n = (size_t) width * height;
+	b.rgb.resize(3 * n);
+	for (size_t i = 0; i < n; ++i) for (int c = 0; c < 3; ++c) b.rgb[3 * i + c] = pixels[i * channels + c];
+	b.width = width; b.height = height;
+	for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) { ctx->envL2W[3 * r + c] = luminaireToWorld[4 * r + c]; ctx->envW2L[3 * r + c] = worldToLuminaire[4 * r + c]; }
+	ctx->envEmitter = emitterIndex;
 	ctx->built = false;
 	return MTSGPU_OK;
 }

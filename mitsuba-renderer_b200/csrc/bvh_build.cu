@@ -488,6 +488,8 @@ static float buildCdf(const std::vector<float> &pdf, std::vector<float> &cdf) {
 
 // Luminaire-selection CDF (Scene::initialize, scene.cpp:320-330): weights are the luminaires'
 // samplingWeight when importanceSampleLuminaires is set (the default), else 1 each.
+static inline float __uint_as_float_host(uint32_t v) { float f; memcpy(&f, &v, 4); return f; }
+
 int rebuildLuminaireCdf(mtsgpu_ctx *ctx, bool importance) {
 	if (ctx->lumImportance == (int) importance) return MTSGPU_OK;
 	cudaStream_t st = ctx->stream;
@@ -531,6 +533,10 @@ int rebuildLuminaireCdf(mtsgpu_ctx *ctx, bool importance) {
 				memcpy(em.p, src.p, 16);
 				if (src.p[3] == 0.0f) em.p[3] = radius;
 				break;
+			case MTSGPU_EMITTER_ENVMAP:            // EnvMapLuminaire::preprocess (envmap.cpp:112-126): the same sphere
+				em.p[4] = src.p[4];
+				em.p[5] = __uint_as_float_host(ctx->envTexture);
+				/* fall through */
 			case MTSGPU_EMITTER_CONSTANT:          // ConstantLuminaire::preprocess (constant.cpp:48-62)
 				memcpy(em.p, src.p, 16);
 				if (!(src.p[3] > 0.0f)) {
@@ -721,6 +727,38 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		buildMipPyramid(ctx->bitmaps[i], (int) texs[i].p[0], (int) texs[i].p[1], texels, mipLevels);
 		texs[i].pad[1] = (uint32_t) (mipLevels.size() / 4) - texs[i].pad[0];
 	}
+	// ---- environment map: its pyramid joins the texture table; the sampling density of EnvMapLuminaire::configure
+	// (envmap.cpp:93-110) is a DiscretePDF over MIP level min(3, levels - 1), luminance x sin(theta)
+	std::vector<float> envData(20, 0.0f);
+	for (size_t e = 0; e < ctx->emitters.size(); ++e) {
+		if (ctx->emitters[e].type != MTSGPU_EMITTER_ENVMAP) continue;
+		REQUIRE(ctx, ctx->envEmitter == (int) e && ctx->envBitmap.width > 0, MTSGPU_ERR_ARG, "emitter %zu: the environment map was not uploaded (mtsgpu_upload_envmap)", e);
+		TextureDev t; memset(&t, 0, sizeof(t));
+		t.type = MTSGPU_TEXTURE_BITMAP; t.p[2] = 8.0f; t.p[8] = t.p[9] = 1.0f;      // EWA, repeat, maxAnisotropy 8 (mipmap.h:57-59)
+		t.pad[0] = (uint32_t) (mipLevels.size() / 4);
+		buildMipPyramid(ctx->envBitmap, 0, 0, texels, mipLevels);
+		t.pad[1] = (uint32_t) (mipLevels.size() / 4) - t.pad[0];
+		ctx->envTexture = (uint32_t) texs.size();
+		if (ctx->textures.empty()) { texs[0] = t; ctx->envTexture = 0; } else texs.push_back(t);
+		const int level = std::min(3, (int) t.pad[1] - 1);
+		const uint32_t *L = &mipLevels[4 * (t.pad[0] + level)];
+		const int resX = (int) L[1], resY = (int) L[2];
+		std::vector<float> pdf((size_t) resX * resY), cdf;
+		for (int y = 0; y < resY; ++y) {
+			const float sinFactor = std::sin(3.14159265358979323846f * (y + .5f) / resY);
+			for (int x = 0; x < resX; ++x) {
+				const float *c = &texels[4 * ((size_t) L[0] + x + (size_t) y * resX)];
+				volatile float lum = c[0] * 0.212671f; volatile float g = c[1] * 0.715160f; volatile float b = c[2] * 0.072169f;
+				lum = lum + g; lum = lum + b;                                   // Spectrum::getLuminance
+				pdf[x + (size_t) y * resX] = lum * sinFactor;
+			}
+		}
+		const float sum = buildCdf(pdf, cdf);
+		for (int k = 0; k < 9; ++k) { envData[k] = ctx->envW2L[k]; envData[9 + k] = ctx->envL2W[k]; }
+		envData[18] = (float) resX; envData[19] = (float) resY;
+		envData.insert(envData.end(), cdf.begin(), cdf.end());
+		for (float v : pdf) { volatile float q = v / sum; envData.push_back((float) q); }
+	}
 	if (texels.empty()) texels.assign(4, 0.0f);
 	if (mipLevels.empty()) mipLevels.assign(4, 0u);
 	float mipLut[128]; mipWeightLut(mipLut);
@@ -747,6 +785,8 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dMipLevels.p, mipLevels.data(), mipLevels.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, ctx->dMipLut.alloc(sizeof(mipLut)));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dMipLut.p, mipLut, sizeof(mipLut), cudaMemcpyHostToDevice, st));
+	CUDA_TRY(ctx, ctx->dEnvData.alloc(envData.size() * sizeof(float)));
+	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dEnvData.p, envData.data(), envData.size() * sizeof(float), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, ctx->dCamera.alloc(sizeof(CameraDev)));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dShapes.p, shapes.data(), nShapes * sizeof(ShapeInfo), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dMaterials.p, mats.data(), mats.size() * sizeof(MaterialDev), cudaMemcpyHostToDevice, st));
@@ -961,7 +1001,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	sc.hasSpheres = anySphere ? 1u : 0u;
 	sc.textures = ctx->dTextures.as<TextureDev>();
 	sc.texels = ctx->dTexels.as<float4>(); sc.mipLevels = ctx->dMipLevels.as<uint4>(); sc.mipLut = ctx->dMipLut.as<float>();
-	sc.camera = ctx->dCamera.as<CameraDev>();
+	sc.camera = ctx->dCamera.as<CameraDev>(); sc.envData = ctx->dEnvData.as<float>();
 	sc.shapes = ctx->dShapes.as<ShapeInfo>();
 	sc.materials = ctx->dMaterials.as<MaterialDev>();
 	sc.areaCdf = ctx->dAreaCdf.as<float>();

@@ -55,6 +55,8 @@ struct mtsgpu_ctx {
 	std::vector<mtsgpu_emitter> emitters;
 	std::vector<mtsgpu_texture> textures;
 	std::vector<HostBitmap> bitmaps;          // parallel to textures; filled by mtsgpu_upload_bitmap
+	HostBitmap envBitmap; int envEmitter = -1; float envL2W[9] = {}, envW2L[9] = {};   // mtsgpu_upload_envmap
+	uint32_t envTexture = 0;                  // index of the map's entry in the device texture table
 	std::vector<HostMesh> meshes;
 	std::vector<int> emitterShape;   // emitter id -> shape index
 	int lumImportance = -1;          // which luminaire CDF is on the device (-1: none)
@@ -66,7 +68,7 @@ struct mtsgpu_ctx {
 	bool built = false;
 	DeviceScene scene;
 	DevBuf dTriAccel, dTriAccelOrig, dNodes, dTriIdx, dPositions, dNormals, dShapes, dMaterials, dEmitters,
-	       dLumCdf, dAreaCdf, dTexcoords, dTextures, dTangents, dShadeTris, dSortedOf, dTexels, dMipLevels, dMipLut, dCamera;
+	       dLumCdf, dAreaCdf, dTexcoords, dTextures, dTangents, dShadeTris, dSortedOf, dTexels, dMipLevels, dMipLut, dCamera, dEnvData;
 	mtsgpu_accel_info accel = {};
 
 	// trace staging + counters

@@ -279,9 +279,9 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		if (MODE == 2) {
 			// direct.cpp:170-199: BSDF-sampled ray — only emitters (or the background on a miss) contribute
 			if ((valid && its.emitterId >= 0) || (!valid && sc.background >= 0)) {
-				const V3 Le = valid ? emitterLe(sc, its.emitterId, its.geoN, -rayD) : backgroundLe(sc);
+				const V3 Le = valid ? emitterLe(sc, its.emitterId, its.geoN, -rayD) : backgroundLe(sc, rayD);
 				const float lumPdf = (flags & PF_PREV_DELTA) ? 0.0f :
-					(valid ? pdfLuminaire(sc, rayO, its.p, its.geoN, its.emitterId, ig.importance != 0) : pdfBackground(sc, ig.importance != 0));
+					(valid ? pdfLuminaire(sc, rayO, its.p, its.geoN, its.emitterId, ig.importance != 0) : pdfBackground(sc, ig.importance != 0, rayD));
 				const float total = (float) (ig.nLum + ig.nBsdf);          // direct.cpp:49-54
 				const float fracBsdf = ig.nBsdf / total, fracLum = ig.nLum / total;
 				const float weightBsdf = 1 / (float) ig.nBsdf;
@@ -296,9 +296,9 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 				const V3 bsdfVal = v3(bv4);
 				if (!valid) {
 					if (sc.background >= 0) {                  // path.cpp:158-163, 172-179, then 187-188
-						const float lumPdf = (flags & PF_PREV_DELTA) ? 0.0f : pdfBackground(sc, ig.importance != 0);
+						const float lumPdf = (flags & PF_PREV_DELTA) ? 0.0f : pdfBackground(sc, ig.importance != 0, rayD);
 						const float w = miWeight(thr4.w, lumPdf);
-						Li = Li + ((thr * backgroundLe(sc)) * bsdfVal) * w;
+						Li = Li + ((thr * backgroundLe(sc, rayD)) * bsdfVal) * w;
 					} else {
 						depth++;                               // path.cpp:166
 					}
@@ -326,7 +326,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 			} else if (MODE == 0 || round == 0) {
 				// camera hit: rRec.alpha (records.inl:93-99)
 				li4.w = valid ? 1.0f : 0.0f;
-				if (!valid && (flags & PF_EMITTED)) Li = Li + backgroundLe(sc);      // path.cpp:62-68 / direct.cpp:74-81
+				if (!valid && (flags & PF_EMITTED)) Li = Li + backgroundLe(sc, rayD);      // path.cpp:62-68 / direct.cpp:74-81
 			}
 
 			// ---- top of the loop body at the new hit (path.cpp:58-95 / direct.cpp:74-100)
@@ -790,7 +790,7 @@ __global__ void k_hook_emitter(const DeviceScene sc, const float *q, uint32_t n,
 		// Scene::pdfLuminaire (scene.cpp:381-394): zero for the delta luminaires
 		const uint32_t type = sc.emitters[ls.emitter].type;
 		o[14] = type == MTSGPU_EMITTER_AREA ? pdfLuminaire(sc, p, ls.p, ls.n, ls.emitter, importance != 0)
-			: (type == MTSGPU_EMITTER_CONSTANT ? pdfBackground(sc, importance != 0) : 0.0f);
+			: ((type == MTSGPU_EMITTER_CONSTANT || type == MTSGPU_EMITTER_ENVMAP) ? pdfBackground(sc, importance != 0, -ls.d) : 0.0f);
 	} else {
 		o[13] = -1.0f;
 	}

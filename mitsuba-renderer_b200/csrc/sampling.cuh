@@ -638,6 +638,48 @@ __device__ inline float spherePdfSolidAngle(V3 center, float radius, float invSu
 	return 1 / (2 * MTS_PI * (1 - cosThetaMax));
 }
 
+// ---- environment map (src/luminaires/envmap.cpp). sc.envData: worldToLuminaire 3x3, luminaireToWorld 3x3, the
+// resolution of the sampling density (a coarse MIP level), its CDF (n + 1) and its normalised pdf (n).
+__device__ inline V3 envXf(const float *m, V3 v) { return v3(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[3] * v.x + m[4] * v.y + m[5] * v.z, m[6] * v.x + m[7] * v.y + m[8] * v.z); }
+
+// EnvMapLuminaire::Le(direction) (envmap.cpp:158-164): bilinear level-0 lookup at the direction's latitude / longitude
+__device__ __noinline__ V3 envLe(const DeviceScene &sc, const EmitterDev &em, V3 direction) {
+	const V3 d = envXf(sc.envData, direction);
+	const float u = .5f * (1 + mts_atan2(d.x, -d.z) / MTS_PI);
+	const float v = mts_acos(fmaxf(-1.0f, fminf(1.0f, d.y))) / MTS_PI;
+	return mipTriangle(sc, sc.textures[__float_as_uint(em.p[5])], 0, u, v) * em.p[4];
+}
+
+// EnvMapLuminaire::pdf (envmap.cpp:184-199); `dir` is -lRec.d, the direction from the shaded point to the map
+__device__ __noinline__ float envPdf(const DeviceScene &sc, V3 dir) {
+	const V3 d = envXf(sc.envData, dir);
+	const int resX = (int) sc.envData[18], resY = (int) sc.envData[19];
+	const float x = .5f * (1 + mts_atan2(d.x, -d.z) / MTS_PI) * resX;
+	const float y = mts_acos(fmaxf(-1.0f, fminf(1.0f, d.y))) / MTS_PI * resY;
+	const int xPos = min(max((int) floorf(x), 0), resX - 1), yPos = min(max((int) floorf(y), 0), resY - 1);
+	const float pdf = sc.envData[20 + resX * resY + 1 + xPos + yPos * resX];
+	const float sinTheta = sqrtf(fmaxf(MTS_EPSILON, 1 - d.y * d.y));
+	const float pixX = 2 * MTS_PI / resX, pixY = MTS_PI / resY;
+	return pdf / (pixX * pixY * sinTheta);
+}
+
+// EnvMapLuminaire::sampleDirection (envmap.cpp:134-156): a texel of the density, then a point inside it
+__device__ __noinline__ V3 envSampleDirection(const DeviceScene &sc, const EmitterDev &em, float sx, float sy, float &pdf, V3 &value) {
+	const int resX = (int) sc.envData[18], resY = (int) sc.envData[19];
+	const float *cdf = sc.envData + 20;
+	const int idx = cdfSampleReuse(cdf, resX * resY, sx);
+	pdf = cdf[resX * resY + 1 + idx];
+	const int row = idx / resX, col = idx - resX * row;
+	const float x = col + sx, y = row + sy;
+	value = mipTriangle(sc, sc.textures[__float_as_uint(em.p[5])], 0, x * (1.0f / resX), y * (1.0f / resY)) * em.p[4];
+	const float pixX = 2 * MTS_PI / resX, pixY = MTS_PI / resY;
+	const float theta = pixY * y, phi = pixX * x - MTS_PI;
+	const float sinTheta = mts_sin(theta), cosTheta = mts_cos(theta);
+	const float sinPhi = mts_sin(phi), cosPhi = mts_cos(phi);
+	pdf = pdf / (pixX * pixY * sinTheta);
+	return envXf(sc.envData + 9, v3(-sinTheta * sinPhi, -cosTheta, sinTheta * cosPhi));
+}
+
 __device__ inline void sampleLuminaire(const DeviceScene &sc, V3 p, float sx, float sy, bool importance, LumSample &out) {
 	out.pdf = 0; out.emitter = -1; out.mis = true;
 	if (sc.nEmitters == 0) return;
@@ -703,6 +745,18 @@ __device__ inline void sampleLuminaire(const DeviceScene &sc, V3 p, float sx, fl
 		out.p = p - dir * (2 * em.p[3]); out.n = v3(0, 0, 0);
 		out.d = dir;
 		pdf = 1.0f; out.mis = false;
+	} else if (em.type == MTSGPU_EMITTER_ENVMAP) {
+		// EnvMapLuminaire::sample (envmap.cpp:170-182)
+		float dirPdf;
+		const V3 d = envSampleDirection(sc, em, sx, sy, dirPdf, value);
+		const V3 center = v3(em.p[0], em.p[1], em.p[2]);
+		float nearHit, farHit;
+		if (length(p - center) <= em.p[3] && bsphereRayIntersect(center, em.p[3], p, -d, nearHit, farHit)) {
+			out.p = p - d * nearHit;
+			out.n = normalize(center - out.p);
+			out.d = d;
+			pdf = dirPdf;
+		}
 	} else {
 		// ConstantLuminaire::sample (constant.cpp:72-86)
 		const V3 d = squareToSphere(sx, sy);
@@ -739,17 +793,21 @@ __device__ inline float pdfLuminaire(const DeviceScene &sc, V3 from, V3 lumP, V3
 }
 
 // Scene::pdfLuminaire for the background luminaire: ConstantLuminaire::pdf (constant.cpp:88-90)
-__device__ inline float pdfBackground(const DeviceScene &sc, bool importance) {
+// `dir`: the direction of the ray that left the scene (-lRec.d)
+__device__ inline float pdfBackground(const DeviceScene &sc, bool importance, V3 dir) {
 	const EmitterDev em = sc.emitters[sc.background];
 	const float luminance = importance ? em.weight : 1.0f;
 	const float fraction = luminance / sc.lumOriginalSum;
+	if (em.type == MTSGPU_EMITTER_ENVMAP) return envPdf(sc, dir) * fraction;
 	return (1.0f / (4 * MTS_PI)) * fraction;
 }
 
-// Scene::LeBackground (scene.h:403-405) -> ConstantLuminaire::Le (constant.cpp:68-70)
-__device__ inline V3 backgroundLe(const DeviceScene &sc) {
+// Scene::LeBackground (scene.h:403-405) -> ConstantLuminaire::Le (constant.cpp:68-70) or the environment map
+// EnvMapLuminaire::Le(ray) = Le(normalize(ray.d)) (envmap.cpp:166-168)
+__device__ inline V3 backgroundLe(const DeviceScene &sc, V3 rayD) {
 	if (sc.background < 0) return v3(0, 0, 0);
 	const EmitterDev em = sc.emitters[sc.background];
+	if (em.type == MTSGPU_EMITTER_ENVMAP) return envLe(sc, em, normalize(rayD));
 	return v3(em.intensity[0], em.intensity[1], em.intensity[2]);
 }
 

@@ -79,6 +79,7 @@ struct DeviceScene {
 	const float4 *texels;       // mip pyramids of the bitmap textures (rgb + pad per texel)
 	const uint4 *mipLevels;     // {offset into texels, width, height, -} per level; TextureDev::pad = {first level, count}
 	const float *mipLut;        // MIPMap's EWA weight table, 128 entries
+	const float *envData;       // environment map: worldToLuminaire 3x3, luminaireToWorld 3x3, density resolution, CDF, pdf (sampling.cuh)
 	const struct CameraDev *camera;   // the render's camera: ray differentials of a camera-ray hit are rebuilt from it
 	const ShapeInfo *shapes;
 	const MaterialDev *materials;

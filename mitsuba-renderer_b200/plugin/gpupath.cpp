@@ -256,7 +256,8 @@ private:
 	 * Luminaire::serialize (luminaire.cpp:66-74) + the subclass's fields. ConfigurableObject::serialize writes the
 	 * parent object first (properties.cpp:358-363) — the whole scene here — so the parent link is cleared for the
 	 * duration of the call; render() runs before any worker touches the scene. */
-	static void decodeLuminaire(const Luminaire *lumConst, mtsgpu_emitter &e) {
+	struct EnvUpload { ref<Bitmap> bitmap; float l2w[16], w2l[16]; };
+	static void decodeLuminaire(const Luminaire *lumConst, mtsgpu_emitter &e, EnvUpload &env) {
 		Luminaire *lum = const_cast<Luminaire *>(lumConst);
 		const std::string cls = lum->getClass()->getName();
 		ConfigurableObject *parent = lum->getParent();
@@ -301,9 +302,22 @@ private:
 			put(e.intensity, Spectrum(s));
 			BSphere bs(s);
 			e.p[0] = bs.center.x; e.p[1] = bs.center.y; e.p[2] = bs.center.z; e.p[3] = bs.radius;
+		} else if (cls == "EnvMapLuminaire") {                  /* envmap.cpp:79-92, after preprocess() */
+			e.type = MTSGPU_EMITTER_ENVMAP;
+			e.intensity[0] = e.intensity[1] = e.intensity[2] = 1.0f;
+			e.p[4] = s->readFloat();                            /* intensityScale */
+			s->readString();
+			BSphere bs(s);
+			e.p[0] = bs.center.x; e.p[1] = bs.center.y; e.p[2] = bs.center.z; e.p[3] = bs.radius;
+			const uint32_t size = s->readUInt();                /* the OpenEXR file, decoded by the host's Bitmap */
+			ref<MemoryStream> file = new MemoryStream(size);
+			s->copyTo(file, size);
+			file->setPos(0);
+			env.bitmap = new Bitmap(Bitmap::EEXR, file);
+			for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) { env.l2w[4 * i + j] = l2w.m[i][j]; env.w2l[4 * i + j] = w2l.m[i][j]; }
 		} else {
 			SLog(EError, "gpupath: luminaire class \"%s\" is outside the supported hot path "
-				"(area, point, spot, directional, constant)", cls.c_str());
+				"(area, point, spot, directional, constant, envmap)", cls.c_str());
 		}
 		(void) l2w;
 	}
@@ -394,6 +408,7 @@ private:
 		std::map<const BSDF *, int> materialIds;
 		std::vector<mtsgpu_emitter> emitters(luminaires.size());
 		std::map<const Luminaire *, int> emitterIds;
+		EnvUpload env; int envIndex = -1;
 		for (size_t i = 0; i < luminaires.size(); ++i) {
 			const Luminaire *lum = luminaires[i];
 			memset(&emitters[i], 0, sizeof(mtsgpu_emitter));
@@ -404,7 +419,8 @@ private:
 				emitters[i].type = MTSGPU_EMITTER_AREA;
 				put(emitters[i].intensity, lum->Le(ShapeSamplingRecord(Point(0.0f), Normal(0, 0, 1)), Vector(0, 0, 1)));
 			} else {
-				decodeLuminaire(lum, emitters[i]);
+				decodeLuminaire(lum, emitters[i], env);
+				if (emitters[i].type == MTSGPU_EMITTER_ENVMAP) envIndex = (int) i;
 			}
 		}
 		struct MeshRef { const TriMesh *mesh; int mat, emit; bool sphere; SphereData sph; };
@@ -446,6 +462,9 @@ private:
 			}
 			check(c, mtsgpu_upload_materials(c, materials.empty() ? NULL : &materials[0], (int) materials.size()));
 			check(c, mtsgpu_upload_emitters(c, emitters.empty() ? NULL : &emitters[0], (int) emitters.size()));
+			if (envIndex >= 0)      /* Bitmap::loadEXR leaves RGBA floats (bitmap.cpp:247-273) */
+				check(c, mtsgpu_upload_envmap(c, envIndex, env.bitmap->getWidth(), env.bitmap->getHeight(), 4,
+					env.bitmap->getFloatData(), env.l2w, env.w2l));
 			for (size_t i = 0; i < meshes.size(); ++i) {
 				if (meshes[i].sphere) {
 					const SphereData &sp = meshes[i].sph;

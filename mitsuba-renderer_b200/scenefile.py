@@ -157,7 +157,7 @@ def twosided(material: Material) -> Material:
     return Material(material.type | BSDF_TWOSIDED, material.p.copy(), material.tex)
 
 
-EMITTER_AREA, EMITTER_POINT, EMITTER_SPOT, EMITTER_DIRECTIONAL, EMITTER_CONSTANT = range(5)
+EMITTER_AREA, EMITTER_POINT, EMITTER_SPOT, EMITTER_DIRECTIONAL, EMITTER_CONSTANT, EMITTER_ENVMAP = range(6)
 
 
 @dataclass
@@ -171,6 +171,7 @@ class Emitter:
     type: int = EMITTER_AREA
     p: tuple = ()
     aux: tuple = ()
+    pixels: Optional[np.ndarray] = None     # environment map: float32 [height, width, 3], values representable in half
 
     def abi_params(self):
         v = np.zeros(11, np.float32); v[:len(self.p)] = self.p
@@ -246,6 +247,16 @@ def directional_light(direction, intensity=(1.0, 1.0, 1.0), sampling_weight=1.0)
 def constant_light(intensity=(1.0, 1.0, 1.0), sampling_weight=1.0):
     """src/luminaires/constant.cpp:29-32: constant background; its bounding sphere is derived from the scene."""
     return Emitter(tuple(intensity), sampling_weight, EMITTER_CONSTANT)
+
+
+def envmap_light(pixels, intensity_scale=1.0, to_world=None, sampling_weight=1.0):
+    """src/luminaires/envmap.cpp:40-51: latitude-longitude environment map read from an OpenEXR file. The pixels are
+    rounded to half precision here, which is what the file holds (Bitmap::loadEXR, bitmap.cpp:247-273)."""
+    m = np.eye(4, dtype=np.float32) if to_world is None else np.asarray(to_world, np.float32).reshape(4, 4)
+    with np.errstate(over="ignore"):
+        px = np.ascontiguousarray(pixels, np.float32).astype(np.float16).astype(np.float32)
+    assert px.ndim == 3 and px.shape[2] == 3
+    return Emitter((1.0, 1.0, 1.0), sampling_weight, EMITTER_ENVMAP, (0.0, 0.0, 0.0, 0.0, float(intensity_scale)), tuple(m.reshape(16)), px)
 
 
 def add_light(scene: "SceneDesc", emitter: Emitter) -> int:
@@ -377,7 +388,7 @@ def write_scene(path: str, scene: SceneDesc) -> None:
     cx, cy, cw, ch = scene.crop_rect
     with open(path, "wb") as f:
         f.write(b"MTSB200\0")
-        f.write(struct.pack("<I", 6))
+        f.write(struct.pack("<I", 7))
         f.write(np.ascontiguousarray(scene.camera_to_world, np.float32).tobytes())
         f.write(struct.pack("<5fI", scene.fov, scene.near_clip, scene.far_clip, scene.aperture_radius,
                             scene.focus_depth, int(scene.map_smaller_side)))
@@ -398,9 +409,15 @@ def write_scene(path: str, scene: SceneDesc) -> None:
             f.write(np.ascontiguousarray(m.p, np.float32).tobytes())
             f.write(struct.pack("<2I", *m.tex))
         f.write(struct.pack("<I", len(scene.emitters)))
-        for e in scene.emitters:
+        for k, e in enumerate(scene.emitters):
             f.write(struct.pack("<4fI", *e.intensity, e.sampling_weight, e.type))
             f.write(e.abi_params().tobytes()); f.write(e.aux_params().tobytes())
+            if e.type == EMITTER_ENVMAP:            # the map travels as the OpenEXR file the reference's plugin reads
+                from . import api
+                exr = (path + ".env%d.exr" % k).encode()
+                rgba = np.concatenate([e.pixels, np.ones(e.pixels.shape[:2] + (1,), np.float32)], axis=2)
+                api.write_exr(exr.decode(), rgba)
+                f.write(struct.pack("<I", len(exr))); f.write(exr)
         f.write(struct.pack("<I", len(scene.shapes)))
         for s in scene.shapes:
             f.write(struct.pack("<I", 0 if s.sphere is None else 1))

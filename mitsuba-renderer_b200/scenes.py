@@ -9,7 +9,7 @@ import numpy as np
 
 from .scenefile import (SceneDesc, Shape, Emitter, lambertian, microfacet, mirror, roughmetal,
                         dielectric, twosided, phong, roughglass, look_at, point_light, spot_light, directional_light,
-                        constant_light, add_light, checkerboard, textured, ward, sphere_shape, bitmap_texture, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
+                        constant_light, envmap_light, add_light, checkerboard, textured, ward, sphere_shape, bitmap_texture, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
                         WRAP_REPEAT, WRAP_BLACK, WRAP_WHITE, WRAP_CLAMP, MODE_PATH, MODE_DIRECT, FILTER_BOX)
 
 F32 = np.float32
@@ -197,6 +197,36 @@ def bitmap_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6) 
     t.append(green_wall)
     s.materials[0] = textured(s.materials[0], 0, 3)
     s.materials[2] = textured(s.materials[2], 0, 4)
+    return s
+
+
+def _sky_image(width, height, seed):
+    """A small latitude-longitude HDR map: a bright sun disc, a sky gradient and dim noisy ground."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    v, u = np.mgrid[0:height, 0:width]
+    theta = (v + 0.5) / height * np.pi
+    phi = (u + 0.5) / width * 2 * np.pi
+    img = np.empty((height, width, 3), np.float64)
+    up = np.clip(np.cos(theta), 0, 1)
+    img[..., 0] = 0.2 + 0.3 * up; img[..., 1] = 0.3 + 0.4 * up; img[..., 2] = 0.5 + 0.9 * up
+    ground = np.cos(theta) < 0
+    img[ground] = np.array([0.12, 0.1, 0.08]) * (0.5 + rng.random((int(ground.sum()), 1)))
+    sun = (theta - 0.9) ** 2 + (phi - 4.2) ** 2 < 0.05
+    img[sun] = [40.0, 36.0, 30.0]
+    return (img * (0.9 + 0.2 * rng.random((height, width, 1)))).astype(F32)
+
+
+def envmap_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6, rotate=True) -> SceneDesc:
+    """The open all-luminaires scene with an environment map (src/luminaires/envmap.cpp) as its background instead of the
+    constant one: a 64 x 32 latitude-longitude map, intensityScale 1.5, rotated about two axes."""
+    s = lights_test_scene(width, height, spp, mode, max_depth, background=False)
+    m = None
+    if rotate:
+        a, b = F32(0.6), F32(-0.35)
+        ry = np.array([[np.cos(a), 0, np.sin(a), 0], [0, 1, 0, 0], [-np.sin(a), 0, np.cos(a), 0], [0, 0, 0, 1]], F32)
+        rx = np.array([[1, 0, 0, 0], [0, np.cos(b), -np.sin(b), 0], [0, np.sin(b), np.cos(b), 0], [0, 0, 0, 1]], F32)
+        m = (ry @ rx).astype(F32)
+    add_light(s, envmap_light(_sky_image(64, 32, 7), 1.5, m, sampling_weight=2.0))
     return s
 
 

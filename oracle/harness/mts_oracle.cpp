@@ -336,9 +336,14 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 	for (size_t i = 0; i < s.emitters.size(); ++i) {
 		const sio::Emitter &e = s.emitters[i];
 		if (e.type == 0) continue;
-		static const char *names[5] = { "area", "point", "spot", "directional", "constant" };
-		if (e.type > 4) SLog(EError, "unknown emitter type %u", e.type);
+		static const char *names[6] = { "area", "point", "spot", "directional", "constant", "envmap" };
+		if (e.type > 5) SLog(EError, "unknown emitter type %u", e.type);
 		Properties lp(names[e.type]);
+		if (e.type == 5) {       /* <luminaire type="envmap"> (envmap.cpp:40-51) */
+			lp.setString("filename", e.envFile);
+			lp.setFloat("intensityScale", e.p[4]);
+			lp.setTransform("toWorld", Transform(Matrix4x4(const_cast<float *>(e.aux))));
+		} else
 		lp.setSpectrum("intensity", rgb(e.intensity));
 		lp.setFloat("samplingWeight", e.samplingWeight);
 		if (e.type == 1 || e.type == 2)

@@ -63,6 +63,10 @@ def main():
     tsess = oracle_util.Session(ts)
     thits, tfull, _ = tsess.trace(rays, "closest_full")       # `wi` in the tangent frames of the anisotropic Ward meshes
     save("uv_textured", rays_digest=gc.digest(rays), out=tsess.uv(rays), hits=thits.view(np.uint8), full=tfull)
+    # ---- environment map: importance sampling and pdf -------------------------------------------------------------------
+    es = gc.scene_envmap()
+    q = gc.emitter_queries(es, 6000)
+    save("emitter_envmap", queries_digest=gc.digest(q), out=oracle_util.Session(es).emitter(q))
     # ---- bitmap textures filtered with the uv partials of the camera's ray differentials -------------------------------------
     bs_ = gc.scene_bitmaps()
     q = gc.lens_camera_samples(bs_, 6000, 31)

@@ -231,3 +231,7 @@ def lens_camera_samples(scene, n, seed):
     q[:, 0] = rng.random(n) * scene.width; q[:, 1] = rng.random(n) * scene.height
     q[:, 2:] = rng.random((n, 2))
     return q
+
+
+def scene_envmap():
+    return scenes.envmap_test_scene(16, 16, 1)

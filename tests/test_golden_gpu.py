@@ -180,3 +180,17 @@ def test_filtered_bitmap_lookups_match_golden(gpu_ctx_factory):
     want = gc.diffuse_reflectance_from_slots(scene, hits, got[:, 6:9])
     err = np.abs(want - ref[:, 6:9]).max(axis=1)
     assert (err > 1e-5).sum() <= 6 and np.median(err) < 1e-7, ((err > 1e-5).sum(), err.max())
+
+
+def test_envmap_sampling_matches_golden(gpu_ctx_factory):
+    """EnvMapLuminaire::sample / pdf (envmap.cpp:134-199) on the rotated 64 x 32 map of the envmap test scene."""
+    es = gc.scene_envmap()
+    q = gc.emitter_queries(es, 6000)
+    ref = gold("emitter_envmap")
+    assert gc.digest(q) == str(ref["queries_digest"])
+    out, ref = gpu_ctx_factory(es).emitter_sample(q), ref["out"]
+    assert np.array_equal(out[:, 13], ref[:, 13]) and (ref[:, 13] == 3).sum() > 1000
+    cols = [c for c in range(15) if c not in (3, 4, 5)]
+    assert close(out[:, cols], ref[:, cols], 2e-5, 2e-6).all()
+    has_n = ref[:, 13] >= 3
+    assert close(out[has_n, 3:6], ref[has_n, 3:6], 2e-5, 2e-6).all()
