@@ -245,6 +245,21 @@ MTSGPU_API int mtsgpu_upload_mesh(mtsgpu_ctx *ctx, int shapeIndex,
 MTSGPU_API int mtsgpu_upload_sphere(mtsgpu_ctx *ctx, int shapeIndex, const float objectToWorld[16], const float worldToObject[16],
                                     float radius, const float center[3], int inverted, int materialId, int emitterId);
 
+/* Instancing (src/shapes/shapegroup.cpp, src/shapes/instance.cpp). A shape group is a set of triangle meshes with an
+ * acceleration structure of its own (ShapeGroup::m_kdtree) that is not part of the scene by itself; mesh `meshIndex`
+ * of group `groupId` (both 0, 1, 2 ... in order) is uploaded like a scene mesh, in the group's object space. Luminaires
+ * cannot be instanced ("Instancing of luminaires is not supported", shapegroup.cpp:66-67). */
+MTSGPU_API int mtsgpu_upload_group_mesh(mtsgpu_ctx *ctx, int groupId, int meshIndex, const float *positions, const float *normals,
+	const float *texcoords, uint32_t nVert, const uint32_t *triangles, uint32_t nTri, int materialId);
+/* An <shape type="instance"> at kd-tree shape index `shapeIndex`: group `groupId` under objectToWorld (worldToObject is
+ * its inverse as the reference's Transform holds it). One primitive of the scene's acceleration structure, boxed like
+ * Instance::getAABB (instance.cpp:47-56); a ray that reaches it is taken to object space — direction not renormalised,
+ * so t is shared (Instance::rayIntersect, instance.cpp:72-86) — and continues in the group's own structure, inside
+ * the interval clipped to the group's box (ShapeKDTree::rayIntersect, skdtree.h:435-466). Hits report the instance's
+ * shape index and prim = 0xFFFFFFFF; shading follows Instance::fillIntersectionRecord (instance.cpp:88-98). */
+MTSGPU_API int mtsgpu_upload_instance(mtsgpu_ctx *ctx, int shapeIndex, int groupId, const float objectToWorld[16],
+	const float worldToObject[16]);
+
 MTSGPU_API int mtsgpu_set_camera(mtsgpu_ctx *ctx, const float rasterToCamera[16], const float cameraToWorld[16],
 	float nearClip, float farClip, float apertureRadius, float focusDepth, float shutterOpen, float shutterOpenTime);
 

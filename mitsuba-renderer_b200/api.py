@@ -29,7 +29,7 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_film_splat_static", "mtsgpu_render_multi", "mtsgpu_serialized_count", "mtsgpu_serialized_load",
     "mtsgpu_serialized_free", "mtsgpu_serialized_save", "mtsgpu_upload_serialized", "mtsgpu_film_develop",
     "mtsgpu_film_develop_device", "mtsgpu_film_save", "mtsgpu_write_exr", "mtsgpu_write_mfilm", "mtsgpu_sampler_values",
-    "mtsgpu_upload_textures", "mtsgpu_intersect_uv", "mtsgpu_upload_sphere", "mtsgpu_upload_bitmap", "mtsgpu_texture_lookup", "mtsgpu_upload_envmap",
+    "mtsgpu_upload_textures", "mtsgpu_intersect_uv", "mtsgpu_upload_sphere", "mtsgpu_upload_bitmap", "mtsgpu_texture_lookup", "mtsgpu_upload_envmap", "mtsgpu_upload_group_mesh", "mtsgpu_upload_instance",
 ]
 SAMPLER_INDEPENDENT, SAMPLER_LD, SAMPLER_STRATIFIED, SAMPLER_HALTON = 0, 1, 2, 3
 FILM_EXR, FILM_M = 0, 1
@@ -108,6 +108,8 @@ def load_library(path: Optional[str] = None):
     lib.mtsgpu_upload_emitters.argtypes = [vp, C.POINTER(Emitter), C.c_int]
     lib.mtsgpu_upload_textures.argtypes = [vp, C.POINTER(Texture), C.c_int]
     lib.mtsgpu_intersect_uv.argtypes = [vp, vp, C.c_size_t, vp]
+    lib.mtsgpu_upload_group_mesh.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, C.c_uint32, vp, C.c_uint32, C.c_int]
+    lib.mtsgpu_upload_instance.argtypes = [vp, C.c_int, C.c_int, vp, vp]
     lib.mtsgpu_upload_envmap.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp]
     lib.mtsgpu_upload_bitmap.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_float]
     lib.mtsgpu_upload_sphere.argtypes = [vp, C.c_int, vp, vp, C.c_float, vp, C.c_int, C.c_int, C.c_int]
@@ -258,7 +260,21 @@ class Context:
                 px = np.ascontiguousarray(e.pixels, np.float32)
                 self._check(self.lib.mtsgpu_upload_envmap(self.h, i, px.shape[1], px.shape[0], px.shape[2], self._ptr(px),
                                                           self._ptr(l2w), self._ptr(w2l)))
+        for g, group in enumerate(scene.groups):   # shape groups: meshes in object space, their own acceleration structure
+            for k, s in enumerate(group):
+                pos = np.ascontiguousarray(s.positions, np.float32)
+                nrm = None if s.normals is None else np.ascontiguousarray(s.normals, np.float32)
+                tri = np.ascontiguousarray(s.triangles, np.uint32)
+                uv = None if s.texcoords is None else np.ascontiguousarray(s.texcoords, np.float32)
+                self._check(self.lib.mtsgpu_upload_group_mesh(self.h, g, k, self._ptr(pos), self._ptr(nrm), self._ptr(uv), len(pos),
+                                                              self._ptr(tri), len(tri), s.material))
         for i, s in enumerate(scene.shapes):
+            if s.instance is not None:              # toWorld and its fp32 Gauss-Jordan inverse (Transform(Matrix4x4))
+                from .scenefile import invert4_f32
+                o2w = np.ascontiguousarray(s.instance[1], np.float32)
+                w2o = np.ascontiguousarray(invert4_f32(o2w))
+                self._check(self.lib.mtsgpu_upload_instance(self.h, i, s.instance[0], self._ptr(o2w), self._ptr(w2o)))
+                continue
             if s.sphere is not None:                # center + radius: objectToWorld = translate(center) (sphere.cpp:44-47)
                 center, radius, inverted = s.sphere
                 o2w = np.eye(4, dtype=np.float32); o2w[:3, 3] = center

@@ -51,6 +51,8 @@ int mtsgpu_create(int device, mtsgpu_ctx **out) {
 
 void mtsgpu_destroy(mtsgpu_ctx *ctx) {
 	if (!ctx) return;
+	for (mtsgpu_ctx *g : ctx->groups) mtsgpu_destroy(g);
+	ctx->groups.clear();
 	cudaSetDevice(ctx->device);
 	cudaStreamSynchronize(ctx->stream);
 	for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -206,6 +208,42 @@ int mtsgpu_upload_sphere(mtsgpu_ctx *ctx, int shapeIndex, const float objectToWo
 	return MTSGPU_OK;
 }
 
+int mtsgpu_upload_group_mesh(mtsgpu_ctx *ctx, int groupId, int meshIndex, const float *positions, const float *normals,
+		const float *texcoords, uint32_t nVert, const uint32_t *triangles, uint32_t nTri, int materialId) {
+	ENTER(ctx);
+	REQUIRE(ctx, groupId >= 0 && (size_t) groupId <= ctx->groups.size(), MTSGPU_ERR_ARG,
+		"upload_group_mesh: groups must be created in order (got %d, expected <= %zu)", groupId, ctx->groups.size());
+	if ((size_t) groupId == ctx->groups.size()) {
+		mtsgpu_ctx *g = nullptr;
+		REQUIRE(ctx, mtsgpu_create(ctx->device, &g) == MTSGPU_OK, MTSGPU_ERR_CUDA, "upload_group_mesh: %s", mtsgpu_last_error(nullptr));
+		ctx->groups.push_back(g);
+	}
+	mtsgpu_ctx *g = ctx->groups[groupId];
+	const int rc = mtsgpu_upload_mesh(g, meshIndex, positions, normals, texcoords, nVert, triangles, nTri, materialId, -1);
+	if (rc != MTSGPU_OK) return setError(ctx, rc, "group %d: %s", groupId, g->error.c_str());
+	ctx->built = false;
+	return MTSGPU_OK;
+}
+
+int mtsgpu_upload_instance(mtsgpu_ctx *ctx, int shapeIndex, int groupId, const float objectToWorld[16], const float worldToObject[16]) {
+	ENTER(ctx);
+	REQUIRE(ctx, objectToWorld && worldToObject, MTSGPU_ERR_ARG, "upload_instance: null argument");
+	REQUIRE(ctx, shapeIndex >= 0 && (size_t) shapeIndex <= ctx->meshes.size(), MTSGPU_ERR_ARG,
+		"upload_instance: shapes must be uploaded in kd-tree order (got %d, expected <= %zu)", shapeIndex, ctx->meshes.size());
+	// "A reference to a 'shapegroup' must be specified!" (instance.cpp:42-45)
+	REQUIRE(ctx, groupId >= 0 && (size_t) groupId < ctx->groups.size(), MTSGPU_ERR_ARG, "upload_instance: shape group %d was not uploaded", groupId);
+	if ((size_t) shapeIndex < ctx->meshes.size()) ctx->meshes.resize(shapeIndex);
+	HostMesh m;
+	m.nVert = 2; m.nTri = 1; m.materialId = -1; m.emitterId = -1; m.hasNormals = false;
+	m.pos.assign(6, 0.0f);
+	m.tri = { 0u, INSTANCE_MARK, 1u };
+	m.instance = true; m.groupId = groupId;
+	memcpy(m.o2w, objectToWorld, 64); memcpy(m.w2o, worldToObject, 64);
+	ctx->meshes.push_back(std::move(m));
+	ctx->built = false;
+	return MTSGPU_OK;
+}
+
 int mtsgpu_set_camera(mtsgpu_ctx *ctx, const float rasterToCamera[16], const float cameraToWorld[16], float nearClip, float farClip,
 		float apertureRadius, float focusDepth, float shutterOpen, float shutterOpenTime) {
 	ENTER(ctx);
@@ -241,6 +279,39 @@ int mtsgpu_set_film(mtsgpu_ctx *ctx, int width, int height, int cropX, int cropY
 
 int mtsgpu_build_accel(mtsgpu_ctx *ctx) {
 	ENTER(ctx);
+	// ---- shape groups first (ShapeGroup::configure builds its kd-tree, shapegroup.cpp:44-47): each one is a context of
+	// its own that sees the scene's materials and textures, so that material ids mean the same thing in both
+	bool anyInstance = false;
+	for (const HostMesh &m : ctx->meshes) anyInstance |= m.instance;
+	if (anyInstance) {
+		for (size_t g = 0; g < ctx->groups.size(); ++g) {
+			mtsgpu_ctx *c = ctx->groups[g];
+			if (c->built) continue;
+			c->materials = ctx->materials; c->textures = ctx->textures; c->bitmaps = ctx->bitmaps;
+			c->emitters.clear();
+			const int rc = buildAccel(c);
+			if (rc != MTSGPU_OK) return setError(ctx, rc, "shape group %zu: %s", g, c->error.c_str());
+		}
+		for (HostMesh &m : ctx->meshes) {
+			if (!m.instance) continue;
+			// Instance::getAABB (instance.cpp:47-56): the eight corners of the group's kd-tree box through objectToWorld
+			const DeviceScene &gs = ctx->groups[m.groupId]->scene;
+			float lo[3] = { INFINITY, INFINITY, INFINITY }, hi[3] = { -INFINITY, -INFINITY, -INFINITY };
+			for (int corner = 0; corner < 8; ++corner) {
+				const float p[3] = { (corner & 1) ? gs.aabbMax[0] : gs.aabbMin[0], (corner & 2) ? gs.aabbMax[1] : gs.aabbMin[1],
+					(corner & 4) ? gs.aabbMax[2] : gs.aabbMin[2] };
+				float q[4];
+				for (int r = 0; r < 4; ++r) {          // Transform::operator()(Point) (transform.h:100-115)
+					volatile float a = m.o2w[4 * r] * p[0]; volatile float b = m.o2w[4 * r + 1] * p[1]; volatile float c2 = m.o2w[4 * r + 2] * p[2];
+					volatile float sum = a + b; sum = sum + c2; sum = sum + m.o2w[4 * r + 3];
+					q[r] = sum;
+				}
+				if (q[3] != 1.0f) { const float inv = 1.0f / q[3]; for (int k = 0; k < 3; ++k) q[k] *= inv; }
+				for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], q[k]); hi[k] = std::max(hi[k], q[k]); }
+			}
+			for (int k = 0; k < 3; ++k) { m.pos[k] = lo[k]; m.pos[3 + k] = hi[k]; }
+		}
+	}
 	return buildAccel(ctx);
 }
 

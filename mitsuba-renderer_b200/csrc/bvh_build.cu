@@ -81,6 +81,14 @@ __global__ void k_prepare_tris(const uint4 *triIdx, const float4 *pos, const Sha
 			const float ar = fabsf(c.w);
 			lo[0] = __fsub_rn(c.x, ar); lo[1] = __fsub_rn(c.y, ar); lo[2] = __fsub_rn(c.z, ar);
 			hi[0] = __fadd_rn(c.x, ar); hi[1] = __fadd_rn(c.y, ar); hi[2] = __fadd_rn(c.z, ar);
+		} else if (t.y == 0xFFFFFFFEu) {
+			// instance of a shape group: its world box sits in the two vertices (Instance::getAABB); a_v = 1 marks the
+			// slot as an instance, b_nu carries the index into the instance table
+			const float4 a = pos[t.x], b = pos[t.z];
+			memset(&r, 0, sizeof(r));
+			r.k = 3u; r.a_v = 1.0f; r.b_nu = __uint_as_float(sh.cdfOffset);
+			r.shapeIndex = t.w; r.primIndex = 0xFFFFFFFFu;
+			lo[0] = a.x; lo[1] = a.y; lo[2] = a.z; hi[0] = b.x; hi[1] = b.y; hi[2] = b.z;
 		} else {
 			const float4 A = pos[t.x], B = pos[t.y], C = pos[t.z];
 			triAccelLoad(A, B, C, r);
@@ -90,7 +98,7 @@ __global__ void k_prepare_tris(const uint4 *triIdx, const float4 *pos, const Sha
 			lo[1] = fminf(A.y, fminf(B.y, C.y)); hi[1] = fmaxf(A.y, fmaxf(B.y, C.y));
 			lo[2] = fminf(A.z, fminf(B.z, C.z)); hi[2] = fmaxf(A.z, fmaxf(B.z, C.z));
 		}
-		if (sh.materialId < 0) r.k |= TRI_NONOCCLUDER;
+		if (sh.materialId < 0 && !sh.isInstance) r.k |= TRI_NONOCCLUDER;     // Instance::m_occluder = true (instance.cpp:25)
 		accelOrig[g] = r;
 		triLo[g] = make_float4(lo[0], lo[1], lo[2], 0);
 		triHi[g] = make_float4(hi[0], hi[1], hi[2], 0);
@@ -373,6 +381,11 @@ __global__ void k_shade_tris(const uint32_t *order, const uint4 *triIdx, const f
 		o[5] = make_float4(xf[14], xf[15], xf[16], xf[17]);                       // o2w[1][2], o2w[2][0..2]
 		return;
 	}
+	if (idx.y == 0xFFFFFFFEu) {                        // instance: only the shape index is read
+		o[0] = make_float4(0, 0, 0, __uint_as_float(idx.w));
+		for (int k = 1; k < 6; ++k) o[k] = make_float4(0, 0, 0, 0);
+		return;
+	}
 	const uint32_t prim = g - shapes[idx.w].triOffset;
 	const float4 p0 = positions[idx.x], p1 = positions[idx.y], p2 = positions[idx.z];
 	const float4 n0 = normals[idx.x], n1 = normals[idx.y], n2 = normals[idx.z];
@@ -624,6 +637,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	std::vector<int> emitterShape(ctx->emitters.size(), -1);
 	size_t tOff = 0, vOff = 0;
 	bool anySphere = false;
+	std::vector<InstanceDev> instances;
 	std::vector<float> sphereXf;      // per sphere: worldToObject 3x3, objectToWorld 3x3, inverted, pad
 	for (size_t s = 0; s < nShapes; ++s) {
 		const HostMesh &m = ctx->meshes[s];
@@ -634,6 +648,13 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		si.nTri = m.nTri; si.nVert = m.nVert; si.hasNormals = m.hasNormals ? 1u : 0u;
 		si.hasTexcoords = m.uv.empty() ? 0u : 1u;
 		si.hasTangents = meshTangents[s].empty() ? 0u : 1u;
+		if (m.instance) {
+			si.isInstance = 1u; anySphere = true;            // non-triangle primitive: the kernels' SPH variants
+			si.cdfOffset = (uint32_t) instances.size();
+			InstanceDev inst; memset(&inst, 0, sizeof(inst));
+			memcpy(inst.w2o, m.w2o, 64); memcpy(inst.o2w, m.o2w, 64); inst.group = (uint32_t) m.groupId;
+			instances.push_back(inst);
+		}
 		if (m.sphere) {
 			si.isSphere = 1u; anySphere = true;
 			si.cdfOffset = (uint32_t) (sphereXf.size() / 20);       // index into the sphere transform table
@@ -655,6 +676,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		}
 		for (uint32_t t = 0; t < m.nTri; ++t) {
 			if (m.sphere) { triIdx[tOff + t] = make_uint4((uint32_t) vOff, SPHERE_MARK, SPHERE_MARK, (uint32_t) s); continue; }
+			if (m.instance) { triIdx[tOff + t] = make_uint4((uint32_t) vOff, INSTANCE_MARK, (uint32_t) vOff + 1, (uint32_t) s); continue; }
 			for (int c = 0; c < 3; ++c)
 				REQUIRE(ctx, m.tri[3*t+c] < m.nVert, MTSGPU_ERR_ARG, "shape %zu: triangle %u references vertex %u >= %u", s, t, m.tri[3*t+c], m.nVert);
 			triIdx[tOff + t] = make_uint4((uint32_t) vOff + m.tri[3*t], (uint32_t) vOff + m.tri[3*t+1], (uint32_t) vOff + m.tri[3*t+2], (uint32_t) s);
@@ -785,6 +807,21 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dMipLevels.p, mipLevels.data(), mipLevels.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, ctx->dMipLut.alloc(sizeof(mipLut)));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dMipLut.p, mipLut, sizeof(mipLut), cudaMemcpyHostToDevice, st));
+	{
+		std::vector<DeviceScene> groupScenes;
+		for (mtsgpu_ctx *g : ctx->groups) groupScenes.push_back(g->scene);
+		if (instances.empty()) { groupScenes.clear(); }
+		CUDA_TRY(ctx, ctx->dInstances.alloc(std::max<size_t>(instances.size(), 1) * sizeof(InstanceDev)));
+		CUDA_TRY(ctx, ctx->dGroupScenes.alloc(std::max<size_t>(groupScenes.size(), 1) * sizeof(DeviceScene)));
+		if (!instances.empty()) {
+			for (const InstanceDev &i : instances)
+				REQUIRE(ctx, i.group < groupScenes.size() && ctx->groups[i.group]->built, MTSGPU_ERR_ARG, "instance of shape group %u, which is not built", i.group);
+			CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dInstances.p, instances.data(), instances.size() * sizeof(InstanceDev), cudaMemcpyHostToDevice, st));
+			CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dGroupScenes.p, groupScenes.data(), groupScenes.size() * sizeof(DeviceScene), cudaMemcpyHostToDevice, st));
+			CUDA_TRY(ctx, cudaStreamSynchronize(st));
+		}
+	}
+	ctx->scene.hasInstances = instances.empty() ? 0u : 1u;
 	CUDA_TRY(ctx, ctx->dEnvData.alloc(envData.size() * sizeof(float)));
 	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dEnvData.p, envData.data(), envData.size() * sizeof(float), cudaMemcpyHostToDevice, st));
 	CUDA_TRY(ctx, ctx->dCamera.alloc(sizeof(CameraDev)));
@@ -1002,6 +1039,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	sc.textures = ctx->dTextures.as<TextureDev>();
 	sc.texels = ctx->dTexels.as<float4>(); sc.mipLevels = ctx->dMipLevels.as<uint4>(); sc.mipLut = ctx->dMipLut.as<float>();
 	sc.camera = ctx->dCamera.as<CameraDev>(); sc.envData = ctx->dEnvData.as<float>();
+	sc.instances = ctx->dInstances.as<InstanceDev>(); sc.groups = ctx->dGroupScenes.as<DeviceScene>();
 	sc.shapes = ctx->dShapes.as<ShapeInfo>();
 	sc.materials = ctx->dMaterials.as<MaterialDev>();
 	sc.areaCdf = ctx->dAreaCdf.as<float>();

@@ -31,7 +31,11 @@ struct HostMesh {
 	std::vector<float> pos, nrm, uv; std::vector<uint32_t> tri;   // uv empty: no texture coordinates
 	// analytic sphere (mtsgpu_upload_sphere): one vertex (the centre) and one primitive {0, SPHERE_MARK, SPHERE_MARK}
 	bool sphere = false, inverted = false; float radius = 0, o2w[16] = {}, w2o[16] = {};
+	// instance of a shape group (mtsgpu_upload_instance): two vertices (the corners of its world box, filled at build
+	// time) and one primitive {0, INSTANCE_MARK, 1}; o2w / w2o as above
+	bool instance = false; int groupId = -1;
 };
+#define INSTANCE_MARK 0xFFFFFFFEu
 #define SPHERE_MARK 0xFFFFFFFFu
 
 // Linear RGB pixels of one BITMAP texture (what MIPMap::fromBitmap receives), top row first
@@ -55,6 +59,7 @@ struct mtsgpu_ctx {
 	std::vector<mtsgpu_emitter> emitters;
 	std::vector<mtsgpu_texture> textures;
 	std::vector<HostBitmap> bitmaps;          // parallel to textures; filled by mtsgpu_upload_bitmap
+	std::vector<mtsgpu_ctx *> groups;         // shape groups: child contexts with their own acceleration structure
 	HostBitmap envBitmap; int envEmitter = -1; float envL2W[9] = {}, envW2L[9] = {};   // mtsgpu_upload_envmap
 	uint32_t envTexture = 0;                  // index of the map's entry in the device texture table
 	std::vector<HostMesh> meshes;
@@ -68,7 +73,7 @@ struct mtsgpu_ctx {
 	bool built = false;
 	DeviceScene scene;
 	DevBuf dTriAccel, dTriAccelOrig, dNodes, dTriIdx, dPositions, dNormals, dShapes, dMaterials, dEmitters,
-	       dLumCdf, dAreaCdf, dTexcoords, dTextures, dTangents, dShadeTris, dSortedOf, dTexels, dMipLevels, dMipLut, dCamera, dEnvData;
+	       dLumCdf, dAreaCdf, dTexcoords, dTextures, dTangents, dShadeTris, dSortedOf, dTexels, dMipLevels, dMipLut, dCamera, dEnvData, dInstances, dGroupScenes;
 	mtsgpu_accel_info accel = {};
 
 	// trace staging + counters

@@ -50,6 +50,7 @@ struct WfArrays {
 	uint32_t *counters;               // [0] next-queue count, [1] shadow-queue count
 	// direct mode keeps the primary hit while secondary rays are traced
 	uint32_t *slotPrim; float4 *rayPrim; uint4 *hitPrim;
+	uint32_t capacity;                // the hit arrays are followed by `capacity` nested-triangle indices (instance hits)
 };
 
 struct BatchDesc {
@@ -135,17 +136,18 @@ k_generate(const CameraDev cam, const FilmDev film, const BatchDesc b, WfArrays 
 // override the choice for experiments.
 template <bool SPH>
 __global__ void __launch_bounds__(TRACE_BLOCK)
-k_closest_wf(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint4 *__restrict__ hits) {
+k_closest_wf(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint4 *__restrict__ hits, uint32_t *__restrict__ nestedOut) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
 	const uint32_t i = blockIdx.x * TRACE_BLOCK + threadIdx.x;
 	if (i >= n) return;
 	const float4 a = __ldg(rays + 2 * (size_t) i), b = __ldg(rays + 2 * (size_t) i + 1);
 	RayIn r = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
-	HitOut ho; ho.t = INFINITY; ho.u = ho.v = 0; ho.tri = 0xFFFFFFFFu;
+	HitOut ho; ho.t = INFINITY; ho.u = ho.v = 0; ho.tri = 0xFFFFFFFFu; ho.nested = 0xFFFFFFFFu;
 	float mint, maxt; uint32_t c0 = 0, c1 = 0;
 	if (clipToScene<false>(sc, r, mint, maxt))
 		traverse<false, false, SPH>(sc, r, mint, maxt, sstack, ho, c0, c1);
 	hits[i] = make_uint4(__float_as_uint(ho.t), __float_as_uint(ho.u), __float_as_uint(ho.v), ho.tri);
+	if (SPH && nestedOut) nestedOut[i] = ho.nested;
 }
 
 template <bool SPH>
@@ -240,7 +242,7 @@ __device__ __forceinline__ bool nextEvent(const DeviceScene &sc, const Integrato
 }
 
 // One shading step for the queue entry i. MODE 0 = path, 1 = direct (primary pass), 2 = direct (secondary pass).
-// BMP: the scene has bitmap textures (the variant without them carries none of the filtering code).
+// BMP: the scene has bitmap textures or instances (the variant without them carries none of that code).
 template <int MODE, bool BMP>
 #ifndef SHADE_MIN_BLOCKS
 #define SHADE_MIN_BLOCKS 6
@@ -273,7 +275,9 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		Isect its;
 		bool alive = valid;
 		if (valid) {
-			fillIntersectionSorted(sc, h.w, __uint_as_float(h.y), __uint_as_float(h.z), rayO, rayD, __uint_as_float(h.x), its);
+			uint32_t nested = 0xFFFFFFFFu;
+			if (BMP && sc.hasInstances) nested = reinterpret_cast<const uint32_t *>(hits + wf.capacity)[i];
+			fillIntersectionSorted(sc, h.w, __uint_as_float(h.y), __uint_as_float(h.z), rayO, rayD, __uint_as_float(h.x), its, nested);
 		}
 
 		if (MODE == 2) {
@@ -344,7 +348,8 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 					float lx = 0, ly = 0;
 					if (b.sampler.lensDraw) smp.get2D(DIM_LENS, lx, ly);
 					const float2 sp = wf.samplePos[slot];
-					duv = cameraHitPartials(sc, sp.x, sp.y, lx, ly, rayO, rayD, b.diffScale, h.w, __uint_as_float(h.y), __uint_as_float(h.z), its.p, its.geoN);
+					duv = cameraHitPartials(sc, sp.x, sp.y, lx, ly, rayO, rayD, b.diffScale, h.w, __uint_as_float(h.y), __uint_as_float(h.z), its.p, its.geoN,
+						sc.hasInstances ? reinterpret_cast<const uint32_t *>(hits + wf.capacity)[i] : 0xFFFFFFFFu);
 				}
 				resolveTextures<BMP>(sc, mat, its.uvx, its.uvy, duv);
 				if (its.emitterId >= 0 && (flags & PF_EMITTED) && (MODE == 0 || round == 0))
@@ -500,13 +505,17 @@ inline unsigned blocksFor(size_t n, unsigned bs) { return (unsigned) ((n + bs - 
 
 // Launch helpers: pick the traversal kernel variant per queue.
 static int launchClosestWf(mtsgpu_ctx *ctx, const float4 *rays, uint32_t n, uint4 *hits, bool persistent) {
+	if (ctx->scene.hasInstances) {     // instance hits also report the nested triangle: the lock-step kernel writes it behind the hits
+		k_closest_wf<true><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, reinterpret_cast<uint32_t *>(hits + ctx->pathCapacity));
+		return MTSGPU_OK;
+	}
 	if (persistent) {
 		uint32_t *rc = nullptr; int e = traceRayCounter(ctx, &rc); if (e) return e;
 		if (ctx->scene.hasSpheres) k_closest_wfp<true><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, rc);
 		else k_closest_wfp<false><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, rc);
 	} else {
-		if (ctx->scene.hasSpheres) k_closest_wf<true><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits);
-		else k_closest_wf<false><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits);
+		if (ctx->scene.hasSpheres) k_closest_wf<true><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, nullptr);
+		else k_closest_wf<false><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, nullptr);
 	}
 	return MTSGPU_OK;
 }
@@ -527,7 +536,7 @@ static int ensureWavefront(mtsgpu_ctx *ctx, uint32_t capacity) {
 	const size_t c = capacity;
 	CUDA_TRY(ctx, ctx->dPathState.alloc(c * (16 * 3 + 8)));
 	CUDA_TRY(ctx, ctx->dRayA.alloc(c * 32)); CUDA_TRY(ctx, ctx->dRayB.alloc(c * 32));
-	CUDA_TRY(ctx, ctx->dHit.alloc(c * 16));
+	CUDA_TRY(ctx, ctx->dHit.alloc(c * 20));                 // uint4 hits + one nested-triangle index each
 	CUDA_TRY(ctx, ctx->dShadowRay.alloc(c * 32)); CUDA_TRY(ctx, ctx->dShadowPayload.alloc(c * 16));
 	CUDA_TRY(ctx, ctx->dQueueA.alloc(c * 4)); CUDA_TRY(ctx, ctx->dQueueB.alloc(c * 4));
 	CUDA_TRY(ctx, ctx->dQueueCounts.alloc(64));
@@ -611,7 +620,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 		if (P->mode == MTSGPU_MODE_DIRECT) {
 			CUDA_TRY(ctx, dPrimSlot.alloc((size_t) ctx->pathCapacity * 4));
 			CUDA_TRY(ctx, dPrimRay.alloc((size_t) ctx->pathCapacity * 32));
-			CUDA_TRY(ctx, dPrimHit.alloc((size_t) ctx->pathCapacity * 16));
+			CUDA_TRY(ctx, dPrimHit.alloc((size_t) ctx->pathCapacity * 20));
 		}
 		// the camera behind DeviceScene::camera (ray differentials for bitmap textures)
 		CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dCamera.p, &ctx->camera, sizeof(CameraDev), cudaMemcpyHostToDevice, st));
@@ -619,7 +628,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 		char *ps = ctx->dPathState.as<char>();
 		wf.thr = (float4 *) ps; wf.li = (float4 *) (ps + (size_t) capacity * 16); wf.bsdfVal = (float4 *) (ps + (size_t) capacity * 32);
 		wf.samplePos = (float2 *) (ps + (size_t) capacity * 48);
-		wf.hit = ctx->dHit.as<uint4>();
+		wf.hit = ctx->dHit.as<uint4>(); wf.capacity = ctx->pathCapacity;
 		wf.shadowRay = ctx->dShadowRay.as<float4>(); wf.shadowPayload = ctx->dShadowPayload.as<float4>();
 		wf.counters = ctx->dQueueCounts.as<uint32_t>();
 		wf.slotPrim = dPrimSlot.as<uint32_t>(); wf.rayPrim = dPrimRay.as<float4>(); wf.hitPrim = dPrimHit.as<uint4>();
@@ -628,6 +637,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 
 		bool bmp = false;
 		for (const mtsgpu_texture &t : ctx->textures) bmp |= t.type == MTSGPU_TEXTURE_BITMAP;
+		bmp |= ctx->scene.hasInstances != 0;          // the same variant also shades instance hits
 		IntegratorDev ig;
 		ig.mode = P->mode; ig.maxDepth = P->maxDepth; ig.rrDepth = P->rrDepth; ig.strictNormals = P->strictNormals;
 		ig.nLum = P->luminaireSamples; ig.nBsdf = P->bsdfSamples; ig.importance = (int) P->importanceSampleLuminaires;

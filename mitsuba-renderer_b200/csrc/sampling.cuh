@@ -272,16 +272,55 @@ __device__ inline void fillSphereIntersection(const DeviceScene &sc, const float
 	its.shape = shape; its.materialId = si.materialId; its.emitterId = si.emitterId;
 }
 
-__device__ inline void fillIntersectionSorted(const DeviceScene &sc, uint32_t tri, float u, float v, V3 rayO, V3 rayD, float t, Isect &its) {
+// Triangle part of ShapeKDTree::fillIntersectionRecord<BARY> (skdtree.h:352-432) from the six float4 of a shading record
+template <bool BARY>
+__device__ __forceinline__ void fillMeshIntersection(const DeviceScene &sc, const ShapeInfo &si, uint32_t shape, const float4 &r0, const float4 &r1,
+		const float4 &r2, const float4 &r3, const float4 &r4, const float4 &r5, float u, float v, V3 rayO, V3 rayD, float t, Isect &its);
+
+// Instance::fillIntersectionRecord (instance.cpp:88-98): the group's own record for the nested triangle — position
+// ray(t) on the WORLD ray (fillIntersectionRecord<false>), everything else in object space — then the frames taken to
+// world space: normals through the inverse transpose, tangents through the matrix, each renormalised; the geometric
+// frame is rebuilt around its transformed normal; wi is expressed in the transformed (not necessarily orthogonal) frame.
+__device__ __noinline__ void fillInstanceIntersection(const DeviceScene &sc, const ShapeInfo &outer, uint32_t shape, uint32_t nested,
+		float u, float v, V3 rayO, V3 rayD, float t, Isect &its) {
+	const InstanceDev &inst = sc.instances[outer.cdfOffset];
+	const DeviceScene &gs = sc.groups[inst.group];
+	const float4 *rec = gs.shadeTris + (size_t) nested * 6;
+	const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2), r3 = __ldg(rec + 3), r4 = __ldg(rec + 4), r5 = __ldg(rec + 5);
+	const uint32_t gshape = __float_as_uint(r0.w);
+	const ShapeInfo gsi = gs.shapes[gshape];
+	fillMeshIntersection<false>(gs, gsi, gshape, r0, r1, r2, r3, r4, r5, u, v, rayO, rayD, t, its);
+	const float *M = inst.o2w, *I = inst.w2o;
+	auto xfVec = [&](V3 a) { return v3(M[0] * a.x + M[1] * a.y + M[2] * a.z, M[4] * a.x + M[5] * a.y + M[6] * a.z, M[8] * a.x + M[9] * a.y + M[10] * a.z); };
+	auto xfNrm = [&](V3 a) { return v3(I[0] * a.x + I[4] * a.y + I[8] * a.z, I[1] * a.x + I[5] * a.y + I[9] * a.z, I[2] * a.x + I[6] * a.y + I[10] * a.z); };
+	its.sh.n = normalize(xfNrm(its.sh.n));
+	its.sh.s = normalize(xfVec(its.sh.s));
+	its.sh.t = normalize(xfVec(its.sh.t));
+	its.shN = its.sh.n;
+	its.geoN = normalize(xfNrm(its.geoN));
+	its.wi = toLocal(its.sh, -rayD);
+	its.shape = shape; its.emitterId = -1;
+}
+
+__device__ inline void fillIntersectionSorted(const DeviceScene &sc, uint32_t tri, float u, float v, V3 rayO, V3 rayD, float t, Isect &its,
+		uint32_t nested = 0xFFFFFFFFu) {
 	const float4 *rec = sc.shadeTris + (size_t) tri * 6;
 	const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2), r3 = __ldg(rec + 3), r4 = __ldg(rec + 4), r5 = __ldg(rec + 5);
 	const uint32_t shape = __float_as_uint(r0.w);
 	const ShapeInfo si = sc.shapes[shape];
 	if (si.isSphere) { fillSphereIntersection(sc, r0, r1, r2, r3, r4, r5, rayO, rayD, t, its); return; }
+	if (si.isInstance) { fillInstanceIntersection(sc, si, shape, nested, u, v, rayO, rayD, t, its); return; }
+	fillMeshIntersection<true>(sc, si, shape, r0, r1, r2, r3, r4, r5, u, v, rayO, rayD, t, its);
+}
+
+template <bool BARY>
+__device__ __forceinline__ void fillMeshIntersection(const DeviceScene &sc, const ShapeInfo &si, uint32_t shape, const float4 &r0, const float4 &r1,
+		const float4 &r2, const float4 &r3, const float4 &r4, const float4 &r5, float u, float v, V3 rayO, V3 rayD, float t, Isect &its) {
 	const uint4 idx = make_uint4(__float_as_uint(r2.w), __float_as_uint(r3.w), __float_as_uint(r4.w), shape);
 	const V3 p0 = v3(r0), p1 = v3(r1), p2 = v3(r2);
 	const float bx = 1 - u - v, by = u, bz = v;
-	its.p = p0 * bx + p1 * by + p2 * bz;      // barycentric position, NOT o + t*d
+	if (BARY) its.p = p0 * bx + p1 * by + p2 * bz;      // barycentric position, NOT o + t*d
+	else its.p = rayO + rayD * t;                       // ray(its.t) (skdtree.h:375-376)
 	V3 fn = cross(p1 - p0, p2 - p0);
 	const float len = length(fn);
 	if (!isZero(fn)) fn = fn * (1.0f / len);
@@ -317,7 +356,23 @@ __device__ inline void fillIntersectionSorted(const DeviceScene &sc, uint32_t tr
 __device__ inline void fillIntersection(const DeviceScene &sc, uint32_t shape, uint32_t prim, float u, float v,
 		V3 rayO, V3 rayD, float t, Isect &its) {
 	const ShapeInfo si = sc.shapes[shape];
-	fillIntersectionSorted(sc, __ldg(sc.sortedOf + si.triOffset + (si.isSphere ? 0u : prim)), u, v, rayO, rayD, t, its);
+	uint32_t nested = 0xFFFFFFFFu;
+#ifdef MTSGPU_HAVE_TRACE
+	if (si.isInstance) {
+		// the C ABI's hit names the instance only: find the nested triangle again by intersecting the group inside
+		// the one-ulp interval [t-, t] — the same arithmetic as the original query, so the same triangle answers
+		// (nothing else can lie in it: t was the closest hit)
+		const RayIn r = { rayO.x, rayO.y, rayO.z, 0.0f, rayD.x, rayD.y, rayD.z, INFINITY };
+		float t2, u2, v2;
+		if (instanceTest<false>(sc, si.cdfOffset, r, nextafterf(t, 0.0f), t, t2, u2, v2, nested)) { u = u2; v = v2; }
+		if (nested == 0xFFFFFFFFu) {             // cannot happen for a hit this library reported
+			its.p = its.geoN = its.shN = its.wi = v3(0, 0, 0); its.uvx = its.uvy = 0; its.sh = makeFrame(v3(0, 0, 1));
+			its.shape = shape; its.materialId = -1; its.emitterId = -1;
+			return;
+		}
+	}
+#endif
+	fillIntersectionSorted(sc, __ldg(sc.sortedOf + si.triOffset + ((si.isSphere || si.isInstance) ? 0u : prim)), u, v, rayO, rayD, t, its, nested);
 }
 
 // ---- textures: Texture2D::getValue (texture.cpp:73-82) + Checkerboard::getValue (checkerboard.cpp:47-55) ----------
@@ -441,7 +496,7 @@ __device__ __noinline__ V3 bitmapValue(const DeviceScene &sc, const TextureDev &
 // sample's raster position and lens sample, and dpdu / dpdv from the hit's shading record: this runs once per path,
 // at the first hit, and only on surfaces with a bitmap texture. `tri` is the sorted triangle index of the hit.
 __device__ __noinline__ float4 cameraHitPartials(const DeviceScene &sc, float sx, float sy, float lx, float ly,
-		V3 rayO, V3 rayD, float diffScale, uint32_t tri, float bu, float bv, V3 p, V3 geoN) {
+		V3 rayO, V3 rayD, float diffScale, uint32_t tri, float bu, float bv, V3 p, V3 geoN, uint32_t nested = 0xFFFFFFFFu) {
 	const float4 zero = make_float4(0, 0, 0, 0);
 	// ---- its.dpdu, its.dpdv (skdtree.h:385-406 for meshes, sphere.cpp:146-165 for spheres)
 	const float4 *rec = sc.shadeTris + (size_t) tri * 6;
@@ -461,6 +516,21 @@ __device__ __noinline__ float4 cameraHitPartials(const DeviceScene &sc, float sx
 		if (zrad > 0) { const float invZRad = 1.0f / zrad; cosPhi = local.x * invZRad; sinPhi = local.y * invZRad; }
 		const V3 dv = v3(local.z * cosPhi, local.z * sinPhi, -mts_sin(theta) * radius) * MTS_PI;
 		dpdv = v3(r3.w * dv.x + r4.x * dv.y + r4.y * dv.z, r4.z * dv.x + r4.w * dv.y + r5.x * dv.z, r5.y * dv.x + r5.z * dv.y + r5.w * dv.z);
+	} else if (si.isInstance) {
+		// Instance::fillIntersectionRecord (instance.cpp:96-97): the group's dpdu / dpdv through objectToWorld
+		const InstanceDev &inst = sc.instances[si.cdfOffset];
+		const DeviceScene &gs = sc.groups[inst.group];
+		const float4 *grec = gs.shadeTris + (size_t) nested * 6;
+		const ShapeInfo gsi = gs.shapes[__float_as_uint(__ldg(grec).w)];
+		if (nested != 0xFFFFFFFFu && gsi.hasNormals && gsi.hasTangents) {
+			const uint32_t i0 = __float_as_uint(__ldg(grec + 2).w), i1 = __float_as_uint(__ldg(grec + 3).w), i2 = __float_as_uint(__ldg(grec + 4).w);
+			const float bx = 1 - bu - bv, by = bu, bz = bv;
+			const V3 du = v3(__ldg(gs.tangents + 2 * i0)) * bx + v3(__ldg(gs.tangents + 2 * i1)) * by + v3(__ldg(gs.tangents + 2 * i2)) * bz;
+			const V3 dv = v3(__ldg(gs.tangents + 2 * i0 + 1)) * bx + v3(__ldg(gs.tangents + 2 * i1 + 1)) * by + v3(__ldg(gs.tangents + 2 * i2 + 1)) * bz;
+			const float *M = inst.o2w;
+			dpdu = v3(M[0] * du.x + M[1] * du.y + M[2] * du.z, M[4] * du.x + M[5] * du.y + M[6] * du.z, M[8] * du.x + M[9] * du.y + M[10] * du.z);
+			dpdv = v3(M[0] * dv.x + M[1] * dv.y + M[2] * dv.z, M[4] * dv.x + M[5] * dv.y + M[6] * dv.z, M[8] * dv.x + M[9] * dv.y + M[10] * dv.z);
+		}
 	} else if (si.hasNormals && si.hasTangents) {
 		const uint32_t i0 = __float_as_uint(r2.w), i1 = __float_as_uint(r3.w), i2 = __float_as_uint(r4.w);
 		const float bx = 1 - bu - bv, by = bu, bz = bv;

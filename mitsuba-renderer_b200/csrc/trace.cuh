@@ -9,6 +9,7 @@
 // and ids agree except when two triangles yield a bit-identical t (documented tie class).
 #pragma once
 #include "types.cuh"
+#define MTSGPU_HAVE_TRACE 1
 
 #define TRACE_BLOCK        128
 #define TRACE_SMEM_STACK   20      // entries per thread kept in shared memory
@@ -107,14 +108,123 @@ __device__ __forceinline__ bool sphereTest(const float4 &q0, const float4 &q1, c
 	return true;
 }
 
+// ---- instances of shape groups (src/shapes/instance.cpp) ---------------------------------------------------------
+// A group's acceleration structure, walked with a stack in local memory only (the caller's shared stack is live).
+// Same node layout, same interval rules and the same TriAccel test as traverse() below; groups hold triangles only.
+#define GROUP_STACK 64
+template <bool SHADOW>
+__device__ __noinline__ bool traverseGroup(const DeviceScene &gs, const RayIn &r, float mint, float maxt, float &hitT, float &hitU, float &hitV, uint32_t &hitTri) {
+	uint2 stack[GROUP_STACK];
+	int sp = 0;
+	const float dx = r.dx, dy = r.dy, dz = r.dz;
+	const float idx = 1.0f / (fabsf(dx) > 1e-20f ? dx : copysignf(1e-20f, dx)), idy = 1.0f / (fabsf(dy) > 1e-20f ? dy : copysignf(1e-20f, dy)),
+		idz = 1.0f / (fabsf(dz) > 1e-20f ? dz : copysignf(1e-20f, dz));
+	const float oix = r.ox * idx, oiy = r.oy * idy, oiz = r.oz * idz;
+	bool found = false;
+	uint32_t cur = 0;                 // root node
+	while (true) {
+		if (!(cur & BVH_LEAF)) {
+			const float4 *np = gs.nodes + (size_t) cur * 8;
+			const float4 lo[3] = { __ldg(np + 0), __ldg(np + 1), __ldg(np + 2) }, hi[3] = { __ldg(np + 3), __ldg(np + 4), __ldg(np + 5) };
+			const uint4 child = __ldg(reinterpret_cast<const uint4 *>(np + 6));
+			const uint32_t cw[4] = { child.x, child.y, child.z, child.w };
+			const float lx[4] = { lo[0].x, lo[0].y, lo[0].z, lo[0].w }, ly[4] = { lo[1].x, lo[1].y, lo[1].z, lo[1].w }, lz[4] = { lo[2].x, lo[2].y, lo[2].z, lo[2].w };
+			const float hx[4] = { hi[0].x, hi[0].y, hi[0].z, hi[0].w }, hy[4] = { hi[1].x, hi[1].y, hi[1].z, hi[1].w }, hz[4] = { hi[2].x, hi[2].y, hi[2].z, hi[2].w };
+			uint32_t next = BVH_EMPTY; float nextT = INFINITY;
+#pragma unroll
+			for (int i = 0; i < 4; ++i) {
+				const float t0x = fmaf(lx[i], idx, -oix), t1x = fmaf(hx[i], idx, -oix);
+				const float t0y = fmaf(ly[i], idy, -oiy), t1y = fmaf(hy[i], idy, -oiy);
+				const float t0z = fmaf(lz[i], idz, -oiz), t1z = fmaf(hz[i], idz, -oiz);
+				const float tnear = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), mint));
+				const float tfar = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), maxt));
+				if (!(tnear <= tfar)) continue;
+				if (tnear < nextT) {                     // keep the nearest child, push the one it displaces
+					if (next != BVH_EMPTY && sp < GROUP_STACK) stack[sp++] = make_uint2(next, __float_as_uint(nextT));
+					next = cw[i]; nextT = tnear;
+				} else if (sp < GROUP_STACK) stack[sp++] = make_uint2(cw[i], __float_as_uint(tnear));
+			}
+			if (next != BVH_EMPTY) { cur = next; continue; }
+		} else {
+			const uint32_t first = cur & 0x0FFFFFFFu, count = ((cur >> 28) & 7u) + 1u;
+			for (uint32_t i = 0; i < count; ++i) {
+				const float4 *tp = gs.triAccel + (size_t) (first + i) * 3;
+				const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+				const uint32_t kraw = __float_as_uint(q0.x);
+				if (SHADOW && (kraw & TRI_NONOCCLUDER)) continue;
+				float u, v, t;
+				if (triAccelTest(q0, q1, q2, kraw & TRI_K_MASK, r, mint, maxt, u, v, t)) {
+					if (SHADOW) return true;
+					maxt = t; found = true;
+					hitT = t; hitU = u; hitV = v; hitTri = first + i;
+				}
+			}
+		}
+		while (true) {
+			if (sp == 0) return found;
+			const uint2 e = stack[--sp];
+			if (!SHADOW && __uint_as_float(e.y) > maxt) continue;
+			cur = e.x;
+			break;
+		}
+	}
+}
+
+// Instance::rayIntersect (instance.cpp:72-86): the ray goes to object space through Transform::operator()(Ray)
+// (transform.h:219-235: origin as a point, direction as a vector, NOT renormalised, so t keeps its meaning), then
+// ShapeKDTree::rayIntersect(ray, mint, maxt, t, temp) (skdtree.h:435-466): clip to the group's box, tighten with the
+// caller's interval, closest hit (or any hit) inside it.
+template <bool SHADOW>
+__device__ __noinline__ bool instanceTest(const DeviceScene &sc, uint32_t instIndex, const RayIn &r, float mint, float maxt,
+		float &t, float &u, float &v, uint32_t &nested) {
+	const InstanceDev &inst = sc.instances[instIndex];
+	const float *M = inst.w2o;
+	RayIn o;
+	o.ox = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(M[0], r.ox), __fmul_rn(M[1], r.oy)), __fmul_rn(M[2], r.oz)), M[3]);
+	o.oy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(M[4], r.ox), __fmul_rn(M[5], r.oy)), __fmul_rn(M[6], r.oz)), M[7]);
+	o.oz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(M[8], r.ox), __fmul_rn(M[9], r.oy)), __fmul_rn(M[10], r.oz)), M[11]);
+	const float w = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(M[12], r.ox), __fmul_rn(M[13], r.oy)), __fmul_rn(M[14], r.oz)), M[15]);
+	if (w != 1.0f) { const float rw = __frcp_rn(w); o.ox = __fmul_rn(o.ox, rw); o.oy = __fmul_rn(o.oy, rw); o.oz = __fmul_rn(o.oz, rw); }
+	o.dx = __fadd_rn(__fadd_rn(__fmul_rn(M[0], r.dx), __fmul_rn(M[1], r.dy)), __fmul_rn(M[2], r.dz));
+	o.dy = __fadd_rn(__fadd_rn(__fmul_rn(M[4], r.dx), __fmul_rn(M[5], r.dy)), __fmul_rn(M[6], r.dz));
+	o.dz = __fadd_rn(__fadd_rn(__fmul_rn(M[8], r.dx), __fmul_rn(M[9], r.dy)), __fmul_rn(M[10], r.dz));
+	o.mint = r.mint; o.maxt = r.maxt;
+	const DeviceScene &gs = sc.groups[inst.group];
+	float nearT = -INFINITY, farT = INFINITY;
+	const float oo[3] = { o.ox, o.oy, o.oz }, dd[3] = { o.dx, o.dy, o.dz };
+#pragma unroll
+	for (int i = 0; i < 3; ++i) {                              // AABB::rayIntersect (aabb.h:349-382)
+		const float minVal = gs.aabbMin[i], maxVal = gs.aabbMax[i];
+		if (dd[i] == 0) {
+			if (oo[i] < minVal || oo[i] > maxVal) return false;
+		} else {
+			const float rcp = __frcp_rn(dd[i]);
+			float t1 = __fmul_rn(__fsub_rn(minVal, oo[i]), rcp), t2 = __fmul_rn(__fsub_rn(maxVal, oo[i]), rcp);
+			if (t1 > t2) { const float tmp = t1; t1 = t2; t2 = tmp; }
+			nearT = (nearT < t1) ? t1 : nearT;
+			farT = (t2 < farT) ? t2 : farT;
+			if (nearT > farT) return false;
+		}
+	}
+	if (mint > nearT) nearT = mint;
+	if (maxt < farT) farT = maxt;
+	if (!(farT > nearT)) return false;
+	return traverseGroup<SHADOW>(gs, o, nearT, farT, t, u, v, nested);
+}
+
 template <bool SHADOW, bool SPH>
-__device__ __forceinline__ bool primTest(const float4 &q0, const float4 &q1, const float4 &q2, uint32_t kraw, const RayIn &r,
-		float mint, float maxt, float &u, float &v, float &t) {
-	if (SPH && (kraw & TRI_K_MASK) == TRI_K_SPHERE) { u = v = 0.0f; return sphereTest<SHADOW>(q0, q1, r, mint, maxt, t); }
+__device__ __forceinline__ bool primTest(const DeviceScene &sc, const float4 &q0, const float4 &q1, const float4 &q2, uint32_t kraw, const RayIn &r,
+		float mint, float maxt, float &u, float &v, float &t, uint32_t &nested) {
+	if (SPH && (kraw & TRI_K_MASK) == TRI_K_SPHERE) {
+		u = v = 0.0f;
+		if (q1.y != 0.0f) return instanceTest<SHADOW>(sc, __float_as_uint(q1.z), r, mint, maxt, t, u, v, nested);   // a_v = 1: an instance
+		return sphereTest<SHADOW>(q0, q1, r, mint, maxt, t);
+	}
 	return triAccelTest(q0, q1, q2, kraw & TRI_K_MASK, r, mint, maxt, u, v, t);
 }
 
-struct HitOut { float t, u, v; uint32_t tri; };   // tri = index into the sorted TriAccel array
+struct HitOut { float t, u, v; uint32_t tri; uint32_t nested; };   // tri = index into the sorted TriAccel array; nested: for an instance
+                                                                  // hit, the sorted triangle index inside its group (else 0xFFFFFFFF)
 
 #define SSTACK(i) sstack[(i) * TRACE_BLOCK + threadIdx.x]
 
@@ -149,7 +259,7 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 	const float oix = r.ox * idx, oiy = r.oy * idy, oiz = r.oz * idz;
 	bool found = false;
 	uint32_t cur = 0;                 // root node
-	hit.t = INFINITY; hit.u = hit.v = 0; hit.tri = 0xFFFFFFFFu;
+	hit.t = INFINITY; hit.u = hit.v = 0; hit.tri = 0xFFFFFFFFu; hit.nested = 0xFFFFFFFFu;
 
 	while (true) {
 		if (!(cur & BVH_LEAF)) {
@@ -203,10 +313,12 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 				if (SHADOW && (kraw & TRI_NONOCCLUDER)) continue;
 				if (COUNT) triTests++;
 				float u, v, t;
-				if (primTest<SHADOW, SPH>(q0, q1, q2, kraw, r, mint, maxt, u, v, t)) {
+				uint32_t nested = 0xFFFFFFFFu;
+				if (primTest<SHADOW, SPH>(sc, q0, q1, q2, kraw, r, mint, maxt, u, v, t, nested)) {
 					if (SHADOW) return true;
 					maxt = t; found = true;            // sahkdtree3.h:278-283: later equal t replaces earlier
 					hit.t = t; hit.u = u; hit.v = v; hit.tri = first + i;
+					if (SPH) hit.nested = nested;
 				}
 			}
 		}
@@ -383,7 +495,8 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 						if (SHADOW && (kraw & TRI_NONOCCLUDER)) continue;
 						if (COUNT) triTests++;
 						float u, v, t;
-						if (primTest<SHADOW, SPH>(q0, q1, q2, kraw, s.r, s.mint, s.maxt, u, v, t)) {
+						uint32_t nestedUnused = 0xFFFFFFFFu;     // scenes with instances take the lock-step kernels
+						if (primTest<SHADOW, SPH>(sc, q0, q1, q2, kraw, s.r, s.mint, s.maxt, u, v, t, nestedUnused)) {
 							s.found = true;
 							if (SHADOW) break;
 							s.maxt = t;                    // sahkdtree3.h:278-283: a later equal t replaces an earlier one

@@ -42,7 +42,11 @@ struct ShapeInfo {
 	uint32_t hasTexcoords;
 	uint32_t hasTangents;     // per-vertex dpdu present (TriMesh::computeTangentSpaceBasis ran for this mesh)
 	uint32_t isSphere;        // analytic sphere (src/shapes/sphere.cpp): one primitive, no mesh arrays
+	uint32_t isInstance;      // instance of a shape group (src/shapes/instance.cpp): one primitive; cdfOffset = index into DeviceScene::instances
 };
+
+// Instance of a shape group: both matrices of its Transform, and which group (DeviceScene::groups) it shows
+struct InstanceDev { float w2o[16]; float o2w[16]; uint32_t group; uint32_t pad[3]; };
 
 struct MaterialDev { uint32_t type; float p[16]; uint32_t tex[2]; uint32_t pad; };   // tex: 0 constant, k: textures[k-1]
 struct TextureDev { uint32_t type; float p[12]; uint32_t pad[3]; };
@@ -79,6 +83,9 @@ struct DeviceScene {
 	const float4 *texels;       // mip pyramids of the bitmap textures (rgb + pad per texel)
 	const uint4 *mipLevels;     // {offset into texels, width, height, -} per level; TextureDev::pad = {first level, count}
 	const float *mipLut;        // MIPMap's EWA weight table, 128 entries
+	const InstanceDev *instances;            // instances of shape groups (empty unless hasInstances)
+	const struct DeviceScene *groups;        // the groups' own scenes: acceleration structure and shading records in object space
+	uint32_t hasInstances, padInst;
 	const float *envData;       // environment map: worldToLuminaire 3x3, luminaireToWorld 3x3, density resolution, CDF, pdf (sampling.cuh)
 	const struct CameraDev *camera;   // the render's camera: ray differentials of a camera-ray hit are rebuilt from it
 	const ShapeInfo *shapes;

@@ -283,6 +283,7 @@ class Shape:
     emitter: int = -1                # index into SceneDesc.emitters, -1: none
     texcoords: Optional[np.ndarray] = None   # float32 [nVert, 2] or None (uv = 0 everywhere, skdtree.h:414)
     sphere: Optional[tuple] = None           # (center xyz, radius, inverted): analytic sphere (src/shapes/sphere.cpp); no arrays
+    instance: Optional[tuple] = None         # (group index, toWorld 4x4): instance of SceneDesc.groups[index] (src/shapes/instance.cpp)
 
 
 def sphere_shape(center, radius, material=-1, inverted=False, emitter=-1) -> "Shape":
@@ -291,6 +292,13 @@ def sphere_shape(center, radius, material=-1, inverted=False, emitter=-1) -> "Sh
     c = np.asarray(center, np.float32)
     box = np.stack([c - np.float32(abs(radius)), c + np.float32(abs(radius))]).astype(np.float32)
     return Shape(box, np.zeros((0, 3), np.uint32), None, material=material, emitter=emitter, sphere=(tuple(float(v) for v in c), float(radius), bool(inverted)))
+
+
+def instance_shape(group, to_world, bounds) -> "Shape":
+    """<shape type="instance"> of shape group `group` under `to_world`. `bounds` (two points) stands in for positions so
+    that scene-bound helpers keep working."""
+    m = np.asarray(to_world, np.float32).reshape(4, 4)
+    return Shape(np.asarray(bounds, np.float32).reshape(2, 3), np.zeros((0, 3), np.uint32), None, instance=(int(group), m))
 
 
 @dataclass
@@ -318,6 +326,7 @@ class SceneDesc:
     materials: List[Material] = field(default_factory=list)
     emitters: List[Emitter] = field(default_factory=list)
     textures: List[Texture] = field(default_factory=list)
+    groups: List[List[Shape]] = field(default_factory=list)     # shape groups (src/shapes/shapegroup.cpp): meshes in object space
     shapes: List[Shape] = field(default_factory=list)
 
     @property
@@ -388,7 +397,7 @@ def write_scene(path: str, scene: SceneDesc) -> None:
     cx, cy, cw, ch = scene.crop_rect
     with open(path, "wb") as f:
         f.write(b"MTSB200\0")
-        f.write(struct.pack("<I", 7))
+        f.write(struct.pack("<I", 8))
         f.write(np.ascontiguousarray(scene.camera_to_world, np.float32).tobytes())
         f.write(struct.pack("<5fI", scene.fov, scene.near_clip, scene.far_clip, scene.aperture_radius,
                             scene.focus_depth, int(scene.map_smaller_side)))
@@ -418,13 +427,7 @@ def write_scene(path: str, scene: SceneDesc) -> None:
                 rgba = np.concatenate([e.pixels, np.ones(e.pixels.shape[:2] + (1,), np.float32)], axis=2)
                 api.write_exr(exr.decode(), rgba)
                 f.write(struct.pack("<I", len(exr))); f.write(exr)
-        f.write(struct.pack("<I", len(scene.shapes)))
-        for s in scene.shapes:
-            f.write(struct.pack("<I", 0 if s.sphere is None else 1))
-            if s.sphere is not None:
-                (cx, cy, cz), radius, inverted = s.sphere
-                f.write(struct.pack("<2i4fI", s.material, s.emitter, cx, cy, cz, radius, int(inverted)))
-                continue
+        def write_mesh(s):
             f.write(struct.pack("<2I2i2I", len(s.positions), len(s.triangles), s.material, s.emitter,
                                 0 if s.normals is None else 1, 0 if s.texcoords is None else 1))
             f.write(np.ascontiguousarray(s.positions, np.float32).tobytes())
@@ -433,3 +436,20 @@ def write_scene(path: str, scene: SceneDesc) -> None:
             if s.texcoords is not None:
                 f.write(np.ascontiguousarray(s.texcoords, np.float32).tobytes())
             f.write(np.ascontiguousarray(s.triangles, np.uint32).tobytes())
+        f.write(struct.pack("<I", len(scene.groups)))
+        for g in scene.groups:
+            f.write(struct.pack("<I", len(g)))
+            for s in g:
+                write_mesh(s)
+        f.write(struct.pack("<I", len(scene.shapes)))
+        for s in scene.shapes:
+            if s.instance is not None:
+                f.write(struct.pack("<2I", 2, s.instance[0]))
+                f.write(np.ascontiguousarray(s.instance[1], np.float32).tobytes())
+                continue
+            f.write(struct.pack("<I", 0 if s.sphere is None else 1))
+            if s.sphere is not None:
+                (cx, cy, cz), radius, inverted = s.sphere
+                f.write(struct.pack("<2i4fI", s.material, s.emitter, cx, cy, cz, radius, int(inverted)))
+                continue
+            write_mesh(s)

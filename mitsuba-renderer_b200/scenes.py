@@ -9,7 +9,7 @@ import numpy as np
 
 from .scenefile import (SceneDesc, Shape, Emitter, lambertian, microfacet, mirror, roughmetal,
                         dielectric, twosided, phong, roughglass, look_at, point_light, spot_light, directional_light,
-                        constant_light, envmap_light, add_light, checkerboard, textured, ward, sphere_shape, bitmap_texture, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
+                        constant_light, envmap_light, add_light, checkerboard, textured, ward, sphere_shape, instance_shape, bitmap_texture, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
                         WRAP_REPEAT, WRAP_BLACK, WRAP_WHITE, WRAP_CLAMP, MODE_PATH, MODE_DIRECT, FILTER_BOX)
 
 F32 = np.float32
@@ -227,6 +227,46 @@ def envmap_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6, 
         rx = np.array([[1, 0, 0, 0], [0, np.cos(b), -np.sin(b), 0], [0, np.sin(b), np.cos(b), 0], [0, 0, 0, 1]], F32)
         m = (ry @ rx).astype(F32)
     add_light(s, envmap_light(_sky_image(64, 32, 7), 1.5, m, sampling_weight=2.0))
+    return s
+
+
+def _xform(scale=(1, 1, 1), rot_y=0.0, rot_x=0.0, translate=(0, 0, 0)):
+    a, b = F32(rot_y), F32(rot_x)
+    ry = np.array([[np.cos(a), 0, np.sin(a), 0], [0, 1, 0, 0], [-np.sin(a), 0, np.cos(a), 0], [0, 0, 0, 1]], F32)
+    rx = np.array([[1, 0, 0, 0], [0, np.cos(b), -np.sin(b), 0], [0, np.sin(b), np.cos(b), 0], [0, 0, 0, 1]], F32)
+    sc = np.diag(np.array(list(scale) + [1], F32)).astype(F32)
+    m = (ry @ rx @ sc).astype(F32)
+    m[:3, 3] = translate
+    return m
+
+
+def instances_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6) -> SceneDesc:
+    """The textured all-BSDF scene plus two shape groups (src/shapes/shapegroup.cpp) shown through five instances
+    (src/shapes/instance.cpp): a group of two meshes — a smooth icosphere with a checkerboard and a rough-metal box —
+    instanced three times (translated; rotated and uniformly scaled; NON-uniformly scaled, which makes the transformed
+    shading frame non-orthogonal), and a glass icosphere instanced twice, once overlapping a wall."""
+    s = textured_test_scene(width, height, spp, mode, max_depth)
+    ball = icosphere(2)
+    uv = np.stack([np.arctan2(ball[0][:, 2], ball[0][:, 0]) / (2 * np.pi) + 0.5, np.arccos(np.clip(ball[0][:, 1], -1, 1)) / np.pi], 1).astype(F32)
+    ball = (ball[0].astype(F32), ball[1].astype(np.uint32), ball[0].astype(F32))      # unit sphere: normals = positions
+    g0_ball = Shape((ball[0] * F32(0.4)).astype(F32), ball[1], ball[2], material=1, texcoords=uv)
+    bx = merge(box_faces(None, [(-0.3, 0.5, -0.3), (-0.3, 0.5, 0.3), (0.3, 0.5, 0.3), (0.3, 0.5, -0.3)], np.array([0.0, 0.75, 0.0])))
+    g0_box = Shape((bx[0] + np.array([0.0, -1.0, 0.0], F32)).astype(F32), bx[1], bx[2], material=6,
+                   texcoords=(bx[0][:, [0, 2]] * F32(0.8)).astype(F32))
+    g1_ball = Shape((ball[0] * F32(0.35)).astype(F32), ball[1], ball[2], material=7)
+    s.groups = [[g0_ball, g0_box], [g1_ball]]
+
+    def inst(g, m):
+        pts = np.concatenate([sh.positions for sh in s.groups[g]])
+        lo, hi = pts.min(0), pts.max(0)
+        corners = np.array([[x, y, z, 1] for x in (lo[0], hi[0]) for y in (lo[1], hi[1]) for z in (lo[2], hi[2])], np.float64)
+        w = (np.asarray(m, np.float64) @ corners.T).T[:, :3]
+        return instance_shape(g, m, [w.min(0), w.max(0)])
+    s.shapes.append(inst(0, _xform(translate=(1.2, 1.6, 2.2))))
+    s.shapes.append(inst(0, _xform((1.4, 1.4, 1.4), 0.7, 0.3, (3.9, 2.0, 1.8))))
+    s.shapes.append(inst(0, _xform((0.8, 1.7, 1.1), -0.5, 0.0, (2.6, 3.6, 3.4))))
+    s.shapes.append(inst(1, _xform((1.0, 1.0, 1.0), 0.0, 0.0, (2.7, 0.9, 1.0))))
+    s.shapes.append(inst(1, _xform((1.3, 0.9, 1.3), 1.1, -0.4, (5.3, 2.8, 3.0))))
     return s
 
 

@@ -356,6 +356,33 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 		lum->setParent(scene);
 	}
 
+	/* <shape type="shapegroup" id="..."> with its meshes as children (shapegroup.cpp:57-82); built on configure() */
+	std::vector<ref<Shape> > groups;
+	for (size_t g = 0; withGeometry && g < s.groups.size(); ++g) {
+		Properties gp("shapegroup");
+		gp.setID(formatString("group%i", (int) g));
+		ref<Shape> group = static_cast<Shape *>(create(MTS_CLASS(Shape), gp));
+		for (size_t i = 0; i < s.groups[g].size(); ++i) {
+			const sio::Shape &sh = s.groups[g][i];
+			ref<TriMesh> mesh = new TriMesh(formatString("group%i_%i", (int) g, (int) i), sh.nTri, sh.nVert,
+				sh.hasNormals != 0, sh.hasUv != 0, false, false, sh.hasNormals == 0);
+			if (sh.hasUv) memcpy(mesh->getVertexTexcoords(), sh.uv.data(), sh.uv.size() * 4);
+			memcpy(mesh->getVertexPositions(), sh.pos.data(), sh.pos.size() * 4);
+			if (sh.hasNormals) memcpy(mesh->getVertexNormals(), sh.nrm.data(), sh.nrm.size() * 4);
+			memcpy(mesh->getTriangles(), sh.tri.data(), sh.tri.size() * 4);
+			if (sh.matId >= 0) {
+				ref<BSDF> bsdf = makeBSDF(s.materials[sh.matId]);
+				mesh->addChild("", bsdf);
+				bsdf->setParent(mesh);
+			}
+			mesh->configure();
+			group->addChild("", mesh);
+			mesh->setParent(group);
+		}
+		group->configure();
+		groups.push_back(group);
+	}
+
 	if (withGeometry) {
 		for (size_t i = 0; i < s.shapes.size(); ++i) {
 			const sio::Shape &sh = s.shapes[i];
@@ -383,6 +410,16 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 				sphere->configure();
 				scene->addChild("", sphere);
 				sphere->setParent(scene);
+				continue;
+			}
+			if (sh.kind == 2) {      /* <shape type="instance"> <ref id="group"/> <transform name="toWorld"/> </shape> (instance.cpp:22-26) */
+				Properties ip("instance");
+				ip.setTransform("toWorld", Transform(Matrix4x4(const_cast<float *>(sh.toWorld))));
+				ref<Shape> inst = static_cast<Shape *>(create(MTS_CLASS(Shape), ip));
+				inst->addChild("", groups[sh.groupId]);
+				inst->configure();
+				scene->addChild("", inst);
+				inst->setParent(scene);
 				continue;
 			}
 			ref<TriMesh> mesh = new TriMesh(formatString("shape%i", (int) i), sh.nTri, sh.nVert,

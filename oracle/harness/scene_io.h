@@ -17,7 +17,8 @@ struct Material { uint32_t type; float p[16]; uint32_t tex[2]; };
 struct Texture  { uint32_t type; float p[12]; float gamma; uint32_t width, height; std::vector<uint8_t> pixels; /* bitmap: RGB, top row first */ };
 struct Emitter  { float intensity[3]; float samplingWeight; uint32_t type; float p[11]; float aux[16]; std::string envFile; /* type 5 */ };
 struct Shape {
-	uint32_t kind;   /* 0 triangle mesh, 1 analytic sphere */
+	uint32_t kind;   /* 0 triangle mesh, 1 analytic sphere, 2 instance of a shape group */
+	uint32_t groupId; float toWorld[16];
 	float center[3], radius; uint32_t inverted;
 	uint32_t nVert, nTri; int32_t matId, emitId; uint32_t hasNormals, hasUv;
 	std::vector<float> pos, nrm, uv; std::vector<uint32_t> tri;
@@ -34,6 +35,7 @@ struct Scene {
 	std::vector<Material> materials;
 	std::vector<Emitter> emitters;
 	std::vector<Shape> shapes;
+	std::vector<std::vector<Shape> > groups;   /* shape groups: meshes in object space */
 };
 
 struct Reader {
@@ -50,7 +52,7 @@ inline void load(const std::string &path, Scene &s) {
 	Reader r(path);
 	char magic[8]; r.raw(magic, 8);
 	if (memcmp(magic, "MTSB200", 8) != 0) throw std::runtime_error("bad magic in " + path);
-	if (r.get<uint32_t>() != 7) throw std::runtime_error("bad version in " + path);
+	if (r.get<uint32_t>() != 8) throw std::runtime_error("bad version in " + path);
 	r.raw(s.cameraToWorld, 64);
 	s.fov = r.get<float>(); s.nearClip = r.get<float>(); s.farClip = r.get<float>();
 	s.apertureRadius = r.get<float>(); s.focusDepth = r.get<float>();
@@ -77,9 +79,26 @@ inline void load(const std::string &path, Scene &s) {
 	s.emitters.resize(r.get<uint32_t>());
 	for (auto &e : s.emitters) { r.raw(e.intensity, 12); e.samplingWeight = r.get<float>(); e.type = r.get<uint32_t>(); r.raw(e.p, 44); r.raw(e.aux, 64);
 		if (e.type == 5) { e.envFile.resize(r.get<uint32_t>()); r.raw(&e.envFile[0], e.envFile.size()); } }
+	auto readMesh = [&](Shape &sh) {
+		sh.kind = 0;
+		sh.nVert = r.get<uint32_t>(); sh.nTri = r.get<uint32_t>();
+		sh.matId = r.get<int32_t>(); sh.emitId = r.get<int32_t>();
+		sh.hasNormals = r.get<uint32_t>(); sh.hasUv = r.get<uint32_t>();
+		sh.pos.resize(3 * (size_t) sh.nVert); r.raw(sh.pos.data(), sh.pos.size() * 4);
+		if (sh.hasNormals) { sh.nrm.resize(3 * (size_t) sh.nVert); r.raw(sh.nrm.data(), sh.nrm.size() * 4); }
+		if (sh.hasUv) { sh.uv.resize(2 * (size_t) sh.nVert); r.raw(sh.uv.data(), sh.uv.size() * 4); }
+		sh.tri.resize(3 * (size_t) sh.nTri); r.raw(sh.tri.data(), sh.tri.size() * 4);
+	};
+	s.groups.resize(r.get<uint32_t>());
+	for (auto &g : s.groups) { g.resize(r.get<uint32_t>()); for (auto &sh : g) readMesh(sh); }
 	s.shapes.resize(r.get<uint32_t>());
 	for (auto &sh : s.shapes) {
 		sh.kind = r.get<uint32_t>();
+		if (sh.kind == 2) {
+			sh.nVert = sh.nTri = sh.hasNormals = sh.hasUv = 0; sh.matId = sh.emitId = -1;
+			sh.groupId = r.get<uint32_t>(); r.raw(sh.toWorld, 64);
+			continue;
+		}
 		if (sh.kind == 1) {
 			sh.nVert = sh.nTri = sh.hasNormals = sh.hasUv = 0;
 			sh.matId = r.get<int32_t>(); sh.emitId = r.get<int32_t>();
