@@ -277,7 +277,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		if (valid) {
 			uint32_t nested = 0xFFFFFFFFu;
 			if (BMP && sc.hasInstances) nested = reinterpret_cast<const uint32_t *>(hits + wf.capacity)[i];
-			fillIntersectionSorted(sc, h.w, __uint_as_float(h.y), __uint_as_float(h.z), rayO, rayD, __uint_as_float(h.x), its, nested);
+			fillIntersectionSorted<BMP>(sc, h.w, __uint_as_float(h.y), __uint_as_float(h.z), rayO, rayD, __uint_as_float(h.x), its, nested);
 		}
 
 		if (MODE == 2) {

@@ -302,6 +302,8 @@ __device__ __noinline__ void fillInstanceIntersection(const DeviceScene &sc, con
 	its.shape = shape; its.emitterId = -1;
 }
 
+// INST: the scene may hold instances (kernels of scenes without them are compiled without that branch)
+template <bool INST = true>
 __device__ inline void fillIntersectionSorted(const DeviceScene &sc, uint32_t tri, float u, float v, V3 rayO, V3 rayD, float t, Isect &its,
 		uint32_t nested = 0xFFFFFFFFu) {
 	const float4 *rec = sc.shadeTris + (size_t) tri * 6;
@@ -309,7 +311,7 @@ __device__ inline void fillIntersectionSorted(const DeviceScene &sc, uint32_t tr
 	const uint32_t shape = __float_as_uint(r0.w);
 	const ShapeInfo si = sc.shapes[shape];
 	if (si.isSphere) { fillSphereIntersection(sc, r0, r1, r2, r3, r4, r5, rayO, rayD, t, its); return; }
-	if (si.isInstance) { fillInstanceIntersection(sc, si, shape, nested, u, v, rayO, rayD, t, its); return; }
+	if (INST && si.isInstance) { fillInstanceIntersection(sc, si, shape, nested, u, v, rayO, rayD, t, its); return; }
 	fillMeshIntersection<true>(sc, si, shape, r0, r1, r2, r3, r4, r5, u, v, rayO, rayD, t, its);
 }
 
@@ -364,7 +366,7 @@ __device__ inline void fillIntersection(const DeviceScene &sc, uint32_t shape, u
 		// (nothing else can lie in it: t was the closest hit)
 		const RayIn r = { rayO.x, rayO.y, rayO.z, 0.0f, rayD.x, rayD.y, rayD.z, INFINITY };
 		float t2, u2, v2;
-		if (instanceTest<false>(sc, si.cdfOffset, r, nextafterf(t, 0.0f), t, t2, u2, v2, nested)) { u = u2; v = v2; }
+		if (instanceTest<false>(sc.instances, sc.groups, si.cdfOffset, r, nextafterf(t, 0.0f), t, t2, u2, v2, nested)) { u = u2; v = v2; }
 		if (nested == 0xFFFFFFFFu) {             // cannot happen for a hit this library reported
 			its.p = its.geoN = its.shN = its.wi = v3(0, 0, 0); its.uvx = its.uvy = 0; its.sh = makeFrame(v3(0, 0, 1));
 			its.shape = shape; its.materialId = -1; its.emitterId = -1;
@@ -384,8 +386,13 @@ __device__ inline V3 textureValue(const TextureDev &t, float u, float v) {
 }
 
 // ---- bitmap textures: MIPMap (src/librender/mipmap.cpp) over the pyramid built by mipmap.cpp ---------------------
+// The three arrays a lookup reads, by value: a __noinline__ callee that took the whole DeviceScene by reference would
+// force the kernel's parameter block into local memory in every kernel that can reach it.
+struct MipRef { const float4 *texels; const uint4 *mipLevels; const float *mipLut; };
+__device__ __forceinline__ MipRef mipRef(const DeviceScene &sc) { MipRef m = { sc.texels, sc.mipLevels, sc.mipLut }; return m; }
+
 // MIPMap::getTexel (mipmap.cpp:220-243), including its `x <= 0` bounds test
-__device__ inline V3 mipTexel(const DeviceScene &sc, const TextureDev &t, int level, int x, int y) {
+__device__ inline V3 mipTexel(const MipRef sc, const TextureDev &t, int level, int x, int y) {
 	const uint4 L = __ldg(sc.mipLevels + t.pad[0] + level);
 	const int w = (int) L.y, h = (int) L.z, wrap = (int) t.p[1];
 	if (x <= 0 || y < 0 || x >= w || y >= h) {
@@ -397,7 +404,7 @@ __device__ inline V3 mipTexel(const DeviceScene &sc, const TextureDev &t, int le
 }
 
 // MIPMap::triangle (mipmap.cpp:245-262)
-__device__ inline V3 mipTriangle(const DeviceScene &sc, const TextureDev &t, int level, float x, float y) {
+__device__ inline V3 mipTriangle(const MipRef sc, const TextureDev &t, int level, float x, float y) {
 	if (t.p[0] == 2.0f) {
 		const uint4 L = __ldg(sc.mipLevels + t.pad[0]);
 		return mipTexel(sc, t, 0, (int) floorf(x * (float) (int) L.y), (int) floorf(y * (float) (int) L.z));
@@ -415,7 +422,7 @@ __device__ inline V3 mipTriangle(const DeviceScene &sc, const TextureDev &t, int
 }
 
 // MIPMap::EWA (mipmap.cpp:318-357)
-__device__ inline V3 mipEWA(const DeviceScene &sc, const TextureDev &t, float u, float v, float dudx, float dudy, float dvdx, float dvdy, int level) {
+__device__ inline V3 mipEWA(const MipRef sc, const TextureDev &t, float u, float v, float dudx, float dudy, float dvdx, float dvdy, int level) {
 	const int levels = (int) t.pad[1];
 	if (level >= levels) return mipTexel(sc, t, levels - 1, 0, 0);
 	const uint4 L = __ldg(sc.mipLevels + t.pad[0] + level);
@@ -453,7 +460,7 @@ __device__ inline float mtsLog2(float x) { return mts_log(x) * (1.0f / 0.6931471
 
 // MIPMap::getValue (mipmap.cpp:264-316) at the uv of Texture2D::getValue (texture.cpp:73-82). duv = {dudx, dudy, dvdx, dvdy}
 // of the hit; all zero for a ray without differentials, which every filter answers with the bilinear level-0 lookup.
-__device__ __noinline__ V3 bitmapValue(const DeviceScene &sc, const TextureDev &t, float u, float v, float4 duv) {
+__device__ __noinline__ V3 bitmapValue(const MipRef sc, const TextureDev t, float u, float v, float4 duv) {
 	const float tu = u * t.p[8] + t.p[6], tv = v * t.p[9] + t.p[7];
 	float dudx = duv.x * t.p[8], dudy = duv.y * t.p[8], dvdx = duv.z * t.p[9], dvdy = duv.w * t.p[9];
 	const int levels = (int) t.pad[1];
@@ -590,7 +597,7 @@ __device__ inline void resolveTextures(const DeviceScene &sc, MaterialDev &m, fl
 	for (int k = 0; k < 2; ++k)
 		if (m.tex[k]) {
 			const TextureDev &t = sc.textures[m.tex[k] - 1];
-			const V3 c = (BMP && t.type == MTSGPU_TEXTURE_BITMAP) ? bitmapValue(sc, t, u, v, duv) : textureValue(t, u, v);
+			const V3 c = (BMP && t.type == MTSGPU_TEXTURE_BITMAP) ? bitmapValue(mipRef(sc), t, u, v, duv) : textureValue(t, u, v);
 			m.p[3 * k] = c.x; m.p[3 * k + 1] = c.y; m.p[3 * k + 2] = c.z;
 		}
 }
@@ -713,41 +720,45 @@ __device__ inline float spherePdfSolidAngle(V3 center, float radius, float invSu
 __device__ inline V3 envXf(const float *m, V3 v) { return v3(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[3] * v.x + m[4] * v.y + m[5] * v.z, m[6] * v.x + m[7] * v.y + m[8] * v.z); }
 
 // EnvMapLuminaire::Le(direction) (envmap.cpp:158-164): bilinear level-0 lookup at the direction's latitude / longitude
-__device__ __noinline__ V3 envLe(const DeviceScene &sc, const EmitterDev &em, V3 direction) {
-	const V3 d = envXf(sc.envData, direction);
+__device__ __noinline__ V3 envLe(const MipRef mr, const TextureDev tex, const float *envData, float scale, V3 direction) {
+	const V3 d = envXf(envData, direction);
 	const float u = .5f * (1 + mts_atan2(d.x, -d.z) / MTS_PI);
 	const float v = mts_acos(fmaxf(-1.0f, fminf(1.0f, d.y))) / MTS_PI;
-	return mipTriangle(sc, sc.textures[__float_as_uint(em.p[5])], 0, u, v) * em.p[4];
+	return mipTriangle(mr, tex, 0, u, v) * scale;
 }
 
 // EnvMapLuminaire::pdf (envmap.cpp:184-199); `dir` is -lRec.d, the direction from the shaded point to the map
-__device__ __noinline__ float envPdf(const DeviceScene &sc, V3 dir) {
-	const V3 d = envXf(sc.envData, dir);
-	const int resX = (int) sc.envData[18], resY = (int) sc.envData[19];
+__device__ __noinline__ float envPdf(const float *envData, V3 dir) {
+	const V3 d = envXf(envData, dir);
+	const int resX = (int) envData[18], resY = (int) envData[19];
 	const float x = .5f * (1 + mts_atan2(d.x, -d.z) / MTS_PI) * resX;
 	const float y = mts_acos(fmaxf(-1.0f, fminf(1.0f, d.y))) / MTS_PI * resY;
 	const int xPos = min(max((int) floorf(x), 0), resX - 1), yPos = min(max((int) floorf(y), 0), resY - 1);
-	const float pdf = sc.envData[20 + resX * resY + 1 + xPos + yPos * resX];
+	const float pdf = envData[20 + resX * resY + 1 + xPos + yPos * resX];
 	const float sinTheta = sqrtf(fmaxf(MTS_EPSILON, 1 - d.y * d.y));
 	const float pixX = 2 * MTS_PI / resX, pixY = MTS_PI / resY;
 	return pdf / (pixX * pixY * sinTheta);
 }
 
-// EnvMapLuminaire::sampleDirection (envmap.cpp:134-156): a texel of the density, then a point inside it
-__device__ __noinline__ V3 envSampleDirection(const DeviceScene &sc, const EmitterDev &em, float sx, float sy, float &pdf, V3 &value) {
-	const int resX = (int) sc.envData[18], resY = (int) sc.envData[19];
-	const float *cdf = sc.envData + 20;
+// EnvMapLuminaire::sampleDirection (envmap.cpp:134-156): a texel of the density, then a point inside it.
+// Returns {direction, pdf}; `value` through the second result.
+struct EnvSample { V3 d, value; float pdf; };
+__device__ __noinline__ EnvSample envSampleDirection(const MipRef mr, const TextureDev tex, const float *envData, float scale, float sx, float sy) {
+	EnvSample out;
+	const int resX = (int) envData[18], resY = (int) envData[19];
+	const float *cdf = envData + 20;
 	const int idx = cdfSampleReuse(cdf, resX * resY, sx);
-	pdf = cdf[resX * resY + 1 + idx];
+	float pdf = cdf[resX * resY + 1 + idx];
 	const int row = idx / resX, col = idx - resX * row;
 	const float x = col + sx, y = row + sy;
-	value = mipTriangle(sc, sc.textures[__float_as_uint(em.p[5])], 0, x * (1.0f / resX), y * (1.0f / resY)) * em.p[4];
+	out.value = mipTriangle(mr, tex, 0, x * (1.0f / resX), y * (1.0f / resY)) * scale;
 	const float pixX = 2 * MTS_PI / resX, pixY = MTS_PI / resY;
 	const float theta = pixY * y, phi = pixX * x - MTS_PI;
 	const float sinTheta = mts_sin(theta), cosTheta = mts_cos(theta);
 	const float sinPhi = mts_sin(phi), cosPhi = mts_cos(phi);
-	pdf = pdf / (pixX * pixY * sinTheta);
-	return envXf(sc.envData + 9, v3(-sinTheta * sinPhi, -cosTheta, sinTheta * cosPhi));
+	out.pdf = pdf / (pixX * pixY * sinTheta);
+	out.d = envXf(envData + 9, v3(-sinTheta * sinPhi, -cosTheta, sinTheta * cosPhi));
+	return out;
 }
 
 __device__ inline void sampleLuminaire(const DeviceScene &sc, V3 p, float sx, float sy, bool importance, LumSample &out) {
@@ -817,8 +828,8 @@ __device__ inline void sampleLuminaire(const DeviceScene &sc, V3 p, float sx, fl
 		pdf = 1.0f; out.mis = false;
 	} else if (em.type == MTSGPU_EMITTER_ENVMAP) {
 		// EnvMapLuminaire::sample (envmap.cpp:170-182)
-		float dirPdf;
-		const V3 d = envSampleDirection(sc, em, sx, sy, dirPdf, value);
+		const EnvSample es = envSampleDirection(mipRef(sc), sc.textures[__float_as_uint(em.p[5])], sc.envData, em.p[4], sx, sy);
+		const V3 d = es.d; const float dirPdf = es.pdf; value = es.value;
 		const V3 center = v3(em.p[0], em.p[1], em.p[2]);
 		float nearHit, farHit;
 		if (length(p - center) <= em.p[3] && bsphereRayIntersect(center, em.p[3], p, -d, nearHit, farHit)) {
@@ -868,7 +879,7 @@ __device__ inline float pdfBackground(const DeviceScene &sc, bool importance, V3
 	const EmitterDev em = sc.emitters[sc.background];
 	const float luminance = importance ? em.weight : 1.0f;
 	const float fraction = luminance / sc.lumOriginalSum;
-	if (em.type == MTSGPU_EMITTER_ENVMAP) return envPdf(sc, dir) * fraction;
+	if (em.type == MTSGPU_EMITTER_ENVMAP) return envPdf(sc.envData, dir) * fraction;
 	return (1.0f / (4 * MTS_PI)) * fraction;
 }
 
@@ -877,7 +888,7 @@ __device__ inline float pdfBackground(const DeviceScene &sc, bool importance, V3
 __device__ inline V3 backgroundLe(const DeviceScene &sc, V3 rayD) {
 	if (sc.background < 0) return v3(0, 0, 0);
 	const EmitterDev em = sc.emitters[sc.background];
-	if (em.type == MTSGPU_EMITTER_ENVMAP) return envLe(sc, em, normalize(rayD));
+	if (em.type == MTSGPU_EMITTER_ENVMAP) return envLe(mipRef(sc), sc.textures[__float_as_uint(em.p[5])], sc.envData, em.p[4], normalize(rayD));
 	return v3(em.intensity[0], em.intensity[1], em.intensity[2]);
 }
 

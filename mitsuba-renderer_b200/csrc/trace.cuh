@@ -175,9 +175,9 @@ __device__ __noinline__ bool traverseGroup(const DeviceScene &gs, const RayIn &r
 // ShapeKDTree::rayIntersect(ray, mint, maxt, t, temp) (skdtree.h:435-466): clip to the group's box, tighten with the
 // caller's interval, closest hit (or any hit) inside it.
 template <bool SHADOW>
-__device__ __noinline__ bool instanceTest(const DeviceScene &sc, uint32_t instIndex, const RayIn &r, float mint, float maxt,
+__device__ __noinline__ bool instanceTest(const InstanceDev *instances, const DeviceScene *groups, uint32_t instIndex, const RayIn r, float mint, float maxt,
 		float &t, float &u, float &v, uint32_t &nested) {
-	const InstanceDev &inst = sc.instances[instIndex];
+	const InstanceDev &inst = instances[instIndex];
 	const float *M = inst.w2o;
 	RayIn o;
 	o.ox = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(M[0], r.ox), __fmul_rn(M[1], r.oy)), __fmul_rn(M[2], r.oz)), M[3]);
@@ -189,7 +189,7 @@ __device__ __noinline__ bool instanceTest(const DeviceScene &sc, uint32_t instIn
 	o.dy = __fadd_rn(__fadd_rn(__fmul_rn(M[4], r.dx), __fmul_rn(M[5], r.dy)), __fmul_rn(M[6], r.dz));
 	o.dz = __fadd_rn(__fadd_rn(__fmul_rn(M[8], r.dx), __fmul_rn(M[9], r.dy)), __fmul_rn(M[10], r.dz));
 	o.mint = r.mint; o.maxt = r.maxt;
-	const DeviceScene &gs = sc.groups[inst.group];
+	const DeviceScene &gs = groups[inst.group];
 	float nearT = -INFINITY, farT = INFINITY;
 	const float oo[3] = { o.ox, o.oy, o.oz }, dd[3] = { o.dx, o.dy, o.dz };
 #pragma unroll
@@ -217,7 +217,7 @@ __device__ __forceinline__ bool primTest(const DeviceScene &sc, const float4 &q0
 		float mint, float maxt, float &u, float &v, float &t, uint32_t &nested) {
 	if (SPH && (kraw & TRI_K_MASK) == TRI_K_SPHERE) {
 		u = v = 0.0f;
-		if (q1.y != 0.0f) return instanceTest<SHADOW>(sc, __float_as_uint(q1.z), r, mint, maxt, t, u, v, nested);   // a_v = 1: an instance
+		if (q1.y != 0.0f) return instanceTest<SHADOW>(sc.instances, sc.groups, __float_as_uint(q1.z), r, mint, maxt, t, u, v, nested);   // a_v = 1: an instance
 		return sphereTest<SHADOW>(q0, q1, r, mint, maxt, t);
 	}
 	return triAccelTest(q0, q1, q2, kraw & TRI_K_MASK, r, mint, maxt, u, v, t);
