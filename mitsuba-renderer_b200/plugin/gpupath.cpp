@@ -23,6 +23,7 @@
 #include <vector>
 #include <algorithm>
 #include "mtsgpu.h"
+#include "instance.h"          /* src/shapes/instance.h (+ shapegroup.h): Instance::getShapeGroup, ShapeGroup::getKDTree */
 
 MTS_NAMESPACE_BEGIN
 
@@ -423,16 +424,50 @@ private:
 				if (emitters[i].type == MTSGPU_EMITTER_ENVMAP) envIndex = (int) i;
 			}
 		}
-		struct MeshRef { const TriMesh *mesh; int mat, emit; bool sphere; SphereData sph; };
+		struct MeshRef { const TriMesh *mesh; int mat, emit; bool sphere; SphereData sph; int group; };   /* group >= 0: an instance (transform in sph) */
+		struct GroupRef { std::vector<MeshRef> members; };
 		std::vector<MeshRef> meshes;
+		std::vector<GroupRef> groups;
+		std::map<const ShapeGroup *, int> groupIds;
 		for (size_t i = 0; i < shapes.size(); ++i) {
 			const Shape *shape = shapes[i];
 			const bool isSphere = shape->getClass()->getName() == "Sphere";
+			if (shape->getClass()->getName() == "Instance") {
+				/* instance.h:42-48: the group it shows (its kd-tree's meshes are uploaded once per group) and its transform */
+				const Instance *inst = static_cast<const Instance *>(shape);
+				const ShapeGroup *group = inst->getShapeGroup();
+				if (!groupIds.count(group)) {
+					GroupRef gr;
+					const std::vector<const Shape *> &members = group->getKDTree()->getShapes();
+					for (size_t k = 0; k < members.size(); ++k) {
+						if (!members[k]->getClass()->derivesFrom(MTS_CLASS(TriMesh)))
+							Log(EError, "gpupath: shape groups may hold triangle meshes only (found %s)", members[k]->getClass()->getName().c_str());
+						MeshRef r; r.mesh = static_cast<const TriMesh *>(members[k]); r.mat = -1; r.emit = -1; r.sphere = false; r.group = -1;
+						if (members[k]->hasBSDF()) {
+							const BSDF *bsdf = members[k]->getBSDF();
+							if (!materialIds.count(bsdf)) {
+								materialIds[bsdf] = (int) materials.size();
+								materials.push_back(decodeBSDF(bsdf, textures, bitmaps));
+							}
+							r.mat = materialIds[bsdf];
+						}
+						gr.members.push_back(r);
+					}
+					groupIds[group] = (int) groups.size();
+					groups.push_back(gr);
+				}
+				MeshRef r; r.mesh = NULL; r.mat = -1; r.emit = -1; r.sphere = false; r.group = groupIds[group];
+				const Transform xf = inst->getWorldTransform();
+				const Matrix4x4 &m = xf.getMatrix(), &mi = xf.getInverseMatrix();
+				for (int a = 0; a < 4; ++a) for (int b = 0; b < 4; ++b) { r.sph.o2w[4 * a + b] = m.m[a][b]; r.sph.w2o[4 * a + b] = mi.m[a][b]; }
+				meshes.push_back(r);
+				continue;
+			}
 			if (!isSphere && !shape->getClass()->derivesFrom(MTS_CLASS(TriMesh)))
-				Log(EError, "gpupath: shape %i (%s) is neither a triangle mesh nor a sphere", (int) i, shape->getClass()->getName().c_str());
+				Log(EError, "gpupath: shape %i (%s) is neither a triangle mesh, a sphere nor an instance", (int) i, shape->getClass()->getName().c_str());
 			if (shape->hasSubsurface() || shape->isMediumTransition())
 				Log(EError, "gpupath: subsurface / medium transitions are outside the supported hot path");
-			MeshRef r; r.mesh = isSphere ? NULL : static_cast<const TriMesh *>(shape); r.mat = -1; r.emit = -1; r.sphere = isSphere;
+			MeshRef r; r.mesh = isSphere ? NULL : static_cast<const TriMesh *>(shape); r.mat = -1; r.emit = -1; r.sphere = isSphere; r.group = -1;
 			if (isSphere) r.sph = decodeSphere(shape);
 			if (shape->hasBSDF()) {
 				const BSDF *bsdf = shape->getBSDF();
@@ -465,7 +500,20 @@ private:
 			if (envIndex >= 0)      /* Bitmap::loadEXR leaves RGBA floats (bitmap.cpp:247-273) */
 				check(c, mtsgpu_upload_envmap(c, envIndex, env.bitmap->getWidth(), env.bitmap->getHeight(), 4,
 					env.bitmap->getFloatData(), env.l2w, env.w2l));
+			for (size_t gi = 0; gi < groups.size(); ++gi)
+				for (size_t k = 0; k < groups[gi].members.size(); ++k) {
+					const TriMesh *m = groups[gi].members[k].mesh;
+					check(c, mtsgpu_upload_group_mesh(c, (int) gi, (int) k,
+						reinterpret_cast<const float *>(m->getVertexPositions()),
+						reinterpret_cast<const float *>(m->getVertexNormals()),
+						reinterpret_cast<const float *>(m->getVertexTexcoords()), (uint32_t) m->getVertexCount(),
+						reinterpret_cast<const uint32_t *>(m->getTriangles()), (uint32_t) m->getTriangleCount(), groups[gi].members[k].mat));
+				}
 			for (size_t i = 0; i < meshes.size(); ++i) {
+				if (meshes[i].group >= 0) {
+					check(c, mtsgpu_upload_instance(c, (int) i, meshes[i].group, meshes[i].sph.o2w, meshes[i].sph.w2o));
+					continue;
+				}
 				if (meshes[i].sphere) {
 					const SphereData &sp = meshes[i].sph;
 					check(c, mtsgpu_upload_sphere(c, (int) i, sp.o2w, sp.w2o, sp.radius, sp.center, sp.inverted, meshes[i].mat, meshes[i].emit));
