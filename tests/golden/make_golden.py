@@ -29,6 +29,16 @@ def main():
         seg = scenes.shadow_segments(rays, scene)
         save(name, rays_digest=gc.digest(rays), hits=hits.view(np.uint8), full=full,
              any_segments=sess.trace(seg, "any")[0].astype(np.uint8), any_rays=sess.trace(rays, "any")[0].astype(np.uint8))
+    # spheres, sphere luminaires and instances of shape groups: non-triangle primitives of the scene's structure
+    for name, scene in (("trace_spheres", gc.scene_spheres()), ("trace_instances", gc.scene_instances())):
+        rays = gc.trace_rays(scene)
+        sess = oracle_util.Session(scene)
+        hits, full, _ = sess.trace(rays, "closest_full")
+        nontri = hits["prim"] == 0xFFFFFFFF
+        hits["u"][nontri] = 0; hits["v"][nontri] = 0         # left unset by the reference for non-triangles
+        seg = scenes.shadow_segments(rays, scene)
+        save(name, rays_digest=gc.digest(rays), hits=hits.view(np.uint8), full=full,
+             any_segments=sess.trace(seg, "any")[0].astype(np.uint8), any_rays=sess.trace(rays, "any")[0].astype(np.uint8))
     scene = gc.scene_smoke()
     rays = scenes.incoherent_rays(scene, 20000, 7)
     sess = oracle_util.Session(scene)

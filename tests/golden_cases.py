@@ -235,3 +235,11 @@ def lens_camera_samples(scene, n, seed):
 
 def scene_envmap():
     return scenes.envmap_test_scene(16, 16, 1)
+
+
+def scene_spheres():
+    return scenes.sphere_lights_test_scene(32, 32, 1)
+
+
+def scene_instances():
+    return scenes.instances_test_scene(32, 32, 1)

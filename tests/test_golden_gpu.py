@@ -194,3 +194,26 @@ def test_envmap_sampling_matches_golden(gpu_ctx_factory):
     assert close(out[:, cols], ref[:, cols], 2e-5, 2e-6).all()
     has_n = ref[:, 13] >= 3
     assert close(out[has_n, 3:6], ref[has_n, 3:6], 2e-5, 2e-6).all()
+
+
+@pytest.mark.parametrize("name,make", [("trace_spheres", gc.scene_spheres), ("trace_instances", gc.scene_instances)])
+def test_ray_queries_on_non_triangle_primitives_match_golden(name, make, gpu_ctx_factory):
+    """Analytic spheres (sphere.cpp:92-131) and instances of shape groups (instance.cpp:72-98) next to the meshes."""
+    scene = make()
+    g = gold(name)
+    rays = gc.trace_rays(scene)
+    assert gc.digest(rays) == str(g["rays_digest"])
+    ctx = gpu_ctx_factory(scene)
+    ref = g["hits"].view(api.HIT_DTYPE).reshape(-1)
+    hits = ctx.trace(rays, TRACE_CLOSEST)
+    got = hits.copy()
+    nontri = got["prim"] == 0xFFFFFFFF
+    assert nontri.sum() > 500
+    got["u"][nontri] = 0; got["v"][nontri] = 0
+    check_closest(got, ref, name)
+    assert np.array_equal(hits["t"].view(np.uint32), ref["t"].view(np.uint32))
+    assert np.array_equal(ctx.trace(scenes.shadow_segments(rays, scene), TRACE_ANY), g["any_segments"])
+    assert np.array_equal(ctx.trace(rays, TRACE_ANY), g["any_rays"])
+    _, full = ctx.intersect_full(rays)
+    same = (hits["shape"] == ref["shape"]) & (ref["shape"] != 0xFFFFFFFF)
+    assert close(full[same], g["full"][same], 2e-5, 2e-6).all()
