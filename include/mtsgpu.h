@@ -263,6 +263,17 @@ MTSGPU_API int mtsgpu_upload_instance(mtsgpu_ctx *ctx, int shapeIndex, int group
 MTSGPU_API int mtsgpu_set_camera(mtsgpu_ctx *ctx, const float rasterToCamera[16], const float cameraToWorld[16],
 	float nearClip, float farClip, float apertureRadius, float focusDepth, float shutterOpen, float shutterOpenTime);
 
+/* OrthographicCamera (src/cameras/orthographic.cpp:30-119) instead: rasterToCamera = cameraToScreen.inverse() *
+ * rasterToScreen with cameraToScreen = Transform::orthographic(nearClip, farClip) (orthographic.cpp:83-86); rays start at
+ * cameraToWorld(rasterToCamera(x, y, 0)) and run along cameraToWorld(0, 0, 1) for t in [0, farClip - nearClip]
+ * (orthographic.cpp:104-119). No lens sample (needsLensSample() is false).
+ * Parity note: in the reference this class re-declares m_nearClip / m_farClip (orthographic.cpp:176), and it is those
+ * uninitialised copies that its constructor and generateRay read: as compiled here every ray comes out with
+ * maxt = 0 and the reference renders nothing. Ray origins and directions agree with it (tested); the interval is the
+ * intended one. */
+MTSGPU_API int mtsgpu_set_camera_orthographic(mtsgpu_ctx *ctx, const float rasterToCamera[16], const float cameraToWorld[16],
+	float nearClip, float farClip, float shutterOpen, float shutterOpenTime);
+
 /* Film geometry (src/librender/film.cpp:24-51) and the film's TabulatedFilter
  * (include/mitsuba/render/rfilter.h:65-118): the 16x16 table m_values, and the filter half-size. */
 MTSGPU_API int mtsgpu_set_film(mtsgpu_ctx *ctx, int width, int height, int cropX, int cropY, int cropW, int cropH,

@@ -29,7 +29,7 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_film_splat_static", "mtsgpu_render_multi", "mtsgpu_serialized_count", "mtsgpu_serialized_load",
     "mtsgpu_serialized_free", "mtsgpu_serialized_save", "mtsgpu_upload_serialized", "mtsgpu_film_develop",
     "mtsgpu_film_develop_device", "mtsgpu_film_save", "mtsgpu_write_exr", "mtsgpu_write_mfilm", "mtsgpu_sampler_values",
-    "mtsgpu_upload_textures", "mtsgpu_intersect_uv", "mtsgpu_upload_sphere", "mtsgpu_upload_bitmap", "mtsgpu_texture_lookup", "mtsgpu_upload_envmap", "mtsgpu_upload_group_mesh", "mtsgpu_upload_instance",
+    "mtsgpu_upload_textures", "mtsgpu_intersect_uv", "mtsgpu_upload_sphere", "mtsgpu_upload_bitmap", "mtsgpu_texture_lookup", "mtsgpu_upload_envmap", "mtsgpu_upload_group_mesh", "mtsgpu_upload_instance", "mtsgpu_set_camera_orthographic",
 ]
 SAMPLER_INDEPENDENT, SAMPLER_LD, SAMPLER_STRATIFIED, SAMPLER_HALTON = 0, 1, 2, 3
 FILM_EXR, FILM_M = 0, 1
@@ -115,6 +115,7 @@ def load_library(path: Optional[str] = None):
     lib.mtsgpu_upload_sphere.argtypes = [vp, C.c_int, vp, vp, C.c_float, vp, C.c_int, C.c_int, C.c_int]
     lib.mtsgpu_upload_mesh.argtypes = [vp, C.c_int, vp, vp, vp, C.c_uint32, vp, C.c_uint32, C.c_int, C.c_int]
     lib.mtsgpu_set_camera.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float]
+    lib.mtsgpu_set_camera_orthographic.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_float, C.c_float]
     lib.mtsgpu_set_film.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_float, C.c_float]
     lib.mtsgpu_build_accel.argtypes = [vp]
     lib.mtsgpu_render.argtypes = [vp, C.POINTER(RenderParams), vp, vp, C.POINTER(Stats)]
@@ -297,6 +298,10 @@ class Context:
     def set_camera(self, scene: SceneDesc):
         r2c = np.ascontiguousarray(raster_to_camera(scene), np.float32)
         c2w = np.ascontiguousarray(scene.camera_to_world, np.float32)
+        if scene.orthographic:
+            self._check(self.lib.mtsgpu_set_camera_orthographic(self.h, self._ptr(r2c), self._ptr(c2w), scene.near_clip,
+                                                                scene.far_clip, 0.0, 0.0))
+            return
         self._check(self.lib.mtsgpu_set_camera(self.h, self._ptr(r2c), self._ptr(c2w), scene.near_clip, scene.far_clip,
                                                scene.aperture_radius, scene.focus_depth, 0.0, 0.0))
 

@@ -253,9 +253,17 @@ int mtsgpu_set_camera(mtsgpu_ctx *ctx, const float rasterToCamera[16], const flo
 	ctx->camera.nearClip = nearClip; ctx->camera.farClip = farClip;
 	ctx->camera.apertureRadius = apertureRadius; ctx->camera.focusDepth = focusDepth;
 	ctx->camera.shutterOpen = shutterOpen; ctx->camera.shutterOpenTime = shutterOpenTime;
+	ctx->camera.orthographic = 0;
 	ctx->haveCamera = true;
 	ctx->lumImportance = -1;          // the background luminaire's sphere depends on the camera position
 	return MTSGPU_OK;
+}
+
+int mtsgpu_set_camera_orthographic(mtsgpu_ctx *ctx, const float rasterToCamera[16], const float cameraToWorld[16], float nearClip, float farClip,
+		float shutterOpen, float shutterOpenTime) {
+	const int rc = mtsgpu_set_camera(ctx, rasterToCamera, cameraToWorld, nearClip, farClip, 0.0f, 0.0f, shutterOpen, shutterOpenTime);
+	if (rc == MTSGPU_OK) ctx->camera.orthographic = 1;
+	return rc;
 }
 
 int mtsgpu_set_film(mtsgpu_ctx *ctx, int width, int height, int cropX, int cropY, int cropW, int cropH,

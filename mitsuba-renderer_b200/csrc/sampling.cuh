@@ -198,7 +198,10 @@ __device__ inline void cameraRay(const CameraDev &cam, float sx, float sy, float
 	const float w = m[12] * sx + m[13] * sy + m[14] * 0.0f + m[15];
 	if (w != 1.0f) { const float rw = 1.0f / w; x *= rw; y *= rw; z *= rw; }
 	V3 lo = v3(0, 0, 0), ld = v3(x, y, z);
-	if (cam.apertureRadius > 0.0f) {
+	if (cam.orthographic) {
+		// OrthographicCamera::generateRay (orthographic.cpp:104-119): origin on the image plane, direction +z
+		lo = ld; ld = v3(0, 0, 1);
+	} else if (cam.apertureRadius > 0.0f) {
 		float px, py;
 		squareToDiskConcentric(lx, ly, px, py);
 		px *= cam.apertureRadius; py *= cam.apertureRadius;
@@ -207,10 +210,14 @@ __device__ inline void cameraRay(const CameraDev &cam, float sx, float sy, float
 		lo.x += px; lo.y += py;
 		ld = itsFocal - lo;
 	}
-	ld = normalize(ld);
-	const float invZ = 1.0f / ld.z;
-	mint = cam.nearClip * invZ;
-	maxt = cam.farClip * invZ;
+	if (cam.orthographic) {
+		mint = 0; maxt = cam.farClip - cam.nearClip;
+	} else {
+		ld = normalize(ld);
+		const float invZ = 1.0f / ld.z;
+		mint = cam.nearClip * invZ;
+		maxt = cam.farClip * invZ;
+	}
 	const float *c = cam.cameraToWorld;
 	{
 		float ox = c[0] * lo.x + c[1] * lo.y + c[2] * lo.z + c[3];

@@ -59,6 +59,7 @@ struct CameraDev {
 	float cameraToWorld[16];
 	float nearClip, farClip, apertureRadius, focusDepth;
 	float shutterOpen, shutterOpenTime;
+	uint32_t orthographic, pad;       // src/cameras/orthographic.cpp instead of perspective.cpp
 };
 
 struct FilmDev {

@@ -310,6 +310,7 @@ class SceneDesc:
     aperture_radius: float = 0.0
     focus_depth: float = 1e4
     map_smaller_side: bool = True
+    orthographic: bool = False       # src/cameras/orthographic.cpp instead of perspective.cpp (fov, aperture unused)
     width: int = 512
     height: int = 512
     crop: Optional[tuple] = None     # (x, y, w, h)
@@ -384,6 +385,11 @@ def raster_to_camera(scene: SceneDesc) -> np.ndarray:
         s1, s2, t = (w, h, f32(1)), (f32(0.5), f32(f32(-0.5) * aspect), f32(1)), (f32(1), f32(-f32(f32(1) / aspect)), f32(0))
     s2r_inv = matmul4_f32(translate_inv(*t), matmul4_f32(scale_inv(*s2), scale_inv(*s1)))
     near, far = f32(scene.near_clip), f32(scene.far_clip)
+    if scene.orthographic:
+        # Transform::orthographic = scale(1, 1, 1 / (far - near)) * translate(0, 0, -near) (transform.cpp:155-158); the
+        # camera's scale applies to x and y only ("no non-unity scale factors in the Z direction", orthographic.cpp:41-42)
+        c2s_inv = matmul4_f32(translate_inv(f32(0), f32(0), f32(-near)), scale_inv(f32(1), f32(1), f32(f32(1.0) / f32(far - near))))
+        return matmul4_f32(c2s_inv, s2r_inv)
     recip = f32(f32(1.0) / f32(far - near))               # Transform::perspective, transform.cpp:100-124
     trafo = np.array([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, f32(far * recip), f32(f32(f32(-near) * far) * recip)], [0, 0, 1, 0]], f32)
     half = f32(f32(f32(scene.fov) / f32(2.0)) * f32(f32(np.pi) / f32(180.0)))     # degToRad (core/util.h:302)
@@ -400,7 +406,7 @@ def write_scene(path: str, scene: SceneDesc) -> None:
         f.write(struct.pack("<I", 8))
         f.write(np.ascontiguousarray(scene.camera_to_world, np.float32).tobytes())
         f.write(struct.pack("<5fI", scene.fov, scene.near_clip, scene.far_clip, scene.aperture_radius,
-                            scene.focus_depth, int(scene.map_smaller_side)))
+                            scene.focus_depth, int(scene.map_smaller_side) | (2 if scene.orthographic else 0)))
         f.write(struct.pack("<7I", scene.width, scene.height, cx, cy, cw, ch, scene.filter_type))
         f.write(struct.pack("<2I2i3I", scene.spp, scene.mode, scene.max_depth, scene.rr_depth,
                             int(scene.strict_normals), scene.luminaire_samples, scene.bsdf_samples))

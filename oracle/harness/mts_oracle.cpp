@@ -313,14 +313,14 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 		ref<Sampler> sampler = static_cast<Sampler *>(create(MTS_CLASS(Sampler), sp));
 		sampler->configure();
 
-		Properties cp("perspective");
+		Properties cp((s.mapSmallerSide & 2) ? "orthographic" : "perspective");     /* bit 1 of the flag word: orthographic camera */
 		cp.setTransform("toWorld", Transform(Matrix4x4(s.cameraToWorld)));
 		cp.setFloat("fov", s.fov);
 		cp.setFloat("nearClip", s.nearClip);
 		cp.setFloat("farClip", s.farClip);
 		cp.setFloat("apertureRadius", s.apertureRadius);
 		cp.setFloat("focusDepth", s.focusDepth);
-		cp.setBoolean("mapSmallerSide", s.mapSmallerSide != 0);
+		cp.setBoolean("mapSmallerSide", (s.mapSmallerSide & 1) != 0);
 		ref<Camera> camera = static_cast<Camera *>(create(MTS_CLASS(Camera), cp));
 		camera->addChild("", sampler);  sampler->setParent(camera);
 		camera->addChild("", out.film); out.film->setParent(camera);

@@ -3,7 +3,7 @@ BSDF f/pdf/sample (1e-5, north_star), luminaire sampling, camera rays, intersect
 import numpy as np
 import pytest
 
-from mitsuba_renderer_b200 import scenes, scenefile
+from mitsuba_renderer_b200 import api, scenes, scenefile
 
 pytestmark = pytest.mark.gpu
 REL, ABS = 1e-5, 1e-7      # tolerance stated by north_star: 1e-5 relative (absolute floor 1e-7)
@@ -169,3 +169,28 @@ def test_film_splat(oracle, gpu_ctx_factory, filter_type, crop):
     mine, size = filter_table(filter_type)
     assert size == info["filter_size"][0]
     assert np.allclose(mine, table, rtol=2e-6, atol=1e-9)
+
+
+def test_orthographic_camera_rays(oracle, gpu_ctx_factory):
+    """OrthographicCamera::generateRay (orthographic.cpp:104-119). The reference's class shadows m_nearClip / m_farClip
+    with uninitialised members of its own (orthographic.cpp:176), so its rays carry maxt = 0 and its renders are empty;
+    origins and directions are compared with it, the interval with the intended [0, farClip - nearClip]."""
+    scene = scenes.cornell_box(200, 120, 1)
+    scene.orthographic = True
+    m = np.array(scene.camera_to_world, np.float32).copy(); m[:3, 0] *= 2.5; m[:3, 1] *= 2.5     # x / y scale: the image plane's extent
+    scene.camera_to_world = m
+    ctx = gpu_ctx_factory(scene)
+    rng = np.random.Generator(np.random.PCG64(8))
+    q = rng.random((20000, 4)).astype(np.float32)
+    q[:, 0] *= scene.width; q[:, 1] *= scene.height
+    ref = oracle.Session(scene).camera(q)
+    gpu = ctx.camera_rays(q)
+    cols = [0, 1, 3, 4, 5, 6]                                                           # o.x, o.y, mint = 0, d: bit-identical
+    assert np.array_equal(gpu[:, cols].view(np.uint32), ref[:, cols].view(np.uint32))
+    # the same uninitialised near plane (0 instead of nearClip) puts the reference's origins on the camera plane itself
+    assert np.allclose(gpu[:, 2] - ref[:, 2], scene.near_clip, rtol=0, atol=1e-6)
+    assert (ref[:, 7] == 0).all()                                                        # the reference's empty interval
+    assert np.allclose(gpu[:, 7], np.float32(scene.far_clip) - np.float32(scene.near_clip), rtol=0, atol=0)
+    # and the camera sees the box: a render is not empty
+    film, _ = ctx.render(api.Context.params_from_scene(scene, seed=1))
+    assert (film[..., 3] > 0).mean() > 0.3
