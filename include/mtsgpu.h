@@ -160,11 +160,13 @@ typedef struct mtsgpu_render_params {
 /* MTSGPU_SAMPLER_STRATIFIED: src/samplers/stratified.cpp:123-182 — per pixel and draw the R x R strata of the unit square
  * (R*R = sppTotal, which must be a perfect square; the reference rounds up, stratified.cpp:37-47) are visited in a
  * random order with a jittered point in each; 1D draws use R*R strata of the unit interval. */
+/* MTSGPU_SAMPLER_HAMMERSLEY: src/samplers/hammersley.cpp:72-99 — as HALTON, except that the first value of pixel sample i
+ * is i / sampleCount and value d > 0 is radicalInverse(prime d-1, i). */
 /* MTSGPU_SAMPLER_HALTON: src/samplers/halton.cpp:68-84 — value number d of pixel sample i is radicalInverse(prime d, i)
  * (src/libcore/util.cpp:740-750), the same for every pixel; fully deterministic, so images can be compared with the
  * reference pixel by pixel. Like the reference it supports no sample arrays (luminaireSamples = bsdfSamples = 1). */
 enum mtsgpu_sampler_type { MTSGPU_SAMPLER_INDEPENDENT = 0, MTSGPU_SAMPLER_LD = 1, MTSGPU_SAMPLER_STRATIFIED = 2,
-                           MTSGPU_SAMPLER_HALTON = 3 };
+                           MTSGPU_SAMPLER_HALTON = 3, MTSGPU_SAMPLER_HAMMERSLEY = 4 };
 
 typedef struct mtsgpu_stats {
 	uint64_t cameraRays;      /* "Camera ray generations" (perspective.cpp:24) */

@@ -31,7 +31,7 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_film_develop_device", "mtsgpu_film_save", "mtsgpu_write_exr", "mtsgpu_write_mfilm", "mtsgpu_sampler_values",
     "mtsgpu_upload_textures", "mtsgpu_intersect_uv", "mtsgpu_upload_sphere", "mtsgpu_upload_bitmap", "mtsgpu_texture_lookup", "mtsgpu_upload_envmap", "mtsgpu_upload_group_mesh", "mtsgpu_upload_instance", "mtsgpu_set_camera_orthographic",
 ]
-SAMPLER_INDEPENDENT, SAMPLER_LD, SAMPLER_STRATIFIED, SAMPLER_HALTON = 0, 1, 2, 3
+SAMPLER_INDEPENDENT, SAMPLER_LD, SAMPLER_STRATIFIED, SAMPLER_HALTON, SAMPLER_HAMMERSLEY = 0, 1, 2, 3, 4
 FILM_EXR, FILM_M = 0, 1
 BITMAP_U8, BITMAP_F32 = 0, 1
 STATIC_SCRATCH_BYTES = 4 << 20

@@ -551,11 +551,15 @@ static int uploadFilter(mtsgpu_ctx *ctx, DevBuf &dTable) {
 }
 
 static int makeSamplerConfig(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, SamplerConfig &cfg) {
-	REQUIRE(ctx, P->samplerType <= MTSGPU_SAMPLER_HALTON, MTSGPU_ERR_UNSUPPORTED, "render: unknown sampler type %u", P->samplerType);
-	if (P->samplerType == MTSGPU_SAMPLER_HALTON && P->mode == MTSGPU_MODE_DIRECT)      // halton.cpp:99-105
+	REQUIRE(ctx, P->samplerType <= MTSGPU_SAMPLER_HAMMERSLEY, MTSGPU_ERR_UNSUPPORTED, "render: unknown sampler type %u", P->samplerType);
+	if ((P->samplerType == MTSGPU_SAMPLER_HALTON || P->samplerType == MTSGPU_SAMPLER_HAMMERSLEY) && P->mode == MTSGPU_MODE_DIRECT)      // halton.cpp:99-105, hammersley.cpp:111-117
 		REQUIRE(ctx, P->luminaireSamples == 1 && P->bsdfSamples == 1, MTSGPU_ERR_UNSUPPORTED, "request2DArray() is not supported by QMC samplers!");
 	cfg.type = P->samplerType; cfg.depth = P->samplerDepth; cfg.log2Count = 0; cfg.resolution = 1;
 	cfg.lensDraw = (ctx->haveCamera && ctx->camera.apertureRadius > 0.0f) ? 1u : 0u;
+	if (cfg.type == MTSGPU_SAMPLER_HAMMERSLEY) {
+		REQUIRE(ctx, P->sppTotal > 0, MTSGPU_ERR_ARG, "render: hammersley needs the sample count");
+		cfg.resolution = P->sppTotal;                  // m_invSamplesPerPixel = 1 / sampleCount (hammersley.cpp:46-47)
+	}
 	if (cfg.type == MTSGPU_SAMPLER_LD) {
 		// the reference rounds the count up to a power of two and renders that many samples (ldsampler.cpp:61-65)
 		REQUIRE(ctx, P->sppTotal > 0 && (P->sppTotal & (P->sppTotal - 1)) == 0, MTSGPU_ERR_ARG,

@@ -99,6 +99,17 @@ struct Sampler {
 		const uint32_t b = (dim - 3u) / 3u, k = (dim - 3u) % 3u;
 		return 2 * cfg.lensDraw + 2 + 4 * b + rouletteDraws + 2 * k;
 	}
+#ifdef __CUDA_ARCH__
+	// value number v of this pixel sample: halton.cpp:68-70 — radicalInverse(prime v, i); hammersley.cpp:72-79 — i / N for
+	// the first value, radicalInverse(prime v-1, i) after it (cfg.resolution carries N)
+	__device__ float qmcValue(uint32_t v) const {
+		if (cfg.type == MTSGPU_SAMPLER_HAMMERSLEY) {
+			if (v == 0) return (float) sample * (1.0f / (float) cfg.resolution);
+			return radicalInverse(c_primes[v - 1], sample);
+		}
+		return radicalInverse(c_primes[v], sample);
+	}
+#endif
 	// which next2D() / next1D() call of the pixel sample a dimension is (renderBlock, then Li)
 	__host__ __device__ uint32_t draw2D(uint32_t dim) const {
 		if (dim == DIM_LENS_) return 0;
@@ -112,12 +123,12 @@ struct Sampler {
 		y = uintToUnitFloat((uint32_t) (z >> 32));
 		if (cfg.type == MTSGPU_SAMPLER_INDEPENDENT) return;
 #ifdef __CUDA_ARCH__
-		if (cfg.type == MTSGPU_SAMPLER_HALTON) {
-			// next2D() is `Point2(nextValue(), nextValue())` (halton.cpp:80-84): the order of the two calls is the
-			// compiler's choice, and GCC (the reference's Linux build, and the oracle's) evaluates arguments right
-			// to left — y takes the first value, x the second
-			const uint32_t v = min(haltonValue(dim), 126u);
-			y = radicalInverse(c_primes[v], sample); x = radicalInverse(c_primes[v + 1], sample);
+		if (cfg.type == MTSGPU_SAMPLER_HALTON || cfg.type == MTSGPU_SAMPLER_HAMMERSLEY) {
+			// next2D() is `Point2(nextValue(), nextValue())` (halton.cpp:80-84, hammersley.cpp:94-99): the order of the
+			// two calls is the compiler's choice, and GCC (the reference's Linux build, and the oracle's) evaluates
+			// arguments right to left — y takes the first value, x the second
+			const uint32_t v = min(haltonValue(dim), 125u);
+			y = qmcValue(v); x = qmcValue(v + 1);
 			return;
 		}
 #endif
@@ -147,8 +158,8 @@ struct Sampler {
 	// 1D draws: only the roulette decision uses them; draw number = how far past rrDepth the path is
 	__host__ __device__ float get1D(uint32_t dim, uint32_t draw1D = 0xFFFFFFFFu) const {
 #ifdef __CUDA_ARCH__
-		if (cfg.type == MTSGPU_SAMPLER_HALTON)
-			return radicalInverse(c_primes[min(haltonValue(dim), 127u)], sample);
+		if (cfg.type == MTSGPU_SAMPLER_HALTON || cfg.type == MTSGPU_SAMPLER_HAMMERSLEY)
+			return qmcValue(min(haltonValue(dim), 126u));
 #endif
 		if (cfg.type == MTSGPU_SAMPLER_STRATIFIED && draw1D < cfg.depth) {         // stratified.cpp:157-161
 			const uint64_t z = splitmix64(key + 0x9E3779B97F4A7C15ull * (uint64_t) (dim + 1));

@@ -610,8 +610,10 @@ private:
 				P.samplerDepth = (uint32_t) ms->readInt();
 			} else if (samplerClass == "HaltonSequence") {
 				P.samplerType = MTSGPU_SAMPLER_HALTON;
+			} else if (samplerClass == "HammersleySequence") {
+				P.samplerType = MTSGPU_SAMPLER_HAMMERSLEY;
 			} else if (samplerClass != "IndependentSampler") {
-				Log(EError, "gpupath: sampler class \"%s\" is outside the supported hot path (independent, ldsampler, stratified, halton)", samplerClass.c_str());
+				Log(EError, "gpupath: sampler class \"%s\" is outside the supported hot path (independent, ldsampler, stratified, halton, hammersley)", samplerClass.c_str());
 			}
 		}
 		const size_t nPix = (size_t) csize.x * csize.y;

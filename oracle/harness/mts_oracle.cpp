@@ -307,7 +307,7 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 		filter->setParent(out.film);
 		out.film->configure();
 
-		Properties sp(s.samplerType == 1 ? "ldsampler" : s.samplerType == 2 ? "stratified" : s.samplerType == 3 ? "halton" : "independent");
+		Properties sp(s.samplerType == 1 ? "ldsampler" : s.samplerType == 2 ? "stratified" : s.samplerType == 3 ? "halton" : s.samplerType == 4 ? "hammersley" : "independent");
 		sp.setInteger("sampleCount", (int) s.spp);
 		if (s.samplerType == 1 || s.samplerType == 2) sp.setInteger("depth", (int) s.samplerDepth);
 		ref<Sampler> sampler = static_cast<Sampler *>(create(MTS_CLASS(Sampler), sp));

@@ -158,6 +158,25 @@ def test_halton_render_matches_reference_pixel_by_pixel(oracle, gpu_ctx_factory,
     assert np.array_equal(gpu2, gpu)
 
 
+@pytest.mark.parametrize("mode", [scenefile.MODE_PATH, scenefile.MODE_DIRECT])
+def test_hammersley_render_matches_reference_pixel_by_pixel(oracle, gpu_ctx_factory, mode):
+    """hammersley.cpp:72-99: as halton, but the first value of sample i is i / N and the primes start one value later.
+    Thin lens on, so that first value is the lens sample's second coordinate."""
+    scene = scenes.textured_test_scene(64, 64, 16, mode, max_depth=7)
+    scene.rr_depth = 3
+    scene.aperture_radius, scene.focus_depth = 0.05, 7.0
+    scene.sampler_type = api.SAMPLER_HAMMERSLEY
+    cpu = oracle.Session(scene).render()[0]
+    gpu, _ = gpu_ctx_factory(scene).render(Context.params_from_scene(scene, seed=1))
+    assert np.array_equal(gpu[..., 3:], cpu[..., 3:])
+    c, g = develop(cpu), develop(gpu)
+    err = np.abs(g - c).max(axis=-1) / (np.abs(c).max(axis=-1) + 1e-3)
+    print(f"mode {mode}: pixels within 2e-3: {(err < 2e-3).mean():.4f}, median rel err {np.median(err):.2e}")
+    assert (err < 2e-3).mean() > 0.999 and np.median(err) < 1e-6
+    halton = copy.copy(scene); halton.sampler_type = api.SAMPLER_HALTON
+    assert not np.array_equal(gpu_ctx_factory(halton).render(Context.params_from_scene(halton, seed=1))[0], gpu)
+
+
 def _halton_variants():
     def thin_lens():
         s = scenes.cornell_box(64, 64, 16, max_depth=6)
