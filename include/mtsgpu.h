@@ -58,13 +58,15 @@ enum mtsgpu_bsdf_type {
 	                               p[7] intIOR, p[8] extIOR, p[9] distribution: 0 beckmann, 1 phong, 2 ggx
 	                               (roughglass.cpp:84-91); p[10] is ignored by the library (scene files keep the
 	                               user-facing roughness of a phong distribution there for the oracle harness) */
-	MTSGPU_BSDF_WARD = 7        /* src/bsdfs/ward.cpp:42         p[0..2] diffuseReflectance, p[3..5] specularReflectance, then the
+	MTSGPU_BSDF_DIFFTRANS = 8,  /* src/bsdfs/difftrans.cpp:62    p[0..2] transmittance: ideally diffuse transmitter, two-sided */
+	MTSGPU_BSDF_WARD = 7,       /* src/bsdfs/ward.cpp:42         p[0..2] diffuseReflectance, p[3..5] specularReflectance, then the
 	                               values after Ward::configure (ward.cpp:120-139) as Ward::serialize writes them: p[6]
 	                               diffuseAmount, p[7] specularAmount, p[8] alphaX, p[9] alphaY, p[10]
 	                               specularSamplingWeight, p[11] diffuseSamplingWeight, p[12] model: 0 ward, 1 ward-duer,
 	                               2 balanced (ward.cpp:45-52). alphaX != alphaY makes the BSDF anisotropic: its meshes must
 	                               carry texture coordinates and vertex normals, and the library computes their tangents as
 	                               TriMesh::computeTangentSpaceBasis does (src/librender/trimesh.cpp:547-662) */
+	MTSGPU_BSDF_TYPE_LAST = 8
 };
 
 /* OR-ed into mtsgpu_material.type: the BRDF is wrapped in the `twosided` adapter (src/bsdfs/twosided.cpp:36-143),

@@ -13,6 +13,7 @@
 
 #define MTS_INV_TWOPI 0.15915494309189533577f
 #define BSDF_DIFFUSE_REFLECTION  0x0001u
+#define BSDF_DIFFUSE_TRANSMISSION 0x0002u
 #define BSDF_DELTA_REFLECTION    0x0004u
 #define BSDF_DELTA_TRANSMISSION  0x0008u
 #define BSDF_GLOSSY_REFLECTION   0x0010u
@@ -308,6 +309,9 @@ __device__ inline V3 bsdfF_base(const MaterialDev &m, V3 wi, V3 wo) {
 		case MTSGPU_BSDF_LAMBERTIAN:
 			if (wi.z <= 0 || wo.z <= 0) return zero;
 			return mp3(m, 0) * MTS_INV_PI;
+		case MTSGPU_BSDF_DIFFTRANS:                         // difftrans.cpp:91-96
+			if (wi.z * wo.z >= 0) return zero;
+			return mp3(m, 0) * MTS_INV_PI;
 		case MTSGPU_BSDF_MICROFACET: {
 			if (wi.z <= 0 || wo.z <= 0) return zero;
 			const float kd = m.p[6], ks = m.p[7], alphaB = m.p[8], intIOR = m.p[9], extIOR = m.p[10];
@@ -361,6 +365,9 @@ __device__ inline float bsdfPdf_base(const MaterialDev &m, V3 wi, V3 wo) {
 		case MTSGPU_BSDF_LAMBERTIAN:
 			if (wi.z <= 0 || wo.z <= 0) return 0.0f;
 			return wo.z * MTS_INV_PI;
+		case MTSGPU_BSDF_DIFFTRANS:                         // difftrans.cpp:98-102
+			if (wi.z * wo.z >= 0) return 0.0f;
+			return fabsf(wo.z) * MTS_INV_PI;
 		case MTSGPU_BSDF_MICROFACET: {
 			if (wi.z <= 0 || wo.z <= 0) return 0.0f;
 			const float kd = m.p[6], ks = m.p[7], alphaB = m.p[8], intIOR = m.p[9], extIOR = m.p[10];
@@ -406,6 +413,10 @@ __device__ inline void bsdfFPdf_base(const MaterialDev &m, V3 wi, V3 wo, V3 &f, 
 		case MTSGPU_BSDF_LAMBERTIAN:
 			if (wi.z <= 0 || wo.z <= 0) return;
 			f = mp3(m, 0) * MTS_INV_PI; pdf = wo.z * MTS_INV_PI;
+			return;
+		case MTSGPU_BSDF_DIFFTRANS:
+			if (wi.z * wo.z >= 0) return;
+			f = mp3(m, 0) * MTS_INV_PI; pdf = fabsf(wo.z) * MTS_INV_PI;
 			return;
 		case MTSGPU_BSDF_MICROFACET: {
 			if (wi.z <= 0 || wo.z <= 0) return;
@@ -546,6 +557,12 @@ __device__ inline V3 bsdfSample2_base(const MaterialDev &m, V3 wi, float sx, flo
 			wo = squareToHemispherePSA(sx, sy);
 			type = BSDF_DIFFUSE_REFLECTION;
 			return mp3(m, 0) * (1.0f / wo.z);              // Spectrum / Float multiplies by the reciprocal
+		case MTSGPU_BSDF_DIFFTRANS:                         // difftrans.cpp:104-118
+			wo = squareToHemispherePSA(sx, sy);
+			if (wi.z > 0) wo.z *= -1;
+			type = BSDF_DIFFUSE_TRANSMISSION;
+			if (wo.z == 0) return zero;
+			return mp3(m, 0) * (1.0f / fabsf(wo.z));
 		case MTSGPU_BSDF_MIRROR:
 			wo = v3(-wi.x, -wi.y, wi.z);
 			type = BSDF_DELTA_REFLECTION;
@@ -586,6 +603,13 @@ __device__ inline V3 bsdfSample3_base(const MaterialDev &m, V3 wi, float sx, flo
 			wo = squareToHemispherePSA(sx, sy);
 			type = BSDF_DIFFUSE_REFLECTION;
 			pdf = wo.z * MTS_INV_PI;
+			return mp3(m, 0) * MTS_INV_PI;
+		case MTSGPU_BSDF_DIFFTRANS:                         // difftrans.cpp:120-135
+			wo = squareToHemispherePSA(sx, sy);
+			if (wi.z > 0) wo.z *= -1;
+			type = BSDF_DIFFUSE_TRANSMISSION;
+			pdf = fabsf(wo.z) * MTS_INV_PI;
+			if (wo.z == 0) return zero;
 			return mp3(m, 0) * MTS_INV_PI;
 		case MTSGPU_BSDF_MIRROR:
 			wo = v3(-wi.x, -wi.y, wi.z);

@@ -200,6 +200,9 @@ private:
 					|| (m.type & MTSGPU_BSDF_TWOSIDED))
 				SLog(EError, "gpupath: TwoSidedBRDF around \"%s\" is not supported", nested.c_str());
 			m.type |= MTSGPU_BSDF_TWOSIDED;
+		} else if (cls == "DiffuseTransmitter") {     /* difftrans.cpp:76-79: the transmittance texture */
+			m.type = MTSGPU_BSDF_DIFFTRANS;
+			readTextureSlot(d, m.p, m.texture[0]);
 		} else if (cls == "Lambertian") {             /* lambertian.cpp:137-141 */
 			m.type = MTSGPU_BSDF_LAMBERTIAN;
 			readTextureSlot(d, m.p, m.texture[0]);

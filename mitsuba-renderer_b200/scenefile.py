@@ -20,7 +20,7 @@ from typing import List, Optional
 
 import numpy as np
 
-MAT_LAMBERTIAN, MAT_MICROFACET, MAT_MIRROR, MAT_ROUGHMETAL, MAT_DIELECTRIC, MAT_PHONG, MAT_ROUGHGLASS, MAT_WARD = range(8)
+MAT_LAMBERTIAN, MAT_MICROFACET, MAT_MIRROR, MAT_ROUGHMETAL, MAT_DIELECTRIC, MAT_PHONG, MAT_ROUGHGLASS, MAT_WARD, MAT_DIFFTRANS = range(9)
 BSDF_TWOSIDED = 0x100     # OR-ed into Material.type: wrapped in the `twosided` adapter (src/bsdfs/twosided.cpp)
 MODE_PATH, MODE_DIRECT = 0, 1
 FILTER_BOX, FILTER_GAUSSIAN = 0, 1
@@ -119,6 +119,11 @@ def phong(diffuse=(0.5, 0.5, 0.5), specular=(0.2, 0.2, 0.2), kd=1.0, ks=1.0, exp
 
 
 WARD_MODELS = {"ward": 0, "ward-duer": 1, "balanced": 2}
+
+
+def difftrans(transmittance=(0.5, 0.5, 0.5)):
+    """src/bsdfs/difftrans.cpp:64-73: ideally diffuse transmitter"""
+    return _mat(MAT_DIFFTRANS, list(transmittance))
 
 
 def ward(diffuse=(0.5, 0.5, 0.5), specular=(0.2, 0.2, 0.2), kd=1.0, ks=1.0, alpha_x=0.1, alpha_y=0.1, model="balanced",

@@ -241,14 +241,18 @@ static ref<BSDF> makeBSDF(const sio::Material &mIn) {
 			p.setBoolean("verifyEnergyConservation", false);
 			break;
 		}
+		case 8: /* difftrans (difftrans.cpp:64-73) */
+			p = Properties("difftrans");
+			p.setSpectrum("transmittance", rgb(m.p));
+			break;
 		default:
 			SLog(EError, "unknown material type %u", m.type);
 	}
 	ref<BSDF> bsdf = static_cast<BSDF *>(create(MTS_CLASS(BSDF), p));
 	/* textured slots: <ref name="reflectance" id="..."/> inside the <bsdf> element */
-	static const char *slotNames[8][2] = { { "reflectance", NULL }, { "diffuseReflectance", "specularReflectance" }, { NULL, NULL },
+	static const char *slotNames[9][2] = { { "reflectance", NULL }, { "diffuseReflectance", "specularReflectance" }, { NULL, NULL },
 		{ "specularReflectance", NULL }, { NULL, NULL }, { "diffuseReflectance", "specularReflectance" },
-		{ "specularReflectance", "specularTransmittance" }, { "diffuseReflectance", "specularReflectance" } };
+		{ "specularReflectance", "specularTransmittance" }, { "diffuseReflectance", "specularReflectance" }, { "transmittance", NULL } };
 	for (int k = 0; k < 2; ++k) {
 		if (!m.tex[k]) continue;
 		if (!g_textures || m.tex[k] > g_textures->size() || !slotNames[m.type][k]) SLog(EError, "bad texture reference");

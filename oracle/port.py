@@ -244,6 +244,10 @@ def bsdf_f_pdf(mtype, p, wi, wo):
         if wi[2] <= 0 or wo[2] <= 0:
             return zero, F(0)
         return (p[0:3] * INV_PI).astype(F), F(wo[2] * INV_PI)
+    if mtype == 8:      # difftrans.cpp:91-102
+        if F(wi[2] * wo[2]) >= 0:
+            return zero, F(0)
+        return (p[0:3] * INV_PI).astype(F), F(abs(wo[2]) * INV_PI)
     if mtype == 5:      # phong.cpp:104-162
         if wi[2] <= 0 or wo[2] <= 0:
             return zero, F(0)

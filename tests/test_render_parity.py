@@ -124,3 +124,27 @@ def test_sample_range_sharding_is_exact(gpu_ctx_factory):
     assert np.allclose(a + b, whole, rtol=1e-5, atol=1e-5)
     again, _ = ctx.render(Context.params_from_scene(s, seed=9))
     assert np.array_equal(again, whole)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", [scenefile.MODE_PATH, scenefile.MODE_DIRECT])
+def test_halton_render_with_diffuse_transmitter_matches_reference(oracle, gpu_ctx_factory, mode):
+    """difftrans.cpp:91-135: the standing panel and the tall block of the textured scene become diffuse transmitters (one
+    of them with a checkerboard transmittance); deterministic sampler, so the images are compared pixel by pixel."""
+    import numpy as np
+    from mitsuba_renderer_b200 import api
+    scene = scenes.textured_test_scene(64, 64, 16, mode, max_depth=7)
+    scene.rr_depth = 3
+    scene.sampler_type = api.SAMPLER_HALTON
+    scene.materials.append(scenefile.textured(scenefile.difftrans((0.8, 0.7, 0.6)), 0, 1))
+    scene.materials.append(scenefile.difftrans((0.5, 0.8, 0.9)))
+    scene.shapes[9].material = len(scene.materials) - 2
+    scene.shapes[4].material = len(scene.materials) - 1
+    cpu = oracle.Session(scene).render()[0]
+    gpu, _ = gpu_ctx_factory(scene).render(api.Context.params_from_scene(scene, seed=1))
+    assert np.array_equal(gpu[..., 3:], cpu[..., 3:])
+    w = np.maximum(cpu[..., 4:5], 1e-20)
+    c, g = cpu[..., :3] / w, gpu[..., :3] / w
+    err = np.abs(g - c).max(axis=-1) / (np.abs(c).max(axis=-1) + 1e-3)
+    print(f"mode {mode}: within 2e-3: {(err < 2e-3).mean():.4f}, median {np.median(err):.2e}")
+    assert (err < 2e-3).mean() > 0.995 and np.median(err) < 1e-6
