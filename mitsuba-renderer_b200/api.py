@@ -236,7 +236,11 @@ class Context:
             texs[i].p[:] = [float(v) for v in t.p]
         self._check(self.lib.mtsgpu_upload_textures(self.h, texs, len(scene.textures)))
         for i, t in enumerate(scene.textures):
-            if t.pixels is not None:
+            if t.pixels is not None and t.pixels.dtype == np.float32:      # exrtexture: linear floats
+                px = np.ascontiguousarray(t.pixels, np.float32)
+                self._check(self.lib.mtsgpu_upload_bitmap(self.h, i, px.shape[1], px.shape[0], px.shape[2], self._ptr(px),
+                                                          BITMAP_F32, 1.0))
+            elif t.pixels is not None:
                 px = np.ascontiguousarray(t.pixels, np.uint8)
                 self._check(self.lib.mtsgpu_upload_bitmap(self.h, i, px.shape[1], px.shape[0], px.shape[2], self._ptr(px),
                                                           BITMAP_U8, t.gamma))

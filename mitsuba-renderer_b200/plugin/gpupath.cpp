@@ -174,8 +174,28 @@ private:
 				v.texture = (uint32_t) d.textures->size();
 				up.texture = (int) d.textures->size() - 1;
 				d.bitmaps->push_back(up);
+			} else if (cls == "EXRTexture") {
+				/* exrtexture.cpp:61-67: Texture2D, file name, then the OpenEXR file; MIPMap::fromBitmap's defaults
+				 * (EWA, repeat, maxAnisotropy 8) */
+				mtsgpu_texture t; memset(&t, 0, sizeof(t));
+				t.type = MTSGPU_TEXTURE_BITMAP;
+				Point2 uvOffset(s); Vector2 uvScale(s);
+				s->readString();
+				t.p[0] = 0; t.p[1] = 0; t.p[2] = 8.0f;
+				t.p[6] = uvOffset.x; t.p[7] = uvOffset.y; t.p[8] = uvScale.x; t.p[9] = uvScale.y;
+				const size_t size = s->readSize();
+				ref<MemoryStream> file = new MemoryStream(size);
+				s->copyTo(file, size);
+				file->setPos(0);
+				BitmapUpload up;
+				up.gamma = 1.0f;
+				up.bitmap = new Bitmap(Bitmap::EEXR, file);         /* 128 bpp: RGBA floats */
+				d.textures->push_back(t);
+				v.texture = (uint32_t) d.textures->size();
+				up.texture = (int) d.textures->size() - 1;
+				d.bitmaps->push_back(up);
 			} else {
-				SLog(EError, "gpupath: texture class \"%s\" is outside the supported hot path (constant spectra, checkerboard, ldrtexture)", cls.c_str());
+				SLog(EError, "gpupath: texture class \"%s\" is outside the supported hot path (constant spectra, checkerboard, ldrtexture, exrtexture)", cls.c_str());
 			}
 			d.seen[id] = v;
 		}
@@ -490,7 +510,9 @@ private:
 			for (size_t i = 0; i < bitmaps.size(); ++i) {
 				const Bitmap *bmp = bitmaps[i].bitmap;
 				const int bpp = bmp->getBitsPerPixel(), w = bmp->getWidth(), h = bmp->getHeight();
-				if (bpp == 1) {                     /* ldrtexture.cpp:185-199: bit k of byte k / 8, set -> 255 */
+				if (bpp == 128) {                   /* an EXRTexture's floats */
+					check(c, mtsgpu_upload_bitmap(c, bitmaps[i].texture, w, h, 4, bmp->getData(), MTSGPU_BITMAP_F32, 1.0f));
+				} else if (bpp == 1) {              /* ldrtexture.cpp:185-199: bit k of byte k / 8, set -> 255 */
 					std::vector<uint8_t> bytes((size_t) w * h);
 					for (size_t k = 0; k < bytes.size(); ++k) bytes[k] = (bmp->getData()[k / 8] & (1 << (k % 8))) ? 255 : 0;
 					check(c, mtsgpu_upload_bitmap(c, bitmaps[i].texture, w, h, 1, &bytes[0], MTSGPU_BITMAP_U8, bitmaps[i].gamma));

@@ -37,7 +37,8 @@ class Material:
 @dataclass
 class Texture:
     """2D texture; `p` uses the layout of `mtsgpu_texture` (include/mtsgpu.h). A bitmap texture also carries its
-    pixels (uint8 [height, width, 3], top row first) and the gamma of LDRTexture (-1: sRGB)."""
+    pixels (uint8 [height, width, 3], top row first) and the gamma of LDRTexture (-1: sRGB); float32 pixels make it an
+    EXRTexture (linear, no gamma)."""
     type: int
     p: np.ndarray  # float32[12]
     pixels: Optional[np.ndarray] = None
@@ -66,6 +67,19 @@ def checkerboard(bright=(0.4, 0.4, 0.4), dark=(0.2, 0.2, 0.2), uscale=1.0, vscal
     p = np.zeros(12, np.float32)
     p[:10] = list(bright) + list(dark) + [uoffset, voffset, uscale, vscale]
     return Texture(TEX_CHECKERBOARD, p)
+
+
+def exr_texture(pixels, uscale=1.0, vscale=1.0, uoffset=0.0, voffset=0.0):
+    """<texture type="exrtexture"> (src/textures/exrtexture.cpp:34-44): linear HDR bitmap behind an EWA MIPMap with
+    `repeat` wrapping (MIPMap::fromBitmap's defaults). The pixels (float [height, width, 3]) are rounded to half
+    precision, which is what the file holds."""
+    with np.errstate(over="ignore"):
+        px = np.ascontiguousarray(pixels, np.float32).astype(np.float16).astype(np.float32)
+    assert px.ndim == 3 and px.shape[2] == 3
+    p = np.zeros(12, np.float32)
+    p[:3] = [MIP_EWA, WRAP_REPEAT, 8.0]
+    p[6:10] = [uoffset, voffset, uscale, vscale]
+    return Texture(TEX_BITMAP, p, px, 1.0)
 
 
 def textured(material: "Material", slot: int, texture_index: int) -> "Material":
@@ -408,7 +422,7 @@ def write_scene(path: str, scene: SceneDesc) -> None:
     cx, cy, cw, ch = scene.crop_rect
     with open(path, "wb") as f:
         f.write(b"MTSB200\0")
-        f.write(struct.pack("<I", 8))
+        f.write(struct.pack("<I", 9))
         f.write(np.ascontiguousarray(scene.camera_to_world, np.float32).tobytes())
         f.write(struct.pack("<5fI", scene.fov, scene.near_clip, scene.far_clip, scene.aperture_radius,
                             scene.focus_depth, int(scene.map_smaller_side) | (2 if scene.orthographic else 0)))
@@ -417,10 +431,16 @@ def write_scene(path: str, scene: SceneDesc) -> None:
                             int(scene.strict_normals), scene.luminaire_samples, scene.bsdf_samples))
         f.write(struct.pack("<2I", scene.sampler_type, scene.sampler_depth))
         f.write(struct.pack("<I", len(scene.textures)))
-        for t in scene.textures:
+        for k, t in enumerate(scene.textures):
             f.write(struct.pack("<I", t.type))
             f.write(np.ascontiguousarray(t.p, np.float32).tobytes())
-            if t.type == TEX_BITMAP:
+            if t.type == TEX_BITMAP and t.pixels.dtype == np.float32:     # exrtexture: travels as the OpenEXR file it is read from
+                from . import api
+                exr = (path + ".tex%d.exr" % k).encode()
+                api.write_exr(exr.decode(), np.concatenate([t.pixels, np.ones(t.pixels.shape[:2] + (1,), np.float32)], axis=2))
+                f.write(struct.pack("<I", 1)); f.write(struct.pack("<I", len(exr))); f.write(exr)
+            elif t.type == TEX_BITMAP:
+                f.write(struct.pack("<I", 0))
                 f.write(struct.pack("<f2I", t.gamma, t.pixels.shape[1], t.pixels.shape[0]))
                 f.write(t.pixels.tobytes())
         f.write(struct.pack("<I", len(scene.materials)))

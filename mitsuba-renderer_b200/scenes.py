@@ -9,7 +9,7 @@ import numpy as np
 
 from .scenefile import (SceneDesc, Shape, Emitter, lambertian, microfacet, mirror, roughmetal,
                         dielectric, twosided, phong, roughglass, look_at, point_light, spot_light, directional_light,
-                        constant_light, envmap_light, add_light, checkerboard, textured, ward, sphere_shape, instance_shape, bitmap_texture, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
+                        constant_light, envmap_light, add_light, checkerboard, textured, ward, sphere_shape, instance_shape, bitmap_texture, exr_texture, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
                         WRAP_REPEAT, WRAP_BLACK, WRAP_WHITE, WRAP_CLAMP, MODE_PATH, MODE_DIRECT, FILTER_BOX)
 
 F32 = np.float32
@@ -185,7 +185,8 @@ def bitmap_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6) 
     """The sphere scene with bitmap textures (src/textures/ldrtexture.cpp over src/librender/mipmap.cpp) in place of the
     checkerboards: an EWA-filtered 64 x 32 image on the walls (seen at grazing angles), a trilinear 20 x 24 image (not a
     power of two: Lanczos up-sampling) with `clamp` wrapping and gamma 2.2, an unfiltered 16 x 8 image, an EWA image
-    with `black` wrapping inside the inverted sphere, and one remaining checkerboard."""
+    with `black` wrapping inside the inverted sphere, an HDR image through `exrtexture` on an analytic sphere, and one
+    remaining checkerboard."""
     s = spheres_test_scene(width, height, spp, mode, max_depth)
     t = s.textures
     green_wall = t[0]
@@ -197,6 +198,9 @@ def bitmap_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6) 
     t.append(green_wall)
     s.materials[0] = textured(s.materials[0], 0, 3)
     s.materials[2] = textured(s.materials[2], 0, 4)
+    # an HDR image through exrtexture (src/textures/exrtexture.cpp: linear, EWA, repeat) on the textured analytic sphere
+    t.append(exr_texture((_test_image(24, 16, 5).astype(F32) / F32(255)) ** F32(2.0) * F32(1.6), uscale=2.0, vscale=1.0))
+    s.materials[13] = textured(s.materials[13], 0, 5)
     return s
 
 

@@ -109,6 +109,15 @@ static const std::vector<sio::Texture> *g_textures = NULL;   /* texture table of
 
 /* <texture type="checkerboard"> (src/textures/checkerboard.cpp:30-33, src/librender/texture.cpp:43-56) */
 static ref<Texture> makeTexture(const sio::Texture &t) {
+	if (t.type == 1 && !t.exrFile.empty()) {      /* <texture type="exrtexture"> (exrtexture.cpp:34-44) */
+		Properties p("exrtexture");
+		p.setString("filename", t.exrFile);
+		p.setFloat("uoffset", t.p[6]); p.setFloat("voffset", t.p[7]);
+		p.setFloat("uscale", t.p[8]); p.setFloat("vscale", t.p[9]);
+		ref<Texture> tex = static_cast<Texture *>(create(MTS_CLASS(Texture), p));
+		tex->configure();
+		return tex;
+	}
 	if (t.type == 1) {
 		/* <texture type="ldrtexture"> reading a 24-bit BMP file written here from the scene file's pixels
 		 * (src/textures/ldrtexture.cpp:37-84) */

@@ -14,7 +14,7 @@ namespace sio {
 enum MaterialType { MAT_LAMBERTIAN = 0, MAT_MICROFACET = 1, MAT_MIRROR = 2, MAT_ROUGHMETAL = 3, MAT_DIELECTRIC = 4 };
 
 struct Material { uint32_t type; float p[16]; uint32_t tex[2]; };
-struct Texture  { uint32_t type; float p[12]; float gamma; uint32_t width, height; std::vector<uint8_t> pixels; /* bitmap: RGB, top row first */ };
+struct Texture  { uint32_t type; float p[12]; float gamma; uint32_t width, height; std::vector<uint8_t> pixels; /* bitmap: RGB, top row first */ std::string exrFile; /* exrtexture instead */ };
 struct Emitter  { float intensity[3]; float samplingWeight; uint32_t type; float p[11]; float aux[16]; std::string envFile; /* type 5 */ };
 struct Shape {
 	uint32_t kind;   /* 0 triangle mesh, 1 analytic sphere, 2 instance of a shape group */
@@ -52,7 +52,7 @@ inline void load(const std::string &path, Scene &s) {
 	Reader r(path);
 	char magic[8]; r.raw(magic, 8);
 	if (memcmp(magic, "MTSB200", 8) != 0) throw std::runtime_error("bad magic in " + path);
-	if (r.get<uint32_t>() != 8) throw std::runtime_error("bad version in " + path);
+	if (r.get<uint32_t>() != 9) throw std::runtime_error("bad version in " + path);
 	r.raw(s.cameraToWorld, 64);
 	s.fov = r.get<float>(); s.nearClip = r.get<float>(); s.farClip = r.get<float>();
 	s.apertureRadius = r.get<float>(); s.focusDepth = r.get<float>();
@@ -69,7 +69,9 @@ inline void load(const std::string &path, Scene &s) {
 	for (auto &t : s.textures) {
 		t.type = r.get<uint32_t>(); r.raw(t.p, 48);
 		t.gamma = -1.0f; t.width = t.height = 0;
-		if (t.type == 1) {
+		if (t.type == 1 && r.get<uint32_t>() == 1) {
+			t.exrFile.resize(r.get<uint32_t>()); r.raw(&t.exrFile[0], t.exrFile.size());
+		} else if (t.type == 1) {
 			t.gamma = r.get<float>(); t.width = r.get<uint32_t>(); t.height = r.get<uint32_t>();
 			t.pixels.resize((size_t) t.width * t.height * 3); r.raw(t.pixels.data(), t.pixels.size());
 		}
