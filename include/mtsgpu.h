@@ -73,12 +73,17 @@ enum mtsgpu_bsdf_type {
  * i.e. queries with wi.z < 0 are mirrored to the upper side. Not valid for dielectric (the adapter rejects
  * BSDFs with transmission, twosided.cpp:72-74). */
 #define MTSGPU_BSDF_TWOSIDED  0x100u
+/* OR-ed into mtsgpu_material.type: the BSDF (with its twosided adapter, if any) is nested in a `mask` BSDF
+ * (src/bsdfs/mask.cpp:28-160): f and pdf are scaled by the luminance of the opacity spectrum in p[13..15] (texture slot 2),
+ * and sampling picks, with probability 1 - opacity, a delta transmission straight through the surface. */
+#define MTSGPU_BSDF_MASKED    0x200u
 #define MTSGPU_BSDF_TYPE_MASK 0x0FFu
 
 typedef struct mtsgpu_material {
-	uint32_t type;   /* mtsgpu_bsdf_type, optionally | MTSGPU_BSDF_TWOSIDED */
+	uint32_t type;   /* mtsgpu_bsdf_type, optionally | MTSGPU_BSDF_TWOSIDED | MTSGPU_BSDF_MASKED */
 	float p[16];
-	uint32_t texture[2]; /* 0: the spectrum in p[0..2] (slot 0) / p[3..5] (slot 1) is constant; k > 0: it is read from
+	uint32_t texture[3]; /* 0: the spectrum in p[0..2] (slot 0) / p[3..5] (slot 1) / p[13..15] (slot 2: the opacity of a MASK
+	                        wrapper) is constant; k > 0: it is read from
 	                        texture k-1 of mtsgpu_upload_textures at the hit's uv (Texture::getValue(its), e.g.
 	                        lambertian.cpp:96-102). Slots that the reference keeps as plain spectra (mirror, dielectric,
 	                        roughmetal eta/k) cannot be textured. */

@@ -44,7 +44,7 @@ class MtsGpuError(RuntimeError):
 
 
 class Material(C.Structure):
-    _fields_ = [("type", C.c_uint32), ("p", C.c_float * 16), ("texture", C.c_uint32 * 2)]
+    _fields_ = [("type", C.c_uint32), ("p", C.c_float * 16), ("texture", C.c_uint32 * 3)]
 
 
 class Texture(C.Structure):
@@ -248,7 +248,7 @@ class Context:
         for i, m in enumerate(scene.materials):
             mats[i].type = m.type
             mats[i].p[:] = [float(v) for v in m.p]
-            mats[i].texture[:] = [int(v) for v in m.tex]
+            mats[i].texture[:] = ([int(v) for v in m.tex] + [0, 0, 0])[:3]
         self._check(self.lib.mtsgpu_upload_materials(self.h, mats, len(scene.materials)))
         ems = (Emitter * max(1, len(scene.emitters)))()
         for i, e in enumerate(scene.emitters):

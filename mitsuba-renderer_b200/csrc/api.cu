@@ -77,7 +77,7 @@ int mtsgpu_upload_materials(mtsgpu_ctx *ctx, const mtsgpu_material *materials, i
 	REQUIRE(ctx, count >= 0 && (count == 0 || materials), MTSGPU_ERR_ARG, "upload_materials: bad arguments");
 	for (int i = 0; i < count; ++i) {
 		const uint32_t t = materials[i].type;
-		REQUIRE(ctx, (t & MTSGPU_BSDF_TYPE_MASK) <= MTSGPU_BSDF_TYPE_LAST && !(t & ~(MTSGPU_BSDF_TYPE_MASK | MTSGPU_BSDF_TWOSIDED)),
+		REQUIRE(ctx, (t & MTSGPU_BSDF_TYPE_MASK) <= MTSGPU_BSDF_TYPE_LAST && !(t & ~(MTSGPU_BSDF_TYPE_MASK | MTSGPU_BSDF_TWOSIDED | MTSGPU_BSDF_MASKED)),
 			MTSGPU_ERR_UNSUPPORTED, "material %d: unsupported BSDF type 0x%x", i, t);
 		REQUIRE(ctx, !((t & MTSGPU_BSDF_TWOSIDED) && ((t & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_DIELECTRIC ||
 			(t & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_ROUGHGLASS)), MTSGPU_ERR_UNSUPPORTED,

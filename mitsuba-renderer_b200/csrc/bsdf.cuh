@@ -648,29 +648,69 @@ __device__ inline V3 bsdfSample3_base(const MaterialDev &m, V3 wi, float sx, flo
 }
 
 // ---- twosided adapter (src/bsdfs/twosided.cpp:81-131): a BRDF seen from below behaves as from above --------
-__device__ inline V3 bsdfF(const MaterialDev &m, V3 wi, V3 wo) {
+__device__ inline V3 bsdfF_two(const MaterialDev &m, V3 wi, V3 wo) {
 	if ((m.type & MTSGPU_BSDF_TWOSIDED) && wi.z < 0) { wi.z *= -1; wo.z *= -1; }
 	return bsdfF_base(m, wi, wo);
 }
-__device__ inline void bsdfFPdf(const MaterialDev &m, V3 wi, V3 wo, V3 &f, float &pdf) {
+__device__ inline void bsdfFPdf_two(const MaterialDev &m, V3 wi, V3 wo, V3 &f, float &pdf) {
 	if ((m.type & MTSGPU_BSDF_TWOSIDED) && wi.z < 0) { wi.z *= -1; wo.z *= -1; }
 	bsdfFPdf_base(m, wi, wo, f, pdf);
 }
-__device__ inline float bsdfPdf(const MaterialDev &m, V3 wi, V3 wo) {
+__device__ inline float bsdfPdf_two(const MaterialDev &m, V3 wi, V3 wo) {
 	if ((m.type & MTSGPU_BSDF_TWOSIDED) && wi.z < 0) { wi.z *= -1; wo.z *= -1; }
 	return bsdfPdf_base(m, wi, wo);
 }
-__device__ inline V3 bsdfSample2(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, uint32_t &type) {
+__device__ inline V3 bsdfSample2_two(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, uint32_t &type) {
 	const bool flipped = (m.type & MTSGPU_BSDF_TWOSIDED) && wi.z < 0;
 	if (flipped) wi.z *= -1;
 	const V3 result = bsdfSample2_base(m, wi, sx, sy, wo, type);
 	if (flipped && !isZero(result)) wo.z *= -1;
 	return result;
 }
-__device__ inline V3 bsdfSample3(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, float &pdf, uint32_t &type) {
+__device__ inline V3 bsdfSample3_two(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, float &pdf, uint32_t &type) {
 	const bool flipped = (m.type & MTSGPU_BSDF_TWOSIDED) && wi.z < 0;
 	if (flipped) wi.z *= -1;
 	const V3 result = bsdfSample3_base(m, wi, sx, sy, wo, pdf, type);
 	if (flipped && !isZero(result) && pdf != 0) wo.z *= -1;
 	return result;
+}
+
+// ---- mask wrapper (src/bsdfs/mask.cpp:68-160): opacity-weighted nested BSDF + a delta transmission straight through ----
+__device__ inline float maskOpacity(const MaterialDev &m) {     // m_opacity->getValue(its).getLuminance()
+	return m.p[13] * 0.212671f + m.p[14] * 0.715160f + m.p[15] * 0.072169f;
+}
+__device__ inline V3 bsdfF(const MaterialDev &m, V3 wi, V3 wo) {
+	const V3 f = bsdfF_two(m, wi, wo);
+	return (m.type & MTSGPU_BSDF_MASKED) ? f * maskOpacity(m) : f;
+}
+__device__ inline void bsdfFPdf(const MaterialDev &m, V3 wi, V3 wo, V3 &f, float &pdf) {
+	bsdfFPdf_two(m, wi, wo, f, pdf);
+	if (m.type & MTSGPU_BSDF_MASKED) { const float o = maskOpacity(m); f = f * o; pdf = pdf * o; }
+}
+__device__ inline float bsdfPdf(const MaterialDev &m, V3 wi, V3 wo) {
+	const float pdf = bsdfPdf_two(m, wi, wo);
+	return (m.type & MTSGPU_BSDF_MASKED) ? pdf * maskOpacity(m) : pdf;
+}
+__device__ inline V3 bsdfSample2(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, uint32_t &type) {
+	if (!(m.type & MTSGPU_BSDF_MASKED)) return bsdfSample2_two(m, wi, sx, sy, wo, type);
+	const float probBSDF = maskOpacity(m);                       // mask.cpp:91-112
+	if (sx <= probBSDF) return bsdfSample2_two(m, wi, sx / probBSDF, sy, wo, type);
+	wo = v3(-wi.x, -wi.y, -wi.z);
+	type = BSDF_DELTA_TRANSMISSION;
+	const float r = 1 / fabsf(wo.z);
+	return v3(r, r, r);
+}
+__device__ inline V3 bsdfSample3(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, float &pdf, uint32_t &type) {
+	if (!(m.type & MTSGPU_BSDF_MASKED)) return bsdfSample3_two(m, wi, sx, sy, wo, pdf, type);
+	const float probBSDF = maskOpacity(m);                       // mask.cpp:125-147
+	if (sx <= probBSDF) {
+		const V3 result = bsdfSample3_two(m, wi, sx / probBSDF, sy, wo, pdf, type) * probBSDF;
+		pdf *= probBSDF;
+		return result;
+	}
+	wo = v3(-wi.x, -wi.y, -wi.z);
+	type = BSDF_DELTA_TRANSMISSION;
+	pdf = (1 - probBSDF) * fabsf(wo.z);
+	const float r = 1 - probBSDF;
+	return v3(r, r, r);
 }

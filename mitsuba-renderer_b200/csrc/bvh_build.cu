@@ -619,7 +619,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		const mtsgpu_material &mat = ctx->materials[m.materialId];
 		const bool anisotropic = (mat.type & MTSGPU_BSDF_TYPE_MASK) == MTSGPU_BSDF_WARD && mat.p[8] != mat.p[9];
 		bool usesRayDifferentials = false;            // a bitmap texture in one of the BSDF's slots (ldrtexture.cpp:243-245)
-		for (int k = 0; k < 2; ++k)
+		for (int k = 0; k < 3; ++k)
 			if (mat.texture[k] > 0 && mat.texture[k] <= ctx->textures.size())
 				usesRayDifferentials |= ctx->textures[mat.texture[k] - 1].type == MTSGPU_TEXTURE_BITMAP;
 		if (!(anisotropic || usesRayDifferentials) || m.sphere) continue;       // a sphere brings its own dpdu / dpdv (sphere.cpp:146-161)
@@ -728,11 +728,11 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	for (size_t i = 0; i < ctx->materials.size(); ++i) {
 		mats[i].type = ctx->materials[i].type;
 		memcpy(mats[i].p, ctx->materials[i].p, 64);
-		for (int k = 0; k < 2; ++k) {
+		for (int k = 0; k < 3; ++k) {
 			const uint32_t t = ctx->materials[i].texture[k];
 			REQUIRE(ctx, t <= ctx->textures.size(), MTSGPU_ERR_ARG, "material %zu: texture %u of slot %d was not uploaded", i, t, k);
 			const uint32_t bt = mats[i].type & MTSGPU_BSDF_TYPE_MASK;
-			const bool slotOk = k == 0 ? (bt != MTSGPU_BSDF_MIRROR && bt != MTSGPU_BSDF_DIELECTRIC)
+			const bool slotOk = k == 2 ? (mats[i].type & MTSGPU_BSDF_MASKED) != 0 : k == 0 ? (bt != MTSGPU_BSDF_MIRROR && bt != MTSGPU_BSDF_DIELECTRIC)
 				: (bt == MTSGPU_BSDF_MICROFACET || bt == MTSGPU_BSDF_PHONG || bt == MTSGPU_BSDF_ROUGHGLASS || bt == MTSGPU_BSDF_WARD);
 			REQUIRE(ctx, t == 0 || slotOk, MTSGPU_ERR_UNSUPPORTED, "material %zu: slot %d of this BSDF is a plain spectrum in the reference and cannot be textured", i, k);
 			mats[i].tex[k] = t;

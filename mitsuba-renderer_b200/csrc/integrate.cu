@@ -343,7 +343,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 			if (alive) {
 				mat = sc.materials[its.materialId];
 				float4 duv = make_float4(0, 0, 0, 0);
-				if (BMP && MODE != 2 && depth == 1 && (mat.tex[0] | mat.tex[1]) && usesRayDifferentials(sc, mat)) {
+				if (BMP && MODE != 2 && depth == 1 && (mat.tex[0] | mat.tex[1] | mat.tex[2]) && usesRayDifferentials(sc, mat)) {
 					// Intersection::getBSDF(ray) (records.inl:55-61): the camera ray is the only one with differentials
 					float lx = 0, ly = 0;
 					if (b.sampler.lensDraw) smp.get2D(DIM_LENS, lx, ly);

@@ -605,18 +605,20 @@ __device__ __noinline__ float4 cameraHitPartials(const DeviceScene &sc, float sx
 }
 
 __device__ inline bool usesRayDifferentials(const DeviceScene &sc, const MaterialDev &m) {
-	return (m.tex[0] && sc.textures[m.tex[0] - 1].type == MTSGPU_TEXTURE_BITMAP) || (m.tex[1] && sc.textures[m.tex[1] - 1].type == MTSGPU_TEXTURE_BITMAP);
+	return (m.tex[0] && sc.textures[m.tex[0] - 1].type == MTSGPU_TEXTURE_BITMAP) || (m.tex[1] && sc.textures[m.tex[1] - 1].type == MTSGPU_TEXTURE_BITMAP)
+		|| (m.tex[2] && sc.textures[m.tex[2] - 1].type == MTSGPU_TEXTURE_BITMAP);
 }
 
 // material with its textured slots replaced by their values at (u, v)
 template <bool BMP = true>
 __device__ inline void resolveTextures(const DeviceScene &sc, MaterialDev &m, float u, float v, float4 duv = make_float4(0, 0, 0, 0)) {
 #pragma unroll
-	for (int k = 0; k < 2; ++k)
+	for (int k = 0; k < 3; ++k)
 		if (m.tex[k]) {
 			const TextureDev &t = sc.textures[m.tex[k] - 1];
 			const V3 c = (BMP && t.type == MTSGPU_TEXTURE_BITMAP) ? bitmapValue(mipRef(sc), t, u, v, duv) : textureValue(t, u, v);
-			m.p[3 * k] = c.x; m.p[3 * k + 1] = c.y; m.p[3 * k + 2] = c.z;
+			const int at = k == 2 ? 13 : 3 * k;              // slot 2: the opacity of a mask wrapper
+			m.p[at] = c.x; m.p[at + 1] = c.y; m.p[at + 2] = c.z;
 		}
 }
 

@@ -48,7 +48,7 @@ struct ShapeInfo {
 // Instance of a shape group: both matrices of its Transform, and which group (DeviceScene::groups) it shows
 struct InstanceDev { float w2o[16]; float o2w[16]; uint32_t group; uint32_t pad[3]; };
 
-struct MaterialDev { uint32_t type; float p[16]; uint32_t tex[2]; uint32_t pad; };   // tex: 0 constant, k: textures[k-1]
+struct MaterialDev { uint32_t type; float p[16]; uint32_t tex[3]; };   // tex: 0 constant, k: textures[k-1]; slot 2 = mask opacity (p[13..15])
 struct TextureDev { uint32_t type; float p[12]; uint32_t pad[3]; };
 // p[]: POINT pos | SPOT pos, axis row, cutoffAngle, invTransitionWidth, cosBeamWidth, cosCutoffAngle |
 //      DIRECTIONAL dir, diskRadius | CONSTANT sphere centre, radius   (derived values filled by rebuildLuminaireCdf)

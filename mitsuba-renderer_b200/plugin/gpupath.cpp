@@ -220,6 +220,20 @@ private:
 					|| (m.type & MTSGPU_BSDF_TWOSIDED))
 				SLog(EError, "gpupath: TwoSidedBRDF around \"%s\" is not supported", nested.c_str());
 			m.type |= MTSGPU_BSDF_TWOSIDED;
+		} else if (cls == "Mask") {                   /* mask.cpp:47-51: the opacity texture, then the nested BSDF instance */
+			float opacity[3]; uint32_t opacityTexture = 0;
+			readTextureSlot(d, opacity, opacityTexture);
+			const unsigned int id = s->readUInt();
+			if (id == 0 || id <= d.maxId)
+				SLog(EError, "gpupath: Mask without a nested BSDF of its own");
+			d.maxId = id;
+			const std::string nested = s->readString();
+			m = decodePayload(nested, d);
+			if (m.type & MTSGPU_BSDF_MASKED)
+				SLog(EError, "gpupath: a Mask inside a Mask is not supported");
+			m.type |= MTSGPU_BSDF_MASKED;
+			memcpy(m.p + 13, opacity, sizeof(opacity));
+			m.texture[2] = opacityTexture;
 		} else if (cls == "DiffuseTransmitter") {     /* difftrans.cpp:76-79: the transmittance texture */
 			m.type = MTSGPU_BSDF_DIFFTRANS;
 			readTextureSlot(d, m.p, m.texture[0]);

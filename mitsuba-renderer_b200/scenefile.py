@@ -31,7 +31,7 @@ class Material:
     """BSDF parameter block; `p` uses the slot layout of `mtsgpu_material` (include/mtsgpu.h)."""
     type: int
     p: np.ndarray  # float32[16]
-    tex: tuple = (0, 0)   # per spectrum slot (p[0..2], p[3..5]): 0 constant, k > 0: SceneDesc.textures[k-1]
+    tex: tuple = (0, 0, 0)   # per spectrum slot (p[0..2], p[3..5], p[13..15] = mask opacity): 0 constant, k > 0: SceneDesc.textures[k-1]
 
 
 @dataclass
@@ -83,8 +83,9 @@ def exr_texture(pixels, uscale=1.0, vscale=1.0, uoffset=0.0, voffset=0.0):
 
 
 def textured(material: "Material", slot: int, texture_index: int) -> "Material":
-    """`material` with spectrum slot 0 (p[0..2]) or 1 (p[3..5]) read from SceneDesc.textures[texture_index]."""
-    tex = list(material.tex); tex[slot] = texture_index + 1
+    """`material` with spectrum slot 0 (p[0..2]), 1 (p[3..5]) or 2 (p[13..15]: the opacity of a mask) read from
+    SceneDesc.textures[texture_index]."""
+    tex = (list(material.tex) + [0, 0, 0])[:3]; tex[slot] = texture_index + 1
     return Material(material.type, material.p.copy(), tuple(tex))
 
 
@@ -168,6 +169,15 @@ def roughglass(specular_reflectance=(1, 1, 1), specular_transmittance=(1, 1, 1),
         stored = f32(f32(f32(2) / f32(f32(alpha) * f32(alpha))) - f32(2))
     return _mat(MAT_ROUGHGLASS, list(specular_reflectance) + list(specular_transmittance)
                 + [float(stored), int_ior, ext_ior, float(d), float(f32(alpha))])
+
+
+BSDF_MASKED = 0x200
+
+
+def masked(material: Material, opacity=(0.5, 0.5, 0.5)) -> Material:
+    """<bsdf type="mask"> around `material` (src/bsdfs/mask.cpp:28-160): opacity in p[13..15], texture slot 2."""
+    p = material.p.copy(); p[13:16] = opacity
+    return Material(material.type | BSDF_MASKED, p, tuple((list(material.tex) + [0, 0, 0])[:3]))
 
 
 def twosided(material: Material) -> Material:
@@ -422,7 +432,7 @@ def write_scene(path: str, scene: SceneDesc) -> None:
     cx, cy, cw, ch = scene.crop_rect
     with open(path, "wb") as f:
         f.write(b"MTSB200\0")
-        f.write(struct.pack("<I", 9))
+        f.write(struct.pack("<I", 10))
         f.write(np.ascontiguousarray(scene.camera_to_world, np.float32).tobytes())
         f.write(struct.pack("<5fI", scene.fov, scene.near_clip, scene.far_clip, scene.aperture_radius,
                             scene.focus_depth, int(scene.map_smaller_side) | (2 if scene.orthographic else 0)))
@@ -447,7 +457,7 @@ def write_scene(path: str, scene: SceneDesc) -> None:
         for m in scene.materials:
             f.write(struct.pack("<I", m.type))
             f.write(np.ascontiguousarray(m.p, np.float32).tobytes())
-            f.write(struct.pack("<2I", *m.tex))
+            f.write(struct.pack("<3I", *((list(m.tex) + [0, 0, 0])[:3])))
         f.write(struct.pack("<I", len(scene.emitters)))
         for k, e in enumerate(scene.emitters):
             f.write(struct.pack("<4fI", *e.intensity, e.sampling_weight, e.type))

@@ -9,7 +9,7 @@ import numpy as np
 
 from .scenefile import (SceneDesc, Shape, Emitter, lambertian, microfacet, mirror, roughmetal,
                         dielectric, twosided, phong, roughglass, look_at, point_light, spot_light, directional_light,
-                        constant_light, envmap_light, add_light, checkerboard, textured, ward, sphere_shape, instance_shape, bitmap_texture, exr_texture, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
+                        constant_light, envmap_light, add_light, checkerboard, textured, ward, sphere_shape, instance_shape, bitmap_texture, exr_texture, masked, difftrans, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
                         WRAP_REPEAT, WRAP_BLACK, WRAP_WHITE, WRAP_CLAMP, MODE_PATH, MODE_DIRECT, FILTER_BOX)
 
 F32 = np.float32
@@ -271,6 +271,19 @@ def instances_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=
     s.shapes.append(inst(0, _xform((0.8, 1.7, 1.1), -0.5, 0.0, (2.6, 3.6, 3.4))))
     s.shapes.append(inst(1, _xform((1.0, 1.0, 1.0), 0.0, 0.0, (2.7, 0.9, 1.0))))
     s.shapes.append(inst(1, _xform((1.3, 0.9, 1.3), 1.1, -0.4, (5.3, 2.8, 3.0))))
+    return s
+
+
+def masks_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6) -> SceneDesc:
+    """The textured scene with the wrappers and transmitters of src/bsdfs: the phong panel behind a checkerboard opacity
+    mask (mask.cpp), the rough-metal block behind a constant one, the tall block a diffuse transmitter (difftrans.cpp)."""
+    s = textured_test_scene(width, height, spp, mode, max_depth)
+    s.textures.append(checkerboard((1.0, 1.0, 1.0), (0.05, 0.05, 0.05), 5.0, 5.0))
+    m = s.materials
+    m[9] = textured(masked(m[9]), 2, len(s.textures) - 1)
+    m[6] = masked(m[6], (0.55, 0.6, 0.7))
+    m.append(difftrans((0.5, 0.8, 0.9)))
+    s.shapes[4].material = len(m) - 1
     return s
 
 

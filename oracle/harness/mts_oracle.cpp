@@ -167,6 +167,24 @@ static ref<Texture> makeTexture(const sio::Texture &t) {
 }
 
 static ref<BSDF> makeBSDF(const sio::Material &mIn) {
+	if (mIn.type & 0x200u) {
+		/* <bsdf type="mask"> <spectrum name="opacity"/> <bsdf .../> </bsdf>  (mask.cpp:30-33, 162-170) */
+		sio::Material inner = mIn; inner.type &= ~0x200u; inner.tex[2] = 0;
+		ref<BSDF> nested = makeBSDF(inner);
+		Properties mp("mask");
+		mp.setSpectrum("opacity", rgb(mIn.p + 13));
+		ref<BSDF> outer = static_cast<BSDF *>(create(MTS_CLASS(BSDF), mp));
+		if (mIn.tex[2]) {
+			if (!g_textures || mIn.tex[2] > g_textures->size()) SLog(EError, "bad texture reference");
+			ref<Texture> tex = makeTexture((*g_textures)[mIn.tex[2] - 1]);
+			outer->addChild("opacity", tex);
+			tex->setParent(outer);
+		}
+		outer->addChild("", nested);
+		nested->setParent(outer);
+		outer->configure();
+		return outer;
+	}
 	if (mIn.type & 0x100u) {
 		/* <bsdf type="twosided"> <bsdf type="..."/> </bsdf>  (twosided.cpp:30-35) */
 		sio::Material inner = mIn; inner.type &= 0xFFu;

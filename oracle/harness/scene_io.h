@@ -13,7 +13,7 @@ namespace sio {
 
 enum MaterialType { MAT_LAMBERTIAN = 0, MAT_MICROFACET = 1, MAT_MIRROR = 2, MAT_ROUGHMETAL = 3, MAT_DIELECTRIC = 4 };
 
-struct Material { uint32_t type; float p[16]; uint32_t tex[2]; };
+struct Material { uint32_t type; float p[16]; uint32_t tex[3]; };
 struct Texture  { uint32_t type; float p[12]; float gamma; uint32_t width, height; std::vector<uint8_t> pixels; /* bitmap: RGB, top row first */ std::string exrFile; /* exrtexture instead */ };
 struct Emitter  { float intensity[3]; float samplingWeight; uint32_t type; float p[11]; float aux[16]; std::string envFile; /* type 5 */ };
 struct Shape {
@@ -52,7 +52,7 @@ inline void load(const std::string &path, Scene &s) {
 	Reader r(path);
 	char magic[8]; r.raw(magic, 8);
 	if (memcmp(magic, "MTSB200", 8) != 0) throw std::runtime_error("bad magic in " + path);
-	if (r.get<uint32_t>() != 9) throw std::runtime_error("bad version in " + path);
+	if (r.get<uint32_t>() != 10) throw std::runtime_error("bad version in " + path);
 	r.raw(s.cameraToWorld, 64);
 	s.fov = r.get<float>(); s.nearClip = r.get<float>(); s.farClip = r.get<float>();
 	s.apertureRadius = r.get<float>(); s.focusDepth = r.get<float>();
@@ -77,7 +77,7 @@ inline void load(const std::string &path, Scene &s) {
 		}
 	}
 	s.materials.resize(r.get<uint32_t>());
-	for (auto &m : s.materials) { m.type = r.get<uint32_t>(); r.raw(m.p, 64); r.raw(m.tex, 8); }
+	for (auto &m : s.materials) { m.type = r.get<uint32_t>(); r.raw(m.p, 64); r.raw(m.tex, 12); }
 	s.emitters.resize(r.get<uint32_t>());
 	for (auto &e : s.emitters) { r.raw(e.intensity, 12); e.samplingWeight = r.get<float>(); e.type = r.get<uint32_t>(); r.raw(e.p, 44); r.raw(e.aux, 64);
 		if (e.type == 5) { e.envFile.resize(r.get<uint32_t>()); r.raw(&e.envFile[0], e.envFile.size()); } }

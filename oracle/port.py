@@ -236,6 +236,10 @@ def bsdf_f_pdf(mtype, p, wi, wo):
     """f(wi,wo) [3] and pdf(wi,wo) of one material (type + 16-float block, include/mtsgpu.h layout)."""
     wi, wo, p = np.asarray(wi, F).copy(), np.asarray(wo, F).copy(), np.asarray(p, F)
     zero = np.zeros(3, F)
+    if mtype & 0x200:   # mask (mask.cpp:68-82): nested f and pdf scaled by the opacity's luminance
+        o = F(F(F(p[13] * F(0.212671)) + F(p[14] * F(0.715160))) + F(p[15] * F(0.072169)))
+        f, pdf = bsdf_f_pdf(mtype & ~0x200, p, wi, wo)
+        return (f * o).astype(F), F(pdf * o)
     if mtype & 0x100:   # twosided adapter (twosided.cpp:81-100)
         if wi[2] < 0:
             wi[2] *= -1; wo[2] *= -1

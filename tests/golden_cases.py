@@ -74,7 +74,9 @@ def bsdf_scene():
                    scenefile.ward((0.5, 0.5, 0.5), (0.2, 0.2, 0.2), 1.0, 1.0, 0.1, 0.1, "balanced"),     # ward.cpp defaults
                    scenefile.ward((0.3, 0.2, 0.1), (0.5, 0.6, 0.7), 0.8, 0.9, 0.05, 0.3, "ward"),
                    scenefile.twosided(scenefile.ward((0.1, 0.2, 0.3), (0.7, 0.6, 0.5), 1.0, 1.0, 0.25, 0.08, "ward-duer", 0.6)),
-                   scenefile.difftrans((0.6, 0.7, 0.4))]                                           # difftrans.cpp
+                   scenefile.difftrans((0.6, 0.7, 0.4)),                                           # difftrans.cpp
+                   scenefile.masked(scenefile.lambertian((0.7, 0.6, 0.5)), (0.3, 0.6, 0.9)),        # mask.cpp
+                   scenefile.masked(scenefile.twosided(scenefile.roughmetal((1, 1, 1), 0.2)), (0.8, 0.8, 0.8))]
     for sh in s.shapes:
         sh.material = 0
     return s

@@ -148,3 +148,27 @@ def test_halton_render_with_diffuse_transmitter_matches_reference(oracle, gpu_ct
     err = np.abs(g - c).max(axis=-1) / (np.abs(c).max(axis=-1) + 1e-3)
     print(f"mode {mode}: within 2e-3: {(err < 2e-3).mean():.4f}, median {np.median(err):.2e}")
     assert (err < 2e-3).mean() > 0.995 and np.median(err) < 1e-6
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", [scenefile.MODE_PATH, scenefile.MODE_DIRECT])
+def test_halton_render_with_masks_matches_reference(oracle, gpu_ctx_factory, mode):
+    """mask.cpp:68-160: the standing phong panel gets a checkerboard opacity (a cut-out), the rough-metal block a
+    constant one; paths pass straight through with probability 1 - opacity."""
+    import numpy as np
+    from mitsuba_renderer_b200 import api
+    scene = scenes.textured_test_scene(64, 64, 16, mode, max_depth=7)
+    scene.rr_depth = 3
+    scene.sampler_type = api.SAMPLER_HALTON
+    scene.textures.append(scenefile.checkerboard((1.0, 1.0, 1.0), (0.05, 0.05, 0.05), 5.0, 5.0))
+    m = scene.materials
+    m[9] = scenefile.textured(scenefile.masked(m[9]), 2, len(scene.textures) - 1)
+    m[6] = scenefile.masked(m[6], (0.55, 0.6, 0.7))
+    cpu = oracle.Session(scene).render()[0]
+    gpu, _ = gpu_ctx_factory(scene).render(api.Context.params_from_scene(scene, seed=1))
+    assert np.array_equal(gpu[..., 3:], cpu[..., 3:])
+    w = np.maximum(cpu[..., 4:5], 1e-20)
+    c, g = cpu[..., :3] / w, gpu[..., :3] / w
+    err = np.abs(g - c).max(axis=-1) / (np.abs(c).max(axis=-1) + 1e-3)
+    print(f"mode {mode}: within 2e-3: {(err < 2e-3).mean():.4f}, median {np.median(err):.2e}")
+    assert (err < 2e-3).mean() > 0.995 and np.median(err) < 1e-6
