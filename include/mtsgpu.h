@@ -254,6 +254,14 @@ MTSGPU_API int mtsgpu_upload_mesh(mtsgpu_ctx *ctx, int shapeIndex,
 MTSGPU_API int mtsgpu_upload_sphere(mtsgpu_ctx *ctx, int shapeIndex, const float objectToWorld[16], const float worldToObject[16],
                                     float radius, const float center[3], int inverted, int materialId, int emitterId);
 
+/* An analytic cylinder (src/shapes/cylinder.cpp:30-205) at kd-tree shape index `shapeIndex`: the open tube
+ * x^2 + y^2 = radius^2, 0 <= z <= length of its object space (no caps), under objectToWorld (scale already taken out,
+ * cylinder.cpp:52-58; worldToObject is its inverse). One primitive, tested as Cylinder::rayIntersect does (ray to
+ * object space, quadratic in x / y, the nearer root inside the z range wins); hits report prim = 0xFFFFFFFF, u = v = 0.
+ * Cannot carry an area luminaire here (refused). */
+MTSGPU_API int mtsgpu_upload_cylinder(mtsgpu_ctx *ctx, int shapeIndex, const float objectToWorld[16], const float worldToObject[16],
+	float radius, float length, int materialId);
+
 /* Instancing (src/shapes/shapegroup.cpp, src/shapes/instance.cpp). A shape group is a set of triangle meshes with an
  * acceleration structure of its own (ShapeGroup::m_kdtree) that is not part of the scene by itself; mesh `meshIndex`
  * of group `groupId` (both 0, 1, 2 ... in order) is uploaded like a scene mesh, in the group's object space. Luminaires

@@ -29,7 +29,7 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_film_splat_static", "mtsgpu_render_multi", "mtsgpu_serialized_count", "mtsgpu_serialized_load",
     "mtsgpu_serialized_free", "mtsgpu_serialized_save", "mtsgpu_upload_serialized", "mtsgpu_film_develop",
     "mtsgpu_film_develop_device", "mtsgpu_film_save", "mtsgpu_write_exr", "mtsgpu_write_mfilm", "mtsgpu_sampler_values",
-    "mtsgpu_upload_textures", "mtsgpu_intersect_uv", "mtsgpu_upload_sphere", "mtsgpu_upload_bitmap", "mtsgpu_texture_lookup", "mtsgpu_upload_envmap", "mtsgpu_upload_group_mesh", "mtsgpu_upload_instance", "mtsgpu_set_camera_orthographic",
+    "mtsgpu_upload_textures", "mtsgpu_intersect_uv", "mtsgpu_upload_sphere", "mtsgpu_upload_bitmap", "mtsgpu_texture_lookup", "mtsgpu_upload_envmap", "mtsgpu_upload_group_mesh", "mtsgpu_upload_instance", "mtsgpu_set_camera_orthographic", "mtsgpu_upload_cylinder",
 ]
 SAMPLER_INDEPENDENT, SAMPLER_LD, SAMPLER_STRATIFIED, SAMPLER_HALTON, SAMPLER_HAMMERSLEY = 0, 1, 2, 3, 4
 FILM_EXR, FILM_M = 0, 1
@@ -109,6 +109,7 @@ def load_library(path: Optional[str] = None):
     lib.mtsgpu_upload_textures.argtypes = [vp, C.POINTER(Texture), C.c_int]
     lib.mtsgpu_intersect_uv.argtypes = [vp, vp, C.c_size_t, vp]
     lib.mtsgpu_upload_group_mesh.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, C.c_uint32, vp, C.c_uint32, C.c_int]
+    lib.mtsgpu_upload_cylinder.argtypes = [vp, C.c_int, vp, vp, C.c_float, C.c_float, C.c_int]
     lib.mtsgpu_upload_instance.argtypes = [vp, C.c_int, C.c_int, vp, vp]
     lib.mtsgpu_upload_envmap.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp]
     lib.mtsgpu_upload_bitmap.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_float]
@@ -274,6 +275,12 @@ class Context:
                 self._check(self.lib.mtsgpu_upload_group_mesh(self.h, g, k, self._ptr(pos), self._ptr(nrm), self._ptr(uv), len(pos),
                                                               self._ptr(tri), len(tri), s.material))
         for i, s in enumerate(scene.shapes):
+            if s.cylinder is not None:
+                from .scenefile import cylinder_params
+                radius, length, o2w, w2o = cylinder_params(s.cylinder)
+                o2w, w2o = np.ascontiguousarray(o2w, np.float32), np.ascontiguousarray(w2o, np.float32)
+                self._check(self.lib.mtsgpu_upload_cylinder(self.h, i, self._ptr(o2w), self._ptr(w2o), radius, length, s.material))
+                continue
             if s.instance is not None:              # toWorld and its fp32 Gauss-Jordan inverse (Transform(Matrix4x4))
                 from .scenefile import invert4_f32
                 o2w = np.ascontiguousarray(s.instance[1], np.float32)

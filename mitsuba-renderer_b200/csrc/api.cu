@@ -208,6 +208,40 @@ int mtsgpu_upload_sphere(mtsgpu_ctx *ctx, int shapeIndex, const float objectToWo
 	return MTSGPU_OK;
 }
 
+int mtsgpu_upload_cylinder(mtsgpu_ctx *ctx, int shapeIndex, const float objectToWorld[16], const float worldToObject[16],
+		float radius, float length, int materialId) {
+	ENTER(ctx);
+	REQUIRE(ctx, objectToWorld && worldToObject, MTSGPU_ERR_ARG, "upload_cylinder: null argument");
+	REQUIRE(ctx, shapeIndex >= 0 && (size_t) shapeIndex <= ctx->meshes.size(), MTSGPU_ERR_ARG,
+		"upload_cylinder: shapes must be uploaded in kd-tree order (got %d, expected <= %zu)", shapeIndex, ctx->meshes.size());
+	REQUIRE(ctx, length > 0 && radius > 0, MTSGPU_ERR_ARG, "upload_cylinder: m_length > 0 && m_radius > 0 (cylinder.cpp:62)");
+	if ((size_t) shapeIndex < ctx->meshes.size()) ctx->meshes.resize(shapeIndex);
+	HostMesh m;
+	m.nVert = 2; m.nTri = 1; m.materialId = materialId; m.emitterId = -1; m.hasNormals = false;
+	m.pos.assign(6, 0.0f);
+	m.tri = { 0u, INSTANCE_MARK, 1u };
+	m.cylinder = true; m.radius = radius; m.length = length;
+	memcpy(m.o2w, objectToWorld, 64); memcpy(m.w2o, worldToObject, 64);
+	// Cylinder::getAABB (cylinder.cpp:186-205): the two end circles, component by component
+	{
+		const float *M = m.o2w;
+		float lo[3], hi[3];
+		for (int i = 0; i < 3; ++i) {
+			volatile float x1 = M[4 * i] * radius, x2 = M[4 * i + 1] * radius;      // objectToWorld(Vector(r,0,0))[i], (0,r,0)[i]
+			volatile float p0 = M[4 * i + 3];                                       // objectToWorld(Point(0,0,0))[i] (affine)
+			volatile float p1 = M[4 * i + 2] * length; p1 = p1 + M[4 * i + 3];      // objectToWorld(Point(0,0,length))[i]
+			volatile float a = x1 * x1, b = x2 * x2; volatile float sum = a + b;
+			const float range = std::sqrt((float) sum);
+			volatile float l0 = p0 - range, l1 = p1 - range, h0 = p0 + range, h1 = p1 + range;
+			lo[i] = std::min((float) l0, (float) l1); hi[i] = std::max((float) h0, (float) h1);
+		}
+		for (int k = 0; k < 3; ++k) { m.pos[k] = lo[k]; m.pos[3 + k] = hi[k]; }
+	}
+	ctx->meshes.push_back(std::move(m));
+	ctx->built = false;
+	return MTSGPU_OK;
+}
+
 int mtsgpu_upload_group_mesh(mtsgpu_ctx *ctx, int groupId, int meshIndex, const float *positions, const float *normals,
 		const float *texcoords, uint32_t nVert, const uint32_t *triangles, uint32_t nTri, int materialId) {
 	ENTER(ctx);

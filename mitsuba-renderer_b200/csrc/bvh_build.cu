@@ -86,7 +86,7 @@ __global__ void k_prepare_tris(const uint4 *triIdx, const float4 *pos, const Sha
 			// slot as an instance, b_nu carries the index into the instance table
 			const float4 a = pos[t.x], b = pos[t.z];
 			memset(&r, 0, sizeof(r));
-			r.k = 3u; r.a_v = 1.0f; r.b_nu = __uint_as_float(sh.cdfOffset);
+			r.k = 3u; r.a_v = sh.isCylinder ? 2.0f : 1.0f; r.b_nu = __uint_as_float(sh.cdfOffset);       // a_v = 2: cylinder
 			r.shapeIndex = t.w; r.primIndex = 0xFFFFFFFFu;
 			lo[0] = a.x; lo[1] = a.y; lo[2] = a.z; hi[0] = b.x; hi[1] = b.y; hi[2] = b.z;
 		} else {
@@ -98,7 +98,7 @@ __global__ void k_prepare_tris(const uint4 *triIdx, const float4 *pos, const Sha
 			lo[1] = fminf(A.y, fminf(B.y, C.y)); hi[1] = fmaxf(A.y, fmaxf(B.y, C.y));
 			lo[2] = fminf(A.z, fminf(B.z, C.z)); hi[2] = fmaxf(A.z, fmaxf(B.z, C.z));
 		}
-		if (sh.materialId < 0 && !sh.isInstance) r.k |= TRI_NONOCCLUDER;     // Instance::m_occluder = true (instance.cpp:25)
+		if (sh.materialId < 0 && !sh.isInstance) r.k |= TRI_NONOCCLUDER;      // a cylinder without a BSDF is no occluder either     // Instance::m_occluder = true (instance.cpp:25)
 		accelOrig[g] = r;
 		triLo[g] = make_float4(lo[0], lo[1], lo[2], 0);
 		triHi[g] = make_float4(hi[0], hi[1], hi[2], 0);
@@ -622,7 +622,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		for (int k = 0; k < 3; ++k)
 			if (mat.texture[k] > 0 && mat.texture[k] <= ctx->textures.size())
 				usesRayDifferentials |= ctx->textures[mat.texture[k] - 1].type == MTSGPU_TEXTURE_BITMAP;
-		if (!(anisotropic || usesRayDifferentials) || m.sphere) continue;       // a sphere brings its own dpdu / dpdv (sphere.cpp:146-161)
+		if (!(anisotropic || usesRayDifferentials) || m.sphere || m.cylinder || m.instance) continue;       // analytic shapes bring their own dpdu / dpdv (sphere.cpp:146-161, cylinder.cpp:152-155)
 		if (!anisotropic && m.uv.empty()) continue;   // computeTangentSpaceBasis returns false without texture coordinates
 		REQUIRE(ctx, !m.uv.empty(), MTSGPU_ERR_ARG, "shape %zu: computeTangentSpace(): texture coordinates are required to generate "
 			"tangent vectors. If you want to render with an anisotropic material, please make sure that all associated shapes have "
@@ -648,6 +648,13 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		si.nTri = m.nTri; si.nVert = m.nVert; si.hasNormals = m.hasNormals ? 1u : 0u;
 		si.hasTexcoords = m.uv.empty() ? 0u : 1u;
 		si.hasTangents = meshTangents[s].empty() ? 0u : 1u;
+		if (m.cylinder) {
+			si.isCylinder = 1u; anySphere = true;
+			si.cdfOffset = (uint32_t) instances.size();
+			InstanceDev inst; memset(&inst, 0, sizeof(inst));
+			memcpy(inst.w2o, m.w2o, 64); memcpy(inst.o2w, m.o2w, 64); inst.radius = m.radius; inst.length = m.length;
+			instances.push_back(inst);
+		}
 		if (m.instance) {
 			si.isInstance = 1u; anySphere = true;            // non-triangle primitive: the kernels' SPH variants
 			si.cdfOffset = (uint32_t) instances.size();
@@ -676,7 +683,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		}
 		for (uint32_t t = 0; t < m.nTri; ++t) {
 			if (m.sphere) { triIdx[tOff + t] = make_uint4((uint32_t) vOff, SPHERE_MARK, SPHERE_MARK, (uint32_t) s); continue; }
-			if (m.instance) { triIdx[tOff + t] = make_uint4((uint32_t) vOff, INSTANCE_MARK, (uint32_t) vOff + 1, (uint32_t) s); continue; }
+			if (m.instance || m.cylinder) { triIdx[tOff + t] = make_uint4((uint32_t) vOff, INSTANCE_MARK, (uint32_t) vOff + 1, (uint32_t) s); continue; }
 			for (int c = 0; c < 3; ++c)
 				REQUIRE(ctx, m.tri[3*t+c] < m.nVert, MTSGPU_ERR_ARG, "shape %zu: triangle %u references vertex %u >= %u", s, t, m.tri[3*t+c], m.nVert);
 			triIdx[tOff + t] = make_uint4((uint32_t) vOff + m.tri[3*t], (uint32_t) vOff + m.tri[3*t+1], (uint32_t) vOff + m.tri[3*t+2], (uint32_t) s);
@@ -815,7 +822,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		CUDA_TRY(ctx, ctx->dGroupScenes.alloc(std::max<size_t>(groupScenes.size(), 1) * sizeof(DeviceScene)));
 		if (!instances.empty()) {
 			for (const InstanceDev &i : instances)
-				REQUIRE(ctx, i.group < groupScenes.size() && ctx->groups[i.group]->built, MTSGPU_ERR_ARG, "instance of shape group %u, which is not built", i.group);
+				REQUIRE(ctx, i.length > 0 || (i.group < groupScenes.size() && ctx->groups[i.group]->built), MTSGPU_ERR_ARG, "instance of shape group %u, which is not built", i.group);
 			CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dInstances.p, instances.data(), instances.size() * sizeof(InstanceDev), cudaMemcpyHostToDevice, st));
 			CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dGroupScenes.p, groupScenes.data(), groupScenes.size() * sizeof(DeviceScene), cudaMemcpyHostToDevice, st));
 			CUDA_TRY(ctx, cudaStreamSynchronize(st));

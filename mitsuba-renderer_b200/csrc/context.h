@@ -34,6 +34,8 @@ struct HostMesh {
 	// instance of a shape group (mtsgpu_upload_instance): two vertices (the corners of its world box, filled at build
 	// time) and one primitive {0, INSTANCE_MARK, 1}; o2w / w2o as above
 	bool instance = false; int groupId = -1;
+	// analytic cylinder (mtsgpu_upload_cylinder): like an instance (two box corners, one primitive, o2w / w2o), radius above, length here
+	bool cylinder = false; float length = 0;
 };
 #define INSTANCE_MARK 0xFFFFFFFEu
 #define SPHERE_MARK 0xFFFFFFFFu

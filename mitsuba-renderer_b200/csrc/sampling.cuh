@@ -320,7 +320,31 @@ __device__ __noinline__ void fillInstanceIntersection(const DeviceScene &sc, con
 	its.shape = shape; its.emitterId = -1;
 }
 
-// INST: the scene may hold instances (kernels of scenes without them are compiled without that branch)
+// Cylinder::fillIntersectionRecord (src/shapes/cylinder.cpp:144-165)
+__device__ __noinline__ void fillCylinderIntersection(const InstanceDev *instances, const ShapeInfo si, uint32_t shape, V3 rayO, V3 rayD, float t, Isect &its) {
+	const InstanceDev &c = instances[si.cdfOffset];
+	const float *M = c.o2w, *I = c.w2o;
+	its.p = rayO + rayD * t;
+	float lx = I[0] * its.p.x + I[1] * its.p.y + I[2] * its.p.z + I[3];
+	float ly = I[4] * its.p.x + I[5] * its.p.y + I[6] * its.p.z + I[7];
+	float lz = I[8] * its.p.x + I[9] * its.p.y + I[10] * its.p.z + I[11];
+	const float lw = I[12] * its.p.x + I[13] * its.p.y + I[14] * its.p.z + I[15];
+	if (lw != 1.0f) { const float rw = 1.0f / lw; lx *= rw; ly *= rw; lz *= rw; }
+	float phi = mts_atan2(ly, lx);
+	if (phi < 0) phi += 2 * MTS_PI;
+	its.uvx = lz / c.length;
+	its.uvy = phi / (2 * MTS_PI);
+	const V3 du = v3(-ly, lx, 0.0f) * (2 * MTS_PI), dv = v3(0.0f, 0.0f, c.length);
+	auto xfVec = [&](V3 a) { return v3(M[0] * a.x + M[1] * a.y + M[2] * a.z, M[4] * a.x + M[5] * a.y + M[6] * a.z, M[8] * a.x + M[9] * a.y + M[10] * a.z); };
+	const V3 dpdu = xfVec(du), dpdv = xfVec(dv);
+	const V3 n = normalize(xfVec(cross(du, dv)));        // Normal(normalize(objectToWorld(Vector cross(dpdu, dpdv))))
+	its.geoN = n; its.shN = n;
+	its.sh.n = n; its.sh.s = normalize(dpdu); its.sh.t = normalize(dpdv);
+	its.wi = toLocal(its.sh, -rayD);
+	its.shape = shape; its.materialId = si.materialId; its.emitterId = -1;
+}
+
+// INST: the scene may hold instances or cylinders (kernels of scenes without them are compiled without those branches)
 template <bool INST = true>
 __device__ inline void fillIntersectionSorted(const DeviceScene &sc, uint32_t tri, float u, float v, V3 rayO, V3 rayD, float t, Isect &its,
 		uint32_t nested = 0xFFFFFFFFu) {
@@ -329,6 +353,7 @@ __device__ inline void fillIntersectionSorted(const DeviceScene &sc, uint32_t tr
 	const uint32_t shape = __float_as_uint(r0.w);
 	const ShapeInfo si = sc.shapes[shape];
 	if (si.isSphere) { fillSphereIntersection(sc, r0, r1, r2, r3, r4, r5, rayO, rayD, t, its); return; }
+	if (INST && si.isCylinder) { fillCylinderIntersection(sc.instances, si, shape, rayO, rayD, t, its); return; }
 	if (INST && si.isInstance) { fillInstanceIntersection(sc, si, shape, nested, u, v, rayO, rayD, t, its); return; }
 	fillMeshIntersection<true>(sc, si, shape, r0, r1, r2, r3, r4, r5, u, v, rayO, rayD, t, its);
 }
@@ -392,7 +417,7 @@ __device__ inline void fillIntersection(const DeviceScene &sc, uint32_t shape, u
 		}
 	}
 #endif
-	fillIntersectionSorted(sc, __ldg(sc.sortedOf + si.triOffset + ((si.isSphere || si.isInstance) ? 0u : prim)), u, v, rayO, rayD, t, its, nested);
+	fillIntersectionSorted(sc, __ldg(sc.sortedOf + si.triOffset + ((si.isSphere || si.isInstance || si.isCylinder) ? 0u : prim)), u, v, rayO, rayD, t, its, nested);
 }
 
 // ---- textures: Texture2D::getValue (texture.cpp:73-82) + Checkerboard::getValue (checkerboard.cpp:47-55) ----------
@@ -541,6 +566,13 @@ __device__ __noinline__ float4 cameraHitPartials(const DeviceScene &sc, float sx
 		if (zrad > 0) { const float invZRad = 1.0f / zrad; cosPhi = local.x * invZRad; sinPhi = local.y * invZRad; }
 		const V3 dv = v3(local.z * cosPhi, local.z * sinPhi, -mts_sin(theta) * radius) * MTS_PI;
 		dpdv = v3(r3.w * dv.x + r4.x * dv.y + r4.y * dv.z, r4.z * dv.x + r4.w * dv.y + r5.x * dv.z, r5.y * dv.x + r5.z * dv.y + r5.w * dv.z);
+	} else if (si.isCylinder) {
+		const InstanceDev &c = sc.instances[si.cdfOffset];
+		const float *M = c.o2w, *I = c.w2o;
+		const float lx = I[0] * p.x + I[1] * p.y + I[2] * p.z + I[3], ly = I[4] * p.x + I[5] * p.y + I[6] * p.z + I[7];
+		const V3 du = v3(-ly, lx, 0.0f) * (2 * MTS_PI), dv = v3(0.0f, 0.0f, c.length);
+		dpdu = v3(M[0] * du.x + M[1] * du.y + M[2] * du.z, M[4] * du.x + M[5] * du.y + M[6] * du.z, M[8] * du.x + M[9] * du.y + M[10] * du.z);
+		dpdv = v3(M[0] * dv.x + M[1] * dv.y + M[2] * dv.z, M[4] * dv.x + M[5] * dv.y + M[6] * dv.z, M[8] * dv.x + M[9] * dv.y + M[10] * dv.z);
 	} else if (si.isInstance) {
 		// Instance::fillIntersectionRecord (instance.cpp:96-97): the group's dpdu / dpdv through objectToWorld
 		const InstanceDev &inst = sc.instances[si.cdfOffset];

@@ -212,11 +212,56 @@ __device__ __noinline__ bool instanceTest(const InstanceDev *instances, const De
 	return traverseGroup<SHADOW>(gs, o, nearT, farT, t, u, v, nested);
 }
 
+// Cylinder::rayIntersect (src/shapes/cylinder.cpp:76-142): the ray in object space (Transform::operator()(Ray)), the
+// quadratic of the infinite tube in x / y (solveQuadratic, util.cpp:450-488), then the z range of the two roots.
+template <bool SHADOW>
+__device__ __noinline__ bool cylinderTest(const InstanceDev *instances, uint32_t index, const RayIn r, float mint, float maxt, float &t) {
+	const InstanceDev &c = instances[index];
+	const float *M = c.w2o;
+	float ox = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(M[0], r.ox), __fmul_rn(M[1], r.oy)), __fmul_rn(M[2], r.oz)), M[3]);
+	float oy = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(M[4], r.ox), __fmul_rn(M[5], r.oy)), __fmul_rn(M[6], r.oz)), M[7]);
+	float oz = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(M[8], r.ox), __fmul_rn(M[9], r.oy)), __fmul_rn(M[10], r.oz)), M[11]);
+	const float w = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(M[12], r.ox), __fmul_rn(M[13], r.oy)), __fmul_rn(M[14], r.oz)), M[15]);
+	if (w != 1.0f) { const float rw = __frcp_rn(w); ox = __fmul_rn(ox, rw); oy = __fmul_rn(oy, rw); oz = __fmul_rn(oz, rw); }
+	const float dx = __fadd_rn(__fadd_rn(__fmul_rn(M[0], r.dx), __fmul_rn(M[1], r.dy)), __fmul_rn(M[2], r.dz));
+	const float dy = __fadd_rn(__fadd_rn(__fmul_rn(M[4], r.dx), __fmul_rn(M[5], r.dy)), __fmul_rn(M[6], r.dz));
+	const float dz = __fadd_rn(__fadd_rn(__fmul_rn(M[8], r.dx), __fmul_rn(M[9], r.dy)), __fmul_rn(M[10], r.dz));
+	const float A = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+	const float B = __fmul_rn(2.0f, __fadd_rn(__fmul_rn(dx, ox), __fmul_rn(dy, oy)));
+	const float C = __fsub_rn(__fadd_rn(__fmul_rn(ox, ox), __fmul_rn(oy, oy)), __fmul_rn(c.radius, c.radius));
+	float nearT, farT;
+	if (A == 0) {
+		if (B == 0) return false;
+		nearT = farT = __fdiv_rn(-C, B);
+	} else {
+		const float discrim = __fsub_rn(__fmul_rn(B, B), __fmul_rn(__fmul_rn(4.0f, A), C));
+		if (discrim < 0) return false;
+		const float sqrtDiscrim = __fsqrt_rn(discrim);
+		const float temp = (B < 0) ? __fmul_rn(-0.5f, __fsub_rn(B, sqrtDiscrim)) : __fmul_rn(-0.5f, __fadd_rn(B, sqrtDiscrim));
+		nearT = __fdiv_rn(temp, A);
+		farT = __fdiv_rn(C, temp);
+		if (nearT > farT) { const float x = nearT; nearT = farT; farT = x; }
+	}
+	if (nearT > maxt || farT < mint) return false;
+	const float zPosNear = __fadd_rn(oz, __fmul_rn(dz, nearT));
+	const float zPosFar = __fadd_rn(oz, __fmul_rn(dz, farT));
+	if (zPosNear >= 0 && zPosNear <= c.length && nearT >= mint) {
+		t = nearT;
+		return true;
+	} else if (zPosFar >= 0 && zPosFar <= c.length) {
+		if (farT > maxt) return false;
+		t = farT;
+		return true;
+	}
+	return false;
+}
+
 template <bool SHADOW, bool SPH>
 __device__ __forceinline__ bool primTest(const DeviceScene &sc, const float4 &q0, const float4 &q1, const float4 &q2, uint32_t kraw, const RayIn &r,
 		float mint, float maxt, float &u, float &v, float &t, uint32_t &nested) {
 	if (SPH && (kraw & TRI_K_MASK) == TRI_K_SPHERE) {
 		u = v = 0.0f;
+		if (q1.y == 2.0f) return cylinderTest<SHADOW>(sc.instances, __float_as_uint(q1.z), r, mint, maxt, t);          // a_v = 2: a cylinder
 		if (q1.y != 0.0f) return instanceTest<SHADOW>(sc.instances, sc.groups, __float_as_uint(q1.z), r, mint, maxt, t, u, v, nested);   // a_v = 1: an instance
 		return sphereTest<SHADOW>(q0, q1, r, mint, maxt, t);
 	}

@@ -42,11 +42,12 @@ struct ShapeInfo {
 	uint32_t hasTexcoords;
 	uint32_t hasTangents;     // per-vertex dpdu present (TriMesh::computeTangentSpaceBasis ran for this mesh)
 	uint32_t isSphere;        // analytic sphere (src/shapes/sphere.cpp): one primitive, no mesh arrays
+	uint32_t isCylinder;      // analytic cylinder (src/shapes/cylinder.cpp): one primitive; cdfOffset = index into DeviceScene::instances
 	uint32_t isInstance;      // instance of a shape group (src/shapes/instance.cpp): one primitive; cdfOffset = index into DeviceScene::instances
 };
 
 // Instance of a shape group: both matrices of its Transform, and which group (DeviceScene::groups) it shows
-struct InstanceDev { float w2o[16]; float o2w[16]; uint32_t group; uint32_t pad[3]; };
+struct InstanceDev { float w2o[16]; float o2w[16]; uint32_t group; float radius, length; uint32_t pad; };   // radius / length: analytic cylinder
 
 struct MaterialDev { uint32_t type; float p[16]; uint32_t tex[3]; };   // tex: 0 constant, k: textures[k-1]; slot 2 = mask opacity (p[13..15])
 struct TextureDev { uint32_t type; float p[12]; uint32_t pad[3]; };

@@ -413,6 +413,39 @@ private:
 		return out;
 	}
 
+	/* Analytic cylinder: Shape::serialize + Cylinder::serialize (cylinder.cpp:69-74): objectToWorld, radius, length */
+	static SphereData decodeCylinder(const Shape *shapeConst, float &length) {
+		Shape *shape = const_cast<Shape *>(shapeConst);
+		ConfigurableObject *parent = shape->getParent();
+		ref<MemoryStream> s = new MemoryStream();
+		ref<InstanceManager> mgr = new InstanceManager();
+		shape->setParent(NULL);
+		mgr->serialize(s, shape);
+		shape->setParent(parent);
+		s->setPos(0);
+		std::vector<mtsgpu_texture> scratch;
+		std::vector<BitmapUpload> scratchBitmaps;
+		Decoder d; d.s = s; d.textures = &scratch; d.bitmaps = &scratchBitmaps;
+		d.maxId = s->readUInt();
+		s->readString();
+		readParent(d);
+		{   /* m_bsdf */
+			const unsigned int id = s->readUInt();
+			if (id > d.maxId) { d.maxId = id; const std::string cls = s->readString(); decodePayload(cls, d); }
+		}
+		if (s->readUInt() != 0) SLog(EError, "gpupath: subsurface scattering is outside the supported hot path");
+		if (s->readUInt() != 0) SLog(EError, "gpupath: area luminaires on cylinders are outside the supported hot path");
+		if (s->readUInt() != 0 || s->readUInt() != 0) SLog(EError, "gpupath: participating media are outside the supported hot path");
+		s->readBool();                                   /* m_occluder */
+		SphereData out; memset(&out, 0, sizeof(out));
+		Transform objectToWorld(s);
+		const Matrix4x4 &m = objectToWorld.getMatrix(), &mi = objectToWorld.getInverseMatrix();
+		for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) { out.o2w[4 * i + j] = m.m[i][j]; out.w2o[4 * i + j] = mi.m[i][j]; }
+		out.radius = s->readFloat();
+		length = s->readFloat();
+		return out;
+	}
+
 	static mtsgpu_material decodeBSDF(const BSDF *bsdf, std::vector<mtsgpu_texture> &textures, std::vector<BitmapUpload> &bitmaps) {
 		ref<MemoryStream> s = new MemoryStream();
 		ref<InstanceManager> mgr = new InstanceManager();
@@ -461,7 +494,7 @@ private:
 				if (emitters[i].type == MTSGPU_EMITTER_ENVMAP) envIndex = (int) i;
 			}
 		}
-		struct MeshRef { const TriMesh *mesh; int mat, emit; bool sphere; SphereData sph; int group; };   /* group >= 0: an instance (transform in sph) */
+		struct MeshRef { const TriMesh *mesh; int mat, emit; bool sphere; SphereData sph; int group; bool cylinder; float length; };   /* group >= 0: an instance (transform in sph) */
 		struct GroupRef { std::vector<MeshRef> members; };
 		std::vector<MeshRef> meshes;
 		std::vector<GroupRef> groups;
@@ -469,6 +502,7 @@ private:
 		for (size_t i = 0; i < shapes.size(); ++i) {
 			const Shape *shape = shapes[i];
 			const bool isSphere = shape->getClass()->getName() == "Sphere";
+			const bool isCylinder = shape->getClass()->getName() == "Cylinder";
 			if (shape->getClass()->getName() == "Instance") {
 				/* instance.h:42-48: the group it shows (its kd-tree's meshes are uploaded once per group) and its transform */
 				const Instance *inst = static_cast<const Instance *>(shape);
@@ -479,7 +513,7 @@ private:
 					for (size_t k = 0; k < members.size(); ++k) {
 						if (!members[k]->getClass()->derivesFrom(MTS_CLASS(TriMesh)))
 							Log(EError, "gpupath: shape groups may hold triangle meshes only (found %s)", members[k]->getClass()->getName().c_str());
-						MeshRef r; r.mesh = static_cast<const TriMesh *>(members[k]); r.mat = -1; r.emit = -1; r.sphere = false; r.group = -1;
+						MeshRef r; r.mesh = static_cast<const TriMesh *>(members[k]); r.mat = -1; r.emit = -1; r.sphere = false; r.group = -1; r.cylinder = false; r.length = 0;
 						if (members[k]->hasBSDF()) {
 							const BSDF *bsdf = members[k]->getBSDF();
 							if (!materialIds.count(bsdf)) {
@@ -493,19 +527,21 @@ private:
 					groupIds[group] = (int) groups.size();
 					groups.push_back(gr);
 				}
-				MeshRef r; r.mesh = NULL; r.mat = -1; r.emit = -1; r.sphere = false; r.group = groupIds[group];
+				MeshRef r; r.mesh = NULL; r.mat = -1; r.emit = -1; r.sphere = false; r.group = groupIds[group]; r.cylinder = false; r.length = 0;
 				const Transform xf = inst->getWorldTransform();
 				const Matrix4x4 &m = xf.getMatrix(), &mi = xf.getInverseMatrix();
 				for (int a = 0; a < 4; ++a) for (int b = 0; b < 4; ++b) { r.sph.o2w[4 * a + b] = m.m[a][b]; r.sph.w2o[4 * a + b] = mi.m[a][b]; }
 				meshes.push_back(r);
 				continue;
 			}
-			if (!isSphere && !shape->getClass()->derivesFrom(MTS_CLASS(TriMesh)))
-				Log(EError, "gpupath: shape %i (%s) is neither a triangle mesh, a sphere nor an instance", (int) i, shape->getClass()->getName().c_str());
+			if (!isSphere && !isCylinder && !shape->getClass()->derivesFrom(MTS_CLASS(TriMesh)))
+				Log(EError, "gpupath: shape %i (%s) is neither a triangle mesh, a sphere, a cylinder nor an instance", (int) i, shape->getClass()->getName().c_str());
 			if (shape->hasSubsurface() || shape->isMediumTransition())
 				Log(EError, "gpupath: subsurface / medium transitions are outside the supported hot path");
-			MeshRef r; r.mesh = isSphere ? NULL : static_cast<const TriMesh *>(shape); r.mat = -1; r.emit = -1; r.sphere = isSphere; r.group = -1;
+			MeshRef r; r.mesh = (isSphere || isCylinder) ? NULL : static_cast<const TriMesh *>(shape); r.mat = -1; r.emit = -1; r.sphere = isSphere; r.group = -1;
+			r.cylinder = isCylinder; r.length = 0;
 			if (isSphere) r.sph = decodeSphere(shape);
+			if (isCylinder) r.sph = decodeCylinder(shape, r.length);
 			if (shape->hasBSDF()) {
 				const BSDF *bsdf = shape->getBSDF();
 				if (!materialIds.count(bsdf)) {
@@ -551,6 +587,10 @@ private:
 			for (size_t i = 0; i < meshes.size(); ++i) {
 				if (meshes[i].group >= 0) {
 					check(c, mtsgpu_upload_instance(c, (int) i, meshes[i].group, meshes[i].sph.o2w, meshes[i].sph.w2o));
+					continue;
+				}
+				if (meshes[i].cylinder) {
+					check(c, mtsgpu_upload_cylinder(c, (int) i, meshes[i].sph.o2w, meshes[i].sph.w2o, meshes[i].sph.radius, meshes[i].length, meshes[i].mat));
 					continue;
 				}
 				if (meshes[i].sphere) {

@@ -312,6 +312,7 @@ class Shape:
     emitter: int = -1                # index into SceneDesc.emitters, -1: none
     texcoords: Optional[np.ndarray] = None   # float32 [nVert, 2] or None (uv = 0 everywhere, skdtree.h:414)
     sphere: Optional[tuple] = None           # (center xyz, radius, inverted): analytic sphere (src/shapes/sphere.cpp); no arrays
+    cylinder: Optional[np.ndarray] = None    # toWorld 4x4 of a <shape type="cylinder"> (src/shapes/cylinder.cpp): unit tube x^2+y^2=1, 0<=z<=1
     instance: Optional[tuple] = None         # (group index, toWorld 4x4): instance of SceneDesc.groups[index] (src/shapes/instance.cpp)
 
 
@@ -321,6 +322,27 @@ def sphere_shape(center, radius, material=-1, inverted=False, emitter=-1) -> "Sh
     c = np.asarray(center, np.float32)
     box = np.stack([c - np.float32(abs(radius)), c + np.float32(abs(radius))]).astype(np.float32)
     return Shape(box, np.zeros((0, 3), np.uint32), None, material=material, emitter=emitter, sphere=(tuple(float(v) for v in c), float(radius), bool(inverted)))
+
+
+def cylinder_params(to_world):
+    """What Cylinder's constructor derives from `toWorld` (cylinder.cpp:52-61), in fp32: radius, length, objectToWorld =
+    toWorld * scale(1/r, 1/r, 1/l) and its inverse (the product of the inverses, toWorld's from Gauss-Jordan)."""
+    f32 = np.float32
+    m = np.asarray(to_world, f32).reshape(4, 4)
+    ln = lambda v: f32(np.sqrt(f32(f32(f32(v[0] * v[0]) + f32(v[1] * v[1])) + f32(v[2] * v[2]))))
+    radius, length = ln(m[:3, 0]), ln(m[:3, 2])
+    sv = [f32(f32(1) / radius), f32(f32(1) / radius), f32(f32(1) / length)]
+    sc = np.diag(sv + [f32(1)]).astype(f32)
+    sc_inv = np.diag([f32(f32(1) / v) for v in sv] + [f32(1)]).astype(f32)
+    return float(radius), float(length), matmul4_f32(m, sc), matmul4_f32(sc_inv, invert4_f32(m))
+
+
+def cylinder_shape(to_world, material=-1) -> "Shape":
+    """<shape type="cylinder"> with a `toWorld` transform; `positions` holds a loose box for the scene-bound helpers."""
+    m = np.asarray(to_world, np.float32).reshape(4, 4)
+    corners = np.array([[x, y, z, 1] for x in (-1, 1) for y in (-1, 1) for z in (0, 1)], np.float64)
+    w = (m.astype(np.float64) @ corners.T).T[:, :3]
+    return Shape(np.stack([w.min(0), w.max(0)]).astype(np.float32), np.zeros((0, 3), np.uint32), None, material=material, cylinder=m)
 
 
 def instance_shape(group, to_world, bounds) -> "Shape":
@@ -484,6 +506,10 @@ def write_scene(path: str, scene: SceneDesc) -> None:
                 write_mesh(s)
         f.write(struct.pack("<I", len(scene.shapes)))
         for s in scene.shapes:
+            if s.cylinder is not None:
+                f.write(struct.pack("<Ii", 3, s.material))
+                f.write(np.ascontiguousarray(s.cylinder, np.float32).tobytes())
+                continue
             if s.instance is not None:
                 f.write(struct.pack("<2I", 2, s.instance[0]))
                 f.write(np.ascontiguousarray(s.instance[1], np.float32).tobytes())

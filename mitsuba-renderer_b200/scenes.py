@@ -9,7 +9,7 @@ import numpy as np
 
 from .scenefile import (SceneDesc, Shape, Emitter, lambertian, microfacet, mirror, roughmetal,
                         dielectric, twosided, phong, roughglass, look_at, point_light, spot_light, directional_light,
-                        constant_light, envmap_light, add_light, checkerboard, textured, ward, sphere_shape, instance_shape, bitmap_texture, exr_texture, masked, difftrans, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
+                        constant_light, envmap_light, add_light, checkerboard, textured, ward, sphere_shape, instance_shape, cylinder_shape, bitmap_texture, exr_texture, masked, difftrans, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
                         WRAP_REPEAT, WRAP_BLACK, WRAP_WHITE, WRAP_CLAMP, MODE_PATH, MODE_DIRECT, FILTER_BOX)
 
 F32 = np.float32
@@ -284,6 +284,21 @@ def masks_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6) -
     m[6] = masked(m[6], (0.55, 0.6, 0.7))
     m.append(difftrans((0.5, 0.8, 0.9)))
     s.shapes[4].material = len(m) - 1
+    return s
+
+
+def cylinders_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6) -> SceneDesc:
+    """The textured scene plus analytic cylinders (src/shapes/cylinder.cpp): an upright checkerboard column, a tilted
+    rough-metal pipe the camera looks into (open ends: the inside is visible), a glass rod and a thin Ward-anisotropic bar."""
+    s = textured_test_scene(width, height, spp, mode, max_depth)
+    m = s.materials
+    m.append(textured(lambertian((0.5, 0.5, 0.5)), 0, 2))
+    col = len(m) - 1
+    rx90 = _xform(rot_x=-np.pi / 2 + 0.06, rot_y=0.04)  # object z -> (almost) world y; see the note on axis-parallel cylinders in DESIGN.md
+    s.shapes.append(cylinder_shape((_xform(translate=(1.0, 0.0, 1.2)) @ rx90 @ _xform((0.35, 0.35, 2.4))).astype(F32), material=col))
+    s.shapes.append(cylinder_shape(_xform((0.5, 0.5, 1.6), 0.5, 0.35, (3.2, 1.6, 0.3)), material=6))
+    s.shapes.append(cylinder_shape(_xform((0.2, 0.2, 2.0), 1.2, -0.2, (3.6, 2.9, 2.6)), material=7))
+    s.shapes.append(cylinder_shape(_xform((0.12, 0.12, 2.5), -0.8, 0.9, (1.2, 3.9, 3.2)), material=11))
     return s
 
 

@@ -443,6 +443,20 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 				sphere->setParent(scene);
 				continue;
 			}
+			if (sh.kind == 3) {      /* <shape type="cylinder"> <transform name="toWorld"/> </shape> (cylinder.cpp:52-58) */
+				Properties cp("cylinder");
+				cp.setTransform("toWorld", Transform(Matrix4x4(const_cast<float *>(sh.toWorld))));
+				ref<Shape> cyl = static_cast<Shape *>(create(MTS_CLASS(Shape), cp));
+				if (sh.matId >= 0) {
+					ref<BSDF> bsdf = makeBSDF(s.materials[sh.matId]);
+					cyl->addChild("", bsdf);
+					bsdf->setParent(cyl);
+				}
+				cyl->configure();
+				scene->addChild("", cyl);
+				cyl->setParent(scene);
+				continue;
+			}
 			if (sh.kind == 2) {      /* <shape type="instance"> <ref id="group"/> <transform name="toWorld"/> </shape> (instance.cpp:22-26) */
 				Properties ip("instance");
 				ip.setTransform("toWorld", Transform(Matrix4x4(const_cast<float *>(sh.toWorld))));

@@ -17,7 +17,7 @@ struct Material { uint32_t type; float p[16]; uint32_t tex[3]; };
 struct Texture  { uint32_t type; float p[12]; float gamma; uint32_t width, height; std::vector<uint8_t> pixels; /* bitmap: RGB, top row first */ std::string exrFile; /* exrtexture instead */ };
 struct Emitter  { float intensity[3]; float samplingWeight; uint32_t type; float p[11]; float aux[16]; std::string envFile; /* type 5 */ };
 struct Shape {
-	uint32_t kind;   /* 0 triangle mesh, 1 analytic sphere, 2 instance of a shape group */
+	uint32_t kind;   /* 0 triangle mesh, 1 analytic sphere, 2 instance of a shape group, 3 analytic cylinder (toWorld) */
 	uint32_t groupId; float toWorld[16];
 	float center[3], radius; uint32_t inverted;
 	uint32_t nVert, nTri; int32_t matId, emitId; uint32_t hasNormals, hasUv;
@@ -96,6 +96,11 @@ inline void load(const std::string &path, Scene &s) {
 	s.shapes.resize(r.get<uint32_t>());
 	for (auto &sh : s.shapes) {
 		sh.kind = r.get<uint32_t>();
+		if (sh.kind == 3) {
+			sh.nVert = sh.nTri = sh.hasNormals = sh.hasUv = 0; sh.emitId = -1;
+			sh.matId = r.get<int32_t>(); r.raw(sh.toWorld, 64);
+			continue;
+		}
 		if (sh.kind == 2) {
 			sh.nVert = sh.nTri = sh.hasNormals = sh.hasUv = 0; sh.matId = sh.emitId = -1;
 			sh.groupId = r.get<uint32_t>(); r.raw(sh.toWorld, 64);

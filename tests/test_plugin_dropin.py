@@ -62,7 +62,7 @@ def test_plugin_renders_through_mitsuba(oracle, mode, lights):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("make", [scenes.textured_test_scene, scenes.lights_test_scene, scenes.sphere_lights_test_scene, scenes.bitmap_test_scene, scenes.envmap_test_scene, scenes.instances_test_scene, scenes.masks_test_scene])
+@pytest.mark.parametrize("make", [scenes.textured_test_scene, scenes.lights_test_scene, scenes.sphere_lights_test_scene, scenes.bitmap_test_scene, scenes.envmap_test_scene, scenes.instances_test_scene, scenes.masks_test_scene, scenes.cylinders_test_scene])
 def test_plugin_with_the_halton_sampler_reproduces_the_cpu_image(oracle, make):
     """The deterministic case through the whole drop-in path: Mitsuba parses nothing differently, the plugin decodes
     BSDFs, textures, luminaires, sampler and camera from the live objects (rasterToCamera rebuilt with the reference's
