@@ -180,7 +180,69 @@ def box_table():
     return (vals / total).astype(np.float32), 0.5
 
 
+def tabulate(ev, size):
+    """TabulatedFilter::TabulatedFilter (src/librender/rfilter.cpp:40-69) in fp32: 15 x 15 samples of one quadrant plus a
+    zero border, normalised by 4 * size^2 / 225 times their sum."""
+    f32 = np.float32
+    size = f32(size)
+    vals = np.zeros((16, 16), np.float32)
+    total = f32(0)
+    for y in range(16):
+        ypos = f32(f32(f32(y) + f32(0.5)) / f32(15)) * size
+        for x in range(16):
+            if x != 15 and y != 15:
+                vals[y, x] = ev(f32(f32(f32(f32(x) + f32(0.5)) / f32(15)) * size), f32(ypos))
+            total = f32(total + vals[y, x])
+    total = f32(total * f32(f32(f32(f32(4) * size) * size) / f32(15 * 15)))
+    return (vals / total).astype(np.float32), float(size)
+
+
+def mitchell_table(B=1.0 / 3.0, C=1.0 / 3.0, half_size=2.0):
+    """mitchell rfilter (src/rfilters/mitchell.cpp:32-73; catmullrom.cpp is the same with B = 0, C = 0.5)"""
+    f32 = np.float32
+    B, C, size = f32(B), f32(C), f32(half_size)
+
+    def mn(x):
+        x = f32(abs(x)); x2 = f32(x * x); x3 = f32(x2 * x)
+        if x < 1:
+            a = f32(f32(f32(12) - f32(f32(9) * B)) - f32(f32(6) * C)); b = f32(f32(f32(-18) + f32(f32(12) * B)) + f32(f32(6) * C))
+            c = f32(f32(6) - f32(f32(2) * B))
+            return f32(f32(f32(1.0) / f32(6.0)) * f32(f32(f32(a * x3) + f32(b * x2)) + c))
+        if x < 2:
+            a = f32(-B - f32(f32(6) * C)); b = f32(f32(f32(6) * B) + f32(f32(30) * C))
+            c = f32(f32(f32(-12) * B) - f32(f32(48) * C)); d = f32(f32(f32(8) * B) + f32(f32(24) * C))
+            return f32(f32(f32(1.0) / f32(6.0)) * f32(f32(f32(f32(a * x3) + f32(b * x2)) + f32(c * x)) + d))
+        return f32(0)
+    return tabulate(lambda x, y: f32(mn(f32(f32(f32(2.0) * x) / size)) * mn(f32(f32(f32(2.0) * y) / size))), size)
+
+
+def wsinc_table(half_size=3.0, cycles=3.0):
+    """windowed sinc rfilter (src/rfilters/wsinc.cpp:30-54 over lanczosSinc, src/libcore/util.cpp:664-674)"""
+    import math
+    f32 = np.float32
+    size, tau = f32(half_size), f32(cycles)
+    pi = f32(3.14159265358979323846)
+
+    def lanczos(t):
+        t = f32(abs(t))
+        if t < f32(1e-4):
+            return f32(1)
+        if t > 1:
+            return f32(0)
+        t = f32(t * pi)
+        tt = f32(t * tau)
+        return f32(f32(f32(math.sin(float(tt))) / tt) * f32(f32(math.sin(float(t))) / t))       # sinf: correctly rounded in glibc
+    return tabulate(lambda x, y: f32(lanczos(f32(x / size)) * lanczos(f32(y / size))), size)
+
+
 def filter_table(filter_type):
+    from .scenefile import FILTER_MITCHELL, FILTER_CATMULLROM, FILTER_WSINC
+    if filter_type == FILTER_MITCHELL:
+        return mitchell_table()
+    if filter_type == FILTER_CATMULLROM:
+        return mitchell_table(0.0, 0.5)
+    if filter_type == FILTER_WSINC:
+        return wsinc_table()
     return box_table() if filter_type == FILTER_BOX else gaussian_table()
 
 

@@ -23,7 +23,7 @@ import numpy as np
 MAT_LAMBERTIAN, MAT_MICROFACET, MAT_MIRROR, MAT_ROUGHMETAL, MAT_DIELECTRIC, MAT_PHONG, MAT_ROUGHGLASS, MAT_WARD, MAT_DIFFTRANS = range(9)
 BSDF_TWOSIDED = 0x100     # OR-ed into Material.type: wrapped in the `twosided` adapter (src/bsdfs/twosided.cpp)
 MODE_PATH, MODE_DIRECT = 0, 1
-FILTER_BOX, FILTER_GAUSSIAN = 0, 1
+FILTER_BOX, FILTER_GAUSSIAN, FILTER_MITCHELL, FILTER_CATMULLROM, FILTER_WSINC = 0, 1, 2, 3, 4     # src/rfilters/*.cpp
 
 
 @dataclass

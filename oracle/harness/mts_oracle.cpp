@@ -332,7 +332,7 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 		fp.setInteger("cropWidth", (int) s.cropW); fp.setInteger("cropHeight", (int) s.cropH);
 		out.film = new RawFilm(fp);
 		ref<ReconstructionFilter> filter = static_cast<ReconstructionFilter *>(
-			create(MTS_CLASS(ReconstructionFilter), Properties(s.filterType == 0 ? "box" : "gaussian")));
+			create(MTS_CLASS(ReconstructionFilter), Properties(s.filterType == 0 ? "box" : s.filterType == 2 ? "mitchell" : s.filterType == 3 ? "catmullrom" : s.filterType == 4 ? "wsinc" : "gaussian")));
 		filter->configure();
 		out.film->addChild("", filter);
 		filter->setParent(out.film);

@@ -142,7 +142,9 @@ def splat_samples(scene, n, seed=12):
 
 
 SPLAT_CASES = {"box": (scenefile.FILTER_BOX, None), "gaussian": (scenefile.FILTER_GAUSSIAN, None),
-               "gaussian_crop": (scenefile.FILTER_GAUSSIAN, (5, 9, 50, 37))}
+               "gaussian_crop": (scenefile.FILTER_GAUSSIAN, (5, 9, 50, 37)),
+               "mitchell": (scenefile.FILTER_MITCHELL, None), "catmullrom": (scenefile.FILTER_CATMULLROM, (3, 2, 40, 45)),
+               "wsinc": (scenefile.FILTER_WSINC, None)}          # negative lobes: weights below zero
 
 
 def render_scene():
