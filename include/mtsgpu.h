@@ -92,6 +92,8 @@ typedef struct mtsgpu_material {
 /* 2D textures (src/librender/texture.cpp:43-82: uv' = uv * uvScale + uvOffset, then the texture's own lookup).
  *   CHECKERBOARD  src/textures/checkerboard.cpp:28-55   p[0..2] brightColor, p[3..5] darkColor, p[6..7] uvOffset,
  *                                                       p[8..9] uvScale
+ *   GRID          src/textures/gridtexture.cpp:29-60    p[0..2] brightColor, p[3..5] darkColor (the lines), p[6..7] uvOffset,
+ *                                                       p[8..9] uvScale, p[10] lineWidth
  *   BITMAP        src/textures/ldrtexture.cpp:35-253 (and exrtexture.cpp) over MIPMap, src/librender/mipmap.cpp:
  *                 p[0] filterType (0 ewa, 1 trilinear, 2 none: MIPMap::EFilterType, mipmap.h:39-46), p[1] wrapMode
  *                 (0 repeat, 1 black, 2 white, 3 clamp: mipmap.h:32-37), p[2] maxAnisotropy, p[6..7] uvOffset,
@@ -99,7 +101,7 @@ typedef struct mtsgpu_material {
  *                 lookup is filtered with the uv partials of the ray differentials (Intersection::computePartials,
  *                 src/librender/intersection.cpp:5-75); every later hit takes the bilinear level-0 lookup, which is
  *                 what the reference's filters reduce to for a ray without differentials. */
-enum mtsgpu_texture_type { MTSGPU_TEXTURE_CHECKERBOARD = 0, MTSGPU_TEXTURE_BITMAP = 1 };
+enum mtsgpu_texture_type { MTSGPU_TEXTURE_CHECKERBOARD = 0, MTSGPU_TEXTURE_BITMAP = 1, MTSGPU_TEXTURE_GRID = 2 };
 enum mtsgpu_bitmap_format { MTSGPU_BITMAP_U8 = 0, MTSGPU_BITMAP_F32 = 1 };
 typedef struct mtsgpu_texture {
 	uint32_t type;   /* mtsgpu_texture_type */

@@ -92,7 +92,7 @@ int mtsgpu_upload_textures(mtsgpu_ctx *ctx, const mtsgpu_texture *textures, int 
 	ENTER(ctx);
 	REQUIRE(ctx, count >= 0 && (count == 0 || textures), MTSGPU_ERR_ARG, "upload_textures: bad arguments");
 	for (int i = 0; i < count; ++i)
-		REQUIRE(ctx, textures[i].type == MTSGPU_TEXTURE_CHECKERBOARD || textures[i].type == MTSGPU_TEXTURE_BITMAP, MTSGPU_ERR_UNSUPPORTED,
+		REQUIRE(ctx, textures[i].type == MTSGPU_TEXTURE_CHECKERBOARD || textures[i].type == MTSGPU_TEXTURE_BITMAP || textures[i].type == MTSGPU_TEXTURE_GRID, MTSGPU_ERR_UNSUPPORTED,
 			"texture %d: unsupported texture type %u", i, textures[i].type);
 	for (int i = 0; i < count; ++i) {
 		if (textures[i].type != MTSGPU_TEXTURE_BITMAP) continue;

@@ -424,6 +424,12 @@ __device__ inline void fillIntersection(const DeviceScene &sc, uint32_t shape, u
 __device__ inline int mtsModulo(int a, int b) { const int r = a % b; return (r < 0) ? r + b : r; }   // util.h modulo()
 __device__ inline V3 textureValue(const TextureDev &t, float u, float v) {
 	const float tu = u * t.p[8] + t.p[6], tv = v * t.p[9] + t.p[7];
+	if (t.type == MTSGPU_TEXTURE_GRID) {                    // GridTexture::getValue (gridtexture.cpp:49-60); .5 is a double there
+		float gx = tu - (int) tu, gy = tv - (int) tv;
+		if (gx > .5f) gx -= 1;
+		if (gy > .5f) gy -= 1;
+		return (fabsf(gx) < t.p[10] || fabsf(gy) < t.p[10]) ? v3(t.p[3], t.p[4], t.p[5]) : v3(t.p[0], t.p[1], t.p[2]);
+	}
 	const int x = 2 * mtsModulo((int) (tu * 2), 2) - 1, y = 2 * mtsModulo((int) (tv * 2), 2) - 1;
 	return (x * y == 1) ? v3(t.p[0], t.p[1], t.p[2]) : v3(t.p[3], t.p[4], t.p[5]);
 }

@@ -152,6 +152,15 @@ private:
 				t.p[6] = uvOffset.x; t.p[7] = uvOffset.y; t.p[8] = uvScale.x; t.p[9] = uvScale.y;
 				d.textures->push_back(t);
 				v.texture = (uint32_t) d.textures->size();
+			} else if (cls == "GridTexture") {                          /* gridtexture.cpp:43-48 */
+				mtsgpu_texture t; memset(&t, 0, sizeof(t));
+				t.type = MTSGPU_TEXTURE_GRID;
+				Point2 uvOffset(s); Vector2 uvScale(s);
+				put(t.p, Spectrum(s)); put(t.p + 3, Spectrum(s));
+				t.p[10] = s->readFloat();
+				t.p[6] = uvOffset.x; t.p[7] = uvOffset.y; t.p[8] = uvScale.x; t.p[9] = uvScale.y;
+				d.textures->push_back(t);
+				v.texture = (uint32_t) d.textures->size();
 			} else if (cls == "LDRTexture") {
 				/* ldrtexture.cpp:209-228: Texture2D, file name, gamma, codec, filter, wrap mode, max. anisotropy, then the
 				 * image file itself — decoded here by the host's Bitmap class, exactly as LDRTexture's own

@@ -82,6 +82,16 @@ def exr_texture(pixels, uscale=1.0, vscale=1.0, uoffset=0.0, voffset=0.0):
     return Texture(TEX_BITMAP, p, px, 1.0)
 
 
+TEX_GRID = 2
+
+
+def grid_texture(bright=(0.4, 0.4, 0.4), dark=(0.2, 0.2, 0.2), line_width=0.01, uscale=1.0, vscale=1.0, uoffset=0.0, voffset=0.0):
+    """src/textures/gridtexture.cpp:31-35: dark lines of `line_width` on the integer uv grid"""
+    p = np.zeros(12, np.float32)
+    p[:11] = list(bright) + list(dark) + [uoffset, voffset, uscale, vscale, line_width]
+    return Texture(TEX_GRID, p)
+
+
 def textured(material: "Material", slot: int, texture_index: int) -> "Material":
     """`material` with spectrum slot 0 (p[0..2]), 1 (p[3..5]) or 2 (p[13..15]: the opacity of a mask) read from
     SceneDesc.textures[texture_index]."""

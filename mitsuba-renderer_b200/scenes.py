@@ -9,7 +9,7 @@ import numpy as np
 
 from .scenefile import (SceneDesc, Shape, Emitter, lambertian, microfacet, mirror, roughmetal,
                         dielectric, twosided, phong, roughglass, look_at, point_light, spot_light, directional_light,
-                        constant_light, envmap_light, add_light, checkerboard, textured, ward, sphere_shape, instance_shape, cylinder_shape, bitmap_texture, exr_texture, masked, difftrans, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
+                        constant_light, envmap_light, add_light, checkerboard, textured, ward, sphere_shape, instance_shape, cylinder_shape, bitmap_texture, exr_texture, grid_texture, masked, difftrans, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
                         WRAP_REPEAT, WRAP_BLACK, WRAP_WHITE, WRAP_CLAMP, MODE_PATH, MODE_DIRECT, FILTER_BOX)
 
 F32 = np.float32
@@ -284,6 +284,8 @@ def masks_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6) -
     m[6] = masked(m[6], (0.55, 0.6, 0.7))
     m.append(difftrans((0.5, 0.8, 0.9)))
     s.shapes[4].material = len(m) - 1
+    s.textures.append(grid_texture((0.8, 0.3, 0.25), (0.1, 0.1, 0.4), 0.06, 2.5, 3.0, 0.2, 0.1))      # gridtexture.cpp on the red wall
+    m[1] = textured(m[1], 0, len(s.textures) - 1)
     return s
 
 

@@ -155,8 +155,9 @@ static ref<Texture> makeTexture(const sio::Texture &t) {
 		files.push_back(path);
 		return tex;
 	}
-	if (t.type != 0) SLog(EError, "unknown texture type %u", t.type);
-	Properties p("checkerboard");
+	if (t.type != 0 && t.type != 2) SLog(EError, "unknown texture type %u", t.type);
+	Properties p(t.type == 2 ? "gridtexture" : "checkerboard");
+	if (t.type == 2) p.setFloat("lineWidth", t.p[10]);
 	p.setSpectrum("brightColor", rgb(t.p));
 	p.setSpectrum("darkColor", rgb(t.p + 3));
 	p.setFloat("uoffset", t.p[6]); p.setFloat("voffset", t.p[7]);

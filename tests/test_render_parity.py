@@ -157,13 +157,9 @@ def test_halton_render_with_masks_matches_reference(oracle, gpu_ctx_factory, mod
     constant one; paths pass straight through with probability 1 - opacity."""
     import numpy as np
     from mitsuba_renderer_b200 import api
-    scene = scenes.textured_test_scene(64, 64, 16, mode, max_depth=7)
+    scene = scenes.masks_test_scene(64, 64, 16, mode, max_depth=7)      # + a diffuse transmitter and a grid texture (gridtexture.cpp)
     scene.rr_depth = 3
     scene.sampler_type = api.SAMPLER_HALTON
-    scene.textures.append(scenefile.checkerboard((1.0, 1.0, 1.0), (0.05, 0.05, 0.05), 5.0, 5.0))
-    m = scene.materials
-    m[9] = scenefile.textured(scenefile.masked(m[9]), 2, len(scene.textures) - 1)
-    m[6] = scenefile.masked(m[6], (0.55, 0.6, 0.7))
     cpu = oracle.Session(scene).render()[0]
     gpu, _ = gpu_ctx_factory(scene).render(api.Context.params_from_scene(scene, seed=1))
     assert np.array_equal(gpu[..., 3:], cpu[..., 3:])
