@@ -260,7 +260,8 @@ MTSGPU_API int mtsgpu_upload_sphere(mtsgpu_ctx *ctx, int shapeIndex, const float
  * x^2 + y^2 = radius^2, 0 <= z <= length of its object space (no caps), under objectToWorld (scale already taken out,
  * cylinder.cpp:52-58; worldToObject is its inverse). One primitive, tested as Cylinder::rayIntersect does (ray to
  * object space, quadratic in x / y, the nearer root inside the z range wins); hits report prim = 0xFFFFFFFF, u = v = 0.
- * Cannot carry an area luminaire here (refused). */
+ * Cannot carry an area luminaire: the reference's own Cylinder has no pdfArea ("Cylinder::pdfArea(): Not implemented!",
+ * src/librender/shape.cpp via Shape::pdfSolidAngle), so a render that reaches such a luminaire stops with an error there. */
 MTSGPU_API int mtsgpu_upload_cylinder(mtsgpu_ctx *ctx, int shapeIndex, const float objectToWorld[16], const float worldToObject[16],
 	float radius, float length, int materialId);
 
