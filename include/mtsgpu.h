@@ -127,10 +127,13 @@ typedef struct mtsgpu_texture {
  *                                                      through a coarse MIP level; p[0..3] bounding sphere as for
  *                                                      CONSTANT, p[4] intensityScale; intensity unused. The map and
  *                                                      its transform follow through mtsgpu_upload_envmap. CONSTANT and
- *                                                      ENVMAP exclude each other (one background luminaire). */
+ *                                                      ENVMAP exclude each other (one background luminaire).
+ *   COLLIMATED   src/luminaires/collimated.cpp:27-75   a beam of parallel light: p[0] radius; its toWorld transform follows
+ *                                                      through mtsgpu_upload_emitter_transform. Lights the points whose
+ *                                                      projection on the beam's plane lies inside the disc, in front of it. */
 enum mtsgpu_emitter_type {
 	MTSGPU_EMITTER_AREA = 0, MTSGPU_EMITTER_POINT = 1, MTSGPU_EMITTER_SPOT = 2, MTSGPU_EMITTER_DIRECTIONAL = 3,
-	MTSGPU_EMITTER_CONSTANT = 4, MTSGPU_EMITTER_ENVMAP = 5
+	MTSGPU_EMITTER_CONSTANT = 4, MTSGPU_EMITTER_ENVMAP = 5, MTSGPU_EMITTER_COLLIMATED = 6
 };
 typedef struct mtsgpu_emitter {
 	float intensity[3];
@@ -232,6 +235,10 @@ MTSGPU_API int mtsgpu_upload_bitmap(mtsgpu_ctx *ctx, int textureIndex, int width
  * inverse (Luminaire::m_luminaireToWorld / m_worldToLuminaire; only the 3x3 parts are used, on directions). */
 MTSGPU_API int mtsgpu_upload_envmap(mtsgpu_ctx *ctx, int emitterIndex, int width, int height, int channels,
 	const float *pixels, const float luminaireToWorld[16], const float worldToLuminaire[16]);
+/* luminaireToWorld and its inverse (Luminaire::m_luminaireToWorld / m_worldToLuminaire, src/librender/luminaire.cpp:28-34)
+ * of luminaire `emitterIndex`, for the types that need a full transform (COLLIMATED). After mtsgpu_upload_emitters. */
+MTSGPU_API int mtsgpu_upload_emitter_transform(mtsgpu_ctx *ctx, int emitterIndex, const float luminaireToWorld[16],
+	const float worldToLuminaire[16]);
 MTSGPU_API int mtsgpu_upload_emitters(mtsgpu_ctx *ctx, const mtsgpu_emitter *emitters, int count);
 
 /* One TriMesh (include/mitsuba/render/trimesh.h:100-133) at kd-tree shape index `shapeIndex`

@@ -29,7 +29,7 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_film_splat_static", "mtsgpu_render_multi", "mtsgpu_serialized_count", "mtsgpu_serialized_load",
     "mtsgpu_serialized_free", "mtsgpu_serialized_save", "mtsgpu_upload_serialized", "mtsgpu_film_develop",
     "mtsgpu_film_develop_device", "mtsgpu_film_save", "mtsgpu_write_exr", "mtsgpu_write_mfilm", "mtsgpu_sampler_values",
-    "mtsgpu_upload_textures", "mtsgpu_intersect_uv", "mtsgpu_upload_sphere", "mtsgpu_upload_bitmap", "mtsgpu_texture_lookup", "mtsgpu_upload_envmap", "mtsgpu_upload_group_mesh", "mtsgpu_upload_instance", "mtsgpu_set_camera_orthographic", "mtsgpu_upload_cylinder",
+    "mtsgpu_upload_textures", "mtsgpu_intersect_uv", "mtsgpu_upload_sphere", "mtsgpu_upload_bitmap", "mtsgpu_texture_lookup", "mtsgpu_upload_envmap", "mtsgpu_upload_group_mesh", "mtsgpu_upload_instance", "mtsgpu_set_camera_orthographic", "mtsgpu_upload_cylinder", "mtsgpu_upload_emitter_transform",
 ]
 SAMPLER_INDEPENDENT, SAMPLER_LD, SAMPLER_STRATIFIED, SAMPLER_HALTON, SAMPLER_HAMMERSLEY = 0, 1, 2, 3, 4
 FILM_EXR, FILM_M = 0, 1
@@ -111,6 +111,7 @@ def load_library(path: Optional[str] = None):
     lib.mtsgpu_upload_group_mesh.argtypes = [vp, C.c_int, C.c_int, vp, vp, vp, C.c_uint32, vp, C.c_uint32, C.c_int]
     lib.mtsgpu_upload_cylinder.argtypes = [vp, C.c_int, vp, vp, C.c_float, C.c_float, C.c_int]
     lib.mtsgpu_upload_instance.argtypes = [vp, C.c_int, C.c_int, vp, vp]
+    lib.mtsgpu_upload_emitter_transform.argtypes = [vp, C.c_int, vp, vp]
     lib.mtsgpu_upload_envmap.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, vp]
     lib.mtsgpu_upload_bitmap.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_float]
     lib.mtsgpu_upload_sphere.argtypes = [vp, C.c_int, vp, vp, C.c_float, vp, C.c_int, C.c_int, C.c_int]
@@ -321,6 +322,11 @@ class Context:
             ems[i].p[:] = [float(v) for v in e.abi_params()]
         self._check(self.lib.mtsgpu_upload_emitters(self.h, ems, len(scene.emitters)))
         for i, e in enumerate(scene.emitters):
+            if e.type == 6:                        # collimated beam: toWorld and its fp32 Gauss-Jordan inverse
+                from .scenefile import invert4_f32
+                l2w = np.ascontiguousarray(np.asarray(e.aux, np.float32).reshape(4, 4))
+                w2l = np.ascontiguousarray(invert4_f32(l2w))
+                self._check(self.lib.mtsgpu_upload_emitter_transform(self.h, i, self._ptr(l2w), self._ptr(w2l)))
             if e.pixels is not None:               # environment map: toWorld and its fp32 Gauss-Jordan inverse (Transform(Matrix4x4))
                 from .scenefile import invert4_f32
                 l2w = np.ascontiguousarray(np.asarray(e.aux, np.float32).reshape(4, 4))

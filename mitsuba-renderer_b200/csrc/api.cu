@@ -142,7 +142,7 @@ int mtsgpu_upload_emitters(mtsgpu_ctx *ctx, const mtsgpu_emitter *emitters, int 
 	REQUIRE(ctx, count >= 0 && (count == 0 || emitters), MTSGPU_ERR_ARG, "upload_emitters: bad arguments");
 	int backgrounds = 0;
 	for (int i = 0; i < count; ++i) {
-		REQUIRE(ctx, emitters[i].type <= MTSGPU_EMITTER_ENVMAP, MTSGPU_ERR_UNSUPPORTED, "emitter %d: unsupported luminaire type %u", i, emitters[i].type);
+		REQUIRE(ctx, emitters[i].type <= MTSGPU_EMITTER_COLLIMATED, MTSGPU_ERR_UNSUPPORTED, "emitter %d: unsupported luminaire type %u", i, emitters[i].type);
 		if (emitters[i].type == MTSGPU_EMITTER_SPOT)      // Assert(m_cutoffAngle >= m_beamWidth), spot.cpp:42
 			REQUIRE(ctx, emitters[i].p[7] >= emitters[i].p[6], MTSGPU_ERR_ARG, "emitter %d: cutoffAngle must be >= beamWidth", i);
 		backgrounds += emitters[i].type == MTSGPU_EMITTER_CONSTANT || emitters[i].type == MTSGPU_EMITTER_ENVMAP;
@@ -150,7 +150,18 @@ int mtsgpu_upload_emitters(mtsgpu_ctx *ctx, const mtsgpu_emitter *emitters, int 
 	REQUIRE(ctx, backgrounds <= 1, MTSGPU_ERR_UNSUPPORTED, "upload_emitters: at most one background luminaire");
 	ctx->emitters.assign(emitters, emitters + count);
 	ctx->envEmitter = -1; ctx->envBitmap = HostBitmap();
+	ctx->emitterXf.assign((size_t) count * 32, 0.0f);
 	ctx->built = false;
+	return MTSGPU_OK;
+}
+
+int mtsgpu_upload_emitter_transform(mtsgpu_ctx *ctx, int emitterIndex, const float luminaireToWorld[16], const float worldToLuminaire[16]) {
+	ENTER(ctx);
+	REQUIRE(ctx, luminaireToWorld && worldToLuminaire && emitterIndex >= 0 && (size_t) emitterIndex < ctx->emitters.size(), MTSGPU_ERR_ARG,
+		"upload_emitter_transform: emitter %d is not in the uploaded table", emitterIndex);
+	memcpy(&ctx->emitterXf[(size_t) emitterIndex * 32], luminaireToWorld, 64);
+	memcpy(&ctx->emitterXf[(size_t) emitterIndex * 32 + 16], worldToLuminaire, 64);
+	ctx->lumImportance = -1;
 	return MTSGPU_OK;
 }
 

@@ -542,6 +542,9 @@ int rebuildLuminaireCdf(mtsgpu_ctx *ctx, bool importance) {
 				em.p[9] = std::cos(cutoffAngle);
 				break;
 			}
+			case MTSGPU_EMITTER_COLLIMATED:        // collimated.cpp:29-37
+				em.p[0] = src.p[0];
+				break;
 			case MTSGPU_EMITTER_DIRECTIONAL:       // DirectionalLuminaire::preprocess (directional.cpp:64-71)
 				memcpy(em.p, src.p, 16);
 				if (src.p[3] == 0.0f) em.p[3] = radius;
@@ -580,6 +583,14 @@ int rebuildLuminaireCdf(mtsgpu_ctx *ctx, bool importance) {
 		}
 	} else {
 		lumCdf.assign(1, 0.0f);
+	}
+	{
+		std::vector<float> xf = ctx->emitterXf;
+		xf.resize(std::max<size_t>(emitters.size(), 1) * 32, 0.0f);
+		CUDA_TRY(ctx, ctx->dEmitterXf.alloc(xf.size() * sizeof(float)));
+		CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dEmitterXf.p, xf.data(), xf.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+		CUDA_TRY(ctx, cudaStreamSynchronize(st));
+		ctx->scene.emitterXf = ctx->dEmitterXf.as<float>();
 	}
 	CUDA_TRY(ctx, ctx->dEmitters.alloc(std::max<size_t>(emitters.size(), 1) * sizeof(EmitterDev)));
 	CUDA_TRY(ctx, ctx->dLumCdf.alloc(lumCdf.size() * sizeof(float)));

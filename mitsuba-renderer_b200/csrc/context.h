@@ -61,6 +61,7 @@ struct mtsgpu_ctx {
 	std::vector<mtsgpu_emitter> emitters;
 	std::vector<mtsgpu_texture> textures;
 	std::vector<HostBitmap> bitmaps;          // parallel to textures; filled by mtsgpu_upload_bitmap
+	std::vector<float> emitterXf;             // 32 floats per emitter (luminaireToWorld, worldToLuminaire), zeros unless uploaded
 	std::vector<mtsgpu_ctx *> groups;         // shape groups: child contexts with their own acceleration structure
 	HostBitmap envBitmap; int envEmitter = -1; float envL2W[9] = {}, envW2L[9] = {};   // mtsgpu_upload_envmap
 	uint32_t envTexture = 0;                  // index of the map's entry in the device texture table
@@ -75,7 +76,7 @@ struct mtsgpu_ctx {
 	bool built = false;
 	DeviceScene scene;
 	DevBuf dTriAccel, dTriAccelOrig, dNodes, dTriIdx, dPositions, dNormals, dShapes, dMaterials, dEmitters,
-	       dLumCdf, dAreaCdf, dTexcoords, dTextures, dTangents, dShadeTris, dSortedOf, dTexels, dMipLevels, dMipLut, dCamera, dEnvData, dInstances, dGroupScenes;
+	       dLumCdf, dAreaCdf, dTexcoords, dTextures, dTangents, dShadeTris, dSortedOf, dTexels, dMipLevels, dMipLut, dCamera, dEnvData, dInstances, dGroupScenes, dEmitterXf;
 	mtsgpu_accel_info accel = {};
 
 	// trace staging + counters

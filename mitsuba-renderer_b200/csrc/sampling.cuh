@@ -884,6 +884,23 @@ __device__ inline void sampleLuminaire(const DeviceScene &sc, V3 p, float sx, fl
 		out.p = p - dir * (2 * em.p[3]); out.n = v3(0, 0, 0);
 		out.d = dir;
 		pdf = 1.0f; out.mis = false;
+	} else if (em.type == MTSGPU_EMITTER_COLLIMATED) {
+		// CollimatedBeamLuminaire::sample (collimated.cpp:63-75)
+		const float *L = sc.emitterXf + (size_t) index * 32, *W = L + 16;
+		float lx = W[0] * p.x + W[1] * p.y + W[2] * p.z + W[3], ly = W[4] * p.x + W[5] * p.y + W[6] * p.z + W[7],
+			lz = W[8] * p.x + W[9] * p.y + W[10] * p.z + W[11];
+		const float lw = W[12] * p.x + W[13] * p.y + W[14] * p.z + W[15];
+		if (lw != 1.0f) { const float rw = 1.0f / lw; lx *= rw; ly *= rw; lz *= rw; }
+		out.mis = false; out.n = v3(0, 0, 0);
+		if (!(sqrtf(lx * lx + ly * ly) > em.p[0] || lz < 0)) {
+			float wx = L[0] * lx + L[1] * ly + L[2] * 0.0f + L[3], wy = L[4] * lx + L[5] * ly + L[6] * 0.0f + L[7],
+				wz = L[8] * lx + L[9] * ly + L[10] * 0.0f + L[11];
+			const float ww = L[12] * lx + L[13] * ly + L[14] * 0.0f + L[15];
+			if (ww != 1.0f) { const float rw = 1.0f / ww; wx *= rw; wy *= rw; wz *= rw; }
+			out.p = v3(wx, wy, wz);
+			out.d = v3(L[0] * 0.0f + L[1] * 0.0f + L[2], L[4] * 0.0f + L[5] * 0.0f + L[6], L[8] * 0.0f + L[9] * 0.0f + L[10]);     // m_direction = luminaireToWorld(Vector(0, 0, 1))
+			pdf = 1.0f;
+		}
 	} else if (em.type == MTSGPU_EMITTER_ENVMAP) {
 		// EnvMapLuminaire::sample (envmap.cpp:170-182)
 		const EnvSample es = envSampleDirection(mipRef(sc), sc.textures[__float_as_uint(em.p[5])], sc.envData, em.p[4], sx, sy);

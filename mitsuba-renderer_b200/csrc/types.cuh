@@ -88,6 +88,7 @@ struct DeviceScene {
 	const InstanceDev *instances;            // instances of shape groups (empty unless hasInstances)
 	const struct DeviceScene *groups;        // the groups' own scenes: acceleration structure and shading records in object space
 	uint32_t hasInstances, padInst;
+	const float *emitterXf;     // per emitter: luminaireToWorld 4x4, worldToLuminaire 4x4 (collimated beams)
 	const float *envData;       // environment map: worldToLuminaire 3x3, luminaireToWorld 3x3, density resolution, CDF, pdf (sampling.cuh)
 	const struct CameraDev *camera;   // the render's camera: ray differentials of a camera-ray hit are rebuilt from it
 	const ShapeInfo *shapes;

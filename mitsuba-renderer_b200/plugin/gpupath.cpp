@@ -349,6 +349,11 @@ private:
 			put(e.intensity, Spectrum(s));
 			BSphere bs(s);
 			e.p[0] = bs.center.x; e.p[1] = bs.center.y; e.p[2] = bs.center.z; e.p[3] = bs.radius;
+		} else if (cls == "CollimatedBeamLuminaire") {          /* collimated.cpp:46-50 */
+			e.type = MTSGPU_EMITTER_COLLIMATED;
+			put(e.intensity, Spectrum(s));
+			e.p[0] = s->readFloat();
+			for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) { env.l2w[4 * i + j] = l2w.m[i][j]; env.w2l[4 * i + j] = w2l.m[i][j]; }
 		} else if (cls == "EnvMapLuminaire") {                  /* envmap.cpp:79-92, after preprocess() */
 			e.type = MTSGPU_EMITTER_ENVMAP;
 			e.intensity[0] = e.intensity[1] = e.intensity[2] = 1.0f;
@@ -364,7 +369,7 @@ private:
 			for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) { env.l2w[4 * i + j] = l2w.m[i][j]; env.w2l[4 * i + j] = w2l.m[i][j]; }
 		} else {
 			SLog(EError, "gpupath: luminaire class \"%s\" is outside the supported hot path "
-				"(area, point, spot, directional, constant, envmap)", cls.c_str());
+				"(area, point, spot, directional, constant, envmap, collimated)", cls.c_str());
 		}
 		(void) l2w;
 	}
@@ -489,6 +494,7 @@ private:
 		std::vector<mtsgpu_emitter> emitters(luminaires.size());
 		std::map<const Luminaire *, int> emitterIds;
 		EnvUpload env; int envIndex = -1;
+		std::vector<EnvUpload> beams; std::vector<int> beamIndex;      /* collimated beams: their transforms */
 		for (size_t i = 0; i < luminaires.size(); ++i) {
 			const Luminaire *lum = luminaires[i];
 			memset(&emitters[i], 0, sizeof(mtsgpu_emitter));
@@ -499,8 +505,10 @@ private:
 				emitters[i].type = MTSGPU_EMITTER_AREA;
 				put(emitters[i].intensity, lum->Le(ShapeSamplingRecord(Point(0.0f), Normal(0, 0, 1)), Vector(0, 0, 1)));
 			} else {
-				decodeLuminaire(lum, emitters[i], env);
-				if (emitters[i].type == MTSGPU_EMITTER_ENVMAP) envIndex = (int) i;
+				EnvUpload one;
+				decodeLuminaire(lum, emitters[i], one);
+				if (emitters[i].type == MTSGPU_EMITTER_ENVMAP) { envIndex = (int) i; env = one; }
+				if (emitters[i].type == MTSGPU_EMITTER_COLLIMATED) { beamIndex.push_back((int) i); beams.push_back(one); }
 			}
 		}
 		struct MeshRef { const TriMesh *mesh; int mat, emit; bool sphere; SphereData sph; int group; bool cylinder; float length; };   /* group >= 0: an instance (transform in sph) */
@@ -581,6 +589,8 @@ private:
 			}
 			check(c, mtsgpu_upload_materials(c, materials.empty() ? NULL : &materials[0], (int) materials.size()));
 			check(c, mtsgpu_upload_emitters(c, emitters.empty() ? NULL : &emitters[0], (int) emitters.size()));
+			for (size_t b = 0; b < beams.size(); ++b)
+				check(c, mtsgpu_upload_emitter_transform(c, beamIndex[b], beams[b].l2w, beams[b].w2l));
 			if (envIndex >= 0)      /* Bitmap::loadEXR leaves RGBA floats (bitmap.cpp:247-273) */
 				check(c, mtsgpu_upload_envmap(c, envIndex, env.bitmap->getWidth(), env.bitmap->getHeight(), 4,
 					env.bitmap->getFloatData(), env.l2w, env.w2l));

@@ -196,7 +196,7 @@ def twosided(material: Material) -> Material:
     return Material(material.type | BSDF_TWOSIDED, material.p.copy(), material.tex)
 
 
-EMITTER_AREA, EMITTER_POINT, EMITTER_SPOT, EMITTER_DIRECTIONAL, EMITTER_CONSTANT, EMITTER_ENVMAP = range(6)
+EMITTER_AREA, EMITTER_POINT, EMITTER_SPOT, EMITTER_DIRECTIONAL, EMITTER_CONSTANT, EMITTER_ENVMAP, EMITTER_COLLIMATED = range(7)
 
 
 @dataclass
@@ -286,6 +286,13 @@ def directional_light(direction, intensity=(1.0, 1.0, 1.0), sampling_weight=1.0)
 def constant_light(intensity=(1.0, 1.0, 1.0), sampling_weight=1.0):
     """src/luminaires/constant.cpp:29-32: constant background; its bounding sphere is derived from the scene."""
     return Emitter(tuple(intensity), sampling_weight, EMITTER_CONSTANT)
+
+
+def collimated_light(origin, target, up=(0, 1, 0), radius=0.01, intensity=(1.0, 1.0, 1.0), sampling_weight=1.0):
+    """src/luminaires/collimated.cpp:29-37 with toWorld = lookAt(origin, target, up): a beam of parallel light of the
+    given radius along the view direction."""
+    m = look_at(origin, target, up)
+    return Emitter(tuple(intensity), sampling_weight, EMITTER_COLLIMATED, (float(radius),), tuple(m.reshape(16)))
 
 
 def envmap_light(pixels, intensity_scale=1.0, to_world=None, sampling_weight=1.0):

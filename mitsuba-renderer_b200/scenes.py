@@ -9,7 +9,7 @@ import numpy as np
 
 from .scenefile import (SceneDesc, Shape, Emitter, lambertian, microfacet, mirror, roughmetal,
                         dielectric, twosided, phong, roughglass, look_at, point_light, spot_light, directional_light,
-                        constant_light, envmap_light, add_light, checkerboard, textured, ward, sphere_shape, instance_shape, cylinder_shape, bitmap_texture, exr_texture, grid_texture, masked, difftrans, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
+                        constant_light, envmap_light, collimated_light, add_light, checkerboard, textured, ward, sphere_shape, instance_shape, cylinder_shape, bitmap_texture, exr_texture, grid_texture, masked, difftrans, MIP_EWA, MIP_TRILINEAR, MIP_NONE,
                         WRAP_REPEAT, WRAP_BLACK, WRAP_WHITE, WRAP_CLAMP, MODE_PATH, MODE_DIRECT, FILTER_BOX)
 
 F32 = np.float32
@@ -231,6 +231,8 @@ def envmap_test_scene(width=96, height=96, spp=16, mode=MODE_PATH, max_depth=6, 
         rx = np.array([[1, 0, 0, 0], [0, np.cos(b), -np.sin(b), 0], [0, np.sin(b), np.cos(b), 0], [0, 0, 0, 1]], F32)
         m = (ry @ rx).astype(F32)
     add_light(s, envmap_light(_sky_image(64, 32, 7), 1.5, m, sampling_weight=2.0))
+    # a collimated beam (src/luminaires/collimated.cpp) slanting down onto the floor
+    add_light(s, collimated_light((4.6, 5.0, 0.2), (3.0, 0.0, 2.6), (0, 1, 0), 0.9, (14.0, 12.0, 9.0), sampling_weight=1.25))
     return s
 
 

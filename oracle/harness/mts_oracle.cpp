@@ -368,8 +368,8 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 	for (size_t i = 0; i < s.emitters.size(); ++i) {
 		const sio::Emitter &e = s.emitters[i];
 		if (e.type == 0) continue;
-		static const char *names[6] = { "area", "point", "spot", "directional", "constant", "envmap" };
-		if (e.type > 5) SLog(EError, "unknown emitter type %u", e.type);
+		static const char *names[7] = { "area", "point", "spot", "directional", "constant", "envmap", "collimated" };
+		if (e.type > 6) SLog(EError, "unknown emitter type %u", e.type);
 		Properties lp(names[e.type]);
 		if (e.type == 5) {       /* <luminaire type="envmap"> (envmap.cpp:40-51) */
 			lp.setString("filename", e.envFile);
@@ -378,8 +378,9 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 		} else
 		lp.setSpectrum("intensity", rgb(e.intensity));
 		lp.setFloat("samplingWeight", e.samplingWeight);
-		if (e.type == 1 || e.type == 2)
+		if (e.type == 1 || e.type == 2 || e.type == 6)
 			lp.setTransform("toWorld", Transform(Matrix4x4(const_cast<float *>(e.aux))));
+		if (e.type == 6) lp.setFloat("radius", e.p[0]);
 		if (e.type == 2) { lp.setFloat("beamWidth", e.p[8]); lp.setFloat("cutoffAngle", e.p[9]); }
 		if (e.type == 3) lp.setPoint("direction", Point(e.aux[0], e.aux[1], e.aux[2]));   /* getVector reads the point-typed entry */
 		ref<Luminaire> lum = static_cast<Luminaire *>(create(MTS_CLASS(Luminaire), lp));
