@@ -353,8 +353,10 @@ __device__ inline void fillIntersectionSorted(const DeviceScene &sc, uint32_t tr
 	const uint32_t shape = __float_as_uint(r0.w);
 	const ShapeInfo si = sc.shapes[shape];
 	if (si.isSphere) { fillSphereIntersection(sc, r0, r1, r2, r3, r4, r5, rayO, rayD, t, its); return; }
-	if (INST && si.isCylinder) { fillCylinderIntersection(sc.instances, si, shape, rayO, rayD, t, its); return; }
-	if (INST && si.isInstance) { fillInstanceIntersection(sc, si, shape, nested, u, v, rayO, rayD, t, its); return; }
+	if constexpr (INST) {       // discarded, not merely dead, in the kernels of scenes without such shapes (a plain `if` cost them 112 bytes of stack)
+		if (si.isCylinder) { fillCylinderIntersection(sc.instances, si, shape, rayO, rayD, t, its); return; }
+		if (si.isInstance) { fillInstanceIntersection(sc, si, shape, nested, u, v, rayO, rayD, t, its); return; }
+	}
 	fillMeshIntersection<true>(sc, si, shape, r0, r1, r2, r3, r4, r5, u, v, rayO, rayD, t, its);
 }
 
@@ -819,6 +821,28 @@ __device__ __noinline__ EnvSample envSampleDirection(const MipRef mr, const Text
 	return out;
 }
 
+// CollimatedBeamLuminaire::sample (collimated.cpp:63-75): the point in the beam's frame, the disc test, the projection
+// back. `xf`: luminaireToWorld 4x4, worldToLuminaire 4x4. Out of line and by value, so that scenes without a beam pay
+// nothing for it in the shading kernel.
+struct BeamSample { V3 p, d; bool ok; };
+__device__ __noinline__ BeamSample collimatedSample(const float *xf, float radius, V3 p) {
+	const float *L = xf, *W = xf + 16;
+	BeamSample out; out.ok = false; out.p = out.d = v3(0, 0, 0);
+	float lx = W[0] * p.x + W[1] * p.y + W[2] * p.z + W[3], ly = W[4] * p.x + W[5] * p.y + W[6] * p.z + W[7],
+		lz = W[8] * p.x + W[9] * p.y + W[10] * p.z + W[11];
+	const float lw = W[12] * p.x + W[13] * p.y + W[14] * p.z + W[15];
+	if (lw != 1.0f) { const float rw = 1.0f / lw; lx *= rw; ly *= rw; lz *= rw; }
+	if (sqrtf(lx * lx + ly * ly) > radius || lz < 0) return out;
+	float wx = L[0] * lx + L[1] * ly + L[2] * 0.0f + L[3], wy = L[4] * lx + L[5] * ly + L[6] * 0.0f + L[7],
+		wz = L[8] * lx + L[9] * ly + L[10] * 0.0f + L[11];
+	const float ww = L[12] * lx + L[13] * ly + L[14] * 0.0f + L[15];
+	if (ww != 1.0f) { const float rw = 1.0f / ww; wx *= rw; wy *= rw; wz *= rw; }
+	out.p = v3(wx, wy, wz);
+	out.d = v3(L[0] * 0.0f + L[1] * 0.0f + L[2], L[4] * 0.0f + L[5] * 0.0f + L[6], L[8] * 0.0f + L[9] * 0.0f + L[10]);     // m_direction = luminaireToWorld(Vector(0, 0, 1))
+	out.ok = true;
+	return out;
+}
+
 __device__ inline void sampleLuminaire(const DeviceScene &sc, V3 p, float sx, float sy, bool importance, LumSample &out) {
 	out.pdf = 0; out.emitter = -1; out.mis = true;
 	if (sc.nEmitters == 0) return;
@@ -885,22 +909,9 @@ __device__ inline void sampleLuminaire(const DeviceScene &sc, V3 p, float sx, fl
 		out.d = dir;
 		pdf = 1.0f; out.mis = false;
 	} else if (em.type == MTSGPU_EMITTER_COLLIMATED) {
-		// CollimatedBeamLuminaire::sample (collimated.cpp:63-75)
-		const float *L = sc.emitterXf + (size_t) index * 32, *W = L + 16;
-		float lx = W[0] * p.x + W[1] * p.y + W[2] * p.z + W[3], ly = W[4] * p.x + W[5] * p.y + W[6] * p.z + W[7],
-			lz = W[8] * p.x + W[9] * p.y + W[10] * p.z + W[11];
-		const float lw = W[12] * p.x + W[13] * p.y + W[14] * p.z + W[15];
-		if (lw != 1.0f) { const float rw = 1.0f / lw; lx *= rw; ly *= rw; lz *= rw; }
+		const BeamSample bs = collimatedSample(sc.emitterXf + (size_t) index * 32, em.p[0], p);
 		out.mis = false; out.n = v3(0, 0, 0);
-		if (!(sqrtf(lx * lx + ly * ly) > em.p[0] || lz < 0)) {
-			float wx = L[0] * lx + L[1] * ly + L[2] * 0.0f + L[3], wy = L[4] * lx + L[5] * ly + L[6] * 0.0f + L[7],
-				wz = L[8] * lx + L[9] * ly + L[10] * 0.0f + L[11];
-			const float ww = L[12] * lx + L[13] * ly + L[14] * 0.0f + L[15];
-			if (ww != 1.0f) { const float rw = 1.0f / ww; wx *= rw; wy *= rw; wz *= rw; }
-			out.p = v3(wx, wy, wz);
-			out.d = v3(L[0] * 0.0f + L[1] * 0.0f + L[2], L[4] * 0.0f + L[5] * 0.0f + L[6], L[8] * 0.0f + L[9] * 0.0f + L[10]);     // m_direction = luminaireToWorld(Vector(0, 0, 1))
-			pdf = 1.0f;
-		}
+		if (bs.ok) { out.p = bs.p; out.d = bs.d; pdf = 1.0f; }
 	} else if (em.type == MTSGPU_EMITTER_ENVMAP) {
 		// EnvMapLuminaire::sample (envmap.cpp:170-182)
 		const EnvSample es = envSampleDirection(mipRef(sc), sc.textures[__float_as_uint(em.p[5])], sc.envData, em.p[4], sx, sy);

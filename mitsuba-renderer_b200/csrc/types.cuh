@@ -32,18 +32,19 @@ struct __align__(128) BVH4Node {
 #define BVH_LEAF       0x80000000u
 #define BVH_LEAF_MAX   4
 
+// 36 bytes, 4-byte aligned: the shading kernel reads one per hit and loads just the words it uses; the flags share one word
 struct ShapeInfo {
 	int32_t materialId, emitterId;
 	uint32_t triOffset, vertOffset;
 	uint32_t nTri, nVert;
-	uint32_t hasNormals;
-	uint32_t cdfOffset;       // into DeviceScene::areaCdf (emitter meshes only)
+	uint32_t cdfOffset;       // into DeviceScene::areaCdf (emitter meshes only); spheres: sphere-table index; cylinders / instances: DeviceScene::instances
 	float invSurfaceArea;     // TriMesh::m_invSurfaceArea (trimesh.cpp:281)
-	uint32_t hasTexcoords;
-	uint32_t hasTangents;     // per-vertex dpdu present (TriMesh::computeTangentSpaceBasis ran for this mesh)
-	uint32_t isSphere;        // analytic sphere (src/shapes/sphere.cpp): one primitive, no mesh arrays
-	uint32_t isCylinder;      // analytic cylinder (src/shapes/cylinder.cpp): one primitive; cdfOffset = index into DeviceScene::instances
-	uint32_t isInstance;      // instance of a shape group (src/shapes/instance.cpp): one primitive; cdfOffset = index into DeviceScene::instances
+	uint32_t hasNormals : 1;
+	uint32_t hasTexcoords : 1;
+	uint32_t hasTangents : 1; // per-vertex dpdu / dpdv present (TriMesh::computeTangentSpaceBasis ran for this mesh)
+	uint32_t isSphere : 1;    // analytic sphere (src/shapes/sphere.cpp): one primitive, no mesh arrays
+	uint32_t isCylinder : 1;  // analytic cylinder (src/shapes/cylinder.cpp): one primitive
+	uint32_t isInstance : 1;  // instance of a shape group (src/shapes/instance.cpp): one primitive
 };
 
 // Instance of a shape group: both matrices of its Transform, and which group (DeviceScene::groups) it shows
