@@ -471,6 +471,10 @@ MTSGPU_API int mtsgpu_get_triaccel(mtsgpu_ctx *ctx, void *outRecords, size_t max
 typedef struct mtsgpu_accel_info {
 	uint64_t triangles, nodes, nodeBytes, triBytes;
 	double buildMs;
+	uint32_t depth;        /* levels of the 4-wide tree; a traversal stack holds at most 3 entries per level */
+	uint32_t builder;      /* 0 Morton radix tree, 1 PLOC, 2 binned SAH (the default) */
+	uint32_t buildLevels;  /* levels of the binary SAH build (or PLOC rounds) */
+	uint32_t reserved;
 } mtsgpu_accel_info;
 MTSGPU_API int mtsgpu_accel_info_get(mtsgpu_ctx *ctx, mtsgpu_accel_info *info);
 

@@ -74,7 +74,8 @@ class Stats(C.Structure):
 
 class AccelInfo(C.Structure):
     _fields_ = [("triangles", C.c_uint64), ("nodes", C.c_uint64), ("nodeBytes", C.c_uint64),
-                ("triBytes", C.c_uint64), ("buildMs", C.c_double)]
+                ("triBytes", C.c_uint64), ("buildMs", C.c_double), ("depth", C.c_uint32), ("builder", C.c_uint32),
+                ("buildLevels", C.c_uint32), ("reserved", C.c_uint32)]
 
 
 class TraceCounters(C.Structure):

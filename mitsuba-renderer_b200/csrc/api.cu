@@ -410,6 +410,7 @@ int mtsgpu_trace_device(mtsgpu_ctx *ctx, const float *d_rays, size_t n, int mode
 	CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
 	CUDA_TRY(ctx, cudaGetLastError());
 	if (elapsedMs) { float ms = 0; cudaEventElapsedTime(&ms, ctx->ev[4], ctx->ev[5]); *elapsedMs = ms; }
+	{ const int frc = checkTraceFlags(ctx); if (frc) return frc; }
 	if (cnt) {
 		uint64_t h[2];
 		CUDA_TRY(ctx, cudaMemcpy(h, cnt, 16, cudaMemcpyDeviceToHost));
@@ -453,7 +454,10 @@ int mtsgpu_trace(mtsgpu_ctx *ctx, const float *rays, size_t n, int mode, void *o
 		CUDA_TRY(ctx, cudaEventRecord(ctx->pipeEv[2 * k], ctx->copyIn));
 		CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipeEv[2 * k], 0));
 		int rc = launchTrace(ctx, reinterpret_cast<const float4 *>(dIn), m, mode, dOut, nullptr);
-		if (rc) return rc;
+		if (rc) {      // no copy may still be in flight into the caller's buffers when this call returns
+			cudaStreamSynchronize(ctx->copyIn); cudaStreamSynchronize(ctx->stream); cudaStreamSynchronize(ctx->copyOut);
+			return rc;
+		}
 		CUDA_TRY(ctx, cudaEventRecord(ctx->pipeEv[2 * k + 1], ctx->stream));
 		CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->copyOut, ctx->pipeEv[2 * k + 1], 0));
 		CUDA_TRY(ctx, cudaMemcpyAsync(static_cast<char *>(out) + off * outStride, dOut, m * outStride, cudaMemcpyDeviceToHost, ctx->copyOut));
@@ -461,7 +465,7 @@ int mtsgpu_trace(mtsgpu_ctx *ctx, const float *rays, size_t n, int mode, void *o
 	CUDA_TRY(ctx, cudaStreamSynchronize(ctx->copyOut));
 	CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
 	CUDA_TRY(ctx, cudaGetLastError());
-	return MTSGPU_OK;
+	return checkTraceFlags(ctx);
 }
 
 int mtsgpu_bsdf_eval(mtsgpu_ctx *ctx, const float *queries, size_t n, float *out) { ENTER(ctx); return hookBsdfEval(ctx, queries, n, out); }

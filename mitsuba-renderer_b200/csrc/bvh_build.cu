@@ -402,9 +402,55 @@ __global__ void k_reorder(const uint32_t *sortedIdx, const TriAccelRec *orig, ui
 	if (i < n) sorted[i] = orig[sortedIdx[i]];
 }
 
+// 128-byte fp32 node -> the 64-byte node of the traversal kernels (types.cuh: BVH4QNode). Per axis: origin = just below the
+// smallest child plane, quantum 2^e with (extent / 2^e) <= 254.5, child planes floor / ceil'ed outwards in fp64 with a
+// hundredth of a quantum of slack for the decode's rounding (m * S + C in trace.cuh: 2^-17 of a quantum range).
+// Empty slots get an inverted box; the traversal also checks the child word.
+__global__ void k_quantize_nodes(const BVH4Node *in, uint32_t n, BVH4QNode *out) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const BVH4Node nd = in[i];
+	const float lo[3][4] = { { nd.lox.x, nd.lox.y, nd.lox.z, nd.lox.w }, { nd.loy.x, nd.loy.y, nd.loy.z, nd.loy.w }, { nd.loz.x, nd.loz.y, nd.loz.z, nd.loz.w } };
+	const float hi[3][4] = { { nd.hix.x, nd.hix.y, nd.hix.z, nd.hix.w }, { nd.hiy.x, nd.hiy.y, nd.hiy.z, nd.hiy.w }, { nd.hiz.x, nd.hiz.y, nd.hiz.z, nd.hiz.w } };
+	const uint32_t cw[4] = { nd.child.x, nd.child.y, nd.child.z, nd.child.w };
+	float origin[3], scale[3]; uint32_t qlo[3] = { 0, 0, 0 }, qhi[3] = { 0, 0, 0 };
+	for (int a = 0; a < 3; ++a) {
+		float mn = INFINITY, mx = -INFINITY;
+		for (int c = 0; c < 4; ++c)
+			if (cw[c] != BVH_EMPTY) { mn = fminf(mn, lo[a][c]); mx = fmaxf(mx, hi[a][c]); }
+		if (!(mn <= mx)) { mn = 0.0f; mx = 0.0f; }
+		// the grid's origin sits a little below the smallest plane so that plane 0 keeps its outward slack too
+		int e = -100;
+		const double ext0 = (double) mx - (double) mn;
+		if (ext0 > 0.0) { int k; frexp(ext0 / 254.0, &k); e = max(-100, min(100, k)); }
+		const float org = __double2float_rd((double) mn - 0.04 * ldexp(1.0, e));
+		const double ext = (double) mx - (double) org;
+		if (ext > 0.0) { int k; frexp(ext / 254.5, &k); e = max(-100, min(100, k)); }     // 2^k >= ext / 254.5
+		const double quantum = ldexp(1.0, e);
+		origin[a] = org; scale[a] = (float) ldexp(1.0, e + 15);
+		for (int c = 0; c < 4; ++c) {
+			uint32_t l = 255u, h = 0u;                     // empty: inverted
+			if (cw[c] != BVH_EMPTY) {
+				const double fl = floor(((double) lo[a][c] - (double) org) / quantum - 0.01), fh = ceil(((double) hi[a][c] - (double) org) / quantum + 0.01);
+				l = (uint32_t) fmin(fmax(fl, 0.0), 255.0); h = (uint32_t) fmin(fmax(fh, 0.0), 255.0);
+			}
+			qlo[a] |= l << (8 * c); qhi[a] |= h << (8 * c);
+		}
+	}
+	BVH4QNode q;
+	q.ox = origin[0]; q.oy = origin[1]; q.oz = origin[2]; q.scaleX = scale[0]; q.scaleY = scale[1]; q.scaleZ = scale[2];
+	for (int c = 0; c < 4; ++c) q.child[c] = cw[c];
+	q.qlox = qlo[0]; q.qloy = qlo[1]; q.qloz = qlo[2]; q.qhix = qhi[0]; q.qhiy = qhi[1]; q.qhiz = qhi[2];
+	out[i] = q;
+}
+
 inline unsigned blocksFor(size_t n, unsigned bs) { return (unsigned) ((n + bs - 1) / bs); }
 
 } // namespace
+
+// sah_build.cu
+int buildSahTree(mtsgpu_ctx *ctx, const uint32_t *initialOrder, const float4 *triLo, const float4 *triHi, int n, float pad,
+	int2 *children, int *count, float4 *boxLo, float4 *boxHi, uint32_t *order, int *levelsOut);
 
 // Host-side TriMesh::computeTangentSpaceBasis (src/librender/trimesh.cpp:547-662): per-vertex dpdu / dpdv from the
 // texture coordinates, accumulated over the triangles in order and averaged; same float operations in the same order.
@@ -917,13 +963,14 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		if (vb.Current() != dVals.as<uint32_t>()) std::swap(dVals.p, dValsAlt.p);
 	}
 	const uint64_t *keys = dKeys.as<uint64_t>();
-	const uint32_t *sortedIdx = dVals.as<uint32_t>();
+	const uint32_t *sortedIdx = dVals.as<uint32_t>();      // the SAH build replaces it by its own leaf order
 
 	// ---- binary tree: the radix tree + refit (default), or PLOC (MTSGPU_BUILDER=ploc). Measured on B200: PLOC with
 	//      r = 16 buys 2-4 % of traversal time on the 10M-triangle scene and nothing on the 1M-triangle grid (both are
 	//      regular meshes, which Morton order already clusters well) for 10x the build time, so it stays an option.
 	const char *builderEnv = getenv("MTSGPU_BUILDER");
 	const bool usePloc = builderEnv && strcmp(builderEnv, "ploc") == 0 && n > 1;
+	const bool useSah = !(builderEnv && (strcmp(builderEnv, "ploc") == 0 || strcmp(builderEnv, "lbvh") == 0)) && n > 1;     // the default
 	int plocRadius = getenv("MTSGPU_PLOC_RADIUS") ? atoi(getenv("MTSGPU_PLOC_RADIUS")) : 16;
 	plocRadius = std::max(1, std::min(plocRadius, PLOC_MAX_RADIUS));
 	int rootNode = 0;
@@ -938,8 +985,16 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	CUDA_TRY(ctx, dBoxLo.alloc(nBin * sizeof(float4)));
 	CUDA_TRY(ctx, dBoxHi.alloc(nBin * sizeof(float4)));
 	const float pad = 4e-6f * std::max(maxAbs, 1e-3f);
-	int plocRounds = 0;
-	if (usePloc) {
+	int plocRounds = 0, sahLevels = 0;
+	DevBuf dSahOrder;
+	if (useSah) {
+		// binned-SAH top-down build (sah_build.cu); the Morton order is only its initial primitive order
+		CUDA_TRY(ctx, dSahOrder.alloc(nTri * sizeof(uint32_t)));
+		const int rc = buildSahTree(ctx, sortedIdx, dTriLo.as<float4>(), dTriHi.as<float4>(), n, pad, dChildren.as<int2>(), dCount.as<int>(),
+			dBoxLo.as<float4>(), dBoxHi.as<float4>(), dSahOrder.as<uint32_t>(), &sahLevels);
+		if (rc) return rc;
+		sortedIdx = dSahOrder.as<uint32_t>();
+	} else if (usePloc) {
 		DevBuf dClusterA, dClusterB, dNN, dPFlags, dPPos, dScanTemp;
 		CUDA_TRY(ctx, dClusterA.alloc(nTri * sizeof(int))); CUDA_TRY(ctx, dClusterB.alloc(nTri * sizeof(int)));
 		CUDA_TRY(ctx, dNN.alloc(nTri * sizeof(int)));
@@ -984,12 +1039,12 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		k_counts_from_range<<<blocksFor(nBin, 256), 256, 0, st>>>(dRange.as<int2>(), n, dCount.as<int>());
 		CUDA_TRY(ctx, cudaGetLastError());
 	}
-	(void) plocRounds;
+	(void) plocRounds; (void) sahLevels;
 
 	// ---- collapse to 4-wide nodes ----
 	const size_t maxNodes = nTri + 1;
 	CUDA_TRY(ctx, dNodesTmp.alloc(maxNodes * sizeof(BVH4Node)));
-	uint32_t nodeCount = 1;
+	uint32_t nodeCount = 1; int wideDepth = 1;
 	if (n == 1) {
 		float4 lo, hi;
 		CUDA_TRY(ctx, cudaMemcpyAsync(&lo, dBoxLo.p, sizeof(float4), cudaMemcpyDeviceToHost, st));
@@ -1010,9 +1065,10 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		uint4 rootItem = make_uint4((uint32_t) rootNode, 0u, 0u, 0u);
 		CUDA_TRY(ctx, cudaMemcpyAsync(dQ0.p, &rootItem, sizeof(rootItem), cudaMemcpyHostToDevice, st));
 		uint32_t counts[2] = { 0u, 1u };   // [queue-out count, node count]
-		uint32_t nIn = 1;
+		uint32_t nIn = 1; wideDepth = 0;
 		uint4 *qIn = dQ0.as<uint4>(), *qOut = dQ1.as<uint4>();
 		while (nIn > 0) {
+			wideDepth++;
 			counts[0] = 0;
 			CUDA_TRY(ctx, cudaMemcpyAsync(dCounts.p, counts, sizeof(counts), cudaMemcpyHostToDevice, st));
 			k_collapse<<<blocksFor(nIn, 128), 128, 0, st>>>(qIn, nIn, qOut, dCounts.as<uint32_t>(), dCounts.as<uint32_t>() + 1,
@@ -1027,8 +1083,11 @@ int buildAccel(mtsgpu_ctx *ctx) {
 		}
 		nodeCount = counts[1];
 	}
-	CUDA_TRY(ctx, ctx->dNodes.alloc((size_t) nodeCount * sizeof(BVH4Node)));
-	CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dNodes.p, dNodesTmp.p, (size_t) nodeCount * sizeof(BVH4Node), cudaMemcpyDeviceToDevice, st));
+	CUDA_TRY(ctx, ctx->dNodes.alloc((size_t) nodeCount * sizeof(BVH4QNode)));
+	k_quantize_nodes<<<blocksFor(nodeCount, 128), 128, 0, st>>>(dNodesTmp.as<BVH4Node>(), nodeCount, ctx->dNodes.as<BVH4QNode>());
+	CUDA_TRY(ctx, cudaGetLastError());
+	CUDA_TRY(ctx, ctx->dTraceFlags.alloc(16));
+	CUDA_TRY(ctx, cudaMemsetAsync(ctx->dTraceFlags.p, 0, 16, st));
 	CUDA_TRY(ctx, ctx->dShadeTris.alloc(nTri * 6 * sizeof(float4)));
 	CUDA_TRY(ctx, ctx->dSortedOf.alloc(nTri * sizeof(uint32_t)));
 	DevBuf dSphereXf;
@@ -1066,7 +1125,11 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	sc.rootIsLeaf = 0;
 	ctx->accel.triangles = nTri;
 	ctx->accel.nodes = nodeCount;
-	ctx->accel.nodeBytes = (uint64_t) nodeCount * sizeof(BVH4Node);
+	ctx->accel.nodeBytes = (uint64_t) nodeCount * sizeof(BVH4QNode);
+	ctx->accel.depth = (uint32_t) wideDepth;
+	ctx->accel.builder = useSah ? 2u : (usePloc ? 1u : 0u);
+	ctx->accel.buildLevels = (uint32_t) (useSah ? sahLevels : plocRounds);
+	sc.traceFlags = ctx->dTraceFlags.as<uint32_t>();
 	ctx->accel.triBytes = (uint64_t) nTri * sizeof(TriAccelRec);
 	ctx->accel.buildMs = ms;
 	ctx->built = true;

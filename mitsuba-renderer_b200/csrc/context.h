@@ -80,7 +80,7 @@ struct mtsgpu_ctx {
 	mtsgpu_accel_info accel = {};
 
 	// trace staging + counters
-	DevBuf dRays, dHits, dCounters, dRayCounters;
+	DevBuf dRays, dHits, dCounters, dRayCounters, dTraceFlags;
 	uint32_t rayCounterNext = 0;
 	int smCount = 0;
 	bool countersEnabled = false;
@@ -108,6 +108,7 @@ int rebuildLuminaireCdf(mtsgpu_ctx *ctx, bool importance);
 unsigned tracePersistentBlocks(mtsgpu_ctx *ctx, size_t n);
 int traceRayCounter(mtsgpu_ctx *ctx, uint32_t **out);
 int launchTrace(mtsgpu_ctx *ctx, const float4 *dRays, size_t n, int mode, void *dOut, uint64_t *dCounters);
+int checkTraceFlags(mtsgpu_ctx *ctx);
 // integrate.cu
 int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, volatile const int *cancel,
 	float *dOutFilm, mtsgpu_stats *stats);

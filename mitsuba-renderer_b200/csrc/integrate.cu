@@ -757,7 +757,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 	{ float ms = 0; cudaEventElapsedTime(&ms, evBegin, evEnd); S.totalMs = ms; }
 	S.shadeMs = S.totalMs - S.traceClosestMs - S.traceAnyMs;
 	if (stats) *stats = S;
-	return MTSGPU_OK;
+	return checkTraceFlags(ctx);
 }
 
 // ================================================================================================
@@ -893,7 +893,7 @@ static int download(mtsgpu_ctx *ctx, void *dst, const DevBuf &buf, size_t bytes)
 	if (bytes) CUDA_TRY(ctx, cudaMemcpyAsync(dst, buf.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
 	CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
 	CUDA_TRY(ctx, cudaGetLastError());
-	return MTSGPU_OK;
+	return checkTraceFlags(ctx);
 }
 
 namespace {

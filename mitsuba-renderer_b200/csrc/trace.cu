@@ -83,6 +83,24 @@ int traceRayCounter(mtsgpu_ctx *ctx, uint32_t **out) {
 	return MTSGPU_OK;
 }
 
+// After the stream has been synchronised: did any traversal kernel of this context (or of its shape groups) run out of
+// stack? The reference's kd-tree cannot (its builder bounds the depth at MTS_KD_MAXDEPTH = 48 entries, gkdtree.h:34); a
+// BVH has no such bound, so an overflow is reported instead of silently dropping a subtree.
+int checkTraceFlags(mtsgpu_ctx *ctx) {
+	uint32_t any = 0;
+	for (size_t i = 0; i <= ctx->groups.size(); ++i) {
+		mtsgpu_ctx *c = i == 0 ? ctx : ctx->groups[i - 1];
+		if (!c->dTraceFlags.p) continue;
+		uint32_t f = 0;
+		CUDA_TRY(ctx, cudaMemcpy(&f, c->dTraceFlags.p, sizeof(f), cudaMemcpyDeviceToHost));
+		if (f) CUDA_TRY(ctx, cudaMemset(c->dTraceFlags.p, 0, sizeof(f)));
+		any |= f;
+	}
+	REQUIRE(ctx, !(any & 1u), MTSGPU_ERR_LIMIT, "traversal stack overflow: the acceleration structure is %u levels deep and a ray needed more than %d stack entries; "
+		"results of this call are incomplete", ctx->accel.depth, TRACE_SMEM_STACK + TRACE_LOCAL_STACK);
+	return MTSGPU_OK;
+}
+
 int launchTrace(mtsgpu_ctx *ctx, const float4 *dRays, size_t n, int mode, void *dOut, uint64_t *dCounters) {
 	REQUIRE(ctx, ctx->built, MTSGPU_ERR_ARG, "trace: call mtsgpu_build_accel first");
 	REQUIRE(ctx, n < (1ull << 31), MTSGPU_ERR_LIMIT, "trace: at most 2^31-1 rays per call");

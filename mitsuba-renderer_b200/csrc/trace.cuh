@@ -108,6 +108,43 @@ __device__ __forceinline__ bool sphereTest(const float4 &q0, const float4 &q1, c
 	return true;
 }
 
+// 256-bit read-only load (LDG.E.256 on sm_100): one L1 wavefront per lane where two 128-bit loads cost two.
+// Written as v4.u64: ptxas 12.9 crashes on the v8.u32 form inside the persistent kernels.
+__device__ __forceinline__ void ldg256(const void *p, uint32_t (&v)[8]) {
+	unsigned long long a, b, c, d;
+	asm("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];" : "=l"(a), "=l"(b), "=l"(c), "=l"(d) : "l"(p));
+	v[0] = (uint32_t) a; v[1] = (uint32_t) (a >> 32); v[2] = (uint32_t) b; v[3] = (uint32_t) (b >> 32);
+	v[4] = (uint32_t) c; v[5] = (uint32_t) (c >> 32); v[6] = (uint32_t) d; v[7] = (uint32_t) (d >> 32);
+}
+
+// Slab test of one ray against the four children of a quantised node (types.cuh: BVH4QNode): two 256-bit loads, then per
+// plane one PRMT (byte -> the float 1 + q / 2^15) and one FFMA: t = m * S + C with S = scale / d and
+// C = (origin - o) / d - S. The near and far words of each axis are picked by the ray's direction signs, so a child
+// costs 6 PRMT + 6 FFMA + 4 min / max. tn[i] = entry distance, +inf when child i is not entered (or empty).
+__device__ __forceinline__ void nodeTest(const float4 *nodes, uint32_t node, float idx, float idy, float idz, float oix, float oiy, float oiz,
+		float mint, float maxt, float (&tn)[4], uint32_t (&cw)[4]) {
+	const char *np = reinterpret_cast<const char *>(nodes) + (size_t) node * 64;
+	uint32_t a[8], b[8];
+	ldg256(np, a); ldg256(np + 32, b);
+	const float Sx = idx * __uint_as_float(a[3]), Sy = idy * __uint_as_float(b[6]), Sz = idz * __uint_as_float(b[7]);
+	const float Cx = fmaf(__uint_as_float(a[0]), idx, -oix) - Sx, Cy = fmaf(__uint_as_float(a[1]), idy, -oiy) - Sy, Cz = fmaf(__uint_as_float(a[2]), idz, -oiz) - Sz;
+	const bool nx = idx < 0.0f, ny = idy < 0.0f, nz = idz < 0.0f;
+	const uint32_t nearX = nx ? b[3] : b[0], farX = nx ? b[0] : b[3];
+	const uint32_t nearY = ny ? b[4] : b[1], farY = ny ? b[1] : b[4];
+	const uint32_t nearZ = nz ? b[5] : b[2], farZ = nz ? b[2] : b[5];
+#pragma unroll
+	for (int i = 0; i < 4; ++i) {
+		const uint32_t sel = 0x7604u | ((uint32_t) i << 4);          // {0x00, byte i, 0x80, 0x3F}
+		const float t0x = fmaf(__uint_as_float(__byte_perm(nearX, 0x3F800000u, sel)), Sx, Cx), t1x = fmaf(__uint_as_float(__byte_perm(farX, 0x3F800000u, sel)), Sx, Cx);
+		const float t0y = fmaf(__uint_as_float(__byte_perm(nearY, 0x3F800000u, sel)), Sy, Cy), t1y = fmaf(__uint_as_float(__byte_perm(farY, 0x3F800000u, sel)), Sy, Cy);
+		const float t0z = fmaf(__uint_as_float(__byte_perm(nearZ, 0x3F800000u, sel)), Sz, Cz), t1z = fmaf(__uint_as_float(__byte_perm(farZ, 0x3F800000u, sel)), Sz, Cz);
+		const float tnear = fmaxf(fmaxf(fmaxf(t0x, t0y), t0z), mint);
+		const float tfar = fminf(fminf(fminf(t1x, t1y), t1z), maxt);
+		cw[i] = a[4 + i];
+		tn[i] = (tnear <= tfar && a[4 + i] != BVH_EMPTY) ? tnear : INFINITY;
+	}
+}
+
 // ---- instances of shape groups (src/shapes/instance.cpp) ---------------------------------------------------------
 // A group's acceleration structure, walked with a stack in local memory only (the caller's shared stack is live).
 // Same node layout, same interval rules and the same TriAccel test as traverse() below; groups hold triangles only.
@@ -124,25 +161,19 @@ __device__ __noinline__ bool traverseGroup(const DeviceScene &gs, const RayIn &r
 	uint32_t cur = 0;                 // root node
 	while (true) {
 		if (!(cur & BVH_LEAF)) {
-			const float4 *np = gs.nodes + (size_t) cur * 8;
-			const float4 lo[3] = { __ldg(np + 0), __ldg(np + 1), __ldg(np + 2) }, hi[3] = { __ldg(np + 3), __ldg(np + 4), __ldg(np + 5) };
-			const uint4 child = __ldg(reinterpret_cast<const uint4 *>(np + 6));
-			const uint32_t cw[4] = { child.x, child.y, child.z, child.w };
-			const float lx[4] = { lo[0].x, lo[0].y, lo[0].z, lo[0].w }, ly[4] = { lo[1].x, lo[1].y, lo[1].z, lo[1].w }, lz[4] = { lo[2].x, lo[2].y, lo[2].z, lo[2].w };
-			const float hx[4] = { hi[0].x, hi[0].y, hi[0].z, hi[0].w }, hy[4] = { hi[1].x, hi[1].y, hi[1].z, hi[1].w }, hz[4] = { hi[2].x, hi[2].y, hi[2].z, hi[2].w };
+			float tn[4]; uint32_t cw[4];
+			nodeTest(gs.nodes, cur, idx, idy, idz, oix, oiy, oiz, mint, maxt, tn, cw);
 			uint32_t next = BVH_EMPTY; float nextT = INFINITY;
 #pragma unroll
 			for (int i = 0; i < 4; ++i) {
-				const float t0x = fmaf(lx[i], idx, -oix), t1x = fmaf(hx[i], idx, -oix);
-				const float t0y = fmaf(ly[i], idy, -oiy), t1y = fmaf(hy[i], idy, -oiy);
-				const float t0z = fmaf(lz[i], idz, -oiz), t1z = fmaf(hz[i], idz, -oiz);
-				const float tnear = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), mint));
-				const float tfar = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), maxt));
-				if (!(tnear <= tfar)) continue;
-				if (tnear < nextT) {                     // keep the nearest child, push the one it displaces
-					if (next != BVH_EMPTY && sp < GROUP_STACK) stack[sp++] = make_uint2(next, __float_as_uint(nextT));
-					next = cw[i]; nextT = tnear;
-				} else if (sp < GROUP_STACK) stack[sp++] = make_uint2(cw[i], __float_as_uint(tnear));
+				if (tn[i] == INFINITY) continue;
+				uint2 pushed;
+				if (tn[i] < nextT) {                     // keep the nearest child, push the one it displaces
+					if (next == BVH_EMPTY) { next = cw[i]; nextT = tn[i]; continue; }
+					pushed = make_uint2(next, __float_as_uint(nextT));
+					next = cw[i]; nextT = tn[i];
+				} else pushed = make_uint2(cw[i], __float_as_uint(tn[i]));
+				if (sp < GROUP_STACK) stack[sp++] = pushed; else atomicOr(gs.traceFlags, 1u);
 			}
 			if (next != BVH_EMPTY) { cur = next; continue; }
 		} else {
@@ -309,22 +340,8 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 	while (true) {
 		if (!(cur & BVH_LEAF)) {
 			if (COUNT) nodeVisits++;
-			const float4 *np = sc.nodes + (size_t) cur * 8;
-			const float4 lox = __ldg(np + 0), loy = __ldg(np + 1), loz = __ldg(np + 2);
-			const float4 hix = __ldg(np + 3), hiy = __ldg(np + 4), hiz = __ldg(np + 5);
-			const uint4 child = __ldg(reinterpret_cast<const uint4 *>(np + 6));
-			float tn[4]; uint32_t cw[4] = { child.x, child.y, child.z, child.w };
-			const float lx[4] = { lox.x, lox.y, lox.z, lox.w }, ly[4] = { loy.x, loy.y, loy.z, loy.w }, lz[4] = { loz.x, loz.y, loz.z, loz.w };
-			const float hx[4] = { hix.x, hix.y, hix.z, hix.w }, hy[4] = { hiy.x, hiy.y, hiy.z, hiy.w }, hz[4] = { hiz.x, hiz.y, hiz.z, hiz.w };
-#pragma unroll
-			for (int i = 0; i < 4; ++i) {
-				const float t0x = fmaf(lx[i], idx, -oix), t1x = fmaf(hx[i], idx, -oix);
-				const float t0y = fmaf(ly[i], idy, -oiy), t1y = fmaf(hy[i], idy, -oiy);
-				const float t0z = fmaf(lz[i], idz, -oiz), t1z = fmaf(hz[i], idz, -oiz);
-				const float tnear = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), mint));
-				const float tfar = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), maxt));
-				tn[i] = (tnear <= tfar) ? tnear : INFINITY;      // empty slots have lo = hi = +inf: never entered
-			}
+			float tn[4]; uint32_t cw[4];
+			nodeTest(sc.nodes, cur, idx, idy, idz, oix, oiy, oiz, mint, maxt, tn, cw);
 			{
 				// nearest hit first; the others in any order (popped entries are culled by their entry distance)
 #define CSWAP(a, b) if (tn[b] < tn[a]) { float tt = tn[a]; tn[a] = tn[b]; tn[b] = tt; uint32_t cc = cw[a]; cw[a] = cw[b]; cw[b] = cc; }
@@ -341,7 +358,9 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 					for (int i = 1; i <= 3; ++i) {
 						if (tn[i] != INFINITY) {
 							const uint2 e = make_uint2(cw[i], __float_as_uint(tn[i]));
-							if (sp < TRACE_SMEM_STACK) stackStore(sbase, sp, e); else lstack[min(sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)] = e;
+							if (sp < TRACE_SMEM_STACK) stackStore(sbase, sp, e);
+							else if (sp < TRACE_SMEM_STACK + TRACE_LOCAL_STACK) lstack[sp - TRACE_SMEM_STACK] = e;
+							else { atomicOr(sc.traceFlags, 1u); continue; }       // stack full: reported by the host call (MTSGPU_ERR_LIMIT)
 							sp++;
 						}
 					}
@@ -371,7 +390,7 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 		while (true) {
 			if (sp == 0) return found;
 			--sp;
-			const uint2 e = (sp < TRACE_SMEM_STACK) ? stackLoad(sbase, sp) : lstack[min(sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)];
+			const uint2 e = (sp < TRACE_SMEM_STACK) ? stackLoad(sbase, sp) : lstack[sp - TRACE_SMEM_STACK];
 			if (!SHADOW && __uint_as_float(e.y) > maxt) continue;
 			cur = e.x;
 			break;
@@ -423,10 +442,12 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 	LaneState s;
 	s.active = false; s.sp = 0; s.cur = BVH_EMPTY; s.leaf = BVH_EMPTY; s.found = false;
 
-#define STACK_PUSH(e) do { if (s.sp < TRACE_SMEM_STACK) stackStore(sbase, s.sp, (e)); else lstack[min(s.sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)] = (e); s.sp++; } while (0)
+#define STACK_PUSH(e) do { if (s.sp < TRACE_SMEM_STACK) { stackStore(sbase, s.sp, (e)); s.sp++; } \
+		else if (s.sp < TRACE_SMEM_STACK + TRACE_LOCAL_STACK) { lstack[s.sp - TRACE_SMEM_STACK] = (e); s.sp++; } \
+		else atomicOr(sc.traceFlags, 1u); } while (0)          /* stack full: reported by the host call (MTSGPU_ERR_LIMIT) */
 	// pop the next entry that can still matter; BVH_EMPTY when the stack is empty
 #define STACK_POP(dst) do { (dst) = BVH_EMPTY; while (s.sp > 0) { --s.sp; \
-		const uint2 e_ = (s.sp < TRACE_SMEM_STACK) ? stackLoad(sbase, s.sp) : lstack[min(s.sp - TRACE_SMEM_STACK, TRACE_LOCAL_STACK - 1)]; \
+		const uint2 e_ = (s.sp < TRACE_SMEM_STACK) ? stackLoad(sbase, s.sp) : lstack[s.sp - TRACE_SMEM_STACK]; \
 		if (!SHADOW && __uint_as_float(e_.y) > s.maxt) continue; (dst) = e_.x; break; } } while (0)
 
 	while (true) {
@@ -480,22 +501,8 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 				const bool inner = s.active && !(s.cur & BVH_LEAF) && (speculate || s.leaf == BVH_EMPTY);      // BVH_EMPTY has the leaf bit set
 				if (inner) {
 					if (COUNT) nodeVisits++;
-					const float4 *np = sc.nodes + (size_t) s.cur * 8;
-					const float4 lox = __ldg(np + 0), loy = __ldg(np + 1), loz = __ldg(np + 2);
-					const float4 hix = __ldg(np + 3), hiy = __ldg(np + 4), hiz = __ldg(np + 5);
-					const uint4 child = __ldg(reinterpret_cast<const uint4 *>(np + 6));
-					float tn[4]; uint32_t cw[4] = { child.x, child.y, child.z, child.w };
-					const float lx[4] = { lox.x, lox.y, lox.z, lox.w }, ly[4] = { loy.x, loy.y, loy.z, loy.w }, lz[4] = { loz.x, loz.y, loz.z, loz.w };
-					const float hx[4] = { hix.x, hix.y, hix.z, hix.w }, hy[4] = { hiy.x, hiy.y, hiy.z, hiy.w }, hz[4] = { hiz.x, hiz.y, hiz.z, hiz.w };
-#pragma unroll
-					for (int i = 0; i < 4; ++i) {
-						const float t0x = fmaf(lx[i], s.idx, -s.oix), t1x = fmaf(hx[i], s.idx, -s.oix);
-						const float t0y = fmaf(ly[i], s.idy, -s.oiy), t1y = fmaf(hy[i], s.idy, -s.oiy);
-						const float t0z = fmaf(lz[i], s.idz, -s.oiz), t1z = fmaf(hz[i], s.idz, -s.oiz);
-						const float tnear = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), s.mint));
-						const float tfar = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), s.maxt));
-						tn[i] = (tnear <= tfar) ? tnear : INFINITY;          // empty slots have lo = hi = +inf: never entered
-					}
+					float tn[4]; uint32_t cw[4];
+					nodeTest(sc.nodes, s.cur, s.idx, s.idy, s.idz, s.oix, s.oiy, s.oiz, s.mint, s.maxt, tn, cw);
 					{
 						// bring the nearest hit to slot 0; the order of the others is immaterial (measured: 28.3 vs
 						// 28.5 node visits per ray with a full sort) because popped entries are culled by distance

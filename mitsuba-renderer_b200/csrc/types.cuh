@@ -32,6 +32,21 @@ struct __align__(128) BVH4Node {
 #define BVH_LEAF       0x80000000u
 #define BVH_LEAF_MAX   4
 
+// ---- the node the traversal kernels read: the same four children in 64 bytes = two 256-bit loads ---------------
+// ncu on the 128-byte node (profiles/r02_base_c4_trace_*): the L1 data pipe ran at 75 % of its wavefront rate — a
+// divergent 128-bit load costs one wavefront per lane, eight of them per node visit — while DRAM sat at 11 %.
+// Child boxes are quantised to 8 bits per plane on a per-node grid (origin + q * 2^e per axis), rounded OUTWARDS from
+// the padded fp32 boxes, so the slab test only ever accepts more than the fp32 test would.
+// Decoding costs one PRMT and one FFMA per plane: the byte goes into bits 8..15 of the mantissa of 1.0f, i.e. the
+// float 1 + q / 2^15, and `scale` holds 2^(e + 15), so plane = origin + (m - 1) * scale.
+struct __align__(64) BVH4QNode {
+	float ox, oy, oz, scaleX;      // words 0-3
+	uint32_t child[4];             // words 4-7
+	uint32_t qlox, qloy, qloz;     // words 8-10: byte i = child i
+	uint32_t qhix, qhiy, qhiz;     // words 11-13
+	float scaleY, scaleZ;          // words 14-15
+};
+
 // 36 bytes, 4-byte aligned: the shading kernel reads one per hit and loads just the words it uses; the flags share one word
 struct ShapeInfo {
 	int32_t materialId, emitterId;
@@ -73,7 +88,7 @@ struct FilmDev {
 
 struct DeviceScene {
 	const float4 *triAccel;     // sorted leaf order, 3 x float4 per triangle
-	const float4 *nodes;        // BVH4Node as 8 x float4
+	const float4 *nodes;        // BVH4QNode as 4 x float4 (two 256-bit loads)
 	const uint4 *triIdx;        // kd primitive order: {v0, v1, v2 (global vertex ids), shape}
 	const float4 *positions;    // global vertex arrays, xyz + pad
 	const float4 *normals;
@@ -89,6 +104,7 @@ struct DeviceScene {
 	const InstanceDev *instances;            // instances of shape groups (empty unless hasInstances)
 	const struct DeviceScene *groups;        // the groups' own scenes: acceleration structure and shading records in object space
 	uint32_t hasInstances, padInst;
+	uint32_t *traceFlags;       // bit 0: a traversal stack overflowed (the call that sees it fails with MTSGPU_ERR_LIMIT)
 	const float *emitterXf;     // per emitter: luminaireToWorld 4x4, worldToLuminaire 4x4 (collimated beams)
 	const float *envData;       // environment map: worldToLuminaire 3x3, luminaireToWorld 3x3, density resolution, CDF, pdf (sampling.cuh)
 	const struct CameraDev *camera;   // the render's camera: ray differentials of a camera-ray hit are rebuilt from it
