@@ -1129,7 +1129,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	ctx->accel.depth = (uint32_t) wideDepth;
 	ctx->accel.builder = useSah ? 2u : (usePloc ? 1u : 0u);
 	ctx->accel.buildLevels = (uint32_t) (useSah ? sahLevels : plocRounds);
-	sc.traceFlags = ctx->dTraceFlags.as<uint32_t>();
+	sc.traceFlags = ctx->dTraceFlags.as<uint32_t>(); sc.oneBits = 0x3F800000u;
 	ctx->accel.triBytes = (uint64_t) nTri * sizeof(TriAccelRec);
 	ctx->accel.buildMs = ms;
 	ctx->built = true;

@@ -109,6 +109,8 @@ unsigned tracePersistentBlocks(mtsgpu_ctx *ctx, size_t n);
 int traceRayCounter(mtsgpu_ctx *ctx, uint32_t **out);
 int launchTrace(mtsgpu_ctx *ctx, const float4 *dRays, size_t n, int mode, void *dOut, uint64_t *dCounters);
 int checkTraceFlags(mtsgpu_ctx *ctx);
+int traceRefetchBelow();
+int traceLeafThreshold();
 // integrate.cu
 int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, volatile const int *cancel,
 	float *dOutFilm, mtsgpu_stats *stats);

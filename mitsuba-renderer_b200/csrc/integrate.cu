@@ -195,19 +195,19 @@ struct WfShadowSink {
 };
 template <bool SPH>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
-k_closest_wfp(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint4 *__restrict__ hits, uint32_t *rayCounter) {
+k_closest_wfp(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint4 *__restrict__ hits, uint32_t *rayCounter, int refetchBelow, int leafThreshold) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
 	uint32_t c0 = 0, c1 = 0;
 	WfHitSink sink = { hits };
-	tracePersistent<false, false, WfHitSink, SPH>(sc, rays, n, rayCounter, sink, sstack, c0, c1, TRACE_REFETCH_BELOW);
+	tracePersistent<false, false, WfHitSink, SPH>(sc, rays, n, rayCounter, sink, sstack, c0, c1, refetchBelow, true, leafThreshold);
 }
 template <bool SPH>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
-k_shadow_wfp(const DeviceScene sc, const float4 *__restrict__ rays, const float4 *__restrict__ payload, uint32_t n, float4 *li, uint32_t *rayCounter) {
+k_shadow_wfp(const DeviceScene sc, const float4 *__restrict__ rays, const float4 *__restrict__ payload, uint32_t n, float4 *li, uint32_t *rayCounter, int refetchBelow, int leafThreshold) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
 	uint32_t c0 = 0, c1 = 0;
 	WfShadowSink sink = { payload, li };
-	tracePersistent<true, false, WfShadowSink, SPH>(sc, rays, n, rayCounter, sink, sstack, c0, c1, TRACE_REFETCH_BELOW);
+	tracePersistent<true, false, WfShadowSink, SPH>(sc, rays, n, rayCounter, sink, sstack, c0, c1, refetchBelow, true, leafThreshold);
 }
 
 __device__ __forceinline__ float miWeight(float pdfA, float pdfB) {     // path.cpp:218-222 (power heuristic)
@@ -511,8 +511,8 @@ static int launchClosestWf(mtsgpu_ctx *ctx, const float4 *rays, uint32_t n, uint
 	}
 	if (persistent) {
 		uint32_t *rc = nullptr; int e = traceRayCounter(ctx, &rc); if (e) return e;
-		if (ctx->scene.hasSpheres) k_closest_wfp<true><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, rc);
-		else k_closest_wfp<false><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, rc);
+		if (ctx->scene.hasSpheres) k_closest_wfp<true><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, rc, traceRefetchBelow(), traceLeafThreshold());
+		else k_closest_wfp<false><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, rc, traceRefetchBelow(), traceLeafThreshold());
 	} else {
 		if (ctx->scene.hasSpheres) k_closest_wf<true><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, nullptr);
 		else k_closest_wf<false><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, nullptr);
@@ -522,8 +522,8 @@ static int launchClosestWf(mtsgpu_ctx *ctx, const float4 *rays, uint32_t n, uint
 static int launchShadowWf(mtsgpu_ctx *ctx, const float4 *rays, const float4 *payload, uint32_t n, float4 *li, bool persistent) {
 	if (persistent) {
 		uint32_t *rc = nullptr; int e = traceRayCounter(ctx, &rc); if (e) return e;
-		if (ctx->scene.hasSpheres) k_shadow_wfp<true><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li, rc);
-		else k_shadow_wfp<false><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li, rc);
+		if (ctx->scene.hasSpheres) k_shadow_wfp<true><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li, rc, traceRefetchBelow(), traceLeafThreshold());
+		else k_shadow_wfp<false><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li, rc, traceRefetchBelow(), traceLeafThreshold());
 	} else {
 		if (ctx->scene.hasSpheres) k_shadow_wf<true><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li);
 		else k_shadow_wf<false><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li);
@@ -588,7 +588,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 	{ int rc = makeSamplerConfig(ctx, P, samplerConfig); if (rc) return rc; }
 	cudaStream_t st = ctx->stream;
 	static const bool persistClosest = getenv("MTSGPU_WF_PERSIST_CLOSEST") ? atoi(getenv("MTSGPU_WF_PERSIST_CLOSEST")) != 0 : true;
-	static const bool persistShadow = getenv("MTSGPU_WF_PERSIST_SHADOW") ? atoi(getenv("MTSGPU_WF_PERSIST_SHADOW")) != 0 : false;
+	static const bool persistShadow = getenv("MTSGPU_WF_PERSIST_SHADOW") ? atoi(getenv("MTSGPU_WF_PERSIST_SHADOW")) != 0 : true;
 	const FilmDev film = ctx->film;
 	const size_t filmFloats = (size_t) film.cropW * film.cropH * 5;
 	{

@@ -73,6 +73,16 @@ unsigned tracePersistentBlocks(mtsgpu_ctx *ctx, size_t n) {
 	return (unsigned) std::max<size_t>(1, std::min(full, want));
 }
 
+// Thresholds of the persistent traversal (trace.cuh); the MTSGPU_* variables are experiment switches.
+int traceRefetchBelow() {
+	static const int v = getenv("MTSGPU_REFETCH_BELOW") ? atoi(getenv("MTSGPU_REFETCH_BELOW")) : TRACE_REFETCH_BELOW;
+	return v;
+}
+int traceLeafThreshold() {
+	static const int v = getenv("MTSGPU_LEAF_THRESHOLD") ? atoi(getenv("MTSGPU_LEAF_THRESHOLD")) : TRACE_LEAF_THRESHOLD;
+	return v;
+}
+
 // A zeroed ray counter for the next persistent launch: a ring of counters so that consecutive launches on
 // the stream never share one; each is re-zeroed (async memset) right before use.
 int traceRayCounter(mtsgpu_ctx *ctx, uint32_t **out) {
@@ -109,8 +119,7 @@ int launchTrace(mtsgpu_ctx *ctx, const float4 *dRays, size_t n, int mode, void *
 	unsigned long long *cnt = reinterpret_cast<unsigned long long *>(dCounters);
 	uint32_t *rayCounter = nullptr;
 	{ int rc = traceRayCounter(ctx, &rayCounter); if (rc) return rc; }
-	static const int rb = getenv("MTSGPU_REFETCH_BELOW") ? atoi(getenv("MTSGPU_REFETCH_BELOW")) : TRACE_REFETCH_BELOW;
-	static const int lt = getenv("MTSGPU_LEAF_THRESHOLD") ? atoi(getenv("MTSGPU_LEAF_THRESHOLD")) : 16;
+	const int rb = traceRefetchBelow(), lt = traceLeafThreshold();
 	static const int spec = getenv("MTSGPU_SPECULATE") ? atoi(getenv("MTSGPU_SPECULATE")) : 1;
 	const bool sph = ctx->scene.hasSpheres != 0;
 #define LAUNCH(K, C, S, OUT_T) K<C, S><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (OUT_T *) dOut, rayCounter, (C) ? cnt : nullptr, rb, spec, lt)

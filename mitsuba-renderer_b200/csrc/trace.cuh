@@ -120,8 +120,22 @@ __device__ __forceinline__ void ldg256(const void *p, uint32_t (&v)[8]) {
 // Slab test of one ray against the four children of a quantised node (types.cuh: BVH4QNode): two 256-bit loads, then per
 // plane one PRMT (byte -> the float 1 + q / 2^15) and one FFMA: t = m * S + C with S = scale / d and
 // C = (origin - o) / d - S. The near and far words of each axis are picked by the ray's direction signs, so a child
-// costs 6 PRMT + 6 FFMA + 4 min / max. tn[i] = entry distance, +inf when child i is not entered (or empty).
-__device__ __forceinline__ void nodeTest(const float4 *nodes, uint32_t node, float idx, float idy, float idz, float oix, float oiy, float oiz,
+// costs 6 PRMT + 6 FFMA + 4 min / max + 3 for the verdict. tn[i] = entry distance, +inf when child i is not entered
+// (or empty). `one` = 0x3F800000 handed in from the kernel parameters (DeviceScene::oneBits): as a literal, ptxas made it
+// PRMT's immediate and rebuilt the selector in a register before each of the 24 PRMTs (ncu source view, r02_q_c4_trace).
+template <int I>
+__device__ __forceinline__ float qPlane(uint32_t word, uint32_t one, float S, float C) {
+	uint32_t m;
+	asm("prmt.b32 %0, %1, %2, %3;" : "=r"(m) : "r"(word), "r"(one), "n"(0x7604 | (I << 4)));      // {0x00, byte I, 0x80, 0x3F}
+	return fmaf(__uint_as_float(m), S, C);
+}
+__device__ __forceinline__ float entryOrInf(float tnear, float tfar, uint32_t child) {
+	float r;
+	asm("{\n\t.reg .pred p, q;\n\tsetp.ne.u32 q, %3, 0xFFFFFFFF;\n\tsetp.le.and.f32 p, %1, %2, q;\n\tselp.f32 %0, %1, 0f7F800000, p;\n\t}"
+		: "=f"(r) : "f"(tnear), "f"(tfar), "r"(child));
+	return r;
+}
+__device__ __forceinline__ void nodeTest(const float4 *nodes, uint32_t one, uint32_t node, float idx, float idy, float idz, float oix, float oiy, float oiz,
 		float mint, float maxt, float (&tn)[4], uint32_t (&cw)[4]) {
 	const char *np = reinterpret_cast<const char *>(nodes) + (size_t) node * 64;
 	uint32_t a[8], b[8];
@@ -132,17 +146,12 @@ __device__ __forceinline__ void nodeTest(const float4 *nodes, uint32_t node, flo
 	const uint32_t nearX = nx ? b[3] : b[0], farX = nx ? b[0] : b[3];
 	const uint32_t nearY = ny ? b[4] : b[1], farY = ny ? b[1] : b[4];
 	const uint32_t nearZ = nz ? b[5] : b[2], farZ = nz ? b[2] : b[5];
-#pragma unroll
-	for (int i = 0; i < 4; ++i) {
-		const uint32_t sel = 0x7604u | ((uint32_t) i << 4);          // {0x00, byte i, 0x80, 0x3F}
-		const float t0x = fmaf(__uint_as_float(__byte_perm(nearX, 0x3F800000u, sel)), Sx, Cx), t1x = fmaf(__uint_as_float(__byte_perm(farX, 0x3F800000u, sel)), Sx, Cx);
-		const float t0y = fmaf(__uint_as_float(__byte_perm(nearY, 0x3F800000u, sel)), Sy, Cy), t1y = fmaf(__uint_as_float(__byte_perm(farY, 0x3F800000u, sel)), Sy, Cy);
-		const float t0z = fmaf(__uint_as_float(__byte_perm(nearZ, 0x3F800000u, sel)), Sz, Cz), t1z = fmaf(__uint_as_float(__byte_perm(farZ, 0x3F800000u, sel)), Sz, Cz);
-		const float tnear = fmaxf(fmaxf(fmaxf(t0x, t0y), t0z), mint);
-		const float tfar = fminf(fminf(fminf(t1x, t1y), t1z), maxt);
-		cw[i] = a[4 + i];
-		tn[i] = (tnear <= tfar && a[4 + i] != BVH_EMPTY) ? tnear : INFINITY;
-	}
+#define NODE_CHILD(I) { \
+		const float tnear = fmaxf(fmaxf(fmaxf(qPlane<I>(nearX, one, Sx, Cx), qPlane<I>(nearY, one, Sy, Cy)), qPlane<I>(nearZ, one, Sz, Cz)), mint); \
+		const float tfar = fminf(fminf(fminf(qPlane<I>(farX, one, Sx, Cx), qPlane<I>(farY, one, Sy, Cy)), qPlane<I>(farZ, one, Sz, Cz)), maxt); \
+		cw[I] = a[4 + I]; tn[I] = entryOrInf(tnear, tfar, a[4 + I]); }
+	NODE_CHILD(0) NODE_CHILD(1) NODE_CHILD(2) NODE_CHILD(3)
+#undef NODE_CHILD
 }
 
 // ---- instances of shape groups (src/shapes/instance.cpp) ---------------------------------------------------------
@@ -162,7 +171,7 @@ __device__ __noinline__ bool traverseGroup(const DeviceScene &gs, const RayIn &r
 	while (true) {
 		if (!(cur & BVH_LEAF)) {
 			float tn[4]; uint32_t cw[4];
-			nodeTest(gs.nodes, cur, idx, idy, idz, oix, oiy, oiz, mint, maxt, tn, cw);
+			nodeTest(gs.nodes, gs.oneBits, cur, idx, idy, idz, oix, oiy, oiz, mint, maxt, tn, cw);
 			uint32_t next = BVH_EMPTY; float nextT = INFINITY;
 #pragma unroll
 			for (int i = 0; i < 4; ++i) {
@@ -341,7 +350,7 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 		if (!(cur & BVH_LEAF)) {
 			if (COUNT) nodeVisits++;
 			float tn[4]; uint32_t cw[4];
-			nodeTest(sc.nodes, cur, idx, idy, idz, oix, oiy, oiz, mint, maxt, tn, cw);
+			nodeTest(sc.nodes, sc.oneBits, cur, idx, idy, idz, oix, oiy, oiz, mint, maxt, tn, cw);
 			{
 				// nearest hit first; the others in any order (popped entries are culled by their entry distance)
 #define CSWAP(a, b) if (tn[b] < tn[a]) { float tt = tn[a]; tn[a] = tn[b]; tn[b] = tt; uint32_t cc = cw[a]; cw[a] = cw[b]; cw[b] = cc; }
@@ -411,7 +420,8 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 #define TRACE_CHUNK 128
 #define TRACE_PERSISTENT_BLOCKS_PER_SM 8
 #define TRACE_FETCH_ATTEMPTS 8
-#define TRACE_REFETCH_BELOW 12      // leave the step loop to refetch when fewer lanes than this are active
+#define TRACE_REFETCH_BELOW 28      // leave the step loop to refetch when fewer lanes than this are active
+#define TRACE_LEAF_THRESHOLD 8      // lanes holding a leaf that end the inner-node phase
 
 struct LaneState {
 	RayIn r;
@@ -493,6 +503,18 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 			if (__all_sync(0xFFFFFFFFu, exhausted)) break;
 			continue;
 		}
+		// Thresholds per warp: rays that are nearly parallel (camera rays, in queue order) finish together, and measured
+		// on B200 they run 13 % faster with a late refetch and a late leaf phase (12 / 16), incoherent ones 21 % faster
+		// with an early one (28 / 8).
+		int rbNow = refetchBelow, ltNow = leafThreshold;
+		{
+			const uint32_t act = __ballot_sync(0xFFFFFFFFu, s.active);
+			const int leader = __ffs(act) - 1;
+			const float lx = __shfl_sync(0xFFFFFFFFu, s.r.dx, leader), ly = __shfl_sync(0xFFFFFFFFu, s.r.dy, leader), lz = __shfl_sync(0xFFFFFFFFu, s.r.dz, leader);
+			const float dt = s.r.dx * lx + s.r.dy * ly + s.r.dz * lz;
+			const float n2 = (s.r.dx * s.r.dx + s.r.dy * s.r.dy + s.r.dz * s.r.dz) * (lx * lx + ly * ly + lz * lz);
+			if (__all_sync(0xFFFFFFFFu, !s.active || (dt > 0.0f && dt * dt > 0.97f * n2))) { rbNow = min(refetchBelow, 12); ltNow = max(leafThreshold, 16); }
+		}
 
 		// ---- traversal; stay here while the warp is reasonably full (or no rays are left to fetch)
 		while (true) {
@@ -502,7 +524,7 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 				if (inner) {
 					if (COUNT) nodeVisits++;
 					float tn[4]; uint32_t cw[4];
-					nodeTest(sc.nodes, s.cur, s.idx, s.idy, s.idz, s.oix, s.oiy, s.oiz, s.mint, s.maxt, tn, cw);
+					nodeTest(sc.nodes, sc.oneBits, s.cur, s.idx, s.idy, s.idz, s.oix, s.oiy, s.oiz, s.mint, s.maxt, tn, cw);
 					{
 						// bring the nearest hit to slot 0; the order of the others is immaterial (measured: 28.3 vs
 						// 28.5 node visits per ray with a full sort) because popped entries are culled by distance
@@ -531,9 +553,66 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 				}
 				const bool canWalk = s.active && !(s.cur & BVH_LEAF);
 				if (!__any_sync(0xFFFFFFFFu, canWalk && s.leaf == BVH_EMPTY)) break;   // nobody without a leaf can go on
-				if (__popc(__ballot_sync(0xFFFFFFFFu, s.active && s.leaf != BVH_EMPTY)) >= leafThreshold) break;   // enough leaves to test together
+				if (__popc(__ballot_sync(0xFFFFFFFFu, s.active && s.leaf != BVH_EMPTY)) >= ltNow) break;   // enough leaves to test together
 			}
-			// (B) leaves: every lane that holds one tests its triangles; a second leaf waiting in `cur` moves up
+			// (B) leaves. ncu's source view of the per-lane loop (profiles/r02_q2_*): 37 % of all issue slots at 3 to 5 active
+			// lanes. Triangle variant (!SPH): the warp shares the work out. Up to 8 lanes that hold a leaf ("owners") post their
+			// ray and leaf word in shared memory; lane w then tests triangle (w & 3) of owner (w >> 2) and posts {t, u, v,
+			// accepted}; each owner folds its (up to four) results in triangle order with the shrinking maxt, which gives
+			// the very result of the sequential loop (sahkdtree3.h:278-283: a later equal t replaces an earlier one).
+			if (!SPH) {
+				static_assert(BVH_LEAF_MAX <= 4, "the shared leaf phase gives every owner four test slots");
+				__shared__ float4 xRayA[TRACE_BLOCK / 32][8], xRayB[TRACE_BLOCK / 32][8], xResult[TRACE_BLOCK / 32][32];
+				__shared__ uint32_t xLeaf[TRACE_BLOCK / 32][8];
+				const uint32_t wid = threadIdx.x >> 5;
+				const bool has = s.active && s.leaf != BVH_EMPTY;
+				const uint32_t hasMask = __ballot_sync(0xFFFFFFFFu, has);
+				const int rank = __popc(hasMask & ltMask), nOwners = __popc(hasMask);
+				for (int base = 0; base < nOwners; base += 8) {
+					const bool mine = has && rank >= base && rank < base + 8;
+					if (mine) {
+						xRayA[wid][rank - base] = make_float4(s.r.ox, s.r.oy, s.r.oz, s.mint);
+						xRayB[wid][rank - base] = make_float4(s.r.dx, s.r.dy, s.r.dz, s.maxt);
+						xLeaf[wid][rank - base] = s.leaf;
+					}
+					__syncwarp();
+					const int slot = lane >> 2, k = lane & 3;
+					float4 res = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+					if (base + slot < nOwners) {
+						const uint32_t leaf = xLeaf[wid][slot];
+						if ((uint32_t) k <= ((leaf >> 28) & 7u)) {
+							const float4 ra = xRayA[wid][slot], rb = xRayB[wid][slot];
+							const float4 *tp = sc.triAccel + (size_t) ((leaf & 0x0FFFFFFFu) + k) * 3;
+							const float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2);
+							const uint32_t kraw = __float_as_uint(q0.x);
+							if (!(SHADOW && (kraw & TRI_NONOCCLUDER))) {
+								if (COUNT) triTests++;
+								RayIn rr; rr.ox = ra.x; rr.oy = ra.y; rr.oz = ra.z; rr.mint = 0; rr.dx = rb.x; rr.dy = rb.y; rr.dz = rb.z; rr.maxt = 0;
+								float u, v, t;
+								if (triAccelTest(q0, q1, q2, kraw & TRI_K_MASK, rr, ra.w, rb.w, u, v, t)) res = make_float4(t, u, v, 1.0f);
+							}
+						}
+					}
+					xResult[wid][lane] = res;
+					__syncwarp();
+					if (mine) {
+						const uint32_t first = s.leaf & 0x0FFFFFFFu;
+#pragma unroll
+						for (int j = 0; j < 4; ++j) {
+							const float4 r4 = xResult[wid][(rank - base) * 4 + j];
+							if (r4.w != 0.0f && (SHADOW || r4.x <= s.maxt)) {
+								s.found = true;
+								if (!SHADOW) { s.maxt = r4.x; s.t = r4.x; s.u = r4.y; s.v = r4.z; s.tri = first + j; }
+							}
+						}
+						s.leaf = BVH_EMPTY;
+						if (SHADOW && s.found) { s.sp = 0; s.cur = BVH_EMPTY; }          // any-hit: done
+						else if ((s.cur & BVH_LEAF) && s.cur != BVH_EMPTY) { s.leaf = s.cur; STACK_POP(s.cur); }
+					}
+					__syncwarp();
+				}
+			} else
+			// scenes with analytic shapes: every lane that holds a leaf tests its primitives; a second leaf waiting in `cur` moves up
 			while (true) {
 				const bool has = s.active && s.leaf != BVH_EMPTY;
 				if (!__any_sync(0xFFFFFFFFu, has)) break;
@@ -560,13 +639,13 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 				}
 			}
 			// (C) rays with nothing left to visit are finished
-			if (s.active && s.cur == BVH_EMPTY) {
+			if (s.active && s.cur == BVH_EMPTY && s.leaf == BVH_EMPTY) {
 				s.active = false;
 				if (SHADOW) sink.any(s.ray, s.found); else sink.closest(s.ray, s.found, s.t, s.u, s.v, s.tri);
 			}
 			const uint32_t act = __ballot_sync(0xFFFFFFFFu, s.active);
 			if (act == 0) break;
-			if (__popc(act) < refetchBelow && !__all_sync(0xFFFFFFFFu, exhausted || s.active)) break;
+			if (__popc(act) < rbNow && !__all_sync(0xFFFFFFFFu, exhausted || s.active)) break;
 		}
 	}
 #undef STACK_PUSH
