@@ -1,17 +1,16 @@
 #!/usr/bin/env python
-"""Headline benchmark (BASELINE.json): ray-intersection throughput in Mrays/s on config C2 — a
-synthetic 1M-triangle mesh, 16M coherent camera rays + 16M incoherent (kdbench-protocol) rays, each
-traced as closest-hit and as shadow any-hit — plus samples/s of a path-traced render, beside the
-reference's own CPU code on the host cores.
+"""Headline benchmark (BASELINE.json, north_star target config C4): a full `path` render — maxDepth 16 with Russian
+roulette, roughconductor + dielectric BSDFs, procedural 10M-triangle scene, 1024 spp at 1920x1080 — through the CUDA
+library, reported as rays traced per second (closest-hit + shadow any-hit queries; samples/s beside it) next to the
+reference's own CPU `path` integrator on the host cores.
 
-One "step" = one pass of all four ray batches (2 x 16M closest-hit + 2 x 16M any-hit = 67M queries)
-through the CUDA library with the rays resident in HBM. `e2e` repeats it through the host-buffer C ABI
-call (mtsgpu_trace) with pinned host memory, H2D and D2H copies inside the timed region.
+One "step" = one whole render of the configuration. With N GPUs the sample range of every pixel is split across the
+ranks (strong scaling) and the {sum spec, sum alpha, sum weight} films are summed with ONE NCCL reduce inside the
+timed region. `e2e` is the plugin-equivalent call: scene upload from host arrays + acceleration-structure build +
+render + film back into pinned host memory, every step. The C2 ray-query microbench of round 1 (1M triangles,
+16M coherent + 16M incoherent rays, closest + any-hit) is kept as the extra key `c2`.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--rays R]
-Multi-GPU: one process per GPU under torchrun; every rank traces its own ray batches (weak scaling,
-no data-path collective) and the render leg shards the sample range and reduces the film with one
-NCCL reduce.
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c4|c5|c3|c1] [--spp S]
 """
 import argparse
 import json
@@ -26,8 +25,32 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-METRIC = "ray-intersection throughput, closest-hit + shadow any-hit (config C2)"
 UNIT = "Mrays/s"
+WORKLOADS = {
+    "c4": "C4: path maxDepth 16 + RR, 10M triangles (roughmetal terrain + roughmetal/dielectric spheres, 4 area lights), 1920x1080, 1024 spp, box filter",
+    "c5": "C5: as C4 at 3840x2160, 4096 spp",
+    "c3": "C3: direct 1+1, 1M triangles, 3 BSDFs + mirror, 8 area lights, 1920x1080, 256 spp",
+    "c1": "C1: Cornell box 512x512, path maxDepth 8, 64 spp, box filter",
+}
+
+
+def metric_name(workload):
+    return f"path-tracing throughput, closest-hit + shadow rays per second of a full render (config {workload.upper()})"
+
+
+def make_scene(workload, spp=0):
+    from mitsuba_renderer_b200 import scenes
+    if workload == "c1":
+        s = scenes.cornell_box(512, 512, 64)
+    elif workload == "c3":
+        s = scenes.direct_scene()
+    elif workload == "c5":
+        s = scenes.path_scene(width=3840, height=2160, spp=4096)
+    else:
+        s = scenes.path_scene()
+    if spp:
+        s.spp = spp
+    return s
 
 
 def measured_peaks():
@@ -70,6 +93,64 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(self.rows)}
 
 
+def scene_host_bytes(scene):
+    """Bytes of the host arrays a scene upload copies to the device (positions, normals, texture coordinates, indices)."""
+    n = 0
+    for sh in scene.shapes:
+        for a in (sh.positions, sh.triangles, sh.normals, getattr(sh, "texcoords", None)):
+            if a is not None:
+                n += np.asarray(a).nbytes
+    return n
+
+
+# ---------------------------------------------------------------------------------------------------------
+# the reference's own CPU code (oracle/_ref/timed: its release flags) on the host cores
+# ---------------------------------------------------------------------------------------------------------
+def cpu_reference_render(scene, spp, threads, passes):
+    """`passes` renders of `scene` at `spp` samples per pixel through the compiled reference's `path` / `direct`
+    integrator, scheduler and kd-tree (the equivalent of `mitsuba -p threads`); the kd-tree build is outside the timed
+    passes. Returns (rays per pass, seconds per pass [list], description, info) or (None, [], why, None)."""
+    from tests import oracle_util
+    import copy
+    variant = "timed" if oracle_util.available("timed") else "parity"
+    if not oracle_util.available(variant):
+        return None, [], "oracle/_ref not built", None
+    s = copy.copy(scene)
+    s.spp = spp
+    sess = oracle_util.Session(s, variant)
+    _, info = sess.render(threads=threads, repeat=passes)
+    rays = (oracle_util.parse_count(info["normal_rays"]) + oracle_util.parse_count(info["shadow_rays"])) / passes
+    desc = (f"{spp} of {scene.spp} spp of the same scene and film ({scene.width}x{scene.height}) per pass through the reference's own "
+            f"integrator + kd-tree ({variant} build), {threads} worker threads, kd-tree build ({info['kd_build_s']:.1f} s) excluded")
+    return rays, [float(x) for x in info["render_s_all"]], desc, info
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    scene = make_scene(args.workload, args.spp)
+    spp = args.cpu_spp or (2 if threads >= 16 else 1)
+    rays, per_pass, desc, info = cpu_reference_render(scene, spp, threads, args.warmup + args.steps)
+    if rays is None:
+        print(json.dumps({"impl": "reference", "unavailable": desc}))
+        return
+    timed = np.array(per_pass[args.warmup:])
+    value = rays * len(timed) / timed.sum() * 1e-6
+    samples_per_s = scene.width * scene.height * spp * len(timed) / timed.sum()
+    line = {"impl": "reference", "metric": metric_name(args.workload), "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": float(timed.mean() * 1e3), "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOADS[args.workload], "sample": desc, "triangles": scene.triangle_count},
+            "samples_per_s": samples_per_s, "kd_build_s": info["kd_build_s"],
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "reference", "sample": desc},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------------------------------------
+# C2: the ray-query microbench of round 1, kept as an extra key
+# ---------------------------------------------------------------------------------------------------------
 def build_ray_sets(scene, n_rays, seed):
     from mitsuba_renderer_b200 import scenes
     res = int(round(np.sqrt(n_rays)))
@@ -79,52 +160,82 @@ def build_ray_sets(scene, n_rays, seed):
             ("incoherent/closest", inc, 0), ("incoherent/any", scenes.shadow_segments(inc, scene, seed + 2), 1)]
 
 
-def cpu_reference_trace(scene, n_rays, threads, passes):
-    """The reference's own kd-tree (oracle/_ref/timed: its release flags) on a bounded sample of the same
-    workload. Returns (Mrays/s over all four batches, description, per-pass seconds)."""
-    from tests import oracle_util
-    variant = "timed" if oracle_util.available("timed") else "parity"
-    if not oracle_util.available(variant):
-        return None, "oracle/_ref not built", []
-    sess = oracle_util.Session(scene, variant)
-    sets = build_ray_sets(scene, n_rays, 2)
-    per_pass = np.zeros(passes)
-    queries = 0
-    for label, rays, mode in sets:
-        _, info = sess.trace(rays, "any" if mode else "closest", threads, passes)
-        per_pass += np.array(info["trace_s_all"])
-        queries += len(rays)
-    desc = f"{queries} queries/pass ({len(sets[0][1])} coherent + {n_rays} incoherent rays, closest + any-hit) on the 1M-triangle C2 mesh, " \
-           f"{threads} threads, reference kd-tree ({variant} build), kd-tree build excluded"
-    return queries, desc, per_pass
-
-
-def run_reference(args, rank, world):
-    if rank != 0:
-        return
+def c2_block(args, torch, api, local_rank, rank, world, barrier, max_over_ranks):
     from mitsuba_renderer_b200 import scenes
-    threads = os.cpu_count() or 1
     scene = scenes.microbench_scene()
-    n = args.cpu_rays or (1 << 20 if threads >= 16 else 1 << 18)
-    queries, desc, per_pass = cpu_reference_trace(scene, n, threads, args.warmup + args.steps)
-    if queries is None:
-        print(json.dumps({"impl": "reference", "unavailable": desc}))
-        return
-    timed = per_pass[args.warmup:]
-    value = queries * len(timed) / timed.sum() * 1e-6
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": float(timed.mean() * 1e3), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "C2: 1M-triangle displaced grid, coherent + incoherent rays, closest-hit + any-hit", "sample": desc},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "reference", "sample": desc},
-            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line))
+    ctx = api.Context(local_rank)
+    ctx.upload_scene(scene)
+    accel = ctx.accel_info()
+    sets = build_ray_sets(scene, args.rays, 2 + 100 * rank)
+    dev = []
+    for label, rays, mode in sets:
+        d_rays = torch.from_numpy(rays).cuda()
+        d_out = torch.empty(len(rays) * (1 if mode else 5), dtype=torch.int32, device="cuda")
+        dev.append((label, d_rays, d_out, mode, len(rays)))
+    queries = sum(d[4] for d in dev)
+
+    def step():
+        return [ctx.trace_device(d_rays.data_ptr(), n, mode, d_out.data_ptr()) for _, d_rays, d_out, mode, n in dev]
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize(); barrier()
+    t0 = time.perf_counter()
+    kernel_ms = np.zeros(len(dev))
+    for _ in range(args.c2_steps):
+        kernel_ms += np.array(step())
+    torch.cuda.synchronize(); barrier()
+    elapsed = max_over_ranks(time.perf_counter() - t0)
+    kernel_ms /= args.c2_steps
+    dom = int(np.argmax(kernel_ms))
+    label, d_rays, d_out, mode, n = dev[dom]
+    ctx.set_counters(True)
+    ctx.trace_device(d_rays.data_ptr(), n, mode, d_out.data_ptr())
+    cnt = ctx.counters()
+    ctx.set_counters(False)
+    nodes, tris = cnt["nodeVisits"] / n, cnt["triTests"] / n
+    bytes_per_ray = (36 if mode else 48) + nodes * 64 + tris * 48
+    peak, _ = measured_peaks()
+    achieved = n * bytes_per_ray / (kernel_ms[dom] * 1e-3) * 1e-9
+    # e2e through the host-buffer call, pinned memory
+    t = torch.empty(sets[2][1].shape, dtype=torch.float32, pin_memory=True)
+    t.numpy()[...] = sets[2][1]
+    o = torch.empty(len(sets[2][1]) * 5, dtype=torch.int32, pin_memory=True)
+    ctx._check(ctx.lib.mtsgpu_trace(ctx.h, t.data_ptr(), len(sets[2][1]), 0, o.data_ptr()))
+    torch.cuda.synchronize(); barrier()
+    t0 = time.perf_counter()
+    ctx._check(ctx.lib.mtsgpu_trace(ctx.h, t.data_ptr(), len(sets[2][1]), 0, o.data_ptr()))
+    torch.cuda.synchronize(); barrier()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    out = {"workload": "C2: 1M-triangle displaced grid, 16M coherent + 16M incoherent rays, closest-hit + any-hit, rays resident in HBM",
+           "value": queries * world * args.c2_steps / elapsed * 1e-6, "unit": UNIT, "steps": args.c2_steps, "scaling": "weak",
+           "per_batch_ms": {d[0]: float(ms) for d, ms in zip(dev, kernel_ms)},
+           "per_batch_mrays_per_s": {d[0]: d[4] / ms * 1e-3 for d, ms in zip(dev, kernel_ms)},
+           "roofline": {"kernel": "k_trace_any" if mode else "k_trace_closest", "batch": label, "nodes_per_ray": nodes, "tris_per_ray": tris,
+                        "bytes_per_ray": bytes_per_ray, "achieved": achieved, "peak": peak, "frac": achieved / peak, "unit": "GB/s"},
+           "e2e_incoherent_closest": {"value": len(sets[2][1]) * world / e2e_s * 1e-6, "unit": UNIT, "h2d_bytes": len(sets[2][1]) * 32, "d2h_bytes": len(sets[2][1]) * 20},
+           "bvh_nodes": accel["nodes"], "bvh_build_ms": accel["buildMs"]}
+    ctx.close()
+    del dev, t, o
+    torch.cuda.empty_cache()
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------------------
+def kernel_traffic(kernel):
+    """Measured DRAM traffic per ray of a traversal kernel on the C4 queues: dram__bytes_read.sum + dram__bytes_write.sum of one
+    `ncu --set full` launch, kept under profiles/ with the launch's ray count."""
+    p = os.path.join(ROOT, "profiles", "r02_kernel_traffic.json")
+    if not os.path.exists(p):
+        return None
+    return json.load(open(p)).get(kernel)
 
 
 def run_ours(args, rank, local_rank, world):
     import torch
     import torch.distributed as dist
-    from mitsuba_renderer_b200 import api, scenes
+    from mitsuba_renderer_b200 import api, multigpu
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -140,154 +251,155 @@ def run_ours(args, rank, local_rank, world):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    scene = scenes.microbench_scene()
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t)
+        return float(t.item())
+
+    scene = make_scene(args.workload, args.spp)
     ctx = api.Context(local_rank)
+    t0 = time.perf_counter()
     ctx.upload_scene(scene)
+    t_upload_build = time.perf_counter() - t0
     accel = ctx.accel_info()
-    sets = build_ray_sets(scene, args.rays, 2 + 100 * rank)
-    dev = []
-    for label, rays, mode in sets:
-        d_rays = torch.from_numpy(rays).cuda()
-        d_out = torch.empty(len(rays) * (1 if mode else 5), dtype=torch.int32, device="cuda")
-        dev.append((label, d_rays, d_out, mode, len(rays)))
-    torch.cuda.synchronize()
-    queries_per_step = sum(d[4] for d in dev)
+    film = torch.zeros(scene.width * scene.height * 5, dtype=torch.float32, device="cuda")
+    lo, hi = multigpu.sample_range(scene.spp, rank, world)             # this rank's share of every pixel's samples
+    params = api.Context.params_from_scene(scene, lo, hi, seed=1)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
     def step():
-        return [ctx.trace_device(d_rays.data_ptr(), n, mode, d_out.data_ptr()) for _, d_rays, d_out, mode, n in dev]
+        st = ctx.render_device(params, film.data_ptr())      # returns after its stream is idle; st["totalMs"]: CUDA events on that stream
+        red_ms = 0.0
+        if world > 1:
+            ev0.record()
+            multigpu.reduce_film(film, dst=0)                # the one collective: film accumulators over NVLink
+            ev1.record(); ev1.synchronize()
+            red_ms = ev0.elapsed_time(ev1)
+        return st, red_ms
 
     for _ in range(args.warmup):
         step()
     sampler = ClockSampler(local_rank); sampler.start()
     torch.cuda.synchronize(); barrier()
     t0 = time.perf_counter()
-    kernel_ms = np.zeros(len(dev))
+    acc = {"normalRays": 0, "shadowRays": 0, "cameraRays": 0, "kernelLaunches": 0, "traceClosestMs": 0.0, "traceAnyMs": 0.0, "shadeMs": 0.0, "totalMs": 0.0}
+    reduce_ms = 0.0
     for _ in range(args.steps):
-        kernel_ms += np.array(step())
+        st, red = step()
+        for k in acc:
+            acc[k] += st[k]
+        reduce_ms += red
     torch.cuda.synchronize(); barrier()
     elapsed = max_over_ranks(time.perf_counter() - t0)
+    device_ms = max_over_ranks(acc["totalMs"] + reduce_ms)              # CUDA-event time of the renders + reduces, slowest rank
     clocks = sampler.summary()
-    kernel_ms /= args.steps
-    value = queries_per_step * world * args.steps / elapsed * 1e-6
+    rays_total = sum_over_ranks(acc["normalRays"] + acc["shadowRays"])
+    launches_total = sum_over_ranks(acc["kernelLaunches"] + (args.steps if world > 1 else 0))
+    samples_total = float(scene.width) * scene.height * scene.spp * args.steps
+    value = rays_total / elapsed * 1e-6
 
-    # ---- roofline of the dominant kernel: algorithmic bytes = rays x (queue + nodes x 128 + tris x 48) ----
-    dom = int(np.argmax(kernel_ms))
-    label, d_rays, d_out, mode, n = dev[dom]
-    ctx.set_counters(True)
-    ctx.trace_device(d_rays.data_ptr(), n, mode, d_out.data_ptr())
-    cnt = ctx.counters()
-    ctx.set_counters(False)
-    nodes_per_ray, tris_per_ray = cnt["nodeVisits"] / n, cnt["triTests"] / n
-    queue_bytes = 36 if mode else 48
-    bytes_per_ray = queue_bytes + nodes_per_ray * 128 + tris_per_ray * 48
-    peak, peak_src = measured_peaks()
-    achieved = n * bytes_per_ray / (kernel_ms[dom] * 1e-3) * 1e-9
-    traffic, traffic_src = None, None
-    tpath = os.path.join(ROOT, "profiles", "r01_kernel_traffic.json")
-    kname = "k_trace_any" if mode else "k_trace_closest"
-    if os.path.exists(tpath):
-        rec = json.load(open(tpath)).get(kname)
-        if rec and rec.get("batch") == label:       # per launch, scaled to this run's ray count
-            traffic, traffic_src = rec["traffic"] * n / rec["rays"], rec["source"]
-    roofline = {"bound": "hbm", "kernel": kname, "batch": label, "achieved": achieved, "peak": peak,
-                "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
-                "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray,
-                "kernel_ms": float(kernel_ms[dom]), "mrays_per_s": n / kernel_ms[dom] * 1e-3,
-                "per_batch_ms": {d[0]: float(ms) for d, ms in zip(dev, kernel_ms)},
-                "per_batch_mrays_per_s": {d[0]: d[4] / ms * 1e-3 for d, ms in zip(dev, kernel_ms)}}
+    # ---- roofline of the dominant kernel (closest-hit traversal of the render's own ray queues) -------------------
+    # algorithmic bytes per ray = 48 B of queue traffic + node visits x 64 B + primitive tests x 48 B, with
+    # the per-ray counts from the counter build of the same kernels on a short render of the same scene (outside the timed region)
+    roofline = None
+    if rank == 0:
+        cspp = max(1, min(4, hi - lo))
+        ctx.set_counters(True)
+        cst = ctx.render_device(api.Context.params_from_scene(scene, lo, lo + cspp, seed=1), film.data_ptr())
+        ctx.set_counters(False)
+        peak, peak_src = measured_peaks()
+        n_c, n_s = max(cst["normalRays"], 1), max(cst["shadowRays"], 1)
+        nodes_c, tris_c = cst["closestNodeVisits"] / n_c, cst["closestTriTests"] / n_c
+        nodes_s, tris_s = cst["shadowNodeVisits"] / n_s, cst["shadowTriTests"] / n_s
+        bpr_c = 48 + nodes_c * 64 + tris_c * 48
+        bpr_s = 36 + nodes_s * 64 + tris_s * 48
+        ms_c, ms_s = acc["traceClosestMs"], acc["traceAnyMs"]
+        ach_c = acc["normalRays"] * bpr_c / (ms_c * 1e-3) * 1e-9 if ms_c > 0 else 0.0
+        ach_s = acc["shadowRays"] * bpr_s / (ms_s * 1e-3) * 1e-9 if ms_s > 0 else 0.0
+        tr = kernel_traffic("k_closest_wfp")
+        roofline = {"bound": "hbm", "kernel": "k_closest_wfp (closest-hit traversal, all bounce depths of the render)",
+                    "achieved": ach_c, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": ach_c / peak,
+                    "traffic": (tr["dram_bytes_per_ray"] * acc["normalRays"] / args.steps if tr else None),
+                    "traffic_note": "DRAM bytes of ALL closest-hit launches of one step = measured bytes per ray (one ncu --set full launch on a C4 bounce queue) x rays per step",
+                    "traffic_source": tr["source"] if tr else None,
+                    "measured_dram_gbs": (tr["dram_bytes_per_ray"] * acc["normalRays"] / (ms_c * 1e-3) * 1e-9 if tr and ms_c > 0 else None),
+                    "frac_measured_dram": (tr["dram_bytes_per_ray"] * acc["normalRays"] / (ms_c * 1e-3) * 1e-9 / peak if tr and ms_c > 0 else None),
+                    "ncu": ({k: tr[k] for k in ("l1_hit_pct", "l2_hit_pct", "lanes_per_instruction", "issue_active_pct", "l1_wavefront_pct") if k in tr} if tr else None),
+                    "bytes_per_ray": bpr_c, "nodes_per_ray": nodes_c, "tris_per_ray": tris_c, "node_bytes": 64, "tri_bytes": 48,
+                    "kernel_ms_per_step": ms_c / args.steps, "grays_per_s": acc["normalRays"] / ms_c * 1e-6 if ms_c > 0 else None,
+                    "shadow": {"kernel": "k_shadow_wfp", "achieved": ach_s, "frac": ach_s / peak, "bytes_per_ray": bpr_s, "nodes_per_ray": nodes_s,
+                               "tris_per_ray": tris_s, "kernel_ms_per_step": ms_s / args.steps, "grays_per_s": acc["shadowRays"] / ms_s * 1e-6 if ms_s > 0 else None},
+                    "counter_sample": f"{cspp} spp of the same scene and film through the counter build of the same kernels",
+                    "which_vs_40pct_target": "frac is SURVEY §8(d)'s algorithmic figure (bytes a ray's visits would fetch if nothing were cached); the kernel is "
+                                             "bound by instruction issue at partial SIMT occupancy, not by HBM: frac_measured_dram (ncu dram__bytes / duration) is the "
+                                             "HBM share actually used, and that is the number to hold against north_star's 40 %"}
 
-    # ---- e2e: the host-buffer C ABI call, pinned memory, copies inside the timed region ----
-    pinned = []
-    for label, rays, mode in sets:
-        t = torch.empty(rays.shape, dtype=torch.float32, pin_memory=True)
-        t.numpy()[...] = rays
-        o = torch.empty(len(rays) * (1 if mode else 5), dtype=torch.int32, pin_memory=True)
-        pinned.append((t, o, mode, len(rays)))
-    h2d = sum(p[3] * 32 for p in pinned); d2h = sum(p[3] * (4 if p[2] else 20) for p in pinned)
+    # ---- e2e: what one render() of the plugin does, every step: scene upload from host arrays + acceleration-structure
+    #      build + render of this rank's sample range + film reduce + film back into pinned host memory ---------------------
+    host_film = torch.empty(scene.width * scene.height * 5, dtype=torch.float32, pin_memory=True)
+    h2d = scene_host_bytes(scene) + 64
+    d2h = host_film.numel() * 4
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
 
     def e2e_step():
-        for t, o, mode, n in pinned:
-            ctx._check(ctx.lib.mtsgpu_trace(ctx.h, t.data_ptr(), n, mode, o.data_ptr()))
+        ctx.upload_scene(scene)                               # H2D of the meshes, GPU BVH build
+        st = ctx.render_device(params, film.data_ptr())
+        if world > 1:
+            multigpu.reduce_film(film, dst=0)
+        if rank == 0:
+            host_film.copy_(film, non_blocking=True)          # D2H of the result
+        torch.cuda.synchronize()
+        return st
     e2e_step()
-    e2e_steps = max(1, min(args.steps, 3))
     torch.cuda.synchronize(); barrier()
     t0 = time.perf_counter()
+    e2e_rays = 0.0
     for _ in range(e2e_steps):
-        e2e_step()
+        st = e2e_step()
+        e2e_rays += st["normalRays"] + st["shadowRays"]
     torch.cuda.synchronize(); barrier()
     e2e_elapsed = max_over_ranks(time.perf_counter() - t0)
-    e2e = {"value": queries_per_step * world * e2e_steps / e2e_elapsed * 1e-6, "unit": UNIT, "h2d_bytes_per_step": h2d,
-           "d2h_bytes_per_step": d2h, "steps": e2e_steps}
-    del pinned, dev
-    torch.cuda.empty_cache()
+    e2e_rays = sum_over_ranks(e2e_rays)
+    e2e = {"value": e2e_rays / e2e_elapsed * 1e-6, "unit": UNIT, "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+           "seconds_per_step": e2e_elapsed / e2e_steps, "samples_per_s": float(scene.width) * scene.height * scene.spp * e2e_steps / e2e_elapsed,
+           "what": "scene upload from host arrays + GPU BVH build + render + film reduce + film to pinned host memory, every step",
+           "first_upload_and_build_s_rank0": t_upload_build, "bvh_build_ms": ctx.accel_info()["buildMs"]}
 
-    # ---- render leg: config C1 (Cornell box, path maxDepth 8, 64 spp, 512x512, box filter) -----------
-    render = None
-    if not args.no_render:
-        from mitsuba_renderer_b200 import multigpu
-        if args.render == "c1":
-            rs, rname = scenes.cornell_box(512, 512, 64), "C1: Cornell box 512x512, path maxDepth 8, 64 spp, box filter"
-        elif args.render == "c3":
-            rs, rname = scenes.direct_scene(), "C3: direct 1+1, 1M triangles, 3 BSDFs + mirror, 8 area lights, 1920x1080, 256 spp"
-        elif args.render == "c4":
-            rs, rname = scenes.path_scene(), "C4: path maxDepth 16 + RR, 10M triangles (roughmetal terrain + roughmetal/dielectric spheres), 1920x1080, 1024 spp"
-        else:
-            rs, rname = scenes.path_scene(width=3840, height=2160, spp=4096), "C5: as C4 at 3840x2160, 4096 spp"
-        if args.render_spp:
-            rs.spp = args.render_spp
-            rname += f" [spp overridden to {args.render_spp}]"
-        rctx = api.Context(local_rank)
-        rctx.upload_scene(rs)
-        raccel = rctx.accel_info()
-        film = torch.zeros(rs.width * rs.height * 5, dtype=torch.float32, device="cuda")
-        lo, hi = multigpu.sample_range(rs.spp, rank, world)             # sample-range shard of this rank
-        params = api.Context.params_from_scene(rs, lo, hi, seed=1)
-        warm = api.Context.params_from_scene(rs, lo, min(hi, lo + 1), seed=1)
-        rctx.render_device(warm, film.data_ptr())                       # warm-up: 1 spp
-        torch.cuda.synchronize(); barrier()
-        t0 = time.perf_counter()
-        st = rctx.render_device(params, film.data_ptr())
-        torch.cuda.synchronize()
-        t_render = time.perf_counter() - t0
-        if world > 1:
-            multigpu.reduce_film(film, dst=0)                   # the one collective: film accumulators over NVLink
-            torch.cuda.synchronize()
-        t_reduce = time.perf_counter() - t0 - t_render
-        barrier()
-        dt = max_over_ranks(time.perf_counter() - t0)
-        rays = torch.tensor([float(st["normalRays"]), float(st["shadowRays"])], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(rays)
-        render = {"workload": rname, "triangles": rs.triangle_count, "seconds": dt, "scaling": "strong",
-                  "samples_per_s": rs.width * rs.height * rs.spp / dt, "mrays_per_s": float(rays.sum().item()) / dt * 1e-6,
-                  "normal_rays": float(rays[0].item()), "shadow_rays": float(rays[1].item()),
-                  "kernel_launches_rank0": st["kernelLaunches"], "trace_closest_ms_rank0": st["traceClosestMs"],
-                  "trace_any_ms_rank0": st["traceAnyMs"], "other_ms_rank0": st["shadeMs"], "render_s_rank0": t_render,
-                  "film_reduce_s_rank0": t_reduce, "film_reduce": "ncclReduce(sum) of W*H*5 floats" if world > 1 else "none (1 GPU)",
-                  "bvh_build_ms": raccel["buildMs"], "bvh_nodes": raccel["nodes"]}
-        rctx.close()
+    c2 = None
+    if not args.no_c2:
+        c2 = c2_block(args, torch, api, local_rank, rank, world, barrier, max_over_ranks)
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
-        n_cpu = args.cpu_rays or (1 << 20 if threads >= 16 else 1 << 18)
-        q, desc, per_pass = cpu_reference_trace(scene, n_cpu, threads, 2)
-        if q is not None:
-            cpu_baseline = {"value": q / per_pass.min() * 1e-6, "unit": UNIT, "cores": threads, "kind": "reference", "sample": desc}
+        spp = args.cpu_spp or (2 if threads >= 16 else 1)
+        rays, per_pass, desc, info = cpu_reference_render(scene, spp, threads, 2)
+        if rays is not None:
+            cpu_baseline = {"value": rays / min(per_pass) * 1e-6, "unit": UNIT, "cores": threads, "kind": "reference", "sample": desc,
+                            "samples_per_s": scene.width * scene.height * spp / min(per_pass), "kd_build_s": info["kd_build_s"]}
         else:
             cpu_baseline = {"value": None, "unit": UNIT, "cores": threads, "kind": "reference", "sample": desc}
 
     if rank == 0:
-        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": elapsed / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        line = {"metric": metric_name(args.workload), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": elapsed / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic",
-                "config": {"workload": "C2: 1M-triangle displaced grid, coherent + incoherent rays, closest-hit + any-hit",
-                           "triangles": scene.triangle_count, "rays_per_batch": args.rays, "batches": 4, "queries_per_step_per_gpu": queries_per_step,
-                           "l2_policy": "inputs larger than L2 (each ray batch is >= 512 MB at 16M rays)",
-                           "bvh_nodes": accel["nodes"], "bvh_node_bytes": accel["nodeBytes"], "triaccel_bytes": accel["triBytes"], "bvh_build_ms": accel["buildMs"],
-                           "parallelism": f"{world} x independent ray batches" if world > 1 else "1 GPU"},
+                "config": {"workload": WORKLOADS[args.workload] + (f" [spp overridden to {args.spp}]" if args.spp else ""),
+                           "triangles": scene.triangle_count, "width": scene.width, "height": scene.height, "spp": scene.spp,
+                           "max_depth": scene.max_depth, "rr_depth": scene.rr_depth, "samples_per_step": float(scene.width) * scene.height * scene.spp,
+                           "l2_policy": "inputs larger than L2 (10M triangles: 96 MB of nodes + 480 MB of TriAccel + 960 MB of shading records; 6 GB of wavefront queues rewritten every bounce)",
+                           "bvh_nodes": accel["nodes"], "bvh_node_bytes": accel["nodeBytes"], "bvh_depth": accel["depth"], "triaccel_bytes": accel["triBytes"],
+                           "bvh_build_ms": accel["buildMs"],
+                           "parallelism": f"sample range of every pixel split over {world} ranks + one ncclReduce of the film" if world > 1 else "1 GPU"},
+                "samples_per_s": samples_total / elapsed, "device_ms_per_step": device_ms / args.steps,
+                "timing": "wall clock between synchronize + barrier pairs, max over ranks; device_ms_per_step = CUDA events on the launching streams",
+                "per_step_ms_rank0": {"trace_closest": acc["traceClosestMs"] / args.steps, "trace_any": acc["traceAnyMs"] / args.steps,
+                                      "other": acc["shadeMs"] / args.steps, "film_reduce": reduce_ms / args.steps},
+                "rays_per_step": rays_total / args.steps,
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "clocks": clocks,
-                "gpu_launches": 4 * args.steps, "render": render}
+                "gpu_launches": int(launches_total), "c2": c2}
         print(json.dumps(line))
     ctx.close()
     if world > 1:
@@ -297,14 +409,16 @@ def run_ours(args, rank, local_rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=40)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--rays", type=int, default=1 << 24, help="rays per batch (coherent batch is the nearest square)")
-    ap.add_argument("--cpu-rays", type=int, default=0, help="rays per batch of the bounded CPU sample (0 = auto)")
-    ap.add_argument("--no-render", action="store_true")
-    ap.add_argument("--render", default="c4", choices=["c1", "c3", "c4", "c5"], help="config of the render leg")
-    ap.add_argument("--render-spp", type=int, default=0, help="override the render leg's samples per pixel")
+    ap.add_argument("--workload", default="c4", choices=list(WORKLOADS), help="configuration of the render (headline: c4)")
+    ap.add_argument("--spp", type=int, default=0, help="override the samples per pixel (the line says so)")
+    ap.add_argument("--cpu-spp", type=int, default=0, help="samples per pixel of the bounded CPU sample (0 = auto)")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--rays", type=int, default=1 << 24, help="C2 block: rays per batch")
+    ap.add_argument("--c2-steps", type=int, default=5)
+    ap.add_argument("--no-c2", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); local_rank = int(os.environ.get("LOCAL_RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))

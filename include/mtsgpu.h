@@ -190,6 +190,9 @@ typedef struct mtsgpu_stats {
 	double   traceAnyMs;      /* ... in the any-hit kernel */
 	double   shadeMs;         /* ... in ray generation + shading + splatting */
 	double   totalMs;         /* whole call, device time */
+	/* filled only when counters are enabled (mtsgpu_set_counters): traversal work on the render's own ray queues, the
+	 * counterpart of rayIntersectHavranCollectStatistics (include/mitsuba/render/sahkdtree3.h:310-410) */
+	uint64_t closestNodeVisits, closestTriTests, shadowNodeVisits, shadowTriTests;
 } mtsgpu_stats;
 
 /* Closest-hit record returned by mtsgpu_trace; mirrors the reference's IntersectionCache

@@ -66,7 +66,9 @@ class RenderParams(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("cameraRays", C.c_uint64), ("normalRays", C.c_uint64), ("shadowRays", C.c_uint64),
                 ("samples", C.c_uint64), ("kernelLaunches", C.c_uint64), ("traceClosestMs", C.c_double),
-                ("traceAnyMs", C.c_double), ("shadeMs", C.c_double), ("totalMs", C.c_double)]
+                ("traceAnyMs", C.c_double), ("shadeMs", C.c_double), ("totalMs", C.c_double),
+                ("closestNodeVisits", C.c_uint64), ("closestTriTests", C.c_uint64), ("shadowNodeVisits", C.c_uint64),
+                ("shadowTriTests", C.c_uint64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

@@ -399,7 +399,7 @@ int mtsgpu_trace_device(mtsgpu_ctx *ctx, const float *d_rays, size_t n, int mode
 	REQUIRE(ctx, n == 0 || (d_rays && d_out), MTSGPU_ERR_ARG, "trace: null buffer");
 	uint64_t *cnt = nullptr;
 	if (ctx->countersEnabled) {
-		CUDA_TRY(ctx, ctx->dCounters.alloc(16));
+		CUDA_TRY(ctx, ctx->dCounters.alloc(64));
 		CUDA_TRY(ctx, cudaMemsetAsync(ctx->dCounters.p, 0, 16, ctx->stream));
 		cnt = ctx->dCounters.as<uint64_t>();
 	}

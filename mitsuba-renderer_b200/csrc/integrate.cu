@@ -193,21 +193,27 @@ struct WfShadowSink {
 		li[slot] = l;
 	}
 };
-template <bool SPH>
+// COUNT: the counter build (mtsgpu_set_counters): node visits and primitive tests of the render's own ray queues, summed into
+// `counters` — a separate instantiation, so the timed kernels carry no counter code.
+template <bool SPH, bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
-k_closest_wfp(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint4 *__restrict__ hits, uint32_t *rayCounter, int refetchBelow, int leafThreshold) {
+k_closest_wfp(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint4 *__restrict__ hits, uint32_t *rayCounter, int refetchBelow, int leafThreshold,
+		unsigned long long *counters) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
 	uint32_t c0 = 0, c1 = 0;
 	WfHitSink sink = { hits };
-	tracePersistent<false, false, WfHitSink, SPH>(sc, rays, n, rayCounter, sink, sstack, c0, c1, refetchBelow, true, leafThreshold);
+	tracePersistent<false, COUNT, WfHitSink, SPH>(sc, rays, n, rayCounter, sink, sstack, c0, c1, refetchBelow, true, leafThreshold);
+	if (COUNT) flushCounters(c0, c1, counters);
 }
-template <bool SPH>
+template <bool SPH, bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
-k_shadow_wfp(const DeviceScene sc, const float4 *__restrict__ rays, const float4 *__restrict__ payload, uint32_t n, float4 *li, uint32_t *rayCounter, int refetchBelow, int leafThreshold) {
+k_shadow_wfp(const DeviceScene sc, const float4 *__restrict__ rays, const float4 *__restrict__ payload, uint32_t n, float4 *li, uint32_t *rayCounter, int refetchBelow, int leafThreshold,
+		unsigned long long *counters) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
 	uint32_t c0 = 0, c1 = 0;
 	WfShadowSink sink = { payload, li };
-	tracePersistent<true, false, WfShadowSink, SPH>(sc, rays, n, rayCounter, sink, sstack, c0, c1, refetchBelow, true, leafThreshold);
+	tracePersistent<true, COUNT, WfShadowSink, SPH>(sc, rays, n, rayCounter, sink, sstack, c0, c1, refetchBelow, true, leafThreshold);
+	if (COUNT) flushCounters(c0, c1, counters);
 }
 
 __device__ __forceinline__ float miWeight(float pdfA, float pdfB) {     // path.cpp:218-222 (power heuristic)
@@ -511,8 +517,13 @@ static int launchClosestWf(mtsgpu_ctx *ctx, const float4 *rays, uint32_t n, uint
 	}
 	if (persistent) {
 		uint32_t *rc = nullptr; int e = traceRayCounter(ctx, &rc); if (e) return e;
-		if (ctx->scene.hasSpheres) k_closest_wfp<true><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, rc, traceRefetchBelow(), traceLeafThreshold());
-		else k_closest_wfp<false><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, rc, traceRefetchBelow(), traceLeafThreshold());
+		const unsigned blocks = tracePersistentBlocks(ctx, n);
+		const int rb = traceRefetchBelow(), lt = traceLeafThreshold();
+		unsigned long long *cnt = ctx->countersEnabled ? ctx->dCounters.as<unsigned long long>() + 2 : nullptr;     // [2..3]: closest-hit queues of a render
+#define WFP(S, C) k_closest_wfp<S, C><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, rc, rb, lt, cnt)
+		if (ctx->scene.hasSpheres) { if (cnt) WFP(true, true); else WFP(true, false); }
+		else { if (cnt) WFP(false, true); else WFP(false, false); }
+#undef WFP
 	} else {
 		if (ctx->scene.hasSpheres) k_closest_wf<true><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, nullptr);
 		else k_closest_wf<false><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, nullptr);
@@ -522,8 +533,13 @@ static int launchClosestWf(mtsgpu_ctx *ctx, const float4 *rays, uint32_t n, uint
 static int launchShadowWf(mtsgpu_ctx *ctx, const float4 *rays, const float4 *payload, uint32_t n, float4 *li, bool persistent) {
 	if (persistent) {
 		uint32_t *rc = nullptr; int e = traceRayCounter(ctx, &rc); if (e) return e;
-		if (ctx->scene.hasSpheres) k_shadow_wfp<true><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li, rc, traceRefetchBelow(), traceLeafThreshold());
-		else k_shadow_wfp<false><<<tracePersistentBlocks(ctx, n), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li, rc, traceRefetchBelow(), traceLeafThreshold());
+		const unsigned blocks = tracePersistentBlocks(ctx, n);
+		const int rb = traceRefetchBelow(), lt = traceLeafThreshold();
+		unsigned long long *cnt = ctx->countersEnabled ? ctx->dCounters.as<unsigned long long>() + 4 : nullptr;     // [4..5]: shadow queues of a render
+#define WFP(S, C) k_shadow_wfp<S, C><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li, rc, rb, lt, cnt)
+		if (ctx->scene.hasSpheres) { if (cnt) WFP(true, true); else WFP(true, false); }
+		else { if (cnt) WFP(false, true); else WFP(false, false); }
+#undef WFP
 	} else {
 		if (ctx->scene.hasSpheres) k_shadow_wf<true><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li);
 		else k_shadow_wf<false><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li);
@@ -598,6 +614,10 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 	DevBuf &dTable = ctx->dFilterTable;
 	{ int rc = uploadFilter(ctx, dTable); if (rc) return rc; }
 
+	if (ctx->countersEnabled) {
+		CUDA_TRY(ctx, ctx->dCounters.alloc(64));
+		CUDA_TRY(ctx, cudaMemsetAsync(ctx->dCounters.p, 0, 64, st));
+	}
 	k_zero<<<blocksFor(filmFloats, 256), 256, 0, st>>>(dOutFilm, filmFloats);
 	CUDA_TRY(ctx, cudaGetLastError());
 	mtsgpu_stats S; memset(&S, 0, sizeof(S));
@@ -756,6 +776,11 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 	CUDA_TRY(ctx, cudaGetLastError());
 	{ float ms = 0; cudaEventElapsedTime(&ms, evBegin, evEnd); S.totalMs = ms; }
 	S.shadeMs = S.totalMs - S.traceClosestMs - S.traceAnyMs;
+	if (ctx->countersEnabled) {
+		unsigned long long h[8];
+		CUDA_TRY(ctx, cudaMemcpy(h, ctx->dCounters.p, sizeof(h), cudaMemcpyDeviceToHost));
+		S.closestNodeVisits = h[2]; S.closestTriTests = h[3]; S.shadowNodeVisits = h[4]; S.shadowTriTests = h[5];
+	}
 	if (stats) *stats = S;
 	return checkTraceFlags(ctx);
 }

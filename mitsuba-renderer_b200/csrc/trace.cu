@@ -25,17 +25,6 @@ struct OccludedSink {
 	__device__ __forceinline__ void any(uint32_t ray, bool occluded) { out[ray] = occluded ? 1u : 0u; }
 };
 
-__device__ __forceinline__ void flushCounters(uint32_t nodeVisits, uint32_t triTests, unsigned long long *counters) {
-	for (int o = 16; o > 0; o >>= 1) {
-		nodeVisits += __shfl_xor_sync(0xFFFFFFFFu, nodeVisits, o);
-		triTests += __shfl_xor_sync(0xFFFFFFFFu, triTests, o);
-	}
-	if ((threadIdx.x & 31) == 0) {
-		atomicAdd(&counters[0], (unsigned long long) nodeVisits);
-		atomicAdd(&counters[1], (unsigned long long) triTests);
-	}
-}
-
 // rays: 2 x float4 per ray {o.xyz, mint}{d.xyz, maxt}; 128-bit loads. Persistent warps pull rays from
 // `rayCounter` (zeroed by the host before the launch).
 template <bool COUNT, bool SPH>

@@ -421,7 +421,7 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 #define TRACE_PERSISTENT_BLOCKS_PER_SM 8
 #define TRACE_FETCH_ATTEMPTS 8
 #define TRACE_REFETCH_BELOW 28      // leave the step loop to refetch when fewer lanes than this are active
-#define TRACE_LEAF_THRESHOLD 8      // lanes holding a leaf that end the inner-node phase
+#define TRACE_LEAF_THRESHOLD 6      // lanes holding a leaf that end the inner-node phase
 
 struct LaneState {
 	RayIn r;
@@ -650,4 +650,16 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 	}
 #undef STACK_PUSH
 #undef STACK_POP
+}
+
+// counter builds: per-warp sums of node visits / primitive tests into two 64-bit device counters
+__device__ __forceinline__ void flushCounters(uint32_t nodeVisits, uint32_t triTests, unsigned long long *counters) {
+	for (int o = 16; o > 0; o >>= 1) {
+		nodeVisits += __shfl_xor_sync(0xFFFFFFFFu, nodeVisits, o);
+		triTests += __shfl_xor_sync(0xFFFFFFFFu, triTests, o);
+	}
+	if ((threadIdx.x & 31) == 0) {
+		atomicAdd(&counters[0], (unsigned long long) nodeVisits);
+		atomicAdd(&counters[1], (unsigned long long) triTests);
+	}
 }

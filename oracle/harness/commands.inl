@@ -2,12 +2,12 @@
  * mts_oracle.cpp). Every numeric result below is produced by the reference's own classes. */
 
 static int cmdTraceImpl(int argc, char **argv) {
-	if (argc < 6) { std::cerr << "trace SCENE RAYS OUT closest|closest_full|any [threads] [repeat]\n"; return 1; }
+	if (argc < 6) { std::cerr << "trace SCENE RAYS OUT closest|closest_full|any|stats [threads] [repeat]\n"; return 1; }
 	sio::Scene sf; sio::load(argv[2], sf);
 	std::vector<float> rays = sio::loadFloats(argv[3]);
 	const size_t n = rays.size() / 8;
 	std::string modeStr = argv[5];
-	int mode = modeStr == "closest" ? 0 : modeStr == "closest_full" ? 1 : modeStr == "any" ? 2 : -1;
+	int mode = modeStr == "closest" ? 0 : modeStr == "closest_full" ? 1 : modeStr == "any" ? 2 : modeStr == "stats" ? 3 : -1;
 	if (mode < 0) { std::cerr << "bad mode\n"; return 1; }
 	int threads = argc > 6 ? atoi(argv[6]) : 1;
 	int repeat = argc > 7 ? atoi(argv[7]) : 1;
@@ -16,7 +16,8 @@ static int cmdTraceImpl(int argc, char **argv) {
 	std::vector<float> tuv; std::vector<uint32_t> ids, occl; std::vector<float> full;
 	if (mode == 2) occl.resize(n); else { tuv.resize(n * 3); ids.resize(n * 2); }
 	if (mode == 1) full.resize(n * 12);
-	TraceCtx ctx = { b.scene.get(), rays.data(), mode, tuv.data(), ids.data(), full.data(), occl.data() };
+	std::atomic<uint64_t> kdTrav(0), kdIsect(0);
+	TraceCtx ctx = { b.scene.get(), rays.data(), mode, tuv.data(), ids.data(), full.data(), occl.data(), &kdTrav, &kdIsect };
 	double best = 1e30;
 	std::string all;
 	for (int r = 0; r < repeat; ++r) {
@@ -37,12 +38,15 @@ static int cmdTraceImpl(int argc, char **argv) {
 	fclose(f);
 	size_t hits = 0;
 	if (mode == 2) for (size_t i = 0; i < n; ++i) hits += occl[i];
+	else if (mode == 3) for (size_t i = 0; i < n; ++i) hits += std::isfinite(tuv[i*3]);
 	else for (size_t i = 0; i < n; ++i) hits += ids[i*2] != 0xFFFFFFFFu;
 	const AABB &bb = b.scene->getKDTree()->getAABB();
 	printf("{\"cmd\": \"trace\", \"mode\": \"%s\", \"rays\": %zu, \"hits\": %zu, \"threads\": %d, "
 		"\"kd_build_s\": %.6f, \"trace_s\": %.6f, \"trace_s_all\": [%s], \"mrays_per_s\": %.6f, "
+		"\"kd_traversals\": %llu, \"kd_intersections\": %llu, "
 		"\"aabb\": [%.9g, %.9g, %.9g, %.9g, %.9g, %.9g]}\n",
 		modeStr.c_str(), n, hits, threads, b.buildSeconds, best, all.c_str(), n / best * 1e-6,
+		(unsigned long long) (kdTrav.load() / (uint64_t) std::max(repeat, 1)), (unsigned long long) (kdIsect.load() / (uint64_t) std::max(repeat, 1)),
 		bb.min.x, bb.min.y, bb.min.z, bb.max.x, bb.max.y, bb.max.z);
 	return 0;
 }
@@ -197,10 +201,12 @@ static int cmdSplat(int argc, char **argv) {
 }
 
 static int cmdRender(int argc, char **argv) {
-	if (argc < 4) { std::cerr << "render SCENE OUT [threads] [integratorPlugin]\n"; return 1; }
+	if (argc < 4) { std::cerr << "render SCENE OUT [threads] [integratorPlugin|-] [repeat]\n"; return 1; }
 	sio::Scene sf; sio::load(argv[2], sf);
 	int threads = argc > 4 ? atoi(argv[4]) : 1;
 	std::string integ = argc > 5 ? argv[5] : "";
+	if (integ == "-") integ = "";
+	const int repeat = argc > 6 ? std::max(atoi(argv[6]), 1) : 1;     /* timing runs: the film then holds all passes */
 	Scheduler *sched = Scheduler::getInstance();
 	for (int i = 0; i < threads; ++i)
 		sched->registerWorker(new LocalWorker(formatString("wrk%i", i)));
@@ -208,20 +214,26 @@ static int cmdRender(int argc, char **argv) {
 
 	Built b = buildScene(sf, integ);
 	ref<RenderQueue> queue = new RenderQueue();
-	ref<RenderJob> job = new RenderJob("ren0", b.scene, queue, NULL, -1, -1, -1, false, false);
-	double t0 = now();
-	job->start();
-	queue->waitLeft(0);
-	double dt = now() - t0;
-	job->join();
+	ref<RenderJob> job;
+	double dt = 1e30; std::string all;
+	for (int r = 0; r < repeat; ++r) {
+		job = new RenderJob(formatString("ren%i", r), b.scene, queue, NULL, -1, -1, -1, false, false);
+		double t0 = now();
+		job->start();
+		queue->waitLeft(0);
+		const double d = now() - t0;
+		job->join();
+		dt = std::min(dt, d);
+		all += (r ? ", " : "") + formatString("%.6f", d);
+	}
 	sio::save(argv[3], b.film->raw().data(), b.film->raw().size() * 4);
 	std::string stats = Statistics::getInstance()->getStats();
 	double samples = (double) sf.cropW * sf.cropH * sf.spp;
 	printf("{\"cmd\": \"render\", \"integrator\": \"%s\", \"threads\": %d, \"width\": %u, \"height\": %u, \"spp\": %u, "
-		"\"kd_build_s\": %.6f, \"render_s\": %.6f, \"samples_per_s\": %.3f, "
+		"\"kd_build_s\": %.6f, \"render_s\": %.6f, \"render_s_all\": [%s], \"repeat\": %d, \"samples_per_s\": %.3f, "
 		"\"normal_rays\": \"%s\", \"shadow_rays\": \"%s\"}\n",
 		integ.empty() ? (sf.mode == 0 ? "path" : "direct") : integ.c_str(), threads, sf.cropW, sf.cropH, sf.spp,
-		b.buildSeconds, dt, samples / dt,
+		b.buildSeconds, dt, all.c_str(), repeat, samples / dt,
 		statValue(stats, "Normal rays traced").c_str(), statValue(stats, "Shadow rays traced").c_str());
 	fflush(stdout);
 	job = NULL; queue = NULL;

@@ -17,6 +17,7 @@
  *   render  SCENE OUT [threads] [integratorPlugin]
  * Each prints one JSON line with timings/counters on stdout.
  */
+#include <atomic>
 #include <mitsuba/render/scene.h>
 #include <mitsuba/render/renderjob.h>
 #include <mitsuba/render/renderqueue.h>
@@ -564,6 +565,24 @@ public:
 		}
 		return false;
 	}
+	/* The same query through the reference's own instrumented traversal (sahkdtree3.h:310-410): kd-tree nodes traversed
+	 * and primitives intersected for this ray — the per-ray work the GPU side's counters are set against. */
+	static bool closestStats(const ShapeKDTree *kd, const Ray &ray, Float &t, uint32_t &traversals, uint32_t &intersections) {
+		uint8_t temp[MTS_KD_INTERSECTION_TEMP];
+		t = std::numeric_limits<Float>::infinity();
+		traversals = intersections = 0;
+		Float mint, maxt;
+		if (!kd->m_aabb.rayIntersect(ray, mint, maxt)) return false;
+		Float rayMinT = ray.mint;
+		if (rayMinT == Epsilon)
+			rayMinT *= std::max(std::max(std::max(std::abs(ray.o.x), std::abs(ray.o.y)), std::abs(ray.o.z)), Epsilon);
+		if (rayMinT > mint) mint = rayMinT;
+		if (ray.maxt < maxt) maxt = ray.maxt;
+		if (!(maxt > mint)) return false;
+		boost::tuple<bool, uint32_t, uint32_t, uint64_t> st = kd->rayIntersectHavranCollectStatistics(ray, mint, maxt, t, temp);
+		traversals = boost::get<1>(st); intersections = boost::get<2>(st);
+		return boost::get<0>(st);
+	}
 	static const TriAccel *triAccel(const ShapeKDTree *kd) { return kd->m_triAccel; }
 	static const AABB &tightAABB(const ShapeKDTree *kd) { return kd->m_tightAABB; }
 };
@@ -572,6 +591,7 @@ MTS_NAMESPACE_END
 struct TraceCtx {
 	const Scene *scene; const float *rays; int mode;
 	float *tuv; uint32_t *ids; float *full; uint32_t *occl;
+	std::atomic<uint64_t> *kdTraversals, *kdIntersections;     /* mode 3 */
 };
 
 static void traceRange(void *c, size_t b, size_t e) {
@@ -583,6 +603,14 @@ static void traceRange(void *c, size_t b, size_t e) {
 		Ray ray(Point(r[0], r[1], r[2]), Vector(r[4], r[5], r[6]), r[3], r[7], 0.0f);
 		if (ctx.mode == 2) {
 			ctx.occl[i] = kd->rayIntersect(ray) ? 1u : 0u;
+			continue;
+		}
+		if (ctx.mode == 3) {
+			Float t; uint32_t nt, ni;
+			const bool hit = Instance::closestStats(kd, ray, t, nt, ni);
+			ctx.tuv[i*3+0] = hit ? t : std::numeric_limits<float>::infinity(); ctx.tuv[i*3+1] = ctx.tuv[i*3+2] = 0;
+			ctx.ids[i*2+0] = nt; ctx.ids[i*2+1] = ni;
+			ctx.kdTraversals->fetch_add(nt, std::memory_order_relaxed); ctx.kdIntersections->fetch_add(ni, std::memory_order_relaxed);
 			continue;
 		}
 		Float t, u, v; uint32_t shape, prim;

@@ -110,6 +110,16 @@ class Session:
             return hits, full, info
         return hits, info
 
+    def kd_stats(self, rays, threads=1):
+        """Per-ray work of the reference's kd-tree on these closest-hit queries, through its own instrumented traversal
+        (rayIntersectHavranCollectStatistics, sahkdtree3.h:310-410): (nodes traversed, primitives intersected) per ray.
+        Only the counts are used: that function reuses its output variable `t` for split distances (sahkdtree3.h:370)."""
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+        out, info = self._io("trace", rays, ["stats", threads, 1])
+        n = len(rays)
+        raw = np.fromfile(out, np.uint32)
+        return raw[3 * n:5 * n].reshape(n, 2).copy(), info
+
     def triaccel(self):
         out = os.path.join(self.dir.name, "ta.bin")
         info = _run(["triaccel", self.scene_path, out], self.variant)
@@ -147,10 +157,13 @@ class Session:
         cx, cy, cw, ch = self.scene.crop_rect
         return np.fromfile(out, np.float32).reshape(ch, cw, 5), np.fromfile(table, np.float32).reshape(16, 16), info
 
-    def render(self, threads=None, integrator=None, env=None):
+    def render(self, threads=None, integrator=None, env=None, repeat=1):
+        """repeat > 1: timing runs (info["render_s_all"]); the returned film then holds the sum of all passes."""
         out = os.path.join(self.dir.name, "film.bin")
         threads = threads or os.cpu_count() or 1
-        args = ["render", self.scene_path, out, threads] + ([integrator] if integrator else [])
+        args = ["render", self.scene_path, out, threads] + ([integrator] if integrator else (["-"] if repeat > 1 else []))
+        if repeat > 1:
+            args.append(repeat)
         e = dict(os.environ)
         if env:
             e.update(env)
