@@ -479,6 +479,7 @@ typedef struct mtsgpu_accel_info {
 	uint32_t buildLevels;  /* levels of the binary SAH build (or PLOC rounds) */
 	uint32_t reserved;
 } mtsgpu_accel_info;
+/* reads them back: what the reference prints as kd-tree statistics (include/mitsuba/render/gkdtree.h:1178-1214) */
 MTSGPU_API int mtsgpu_accel_info_get(mtsgpu_ctx *ctx, mtsgpu_accel_info *info);
 
 /* Per-ray traversal work (node visits, triangle tests) of the last mtsgpu_trace* call made with counters

@@ -382,10 +382,11 @@ class Context:
         c2w = np.ascontiguousarray(scene.camera_to_world, np.float32)
         if scene.orthographic:
             self._check(self.lib.mtsgpu_set_camera_orthographic(self.h, self._ptr(r2c), self._ptr(c2w), scene.near_clip,
-                                                                scene.far_clip, 0.0, 0.0))
+                                                                scene.far_clip, scene.shutter_open, max(scene.shutter_close - scene.shutter_open, 0.0)))
             return
         self._check(self.lib.mtsgpu_set_camera(self.h, self._ptr(r2c), self._ptr(c2w), scene.near_clip, scene.far_clip,
-                                               scene.aperture_radius, scene.focus_depth, 0.0, 0.0))
+                                               scene.aperture_radius, scene.focus_depth, scene.shutter_open,
+                                               max(scene.shutter_close - scene.shutter_open, 0.0)))
 
     def set_film(self, scene: SceneDesc, table=None, size=None):
         cx, cy, cw, ch = scene.crop_rect
@@ -411,7 +412,7 @@ class Context:
         p.strictNormals = int(scene.strict_normals)
         p.luminaireSamples = scene.luminaire_samples; p.bsdfSamples = scene.bsdf_samples
         p.sppTotal = scene.spp; p.sppBegin = spp_begin; p.sppEnd = scene.spp if spp_end is None else spp_end
-        p.seed = seed; p.importanceSampleLuminaires = 1
+        p.seed = seed; p.importanceSampleLuminaires = int(getattr(scene, "importance_sample_luminaires", True))
         p.samplerType = getattr(scene, "sampler_type", 0); p.samplerDepth = getattr(scene, "sampler_depth", 3)
         return p
 

@@ -10,6 +10,8 @@
 //   6. k_reorder        TriAccel records gathered into leaf order so a leaf is one contiguous run
 // Only hit results must agree with the reference's kd-tree, not the tree.
 #include "context.h"
+#define TRACE_STACK_FAST 20       // = TRACE_SMEM_STACK, TRACE_SMEM_STACK + TRACE_LOCAL_STACK of trace.cuh (checked there)
+#define TRACE_STACK_TOTAL 96
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 #include <algorithm>
@@ -1130,6 +1132,11 @@ int buildAccel(mtsgpu_ctx *ctx) {
 	ctx->accel.builder = useSah ? 2u : (usePloc ? 1u : 0u);
 	ctx->accel.buildLevels = (uint32_t) (useSah ? sahLevels : plocRounds);
 	sc.traceFlags = ctx->dTraceFlags.as<uint32_t>(); sc.oneBits = 0x3F800000u;
+	{
+		// MTSGPU_DEBUG_STACK_ENTRIES shrinks the traversal stacks so that tests can provoke the overflow report
+		const int total = getenv("MTSGPU_DEBUG_STACK_ENTRIES") ? std::max(atoi(getenv("MTSGPU_DEBUG_STACK_ENTRIES")), 1) : TRACE_STACK_TOTAL;
+		sc.stackTotal = std::min(total, (int) TRACE_STACK_TOTAL); sc.stackFast = std::min(sc.stackTotal, (int) TRACE_STACK_FAST);
+	}
 	ctx->accel.triBytes = (uint64_t) nTri * sizeof(TriAccelRec);
 	ctx->accel.buildMs = ms;
 	ctx->built = true;

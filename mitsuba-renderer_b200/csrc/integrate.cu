@@ -324,7 +324,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 					bool survive = true;
 					if ((int) depth >= ig.rrDepth && !(flags & PF_PREV_TRANS)) {
 						const float approxAlbedo = fminf(0.9f, maxc(bsdfVal));
-						const float rr = smp.get1D(DIM_BOUNCE(depth - 1, 2), depth - (uint32_t) ig.rrDepth);
+						const float rr = smp.get1D(DIM_BOUNCE(depth - 1, 2), smp.rouletteDraws);      // the path's k-th roulette draw is its k-th next1D() (after the time sample)
 						smp.rouletteDraws = min(smp.rouletteDraws + 1u, 255u);
 						flags = (flags & ~PF_RR_MASK) | (smp.rouletteDraws << PF_RR_SHIFT);
 						if (rr > approxAlbedo) survive = false;
@@ -336,7 +336,8 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 			} else if (MODE == 0 || round == 0) {
 				// camera hit: rRec.alpha (records.inl:93-99)
 				li4.w = valid ? 1.0f : 0.0f;
-				if (!valid && (flags & PF_EMITTED)) Li = Li + backgroundLe(sc, rayD);      // path.cpp:62-68 / direct.cpp:74-81
+				if (MODE == 0 && ig.maxDepth == 0) alive = false;      // path.cpp:60: `while (depth <= maxDepth || maxDepth < 0)` never runs: black
+				else if (!valid && (flags & PF_EMITTED)) Li = Li + backgroundLe(sc, rayD);      // path.cpp:62-68 / direct.cpp:74-81
 			}
 
 			// ---- top of the loop body at the new hit (path.cpp:58-95 / direct.cpp:74-100)
@@ -420,6 +421,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 				if (MODE == 0 && !cont) alive = false;
 			}
 			flags = (flags & ~PF_DEPTH_MASK) | (depth & PF_DEPTH_MASK);
+			if (smp.overflow) atomicOr(sc.traceFlags, 2u);      // halton.cpp:74-84: the reference stops with an error here
 			wf.li[slot] = make_float4(Li.x, Li.y, Li.z, li4.w);
 			if (emitRay) {
 				wf.thr[slot] = make_float4(thr.x, thr.y, thr.z, thr4.w);
@@ -572,6 +574,7 @@ static int makeSamplerConfig(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, Sam
 		REQUIRE(ctx, P->luminaireSamples == 1 && P->bsdfSamples == 1, MTSGPU_ERR_UNSUPPORTED, "request2DArray() is not supported by QMC samplers!");
 	cfg.type = P->samplerType; cfg.depth = P->samplerDepth; cfg.log2Count = 0; cfg.resolution = 1;
 	cfg.lensDraw = (ctx->haveCamera && ctx->camera.apertureRadius > 0.0f) ? 1u : 0u;
+	cfg.timeDraw = (ctx->haveCamera && ctx->camera.shutterOpenTime > 0.0f) ? 1u : 0u;      // Camera::needsTimeSample (camera.h:64)
 	if (cfg.type == MTSGPU_SAMPLER_HAMMERSLEY) {
 		REQUIRE(ctx, P->sppTotal > 0, MTSGPU_ERR_ARG, "render: hammersley needs the sample count");
 		cfg.resolution = P->sppTotal;                  // m_invSamplesPerPixel = 1 / sampleCount (hammersley.cpp:46-47)

@@ -1,6 +1,7 @@
 // Batch ray-query kernels behind mtsgpu_trace / mtsgpu_trace_device and the wavefront loop.
 #include "context.h"
 #include "trace.cuh"
+static_assert(TRACE_SMEM_STACK == 20 && TRACE_SMEM_STACK + TRACE_LOCAL_STACK == 96, "bvh_build.cu: TRACE_STACK_FAST / TRACE_STACK_TOTAL");
 #include <algorithm>
 #include <cstdlib>
 
@@ -95,6 +96,7 @@ int checkTraceFlags(mtsgpu_ctx *ctx) {
 		if (f) CUDA_TRY(ctx, cudaMemset(c->dTraceFlags.p, 0, sizeof(f)));
 		any |= f;
 	}
+	REQUIRE(ctx, !(any & 2u), MTSGPU_ERR_LIMIT, "Lookup depth exceeds the prime number table size! (halton / hammersley sampler: a path drew more than %d values)", 1000);
 	REQUIRE(ctx, !(any & 1u), MTSGPU_ERR_LIMIT, "traversal stack overflow: the acceleration structure is %u levels deep and a ray needed more than %d stack entries; "
 		"results of this call are incomplete", ctx->accel.depth, TRACE_SMEM_STACK + TRACE_LOCAL_STACK);
 	return MTSGPU_OK;

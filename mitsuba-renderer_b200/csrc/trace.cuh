@@ -182,7 +182,7 @@ __device__ __noinline__ bool traverseGroup(const DeviceScene &gs, const RayIn &r
 					pushed = make_uint2(next, __float_as_uint(nextT));
 					next = cw[i]; nextT = tn[i];
 				} else pushed = make_uint2(cw[i], __float_as_uint(tn[i]));
-				if (sp < GROUP_STACK) stack[sp++] = pushed; else atomicOr(gs.traceFlags, 1u);
+				if (sp < GROUP_STACK && sp < gs.stackTotal) stack[sp++] = pushed; else atomicOr(gs.traceFlags, 1u);
 			}
 			if (next != BVH_EMPTY) { cur = next; continue; }
 		} else {
@@ -357,7 +357,7 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 				CSWAP(0, 1) CSWAP(0, 2) CSWAP(0, 3)
 #undef CSWAP
 				const int h1 = tn[1] != INFINITY, h2 = tn[2] != INFINITY, h3 = tn[3] != INFINITY;
-				if (sp + 3 <= TRACE_SMEM_STACK) {       // common case: three predicated stores, no branches
+				if (sp + 3 <= sc.stackFast) {       // common case: three predicated stores, no branches
 					if (h1) stackStore(sbase, sp, make_uint2(cw[1], __float_as_uint(tn[1])));
 					if (h2) stackStore(sbase, sp + h1, make_uint2(cw[2], __float_as_uint(tn[2])));
 					if (h3) stackStore(sbase, sp + h1 + h2, make_uint2(cw[3], __float_as_uint(tn[3])));
@@ -367,9 +367,8 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 					for (int i = 1; i <= 3; ++i) {
 						if (tn[i] != INFINITY) {
 							const uint2 e = make_uint2(cw[i], __float_as_uint(tn[i]));
-							if (sp < TRACE_SMEM_STACK) stackStore(sbase, sp, e);
-							else if (sp < TRACE_SMEM_STACK + TRACE_LOCAL_STACK) lstack[sp - TRACE_SMEM_STACK] = e;
-							else { atomicOr(sc.traceFlags, 1u); continue; }       // stack full: reported by the host call (MTSGPU_ERR_LIMIT)
+							if (sp >= sc.stackTotal) { atomicOr(sc.traceFlags, 1u); continue; }       // stack full: reported by the host call (MTSGPU_ERR_LIMIT)
+							if (sp < TRACE_SMEM_STACK) stackStore(sbase, sp, e); else lstack[sp - TRACE_SMEM_STACK] = e;
 							sp++;
 						}
 					}
@@ -452,9 +451,8 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 	LaneState s;
 	s.active = false; s.sp = 0; s.cur = BVH_EMPTY; s.leaf = BVH_EMPTY; s.found = false;
 
-#define STACK_PUSH(e) do { if (s.sp < TRACE_SMEM_STACK) { stackStore(sbase, s.sp, (e)); s.sp++; } \
-		else if (s.sp < TRACE_SMEM_STACK + TRACE_LOCAL_STACK) { lstack[s.sp - TRACE_SMEM_STACK] = (e); s.sp++; } \
-		else atomicOr(sc.traceFlags, 1u); } while (0)          /* stack full: reported by the host call (MTSGPU_ERR_LIMIT) */
+#define STACK_PUSH(e) do { if (s.sp >= sc.stackTotal) atomicOr(sc.traceFlags, 1u);          /* stack full: reported by the host call (MTSGPU_ERR_LIMIT) */ \
+		else { if (s.sp < TRACE_SMEM_STACK) stackStore(sbase, s.sp, (e)); else lstack[s.sp - TRACE_SMEM_STACK] = (e); s.sp++; } } while (0)
 	// pop the next entry that can still matter; BVH_EMPTY when the stack is empty
 #define STACK_POP(dst) do { (dst) = BVH_EMPTY; while (s.sp > 0) { --s.sp; \
 		const uint2 e_ = (s.sp < TRACE_SMEM_STACK) ? stackLoad(sbase, s.sp) : lstack[s.sp - TRACE_SMEM_STACK]; \
@@ -536,7 +534,7 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 						// push the remaining hits. Common case: room in the shared-memory stack -> three predicated
 						// stores at computed slots, no branches
 						const int h1 = tn[1] != INFINITY, h2 = tn[2] != INFINITY, h3 = tn[3] != INFINITY;
-						if (s.sp + 3 <= TRACE_SMEM_STACK) {
+						if (s.sp + 3 <= sc.stackFast) {
 							if (h1) stackStore(sbase, s.sp, make_uint2(cw[1], __float_as_uint(tn[1])));
 							if (h2) stackStore(sbase, s.sp + h1, make_uint2(cw[2], __float_as_uint(tn[2])));
 							if (h3) stackStore(sbase, s.sp + h1 + h2, make_uint2(cw[3], __float_as_uint(tn[3])));

@@ -105,7 +105,8 @@ struct DeviceScene {
 	const struct DeviceScene *groups;        // the groups' own scenes: acceleration structure and shading records in object space
 	uint32_t hasInstances;
 	uint32_t oneBits;           // 0x3F800000: the node decode's PRMT takes it from the parameter bank (trace.cuh: qPlane)
-	uint32_t *traceFlags;       // bit 0: a traversal stack overflowed (the call that sees it fails with MTSGPU_ERR_LIMIT)
+	uint32_t *traceFlags;       // bit 0: a traversal stack overflowed (the call that sees it fails with MTSGPU_ERR_LIMIT); bit 1: sampling.cuh
+	int stackFast, stackTotal;  // traversal stack entries: shared-memory part, whole (TRACE_SMEM_STACK, + TRACE_LOCAL_STACK; tests shrink them)
 	const float *emitterXf;     // per emitter: luminaireToWorld 4x4, worldToLuminaire 4x4 (collimated beams)
 	const float *envData;       // environment map: worldToLuminaire 3x3, luminaireToWorld 3x3, density resolution, CDF, pdf (sampling.cuh)
 	const struct CameraDev *camera;   // the render's camera: ray differentials of a camera-ray hit are rebuilt from it

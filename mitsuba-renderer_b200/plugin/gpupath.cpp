@@ -684,7 +684,25 @@ private:
 		P.mode = m_mode; P.maxDepth = m_maxDepth; P.rrDepth = m_rrDepth; P.strictNormals = m_strictNormals ? 1 : 0;
 		P.luminaireSamples = m_luminaireSamples; P.bsdfSamples = m_bsdfSamples;
 		P.sppTotal = (uint32_t) sampler->getSampleCount(); P.sppBegin = 0; P.sppEnd = P.sppTotal;
-		P.seed = (uint32_t) m_seed; P.importanceSampleLuminaires = 1;
+		P.seed = (uint32_t) m_seed;
+		/* Scene property importanceSampleLuminaires (scene.cpp:51): it selects the luminaire CDF (scene.cpp:320-330) and the
+		   fraction in Scene::pdfLuminaire (scene.cpp:381-394). The member is private and has no getter; it only changes
+		   anything when the luminaires' sampling weights differ, and then Scene::toString() states it (scene.cpp:759). */
+		P.importanceSampleLuminaires = 1;
+		{
+			const std::vector<Luminaire *> &lums = scene->getLuminaires();
+			bool weightsDiffer = false;
+			for (size_t i = 1; i < lums.size(); ++i)
+				weightsDiffer |= lums[i]->getSamplingWeight() != lums[0]->getSamplingWeight();
+			if (weightsDiffer) {
+				const std::string desc = scene->toString();
+				const std::string key = "importanceSampleLuminaires = ";
+				const size_t pos = desc.find(key);
+				if (pos == std::string::npos || pos + key.size() >= desc.size())
+					Log(EError, "gpupath: cannot tell whether the scene importance-samples its luminaires");
+				P.importanceSampleLuminaires = desc[pos + key.size()] != '0' ? 1 : 0;
+			}
+		}
 		P.samplerType = MTSGPU_SAMPLER_INDEPENDENT; P.samplerDepth = 0;
 		{
 			const std::string samplerClass = sampler->getClass()->getName();

@@ -392,6 +392,9 @@ class SceneDesc:
     bsdf_samples: int = 1
     sampler_type: int = 0            # 0 independent, 1 ldsampler, 2 stratified, 3 halton (src/samplers/*.cpp)
     sampler_depth: int = 3           # ldsampler `depth`
+    shutter_open: float = 0.0        # Camera properties shutterOpen / shutterClose (camera.cpp:28-35): a non-empty interval
+    shutter_close: float = 0.0       #   makes renderBlock draw a time sample (integrator.cpp:159-160)
+    importance_sample_luminaires: bool = True     # Scene property (scene.cpp:51)
     materials: List[Material] = field(default_factory=list)
     emitters: List[Emitter] = field(default_factory=list)
     textures: List[Texture] = field(default_factory=list)
@@ -471,7 +474,7 @@ def write_scene(path: str, scene: SceneDesc) -> None:
     cx, cy, cw, ch = scene.crop_rect
     with open(path, "wb") as f:
         f.write(b"MTSB200\0")
-        f.write(struct.pack("<I", 10))
+        f.write(struct.pack("<I", 11))
         f.write(np.ascontiguousarray(scene.camera_to_world, np.float32).tobytes())
         f.write(struct.pack("<5fI", scene.fov, scene.near_clip, scene.far_clip, scene.aperture_radius,
                             scene.focus_depth, int(scene.map_smaller_side) | (2 if scene.orthographic else 0)))
@@ -479,6 +482,7 @@ def write_scene(path: str, scene: SceneDesc) -> None:
         f.write(struct.pack("<2I2i3I", scene.spp, scene.mode, scene.max_depth, scene.rr_depth,
                             int(scene.strict_normals), scene.luminaire_samples, scene.bsdf_samples))
         f.write(struct.pack("<2I", scene.sampler_type, scene.sampler_depth))
+        f.write(struct.pack("<2fI", scene.shutter_open, scene.shutter_close, int(scene.importance_sample_luminaires)))
         f.write(struct.pack("<I", len(scene.textures)))
         for k, t in enumerate(scene.textures):
             f.write(struct.pack("<I", t.type))

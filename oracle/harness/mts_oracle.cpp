@@ -296,7 +296,9 @@ static ref<BSDF> makeBSDF(const sio::Material &mIn) {
 static Built buildScene(const sio::Scene &s, const std::string &integratorOverride, bool withGeometry = true) {
 	Built out;
 	g_textures = &s.textures;
-	ref<Scene> scene = new Scene(Properties("scene"));
+	Properties sceneProps("scene");
+	sceneProps.setBoolean("importanceSampleLuminaires", s.importanceSampleLuminaires != 0);     /* scene.cpp:51 */
+	ref<Scene> scene = new Scene(sceneProps);
 
 	/* integrator */
 	{
@@ -353,6 +355,8 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 		cp.setFloat("farClip", s.farClip);
 		cp.setFloat("apertureRadius", s.apertureRadius);
 		cp.setFloat("focusDepth", s.focusDepth);
+		cp.setFloat("shutterOpen", s.shutterOpen);                 /* camera.cpp:28-35 */
+		cp.setFloat("shutterClose", s.shutterClose);
 		cp.setBoolean("mapSmallerSide", (s.mapSmallerSide & 1) != 0);
 		ref<Camera> camera = static_cast<Camera *>(create(MTS_CLASS(Camera), cp));
 		camera->addChild("", sampler);  sampler->setParent(camera);

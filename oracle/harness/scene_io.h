@@ -30,6 +30,7 @@ struct Scene {
 	uint32_t mapSmallerSide;
 	uint32_t width, height, cropX, cropY, cropW, cropH, filterType;
 	uint32_t spp, mode; int32_t maxDepth, rrDepth; uint32_t strictNormals, nLumSamples, nBsdfSamples;
+	float shutterOpen, shutterClose; uint32_t importanceSampleLuminaires;
 	uint32_t samplerType, samplerDepth;
 	std::vector<Texture> textures;
 	std::vector<Material> materials;
@@ -52,7 +53,7 @@ inline void load(const std::string &path, Scene &s) {
 	Reader r(path);
 	char magic[8]; r.raw(magic, 8);
 	if (memcmp(magic, "MTSB200", 8) != 0) throw std::runtime_error("bad magic in " + path);
-	if (r.get<uint32_t>() != 10) throw std::runtime_error("bad version in " + path);
+	if (r.get<uint32_t>() != 11) throw std::runtime_error("bad version in " + path);
 	r.raw(s.cameraToWorld, 64);
 	s.fov = r.get<float>(); s.nearClip = r.get<float>(); s.farClip = r.get<float>();
 	s.apertureRadius = r.get<float>(); s.focusDepth = r.get<float>();
@@ -65,6 +66,7 @@ inline void load(const std::string &path, Scene &s) {
 	s.maxDepth = r.get<int32_t>(); s.rrDepth = r.get<int32_t>();
 	s.strictNormals = r.get<uint32_t>(); s.nLumSamples = r.get<uint32_t>(); s.nBsdfSamples = r.get<uint32_t>();
 	s.samplerType = r.get<uint32_t>(); s.samplerDepth = r.get<uint32_t>();
+	s.shutterOpen = r.get<float>(); s.shutterClose = r.get<float>(); s.importanceSampleLuminaires = r.get<uint32_t>();
 	s.textures.resize(r.get<uint32_t>());
 	for (auto &t : s.textures) {
 		t.type = r.get<uint32_t>(); r.raw(t.p, 48);

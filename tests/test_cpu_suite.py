@@ -92,7 +92,7 @@ def test_scene_file_round_trip(tmp_path):
     scenefile.write_scene(path, s)
     raw = open(path, "rb").read()
     assert raw[:8] == b"MTSB200\0"
-    expect = 8 + 4 + 64 + 24 + 28 + 28 + 8 + 4 + len(s.textures) * 52 + 4 + len(s.materials) * 80 + 4 + len(s.emitters) * 128 + 4 + 4      # ... shape groups (count), shapes (count)
+    expect = 8 + 4 + 64 + 24 + 28 + 28 + 8 + 12 + 4 + len(s.textures) * 52 + 4 + len(s.materials) * 80 + 4 + len(s.emitters) * 128 + 4 + 4      # ... shape groups (count), shapes (count)
     for sh in s.shapes:
         expect += 28 + sh.positions.nbytes + (0 if sh.normals is None else sh.normals.nbytes) + sh.triangles.nbytes
         expect += 0 if sh.texcoords is None else sh.texcoords.nbytes

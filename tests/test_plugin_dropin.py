@@ -81,3 +81,23 @@ def test_plugin_with_the_halton_sampler_reproduces_the_cpu_image(oracle, make):
     err = np.abs(g - c).max(axis=-1) / (np.abs(c).max(axis=-1) + 1e-3)
     print(f"plugin vs cpu: within 2e-3: {(err < 2e-3).mean():.4f}, median {np.median(err):.2e}, means {c.mean():.6f} {g.mean():.6f}")
     assert (err < 2e-3).mean() > 0.999 and np.median(err) < 1e-6
+
+
+@pytest.mark.gpu
+def test_plugin_reads_the_scene_level_switches(oracle):
+    """importanceSampleLuminaires = false with unequal sampling weights (scene.cpp:51; the plugin infers it, the member
+    has no getter) and a shutter interval (the time sample of renderBlock): still the CPU image, pixel by pixel."""
+    need_plugin()
+    s = scenes.lights_test_scene(64, 64, 16, scenefile.MODE_PATH, max_depth=6)
+    s.rr_depth = 3
+    s.sampler_type = 3
+    s.importance_sample_luminaires = False
+    s.shutter_open, s.shutter_close = 0.0, 0.5
+    sess = oracle.Session(s)
+    gpu, info = sess.render(2, "gpupath", env={"MTS_PLUGIN_PATH": PLUGIN_DIR})
+    cpu, _ = sess.render()
+    assert info["integrator"] == "gpupath" and gpu[..., 4].sum() > 0
+    assert np.array_equal(gpu[..., 3:], cpu[..., 3:])
+    g, c = develop(gpu), develop(cpu)
+    err = np.abs(g - c).max(axis=-1) / (np.abs(c).max(axis=-1) + 1e-3)
+    assert (err < 2e-3).mean() > 0.999 and np.median(err) < 1e-6

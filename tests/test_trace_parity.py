@@ -174,3 +174,27 @@ def test_ploc_builder_gives_the_same_hits(monkeypatch):
         check_closest(ctx.trace(rays, TRACE_CLOSEST), g["hits"].view(api.HIT_DTYPE).reshape(-1), name + " (ploc)")
         assert np.array_equal(ctx.trace(scenes.shadow_segments(rays, scene), TRACE_ANY), g["any_segments"])
         ctx.close()
+
+
+def test_traversal_stack_overflow_is_reported(monkeypatch):
+    """A ray that needs more stack entries than there are must make the call fail (MTSGPU_ERR_LIMIT), not lose a subtree
+    silently. The real limit is 96 entries against at most 3 per level of the tree (accel_info: depth); the debug switch
+    shrinks it so that an ordinary scene overflows."""
+    from mitsuba_renderer_b200 import api
+    scene = scenes.microbench_scene(cells=120, pad_cells=9)
+    rays = scenes.incoherent_rays(scene, 20000, 3)
+    monkeypatch.setenv("MTSGPU_DEBUG_STACK_ENTRIES", "2")
+    ctx = api.Context(0)
+    ctx.upload_scene(scene)
+    with pytest.raises(api.MtsGpuError, match="stack overflow"):
+        ctx.trace(rays)
+    with pytest.raises(api.MtsGpuError, match="stack overflow"):
+        ctx.trace(scenes.shadow_segments(rays, scene), TRACE_ANY)
+    ctx.close()
+    monkeypatch.delenv("MTSGPU_DEBUG_STACK_ENTRIES")
+    ctx = api.Context(0)
+    ctx.upload_scene(scene)
+    info = ctx.accel_info()
+    assert 3 * info["depth"] <= 96
+    assert (ctx.trace(rays)["shape"] != 0xFFFFFFFF).any()
+    ctx.close()

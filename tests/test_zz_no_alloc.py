@@ -71,3 +71,25 @@ def test_static_splat_rejects_oversized_requests():
         assert ctx.film_splat_static(make_samples(small, 1000, 2))[..., 4].sum() > 0     # still usable afterwards
     finally:
         ctx.close()
+
+
+@pytest.mark.parametrize("name", ["box", "gaussian_crop", "mitchell"])
+def test_static_splat_matches_the_references_image_block(name):
+    """The same entry point against the reference itself: the committed golden films of ImageBlock::putSample
+    (tests/golden/splat_*.npz, made from the compiled reference by tests/golden/make_golden.py), same bound as the
+    allocating splat's golden test. Two calls in a row on the same context."""
+    import os
+    from tests import golden_cases as gc
+    ft, crop = gc.SPLAT_CASES[name]
+    ss = gc.splat_scene(ft, crop)
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "splat_" + name + ".npz"))
+    q = gc.splat_samples(ss, 8000)
+    assert gc.digest(q) == str(g["samples_digest"])
+    ctx = api.Context(0)
+    try:
+        ctx.set_film(ss, g["table"], float(g["filter_size"]))
+        for _ in range(2):
+            film = ctx.film_splat_static(q)
+            assert np.abs(film - g["film"]).max() <= TOL * max(1.0, np.abs(g["film"]).max())
+    finally:
+        ctx.close()
