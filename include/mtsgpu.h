@@ -225,7 +225,7 @@ MTSGPU_API int mtsgpu_upload_materials(mtsgpu_ctx *ctx, const mtsgpu_material *m
 /* Textures referenced by mtsgpu_material.texture (Texture2D::getValue, src/librender/texture.cpp:73-82). */
 MTSGPU_API int mtsgpu_upload_textures(mtsgpu_ctx *ctx, const mtsgpu_texture *textures, int count);
 /* Pixels of BITMAP texture `textureIndex` (after mtsgpu_upload_textures, before mtsgpu_build_accel), top row first.
- * MTSGPU_BITMAP_U8: `channels` (1, 3 or 4) bytes per pixel as Bitmap::getData() holds them; they are linearised with
+ * MTSGPU_BITMAP_U8: `channels` (1, 2, 3 or 4; one and two take the first as grey) bytes per pixel as Bitmap::getData() holds them; they are linearised with
  * the table of LDRTexture::initializeFrom (src/textures/ldrtexture.cpp:124-207): gamma == -1 selects the sRGB curve,
  * any other value is the exponent. MTSGPU_BITMAP_F32: `channels` (3 or 4) linear floats per pixel, as EXRTexture hands
  * them to MIPMap::fromBitmap (src/textures/exrtexture.cpp:52-60); gamma is ignored. The library builds the pyramid of

@@ -44,7 +44,12 @@ int mtsgpu_create(int device, mtsgpu_ctx **out) {
 	if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
 		g_createError = cudaGetErrorString(e); delete ctx; return MTSGPU_ERR_CUDA;
 	}
-	for (int i = 0; i < 8; ++i) cudaEventCreate(&ctx->ev[i]);
+	for (int i = 0; i < 8; ++i)
+		if ((e = cudaEventCreate(&ctx->ev[i])) != cudaSuccess) {
+			g_createError = std::string("cudaEventCreate: ") + cudaGetErrorString(e);
+			for (int k = 0; k < i; ++k) cudaEventDestroy(ctx->ev[k]);
+			cudaStreamDestroy(ctx->stream); delete ctx; return MTSGPU_ERR_CUDA;
+		}
 	*out = ctx;
 	return MTSGPU_OK;
 }
@@ -85,6 +90,7 @@ int mtsgpu_upload_materials(mtsgpu_ctx *ctx, const mtsgpu_material *materials, i
 	}
 	ctx->materials.assign(materials, materials + count);
 	ctx->built = false;
+	for (mtsgpu_ctx *g : ctx->groups) g->built = false;      // groups share these tables: rebuild (and re-validate) them too
 	return MTSGPU_OK;
 }
 
@@ -103,6 +109,7 @@ int mtsgpu_upload_textures(mtsgpu_ctx *ctx, const mtsgpu_texture *textures, int 
 	ctx->textures.assign(textures, textures + count);
 	ctx->bitmaps.assign(count, HostBitmap());
 	ctx->built = false;
+	for (mtsgpu_ctx *g : ctx->groups) g->built = false;      // groups share these tables: rebuild (and re-validate) them too
 	return MTSGPU_OK;
 }
 
@@ -134,6 +141,7 @@ int mtsgpu_upload_bitmap(mtsgpu_ctx *ctx, int textureIndex, int width, int heigh
 	}
 	b.width = width; b.height = height;
 	ctx->built = false;
+	for (mtsgpu_ctx *g : ctx->groups) g->built = false;
 	return MTSGPU_OK;
 }
 

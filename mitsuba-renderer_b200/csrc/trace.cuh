@@ -135,6 +135,9 @@ __device__ __forceinline__ float entryOrInf(float tnear, float tfar, uint32_t ch
 		: "=f"(r) : "f"(tnear), "f"(tfar), "r"(child));
 	return r;
 }
+// The planes' t values carry the rounding of o / d (about 2^-22 |o / d| in all): for origins within a few scene extents that
+// is far inside the boxes' pad, but not for a distant camera. Each axis is therefore widened by 2^-21 |o / d| (two FADDs
+// per axis and node), so the box test stays conservative wherever the ray starts.
 __device__ __forceinline__ void nodeTest(const float4 *nodes, uint32_t one, uint32_t node, float idx, float idy, float idz, float oix, float oiy, float oiz,
 		float mint, float maxt, float (&tn)[4], uint32_t (&cw)[4]) {
 	const char *np = reinterpret_cast<const char *>(nodes) + (size_t) node * 64;
@@ -142,13 +145,15 @@ __device__ __forceinline__ void nodeTest(const float4 *nodes, uint32_t one, uint
 	ldg256(np, a); ldg256(np + 32, b);
 	const float Sx = idx * __uint_as_float(a[3]), Sy = idy * __uint_as_float(b[6]), Sz = idz * __uint_as_float(b[7]);
 	const float Cx = fmaf(__uint_as_float(a[0]), idx, -oix) - Sx, Cy = fmaf(__uint_as_float(a[1]), idy, -oiy) - Sy, Cz = fmaf(__uint_as_float(a[2]), idz, -oiz) - Sz;
+	const float ex = fabsf(oix) * 4.76837158e-7f, ey = fabsf(oiy) * 4.76837158e-7f, ez = fabsf(oiz) * 4.76837158e-7f;      // 2^-21 |o / d|
+	const float CxN = Cx - ex, CxF = Cx + ex, CyN = Cy - ey, CyF = Cy + ey, CzN = Cz - ez, CzF = Cz + ez;
 	const bool nx = idx < 0.0f, ny = idy < 0.0f, nz = idz < 0.0f;
 	const uint32_t nearX = nx ? b[3] : b[0], farX = nx ? b[0] : b[3];
 	const uint32_t nearY = ny ? b[4] : b[1], farY = ny ? b[1] : b[4];
 	const uint32_t nearZ = nz ? b[5] : b[2], farZ = nz ? b[2] : b[5];
 #define NODE_CHILD(I) { \
-		const float tnear = fmaxf(fmaxf(fmaxf(qPlane<I>(nearX, one, Sx, Cx), qPlane<I>(nearY, one, Sy, Cy)), qPlane<I>(nearZ, one, Sz, Cz)), mint); \
-		const float tfar = fminf(fminf(fminf(qPlane<I>(farX, one, Sx, Cx), qPlane<I>(farY, one, Sy, Cy)), qPlane<I>(farZ, one, Sz, Cz)), maxt); \
+		const float tnear = fmaxf(fmaxf(fmaxf(qPlane<I>(nearX, one, Sx, CxN), qPlane<I>(nearY, one, Sy, CyN)), qPlane<I>(nearZ, one, Sz, CzN)), mint); \
+		const float tfar = fminf(fminf(fminf(qPlane<I>(farX, one, Sx, CxF), qPlane<I>(farY, one, Sy, CyF)), qPlane<I>(farZ, one, Sz, CzF)), maxt); \
 		cw[I] = a[4 + I]; tn[I] = entryOrInf(tnear, tfar, a[4 + I]); }
 	NODE_CHILD(0) NODE_CHILD(1) NODE_CHILD(2) NODE_CHILD(3)
 #undef NODE_CHILD

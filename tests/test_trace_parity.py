@@ -198,3 +198,29 @@ def test_traversal_stack_overflow_is_reported(monkeypatch):
     assert 3 * info["depth"] <= 96
     assert (ctx.trace(rays)["shape"] != 0xFFFFFFFF).any()
     ctx.close()
+
+
+def test_rays_from_far_outside_the_scene(oracle, gpu_ctx_factory):
+    """Origins hundreds of scene extents away (a distant camera): the box test's rounding grows with |o / d|, and the
+    traversal widens its slabs accordingly (trace.cuh: nodeTest). Every hit the kd-tree reports must be reported identically;
+    where the two differ at all the GPU's hit is the nearer one (the kd-tree's own split-plane arithmetic loses a few
+    hits at that distance)."""
+    scene = scenes.microbench_scene(cells=200, pad_cells=11)
+    ctx = gpu_ctx_factory(scene)
+    sess = oracle.Session(scene)
+    lo, hi = scenes.scene_bounds(scene)
+    base = scenes.incoherent_rays(scene, 200000, 9)
+    for factor in (50.0, 400.0):
+        rays = base.copy()
+        rays[:, 0:3] -= rays[:, 4:7] * np.float32(factor * np.linalg.norm(hi - lo))
+        rays[:, 3] = 0.0
+        ref, _ = sess.trace(rays, "closest")
+        gpu = ctx.trace(rays)
+        rhit, ghit = ref["shape"] != 0xFFFFFFFF, gpu["shape"] != 0xFFFFFFFF
+        same = (gpu["shape"] == ref["shape"]) & (gpu["prim"] == ref["prim"])
+        assert np.array_equal(gpu["t"][same & rhit].view(np.uint32), ref["t"][same & rhit].view(np.uint32))
+        differ = ~same
+        assert differ.mean() < 2e-3, differ.mean()
+        assert not (rhit & ~ghit).any(), "a hit of the reference is missing"
+        assert (gpu["t"][differ & ghit] <= ref["t"][differ & ghit]).all()
+        print(f"origins {factor} extents away: {rhit.sum()} reference hits, {int(differ.sum())} differ (GPU nearer or reference missed)")
