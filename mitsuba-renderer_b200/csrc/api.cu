@@ -67,6 +67,8 @@ void mtsgpu_destroy(mtsgpu_ctx *ctx) {
 	}
 	cudaStreamDestroy(ctx->stream);
 	if (ctx->hCounts) cudaFreeHost(ctx->hCounts);
+	for (int i = 0; i < 16; ++i) if (ctx->pollEv[i]) cudaEventDestroy(ctx->pollEv[i]);
+	for (int k = 0; k < 2; ++k) for (cudaEvent_t e : ctx->evPool[k]) cudaEventDestroy(e);
 	delete ctx;
 }
 

@@ -90,7 +90,10 @@ struct mtsgpu_ctx {
 	DevBuf dPathState, dRayA, dRayB, dHit, dShadowRay, dShadowPayload, dQueueA, dQueueB, dQueueCounts,
 	       dResult, dFilm, dStage, dStageOut;
 	DevBuf dPrimSlot, dPrimRay, dPrimHit, dFilterTable;
-	uint32_t *hCounts = nullptr;     // pinned host mirror of the queue counters
+	uint32_t *hCounts = nullptr;     // pinned host ring of polled queue lengths
+	cudaEvent_t pollEv[16] = {};     // one per ring slot
+	std::vector<cudaEvent_t> evPool[2];      // timing events of the traversal launches, two alternating sets
+	DevBuf dWfStats;
 	uint32_t pathCapacity = 0;
 };
 

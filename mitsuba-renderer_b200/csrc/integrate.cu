@@ -27,6 +27,9 @@
 #define TILE 16
 #define TILE_PIX (TILE * TILE)
 #define WF_BLOCK 128
+#define WF_POLL_RING 16           // pinned slots / events of the asynchronous queue-length polls
+#define WF_POLL_AHEAD 6           // bounces the host may enqueue beyond the last poll it has seen
+#define SHADE_CHUNK 512           // queue entries a shading block lists before it shades the ones that need it
 
 // path-state flag word
 #define PF_DEPTH_MASK   0x0000FFFFu
@@ -136,40 +139,42 @@ k_generate(const CameraDev cam, const FilmDev film, const BatchDesc b, WfArrays 
 // override the choice for experiments.
 template <bool SPH>
 __global__ void __launch_bounds__(TRACE_BLOCK)
-k_closest_wf(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint4 *__restrict__ hits, uint32_t *__restrict__ nestedOut) {
+k_closest_wf(const DeviceScene sc, const float4 *__restrict__ rays, const uint32_t *__restrict__ nPtr, uint4 *__restrict__ hits, uint32_t *__restrict__ nestedOut) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
-	const uint32_t i = blockIdx.x * TRACE_BLOCK + threadIdx.x;
-	if (i >= n) return;
-	const float4 a = __ldg(rays + 2 * (size_t) i), b = __ldg(rays + 2 * (size_t) i + 1);
-	RayIn r = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
-	HitOut ho; ho.t = INFINITY; ho.u = ho.v = 0; ho.tri = 0xFFFFFFFFu; ho.nested = 0xFFFFFFFFu;
-	float mint, maxt; uint32_t c0 = 0, c1 = 0;
-	if (clipToScene<false>(sc, r, mint, maxt))
-		traverse<false, false, SPH>(sc, r, mint, maxt, sstack, ho, c0, c1);
-	hits[i] = make_uint4(__float_as_uint(ho.t), __float_as_uint(ho.u), __float_as_uint(ho.v), ho.tri);
-	if (SPH && nestedOut) nestedOut[i] = ho.nested;
+	const uint32_t n = *nPtr;                  // the queue length lives on the device: no host round trip between bounces
+	for (uint32_t i = blockIdx.x * TRACE_BLOCK + threadIdx.x; i < n; i += gridDim.x * TRACE_BLOCK) {
+		const float4 a = __ldg(rays + 2 * (size_t) i), b = __ldg(rays + 2 * (size_t) i + 1);
+		RayIn r = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+		HitOut ho; ho.t = INFINITY; ho.u = ho.v = 0; ho.tri = 0xFFFFFFFFu; ho.nested = 0xFFFFFFFFu;
+		float mint, maxt; uint32_t c0 = 0, c1 = 0;
+		if (clipToScene<false>(sc, r, mint, maxt))
+			traverse<false, false, SPH>(sc, r, mint, maxt, sstack, ho, c0, c1);
+		hits[i] = make_uint4(__float_as_uint(ho.t), __float_as_uint(ho.u), __float_as_uint(ho.v), ho.tri);
+		if (SPH && nestedOut) nestedOut[i] = ho.nested;
+	}
 }
 
 template <bool SPH>
 __global__ void __launch_bounds__(TRACE_BLOCK)
-k_shadow_wf(const DeviceScene sc, const float4 *__restrict__ rays, const float4 *__restrict__ payload, uint32_t n, float4 *li) {
+k_shadow_wf(const DeviceScene sc, const float4 *__restrict__ rays, const float4 *__restrict__ payload, const uint32_t *__restrict__ nPtr, float4 *li) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
-	const uint32_t i = blockIdx.x * TRACE_BLOCK + threadIdx.x;
-	if (i >= n) return;
-	const float4 a = __ldg(rays + 2 * (size_t) i), b = __ldg(rays + 2 * (size_t) i + 1);
-	RayIn r = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
-	float mint, maxt; uint32_t c0 = 0, c1 = 0;
-	bool occluded = false;
-	if (clipToScene<true>(sc, r, mint, maxt)) {
-		HitOut ho;
-		occluded = traverse<true, false, SPH>(sc, r, mint, maxt, sstack, ho, c0, c1);
-	}
-	if (!occluded) {
-		const float4 p = __ldg(payload + i);
-		const uint32_t slot = __float_as_uint(p.w);
-		float4 l = li[slot];                 // one shadow ray per slot and pass: plain read-modify-write
-		l.x += p.x; l.y += p.y; l.z += p.z;
-		li[slot] = l;
+	const uint32_t n = *nPtr;
+	for (uint32_t i = blockIdx.x * TRACE_BLOCK + threadIdx.x; i < n; i += gridDim.x * TRACE_BLOCK) {
+		const float4 a = __ldg(rays + 2 * (size_t) i), b = __ldg(rays + 2 * (size_t) i + 1);
+		RayIn r = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+		float mint, maxt; uint32_t c0 = 0, c1 = 0;
+		bool occluded = false;
+		if (clipToScene<true>(sc, r, mint, maxt)) {
+			HitOut ho;
+			occluded = traverse<true, false, SPH>(sc, r, mint, maxt, sstack, ho, c0, c1);
+		}
+		if (!occluded) {
+			const float4 p = __ldg(payload + i);
+			const uint32_t slot = __float_as_uint(p.w);
+			float4 l = li[slot];                 // one shadow ray per slot and pass: plain read-modify-write
+			l.x += p.x; l.y += p.y; l.z += p.z;
+			li[slot] = l;
+		}
 	}
 }
 
@@ -197,20 +202,22 @@ struct WfShadowSink {
 // `counters` — a separate instantiation, so the timed kernels carry no counter code.
 template <bool SPH, bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
-k_closest_wfp(const DeviceScene sc, const float4 *__restrict__ rays, uint32_t n, uint4 *__restrict__ hits, uint32_t *rayCounter, int refetchBelow, int leafThreshold,
+k_closest_wfp(const DeviceScene sc, const float4 *__restrict__ rays, const uint32_t *__restrict__ nPtr, uint4 *__restrict__ hits, uint32_t *rayCounter, int refetchBelow, int leafThreshold,
 		unsigned long long *counters) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
 	uint32_t c0 = 0, c1 = 0;
+	const uint32_t n = *nPtr;
 	WfHitSink sink = { hits };
 	tracePersistent<false, COUNT, WfHitSink, SPH>(sc, rays, n, rayCounter, sink, sstack, c0, c1, refetchBelow, true, leafThreshold);
 	if (COUNT) flushCounters(c0, c1, counters);
 }
 template <bool SPH, bool COUNT>
 __global__ void __launch_bounds__(TRACE_BLOCK, TRACE_PERSISTENT_BLOCKS_PER_SM)
-k_shadow_wfp(const DeviceScene sc, const float4 *__restrict__ rays, const float4 *__restrict__ payload, uint32_t n, float4 *li, uint32_t *rayCounter, int refetchBelow, int leafThreshold,
+k_shadow_wfp(const DeviceScene sc, const float4 *__restrict__ rays, const float4 *__restrict__ payload, const uint32_t *__restrict__ nPtr, float4 *li, uint32_t *rayCounter, int refetchBelow, int leafThreshold,
 		unsigned long long *counters) {
 	__shared__ uint2 sstack[TRACE_SMEM_STACK * TRACE_BLOCK];
 	uint32_t c0 = 0, c1 = 0;
+	const uint32_t n = *nPtr;
 	WfShadowSink sink = { payload, li };
 	tracePersistent<true, COUNT, WfShadowSink, SPH>(sc, rays, n, rayCounter, sink, sstack, c0, c1, refetchBelow, true, leafThreshold);
 	if (COUNT) flushCounters(c0, c1, counters);
@@ -254,16 +261,50 @@ template <int MODE, bool BMP>
 #define SHADE_MIN_BLOCKS 6
 #endif
 __global__ void __launch_bounds__(WF_BLOCK, SHADE_MIN_BLOCKS)      // 6: <= 80 registers, measured 9 % faster than the uncapped 122
-k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const FilmDev film, WfArrays wf, uint32_t n, uint32_t round) {
-	const uint32_t i = blockIdx.x * WF_BLOCK + threadIdx.x;
+k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const FilmDev film, WfArrays wf, const uint32_t *__restrict__ nIn, uint32_t round) {
+	// The queue length is read on the device (no host round trip per bounce), and a block works through chunks of
+	// SHADE_CHUNK queue entries: it first lists the entries that need shading at all — from the second bounce on more than
+	// half of the rays have left the scene, and a miss without a background luminaire changes nothing (ncu, r02_shade_base:
+	// 9.9 of 32 lanes active on the bounce-2 queue) — then shades the listed ones with full warps. The list keeps the queue order.
+	__shared__ uint32_t sList[SHADE_CHUNK];
+	__shared__ uint32_t sCount[SHADE_CHUNK / 32];
+	const uint32_t n = *nIn;
+	const uint32_t *slots = (MODE == 1) ? wf.slotPrim : wf.slotCur;
+	const float4 *rays = (MODE == 1) ? wf.rayPrim : wf.rayCur;
+	const uint4 *hits = (MODE == 1) ? wf.hitPrim : wf.hit;
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	for (uint32_t chunk0 = blockIdx.x * SHADE_CHUNK; chunk0 < n; chunk0 += gridDim.x * SHADE_CHUNK) {
+	uint32_t needMask[SHADE_CHUNK / WF_BLOCK];
+#pragma unroll
+	for (int k = 0; k < SHADE_CHUNK / WF_BLOCK; ++k) {
+		const uint32_t idx = chunk0 + k * WF_BLOCK + threadIdx.x;
+		const bool need = idx < n && (sc.background >= 0 || __ldg(&hits[idx].w) != 0xFFFFFFFFu);
+		needMask[k] = __ballot_sync(0xFFFFFFFFu, need);
+		if (lane == 0) sCount[k * (WF_BLOCK / 32) + warp] = __popc(needMask[k]);
+	}
+	__syncthreads();
+	uint32_t listed = 0;
+	{
+		uint32_t run = 0;
+#pragma unroll
+		for (int c = 0; c < SHADE_CHUNK / 32; ++c) {
+			const uint32_t cnt = sCount[c];
+			const int k = c / (WF_BLOCK / 32);
+			if ((uint32_t) (c % (WF_BLOCK / 32)) == warp && ((needMask[k] >> lane) & 1u))
+				sList[run + __popc(needMask[k] & ((1u << lane) - 1u))] = chunk0 + k * WF_BLOCK + threadIdx.x;
+			run += cnt;
+		}
+		listed = run;
+	}
+	__syncthreads();
+	for (uint32_t j0 = 0; j0 < listed; j0 += WF_BLOCK) {
+	const bool entry = j0 + threadIdx.x < listed;
+	const uint32_t i = entry ? sList[j0 + threadIdx.x] : 0u;
 	bool emitRay = false, emitShadow = false;
 	float4 nr0, nr1, sr0, sr1; V3 contrib = v3(0, 0, 0);
 	uint32_t slot = 0;
 
-	if (i < n) {
-		const uint32_t *slots = (MODE == 1) ? wf.slotPrim : wf.slotCur;
-		const float4 *rays = (MODE == 1) ? wf.rayPrim : wf.rayCur;
-		const uint4 *hits = (MODE == 1) ? wf.hitPrim : wf.hit;
+	if (entry) {
 		slot = slots[i];
 		const float4 ra = rays[2 * (size_t) i], rb = rays[2 * (size_t) i + 1];
 		const uint4 h = hits[i];
@@ -430,18 +471,35 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		}
 	}
 
-	const uint32_t rp = warpAppend(&wf.counters[0], emitRay);
+	const uint32_t rp = warpAppend(&wf.counters[1], emitRay);
 	if (emitRay) {
 		wf.slotNext[rp] = slot;
 		wf.rayNext[2 * (size_t) rp] = nr0;
 		wf.rayNext[2 * (size_t) rp + 1] = nr1;
 	}
-	const uint32_t sp = warpAppend(&wf.counters[1], emitShadow);
+	const uint32_t sp = warpAppend(&wf.counters[2], emitShadow);
 	if (emitShadow) {
 		wf.shadowRay[2 * (size_t) sp] = sr0;
 		wf.shadowRay[2 * (size_t) sp + 1] = sr1;
 		wf.shadowPayload[sp] = make_float4(contrib.x, contrib.y, contrib.z, __uint_as_float(slot));
 	}
+	}      // listed entries
+	__syncthreads();      // sList is rewritten by the next chunk
+	}      // chunks
+}
+
+// End of a bounce: add the queue lengths to the statistics, make the next ray queue the current one, empty the others.
+// counters: [0] current ray queue, [1] next ray queue, [2] shadow queue; stats: [0] camera rays, [1] closest-hit queries, [2] shadow queries
+__global__ void k_advance(uint32_t *counters, unsigned long long *stats, int what) {
+	if (what == 0) { stats[0] += counters[0]; return; }                     // after k_generate
+	if (what == 1) {                                                        // path: one bounce done
+		stats[1] += counters[0]; stats[2] += counters[2];
+		counters[0] = counters[1]; counters[1] = 0; counters[2] = 0;
+		return;
+	}
+	if (what == 2) { stats[1] += counters[0]; return; }                     // direct: primary hits traced
+	stats[1] += counters[1]; stats[2] += counters[2];                       // direct: one round done (the primary queue stays)
+	counters[1] = 0; counters[2] = 0;
 }
 
 // ImageBlock::putSample (imageblock.h:80-138) for all samples of one tile, accumulated in shared
@@ -511,40 +569,45 @@ inline unsigned blocksFor(size_t n, unsigned bs) { return (unsigned) ((n + bs - 
 
 } // namespace
 
-// Launch helpers: pick the traversal kernel variant per queue.
-static int launchClosestWf(mtsgpu_ctx *ctx, const float4 *rays, uint32_t n, uint4 *hits, bool persistent) {
+// Launch helpers: pick the traversal kernel variant per queue. `nPtr`: the queue's length in device memory (the host does not
+// know it); grids are one resident wave, the kernels loop or pull work until the queue is empty.
+static unsigned fullGrid(mtsgpu_ctx *ctx, unsigned perSM) {
+	(void) tracePersistentBlocks(ctx, 1);          // fills ctx->smCount
+	return (unsigned) ctx->smCount * perSM;
+}
+static int launchClosestWf(mtsgpu_ctx *ctx, const float4 *rays, const uint32_t *nPtr, uint4 *hits, bool persistent) {
 	if (ctx->scene.hasInstances) {     // instance hits also report the nested triangle: the lock-step kernel writes it behind the hits
-		k_closest_wf<true><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, reinterpret_cast<uint32_t *>(hits + ctx->pathCapacity));
+		k_closest_wf<true><<<fullGrid(ctx, 16), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, nPtr, hits, reinterpret_cast<uint32_t *>(hits + ctx->pathCapacity));
 		return MTSGPU_OK;
 	}
 	if (persistent) {
 		uint32_t *rc = nullptr; int e = traceRayCounter(ctx, &rc); if (e) return e;
-		const unsigned blocks = tracePersistentBlocks(ctx, n);
+		const unsigned blocks = fullGrid(ctx, TRACE_PERSISTENT_BLOCKS_PER_SM);
 		const int rb = traceRefetchBelow(), lt = traceLeafThreshold();
 		unsigned long long *cnt = ctx->countersEnabled ? ctx->dCounters.as<unsigned long long>() + 2 : nullptr;     // [2..3]: closest-hit queues of a render
-#define WFP(S, C) k_closest_wfp<S, C><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, rc, rb, lt, cnt)
+#define WFP(S, C) k_closest_wfp<S, C><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, nPtr, hits, rc, rb, lt, cnt)
 		if (ctx->scene.hasSpheres) { if (cnt) WFP(true, true); else WFP(true, false); }
 		else { if (cnt) WFP(false, true); else WFP(false, false); }
 #undef WFP
 	} else {
-		if (ctx->scene.hasSpheres) k_closest_wf<true><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, nullptr);
-		else k_closest_wf<false><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, n, hits, nullptr);
+		if (ctx->scene.hasSpheres) k_closest_wf<true><<<fullGrid(ctx, 16), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, nPtr, hits, nullptr);
+		else k_closest_wf<false><<<fullGrid(ctx, 16), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, nPtr, hits, nullptr);
 	}
 	return MTSGPU_OK;
 }
-static int launchShadowWf(mtsgpu_ctx *ctx, const float4 *rays, const float4 *payload, uint32_t n, float4 *li, bool persistent) {
+static int launchShadowWf(mtsgpu_ctx *ctx, const float4 *rays, const float4 *payload, const uint32_t *nPtr, float4 *li, bool persistent) {
 	if (persistent) {
 		uint32_t *rc = nullptr; int e = traceRayCounter(ctx, &rc); if (e) return e;
-		const unsigned blocks = tracePersistentBlocks(ctx, n);
+		const unsigned blocks = fullGrid(ctx, TRACE_PERSISTENT_BLOCKS_PER_SM);
 		const int rb = traceRefetchBelow(), lt = traceLeafThreshold();
 		unsigned long long *cnt = ctx->countersEnabled ? ctx->dCounters.as<unsigned long long>() + 4 : nullptr;     // [4..5]: shadow queues of a render
-#define WFP(S, C) k_shadow_wfp<S, C><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li, rc, rb, lt, cnt)
+#define WFP(S, C) k_shadow_wfp<S, C><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, nPtr, li, rc, rb, lt, cnt)
 		if (ctx->scene.hasSpheres) { if (cnt) WFP(true, true); else WFP(true, false); }
 		else { if (cnt) WFP(false, true); else WFP(false, false); }
 #undef WFP
 	} else {
-		if (ctx->scene.hasSpheres) k_shadow_wf<true><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li);
-		else k_shadow_wf<false><<<blocksFor(n, TRACE_BLOCK), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, n, li);
+		if (ctx->scene.hasSpheres) k_shadow_wf<true><<<fullGrid(ctx, 16), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, nPtr, li);
+		else k_shadow_wf<false><<<fullGrid(ctx, 16), TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, nPtr, li);
 	}
 	return MTSGPU_OK;
 }
@@ -671,15 +734,51 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 		if (P->mode == MTSGPU_MODE_DIRECT) ig.strictNormals = 0;     // MIDirectIntegrator has no such property
 		const int splatSmem = (TILE + 2 * film.border) * (TILE + 2 * film.border) * 5 * (int) sizeof(float);
 
-		if (!ctx->hCounts) CUDA_TRY(ctx, cudaMallocHost(&ctx->hCounts, 64));     // pinned, kept for the context's lifetime
-		uint32_t *hCounts = ctx->hCounts;
+		// ---- no host round trip inside a batch: queue lengths stay in device memory (counters[0] current ray queue, [1] next ray
+		// queue, [2] shadow queue; k_advance rotates them and keeps the statistics), every kernel reads its own length, and
+		// the host only learns — a few bounces late, through an asynchronous copy it polls — when a batch has run dry.
+		if (!ctx->hCounts) CUDA_TRY(ctx, cudaMallocHost(&ctx->hCounts, WF_POLL_RING * sizeof(uint32_t)));     // pinned, kept for the context's lifetime
+		volatile uint32_t *hRing = ctx->hCounts;
+		for (int i = 0; i < WF_POLL_RING; ++i)
+			if (!ctx->pollEv[i]) CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->pollEv[i], cudaEventDisableTiming));
+		CUDA_TRY(ctx, ctx->dWfStats.alloc(4 * sizeof(unsigned long long)));
+		CUDA_TRY(ctx, cudaMemsetAsync(ctx->dWfStats.p, 0, 4 * sizeof(unsigned long long), st));
+		unsigned long long *dStats = ctx->dWfStats.as<unsigned long long>();
 		int rc = MTSGPU_OK;
 		auto fail = [&](int code) { return code; };
 		float msClosest = 0, msShadow = 0;
+		// kernel-class timing: event pairs around the traversal launches, two sets used by alternate batches and read back
+		// one batch late (by then they have long completed)
+		std::vector<int> evKind[2]; size_t evUsed[2] = { 0, 0 };
+		auto stamp = [&](int set, int kind) -> cudaError_t {        // kind: 0 / 1 = before / after closest-hit, 2 / 3 = shadow
+			std::vector<cudaEvent_t> &pool = ctx->evPool[set];
+			if (evUsed[set] == pool.size()) { cudaEvent_t e; cudaError_t er = cudaEventCreate(&e); if (er != cudaSuccess) return er; pool.push_back(e); }
+			if (evKind[set].size() <= evUsed[set]) evKind[set].resize(evUsed[set] + 1);
+			evKind[set][evUsed[set]] = kind;
+			return cudaEventRecord(pool[evUsed[set]++], st);
+		};
+		auto harvest = [&](int set) -> cudaError_t {
+			if (evUsed[set] == 0) return cudaSuccess;
+			std::vector<cudaEvent_t> &pool = ctx->evPool[set];
+			cudaError_t er = cudaEventSynchronize(pool[evUsed[set] - 1]);
+			if (er != cudaSuccess) return er;
+			for (size_t i = 0; i + 1 < evUsed[set]; i += 2) {
+				float ms = 0; cudaEventElapsedTime(&ms, pool[i], pool[i + 1]);
+				if (evKind[set][i] == 0) msClosest += ms; else msShadow += ms;
+			}
+			evUsed[set] = 0;
+			return cudaSuccess;
+		};
+		const unsigned shadeGrid = fullGrid(ctx, SHADE_MIN_BLOCKS);
+#define LAUNCH_SHADE(M, NIN, ROUND) do { if (bmp) k_shade<M, true><<<shadeGrid, WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, (NIN), (ROUND)); \
+			else k_shade<M, false><<<shadeGrid, WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, (NIN), (ROUND)); S.kernelLaunches++; } while (0)
+		uint32_t batchIndex = 0;
 
 		for (uint32_t t0 = 0; t0 < nTiles && rc == MTSGPU_OK; t0 += tilesPerBatch) {
-			for (uint32_t s0 = 0; s0 < spp; s0 += sampleChunk) {
+			for (uint32_t s0 = 0; s0 < spp; s0 += sampleChunk, ++batchIndex) {
 				if (cancel && *cancel) { rc = setError(ctx, MTSGPU_ERR_CANCELLED, "render cancelled"); break; }
+				const int evSet = (int) (batchIndex & 1u);
+				CUDA_TRY(ctx, harvest(evSet));                   // the events of the batch before the previous one
 				BatchDesc b;
 				b.tileBegin = t0; b.tileCount = std::min(tilesPerBatch, nTiles - t0); b.tilesX = tilesX;
 				b.sampleBegin = P->sppBegin + s0; b.sampleCount = std::min(sampleChunk, spp - s0);
@@ -687,81 +786,66 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 				b.sampler = samplerConfig;
 				b.diffScale = 1.0f / std::sqrt((float) P->sppTotal);          // integrator.cpp:145
 				int cur = 0;
-				wf.slotNext = slotBuf[cur]; wf.rayNext = rayBuf[cur];
-				CUDA_TRY(ctx, cudaMemsetAsync(wf.counters, 0, 8, st));
+				const bool direct = P->mode == MTSGPU_MODE_DIRECT;
+				wf.slotNext = direct ? wf.slotPrim : slotBuf[cur]; wf.rayNext = direct ? wf.rayPrim : rayBuf[cur];
+				CUDA_TRY(ctx, cudaMemsetAsync(wf.counters, 0, 16, st));
 				k_generate<<<blocksFor(b.slots, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->camera, film, b, wf);
-				S.kernelLaunches++;
-				CUDA_TRY(ctx, cudaMemcpyAsync(hCounts, wf.counters, 8, cudaMemcpyDeviceToHost, st));
-				CUDA_TRY(ctx, cudaStreamSynchronize(st));
-				uint32_t nRays = hCounts[0];
-				S.cameraRays += nRays;
+				k_advance<<<1, 1, 0, st>>>(wf.counters, dStats, 0);
+				S.kernelLaunches += 2;
 
-				if (P->mode == MTSGPU_MODE_PATH) {
-					while (nRays > 0) {
+				if (!direct) {
+					// path.cpp:60-216: at most maxDepth closest-hit queries per path (the camera ray included); unbounded depth
+					// runs until the polled queue length reads zero
+					const int maxBounces = P->maxDepth > 0 ? P->maxDepth : (P->maxDepth == 0 ? 1 : -1);
+					uint32_t enq = 0, seen = 0; bool dry = false;
+					for (int bounce = 0; maxBounces < 0 || bounce < maxBounces; ++bounce) {
 						if (cancel && *cancel) { rc = setError(ctx, MTSGPU_ERR_CANCELLED, "render cancelled"); break; }
+						while (seen < enq) {                 // finished polls: never wait unless the host is WF_POLL_AHEAD bounces ahead
+							cudaEvent_t pe = ctx->pollEv[seen % WF_POLL_RING];
+							if (enq - seen >= WF_POLL_AHEAD) CUDA_TRY(ctx, cudaEventSynchronize(pe));
+							else if (cudaEventQuery(pe) != cudaSuccess) break;
+							if (hRing[seen % WF_POLL_RING] == 0) dry = true;
+							seen++;
+						}
+						if (dry) break;
 						wf.slotCur = slotBuf[cur]; wf.rayCur = rayBuf[cur];
 						wf.slotNext = slotBuf[cur ^ 1]; wf.rayNext = rayBuf[cur ^ 1];
-						cudaEventRecord(evA, st);
-						if (launchClosestWf(ctx, wf.rayCur, nRays, wf.hit, persistClosest)) return fail(MTSGPU_ERR_CUDA);
-						cudaEventRecord(evB, st);
-						S.normalRays += nRays;
-						CUDA_TRY(ctx, cudaMemsetAsync(wf.counters, 0, 8, st));
-						if (bmp) k_shade<0, true><<<blocksFor(nRays, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nRays, 0); else k_shade<0, false><<<blocksFor(nRays, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nRays, 0);
-						CUDA_TRY(ctx, cudaMemcpyAsync(hCounts, wf.counters, 8, cudaMemcpyDeviceToHost, st));
-						CUDA_TRY(ctx, cudaStreamSynchronize(st));
-						{ float ms = 0; cudaEventElapsedTime(&ms, evA, evB); msClosest += ms; }
-						S.kernelLaunches += 2;
-						const uint32_t nShadow = hCounts[1];
-						if (nShadow > 0) {
-							cudaEventRecord(evA, st);
-							if (launchShadowWf(ctx, wf.shadowRay, wf.shadowPayload, nShadow, wf.li, persistShadow)) return fail(MTSGPU_ERR_CUDA);
-							cudaEventRecord(evB, st);
-							CUDA_TRY(ctx, cudaEventSynchronize(evB));
-							{ float ms = 0; cudaEventElapsedTime(&ms, evA, evB); msShadow += ms; }
-							S.shadowRays += nShadow; S.kernelLaunches++;
-						}
-						nRays = hCounts[0];
+						CUDA_TRY(ctx, stamp(evSet, 0));
+						if (launchClosestWf(ctx, wf.rayCur, wf.counters, wf.hit, persistClosest)) return fail(MTSGPU_ERR_CUDA);
+						CUDA_TRY(ctx, stamp(evSet, 1));
+						LAUNCH_SHADE(0, wf.counters, 0u);
+						CUDA_TRY(ctx, stamp(evSet, 2));
+						if (launchShadowWf(ctx, wf.shadowRay, wf.shadowPayload, wf.counters + 2, wf.li, persistShadow)) return fail(MTSGPU_ERR_CUDA);
+						CUDA_TRY(ctx, stamp(evSet, 3));
+						k_advance<<<1, 1, 0, st>>>(wf.counters, dStats, 1);
+						S.kernelLaunches += 3;
+						CUDA_TRY(ctx, cudaMemcpyAsync((void *) (hRing + enq % WF_POLL_RING), wf.counters, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+						CUDA_TRY(ctx, cudaEventRecord(ctx->pollEv[enq % WF_POLL_RING], st));
+						enq++;
 						cur ^= 1;
 					}
 				} else {
-					// primary hit once, kept in the *Prim buffers; then `rounds` passes of (NEE, BSDF ray)
-					wf.slotCur = slotBuf[cur]; wf.rayCur = rayBuf[cur];
-					cudaEventRecord(evA, st);
-						if (launchClosestWf(ctx, wf.rayCur, nRays, wf.hitPrim, persistClosest)) return fail(MTSGPU_ERR_CUDA);
-					cudaEventRecord(evB, st);
-					CUDA_TRY(ctx, cudaMemcpyAsync(wf.slotPrim, wf.slotCur, (size_t) nRays * 4, cudaMemcpyDeviceToDevice, st));
-					CUDA_TRY(ctx, cudaMemcpyAsync(wf.rayPrim, wf.rayCur, (size_t) nRays * 32, cudaMemcpyDeviceToDevice, st));
-					CUDA_TRY(ctx, cudaEventSynchronize(evB));
-					{ float ms = 0; cudaEventElapsedTime(&ms, evA, evB); msClosest += ms; }
-					S.normalRays += nRays; S.kernelLaunches++;
-					const uint32_t nPrim = nRays;
+					// primary hit once, kept in the *Prim buffers (k_generate wrote them); then `rounds` passes of (NEE, BSDF ray)
+					CUDA_TRY(ctx, stamp(evSet, 0));
+					if (launchClosestWf(ctx, wf.rayPrim, wf.counters, wf.hitPrim, persistClosest)) return fail(MTSGPU_ERR_CUDA);
+					CUDA_TRY(ctx, stamp(evSet, 1));
+					k_advance<<<1, 1, 0, st>>>(wf.counters, dStats, 2);
+					S.kernelLaunches += 2;
 					const int rounds = std::max(P->luminaireSamples, P->bsdfSamples);
 					for (int r = 0; r < rounds; ++r) {
-						wf.slotNext = slotBuf[cur ^ 1]; wf.rayNext = rayBuf[cur ^ 1];
-						CUDA_TRY(ctx, cudaMemsetAsync(wf.counters, 0, 8, st));
-						if (bmp) k_shade<1, true><<<blocksFor(nPrim, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nPrim, (uint32_t) r); else k_shade<1, false><<<blocksFor(nPrim, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nPrim, (uint32_t) r);
-						CUDA_TRY(ctx, cudaMemcpyAsync(hCounts, wf.counters, 8, cudaMemcpyDeviceToHost, st));
-						CUDA_TRY(ctx, cudaStreamSynchronize(st));
-						S.kernelLaunches++;
-						const uint32_t nSec = hCounts[0], nShadow = hCounts[1];
-						if (nShadow > 0) {
-							cudaEventRecord(evA, st);
-							if (launchShadowWf(ctx, wf.shadowRay, wf.shadowPayload, nShadow, wf.li, persistShadow)) return fail(MTSGPU_ERR_CUDA);
-							cudaEventRecord(evB, st);
-							CUDA_TRY(ctx, cudaEventSynchronize(evB));
-							{ float ms = 0; cudaEventElapsedTime(&ms, evA, evB); msShadow += ms; }
-							S.shadowRays += nShadow; S.kernelLaunches++;
-						}
-						if (nSec > 0) {
-							wf.slotCur = slotBuf[cur ^ 1]; wf.rayCur = rayBuf[cur ^ 1];
-							cudaEventRecord(evA, st);
-						if (launchClosestWf(ctx, wf.rayCur, nSec, wf.hit, persistClosest)) return fail(MTSGPU_ERR_CUDA);
-							cudaEventRecord(evB, st);
-							if (bmp) k_shade<2, true><<<blocksFor(nSec, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nSec, (uint32_t) r); else k_shade<2, false><<<blocksFor(nSec, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, nSec, (uint32_t) r);
-							CUDA_TRY(ctx, cudaStreamSynchronize(st));
-							{ float ms = 0; cudaEventElapsedTime(&ms, evA, evB); msClosest += ms; }
-							S.normalRays += nSec; S.kernelLaunches += 2;
-						}
+						if (cancel && *cancel) { rc = setError(ctx, MTSGPU_ERR_CANCELLED, "render cancelled"); break; }
+						wf.slotNext = slotBuf[0]; wf.rayNext = rayBuf[0];
+						wf.slotCur = slotBuf[0]; wf.rayCur = rayBuf[0];
+						LAUNCH_SHADE(1, wf.counters, (uint32_t) r);
+						CUDA_TRY(ctx, stamp(evSet, 2));
+						if (launchShadowWf(ctx, wf.shadowRay, wf.shadowPayload, wf.counters + 2, wf.li, persistShadow)) return fail(MTSGPU_ERR_CUDA);
+						CUDA_TRY(ctx, stamp(evSet, 3));
+						CUDA_TRY(ctx, stamp(evSet, 0));
+						if (launchClosestWf(ctx, wf.rayCur, wf.counters + 1, wf.hit, persistClosest)) return fail(MTSGPU_ERR_CUDA);
+						CUDA_TRY(ctx, stamp(evSet, 1));
+						LAUNCH_SHADE(2, wf.counters + 1, (uint32_t) r);
+						k_advance<<<1, 1, 0, st>>>(wf.counters, dStats, 3);
+						S.kernelLaunches += 3;
 					}
 				}
 				if (rc != MTSGPU_OK) break;
@@ -769,6 +853,14 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 				S.kernelLaunches++;
 				CUDA_TRY(ctx, cudaGetLastError());
 			}
+		}
+#undef LAUNCH_SHADE
+		CUDA_TRY(ctx, harvest(0)); CUDA_TRY(ctx, harvest(1));
+		{
+			unsigned long long h[4];
+			CUDA_TRY(ctx, cudaMemcpyAsync(h, dStats, sizeof(h), cudaMemcpyDeviceToHost, st));
+			CUDA_TRY(ctx, cudaStreamSynchronize(st));
+			S.cameraRays = h[0]; S.normalRays = h[1]; S.shadowRays = h[2];
 		}
 		S.samples = S.cameraRays;
 		S.traceClosestMs = msClosest; S.traceAnyMs = msShadow;
