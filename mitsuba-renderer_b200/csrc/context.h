@@ -89,7 +89,7 @@ struct mtsgpu_ctx {
 	// wavefront state (integrate.cu)
 	DevBuf dPathState, dRayA, dRayB, dHit, dShadowRay, dShadowPayload, dQueueA, dQueueB, dQueueCounts,
 	       dResult, dFilm, dStage, dStageOut;
-	DevBuf dPrimSlot, dPrimRay, dPrimHit, dFilterTable;
+	DevBuf dPrimSlot, dPrimRay, dPrimHit, dPrimState, dStateA, dStateB, dFilterTable;
 	uint32_t *hCounts = nullptr;     // pinned host ring of polled queue lengths
 	cudaEvent_t pollEv[16] = {};     // one per ring slot
 	std::vector<cudaEvent_t> evPool[2];      // timing events of the traversal launches, two alternating sets

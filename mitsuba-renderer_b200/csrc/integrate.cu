@@ -41,9 +41,11 @@
 #define PF_RR_MASK      0x0FF00000u
 
 struct WfArrays {
-	float4 *thr;        // per slot: throughput.rgb, previous bsdfPdf
-	float4 *li;         // per slot: Li.rgb, alpha
-	float4 *bsdfVal;    // per slot: previous bsdfVal.rgb (f*cos/pdf), flag word
+	float4 *li;         // per slot: Li.rgb, alpha — touched only when a path adds radiance (emitter hit, background, unoccluded shadow ray)
+	// per queue position, travelling with the ray (2 x float4: {throughput.rgb, previous bsdfPdf} {previous bsdfVal.rgb (f*cos/pdf),
+	// flag word}): read and written in queue order, where the slot-indexed arrays of the first version cost six random
+	// 32-byte sectors per hit from the second bounce on (k_shade was bound by DRAM transactions, ~50 G sectors/s)
+	float4 *stateCur, *stateNext, *statePrim;
 	float2 *samplePos;  // per slot: film sample position; x = NaN marks a slot outside the crop window
 	uint32_t *slotCur, *slotNext;     // ray queues: slot ids by queue position
 	float4 *rayCur, *rayNext;         // 2 x float4 per queue position
@@ -117,9 +119,7 @@ k_generate(const CameraDev cam, const FilmDev film, const BatchDesc b, WfArrays 
 			r0 = make_float4(o.x, o.y, o.z, mint);
 			r1 = make_float4(d.x, d.y, d.z, maxt);
 			wf.samplePos[slot] = make_float2(sx, sy);
-			wf.thr[slot] = make_float4(1, 1, 1, 0);
 			wf.li[slot] = make_float4(0, 0, 0, 0);
-			wf.bsdfVal[slot] = make_float4(0, 0, 0, __uint_as_float(1u | PF_EMITTED));   // depth = 1 (integrator.h:186-191)
 		} else {
 			wf.samplePos[slot] = make_float2(__int_as_float(0x7FC00000), 0);
 		}
@@ -129,6 +129,8 @@ k_generate(const CameraDev cam, const FilmDev film, const BatchDesc b, WfArrays 
 		wf.slotNext[pos] = slot;
 		wf.rayNext[2 * (size_t) pos] = r0;
 		wf.rayNext[2 * (size_t) pos + 1] = r1;
+		wf.stateNext[2 * (size_t) pos] = make_float4(1, 1, 1, 0);
+		wf.stateNext[2 * (size_t) pos + 1] = make_float4(0, 0, 0, __uint_as_float(1u | PF_EMITTED));   // depth = 1 (integrator.h:186-191)
 	}
 }
 
@@ -301,7 +303,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 	const bool entry = j0 + threadIdx.x < listed;
 	const uint32_t i = entry ? sList[j0 + threadIdx.x] : 0u;
 	bool emitRay = false, emitShadow = false;
-	float4 nr0, nr1, sr0, sr1; V3 contrib = v3(0, 0, 0);
+	float4 nr0, nr1, sr0, sr1, st0, st1; V3 contrib = v3(0, 0, 0);
 	uint32_t slot = 0;
 
 	if (entry) {
@@ -310,10 +312,12 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		const uint4 h = hits[i];
 		const V3 rayO = v3(ra), rayD = v3(rb);
 		const bool valid = h.w != 0xFFFFFFFFu;
-		float4 thr4 = wf.thr[slot], li4 = wf.li[slot], bv4 = wf.bsdfVal[slot];
+		const float4 *state = (MODE == 1) ? wf.statePrim : wf.stateCur;
+		float4 thr4 = state[2 * (size_t) i], bv4 = state[2 * (size_t) i + 1];
 		uint32_t flags = __float_as_uint(bv4.w);
 		uint32_t depth = flags & PF_DEPTH_MASK;
-		V3 thr = v3(thr4), Li = v3(li4);
+		V3 thr = v3(thr4), Li = v3(0, 0, 0);            // Li: the radiance this step adds (at most one term), folded into li[slot] at the end
+		bool liDirty = false, alphaDirty = false;
 		int px, py; uint32_t sample;
 		slotToPixel(b, film, slot, px, py, sample);
 		Sampler smp; smp.init((uint32_t) ((py + film.cropY) * film.width + px + film.cropX), sample, b.seed, b.sampler);
@@ -337,8 +341,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 				const float fracBsdf = ig.nBsdf / total, fracLum = ig.nLum / total;
 				const float weightBsdf = 1 / (float) ig.nBsdf;
 				const float w = miWeight(thr4.w * fracBsdf, lumPdf * fracLum) * weightBsdf;
-				Li = Li + (Le * v3(bv4)) * w;
-				wf.li[slot] = make_float4(Li.x, Li.y, Li.z, li4.w);
+				Li = Li + (Le * v3(bv4)) * w; liDirty = true;
 			}
 			alive = false;
 		} else {
@@ -349,7 +352,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 					if (sc.background >= 0) {                  // path.cpp:158-163, 172-179, then 187-188
 						const float lumPdf = (flags & PF_PREV_DELTA) ? 0.0f : pdfBackground(sc, ig.importance != 0, rayD);
 						const float w = miWeight(thr4.w, lumPdf);
-						Li = Li + ((thr * backgroundLe(sc, rayD)) * bsdfVal) * w;
+						Li = Li + ((thr * backgroundLe(sc, rayD)) * bsdfVal) * w; liDirty = true;
 					} else {
 						depth++;                               // path.cpp:166
 					}
@@ -359,7 +362,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 						const V3 Le = emitterLe(sc, its.emitterId, its.geoN, -rayD);
 						const float lumPdf = (flags & PF_PREV_DELTA) ? 0.0f : pdfLuminaire(sc, rayO, its.p, its.geoN, its.emitterId, ig.importance != 0);
 						const float w = miWeight(thr4.w, lumPdf);
-						Li = Li + ((thr * Le) * bsdfVal) * w;
+						Li = Li + ((thr * Le) * bsdfVal) * w; liDirty = true;
 					}
 					flags &= ~PF_EMITTED;                      // rRec.type = ERadianceNoEmission
 					bool survive = true;
@@ -376,15 +379,15 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 				}
 			} else if (MODE == 0 || round == 0) {
 				// camera hit: rRec.alpha (records.inl:93-99)
-				li4.w = valid ? 1.0f : 0.0f;
+				alphaDirty = valid;               // k_generate left alpha = 0
 				if (MODE == 0 && ig.maxDepth == 0) alive = false;      // path.cpp:60: `while (depth <= maxDepth || maxDepth < 0)` never runs: black
-				else if (!valid && (flags & PF_EMITTED)) Li = Li + backgroundLe(sc, rayD);      // path.cpp:62-68 / direct.cpp:74-81
+				else if (!valid && (flags & PF_EMITTED)) { Li = Li + backgroundLe(sc, rayD); liDirty = true; }      // path.cpp:62-68 / direct.cpp:74-81
 			}
 
 			// ---- top of the loop body at the new hit (path.cpp:58-95 / direct.cpp:74-100)
 			if (alive && its.materialId < 0 && its.emitterId >= 0 && (flags & PF_EMITTED) && (MODE == 0 || round == 0)) {
 				// direct.cpp adds emission before the BSDF check; path.cpp checks the BSDF first
-				if (MODE == 1) Li = Li + emitterLe(sc, its.emitterId, its.geoN, -rayD);
+				if (MODE == 1) { Li = Li + emitterLe(sc, its.emitterId, its.geoN, -rayD); liDirty = true; }
 			}
 			if (alive && its.materialId < 0) alive = false;             // no BSDF: give up (path.cpp:70-77)
 			MaterialDev mat;
@@ -401,7 +404,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 				}
 				resolveTextures<BMP>(sc, mat, its.uvx, its.uvy, duv);
 				if (its.emitterId >= 0 && (flags & PF_EMITTED) && (MODE == 0 || round == 0))
-					Li = Li + (MODE == 0 ? thr : v3(1, 1, 1)) * emitterLe(sc, its.emitterId, its.geoN, -rayD);
+					{ Li = Li + (MODE == 0 ? thr : v3(1, 1, 1)) * emitterLe(sc, its.emitterId, its.geoN, -rayD); liDirty = true; }
 				if (MODE == 0 && ig.maxDepth > 0 && (int) depth >= ig.maxDepth) alive = false;
 				if (MODE == 0 && depth >= PF_DEPTH_MASK - 1u) alive = false;      // safety net: the depth field is 16 bits wide
 			}
@@ -463,12 +466,15 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 			}
 			flags = (flags & ~PF_DEPTH_MASK) | (depth & PF_DEPTH_MASK);
 			if (smp.overflow) atomicOr(sc.traceFlags, 2u);      // halton.cpp:74-84: the reference stops with an error here
-			wf.li[slot] = make_float4(Li.x, Li.y, Li.z, li4.w);
-			if (emitRay) {
-				wf.thr[slot] = make_float4(thr.x, thr.y, thr.z, thr4.w);
-				wf.bsdfVal[slot] = make_float4(bv4.x, bv4.y, bv4.z, __uint_as_float(flags));
-			}
+			if (emitRay) { thr4 = make_float4(thr.x, thr.y, thr.z, thr4.w); bv4.w = __uint_as_float(flags); }
 		}
+		if (liDirty || alphaDirty) {
+			float4 l = wf.li[slot];
+			if (liDirty) { l.x += Li.x; l.y += Li.y; l.z += Li.z; }
+			if (alphaDirty) l.w = 1.0f;
+			wf.li[slot] = l;
+		}
+		if (emitRay) { st0 = thr4; st1 = bv4; }
 	}
 
 	const uint32_t rp = warpAppend(&wf.counters[1], emitRay);
@@ -476,6 +482,8 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		wf.slotNext[rp] = slot;
 		wf.rayNext[2 * (size_t) rp] = nr0;
 		wf.rayNext[2 * (size_t) rp + 1] = nr1;
+		wf.stateNext[2 * (size_t) rp] = st0;
+		wf.stateNext[2 * (size_t) rp + 1] = st1;
 	}
 	const uint32_t sp = warpAppend(&wf.counters[2], emitShadow);
 	if (emitShadow) {
@@ -615,8 +623,9 @@ static int launchShadowWf(mtsgpu_ctx *ctx, const float4 *rays, const float4 *pay
 static int ensureWavefront(mtsgpu_ctx *ctx, uint32_t capacity) {
 	if (ctx->pathCapacity >= capacity) return MTSGPU_OK;
 	const size_t c = capacity;
-	CUDA_TRY(ctx, ctx->dPathState.alloc(c * (16 * 3 + 8)));
+	CUDA_TRY(ctx, ctx->dPathState.alloc(c * (16 + 8)));            // per slot: li + sample position
 	CUDA_TRY(ctx, ctx->dRayA.alloc(c * 32)); CUDA_TRY(ctx, ctx->dRayB.alloc(c * 32));
+	CUDA_TRY(ctx, ctx->dStateA.alloc(c * 32)); CUDA_TRY(ctx, ctx->dStateB.alloc(c * 32));     // per queue position, beside the rays
 	CUDA_TRY(ctx, ctx->dHit.alloc(c * 20));                 // uint4 hits + one nested-triangle index each
 	CUDA_TRY(ctx, ctx->dShadowRay.alloc(c * 32)); CUDA_TRY(ctx, ctx->dShadowPayload.alloc(c * 16));
 	CUDA_TRY(ctx, ctx->dQueueA.alloc(c * 4)); CUDA_TRY(ctx, ctx->dQueueB.alloc(c * 4));
@@ -695,7 +704,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 	cudaEvent_t evBegin = ctx->ev[0], evEnd = ctx->ev[1], evA = ctx->ev[2], evB = ctx->ev[3];
 	CUDA_TRY(ctx, cudaEventRecord(evBegin, st));
 	if (spp > 0) {
-		const uint32_t maxSlots = 1u << 25;     // 192 B of queue + path state per slot => ~6.4 GB at full size
+		const uint32_t maxSlots = 1u << 25;     // 228 B of queues + path state per slot => ~7.6 GB at full size
 		uint32_t sampleChunk = std::min<uint32_t>(spp, maxSlots / TILE_PIX);
 		uint32_t tilesPerBatch = std::max<uint32_t>(1u, std::min<uint32_t>(nTiles, maxSlots / (TILE_PIX * sampleChunk)));
 		const uint32_t capacity = tilesPerBatch * sampleChunk * TILE_PIX;
@@ -710,14 +719,17 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 		if (P->mode == MTSGPU_MODE_DIRECT) {
 			CUDA_TRY(ctx, dPrimSlot.alloc((size_t) ctx->pathCapacity * 4));
 			CUDA_TRY(ctx, dPrimRay.alloc((size_t) ctx->pathCapacity * 32));
+			CUDA_TRY(ctx, ctx->dPrimState.alloc((size_t) ctx->pathCapacity * 32));
 			CUDA_TRY(ctx, dPrimHit.alloc((size_t) ctx->pathCapacity * 20));
 		}
 		// the camera behind DeviceScene::camera (ray differentials for bitmap textures)
 		CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dCamera.p, &ctx->camera, sizeof(CameraDev), cudaMemcpyHostToDevice, st));
 		WfArrays wf;
 		char *ps = ctx->dPathState.as<char>();
-		wf.thr = (float4 *) ps; wf.li = (float4 *) (ps + (size_t) capacity * 16); wf.bsdfVal = (float4 *) (ps + (size_t) capacity * 32);
-		wf.samplePos = (float2 *) (ps + (size_t) capacity * 48);
+		wf.li = (float4 *) ps;
+		wf.samplePos = (float2 *) (ps + (size_t) capacity * 16);
+		wf.statePrim = ctx->dPrimState.as<float4>();
+		float4 *stateBuf[2] = { ctx->dStateA.as<float4>(), ctx->dStateB.as<float4>() };
 		wf.hit = ctx->dHit.as<uint4>(); wf.capacity = ctx->pathCapacity;
 		wf.shadowRay = ctx->dShadowRay.as<float4>(); wf.shadowPayload = ctx->dShadowPayload.as<float4>();
 		wf.counters = ctx->dQueueCounts.as<uint32_t>();
@@ -788,6 +800,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 				int cur = 0;
 				const bool direct = P->mode == MTSGPU_MODE_DIRECT;
 				wf.slotNext = direct ? wf.slotPrim : slotBuf[cur]; wf.rayNext = direct ? wf.rayPrim : rayBuf[cur];
+				wf.stateNext = direct ? wf.statePrim : stateBuf[cur]; wf.stateCur = stateBuf[cur];
 				CUDA_TRY(ctx, cudaMemsetAsync(wf.counters, 0, 16, st));
 				k_generate<<<blocksFor(b.slots, WF_BLOCK), WF_BLOCK, 0, st>>>(ctx->camera, film, b, wf);
 				k_advance<<<1, 1, 0, st>>>(wf.counters, dStats, 0);
@@ -808,8 +821,8 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 							seen++;
 						}
 						if (dry) break;
-						wf.slotCur = slotBuf[cur]; wf.rayCur = rayBuf[cur];
-						wf.slotNext = slotBuf[cur ^ 1]; wf.rayNext = rayBuf[cur ^ 1];
+						wf.slotCur = slotBuf[cur]; wf.rayCur = rayBuf[cur]; wf.stateCur = stateBuf[cur];
+						wf.slotNext = slotBuf[cur ^ 1]; wf.rayNext = rayBuf[cur ^ 1]; wf.stateNext = stateBuf[cur ^ 1];
 						CUDA_TRY(ctx, stamp(evSet, 0));
 						if (launchClosestWf(ctx, wf.rayCur, wf.counters, wf.hit, persistClosest)) return fail(MTSGPU_ERR_CUDA);
 						CUDA_TRY(ctx, stamp(evSet, 1));
@@ -834,8 +847,8 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 					const int rounds = std::max(P->luminaireSamples, P->bsdfSamples);
 					for (int r = 0; r < rounds; ++r) {
 						if (cancel && *cancel) { rc = setError(ctx, MTSGPU_ERR_CANCELLED, "render cancelled"); break; }
-						wf.slotNext = slotBuf[0]; wf.rayNext = rayBuf[0];
-						wf.slotCur = slotBuf[0]; wf.rayCur = rayBuf[0];
+						wf.slotNext = slotBuf[0]; wf.rayNext = rayBuf[0]; wf.stateNext = stateBuf[0];
+						wf.slotCur = slotBuf[0]; wf.rayCur = rayBuf[0]; wf.stateCur = stateBuf[0];
 						LAUNCH_SHADE(1, wf.counters, (uint32_t) r);
 						CUDA_TRY(ctx, stamp(evSet, 2));
 						if (launchShadowWf(ctx, wf.shadowRay, wf.shadowPayload, wf.counters + 2, wf.li, persistShadow)) return fail(MTSGPU_ERR_CUDA);
