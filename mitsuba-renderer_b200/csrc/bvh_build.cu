@@ -10,7 +10,10 @@
 //   6. k_reorder        TriAccel records gathered into leaf order so a leaf is one contiguous run
 // Only hit results must agree with the reference's kd-tree, not the tree.
 #include "context.h"
-#define TRACE_STACK_FAST 20       // = TRACE_SMEM_STACK, TRACE_SMEM_STACK + TRACE_LOCAL_STACK of trace.cuh (checked there)
+#ifndef TRACE_SMEM_STACK
+#define TRACE_SMEM_STACK 20
+#endif
+#define TRACE_STACK_FAST TRACE_SMEM_STACK       // = TRACE_SMEM_STACK, TRACE_SMEM_STACK + TRACE_LOCAL_STACK of trace.cuh (checked there)
 #define TRACE_STACK_TOTAL 96
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>

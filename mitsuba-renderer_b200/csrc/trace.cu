@@ -1,7 +1,7 @@
 // Batch ray-query kernels behind mtsgpu_trace / mtsgpu_trace_device and the wavefront loop.
 #include "context.h"
 #include "trace.cuh"
-static_assert(TRACE_SMEM_STACK == 20 && TRACE_SMEM_STACK + TRACE_LOCAL_STACK == 96, "bvh_build.cu: TRACE_STACK_FAST / TRACE_STACK_TOTAL");
+static_assert(TRACE_SMEM_STACK + TRACE_LOCAL_STACK == 96, "bvh_build.cu: TRACE_STACK_FAST / TRACE_STACK_TOTAL");
 #include <algorithm>
 #include <cstdlib>
 

@@ -12,8 +12,10 @@
 #define MTSGPU_HAVE_TRACE 1
 
 #define TRACE_BLOCK        128
+#ifndef TRACE_SMEM_STACK
 #define TRACE_SMEM_STACK   20      // entries per thread kept in shared memory
-#define TRACE_LOCAL_STACK  76      // overflow entries in local memory (deep LBVH chains)
+#endif
+#define TRACE_LOCAL_STACK  (96 - TRACE_SMEM_STACK)      // overflow entries in local memory (deep chains)
 
 struct RayIn { float ox, oy, oz, mint, dx, dy, dz, maxt; };
 
