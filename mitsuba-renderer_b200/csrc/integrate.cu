@@ -704,7 +704,11 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 	cudaEvent_t evBegin = ctx->ev[0], evEnd = ctx->ev[1], evA = ctx->ev[2], evB = ctx->ev[3];
 	CUDA_TRY(ctx, cudaEventRecord(evBegin, st));
 	if (spp > 0) {
-		const uint32_t maxSlots = 1u << 25;     // 228 B of queues + path state per slot => ~7.6 GB at full size
+		static const uint32_t slotsLog2 = getenv("MTSGPU_BATCH_LOG2") ? (uint32_t) std::min(std::max(atoi(getenv("MTSGPU_BATCH_LOG2")), 16), 28) : 27u;
+		// 228 B of queues + path state per slot => 30.6 GB at the default size (2^27 slots), allocated only as far as the job needs.
+		// Measured on C4 (B200): 2^25 -> 2^27 slots per batch = -11 % render time: every bounce of a batch is one launch of each
+		// kernel, and the late bounces (1-2 % of the rays) and each launch's drain phase weigh less in a larger batch.
+		const uint32_t maxSlots = 1u << slotsLog2;
 		uint32_t sampleChunk = std::min<uint32_t>(spp, maxSlots / TILE_PIX);
 		uint32_t tilesPerBatch = std::max<uint32_t>(1u, std::min<uint32_t>(nTiles, maxSlots / (TILE_PIX * sampleChunk)));
 		const uint32_t capacity = tilesPerBatch * sampleChunk * TILE_PIX;
