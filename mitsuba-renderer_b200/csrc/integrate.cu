@@ -26,10 +26,10 @@
 
 #define TILE 16
 #define TILE_PIX (TILE * TILE)
-#define WF_BLOCK 128
+#define WF_BLOCK 256
 #define WF_POLL_RING 16           // pinned slots / events of the asynchronous queue-length polls
 #define WF_POLL_AHEAD 6           // bounces the host may enqueue beyond the last poll it has seen
-#define SHADE_CHUNK 512           // queue entries a shading block lists before it shades the ones that need it
+#define SHADE_CHUNK 1024          // queue entries a shading block lists before it shades the ones that need it
 
 // path-state flag word
 #define PF_DEPTH_MASK   0x0000FFFFu
@@ -87,6 +87,27 @@ __device__ __forceinline__ uint32_t warpAppend(uint32_t *counter, bool pred) {
 	return base + __popc(mask & ((1u << lane) - 1u));
 }
 
+// Block-aggregated queue append: ONE atomic per block and call. Appends to one address serialise in L2 at about 145 M/s on
+// B200 (k_generate: 4.2 M warp-level appends took 29 ms), and with one append per warp k_shade needed ~125 M/s on each of
+// its two queues: it was bound by exactly that. `agg` / `base`: shared scratch, double-buffered by `parity` so that one
+// barrier pair per call suffices. Must be called by every thread of the block.
+__device__ __forceinline__ uint32_t blockAppend(uint32_t *counter, bool pred, uint32_t (*agg)[WF_BLOCK / 32], uint32_t *base, int parity) {
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	const uint32_t mask = __ballot_sync(0xFFFFFFFFu, pred);
+	if (lane == 0) agg[parity][warp] = __popc(mask);
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		uint32_t total = 0;
+#pragma unroll
+		for (int w = 0; w < WF_BLOCK / 32; ++w) total += agg[parity][w];
+		base[parity] = total ? atomicAdd(counter, total) : 0u;
+	}
+	__syncthreads();
+	uint32_t pos = base[parity];
+	for (uint32_t w = 0; w < warp; ++w) pos += agg[parity][w];
+	return pos + __popc(mask & ((1u << lane) - 1u));
+}
+
 __device__ __forceinline__ void slotToPixel(const BatchDesc &b, const FilmDev &film, uint32_t slot,
 		int &px, int &py, uint32_t &sample) {
 	const uint32_t pix = slot % TILE_PIX;
@@ -124,7 +145,8 @@ k_generate(const CameraDev cam, const FilmDev film, const BatchDesc b, WfArrays 
 			wf.samplePos[slot] = make_float2(__int_as_float(0x7FC00000), 0);
 		}
 	}
-	const uint32_t pos = warpAppend(&wf.counters[0], alive);
+	__shared__ uint32_t sAgg[2][WF_BLOCK / 32], sBase[2];
+	const uint32_t pos = blockAppend(&wf.counters[0], alive, sAgg, sBase, 0);
 	if (alive) {
 		wf.slotNext[pos] = slot;
 		wf.rayNext[2 * (size_t) pos] = r0;
@@ -260,9 +282,9 @@ __device__ __forceinline__ bool nextEvent(const DeviceScene &sc, const Integrato
 // BMP: the scene has bitmap textures or instances (the variant without them carries none of that code).
 template <int MODE, bool BMP>
 #ifndef SHADE_MIN_BLOCKS
-#define SHADE_MIN_BLOCKS 6
+#define SHADE_MIN_BLOCKS 3
 #endif
-__global__ void __launch_bounds__(WF_BLOCK, SHADE_MIN_BLOCKS)      // 6: <= 80 registers, measured 9 % faster than the uncapped 122
+__global__ void __launch_bounds__(WF_BLOCK, SHADE_MIN_BLOCKS)      // 3 x 256 threads: <= 85 registers
 k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const FilmDev film, WfArrays wf, const uint32_t *__restrict__ nIn, uint32_t round) {
 	// The queue length is read on the device (no host round trip per bounce), and a block works through chunks of
 	// SHADE_CHUNK queue entries: it first lists the entries that need shading at all — from the second bounce on more than
@@ -270,6 +292,8 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 	// 9.9 of 32 lanes active on the bounce-2 queue) — then shades the listed ones with full warps. The list keeps the queue order.
 	__shared__ uint32_t sList[SHADE_CHUNK];
 	__shared__ uint32_t sCount[SHADE_CHUNK / 32];
+	__shared__ uint32_t sAggR[2][WF_BLOCK / 32], sAggS[2][WF_BLOCK / 32], sBaseR[2], sBaseS[2];
+	int parity = 0;
 	const uint32_t n = *nIn;
 	const uint32_t *slots = (MODE == 1) ? wf.slotPrim : wf.slotCur;
 	const float4 *rays = (MODE == 1) ? wf.rayPrim : wf.rayCur;
@@ -477,7 +501,7 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		if (emitRay) { st0 = thr4; st1 = bv4; }
 	}
 
-	const uint32_t rp = warpAppend(&wf.counters[1], emitRay);
+	const uint32_t rp = blockAppend(&wf.counters[1], emitRay, sAggR, sBaseR, parity);
 	if (emitRay) {
 		wf.slotNext[rp] = slot;
 		wf.rayNext[2 * (size_t) rp] = nr0;
@@ -485,7 +509,8 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		wf.stateNext[2 * (size_t) rp] = st0;
 		wf.stateNext[2 * (size_t) rp + 1] = st1;
 	}
-	const uint32_t sp = warpAppend(&wf.counters[2], emitShadow);
+	const uint32_t sp = blockAppend(&wf.counters[2], emitShadow, sAggS, sBaseS, parity);
+	parity ^= 1;
 	if (emitShadow) {
 		wf.shadowRay[2 * (size_t) sp] = sr0;
 		wf.shadowRay[2 * (size_t) sp + 1] = sr1;
