@@ -410,7 +410,7 @@ __global__ void k_reorder(const uint32_t *sortedIdx, const TriAccelRec *orig, ui
 // 128-byte fp32 node -> the 64-byte node of the traversal kernels (types.cuh: BVH4QNode). Per axis: origin = just below the
 // smallest child plane, quantum 2^e with (extent / 2^e) <= 254.5, child planes floor / ceil'ed outwards in fp64 with a
 // hundredth of a quantum of slack for the decode's rounding (m * S + C in trace.cuh: 2^-17 of a quantum range).
-// Empty slots get an inverted box; the traversal also checks the child word.
+// Empty slots get an inverted box and the child word of slot 0 (k_collapse fills the slots in order, so slot 0 is real).
 __global__ void k_quantize_nodes(const BVH4Node *in, uint32_t n, BVH4QNode *out) {
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n) return;
@@ -444,7 +444,7 @@ __global__ void k_quantize_nodes(const BVH4Node *in, uint32_t n, BVH4QNode *out)
 	}
 	BVH4QNode q;
 	q.ox = origin[0]; q.oy = origin[1]; q.oz = origin[2]; q.scaleX = scale[0]; q.scaleY = scale[1]; q.scaleZ = scale[2];
-	for (int c = 0; c < 4; ++c) q.child[c] = cw[c];
+	for (int c = 0; c < 4; ++c) q.child[c] = cw[c] != BVH_EMPTY ? cw[c] : cw[0];     // empty slot: inverted box + a real child's word (trace.cuh: entryOrInf)
 	q.qlox = qlo[0]; q.qloy = qlo[1]; q.qloz = qlo[2]; q.qhix = qhi[0]; q.qhiy = qhi[1]; q.qhiz = qhi[2];
 	out[i] = q;
 }

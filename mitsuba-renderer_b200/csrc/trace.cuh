@@ -122,7 +122,7 @@ __device__ __forceinline__ void ldg256(const void *p, uint32_t (&v)[8]) {
 // Slab test of one ray against the four children of a quantised node (types.cuh: BVH4QNode): two 256-bit loads, then per
 // plane one PRMT (byte -> the float 1 + q / 2^15) and one FFMA: t = m * S + C with S = scale / d and
 // C = (origin - o) / d - S. The near and far words of each axis are picked by the ray's direction signs, so a child
-// costs 6 PRMT + 6 FFMA + 4 min / max + 3 for the verdict. tn[i] = entry distance, +inf when child i is not entered
+// costs 6 PRMT + 6 FFMA + 4 min / max + 2 for the verdict. tn[i] = entry distance, +inf when child i is not entered
 // (or empty). `one` = 0x3F800000 handed in from the kernel parameters (DeviceScene::oneBits): as a literal, ptxas made it
 // PRMT's immediate and rebuilt the selector in a register before each of the 24 PRMTs (ncu source view, r02_q_c4_trace).
 template <int I>
@@ -131,10 +131,11 @@ __device__ __forceinline__ float qPlane(uint32_t word, uint32_t one, float S, fl
 	asm("prmt.b32 %0, %1, %2, %3;" : "=r"(m) : "r"(word), "r"(one), "n"(0x7604 | (I << 4)));      // {0x00, byte I, 0x80, 0x3F}
 	return fmaf(__uint_as_float(m), S, C);
 }
-__device__ __forceinline__ float entryOrInf(float tnear, float tfar, uint32_t child) {
+// An empty slot needs no test of its own: the builder gives it an inverted box (never entered) and, should rounding ever
+// collapse that box for a far-away degenerate node, the child word of slot 0 — a second visit of a real child changes no result.
+__device__ __forceinline__ float entryOrInf(float tnear, float tfar) {
 	float r;
-	asm("{\n\t.reg .pred p, q;\n\tsetp.ne.u32 q, %3, 0xFFFFFFFF;\n\tsetp.le.and.f32 p, %1, %2, q;\n\tselp.f32 %0, %1, 0f7F800000, p;\n\t}"
-		: "=f"(r) : "f"(tnear), "f"(tfar), "r"(child));
+	asm("{\n\t.reg .pred p;\n\tsetp.le.f32 p, %1, %2;\n\tselp.f32 %0, %1, 0f7F800000, p;\n\t}" : "=f"(r) : "f"(tnear), "f"(tfar));
 	return r;
 }
 // The planes' t values carry the rounding of o / d (about 2^-22 |o / d| in all): for origins within a few scene extents that
@@ -156,7 +157,7 @@ __device__ __forceinline__ void nodeTest(const float4 *nodes, uint32_t one, uint
 #define NODE_CHILD(I) { \
 		const float tnear = fmaxf(fmaxf(fmaxf(qPlane<I>(nearX, one, Sx, CxN), qPlane<I>(nearY, one, Sy, CyN)), qPlane<I>(nearZ, one, Sz, CzN)), mint); \
 		const float tfar = fminf(fminf(fminf(qPlane<I>(farX, one, Sx, CxF), qPlane<I>(farY, one, Sy, CyF)), qPlane<I>(farZ, one, Sz, CzF)), maxt); \
-		cw[I] = a[4 + I]; tn[I] = entryOrInf(tnear, tfar, a[4 + I]); }
+		cw[I] = a[4 + I]; tn[I] = entryOrInf(tnear, tfar); }
 	NODE_CHILD(0) NODE_CHILD(1) NODE_CHILD(2) NODE_CHILD(3)
 #undef NODE_CHILD
 }
