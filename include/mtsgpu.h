@@ -195,6 +195,17 @@ typedef struct mtsgpu_stats {
 	uint64_t closestNodeVisits, closestTriTests, shadowNodeVisits, shadowTriTests;
 } mtsgpu_stats;
 
+/* Progress and preview while mtsgpu_render / mtsgpu_render_device run. Replaces, for this integrator, the ProgressReporter
+ * updates and RenderQueue::signalRefresh / the mutex-guarded film merge that BlockedRenderProcess::processResult performs after
+ * every block (src/librender/renderproc.cpp:123-130, include/mitsuba/render/renderqueue.h:109-112): between wavefront batches,
+ * at most once per `minIntervalSeconds`, `fn(user, fraction, film)` is called ON THE THREAD THAT CALLED mtsgpu_render with the
+ * fraction of the work enqueued so far and — if wantFilm — the {sum spec.rgb, sum alpha, sum weight} accumulators as they stood
+ * at that point (cropW * cropH * 5 floats in pinned host memory owned by the library, valid during the call; tiles not yet
+ * rendered are zero). The copy runs on its own stream from a device-side snapshot, the render is not synchronised for it.
+ * A last call with fraction 1 and film = NULL follows the render. fn = NULL switches it off. */
+typedef void (*mtsgpu_progress_fn)(void *user, double fraction, const float *film);
+MTSGPU_API int mtsgpu_set_progress(mtsgpu_ctx *ctx, mtsgpu_progress_fn fn, void *user, double minIntervalSeconds, int wantFilm);
+
 /* Closest-hit record returned by mtsgpu_trace; mirrors the reference's IntersectionCache
  * (include/mitsuba/render/skdtree.h:232-236) plus t. Miss: t = +inf, shape = prim = 0xFFFFFFFF. */
 typedef struct mtsgpu_hit {

@@ -25,7 +25,7 @@ EXPORTED_SYMBOLS = [
     "mtsgpu_upload_emitters", "mtsgpu_upload_mesh", "mtsgpu_set_camera", "mtsgpu_set_film", "mtsgpu_build_accel",
     "mtsgpu_render", "mtsgpu_render_device", "mtsgpu_trace", "mtsgpu_trace_device", "mtsgpu_bsdf_eval",
     "mtsgpu_emitter_sample", "mtsgpu_camera_rays", "mtsgpu_film_splat", "mtsgpu_intersect_full",
-    "mtsgpu_get_triaccel", "mtsgpu_accel_info_get", "mtsgpu_set_counters", "mtsgpu_get_counters",
+    "mtsgpu_get_triaccel", "mtsgpu_accel_info_get", "mtsgpu_set_counters", "mtsgpu_get_counters", "mtsgpu_set_progress",
     "mtsgpu_film_splat_static", "mtsgpu_render_multi", "mtsgpu_serialized_count", "mtsgpu_serialized_load",
     "mtsgpu_serialized_free", "mtsgpu_serialized_save", "mtsgpu_upload_serialized", "mtsgpu_film_develop",
     "mtsgpu_film_develop_device", "mtsgpu_film_save", "mtsgpu_write_exr", "mtsgpu_write_mfilm", "mtsgpu_sampler_values",
@@ -72,6 +72,9 @@ class Stats(C.Structure):
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+PROGRESS_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_double, C.POINTER(C.c_float))
 
 
 class AccelInfo(C.Structure):
@@ -136,6 +139,7 @@ def load_library(path: Optional[str] = None):
     lib.mtsgpu_get_triaccel.argtypes = [vp, vp, C.c_size_t, vp]
     lib.mtsgpu_accel_info_get.argtypes = [vp, C.POINTER(AccelInfo)]
     lib.mtsgpu_set_counters.argtypes = [vp, C.c_int]
+    lib.mtsgpu_set_progress.argtypes = [vp, PROGRESS_FN, vp, C.c_double, C.c_int]
     lib.mtsgpu_get_counters.argtypes = [vp, C.POINTER(TraceCounters)]
     lib.mtsgpu_sampler_values.argtypes = [vp, C.POINTER(RenderParams), C.c_uint32, C.c_uint32, vp]
     lib.mtsgpu_film_develop.argtypes = [vp, vp, C.c_int, vp]
@@ -439,6 +443,23 @@ class Context:
         ms = C.c_float(0)
         self._check(self.lib.mtsgpu_trace_device(self.h, C.c_void_p(d_rays_ptr), n, mode, C.c_void_p(d_out_ptr), C.byref(ms)))
         return ms.value
+
+    def set_progress(self, fn=None, min_interval=0.0, want_film=True):
+        """mtsgpu_set_progress: fn(fraction, film or None) is called between wavefront batches on the rendering thread; film is a
+        (cropH, cropW, 5) copy of the accumulators at that point."""
+        if fn is None:
+            self._progress_cb = None
+            self._check(self.lib.mtsgpu_set_progress(self.h, C.cast(None, PROGRESS_FN), None, 0.0, 0))
+            return
+        shape = self.film_shape
+
+        def trampoline(_user, fraction, film_ptr):
+            film = None
+            if film_ptr:
+                film = np.ctypeslib.as_array(film_ptr, shape=(shape[0] * shape[1] * 5,)).reshape(shape).copy()
+            fn(float(fraction), film)
+        self._progress_cb = PROGRESS_FN(trampoline)          # keep the ctypes thunk alive
+        self._check(self.lib.mtsgpu_set_progress(self.h, self._progress_cb, None, float(min_interval), int(want_film)))
 
     def set_counters(self, enabled: bool):
         self._check(self.lib.mtsgpu_set_counters(self.h, int(enabled)))

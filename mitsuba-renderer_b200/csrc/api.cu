@@ -67,6 +67,8 @@ void mtsgpu_destroy(mtsgpu_ctx *ctx) {
 	}
 	cudaStreamDestroy(ctx->stream);
 	if (ctx->hCounts) cudaFreeHost(ctx->hCounts);
+	if (ctx->hProgressFilm) cudaFreeHost(ctx->hProgressFilm);
+	if (ctx->progressStream) { cudaStreamDestroy(ctx->progressStream); cudaEventDestroy(ctx->progressSnap); cudaEventDestroy(ctx->progressCopied); }
 	for (int i = 0; i < 16; ++i) if (ctx->pollEv[i]) cudaEventDestroy(ctx->pollEv[i]);
 	for (int k = 0; k < 2; ++k) for (cudaEvent_t e : ctx->evPool[k]) cudaEventDestroy(e);
 	delete ctx;
@@ -382,6 +384,13 @@ int mtsgpu_accel_info_get(mtsgpu_ctx *ctx, mtsgpu_accel_info *info) {
 	ENTER(ctx);
 	REQUIRE(ctx, ctx->built && info, MTSGPU_ERR_ARG, "accel_info: call mtsgpu_build_accel first");
 	*info = ctx->accel;
+	return MTSGPU_OK;
+}
+
+int mtsgpu_set_progress(mtsgpu_ctx *ctx, mtsgpu_progress_fn fn, void *user, double minIntervalSeconds, int wantFilm) {
+	ENTER(ctx);
+	REQUIRE(ctx, minIntervalSeconds >= 0, MTSGPU_ERR_ARG, "set_progress: negative interval");
+	ctx->progressFn = fn; ctx->progressUser = user; ctx->progressInterval = minIntervalSeconds; ctx->progressWantFilm = fn && wantFilm;
 	return MTSGPU_OK;
 }
 

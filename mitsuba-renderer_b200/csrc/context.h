@@ -94,6 +94,10 @@ struct mtsgpu_ctx {
 	cudaEvent_t pollEv[16] = {};     // one per ring slot
 	std::vector<cudaEvent_t> evPool[2];      // timing events of the traversal launches, two alternating sets
 	DevBuf dWfStats;
+	// progress / preview callback (mtsgpu_set_progress)
+	mtsgpu_progress_fn progressFn = nullptr; void *progressUser = nullptr; double progressInterval = 0; bool progressWantFilm = false;
+	cudaStream_t progressStream = nullptr; cudaEvent_t progressSnap = nullptr, progressCopied = nullptr;
+	DevBuf dProgressSnap; float *hProgressFilm = nullptr; size_t hProgressBytes = 0;
 	uint32_t pathCapacity = 0;
 };
 

@@ -22,6 +22,7 @@
 #include "bsdf.cuh"
 #include "sampling.cuh"
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
 
 #define TILE 16
@@ -645,6 +646,10 @@ static int launchShadowWf(mtsgpu_ctx *ctx, const float4 *rays, const float4 *pay
 	return MTSGPU_OK;
 }
 
+static double wallSeconds() {
+	return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 static int ensureWavefront(mtsgpu_ctx *ctx, uint32_t capacity) {
 	if (ctx->pathCapacity >= capacity) return MTSGPU_OK;
 	const size_t c = capacity;
@@ -729,7 +734,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 	cudaEvent_t evBegin = ctx->ev[0], evEnd = ctx->ev[1], evA = ctx->ev[2], evB = ctx->ev[3];
 	CUDA_TRY(ctx, cudaEventRecord(evBegin, st));
 	if (spp > 0) {
-		static const uint32_t slotsLog2 = getenv("MTSGPU_BATCH_LOG2") ? (uint32_t) std::min(std::max(atoi(getenv("MTSGPU_BATCH_LOG2")), 16), 28) : 27u;
+		const uint32_t slotsLog2 = getenv("MTSGPU_BATCH_LOG2") ? (uint32_t) std::min(std::max(atoi(getenv("MTSGPU_BATCH_LOG2")), 16), 28) : 27u;
 		// 228 B of queues + path state per slot => 30.6 GB at the default size (2^27 slots), allocated only as far as the job needs.
 		// Measured on C4 (B200): 2^25 -> 2^27 slots per batch = -11 % render time: every bounce of a batch is one launch of each
 		// kernel, and the late bounces (1-2 % of the rays) and each launch's drain phase weigh less in a larger batch.
@@ -814,6 +819,31 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 #define LAUNCH_SHADE(M, NIN, ROUND) do { if (bmp) k_shade<M, true><<<shadeGrid, WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, (NIN), (ROUND)); \
 			else k_shade<M, false><<<shadeGrid, WF_BLOCK, 0, st>>>(ctx->scene, ig, b, film, wf, (NIN), (ROUND)); S.kernelLaunches++; } while (0)
 		uint32_t batchIndex = 0;
+		// ---- progress / preview (mtsgpu_set_progress): a device-side snapshot of the film after a batch's splat, copied to pinned
+		// memory on a stream of its own; the callback runs from this loop once the copy has landed (never waited for)
+		const uint32_t batchesTotal = ((nTiles + tilesPerBatch - 1) / tilesPerBatch) * ((spp + sampleChunk - 1) / sampleChunk);
+		bool progressPending = false; double progressFraction = 0, progressLast = wallSeconds();
+		if (ctx->progressFn && !ctx->progressStream) {
+			CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->progressStream, cudaStreamNonBlocking));
+			CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->progressSnap, cudaEventDisableTiming));
+			CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->progressCopied, cudaEventDisableTiming));
+		}
+		if (ctx->progressFn && ctx->progressWantFilm) {
+			CUDA_TRY(ctx, ctx->dProgressSnap.alloc(filmFloats * sizeof(float)));
+			if (ctx->hProgressBytes < filmFloats * sizeof(float)) {
+				if (ctx->hProgressFilm) cudaFreeHost(ctx->hProgressFilm);
+				ctx->hProgressFilm = nullptr; ctx->hProgressBytes = 0;
+				CUDA_TRY(ctx, cudaMallocHost(&ctx->hProgressFilm, filmFloats * sizeof(float)));
+				ctx->hProgressBytes = filmFloats * sizeof(float);
+			}
+		}
+		auto progressDeliver = [&](bool wait) {
+			if (!progressPending) return;
+			if (wait) cudaEventSynchronize(ctx->progressCopied);
+			else if (cudaEventQuery(ctx->progressCopied) != cudaSuccess) return;
+			progressPending = false; progressLast = wallSeconds();
+			ctx->progressFn(ctx->progressUser, progressFraction, ctx->progressWantFilm ? ctx->hProgressFilm : nullptr);
+		};
 
 		for (uint32_t t0 = 0; t0 < nTiles && rc == MTSGPU_OK; t0 += tilesPerBatch) {
 			for (uint32_t s0 = 0; s0 < spp; s0 += sampleChunk, ++batchIndex) {
@@ -850,6 +880,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 							seen++;
 						}
 						if (dry) break;
+						progressDeliver(false);
 						wf.slotCur = slotBuf[cur]; wf.rayCur = rayBuf[cur]; wf.stateCur = stateBuf[cur];
 						wf.slotNext = slotBuf[cur ^ 1]; wf.rayNext = rayBuf[cur ^ 1]; wf.stateNext = stateBuf[cur ^ 1];
 						CUDA_TRY(ctx, stamp(evSet, 0));
@@ -894,8 +925,25 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 				k_splat<<<b.tileCount, TILE_PIX, splatSmem, st>>>(film, b, wf.li, wf.samplePos, dTable.as<float>(), dOutFilm);
 				S.kernelLaunches++;
 				CUDA_TRY(ctx, cudaGetLastError());
+				if (ctx->progressFn) {
+					progressDeliver(false);
+					if (!progressPending && batchIndex + 1 < batchesTotal && wallSeconds() - progressLast >= ctx->progressInterval) {
+						progressFraction = (double) (batchIndex + 1) / (double) batchesTotal;
+						if (ctx->progressWantFilm) {
+							CUDA_TRY(ctx, cudaMemcpyAsync(ctx->dProgressSnap.p, dOutFilm, filmFloats * sizeof(float), cudaMemcpyDeviceToDevice, st));
+							CUDA_TRY(ctx, cudaEventRecord(ctx->progressSnap, st));
+							CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->progressStream, ctx->progressSnap, 0));
+							CUDA_TRY(ctx, cudaMemcpyAsync(ctx->hProgressFilm, ctx->dProgressSnap.p, filmFloats * sizeof(float), cudaMemcpyDeviceToHost, ctx->progressStream));
+							CUDA_TRY(ctx, cudaEventRecord(ctx->progressCopied, ctx->progressStream));
+						} else {
+							CUDA_TRY(ctx, cudaEventRecord(ctx->progressCopied, st));
+						}
+						progressPending = true;
+					}
+				}
 			}
 		}
+		if (ctx->progressFn) progressDeliver(true);
 #undef LAUNCH_SHADE
 		CUDA_TRY(ctx, harvest(0)); CUDA_TRY(ctx, harvest(1));
 		{
@@ -919,7 +967,9 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 		S.closestNodeVisits = h[2]; S.closestTriTests = h[3]; S.shadowNodeVisits = h[4]; S.shadowTriTests = h[5];
 	}
 	if (stats) *stats = S;
-	return checkTraceFlags(ctx);
+	{ const int frc = checkTraceFlags(ctx); if (frc) return frc; }
+	if (ctx->progressFn) ctx->progressFn(ctx->progressUser, 1.0, nullptr);
+	return MTSGPU_OK;
 }
 
 // ================================================================================================

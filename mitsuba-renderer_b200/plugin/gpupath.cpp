@@ -48,6 +48,8 @@ public:
 		/* number of GPUs to shard the sample range over (devices device .. device+gpus-1) */
 		m_gpus = props.getInteger("gpus", 1);
 		m_seed = props.getInteger("seed", 0);
+		/* seconds between film previews (RenderQueue::signalRefresh) while the GPU renders; 0: after every wavefront batch */
+		m_refreshInterval = props.getFloat("refreshInterval", 2.0f);
 		AssertEx(m_rrDepth > 0, "rrDepth == 0 breaks the computation of alpha values!");
 		Assert(m_luminaireSamples + m_bsdfSamples > 0);
 	}
@@ -56,6 +58,7 @@ public:
 		m_mode = stream->readInt(); m_maxDepth = stream->readInt(); m_rrDepth = stream->readInt();
 		m_strictNormals = stream->readBool(); m_luminaireSamples = stream->readInt(); m_bsdfSamples = stream->readInt();
 		m_device = stream->readInt(); m_seed = stream->readInt(); m_gpus = stream->readInt();
+		m_refreshInterval = stream->readFloat();
 	}
 
 	void serialize(Stream *stream, InstanceManager *manager) const {
@@ -63,6 +66,7 @@ public:
 		stream->writeInt(m_mode); stream->writeInt(m_maxDepth); stream->writeInt(m_rrDepth);
 		stream->writeBool(m_strictNormals); stream->writeInt(m_luminaireSamples); stream->writeInt(m_bsdfSamples);
 		stream->writeInt(m_device); stream->writeInt(m_seed); stream->writeInt(m_gpus);
+		stream->writeFloat(m_refreshInterval);
 	}
 
 	Spectrum Li(const RayDifferential &, RadianceQueryRecord &) const {
@@ -735,9 +739,14 @@ private:
 		const size_t nPix = (size_t) csize.x * csize.y;
 		std::vector<float> accum(nPix * 5);
 		mtsgpu_stats stats;
+		ProgressReporter progress("Rendering", (long long) nPix * (long long) P.sppTotal, job);
+		RefreshState refresh = { &progress, film, queue, job, csize, coff, (long long) nPix * (long long) P.sppTotal, 0 };
+		/* previews need the whole film on one GPU; with several GPUs only the progress bar moves */
+		check(ctx, mtsgpu_set_progress(ctx, &GPUPathIntegrator::onProgress, &refresh, m_refreshInterval, ctxs.size() == 1 ? 1 : 0));
 		timer->reset();
 		const int rc = ctxs.size() == 1 ? mtsgpu_render(ctx, &P, &m_cancel, &accum[0], &stats)
 			: mtsgpu_render_multi(&ctxs[0], (int) ctxs.size(), &P, &m_cancel, &accum[0], &stats);   /* sample range split + NVLink peer reduce */
+		mtsgpu_set_progress(ctx, NULL, NULL, 0.0, 0);
 		if (rc == MTSGPU_ERR_CANCELLED)
 			return false;
 		check(ctx, rc);
@@ -747,8 +756,19 @@ private:
 			stats.samples * 1e-3 / std::max(stats.totalMs, 1e-3), stats.normalRays * 1e-6, stats.shadowRays * 1e-6,
 			stats.traceClosestMs, stats.traceAnyMs);
 
-		/* ---- hand {sum spec, sum alpha, sum weight} to the film as one full-frame ImageBlock, through the
-		        block's own wire format (ImageBlock::load, imageblock.cpp:89-106): there is no alpha setter ---- */
+		if (refresh.refreshes > 0)
+			film->clear();            /* the previews were put into the film; the final accumulators replace them */
+		ref<ImageBlock> block = makeBlock(&accum[0], csize, coff);
+		film->putImageBlock(block);
+		progress.finish();
+		queue->signalWorkEnd(job, block);
+		return true;
+	}
+
+	/* {sum spec, sum alpha, sum weight} as one full-frame ImageBlock, through the block's own wire format
+	   (ImageBlock::load, imageblock.cpp:89-106): there is no alpha setter */
+	static ref<ImageBlock> makeBlock(const float *accum, const Vector2i &csize, const Point2i &coff) {
+		const size_t nPix = (size_t) csize.x * csize.y;
 		ref<ImageBlock> block = new ImageBlock(csize, 0, true, true, false, false);
 		ref<MemoryStream> ms = new MemoryStream(nPix * 20 + 64);
 		coff.serialize(ms); csize.serialize(ms);
@@ -766,13 +786,31 @@ private:
 		ms->writeInt(0);
 		ms->setPos(0);
 		block->load(ms);
-		film->putImageBlock(block);
-		queue->signalWorkEnd(job, block);
-		return true;
+		return block;
+	}
+
+	/* Progress bar and preview while the GPU renders: what BlockedRenderProcess::processResult does after every block
+	   (renderproc.cpp:123-130: merge into the film, ProgressReporter::update, and the GUI / `-r` path through
+	   RenderQueue::signalRefresh, renderqueue.h:109-112). Called by the library between wavefront batches, on this thread. */
+	struct RefreshState {
+		ProgressReporter *progress; Film *film; RenderQueue *queue; const RenderJob *job;
+		Vector2i csize; Point2i coff; long long total; int refreshes;
+	};
+	static void onProgress(void *user, double fraction, const float *accum) {
+		RefreshState *r = static_cast<RefreshState *>(user);
+		r->progress->update((long long) (fraction * (double) r->total));
+		if (accum) {
+			r->film->clear();
+			ref<ImageBlock> block = makeBlock(accum, r->csize, r->coff);
+			r->film->putImageBlock(block);
+			r->queue->signalRefresh(r->job, NULL);
+			r->refreshes++;
+		}
 	}
 
 	int m_mode, m_maxDepth, m_rrDepth, m_luminaireSamples, m_bsdfSamples, m_device, m_seed, m_gpus;
 	bool m_strictNormals;
+	Float m_refreshInterval;      /* seconds between previews (property `refreshInterval`, default 2) */
 	volatile int m_cancel;
 };
 

@@ -200,6 +200,23 @@ static int cmdSplat(int argc, char **argv) {
 	return 0;
 }
 
+/* Counts what a GUI or the `-r` flush thread would see: refresh signals (renderqueue.h:109-112) and finished blocks. */
+class CountingListener : public RenderListener {
+public:
+	int refreshes, blocks; double weightAtLastRefresh; const RawFilm *film;
+	CountingListener(const RawFilm *f) : refreshes(0), blocks(0), weightAtLastRefresh(0), film(f) { }
+	void workBeginEvent(const RenderJob *, const RectangularWorkUnit *, int) { }
+	void workEndEvent(const RenderJob *, const ImageBlock *) { blocks++; }
+	void refreshEvent(const RenderJob *, const Bitmap *) {
+		refreshes++;
+		double w = 0;
+		const std::vector<float> &raw = film->raw();
+		for (size_t i = 4; i < raw.size(); i += 5) w += raw[i];
+		weightAtLastRefresh = w;
+	}
+	void finishJobEvent(const RenderJob *, bool) { }
+};
+
 static int cmdRender(int argc, char **argv) {
 	if (argc < 4) { std::cerr << "render SCENE OUT [threads] [integratorPlugin|-] [repeat]\n"; return 1; }
 	sio::Scene sf; sio::load(argv[2], sf);
@@ -214,6 +231,8 @@ static int cmdRender(int argc, char **argv) {
 
 	Built b = buildScene(sf, integ);
 	ref<RenderQueue> queue = new RenderQueue();
+	ref<CountingListener> listener = new CountingListener(b.film.get());
+	queue->registerListener(listener);
 	ref<RenderJob> job;
 	double dt = 1e30; std::string all;
 	for (int r = 0; r < repeat; ++r) {
@@ -231,9 +250,9 @@ static int cmdRender(int argc, char **argv) {
 	double samples = (double) sf.cropW * sf.cropH * sf.spp;
 	printf("{\"cmd\": \"render\", \"integrator\": \"%s\", \"threads\": %d, \"width\": %u, \"height\": %u, \"spp\": %u, "
 		"\"kd_build_s\": %.6f, \"render_s\": %.6f, \"render_s_all\": [%s], \"repeat\": %d, \"samples_per_s\": %.3f, "
-		"\"normal_rays\": \"%s\", \"shadow_rays\": \"%s\"}\n",
+		"\"refresh_events\": %d, \"film_weight_at_last_refresh\": %.3f, \"normal_rays\": \"%s\", \"shadow_rays\": \"%s\"}\n",
 		integ.empty() ? (sf.mode == 0 ? "path" : "direct") : integ.c_str(), threads, sf.cropW, sf.cropH, sf.spp,
-		b.buildSeconds, dt, all.c_str(), repeat, samples / dt,
+		b.buildSeconds, dt, all.c_str(), repeat, samples / dt, listener->refreshes, listener->weightAtLastRefresh,
 		statValue(stats, "Normal rays traced").c_str(), statValue(stats, "Shadow rays traced").c_str());
 	fflush(stdout);
 	job = NULL; queue = NULL;

@@ -321,6 +321,7 @@ static Built buildScene(const sio::Scene &s, const std::string &integratorOverri
 			p.setInteger("luminaireSamples", (int) s.nLumSamples);
 			p.setInteger("bsdfSamples", (int) s.nBsdfSamples);
 			if (getenv("MTS_ORACLE_GPUS")) p.setInteger("gpus", atoi(getenv("MTS_ORACLE_GPUS")));
+			if (getenv("MTS_ORACLE_REFRESH")) p.setFloat("refreshInterval", (Float) atof(getenv("MTS_ORACLE_REFRESH")));
 		}
 		ref<Integrator> integrator = static_cast<Integrator *>(create(MTS_CLASS(Integrator), p));
 		scene->addChild("", integrator);
