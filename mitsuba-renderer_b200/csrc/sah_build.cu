@@ -21,7 +21,9 @@
 #include <climits>
 #include <cfloat>
 
+#ifndef SAH_BINS
 #define SAH_BINS   16
+#endif
 #define SAH_SMALL  4
 #define SAH_MAX_SAH_LEVEL 64      // below this many levels every split is a median split: bounds the depth
 

@@ -16,7 +16,7 @@ def main():
     which = sys.argv[1] if len(sys.argv) > 1 else "c4"
     res = int(sys.argv[2]) if len(sys.argv) > 2 else 2048
     scene = scenes.path_scene() if which == "c4" else scenes.direct_scene()
-    ctx = api.Context(0)
+    ctx = api.Context(0, os.environ.get("MTSGPU_LIB"))
     ctx.upload_scene(scene)
     print("accel", ctx.accel_info())
     prim = scenes.coherent_rays(scene, res)
