@@ -555,12 +555,12 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 			}
 			// (B) leaves. ncu's source view of the per-lane loop (profiles/r02_q2_*): 37 % of all issue slots at 3 to 5 active
 			// lanes. Triangle variant (!SPH): the warp shares the work out. Up to 8 lanes that hold a leaf ("owners") post their
-			// ray and leaf word in shared memory; lane w then tests triangle (w & 3) of owner (w >> 2) and posts {t, u, v,
-			// accepted}; each owner folds its (up to four) results in triangle order with the shrinking maxt, which gives
-			// the very result of the sequential loop (sahkdtree3.h:278-283: a later equal t replaces an earlier one).
+			// ray and leaf word in shared memory; lane w then tests triangle (w & 3) of owner (w >> 2); the four lanes of an owner
+			// fold their results by shuffles — smallest t, of equal t the later triangle — which is the very result of the
+			// sequential loop (sahkdtree3.h:278-283: a later equal t replaces an earlier one).
 			if (!SPH) {
 				static_assert(BVH_LEAF_MAX <= 4, "the shared leaf phase gives every owner four test slots");
-				__shared__ float4 xRayA[TRACE_BLOCK / 32][8], xRayB[TRACE_BLOCK / 32][8], xResult[TRACE_BLOCK / 32][32];
+				__shared__ float4 xRayA[TRACE_BLOCK / 32][8], xRayB[TRACE_BLOCK / 32][8];
 				__shared__ uint32_t xLeaf[TRACE_BLOCK / 32][8];
 				const uint32_t wid = threadIdx.x >> 5;
 				const bool has = s.active && s.leaf != BVH_EMPTY;
@@ -575,7 +575,7 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 					}
 					__syncwarp();
 					const int slot = lane >> 2, k = lane & 3;
-					float4 res = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+					float rt = 0.0f, ru = 0.0f, rv = 0.0f; int rk = -1;          // this lane's result; rk = triangle slot, -1: not accepted
 					if (base + slot < nOwners) {
 						const uint32_t leaf = xLeaf[wid][slot];
 						if ((uint32_t) k <= ((leaf >> 28) & 7u)) {
@@ -586,23 +586,33 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 							if (!(SHADOW && (kraw & TRI_NONOCCLUDER))) {
 								if (COUNT) triTests++;
 								RayIn rr; rr.ox = ra.x; rr.oy = ra.y; rr.oz = ra.z; rr.mint = 0; rr.dx = rb.x; rr.dy = rb.y; rr.dz = rb.z; rr.maxt = 0;
-								float u, v, t;
-								if (triAccelTest(q0, q1, q2, kraw & TRI_K_MASK, rr, ra.w, rb.w, u, v, t)) res = make_float4(t, u, v, 1.0f);
+								if (triAccelTest(q0, q1, q2, kraw & TRI_K_MASK, rr, ra.w, rb.w, ru, rv, rt)) rk = k;
 							}
 						}
 					}
-					xResult[wid][lane] = res;
-					__syncwarp();
-					if (mine) {
-						const uint32_t first = s.leaf & 0x0FFFFFFFu;
+					if (SHADOW) {
+						// any-hit: an owner only needs to know whether one of its four lanes accepted
+						const uint32_t acc = __ballot_sync(0xFFFFFFFFu, rk >= 0);
+						if (mine && ((acc >> (4 * (rank - base))) & 0xFu)) s.found = true;
+					} else {
+						// closest hit: the four lanes of an owner fold their results with two butterfly steps — smallest t wins, of
+						// equal t the LATER triangle (what the sequential loop's "t <= maxt, then maxt = t" leaves behind) — and the
+						// owner fetches the winner with four shuffles
 #pragma unroll
-						for (int j = 0; j < 4; ++j) {
-							const float4 r4 = xResult[wid][(rank - base) * 4 + j];
-							if (r4.w != 0.0f && (SHADOW || r4.x <= s.maxt)) {
-								s.found = true;
-								if (!SHADOW) { s.maxt = r4.x; s.t = r4.x; s.u = r4.y; s.v = r4.z; s.tri = first + j; }
-							}
+						for (int m = 1; m <= 2; m <<= 1) {
+							const float ot = __shfl_xor_sync(0xFFFFFFFFu, rt, m), ou = __shfl_xor_sync(0xFFFFFFFFu, ru, m), ov = __shfl_xor_sync(0xFFFFFFFFu, rv, m);
+							const int ok = __shfl_xor_sync(0xFFFFFFFFu, rk, m);
+							if (ok >= 0 && (rk < 0 || ot < rt || (ot == rt && ok > rk))) { rt = ot; ru = ou; rv = ov; rk = ok; }
 						}
+						const int src = mine ? 4 * (rank - base) : 0;
+						const float wt = __shfl_sync(0xFFFFFFFFu, rt, src), wu = __shfl_sync(0xFFFFFFFFu, ru, src), wv = __shfl_sync(0xFFFFFFFFu, rv, src);
+						const int wk = __shfl_sync(0xFFFFFFFFu, rk, src);
+						if (mine && wk >= 0) {          // accepted against the owner's [mint, maxt] as posted, i.e. wt <= s.maxt
+							s.found = true;
+							s.maxt = wt; s.t = wt; s.u = wu; s.v = wv; s.tri = (s.leaf & 0x0FFFFFFFu) + (uint32_t) wk;
+						}
+					}
+					if (mine) {
 						s.leaf = BVH_EMPTY;
 						if (SHADOW && s.found) { s.sp = 0; s.cur = BVH_EMPTY; }          // any-hit: done
 						else if ((s.cur & BVH_LEAF) && s.cur != BVH_EMPTY) { s.leaf = s.cur; STACK_POP(s.cur); }
