@@ -5,6 +5,8 @@
 #include <vector>
 #include <cstdio>
 #include <cstdarg>
+#include <cstring>
+#include <memory>
 #include "types.cuh"
 
 #define MTSGPU_PIPE_CHUNKS 16
@@ -26,9 +28,21 @@ struct DevBuf {
 	template <typename T> T *as() const { return static_cast<T *>(p); }
 };
 
+// std::vector whose resize() leaves trivially constructible elements uninitialised: the mesh copies of a large scene are
+// filled by a parallel memcpy right after (value-initialising 200 MB first costs as much as the copy)
+template <typename T> struct NoInitAlloc : std::allocator<T> {
+	template <typename U> struct rebind { using other = NoInitAlloc<U>; };
+	NoInitAlloc() = default;
+	template <typename U> NoInitAlloc(const NoInitAlloc<U> &) { }
+	template <typename U> void construct(U *p) noexcept { ::new (static_cast<void *>(p)) U; }
+	template <typename U, typename... A> void construct(U *p, A &&... a) { ::new (static_cast<void *>(p)) U(std::forward<A>(a)...); }
+};
+typedef std::vector<float, NoInitAlloc<float> > HostFloats;
+typedef std::vector<uint32_t, NoInitAlloc<uint32_t> > HostIndices;
+
 struct HostMesh {
 	uint32_t nVert, nTri; int materialId, emitterId; bool hasNormals;
-	std::vector<float> pos, nrm, uv; std::vector<uint32_t> tri;   // uv empty: no texture coordinates
+	HostFloats pos, nrm, uv; HostIndices tri;   // uv empty: no texture coordinates
 	// analytic sphere (mtsgpu_upload_sphere): one vertex (the centre) and one primitive {0, SPHERE_MARK, SPHERE_MARK}
 	bool sphere = false, inverted = false; float radius = 0, o2w[16] = {}, w2o[16] = {};
 	// instance of a shape group (mtsgpu_upload_instance): two vertices (the corners of its world box, filled at build
