@@ -104,6 +104,9 @@ def load_library(path: Optional[str] = None):
     if not os.path.exists(path):
         raise MtsGpuError(-1, f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
                               "(there is no CPU fallback)")
+    if "MTSGPU_HOST_THREADS" not in os.environ and int(os.environ.get("LOCAL_WORLD_SIZE", "1")) > 1:
+        # one process per GPU (torchrun): the ranks of a node share its cores for the host-side mesh copies
+        os.environ["MTSGPU_HOST_THREADS"] = str(max(1, (os.cpu_count() or 1) // int(os.environ["LOCAL_WORLD_SIZE"])))
     lib = C.CDLL(path)
     vp, fp, u32p = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint32)
     lib.mtsgpu_create.argtypes = [C.c_int, C.POINTER(vp)]

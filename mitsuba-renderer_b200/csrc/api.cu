@@ -1,5 +1,6 @@
 // C ABI entry points of libmtscuda.so (declared in include/mtsgpu.h).
 #include "context.h"
+#include <omp.h>
 #include <cstring>
 #include <cmath>
 #include <algorithm>
@@ -29,11 +30,22 @@ template <typename V, typename T> static void hostCopy(V &dst, const T *src, siz
 	dst.resize(n);                                   // NoInitAlloc: no value-initialisation pass
 	const size_t chunk = (size_t) 1 << 18;           // elements
 	const int64_t nChunks = (int64_t) ((n + chunk - 1) / chunk);
-#pragma omp parallel for schedule(static) if (nChunks > 4)
+#pragma omp parallel for schedule(static) num_threads(hostThreads()) if (nChunks > 4)
 	for (int64_t c = 0; c < nChunks; ++c) {
 		const size_t b = (size_t) c * chunk, e = std::min(n, b + chunk);
 		memcpy(dst.data() + b, src + b, (e - b) * sizeof(T));
 	}
+}
+
+// Threads for the host-side copies and flatten loops: MTSGPU_HOST_THREADS, else all cores (at most 16). Not OMP_NUM_THREADS:
+// launchers that start one process per GPU set it to 1 for every rank (torchrun does), which made upload + build 2.4x slower.
+int hostThreads() {
+	static const int n = [] {
+		const char *e = getenv("MTSGPU_HOST_THREADS");
+		const int want = e ? atoi(e) : std::min(omp_get_num_procs(), 16);
+		return std::min(std::max(want, 1), 64);
+	}();
+	return n;
 }
 
 extern "C" {

@@ -749,7 +749,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 			const float w = m.sphere ? m.radius : 0.0f;
 			const int64_t nv = m.nVert, nt = m.nTri;
 			float4 *dp = pos.data() + vOff, *dn = nrm.data() + vOff;
-#pragma omp parallel for schedule(static) if (nv > 65536)
+#pragma omp parallel for schedule(static) num_threads(hostThreads()) if (nv > 65536)
 			for (int64_t v = 0; v < nv; ++v) {
 				dp[v] = make_float4(mp[3*v], mp[3*v+1], mp[3*v+2], w);
 				dn[v] = mn ? make_float4(mn[3*v], mn[3*v+1], mn[3*v+2], 0) : make_float4(0, 0, 0, 0);
@@ -760,7 +760,7 @@ int buildAccel(mtsgpu_ctx *ctx) {
 			else {
 				const uint32_t *mt = m.tri.data();
 				int64_t bad = -1;
-#pragma omp parallel for schedule(static) reduction(max : bad) if (nt > 65536)
+#pragma omp parallel for schedule(static) num_threads(hostThreads()) reduction(max : bad) if (nt > 65536)
 				for (int64_t t = 0; t < nt; ++t) {
 					const uint32_t a = mt[3*t], b = mt[3*t+1], c = mt[3*t+2];
 					if (a >= m.nVert || b >= m.nVert || c >= m.nVert) bad = std::max(bad, t);

@@ -129,6 +129,7 @@ int rebuildLuminaireCdf(mtsgpu_ctx *ctx, bool importance);
 unsigned tracePersistentBlocks(mtsgpu_ctx *ctx, size_t n);
 int traceRayCounter(mtsgpu_ctx *ctx, uint32_t **out);
 int launchTrace(mtsgpu_ctx *ctx, const float4 *dRays, size_t n, int mode, void *dOut, uint64_t *dCounters);
+int hostThreads();      // api.cu: threads of the host-side copy / flatten loops (MTSGPU_HOST_THREADS)
 int checkTraceFlags(mtsgpu_ctx *ctx);
 int traceRefetchBelow();
 int traceLeafThreshold();
