@@ -109,6 +109,32 @@ __device__ __forceinline__ uint32_t blockAppend(uint32_t *counter, bool pred, ui
 	return pos + __popc(mask & ((1u << lane) - 1u));
 }
 
+// Two queues at once: the counters of the next-ray and the shadow queue are the halves of one aligned 64-bit word, so a
+// block reserves room in both with ONE atomic behind ONE barrier pair. With an append per queue k_shade's blocks sat at
+// barriers for two atomic round trips per 256 entries (ncu, profiles/r02_final_c4_bounce2: barrier = 2.8 of 13.7 stall
+// cycles per issue). Per-warp counts travel packed (16 bits each: a block emits at most WF_BLOCK entries per queue and call).
+__device__ __forceinline__ void blockAppend2(unsigned long long *counter2, bool predA, bool predB, uint32_t (*agg)[WF_BLOCK / 32],
+		unsigned long long *base, int parity, uint32_t &posA, uint32_t &posB) {
+	static_assert(WF_BLOCK < 65536, "packed per-warp counts");
+	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	const uint32_t maskA = __ballot_sync(0xFFFFFFFFu, predA), maskB = __ballot_sync(0xFFFFFFFFu, predB);
+	if (lane == 0) agg[parity][warp] = __popc(maskA) | (__popc(maskB) << 16);
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		uint32_t total = 0;
+#pragma unroll
+		for (int w = 0; w < WF_BLOCK / 32; ++w) total += agg[parity][w];
+		base[parity] = total ? atomicAdd(counter2, (unsigned long long) (total & 0xFFFFu) | ((unsigned long long) (total >> 16) << 32)) : 0ull;
+	}
+	__syncthreads();
+	const unsigned long long b = base[parity];
+	uint32_t before = 0;
+	for (uint32_t w = 0; w < warp; ++w) before += agg[parity][w];
+	const uint32_t lt = (1u << lane) - 1u;
+	posA = (uint32_t) b + (before & 0xFFFFu) + __popc(maskA & lt);
+	posB = (uint32_t) (b >> 32) + (before >> 16) + __popc(maskB & lt);
+}
+
 __device__ __forceinline__ void slotToPixel(const BatchDesc &b, const FilmDev &film, uint32_t slot,
 		int &px, int &py, uint32_t &sample) {
 	const uint32_t pix = slot % TILE_PIX;
@@ -293,7 +319,8 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 	// 9.9 of 32 lanes active on the bounce-2 queue) — then shades the listed ones with full warps. The list keeps the queue order.
 	__shared__ uint32_t sList[SHADE_CHUNK];
 	__shared__ uint32_t sCount[SHADE_CHUNK / 32];
-	__shared__ uint32_t sAggR[2][WF_BLOCK / 32], sAggS[2][WF_BLOCK / 32], sBaseR[2], sBaseS[2];
+	__shared__ uint32_t sAgg[2][WF_BLOCK / 32];
+	__shared__ unsigned long long sBase[2];
 	int parity = 0;
 	const uint32_t n = *nIn;
 	const uint32_t *slots = (MODE == 1) ? wf.slotPrim : wf.slotCur;
@@ -502,7 +529,9 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		if (emitRay) { st0 = thr4; st1 = bv4; }
 	}
 
-	const uint32_t rp = blockAppend(&wf.counters[1], emitRay, sAggR, sBaseR, parity);
+	uint32_t rp, sp;
+	blockAppend2(reinterpret_cast<unsigned long long *>(&wf.counters[2]), emitRay, emitShadow, sAgg, sBase, parity, rp, sp);
+	parity ^= 1;
 	if (emitRay) {
 		wf.slotNext[rp] = slot;
 		wf.rayNext[2 * (size_t) rp] = nr0;
@@ -510,8 +539,6 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 		wf.stateNext[2 * (size_t) rp] = st0;
 		wf.stateNext[2 * (size_t) rp + 1] = st1;
 	}
-	const uint32_t sp = blockAppend(&wf.counters[2], emitShadow, sAggS, sBaseS, parity);
-	parity ^= 1;
 	if (emitShadow) {
 		wf.shadowRay[2 * (size_t) sp] = sr0;
 		wf.shadowRay[2 * (size_t) sp + 1] = sr1;
@@ -523,17 +550,17 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 }
 
 // End of a bounce: add the queue lengths to the statistics, make the next ray queue the current one, empty the others.
-// counters: [0] current ray queue, [1] next ray queue, [2] shadow queue; stats: [0] camera rays, [1] closest-hit queries, [2] shadow queries
+// counters: [0] current ray queue, [2] next ray queue, [3] shadow queue ([2] and [3] are one 64-bit word for blockAppend2); stats: [0] camera rays, [1] closest-hit queries, [2] shadow queries
 __global__ void k_advance(uint32_t *counters, unsigned long long *stats, int what) {
 	if (what == 0) { stats[0] += counters[0]; return; }                     // after k_generate
 	if (what == 1) {                                                        // path: one bounce done
-		stats[1] += counters[0]; stats[2] += counters[2];
-		counters[0] = counters[1]; counters[1] = 0; counters[2] = 0;
+		stats[1] += counters[0]; stats[2] += counters[3];
+		counters[0] = counters[2]; counters[2] = 0; counters[3] = 0;
 		return;
 	}
 	if (what == 2) { stats[1] += counters[0]; return; }                     // direct: primary hits traced
-	stats[1] += counters[1]; stats[2] += counters[2];                       // direct: one round done (the primary queue stays)
-	counters[1] = 0; counters[2] = 0;
+	stats[1] += counters[2]; stats[2] += counters[3];                       // direct: one round done (the primary queue stays)
+	counters[2] = 0; counters[3] = 0;
 }
 
 // ImageBlock::putSample (imageblock.h:80-138) for all samples of one tile, accumulated in shared
@@ -780,8 +807,8 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 		if (P->mode == MTSGPU_MODE_DIRECT) ig.strictNormals = 0;     // MIDirectIntegrator has no such property
 		const int splatSmem = (TILE + 2 * film.border) * (TILE + 2 * film.border) * 5 * (int) sizeof(float);
 
-		// ---- no host round trip inside a batch: queue lengths stay in device memory (counters[0] current ray queue, [1] next ray
-		// queue, [2] shadow queue; k_advance rotates them and keeps the statistics), every kernel reads its own length, and
+		// ---- no host round trip inside a batch: queue lengths stay in device memory (counters[0] current ray queue, [2] next ray
+		// queue, [3] shadow queue; k_advance rotates them and keeps the statistics), every kernel reads its own length, and
 		// the host only learns — a few bounces late, through an asynchronous copy it polls — when a batch has run dry.
 		if (!ctx->hCounts) CUDA_TRY(ctx, cudaMallocHost(&ctx->hCounts, WF_POLL_RING * sizeof(uint32_t)));     // pinned, kept for the context's lifetime
 		volatile uint32_t *hRing = ctx->hCounts;
@@ -888,7 +915,7 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 						CUDA_TRY(ctx, stamp(evSet, 1));
 						LAUNCH_SHADE(0, wf.counters, 0u);
 						CUDA_TRY(ctx, stamp(evSet, 2));
-						if (launchShadowWf(ctx, wf.shadowRay, wf.shadowPayload, wf.counters + 2, wf.li, persistShadow)) return fail(MTSGPU_ERR_CUDA);
+						if (launchShadowWf(ctx, wf.shadowRay, wf.shadowPayload, wf.counters + 3, wf.li, persistShadow)) return fail(MTSGPU_ERR_CUDA);
 						CUDA_TRY(ctx, stamp(evSet, 3));
 						k_advance<<<1, 1, 0, st>>>(wf.counters, dStats, 1);
 						S.kernelLaunches += 3;
@@ -911,12 +938,12 @@ int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *P, volatile const 
 						wf.slotCur = slotBuf[0]; wf.rayCur = rayBuf[0]; wf.stateCur = stateBuf[0];
 						LAUNCH_SHADE(1, wf.counters, (uint32_t) r);
 						CUDA_TRY(ctx, stamp(evSet, 2));
-						if (launchShadowWf(ctx, wf.shadowRay, wf.shadowPayload, wf.counters + 2, wf.li, persistShadow)) return fail(MTSGPU_ERR_CUDA);
+						if (launchShadowWf(ctx, wf.shadowRay, wf.shadowPayload, wf.counters + 3, wf.li, persistShadow)) return fail(MTSGPU_ERR_CUDA);
 						CUDA_TRY(ctx, stamp(evSet, 3));
 						CUDA_TRY(ctx, stamp(evSet, 0));
-						if (launchClosestWf(ctx, wf.rayCur, wf.counters + 1, wf.hit, persistClosest)) return fail(MTSGPU_ERR_CUDA);
+						if (launchClosestWf(ctx, wf.rayCur, wf.counters + 2, wf.hit, persistClosest)) return fail(MTSGPU_ERR_CUDA);
 						CUDA_TRY(ctx, stamp(evSet, 1));
-						LAUNCH_SHADE(2, wf.counters + 1, (uint32_t) r);
+						LAUNCH_SHADE(2, wf.counters + 2, (uint32_t) r);
 						k_advance<<<1, 1, 0, st>>>(wf.counters, dStats, 3);
 						S.kernelLaunches += 3;
 					}
