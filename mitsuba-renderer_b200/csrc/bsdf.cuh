@@ -23,15 +23,17 @@
 
 // ---- src/libcore/util.cpp helpers ---------------------------------------------------------------
 __device__ inline V3 sphericalDirection(float theta, float phi) {           // util.cpp:543-550
-	const float sinTheta = mts_sin(theta);
-	return v3(sinTheta * mts_cos(phi), sinTheta * mts_sin(phi), mts_cos(theta));
+	float sinTheta, cosTheta, sinPhi, cosPhi;
+	mts_sincos(theta, sinTheta, cosTheta); mts_sincos(phi, sinPhi, cosPhi);
+	return v3(sinTheta * cosPhi, sinTheta * sinPhi, cosTheta);
 }
 
 __device__ inline V3 squareToHemispherePSA(float sx, float sy) {            // util.cpp:572-588
 	const float r = sqrtf(sx);
 	const float phi = 2.0f * MTS_PI * sy;
-	const float dirX = r * mts_cos(phi);
-	const float dirY = r * mts_sin(phi);
+	float sinPhi, cosPhi; mts_sincos(phi, sinPhi, cosPhi);
+	const float dirX = r * cosPhi;
+	const float dirY = r * sinPhi;
 	const float z = sqrtf(1 - fminf(1.0f, dirX * dirX + dirY * dirY));
 	if (z == 0)
 		return normalize(v3(dirX, dirY, MTS_EPSILON));
@@ -80,7 +82,7 @@ __device__ inline float frameTanTheta(V3 v) {                                // 
 // ---- Beckmann microfacet terms shared by microfacet.cpp:95-134 and roughmetal.cpp:75-114 -----------
 __device__ inline float beckmannD(V3 m, float alphaB) {
 	const float ex = frameTanTheta(m) / alphaB;
-	return mts_exp(-(ex * ex)) / (MTS_PI * alphaB * alphaB * mts_pow(m.z, 4.0f));
+	return mts_exp(-(ex * ex)) / (MTS_PI * alphaB * alphaB * mts_pow4(m.z));
 }
 
 __device__ inline V3 sampleBeckmannD(float sx, float sy, float alphaB) {
@@ -127,7 +129,7 @@ __device__ inline float rgEvalD(V3 m, float alpha, int distr) {                 
 	float result;
 	if (distr == 0) {
 		const float ex = frameTanTheta(m) / alpha;
-		result = mts_exp(-(ex * ex)) / (MTS_PI * alpha * alpha * mts_pow(m.z, 4.0f));
+		result = mts_exp(-(ex * ex)) / (MTS_PI * alpha * alpha * mts_pow4(m.z));
 	} else if (distr == 1) {
 		result = (alpha + 2) * MTS_INV_TWOPI * mts_pow(m.z, alpha);
 	} else {
@@ -266,7 +268,7 @@ __device__ inline float wardSpecRef(const MaterialDev &m, V3 wi, V3 wo) {       
 	const int model = (int) m.p[12];
 	if (model == 0) factor1 = 1.0f / (4.0f * MTS_PI * ax * ay * sqrtf(wi.z * wo.z));
 	else if (model == 1) factor1 = 1.0f / (4.0f * MTS_PI * ax * ay * wi.z * wo.z);
-	else factor1 = (float) ((double) dot(H, H) / ((double) (MTS_PI * ax * ay) * pow((double) H.z, 4.0)));
+	else factor1 = (float) ((double) dot(H, H) / ((double) (MTS_PI * ax * ay) * mts_pow4d(H.z)));
 	const float factor2 = H.x / ax, factor3 = H.y / ay;
 	const float exponent = -(factor2 * factor2 + factor3 * factor3) / (H.z * H.z);
 	return factor1 * mts_exp(exponent) * m.p[7];
@@ -274,7 +276,7 @@ __device__ inline float wardSpecRef(const MaterialDev &m, V3 wi, V3 wo) {       
 __device__ inline float wardPdfSpec(const MaterialDev &m, V3 wi, V3 wo) {                    // ward.cpp:196-205
 	const float ax = m.p[8], ay = m.p[9];
 	const V3 H = normalize(wi + wo);
-	const float factor1 = (float) (1.0 / ((double) (4.0f * MTS_PI * ax * ay * dot(H, wi)) * pow((double) H.z, 3.0)));
+	const float factor1 = (float) (1.0 / ((double) (4.0f * MTS_PI * ax * ay * dot(H, wi)) * ((double) H.z * (double) H.z * (double) H.z)));
 	const float factor2 = H.x / ax, factor3 = H.y / ay;
 	const float exponent = -(factor2 * factor2 + factor3 * factor3) / (H.z * H.z);
 	return factor1 * mts_exp(exponent);
