@@ -693,26 +693,37 @@ __device__ inline float bsdfPdf(const MaterialDev &m, V3 wi, V3 wo) {
 	const float pdf = bsdfPdf_two(m, wi, wo);
 	return (m.type & MTSGPU_BSDF_MASKED) ? pdf * maskOpacity(m) : pdf;
 }
+// (Both samplers reach the nested BSDF through ONE call site: with a call in the masked and one in the plain branch ptxas kept
+// the nested sampler — 20 000 instructions — out of line, and with it the material record, wo, pdf and type in local memory.)
 __device__ inline V3 bsdfSample2(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, uint32_t &type) {
-	if (!(m.type & MTSGPU_BSDF_MASKED)) return bsdfSample2_two(m, wi, sx, sy, wo, type);
-	const float probBSDF = maskOpacity(m);                       // mask.cpp:91-112
-	if (sx <= probBSDF) return bsdfSample2_two(m, wi, sx / probBSDF, sy, wo, type);
-	wo = v3(-wi.x, -wi.y, -wi.z);
-	type = BSDF_DELTA_TRANSMISSION;
-	const float r = 1 / fabsf(wo.z);
-	return v3(r, r, r);
+	const bool masked = (m.type & MTSGPU_BSDF_MASKED) != 0;
+	if (masked) {
+		const float probBSDF = maskOpacity(m);                   // mask.cpp:91-112
+		if (!(sx <= probBSDF)) {
+			wo = v3(-wi.x, -wi.y, -wi.z);
+			type = BSDF_DELTA_TRANSMISSION;
+			const float r = 1 / fabsf(wo.z);
+			return v3(r, r, r);
+		}
+		sx = sx / probBSDF;
+	}
+	return bsdfSample2_two(m, wi, sx, sy, wo, type);
 }
 __device__ inline V3 bsdfSample3(const MaterialDev &m, V3 wi, float sx, float sy, V3 &wo, float &pdf, uint32_t &type) {
-	if (!(m.type & MTSGPU_BSDF_MASKED)) return bsdfSample3_two(m, wi, sx, sy, wo, pdf, type);
-	const float probBSDF = maskOpacity(m);                       // mask.cpp:125-147
-	if (sx <= probBSDF) {
-		const V3 result = bsdfSample3_two(m, wi, sx / probBSDF, sy, wo, pdf, type) * probBSDF;
-		pdf *= probBSDF;
-		return result;
+	const bool masked = (m.type & MTSGPU_BSDF_MASKED) != 0;
+	float probBSDF = 1.0f;
+	if (masked) {
+		probBSDF = maskOpacity(m);                               // mask.cpp:125-147
+		if (!(sx <= probBSDF)) {
+			wo = v3(-wi.x, -wi.y, -wi.z);
+			type = BSDF_DELTA_TRANSMISSION;
+			pdf = (1 - probBSDF) * fabsf(wo.z);
+			const float r = 1 - probBSDF;
+			return v3(r, r, r);
+		}
+		sx = sx / probBSDF;
 	}
-	wo = v3(-wi.x, -wi.y, -wi.z);
-	type = BSDF_DELTA_TRANSMISSION;
-	pdf = (1 - probBSDF) * fabsf(wo.z);
-	const float r = 1 - probBSDF;
-	return v3(r, r, r);
+	V3 result = bsdfSample3_two(m, wi, sx, sy, wo, pdf, type);
+	if (masked) { result = result * probBSDF; pdf *= probBSDF; }
+	return result;
 }
