@@ -307,6 +307,21 @@ __device__ __forceinline__ bool nextEvent(const DeviceScene &sc, const Integrato
 
 // One shading step for the queue entry i. MODE 0 = path, 1 = direct (primary pass), 2 = direct (secondary pass).
 // BMP: the scene has bitmap textures or instances (the variant without them carries none of that code).
+#ifndef SHADE_BINS
+#define SHADE_BINS 4      // BSDF classes k_shade orders its list by (1: queue order only)
+#endif
+// Class of the BSDF a hit will run: 0 ideally diffuse or none, 1 delta (mirror, dielectric), 2 Beckmann microfacet (roughmetal,
+// microfacet), 3 the rest (phong, ward, roughglass). Only the order of the work depends on it.
+__device__ __forceinline__ uint32_t shadeClass(const DeviceScene &sc, uint32_t tri) {
+	const uint32_t shape = __float_as_uint(__ldg(&sc.shadeTris[6 * (size_t) tri].w));
+	const int mat = sc.shapes[shape].materialId;
+	if (mat < 0) return 0u;
+	const uint32_t t = sc.materials[mat].type & MTSGPU_BSDF_TYPE_MASK;
+	if (t == MTSGPU_BSDF_ROUGHMETAL || t == MTSGPU_BSDF_MICROFACET) return 2u % SHADE_BINS;
+	if (t == MTSGPU_BSDF_MIRROR || t == MTSGPU_BSDF_DIELECTRIC) return 1u % SHADE_BINS;
+	if (t == MTSGPU_BSDF_LAMBERTIAN || t == MTSGPU_BSDF_DIFFTRANS) return 0u;
+	return 3u % SHADE_BINS;
+}
 template <int MODE, bool BMP>
 #ifndef SHADE_MIN_BLOCKS
 #define SHADE_MIN_BLOCKS 3
@@ -318,7 +333,8 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 	// half of the rays have left the scene, and a miss without a background luminaire changes nothing (ncu, r02_shade_base:
 	// 9.9 of 32 lanes active on the bounce-2 queue) — then shades the listed ones with full warps. The list keeps the queue order.
 	__shared__ uint32_t sList[SHADE_CHUNK];
-	__shared__ uint32_t sCount[SHADE_CHUNK / 32];
+	__shared__ uint32_t sCount[SHADE_BINS * (SHADE_CHUNK / 32)];      // per (class, warp-sized piece of the chunk): entries, then their offset in the list
+	__shared__ uint32_t sListed;
 	__shared__ uint32_t sAgg[2][WF_BLOCK / 32];
 	__shared__ unsigned long long sBase[2];
 	int parity = 0;
@@ -328,29 +344,48 @@ k_shade(const DeviceScene sc, const IntegratorDev ig, const BatchDesc b, const F
 	const uint4 *hits = (MODE == 1) ? wf.hitPrim : wf.hit;
 	const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
 	for (uint32_t chunk0 = blockIdx.x * SHADE_CHUNK; chunk0 < n; chunk0 += gridDim.x * SHADE_CHUNK) {
-	uint32_t needMask[SHADE_CHUNK / WF_BLOCK];
+	// The list is ordered by BSDF class, queue order within a class (a counting sort over the chunk): the classes differ in the
+	// code they run — ncu on the C4 queues: the rough-metal sampling code ran with 13.6 of 31 lanes, the other lanes held hits on
+	// the glass spheres — so warps that see one class run it with full lanes. The class of a hit costs one sector of its shading
+	// record (fetched again, from cache, by the shading pass) and two table lookups.
+	uint32_t ownMask[SHADE_CHUNK / WF_BLOCK], ownBin[SHADE_CHUNK / WF_BLOCK];
 #pragma unroll
 	for (int k = 0; k < SHADE_CHUNK / WF_BLOCK; ++k) {
 		const uint32_t idx = chunk0 + k * WF_BLOCK + threadIdx.x;
-		const bool need = idx < n && (sc.background >= 0 || __ldg(&hits[idx].w) != 0xFFFFFFFFu);
-		needMask[k] = __ballot_sync(0xFFFFFFFFu, need);
-		if (lane == 0) sCount[k * (WF_BLOCK / 32) + warp] = __popc(needMask[k]);
-	}
-	__syncthreads();
-	uint32_t listed = 0;
-	{
-		uint32_t run = 0;
+		const uint32_t tri = idx < n ? __ldg(&hits[idx].w) : 0xFFFFFFFFu;
+		const bool need = idx < n && (sc.background >= 0 || tri != 0xFFFFFFFFu);
+		uint32_t bin = 0;
+		if (SHADE_BINS > 1 && tri != 0xFFFFFFFFu) bin = shadeClass(sc, tri);
+		uint32_t mine = 0;
 #pragma unroll
-		for (int c = 0; c < SHADE_CHUNK / 32; ++c) {
-			const uint32_t cnt = sCount[c];
-			const int k = c / (WF_BLOCK / 32);
-			if ((uint32_t) (c % (WF_BLOCK / 32)) == warp && ((needMask[k] >> lane) & 1u))
-				sList[run + __popc(needMask[k] & ((1u << lane) - 1u))] = chunk0 + k * WF_BLOCK + threadIdx.x;
-			run += cnt;
+		for (uint32_t bb = 0; bb < SHADE_BINS; ++bb) {
+			const uint32_t m = __ballot_sync(0xFFFFFFFFu, need && bin == bb);
+			if (lane == 0) sCount[bb * (SHADE_CHUNK / 32) + k * (WF_BLOCK / 32) + warp] = __popc(m);
+			if (bin == bb) mine = m;
 		}
-		listed = run;
+		ownMask[k] = need ? mine : 0u; ownBin[k] = bin;
 	}
 	__syncthreads();
+	if (warp == 0) {
+		// exclusive scan of the SHADE_BINS * 32 counts: every lane sums its SHADE_BINS consecutive counts, the lanes scan by shuffles
+		uint32_t c[SHADE_BINS], sum = 0;
+#pragma unroll
+		for (int q = 0; q < SHADE_BINS; ++q) { c[q] = sCount[lane * SHADE_BINS + q]; sum += c[q]; }
+		uint32_t incl = sum;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o); if ((int) lane >= o) incl += v; }
+		uint32_t run = incl - sum;
+#pragma unroll
+		for (int q = 0; q < SHADE_BINS; ++q) { sCount[lane * SHADE_BINS + q] = run; run += c[q]; }
+		if (lane == 31) sListed = incl;
+	}
+	__syncthreads();
+#pragma unroll
+	for (int k = 0; k < SHADE_CHUNK / WF_BLOCK; ++k)
+		if (ownMask[k])
+			sList[sCount[ownBin[k] * (SHADE_CHUNK / 32) + k * (WF_BLOCK / 32) + warp] + __popc(ownMask[k] & ((1u << lane) - 1u))] = chunk0 + k * WF_BLOCK + threadIdx.x;
+	__syncthreads();
+	const uint32_t listed = sListed;
 	for (uint32_t j0 = 0; j0 < listed; j0 += WF_BLOCK) {
 	const bool entry = j0 + threadIdx.x < listed;
 	const uint32_t i = entry ? sList[j0 + threadIdx.x] : 0u;
