@@ -333,7 +333,7 @@ def run_ours(args, rank, local_rank, world):
                                "tris_per_ray": tris_s, "kernel_ms_per_step": ms_s / args.steps, "grays_per_s": acc["shadowRays"] / ms_s * 1e-6 if ms_s > 0 else None},
                     "counter_sample": f"{cspp} spp of the same scene and film through the counter build of the same kernels",
                     "which_vs_40pct_target": "frac is SURVEY §8(d)'s algorithmic figure (bytes a ray's visits would fetch if nothing were cached); the kernel is "
-                                             "bound by instruction issue at partial SIMT occupancy, not by HBM: frac_measured_dram (ncu dram__bytes / duration) is the "
+                                             "bound by instruction issue at partial SIMT occupancy and by the L1 data pipe (ncu: 69 % / 75 %), not by HBM: frac_measured_dram (ncu dram__bytes / duration) is the "
                                              "HBM share actually used, and that is the number to hold against north_star's 40 %"}
 
     # ---- e2e: what one render() of the plugin does, every step: scene upload from host arrays + acceleration-structure
