@@ -131,8 +131,8 @@ int traceRayCounter(mtsgpu_ctx *ctx, uint32_t **out);
 int launchTrace(mtsgpu_ctx *ctx, const float4 *dRays, size_t n, int mode, void *dOut, uint64_t *dCounters);
 int hostThreads();      // api.cu: threads of the host-side copy / flatten loops (MTSGPU_HOST_THREADS)
 int checkTraceFlags(mtsgpu_ctx *ctx);
-int traceRefetchBelow();
-int traceLeafThreshold();
+int traceRefetchBelow(const mtsgpu_ctx *ctx);
+int traceLeafThreshold(const mtsgpu_ctx *ctx);
 // integrate.cu
 int renderDevice(mtsgpu_ctx *ctx, const mtsgpu_render_params *params, volatile const int *cancel,
 	float *dOutFilm, mtsgpu_stats *stats);

@@ -679,7 +679,7 @@ static int launchClosestWf(mtsgpu_ctx *ctx, const float4 *rays, const uint32_t *
 	if (persistent) {
 		uint32_t *rc = nullptr; int e = traceRayCounter(ctx, &rc); if (e) return e;
 		const unsigned blocks = fullGrid(ctx, TRACE_PERSISTENT_BLOCKS_PER_SM);
-		const int rb = traceRefetchBelow(), lt = traceLeafThreshold();
+		const int rb = traceRefetchBelow(ctx), lt = traceLeafThreshold(ctx);
 		unsigned long long *cnt = ctx->countersEnabled ? ctx->dCounters.as<unsigned long long>() + 2 : nullptr;     // [2..3]: closest-hit queues of a render
 #define WFP(S, C) k_closest_wfp<S, C><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, nPtr, hits, rc, rb, lt, cnt)
 		if (ctx->scene.hasSpheres) { if (cnt) WFP(true, true); else WFP(true, false); }
@@ -695,7 +695,7 @@ static int launchShadowWf(mtsgpu_ctx *ctx, const float4 *rays, const float4 *pay
 	if (persistent) {
 		uint32_t *rc = nullptr; int e = traceRayCounter(ctx, &rc); if (e) return e;
 		const unsigned blocks = fullGrid(ctx, TRACE_PERSISTENT_BLOCKS_PER_SM);
-		const int rb = traceRefetchBelow(), lt = traceLeafThreshold();
+		const int rb = traceRefetchBelow(ctx), lt = traceLeafThreshold(ctx);
 		unsigned long long *cnt = ctx->countersEnabled ? ctx->dCounters.as<unsigned long long>() + 4 : nullptr;     // [4..5]: shadow queues of a render
 #define WFP(S, C) k_shadow_wfp<S, C><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, rays, payload, nPtr, li, rc, rb, lt, cnt)
 		if (ctx->scene.hasSpheres) { if (cnt) WFP(true, true); else WFP(true, false); }

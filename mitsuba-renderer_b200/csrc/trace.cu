@@ -63,14 +63,17 @@ unsigned tracePersistentBlocks(mtsgpu_ctx *ctx, size_t n) {
 	return (unsigned) std::max<size_t>(1, std::min(full, want));
 }
 
-// Thresholds of the persistent traversal (trace.cuh); the MTSGPU_* variables are experiment switches.
-int traceRefetchBelow() {
-	static const int v = getenv("MTSGPU_REFETCH_BELOW") ? atoi(getenv("MTSGPU_REFETCH_BELOW")) : TRACE_REFETCH_BELOW;
-	return v;
+// Thresholds of the persistent traversal (trace.cuh); the MTSGPU_* variables are experiment switches. Trees of a few levels
+// (the 36-triangle Cornell box: rays finish after two or three steps) run faster with the late pair, refetch below 12 lanes
+// and leaf phase at 16 parked leaves: C1 26.5 -> 23.6 ms; everything deeper keeps 28 / 6, tuned on the 1M and 10M scenes.
+#define TRACE_TINY_TREE_DEPTH 3
+int traceRefetchBelow(const mtsgpu_ctx *ctx) {
+	static const int v = getenv("MTSGPU_REFETCH_BELOW") ? atoi(getenv("MTSGPU_REFETCH_BELOW")) : -1;
+	return v >= 0 ? v : (ctx->accel.depth <= TRACE_TINY_TREE_DEPTH ? 12 : TRACE_REFETCH_BELOW);
 }
-int traceLeafThreshold() {
-	static const int v = getenv("MTSGPU_LEAF_THRESHOLD") ? atoi(getenv("MTSGPU_LEAF_THRESHOLD")) : TRACE_LEAF_THRESHOLD;
-	return v;
+int traceLeafThreshold(const mtsgpu_ctx *ctx) {
+	static const int v = getenv("MTSGPU_LEAF_THRESHOLD") ? atoi(getenv("MTSGPU_LEAF_THRESHOLD")) : -1;
+	return v >= 0 ? v : (ctx->accel.depth <= TRACE_TINY_TREE_DEPTH ? 16 : TRACE_LEAF_THRESHOLD);
 }
 
 // A zeroed ray counter for the next persistent launch: a ring of counters so that consecutive launches on
@@ -110,7 +113,7 @@ int launchTrace(mtsgpu_ctx *ctx, const float4 *dRays, size_t n, int mode, void *
 	unsigned long long *cnt = reinterpret_cast<unsigned long long *>(dCounters);
 	uint32_t *rayCounter = nullptr;
 	{ int rc = traceRayCounter(ctx, &rayCounter); if (rc) return rc; }
-	const int rb = traceRefetchBelow(), lt = traceLeafThreshold();
+	const int rb = traceRefetchBelow(ctx), lt = traceLeafThreshold(ctx);
 	static const int spec = getenv("MTSGPU_SPECULATE") ? atoi(getenv("MTSGPU_SPECULATE")) : 1;
 	const bool sph = ctx->scene.hasSpheres != 0;
 #define LAUNCH(K, C, S, OUT_T) K<C, S><<<blocks, TRACE_BLOCK, 0, ctx->stream>>>(ctx->scene, dRays, (uint32_t) n, (OUT_T *) dOut, rayCounter, (C) ? cnt : nullptr, rb, spec, lt)
