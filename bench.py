@@ -308,6 +308,7 @@ def run_ours(args, rank, local_rank, world):
         cspp = max(1, min(4, hi - lo))
         ctx.set_counters(True)
         cst = ctx.render_device(api.Context.params_from_scene(scene, lo, lo + cspp, seed=1), film.data_ptr())
+        max_stack = ctx.counters()["maxStackEntries"]
         ctx.set_counters(False)
         peak, peak_src = measured_peaks()
         n_c, n_s = max(cst["normalRays"], 1), max(cst["shadowRays"], 1)
@@ -332,6 +333,7 @@ def run_ours(args, rank, local_rank, world):
                     "shadow": {"kernel": "k_shadow_wfp", "achieved": ach_s, "frac": ach_s / peak, "bytes_per_ray": bpr_s, "nodes_per_ray": nodes_s,
                                "tris_per_ray": tris_s, "kernel_ms_per_step": ms_s / args.steps, "grays_per_s": acc["shadowRays"] / ms_s * 1e-6 if ms_s > 0 else None},
                     "counter_sample": f"{cspp} spp of the same scene and film through the counter build of the same kernels",
+                    "max_stack_entries": max_stack, "stack_limit": 96,
                     "which_vs_40pct_target": "frac is SURVEY §8(d)'s algorithmic figure (bytes a ray's visits would fetch if nothing were cached); the kernel is "
                                              "bound by instruction issue at partial SIMT occupancy and by the L1 data pipe (ncu: 69 % / 75 %), not by HBM: frac_measured_dram (ncu dram__bytes / duration) is the "
                                              "HBM share actually used, and that is the number to hold against north_star's 40 %"}

@@ -499,6 +499,8 @@ MTSGPU_API int mtsgpu_accel_info_get(mtsgpu_ctx *ctx, mtsgpu_accel_info *info);
  * so the timed kernels carry no counter code. */
 typedef struct mtsgpu_trace_counters {
 	uint64_t rays, nodeVisits, triTests;
+	uint64_t maxStackEntries;   /* deepest traversal stack any ray reached since counters were switched on (trace calls and
+	                             * renders; the limit is 96 entries, past which calls fail with MTSGPU_ERR_LIMIT) */
 } mtsgpu_trace_counters;
 MTSGPU_API int mtsgpu_set_counters(mtsgpu_ctx *ctx, int enabled);
 MTSGPU_API int mtsgpu_get_counters(mtsgpu_ctx *ctx, mtsgpu_trace_counters *out);

@@ -84,7 +84,7 @@ class AccelInfo(C.Structure):
 
 
 class TraceCounters(C.Structure):
-    _fields_ = [("rays", C.c_uint64), ("nodeVisits", C.c_uint64), ("triTests", C.c_uint64)]
+    _fields_ = [("rays", C.c_uint64), ("nodeVisits", C.c_uint64), ("triTests", C.c_uint64), ("maxStackEntries", C.c_uint64)]
 
 
 HIT_DTYPE = np.dtype([("t", np.float32), ("u", np.float32), ("v", np.float32), ("shape", np.uint32), ("prim", np.uint32)])

@@ -537,12 +537,23 @@ int mtsgpu_get_triaccel(mtsgpu_ctx *ctx, void *outRecords, size_t maxRecords, fl
 	return MTSGPU_OK;
 }
 
-int mtsgpu_set_counters(mtsgpu_ctx *ctx, int enabled) { ENTER(ctx); ctx->countersEnabled = enabled != 0; return MTSGPU_OK; }
+int mtsgpu_set_counters(mtsgpu_ctx *ctx, int enabled) {
+	ENTER(ctx);
+	if (enabled && !ctx->countersEnabled && ctx->dTraceFlags.p)      // word 1 of the flag buffer: deepest stack seen by the counter builds
+		CUDA_TRY(ctx, cudaMemset((char *) ctx->dTraceFlags.p + 4, 0, 4));
+	ctx->countersEnabled = enabled != 0;
+	return MTSGPU_OK;
+}
 
 int mtsgpu_get_counters(mtsgpu_ctx *ctx, mtsgpu_trace_counters *out) {
 	ENTER(ctx);
 	REQUIRE(ctx, out, MTSGPU_ERR_ARG, "get_counters: null argument");
 	*out = ctx->lastCounters;
+	if (ctx->dTraceFlags.p) {
+		uint32_t deepest = 0;
+		CUDA_TRY(ctx, cudaMemcpy(&deepest, (const char *) ctx->dTraceFlags.p + 4, 4, cudaMemcpyDeviceToHost));
+		out->maxStackEntries = deepest;
+	}
 	return MTSGPU_OK;
 }
 

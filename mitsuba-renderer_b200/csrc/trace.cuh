@@ -348,6 +348,7 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 	uint2 lstack[TRACE_LOCAL_STACK];
 	const uint32_t sbase = (uint32_t) __cvta_generic_to_shared(sstack) + threadIdx.x * 8u;
 	int sp = 0;
+	uint32_t deepest = 0;
 	const float idx = safeRcp(r.dx), idy = safeRcp(r.dy), idz = safeRcp(r.dz);
 	const float oix = r.ox * idx, oiy = r.oy * idy, oiz = r.oz * idz;
 	bool found = false;
@@ -381,6 +382,7 @@ __device__ __forceinline__ bool traverse(const DeviceScene &sc, const RayIn &r, 
 						}
 					}
 				}
+				if (COUNT && (uint32_t) sp > deepest) { deepest = (uint32_t) sp; atomicMax(sc.traceFlags + 1, deepest); }      // counter builds: deepest stack seen
 				if (tn[0] != INFINITY) { cur = cw[0]; continue; }
 			}
 		} else {
@@ -456,6 +458,7 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 	uint32_t poolNext = 0, poolEnd = 0;            // warp-uniform
 	bool exhausted = false;                        // this lane drew an index >= n
 	const uint32_t sbase = (uint32_t) __cvta_generic_to_shared(sstack) + threadIdx.x * 8u;
+	uint32_t deepest = 0;
 	LaneState s;
 	s.active = false; s.sp = 0; s.cur = BVH_EMPTY; s.leaf = BVH_EMPTY; s.found = false;
 
@@ -545,6 +548,7 @@ __device__ __forceinline__ void tracePersistent(const DeviceScene &sc, const flo
 								if (tn[i] != INFINITY) STACK_PUSH(make_uint2(cw[i], __float_as_uint(tn[i])));
 						}
 					}
+					if (COUNT && (uint32_t) s.sp > deepest) { deepest = (uint32_t) s.sp; atomicMax(sc.traceFlags + 1, deepest); }      // counter builds: deepest stack seen
 					// next node: the nearest child, else the stack. A leaf is parked (one slot) and the walk goes on from the
 					// stack. ONE pop site serves both cases: as two divergent regions the pops were 8.9 % of the issue slots at
 					// ~3 active lanes (profiles/r02_last_c4_64spp_digest.txt); lanes that pop for either reason now share the issue.

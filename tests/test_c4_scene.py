@@ -64,10 +64,15 @@ def test_hit_ids_on_the_10m_triangle_tree(c4):
     parts = {"camera": slice(0, len(cam)), "incoherent": slice(len(cam), len(cam) + len(inc)), "bounce": slice(len(cam) + len(inc), len(rays))}
     for k, sl in parts.items():
         assert 0.02 < hit[sl].mean() <= 1.0, (k, hit[sl].mean())
+    ctx.set_counters(True)              # counter build: deepest traversal stack any of these rays needs (limit: 96 entries)
+    ctx.trace(rays[::8]); ctx.trace(scenes.shadow_segments(rays[::8], scene), TRACE_ANY)
+    deepest = ctx.counters()["maxStackEntries"]
+    ctx.set_counters(False)
+    assert 0 < deepest <= 3 * info["depth"] <= 96, (deepest, info)
     seg = scenes.shadow_segments(rays, scene)
     assert np.array_equal(sess.trace(seg, "any", threads)[0], ctx.trace(seg, TRACE_ANY))
     print(f"C4 tree: {len(rays)} rays, hit rates { {k: round(float(hit[sl].mean()), 3) for k, sl in parts.items()} }, exact-t ties {ties}, "
-          f"wide-tree depth {info['depth']}, kd build {rinfo['kd_build_s']:.1f} s")
+          f"wide-tree depth {info['depth']}, deepest stack {deepest} entries, kd build {rinfo['kd_build_s']:.1f} s")
 
 
 def test_halton_render_on_the_c4_scene(c4):
