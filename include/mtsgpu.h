@@ -347,7 +347,9 @@ MTSGPU_API int mtsgpu_render_device(mtsgpu_ctx *ctx, const mtsgpu_render_params 
  * single kernel that loads the peers' buffers over NVLink peer mappings, and copied to outFilm (host). Replaces the
  * distribution of work units to local/remote workers and the mutex-guarded merge of their results
  * (BlockedRenderProcess, src/librender/renderproc.cpp:106-160; RemoteWorker, src/libcore/sched_remote.cpp).
- * stats: counters summed, times = max over GPUs (+ the reduce). */
+ * stats: counters summed, times = max over GPUs (+ the reduce). A progress callback set on ctxs[0] (mtsgpu_set_progress) is
+ * called on the CALLING thread as in mtsgpu_render, with the fraction of ctxs[0]'s share enqueued and film = NULL (partial
+ * films stay on their GPUs); the other contexts' callbacks are not used. */
 MTSGPU_API int mtsgpu_render_multi(mtsgpu_ctx **ctxs, int nCtx, const mtsgpu_render_params *params,
 	volatile const int *cancel, float *outFilm, mtsgpu_stats *stats);
 

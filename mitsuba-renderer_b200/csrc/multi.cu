@@ -5,6 +5,8 @@
 // Replaces the work-unit distribution over workers and the mutex-guarded merge of
 // BlockedRenderProcess::processResult (src/librender/renderproc.cpp:106-160, 123-130).
 #include "context.h"
+#include <atomic>
+#include <chrono>
 #include <thread>
 #include <vector>
 #include <cstring>
@@ -14,6 +16,12 @@
 namespace {
 
 struct FilmPtrs { const float *p[MULTI_MAX_GPUS]; int n; };
+
+// Progress of the first context's render, handed from its worker thread to the thread that called mtsgpu_render_multi: the
+// callback contract (mtsgpu.h) is "called on the calling thread" — Mitsuba's ProgressReporter and RenderQueue want a registered
+// Thread, which a worker spawned here is not.
+struct ProgressRelay { std::atomic<double> fraction { 0.0 }; };
+void relayProgress(void *user, double fraction, const float *) { static_cast<ProgressRelay *>(user)->fraction.store(fraction); }
 
 // out[i] = sum over GPUs of film_g[i]; film_0 is local, the others are peer-mapped (loads cross NVLink).
 // 128-bit loads; grid sized to cover the SMs a few times (grid-stride).
@@ -58,8 +66,15 @@ extern "C" int mtsgpu_render_multi(mtsgpu_ctx **ctxs, int nCtx, const mtsgpu_ren
 	std::vector<int> rcs(nCtx, MTSGPU_OK);
 	std::vector<mtsgpu_stats> sts(nCtx);
 	std::vector<std::thread> threads;
+	// the caller's progress callback (set on the first context) is served from THIS thread; the workers only report a fraction
+	const mtsgpu_progress_fn userFn = c0->progressFn; void *const userArg = c0->progressUser;
+	const double userInterval = c0->progressInterval; const bool userWantFilm = c0->progressWantFilm;
+	ProgressRelay relay;
+	std::atomic<int> running { nCtx };
+	if (userFn) { c0->progressFn = relayProgress; c0->progressUser = &relay; c0->progressWantFilm = false; }
 	for (int i = 0; i < nCtx; ++i) {
 		threads.emplace_back([&, i]() {
+			struct Done { std::atomic<int> &r; ~Done() { r.fetch_sub(1); } } done { running };
 			mtsgpu_ctx *c = ctxs[i];
 			mtsgpu_render_params p = *params;
 			p.sppBegin = lo + (uint32_t) ((uint64_t) span * i / nCtx);
@@ -71,7 +86,21 @@ extern "C" int mtsgpu_render_multi(mtsgpu_ctx **ctxs, int nCtx, const mtsgpu_ren
 			rcs[i] = renderDevice(c, &p, cancel, c->dFilm.as<float>(), &sts[i]);
 		});
 	}
+	if (userFn) {
+		double shown = 0.0;
+		auto last = std::chrono::steady_clock::now();
+		while (running.load() > 0) {
+			std::this_thread::sleep_for(std::chrono::milliseconds(5));
+			const double f = relay.fraction.load();
+			const auto now = std::chrono::steady_clock::now();
+			if (f > shown && f < 1.0 && std::chrono::duration<double>(now - last).count() >= userInterval) {
+				userFn(userArg, f, nullptr);      // partial films stay on their GPUs: previews are a single-GPU feature
+				shown = f; last = now;
+			}
+		}
+	}
 	for (auto &t : threads) t.join();
+	if (userFn) { c0->progressFn = userFn; c0->progressUser = userArg; c0->progressWantFilm = userWantFilm; }
 	for (int i = 0; i < nCtx; ++i)
 		if (rcs[i] != MTSGPU_OK) {
 			if (i != 0) c0->error = ctxs[i]->error;
@@ -125,5 +154,6 @@ extern "C" int mtsgpu_render_multi(mtsgpu_ctx **ctxs, int nCtx, const mtsgpu_ren
 		S.totalMs += ms; S.kernelLaunches += nCtx > 1 ? 1 : 0;
 		*stats = S;
 	}
+	if (userFn) userFn(userArg, 1.0, nullptr);
 	return MTSGPU_OK;
 }

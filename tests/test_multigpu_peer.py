@@ -40,6 +40,31 @@ def test_render_multi_equals_single_gpu():
             c.close()
 
 
+def test_render_multi_reports_progress_on_the_calling_thread():
+    """The callback contract of mtsgpu_set_progress holds for the multi-GPU call too: Mitsuba's ProgressReporter and RenderQueue
+    (renderproc.cpp:123-130) must be driven from a registered thread, never from the per-GPU worker threads."""
+    import threading
+    two_gpus()
+    s = scenes.material_test_scene(128, 128, 64, scenefile.MODE_PATH, max_depth=8)
+    ctxs = [api.Context(0), api.Context(1)]
+    try:
+        for c in ctxs:
+            c.upload_scene(s)
+        calls = []
+        ctxs[0].set_progress(lambda fraction, film: calls.append((fraction, film, threading.get_ident())), 0.0, True)
+        p = api.Context.params_from_scene(s, seed=5)
+        multi, _ = api.render_multi(ctxs, p)
+        ctxs[0].set_progress(None)
+        assert calls and calls[-1][0] == 1.0 and all(f is None for _, f, _ in calls)
+        assert {t for _, _, t in calls} == {threading.get_ident()}
+        assert [f for f, _, _ in calls] == sorted(f for f, _, _ in calls)
+        single, _ = ctxs[0].render(p)
+        assert np.allclose(multi, single, rtol=2e-5, atol=2e-5)
+    finally:
+        for c in ctxs:
+            c.close()
+
+
 def test_plugin_with_two_gpus(oracle):
     two_gpus()
     plugin_dir = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "mitsuba-renderer_b200")
