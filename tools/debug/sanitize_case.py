@@ -1,8 +1,9 @@
-"""A small but structurally complete case for compute-sanitizer: a 300-cell terrain with spheres (≈ 200k triangles, so the
-SAH build runs many levels and the traversal kernels use their shared leaf phase and both stack tiers), closest + any-hit
-queries and a short `path` render with roulette, then the instancing / sphere / cylinder scene.
+"""A small but structurally complete case for debugging runs (a bounds-checking build, printf tracing, a memory checker where one
+is available): a 300-cell terrain with spheres (~ 200k triangles, so the SAH build runs many levels and the traversal kernels use
+their shared leaf phase and both stack tiers), closest + any-hit queries and a short `path` render with roulette, then the
+instancing / cylinder / bitmap-texture scenes.
 
-    compute-sanitizer --tool memcheck python tools/debug/sanitize_case.py
+    python tools/debug/sanitize_case.py
 """
 import os
 import sys
