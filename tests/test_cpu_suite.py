@@ -123,6 +123,24 @@ def test_raster_to_camera_reproduces_reference_rays():
     assert np.abs(g["rays"][:, 3] - s.near_clip / d[:, 2]).max() < 1e-6
 
 
+def test_ranks_of_a_node_share_its_cores_for_host_side_copies(monkeypatch):
+    """One process per GPU (torchrun sets OMP_NUM_THREADS=1 for every rank): the host layer gives each rank its share of the
+    cores through MTSGPU_HOST_THREADS before the library is loaded, and leaves an explicit setting alone."""
+    if not os.path.exists(api.LIB_PATH):
+        pytest.skip("library not built")
+    monkeypatch.delenv("MTSGPU_HOST_THREADS", raising=False)
+    monkeypatch.setenv("LOCAL_WORLD_SIZE", "4")
+    api.load_library(api.LIB_PATH)
+    assert os.environ["MTSGPU_HOST_THREADS"] == str(max(1, (os.cpu_count() or 1) // 4))
+    monkeypatch.setenv("MTSGPU_HOST_THREADS", "3")
+    api.load_library(api.LIB_PATH)
+    assert os.environ["MTSGPU_HOST_THREADS"] == "3"
+    monkeypatch.delenv("MTSGPU_HOST_THREADS", raising=False)
+    monkeypatch.setenv("LOCAL_WORLD_SIZE", "1")
+    api.load_library(api.LIB_PATH)
+    assert "MTSGPU_HOST_THREADS" not in os.environ
+
+
 def test_sample_range_sharding_covers_every_sample_once():
     for spp in (1, 7, 64, 1024, 4096):
         for world in (1, 2, 3, 4, 8):
